@@ -1,0 +1,117 @@
+"""ctypes binding of libasdmatch_cuda.so (include/asdmatch.h).
+
+The product path has no CPU fallback: if the library is missing, cannot be loaded, or finds no B200, the
+calls below raise.  Nothing in this package imports oracle/.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libasdmatch_cuda.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("angle", "<f4"), ("octave", "<i4")])
+PROJ_QUERY_DTYPE = np.dtype(
+    [("valid", "u1"), ("blocks", "u1"), ("pad", "<i2"), ("u", "<f4"), ("v", "<f4"), ("r", "<f4"),
+     ("min_level", "<i4"), ("max_level", "<i4"), ("angle", "<f4")])
+assert KP_DTYPE.itemsize == 16 and PROJ_QUERY_DTYPE.itemsize == 28
+
+ASDM_JOB_BOW_KF_KF = 1
+ASDM_JOB_TRIANGULATION = 2
+ASDM_PROJ_RATIO_LEVEL = 0
+ASDM_PROJ_BEST_ONLY = 1
+TH_LOW = 0.5
+TH_HIGH = 1.5
+HISTO_LENGTH = 30
+
+# every symbol include/asdmatch.h declares (tests/test_abi.py checks the .so exports exactly these)
+EXPORTS = [
+    "asdm_create", "asdm_destroy", "asdm_last_error", "asdm_stream", "asdm_synchronize", "asdm_set_stream",
+    "asdm_host_alloc", "asdm_host_free", "asdm_set_option", "asdm_get_stat",
+    "asdm_set_create", "asdm_set_retain", "asdm_set_release", "asdm_set_size", "asdm_set_featvec",
+    "asdm_set_read_desc",
+    "asdm_search_by_bow_kf_f", "asdm_search_by_bow_kf_kf", "asdm_search_for_triangulation",
+    "asdm_search_by_projection", "asdm_search_for_initialization", "asdm_stereo_row_match",
+    "asdm_job_prepare", "asdm_job_run", "asdm_job_fetch", "asdm_job_settle", "asdm_job_out_stride",
+    "asdm_job_device_outputs", "asdm_job_destroy",
+]
+
+
+class Grid(C.Structure):
+    _fields_ = [("min_x", C.c_float), ("min_y", C.c_float), ("max_x", C.c_float), ("max_y", C.c_float),
+                ("inv_w", C.c_float), ("inv_h", C.c_float), ("cols", C.c_int32), ("rows", C.c_int32)]
+
+
+class FeatVec(C.Structure):
+    _fields_ = [("n_nodes", C.c_int32), ("node_ids", C.c_void_p), ("off", C.c_void_p), ("idx", C.c_void_p)]
+
+
+class ProjParams(C.Structure):
+    _fields_ = [("mode", C.c_int32), ("th_accept", C.c_float), ("best_init", C.c_float), ("nnratio", C.c_float),
+                ("check_ori", C.c_int32), ("count_twice", C.c_int32)]
+
+
+class JobDesc(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("n_kf", C.c_int32), ("sets", C.POINTER(C.c_void_p)),
+                ("masks", C.POINTER(C.c_void_p)), ("n_pairs", C.c_int32), ("ia", C.c_void_p), ("ib", C.c_void_p),
+                ("nnratio", C.c_float), ("check_ori", C.c_int32), ("F12", C.c_void_p), ("epipoles", C.c_void_p),
+                ("scale_factors", C.c_void_p), ("level_sigma2", C.c_void_p), ("n_levels", C.c_int32)]
+
+
+class AsdmError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load():
+    """Loads libasdmatch_cuda.so; raises if it was not built (python -c 'import __graft_entry__ as g; g.build()')."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise AsdmError(f"{LIB_PATH} is missing: build it with `make -C {os.path.join(_HERE, 'csrc')}` "
+                        "(there is no CPU fallback for the matcher)")
+    lib = C.CDLL(LIB_PATH)
+    vp, i32, f32 = C.c_void_p, C.c_int32, C.c_float
+    lib.asdm_create.argtypes = [C.c_int, C.POINTER(vp)]
+    lib.asdm_destroy.argtypes = [vp]
+    lib.asdm_last_error.argtypes = [vp]
+    lib.asdm_last_error.restype = C.c_char_p
+    lib.asdm_stream.argtypes = [vp]
+    lib.asdm_stream.restype = vp
+    lib.asdm_synchronize.argtypes = [vp]
+    lib.asdm_set_stream.argtypes = [vp, vp]
+    lib.asdm_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
+    lib.asdm_host_free.argtypes = [vp]
+    lib.asdm_set_option.argtypes = [vp, C.c_char_p, C.c_int]
+    lib.asdm_get_stat.argtypes = [vp, C.c_char_p, C.POINTER(C.c_int64)]
+    lib.asdm_set_create.argtypes = [vp, vp, C.c_int, C.c_int, vp, C.POINTER(Grid), C.POINTER(vp)]
+    lib.asdm_set_retain.argtypes = [vp]
+    lib.asdm_set_release.argtypes = [vp]
+    lib.asdm_set_size.argtypes = [vp]
+    lib.asdm_set_featvec.argtypes = [vp, C.POINTER(FeatVec)]
+    lib.asdm_set_read_desc.argtypes = [vp, C.c_int, C.c_int, vp]
+    lib.asdm_search_by_bow_kf_f.argtypes = [vp, vp, vp, vp, f32, C.c_int, vp, vp, C.POINTER(i32)]
+    lib.asdm_search_by_bow_kf_kf.argtypes = [vp, vp, vp, vp, vp, f32, C.c_int, vp, vp, C.POINTER(i32)]
+    lib.asdm_search_for_triangulation.argtypes = [vp, vp, vp, vp, vp, vp, f32, f32, vp, vp, C.c_int, C.c_int, vp, vp,
+                                                  C.POINTER(i32)]
+    lib.asdm_search_by_projection.argtypes = [vp, vp, vp, C.c_int, vp, vp, vp, vp, C.POINTER(ProjParams), vp, vp,
+                                              C.POINTER(i32)]
+    lib.asdm_search_for_initialization.argtypes = [vp, vp, vp, vp, C.c_int, f32, C.c_int, vp, vp, C.POINTER(i32)]
+    lib.asdm_stereo_row_match.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, f32, f32, vp, vp]
+    lib.asdm_job_prepare.argtypes = [vp, C.POINTER(JobDesc), C.POINTER(vp)]
+    lib.asdm_job_run.argtypes = [vp]
+    lib.asdm_job_fetch.argtypes = [vp, vp, vp, vp]
+    lib.asdm_job_settle.argtypes = [vp]
+    lib.asdm_job_out_stride.argtypes = [vp]
+    lib.asdm_job_device_outputs.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
+    lib.asdm_job_destroy.argtypes = [vp]
+    _lib = lib
+    return lib
+
+
+def ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)

@@ -1,0 +1,952 @@
+// asdmatch.cu -- C ABI of libasdmatch_cuda.so (include/asdmatch.h). Host-side orchestration only: every
+// distance, selection, ratio test and histogram runs in the sm_100a kernels of kernels_*.cuh / tc_shortlist.cu.
+// There is no CPU fallback: without a CUDA device asdm_create fails.
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+
+#include "internal.cuh"
+#include "kernels_dense.cuh"
+#include "kernels_proj.cuh"
+#include "kernels_set.cuh"
+
+// ------------------------------------------------------------------------------------------------ utilities
+static int fail(asdm_ctx* ctx, int code, const char* what, cudaError_t e = cudaSuccess) {
+  if (ctx) {
+    char buf[512];
+    if (e != cudaSuccess)
+      snprintf(buf, sizeof buf, "%s: %s", what, cudaGetErrorString(e));
+    else
+      snprintf(buf, sizeof buf, "%s", what);
+    ctx->err = buf;
+  }
+  if (e != cudaSuccess) cudaGetLastError();  // clear the sticky-less error state
+  return code;
+}
+
+#define CK(call)                                                        \
+  do {                                                                  \
+    cudaError_t e__ = (call);                                           \
+    if (e__ != cudaSuccess) return fail(ctx, e__ == cudaErrorMemoryAllocation ? ASDM_ERR_OOM : ASDM_ERR_CUDA, #call, e__); \
+  } while (0)
+
+#define LAUNCHED(ctx)           \
+  do {                          \
+    (ctx)->stat_launches++;     \
+    (ctx)->stat_total_launches++; \
+  } while (0)
+
+static int ensure(asdm_ctx* ctx, DevBuf& b, size_t bytes) {
+  if (bytes <= b.cap) return ASDM_OK;
+  if (b.p) {
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaFree(b.p));
+    b.p = nullptr;
+    b.cap = 0;
+  }
+  size_t want = std::max(bytes, (size_t)4096);
+  want = (want + 255) & ~(size_t)255;
+  CK(cudaMalloc(&b.p, want));
+  b.cap = want;
+  return ASDM_OK;
+}
+
+static void release(DevBuf& b) {
+  if (b.p) cudaFree(b.p);
+  b.p = nullptr;
+  b.cap = 0;
+}
+
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// Smallest keep threshold t such that a candidate farther than t can neither be accepted (d > TH_LOW) nor make
+// the ratio test fail as second best: for every fp32 d > t, fl(nnratio*d) > th_accept >= best1.
+static float bow_keep_threshold(float nnratio, float th_accept) {
+  if (!(nnratio > 0.f)) return ASDM_BEST_INIT_BOW;
+  float t = th_accept / nnratio;
+  if (!(t < ASDM_BEST_INIT_BOW)) return ASDM_BEST_INIT_BOW;
+  for (int it = 0; it < 64 && !(nnratio * t > th_accept); it++) t = nextafterf(t, INFINITY);
+  t = nextafterf(nextafterf(t, INFINITY), INFINITY);
+  return std::min(std::max(t, th_accept), ASDM_BEST_INIT_BOW);
+}
+
+// ------------------------------------------------------------------------------------------------- context
+extern "C" int asdm_create(int device, asdm_ctx** out) {
+  if (!out) return ASDM_ERR_INVALID;
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev <= 0 || device < 0 || device >= ndev) {
+    cudaGetLastError();
+    return ASDM_ERR_CUDA;  // no device: there is no CPU path behind this library
+  }
+  asdm_ctx* ctx = new (std::nothrow) asdm_ctx();
+  if (!ctx) return ASDM_ERR_OOM;
+  ctx->device = device;
+  if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    cudaGetLastError();
+    delete ctx;
+    return ASDM_ERR_CUDA;
+  }
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) {
+    ctx->sm_count = prop.multiProcessorCount;
+    if (prop.major != 10) {
+      cudaStreamDestroy(ctx->stream);
+      delete ctx;
+      return ASDM_ERR_CUDA;  // kernels are built for sm_100a only
+    }
+  }
+  cudaFuncSetAttribute(k_cand_exact, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                       (int)(ASDM_DESC_DIM * (CE_TM + CE_TN) * sizeof(float)));
+  *out = ctx;
+  return ASDM_OK;
+}
+
+extern "C" int asdm_destroy(asdm_ctx* ctx) {
+  if (!ctx) return ASDM_ERR_INVALID;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  for (auto& b : ctx->scratch) release(b);
+  if (ctx->h_pin) cudaFreeHost(ctx->h_pin);
+  if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+  return ASDM_OK;
+}
+
+extern "C" const char* asdm_last_error(const asdm_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+extern "C" void* asdm_stream(asdm_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+extern "C" int asdm_set_stream(asdm_ctx* ctx, void* stream) {
+  if (!ctx) return ASDM_ERR_INVALID;
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+  ctx->stream = (cudaStream_t)stream;
+  ctx->own_stream = false;
+  return ASDM_OK;
+}
+
+extern "C" int asdm_synchronize(asdm_ctx* ctx) {
+  if (!ctx) return ASDM_ERR_INVALID;
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return ASDM_OK;
+}
+
+extern "C" int asdm_set_option(asdm_ctx* ctx, const char* key, int value) {
+  if (!ctx || !key) return ASDM_ERR_INVALID;
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  if (!strcmp(key, "force_exact")) ctx->opt_force_exact = value;
+  else if (!strcmp(key, "cand_cap")) ctx->opt_cand_cap = std::max(1, value);
+  else if (!strcmp(key, "list_cap_per_query")) ctx->opt_list_cap_per_query = std::max(1, value);
+  else return fail(ctx, ASDM_ERR_INVALID, "unknown option");
+  return ASDM_OK;
+}
+
+extern "C" int asdm_get_stat(asdm_ctx* ctx, const char* key, int64_t* value) {
+  if (!ctx || !key || !value) return ASDM_ERR_INVALID;
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  if (!strcmp(key, "gpu_launches")) *value = ctx->stat_launches;
+  else if (!strcmp(key, "total_launches")) *value = ctx->stat_total_launches;
+  else if (!strcmp(key, "cand_cap")) *value = ctx->stat_cand_cap;
+  else if (!strcmp(key, "retries")) *value = ctx->stat_retries;
+  else if (!strcmp(key, "tc_used")) *value = ctx->stat_tc_used;
+  else if (!strcmp(key, "tc_pairs")) *value = ctx->stat_tc_pairs;
+  else if (!strcmp(key, "sm_count")) *value = ctx->sm_count;
+  else return fail(ctx, ASDM_ERR_INVALID, "unknown stat");
+  return ASDM_OK;
+}
+
+extern "C" int asdm_host_alloc(void** out, size_t bytes) {
+  if (!out) return ASDM_ERR_INVALID;
+  if (cudaHostAlloc(out, bytes, cudaHostAllocDefault) != cudaSuccess) {
+    cudaGetLastError();
+    return ASDM_ERR_OOM;
+  }
+  return ASDM_OK;
+}
+extern "C" int asdm_host_free(void* p) {
+  if (p && cudaFreeHost(p) != cudaSuccess) {
+    cudaGetLastError();
+    return ASDM_ERR_CUDA;
+  }
+  return ASDM_OK;
+}
+
+static int pin_reserve(asdm_ctx* ctx, size_t bytes) {
+  if (bytes <= ctx->h_pin_cap) return ASDM_OK;
+  if (ctx->h_pin) {
+    CK(cudaStreamSynchronize(ctx->stream));
+    cudaFreeHost(ctx->h_pin);
+    ctx->h_pin = nullptr;
+    ctx->h_pin_cap = 0;
+  }
+  size_t want = align_up(std::max(bytes, (size_t)1 << 16), 4096);
+  CK(cudaHostAlloc(&ctx->h_pin, want, cudaHostAllocDefault));
+  ctx->h_pin_cap = want;
+  return ASDM_OK;
+}
+
+// --------------------------------------------------------------------------------------- descriptor sets
+static void set_free(asdm_set* s) {
+  if (!s) return;
+  cudaSetDevice(s->ctx->device);
+  if (s->desc) cudaFree(s->desc);  // one arena: every other device pointer lives inside it
+  if (s->node_id) cudaFree(s->node_id);
+  delete s;
+}
+
+extern "C" int asdm_set_create(asdm_ctx* ctx, const float* desc, int n, int row_stride_bytes, const asdm_kp* kps,
+                               const asdm_grid* grid, asdm_set** out) {
+  if (!ctx || !out || n < 0 || (n > 0 && !desc)) return ASDM_ERR_INVALID;
+  *out = nullptr;
+  if (row_stride_bytes == 0) row_stride_bytes = ASDM_DESC_DIM * sizeof(float);
+  if (row_stride_bytes < (int)(ASDM_DESC_DIM * sizeof(float))) return fail(ctx, ASDM_ERR_INVALID, "row stride < 512 B");
+  if (grid && (!kps || grid->cols <= 0 || grid->rows <= 0 || (int64_t)grid->cols * grid->rows > (1 << 20)))
+    return fail(ctx, ASDM_ERR_INVALID, "bad grid");
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  CK(cudaSetDevice(ctx->device));
+  asdm_set* s = new (std::nothrow) asdm_set();
+  if (!s) return fail(ctx, ASDM_ERR_OOM, "host allocation");
+  s->ctx = ctx;
+  s->n = n;
+  s->n_pad = (int)align_up((size_t)std::max(n, 1), 256);
+  const int nc = grid ? grid->cols * grid->rows : 0;
+  // one arena per set
+  size_t off = 0;
+  const size_t o_desc = off; off += align_up((size_t)s->n_pad * ASDM_DESC_DIM * sizeof(float), 1024);
+  const size_t o_bf = off;   off += align_up((size_t)s->n_pad * ASDM_DESC_DIM * sizeof(__nv_bfloat16), 1024);
+  const size_t o_norm = off; off += align_up((size_t)s->n_pad * sizeof(float), 256);
+  const size_t o_flags = off; off += 256;
+  const size_t o_kps = off;  off += kps ? align_up((size_t)s->n_pad * sizeof(asdm_kp), 256) : 0;
+  const size_t o_cs = off;   off += grid ? align_up((size_t)(nc + 1) * sizeof(int32_t), 256) : 0;
+  const size_t o_ci = off;   off += grid ? align_up((size_t)s->n_pad * sizeof(int32_t), 256) : 0;
+  const size_t o_tmp = off;  off += grid ? align_up((size_t)s->n_pad * sizeof(int32_t), 256) : 0;
+  char* base = nullptr;
+  cudaError_t e = cudaMalloc(&base, off);
+  if (e != cudaSuccess) {
+    delete s;
+    return fail(ctx, ASDM_ERR_OOM, "cudaMalloc(set)", e);
+  }
+  s->desc = (float*)(base + o_desc);
+  s->desc_bf = (__nv_bfloat16*)(base + o_bf);
+  s->norm2 = (float*)(base + o_norm);
+  s->d_flags = (int32_t*)(base + o_flags);
+  int rc = ASDM_OK;
+  auto bail = [&](int code) {
+    set_free(s);
+    return code;
+  };
+#define CKS(call)                                              \
+  do {                                                         \
+    cudaError_t e__ = (call);                                  \
+    if (e__ != cudaSuccess) return bail(fail(ctx, ASDM_ERR_CUDA, #call, e__)); \
+  } while (0)
+  CKS(cudaMemsetAsync(s->d_flags, 0, 256, ctx->stream));
+  if (n > 0) {
+    if (row_stride_bytes == (int)(ASDM_DESC_DIM * sizeof(float)))
+      CKS(cudaMemcpyAsync(s->desc, desc, (size_t)n * ASDM_DESC_DIM * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    else
+      CKS(cudaMemcpy2DAsync(s->desc, ASDM_DESC_DIM * sizeof(float), desc, row_stride_bytes,
+                            ASDM_DESC_DIM * sizeof(float), n, cudaMemcpyHostToDevice, ctx->stream));
+  }
+  if (s->n_pad > n)
+    CKS(cudaMemsetAsync(s->desc + (size_t)n * ASDM_DESC_DIM, 0, (size_t)(s->n_pad - n) * ASDM_DESC_DIM * sizeof(float),
+                        ctx->stream));
+  ctx->stat_launches = 0;
+  k_pack_desc<<<(s->n_pad * 32 + 255) / 256, 256, 0, ctx->stream>>>(s->desc, n, s->n_pad, s->desc_bf, s->norm2, s->d_flags);
+  LAUNCHED(ctx);
+  if (kps) {
+    s->kps = (asdm_kp*)(base + o_kps);
+    s->has_kps = true;
+    if (n > 0) CKS(cudaMemcpyAsync(s->kps, kps, (size_t)n * sizeof(asdm_kp), cudaMemcpyHostToDevice, ctx->stream));
+  }
+  if (grid) {
+    s->grid = *grid;
+    s->has_grid = true;
+    s->cell_start = (int32_t*)(base + o_cs);
+    s->cell_items = (int32_t*)(base + o_ci);
+    const size_t smem = (size_t)(nc + 1) * sizeof(int32_t);
+    if (smem > 48 * 1024) cudaFuncSetAttribute(k_build_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_build_grid<<<1, 1024, smem, ctx->stream>>>(s->kps, n, *grid, (int32_t*)(base + o_tmp), s->cell_start, s->cell_items);
+    LAUNCHED(ctx);
+  }
+  CKS(cudaGetLastError());
+  // the caller's host buffers may be reused as soon as we return
+  CKS(cudaStreamSynchronize(ctx->stream));
+#undef CKS
+  (void)rc;
+  *out = s;
+  return ASDM_OK;
+}
+
+extern "C" int asdm_set_retain(asdm_set* s) {
+  if (!s) return ASDM_ERR_INVALID;
+  s->ref.fetch_add(1);
+  return ASDM_OK;
+}
+
+extern "C" int asdm_set_release(asdm_set* s) {
+  if (!s) return ASDM_ERR_INVALID;
+  if (s->ref.fetch_sub(1) == 1) {
+    asdm_ctx* ctx = s->ctx;
+    std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    set_free(s);
+  }
+  return ASDM_OK;
+}
+
+extern "C" int asdm_set_size(const asdm_set* s) { return s ? s->n : ASDM_ERR_INVALID; }
+
+extern "C" int asdm_set_featvec(asdm_set* s, const asdm_featvec* fv) {
+  if (!s || !fv || fv->n_nodes < 0) return ASDM_ERR_INVALID;
+  asdm_ctx* ctx = s->ctx;
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  CK(cudaSetDevice(ctx->device));
+  // per-feature node id and scan position: the flattening of DBoW2::FeatureVector the kernels gate on
+  std::vector<uint32_t> node((size_t)s->n_pad, 0u);
+  std::vector<int32_t> pos((size_t)s->n_pad, -1);
+  for (int k = 0; k < fv->n_nodes; k++) {
+    if (k > 0 && !(fv->node_ids[k] > fv->node_ids[k - 1])) return fail(ctx, ASDM_ERR_INVALID, "node ids not ascending");
+    for (int e = fv->off[k]; e < fv->off[k + 1]; e++) {
+      const int i = fv->idx[e];
+      if (i < 0 || i >= s->n) return fail(ctx, ASDM_ERR_INVALID, "feature index out of range");
+      if (pos[i] >= 0) return fail(ctx, ASDM_ERR_INVALID, "feature listed twice in the FeatureVector");
+      node[i] = fv->node_ids[k];
+      pos[i] = e;
+    }
+  }
+  if (!s->node_id) {
+    void* p = nullptr;
+    CK(cudaMalloc(&p, (size_t)s->n_pad * 8));
+    s->node_id = (uint32_t*)p;
+    s->fv_pos = (int32_t*)((char*)p + (size_t)s->n_pad * 4);
+  }
+  CK(cudaMemcpyAsync(s->node_id, node.data(), (size_t)s->n_pad * 4, cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemcpyAsync(s->fv_pos, pos.data(), (size_t)s->n_pad * 4, cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  s->has_fv = true;
+  return ASDM_OK;
+}
+
+extern "C" int asdm_set_read_desc(asdm_set* s, int row0, int n_rows, float* out) {
+  if (!s || !out || row0 < 0 || n_rows < 0 || row0 + n_rows > s->n) return ASDM_ERR_INVALID;
+  asdm_ctx* ctx = s->ctx;
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaMemcpyAsync(out, s->desc + (size_t)row0 * ASDM_DESC_DIM, (size_t)n_rows * ASDM_DESC_DIM * sizeof(float),
+                     cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return ASDM_OK;
+}
+
+// ------------------------------------------------------------------------------- batched keyframe-pair jobs
+struct asdm_job {
+  asdm_ctx* ctx = nullptr;
+  int kind = 0;
+  int n_pairs = 0;
+  int n_stride = 0;    // max nA over pairs (query slots per pair)
+  int m_stride = 0;    // max nB over pairs
+  int out_stride = 0;  // entries per pair in match12 / dist12
+  BowParams P{};
+  std::vector<asdm_set*> sets;  // retained
+  std::vector<PairDesc> h_pairs;
+  DevBuf d_pairs, d_masks, d_cnt, d_cand, d_owner, d_acc, d_flags, d_match, d_dist, d_nm;
+  DevBuf d_work, d_tmaps, d_list, d_list_pair;
+  int cap = 8;
+  int use_tc = 0;
+  int n_work = 0;
+  int list_cap = 0;
+  float t_keep_tc = 0.f;
+  bool ran = false;
+  int32_t* h_flags = nullptr;  // pinned, 8 ints: [0] cand overflow, [1] list overflow, [2] list count
+};
+
+static void job_free(asdm_job* j) {
+  if (!j) return;
+  cudaSetDevice(j->ctx->device);
+  cudaStreamSynchronize(j->ctx->stream);
+  DevBuf* bufs[] = {&j->d_pairs, &j->d_masks, &j->d_cnt, &j->d_cand, &j->d_owner, &j->d_acc, &j->d_flags,
+                    &j->d_match, &j->d_dist, &j->d_nm, &j->d_work, &j->d_tmaps, &j->d_list, &j->d_list_pair};
+  for (DevBuf* b : bufs) release(*b);
+  if (j->h_flags) cudaFreeHost(j->h_flags);
+  for (asdm_set* s : j->sets) asdm_set_release(s);
+  delete j;
+}
+
+static int job_alloc_scratch(asdm_job* j) {
+  asdm_ctx* ctx = j->ctx;
+  const size_t P = (size_t)j->n_pairs;
+  int rc;
+  if ((rc = ensure(ctx, j->d_cnt, P * j->n_stride * sizeof(int32_t)))) return rc;
+  if ((rc = ensure(ctx, j->d_cand, P * j->n_stride * (size_t)j->cap * sizeof(Cand)))) return rc;
+  if ((rc = ensure(ctx, j->d_owner, P * 2 * j->m_stride * sizeof(int32_t)))) return rc;
+  if ((rc = ensure(ctx, j->d_acc, P * j->n_stride * sizeof(int32_t)))) return rc;
+  if ((rc = ensure(ctx, j->d_flags, 64))) return rc;
+  if ((rc = ensure(ctx, j->d_match, P * j->out_stride * sizeof(int32_t)))) return rc;
+  if ((rc = ensure(ctx, j->d_dist, P * j->out_stride * sizeof(float)))) return rc;
+  if ((rc = ensure(ctx, j->d_nm, P * sizeof(int32_t)))) return rc;
+  if (j->use_tc) {
+    if ((rc = ensure(ctx, j->d_list, (size_t)j->list_cap * sizeof(TcPair)))) return rc;
+    if ((rc = ensure(ctx, j->d_list_pair, (size_t)j->list_cap * sizeof(int32_t)))) return rc;
+  }
+  return ASDM_OK;
+}
+
+static int job_prepare(asdm_ctx* ctx, const asdm_job_desc* d, int kind_internal, asdm_job** out) {
+  if (!ctx || !d || !out) return ASDM_ERR_INVALID;
+  *out = nullptr;
+  if (d->n_kf <= 0 || d->n_pairs < 0 || !d->sets || !d->masks || (d->n_pairs > 0 && (!d->ia || !d->ib)))
+    return fail(ctx, ASDM_ERR_INVALID, "bad job description");
+  if (kind_internal == KIND_TRIANGULATION &&
+      (!d->F12 || !d->epipoles || !d->scale_factors || !d->level_sigma2 || d->n_levels <= 0 || d->n_levels > ASDM_MAX_LEVELS))
+    return fail(ctx, ASDM_ERR_INVALID, "triangulation job needs F12, epipoles and level tables");
+  for (int k = 0; k < d->n_kf; k++) {
+    const asdm_set* s = d->sets[k];
+    if (!s || s->ctx != ctx || !d->masks[k]) return fail(ctx, ASDM_ERR_INVALID, "bad keyframe set / mask");
+    if (!s->has_fv) return fail(ctx, ASDM_ERR_INVALID, "keyframe set has no FeatureVector (asdm_set_featvec)");
+    if (!s->has_kps) return fail(ctx, ASDM_ERR_INVALID, "keyframe set has no keypoints");
+  }
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  CK(cudaSetDevice(ctx->device));
+  asdm_job* j = new (std::nothrow) asdm_job();
+  if (!j) return fail(ctx, ASDM_ERR_OOM, "host allocation");
+  j->ctx = ctx;
+  j->kind = kind_internal;
+  j->n_pairs = d->n_pairs;
+  auto bail = [&](int code) {
+    job_free(j);
+    return code;
+  };
+  for (int k = 0; k < d->n_kf; k++) {
+    asdm_set_retain(d->sets[k]);
+    j->sets.push_back(d->sets[k]);
+  }
+  // masks of all keyframes, packed
+  std::vector<size_t> mask_off(d->n_kf);
+  size_t mtot = 0;
+  for (int k = 0; k < d->n_kf; k++) {
+    mask_off[k] = mtot;
+    mtot += align_up((size_t)std::max(d->sets[k]->n, 1), 16);
+  }
+  int rc;
+  if ((rc = ensure(ctx, j->d_masks, mtot))) return bail(rc);
+  if ((rc = pin_reserve(ctx, mtot))) return bail(rc);
+  for (int k = 0; k < d->n_kf; k++) memcpy((char*)ctx->h_pin + mask_off[k], d->masks[k], (size_t)d->sets[k]->n);
+  if (cudaMemcpyAsync(j->d_masks.p, ctx->h_pin, mtot, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess)
+    return bail(fail(ctx, ASDM_ERR_CUDA, "mask upload"));
+  if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) return bail(fail(ctx, ASDM_ERR_CUDA, "mask upload sync"));
+
+  BowParams& P = j->P;
+  memset(&P, 0, sizeof P);
+  P.kind = kind_internal;
+  P.nnratio = d->nnratio;
+  P.check_ori = d->check_ori ? 1 : 0;
+  P.th_accept = ASDM_TH_LOW;
+  if (kind_internal == KIND_TRIANGULATION) {
+    P.mask_sense = 0;          // usable features are those WITHOUT a map point (ORBmatcher.cc:708-712, :730)
+    P.t_keep = ASDM_TH_LOW;    // :737
+    P.n_levels = d->n_levels;
+    for (int l = 0; l < d->n_levels; l++) {
+      P.scale_factors[l] = d->scale_factors[l];
+      P.level_sigma2[l] = d->level_sigma2[l];
+    }
+  } else {
+    P.mask_sense = 1;
+    P.strict = kind_internal == KIND_BOW_KF_KF ? 1 : 0;  // :609 vs :231
+    P.t_keep = bow_keep_threshold(d->nnratio, ASDM_TH_LOW);
+  }
+
+  j->h_pairs.resize((size_t)d->n_pairs);
+  int all_tc = 1;
+  for (int p = 0; p < d->n_pairs; p++) {
+    const int a = d->ia[p], b = d->ib[p];
+    if (a < 0 || a >= d->n_kf || b < 0 || b >= d->n_kf) return bail(fail(ctx, ASDM_ERR_INVALID, "pair index out of range"));
+    const asdm_set *A = d->sets[a], *B = d->sets[b];
+    PairDesc& pd = j->h_pairs[p];
+    memset(&pd, 0, sizeof pd);
+    pd.descA = A->desc; pd.descB = B->desc;
+    pd.bfA = A->desc_bf; pd.bfB = B->desc_bf;
+    pd.normA = A->norm2; pd.normB = B->norm2;
+    pd.nodeA = A->node_id; pd.nodeB = B->node_id;
+    pd.posA = A->fv_pos; pd.posB = B->fv_pos;
+    pd.maskA = (const uint8_t*)j->d_masks.p + mask_off[a];
+    pd.maskB = (const uint8_t*)j->d_masks.p + mask_off[b];
+    pd.kpA = A->kps; pd.kpB = B->kps;
+    pd.nA = A->n; pd.nB = B->n;
+    pd.setA = a; pd.setB = b;
+    if (kind_internal == KIND_TRIANGULATION) {
+      memcpy(pd.F12, d->F12 + 9 * (size_t)p, 9 * sizeof(float));
+      pd.ex = d->epipoles[2 * p];
+      pd.ey = d->epipoles[2 * p + 1];
+    }
+    j->n_stride = std::max(j->n_stride, A->n);
+    j->m_stride = std::max(j->m_stride, B->n);
+  }
+  j->n_stride = std::max(j->n_stride, 1);
+  j->m_stride = std::max(j->m_stride, 1);
+  j->out_stride = kind_internal == KIND_BOW_KF_F ? j->m_stride : j->n_stride;
+  j->cap = ctx->opt_cand_cap;
+
+  // tensor-core shortlist only when every set passed the range check of k_pack_desc
+  if (!ctx->opt_force_exact && d->n_pairs > 0) {
+    for (int k = 0; k < d->n_kf; k++) {
+      asdm_set* s = d->sets[k];
+      if (s->tc_ok < 0) {
+        int32_t f = 1;
+        if (cudaMemcpyAsync(&f, s->d_flags, sizeof f, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
+            cudaStreamSynchronize(ctx->stream) != cudaSuccess)
+          return bail(fail(ctx, ASDM_ERR_CUDA, "flag readback"));
+        s->tc_ok = f ? 0 : 1;
+      }
+      all_tc &= s->tc_ok;
+    }
+    if (all_tc) {
+      // work units: one resident 256-row B tile x a run of 128-row A tiles; split runs until the grid is full
+      std::vector<TcWork> work;
+      long tiles = 0;
+      for (int p = 0; p < d->n_pairs; p++)
+        tiles += (long)((j->h_pairs[p].nB + 255) / 256) * ((j->h_pairs[p].nA + 127) / 128);
+      const long target_units = (long)ctx->sm_count * 4;
+      int run = (int)std::max<long>(1, std::min<long>(32, tiles / std::max<long>(1, target_units)));
+      for (int p = 0; p < d->n_pairs; p++) {
+        const int nt_n = (j->h_pairs[p].nB + 255) / 256, nt_m = (j->h_pairs[p].nA + 127) / 128;
+        for (int tn = 0; tn < nt_n; tn++)
+          for (int m0 = 0; m0 < nt_m; m0 += run) work.push_back(TcWork{p, tn, m0, std::min(run, nt_m - m0)});
+      }
+      bool maps_ok = true;
+      for (int k = 0; k < d->n_kf && maps_ok; k++) maps_ok = asdm_tc_build_tmap(ctx, d->sets[k]) == ASDM_OK;
+      if (maps_ok && !work.empty()) {
+        j->use_tc = 1;
+        j->n_work = (int)work.size();
+        if ((rc = ensure(ctx, j->d_work, work.size() * sizeof(TcWork)))) return bail(rc);
+        if ((rc = ensure(ctx, j->d_tmaps, (size_t)d->n_kf * 128))) return bail(rc);
+        std::vector<uint8_t> maps((size_t)d->n_kf * 128);
+        for (int k = 0; k < d->n_kf; k++) memcpy(maps.data() + (size_t)k * 128, d->sets[k]->tmap_bf.data(), 128);
+        if (cudaMemcpy(j->d_work.p, work.data(), work.size() * sizeof(TcWork), cudaMemcpyHostToDevice) != cudaSuccess ||
+            cudaMemcpy(j->d_tmaps.p, maps.data(), maps.size(), cudaMemcpyHostToDevice) != cudaSuccess)
+          return bail(fail(ctx, ASDM_ERR_CUDA, "work upload"));
+        long q = 0;
+        for (int p = 0; p < d->n_pairs; p++) q += j->h_pairs[p].nA;
+        j->list_cap = (int)std::min<long>((long)1 << 30, std::max<long>(4096, q * ctx->opt_list_cap_per_query));
+      }
+    }
+  }
+  if ((rc = ensure(ctx, j->d_pairs, std::max<size_t>(1, j->h_pairs.size()) * sizeof(PairDesc)))) return bail(rc);
+  if (!j->h_pairs.empty() &&
+      cudaMemcpy(j->d_pairs.p, j->h_pairs.data(), j->h_pairs.size() * sizeof(PairDesc), cudaMemcpyHostToDevice) != cudaSuccess)
+    return bail(fail(ctx, ASDM_ERR_CUDA, "pair upload"));
+  if ((rc = job_alloc_scratch(j))) return bail(rc);
+  if (cudaHostAlloc((void**)&j->h_flags, 64, cudaHostAllocDefault) != cudaSuccess)
+    return bail(fail(ctx, ASDM_ERR_OOM, "pinned flags"));
+  *out = j;
+  return ASDM_OK;
+}
+
+static int job_run(asdm_job* j) {
+  asdm_ctx* ctx = j->ctx;
+  CK(cudaSetDevice(ctx->device));
+  ctx->stat_launches = 0;
+  ctx->stat_tc_used = j->use_tc;
+  ctx->stat_cand_cap = j->cap;
+  j->ran = true;
+  if (j->n_pairs == 0) return ASDM_OK;
+  const PairDesc* pairs = (const PairDesc*)j->d_pairs.p;
+  int32_t* flags = (int32_t*)j->d_flags.p;
+  CK(cudaMemsetAsync(j->d_cnt.p, 0, (size_t)j->n_pairs * j->n_stride * sizeof(int32_t), ctx->stream));
+  CK(cudaMemsetAsync(flags, 0, 64, ctx->stream));
+  if (j->use_tc) {
+    CK(asdm_tc_shortlist_launch(ctx, pairs, j->d_tmaps.p, (const TcWork*)j->d_work.p, j->n_work, j->P.t_keep,
+                                (TcPair*)j->d_list.p, (int32_t*)j->d_list_pair.p, j->list_cap, flags + 2));
+    LAUNCHED(ctx);
+    const int blocks = ctx->sm_count * 8;
+    k_rerank<<<blocks, 256, 0, ctx->stream>>>(pairs, j->P, j->cap, j->n_stride, (const TcPair*)j->d_list.p,
+                                              (const int32_t*)j->d_list_pair.p, flags + 2, j->list_cap,
+                                              (int32_t*)j->d_cnt.p, (Cand*)j->d_cand.p, flags);
+    LAUNCHED(ctx);
+  } else {
+    dim3 grid((j->n_stride + CE_TM - 1) / CE_TM, (j->m_stride + CE_TN - 1) / CE_TN, j->n_pairs);
+    if (grid.y > 65535 || grid.z > 65535) return fail(ctx, ASDM_ERR_INVALID, "job too large for the exact kernel grid");
+    k_cand_exact<<<grid, 256, ASDM_DESC_DIM * (CE_TM + CE_TN) * sizeof(float), ctx->stream>>>(
+        pairs, j->P, j->cap, j->n_stride, (int32_t*)j->d_cnt.p, (Cand*)j->d_cand.p, flags);
+    LAUNCHED(ctx);
+  }
+  if (j->kind == KIND_TRIANGULATION)
+    k_resolve_tri<<<j->n_pairs, 512, 0, ctx->stream>>>(pairs, j->P, j->cap, j->n_stride, j->out_stride,
+                                                       (const int32_t*)j->d_cnt.p, (const Cand*)j->d_cand.p,
+                                                       (int32_t*)j->d_acc.p, (int32_t*)j->d_match.p,
+                                                       (float*)j->d_dist.p, (int32_t*)j->d_nm.p);
+  else
+    k_resolve_bow<<<j->n_pairs, 512, 0, ctx->stream>>>(pairs, j->P, j->cap, j->n_stride, j->m_stride, j->out_stride,
+                                                       (const int32_t*)j->d_cnt.p, (Cand*)j->d_cand.p,
+                                                       (int32_t*)j->d_owner.p, (int32_t*)j->d_acc.p,
+                                                       (int32_t*)j->d_match.p, (float*)j->d_dist.p,
+                                                       (int32_t*)j->d_nm.p);
+  LAUNCHED(ctx);
+  CK(cudaGetLastError());
+  return ASDM_OK;
+}
+
+// Waits for the run; when a candidate pool overflowed, grows it and runs again (results are only ever taken
+// from a run without overflow).
+static int job_settle(asdm_job* j) {
+  asdm_ctx* ctx = j->ctx;
+  if (!j->ran) {
+    int rc = job_run(j);
+    if (rc) return rc;
+  }
+  ctx->stat_retries = 0;
+  for (int attempt = 0; attempt < 24; attempt++) {
+    CK(cudaMemcpyAsync(j->h_flags, j->d_flags.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    const bool cand_over = j->h_flags[0] != 0, list_over = j->h_flags[1] != 0;
+    ctx->stat_tc_pairs = j->use_tc ? j->h_flags[2] : 0;
+    if (!cand_over && !list_over) return ASDM_OK;
+    ctx->stat_retries++;
+    if (cand_over) j->cap = std::min(std::max(j->cap * 2, 2), std::max(j->m_stride, 2));
+    if (list_over) {
+      const long need = std::max<long>((long)j->h_flags[2] + 1024, (long)j->list_cap * 2);
+      if (need > ((long)1 << 30)) j->use_tc = 0;  // absurdly dense: take the exact kernel
+      else j->list_cap = (int)need;
+    }
+    int rc = job_alloc_scratch(j);
+    if (rc) return rc;
+    if ((rc = job_run(j))) return rc;
+  }
+  return fail(ctx, ASDM_ERR_INTERNAL, "candidate pool kept overflowing");
+}
+
+extern "C" int asdm_job_prepare(asdm_ctx* ctx, const asdm_job_desc* desc, asdm_job** out) {
+  if (!desc) return ASDM_ERR_INVALID;
+  if (desc->kind != ASDM_JOB_BOW_KF_KF && desc->kind != ASDM_JOB_TRIANGULATION)
+    return fail(ctx, ASDM_ERR_INVALID, "unknown job kind");
+  return job_prepare(ctx, desc, desc->kind == ASDM_JOB_BOW_KF_KF ? KIND_BOW_KF_KF : KIND_TRIANGULATION, out);
+}
+
+extern "C" int asdm_job_run(asdm_job* j) {
+  if (!j) return ASDM_ERR_INVALID;
+  std::lock_guard<std::recursive_mutex> lk(j->ctx->mu);
+  return job_run(j);
+}
+
+extern "C" int asdm_job_out_stride(const asdm_job* j) { return j ? j->out_stride : ASDM_ERR_INVALID; }
+
+extern "C" int asdm_job_fetch(asdm_job* j, int32_t* match12, float* dist12, int32_t* nmatches) {
+  if (!j) return ASDM_ERR_INVALID;
+  asdm_ctx* ctx = j->ctx;
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  CK(cudaSetDevice(ctx->device));
+  int rc = job_settle(j);
+  if (rc) return rc;
+  const size_t n = (size_t)j->n_pairs * j->out_stride;
+  if (match12 && n) CK(cudaMemcpyAsync(match12, j->d_match.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  if (dist12 && n) CK(cudaMemcpyAsync(dist12, j->d_dist.p, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+  if (nmatches && j->n_pairs)
+    CK(cudaMemcpyAsync(nmatches, j->d_nm.p, (size_t)j->n_pairs * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return ASDM_OK;
+}
+
+extern "C" int asdm_job_settle(asdm_job* j) {
+  if (!j) return ASDM_ERR_INVALID;
+  std::lock_guard<std::recursive_mutex> lk(j->ctx->mu);
+  return job_settle(j);
+}
+
+extern "C" int asdm_job_device_outputs(asdm_job* j, void** match12, void** dist12, void** nmatches) {
+  if (!j) return ASDM_ERR_INVALID;
+  if (match12) *match12 = j->d_match.p;
+  if (dist12) *dist12 = j->d_dist.p;
+  if (nmatches) *nmatches = j->d_nm.p;
+  return ASDM_OK;
+}
+
+extern "C" int asdm_job_destroy(asdm_job* j) {
+  if (!j) return ASDM_ERR_INVALID;
+  asdm_ctx* ctx = j->ctx;
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  job_free(j);
+  return ASDM_OK;
+}
+
+// ------------------------------------------------------------------- single keyframe-pair entry points
+static int single_pair(asdm_ctx* ctx, int kind, asdm_set* a, const uint8_t* mask_a, asdm_set* b, const uint8_t* mask_b,
+                       float nnratio, int check_ori, const float* F12, float ex, float ey, const float* sf,
+                       const float* ls, int n_levels, int32_t* match, float* dist, int32_t* nmatches) {
+  if (!ctx || !a || !b || !mask_a || !match) return ASDM_ERR_INVALID;
+  std::vector<uint8_t> ones;
+  if (!mask_b) {
+    ones.assign((size_t)std::max(b->n, 1), 1);
+    mask_b = ones.data();
+  }
+  asdm_set* sets[2] = {a, b};
+  const uint8_t* masks[2] = {mask_a, mask_b};
+  const int32_t ia = 0, ib = 1;
+  const float ep[2] = {ex, ey};
+  asdm_job_desc d;
+  memset(&d, 0, sizeof d);
+  d.n_kf = 2;
+  d.sets = sets;
+  d.masks = masks;
+  d.n_pairs = 1;
+  d.ia = &ia;
+  d.ib = &ib;
+  d.nnratio = nnratio;
+  d.check_ori = check_ori;
+  d.F12 = F12;
+  d.epipoles = ep;
+  d.scale_factors = sf;
+  d.level_sigma2 = ls;
+  d.n_levels = n_levels;
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  asdm_job* j = nullptr;
+  int rc = job_prepare(ctx, &d, kind, &j);
+  if (rc) return rc;
+  rc = job_run(j);
+  if (!rc) rc = job_settle(j);
+  const int64_t launches = ctx->stat_launches;
+  if (!rc) {
+    int32_t nm = 0;
+    const size_t n = (size_t)j->out_stride;
+    cudaError_t e = cudaMemcpyAsync(match, j->d_match.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess && dist)
+      e = cudaMemcpyAsync(dist, j->d_dist.p, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&nm, j->d_nm.p, sizeof nm, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) rc = fail(ctx, ASDM_ERR_CUDA, "result download", e);
+    if (nmatches) *nmatches = nm;
+  }
+  job_free(j);
+  ctx->stat_launches = launches;
+  return rc;
+}
+
+extern "C" int asdm_search_by_bow_kf_f(asdm_ctx* ctx, asdm_set* kf, const uint8_t* valid_kf, asdm_set* f, float nnratio,
+                                       int check_ori, int32_t* match_f, float* dist_f, int32_t* nmatches) {
+  return single_pair(ctx, KIND_BOW_KF_F, kf, valid_kf, f, nullptr, nnratio, check_ori, nullptr, 0.f, 0.f, nullptr,
+                     nullptr, 0, match_f, dist_f, nmatches);
+}
+
+extern "C" int asdm_search_by_bow_kf_kf(asdm_ctx* ctx, asdm_set* kf1, const uint8_t* valid1, asdm_set* kf2,
+                                        const uint8_t* valid2, float nnratio, int check_ori, int32_t* match12,
+                                        float* dist12, int32_t* nmatches) {
+  if (!valid2) return ASDM_ERR_INVALID;
+  return single_pair(ctx, KIND_BOW_KF_KF, kf1, valid1, kf2, valid2, nnratio, check_ori, nullptr, 0.f, 0.f, nullptr,
+                     nullptr, 0, match12, dist12, nmatches);
+}
+
+extern "C" int asdm_search_for_triangulation(asdm_ctx* ctx, asdm_set* kf1, const uint8_t* has_mp1, asdm_set* kf2,
+                                             const uint8_t* has_mp2, const float* F12, float ex, float ey,
+                                             const float* scale_factors2, const float* level_sigma2_2, int n_levels,
+                                             int check_ori, int32_t* match12, float* dist12, int32_t* nmatches) {
+  if (!has_mp2 || !F12) return ASDM_ERR_INVALID;
+  return single_pair(ctx, KIND_TRIANGULATION, kf1, has_mp1, kf2, has_mp2, 0.f, check_ori, F12, ex, ey, scale_factors2,
+                     level_sigma2_2, n_levels, match12, dist12, nmatches);
+}
+
+// ------------------------------------------------------------------------- projection-gated entry points
+// scratch slots of the context
+enum { SC_QUERY = 0, SC_QDESC = 1, SC_SEG = 2, SC_ENT = 3, SC_STATE = 4, SC_BLOCK = 5, SC_MISC = 6 };
+
+struct ProjDev {
+  asdm_proj_query* q;
+  ProjSeg* seg;
+  int32_t *ent_j, *ent_q;
+  float* ent_d;
+  int32_t *total, *overflow;
+};
+
+// gather + distance with automatic growth of the entry pool; queries are already on the device
+static int proj_candidates(asdm_ctx* ctx, asdm_set* target, int nq, const float* d_desc_q, const int32_t* d_q_rows,
+                           int* ent_cap_io, ProjDev* out) {
+  int ent_cap = std::max(*ent_cap_io, 1 << 14);
+  for (int attempt = 0; attempt < 20; attempt++) {
+    int rc;
+    if ((rc = ensure(ctx, ctx->scratch[SC_SEG], (size_t)std::max(nq, 1) * sizeof(ProjSeg)))) return rc;
+    if ((rc = ensure(ctx, ctx->scratch[SC_ENT], (size_t)ent_cap * 12))) return rc;
+    if ((rc = ensure(ctx, ctx->scratch[SC_MISC], 256))) return rc;
+    ProjDev pd;
+    pd.q = (asdm_proj_query*)ctx->scratch[SC_QUERY].p;
+    pd.seg = (ProjSeg*)ctx->scratch[SC_SEG].p;
+    pd.ent_j = (int32_t*)ctx->scratch[SC_ENT].p;
+    pd.ent_q = pd.ent_j + ent_cap;
+    pd.ent_d = (float*)(pd.ent_q + ent_cap);
+    pd.total = (int32_t*)ctx->scratch[SC_MISC].p;
+    pd.overflow = pd.total + 1;
+    CK(cudaMemsetAsync(pd.total, 0, 8, ctx->stream));
+    if (nq > 0) {
+      k_proj_gather<<<(nq + 127) / 128, 128, 0, ctx->stream>>>(pd.q, nq, target->kps, target->grid, target->cell_start,
+                                                               target->cell_items, pd.seg, pd.ent_j, pd.ent_q, ent_cap,
+                                                               pd.total, pd.overflow);
+      LAUNCHED(ctx);
+    }
+    int32_t h[2] = {0, 0};
+    CK(cudaMemcpyAsync(h, pd.total, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (h[1]) {  // pool too small: h[0] is the exact demand
+      ent_cap = std::max(ent_cap * 2, h[0] + 1024);
+      ctx->stat_retries++;
+      continue;
+    }
+    if (h[0] > 0) {
+      const int blocks = std::min((h[0] + 255) / 256, ctx->sm_count * 8);
+      k_proj_dist<<<blocks, 256, 0, ctx->stream>>>(d_desc_q, d_q_rows, target->desc, pd.ent_j, pd.ent_q, ent_cap, pd.total,
+                                                   pd.ent_d);
+      LAUNCHED(ctx);
+    }
+    *ent_cap_io = ent_cap;
+    *out = pd;
+    return ASDM_OK;
+  }
+  return fail(ctx, ASDM_ERR_INTERNAL, "projection entry pool kept overflowing");
+}
+
+extern "C" int asdm_search_by_projection(asdm_ctx* ctx, asdm_set* target, const asdm_proj_query* q, int nq,
+                                         const float* desc_q, asdm_set* q_set, const int32_t* q_rows,
+                                         const uint8_t* blocked0, const asdm_proj_params* p, int32_t* assign,
+                                         float* dist_t, int32_t* nmatches) {
+  if (!ctx || !target || nq < 0 || (nq > 0 && !q) || !p || !assign) return ASDM_ERR_INVALID;
+  if (!target->has_grid) return fail(ctx, ASDM_ERR_INVALID, "target set has no grid");
+  if (!desc_q && !q_set) return fail(ctx, ASDM_ERR_INVALID, "query descriptors missing");
+  if (p->mode != ASDM_PROJ_RATIO_LEVEL && p->mode != ASDM_PROJ_BEST_ONLY) return fail(ctx, ASDM_ERR_INVALID, "bad mode");
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  CK(cudaSetDevice(ctx->device));
+  ctx->stat_launches = 0;
+  ctx->stat_retries = 0;
+  const int n_t = target->n;
+  int rc;
+  if ((rc = ensure(ctx, ctx->scratch[SC_QUERY], (size_t)std::max(nq, 1) * sizeof(asdm_proj_query)))) return rc;
+  if (nq > 0) CK(cudaMemcpyAsync(ctx->scratch[SC_QUERY].p, q, (size_t)nq * sizeof(asdm_proj_query), cudaMemcpyHostToDevice, ctx->stream));
+  const float* d_desc_q = nullptr;
+  const int32_t* d_rows = nullptr;
+  if (desc_q) {
+    if ((rc = ensure(ctx, ctx->scratch[SC_QDESC], (size_t)std::max(nq, 1) * ASDM_DESC_DIM * sizeof(float)))) return rc;
+    if (nq > 0)
+      CK(cudaMemcpyAsync(ctx->scratch[SC_QDESC].p, desc_q, (size_t)nq * ASDM_DESC_DIM * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    d_desc_q = (const float*)ctx->scratch[SC_QDESC].p;
+  } else {
+    if (q_set->ctx != ctx) return fail(ctx, ASDM_ERR_INVALID, "query set belongs to another context");
+    d_desc_q = q_set->desc;
+    if (q_rows) {
+      for (int i = 0; i < nq; i++)
+        if (q[i].valid && (q_rows[i] < 0 || q_rows[i] >= q_set->n)) return fail(ctx, ASDM_ERR_INVALID, "query row out of range");
+      if ((rc = ensure(ctx, ctx->scratch[SC_QDESC], (size_t)std::max(nq, 1) * sizeof(int32_t)))) return rc;
+      if (nq > 0) CK(cudaMemcpyAsync(ctx->scratch[SC_QDESC].p, q_rows, (size_t)nq * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+      d_rows = (const int32_t*)ctx->scratch[SC_QDESC].p;
+    } else if (nq > q_set->n) {
+      return fail(ctx, ASDM_ERR_INVALID, "more queries than rows in the query set");
+    }
+  }
+  const uint8_t* d_blocked = nullptr;
+  if (blocked0) {
+    if ((rc = ensure(ctx, ctx->scratch[SC_BLOCK], (size_t)std::max(n_t, 1)))) return rc;
+    if (n_t > 0) CK(cudaMemcpyAsync(ctx->scratch[SC_BLOCK].p, blocked0, (size_t)n_t, cudaMemcpyHostToDevice, ctx->stream));
+    d_blocked = (const uint8_t*)ctx->scratch[SC_BLOCK].p;
+  }
+  ProjDev pd;
+  if ((rc = proj_candidates(ctx, target, nq, d_desc_q, d_rows, &ctx->proj_ent_cap, &pd))) return rc;
+  // state: acc[nq] own[2*n_t] assign[n_t] dist[n_t] nm[1]
+  const size_t state = ((size_t)std::max(nq, 1) + 4 * (size_t)std::max(n_t, 1) + 4) * 4;
+  if ((rc = ensure(ctx, ctx->scratch[SC_STATE], state))) return rc;
+  int32_t* acc = (int32_t*)ctx->scratch[SC_STATE].p;
+  int32_t* own = acc + std::max(nq, 1);
+  int32_t* d_assign = own + 2 * (size_t)std::max(n_t, 1);
+  float* d_dist = (float*)(d_assign + std::max(n_t, 1));
+  int32_t* d_nm = (int32_t*)(d_dist + std::max(n_t, 1));
+  ProjParamsDev P{p->mode, p->th_accept, p->best_init, p->nnratio, p->check_ori ? 1 : 0, p->count_twice ? 1 : 0};
+  k_proj_resolve<<<1, 1024, 0, ctx->stream>>>(pd.q, nq, target->kps, n_t, d_blocked, pd.seg, pd.ent_j, pd.ent_d, P, acc,
+                                              own, d_assign, d_dist, d_nm);
+  LAUNCHED(ctx);
+  CK(cudaGetLastError());
+  int32_t nm = 0;
+  if (n_t > 0) CK(cudaMemcpyAsync(assign, d_assign, (size_t)n_t * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  if (dist_t && n_t > 0) CK(cudaMemcpyAsync(dist_t, d_dist, (size_t)n_t * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(&nm, d_nm, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  if (nmatches) *nmatches = nm;
+  return ASDM_OK;
+}
+
+extern "C" int asdm_search_for_initialization(asdm_ctx* ctx, asdm_set* f1, asdm_set* f2, float* prev_matched,
+                                              int window_size, float nnratio, int check_ori, int32_t* matches12,
+                                              float* dist12, int32_t* nmatches) {
+  if (!ctx || !f1 || !f2 || !prev_matched || !matches12) return ASDM_ERR_INVALID;
+  if (!f1->has_kps || !f2->has_grid) return fail(ctx, ASDM_ERR_INVALID, "F1 needs keypoints and F2 a grid");
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  CK(cudaSetDevice(ctx->device));
+  ctx->stat_launches = 0;
+  ctx->stat_retries = 0;
+  const int n1 = f1->n, n2 = f2->n;
+  int rc;
+  if ((rc = ensure(ctx, ctx->scratch[SC_QUERY], (size_t)std::max(n1, 1) * sizeof(asdm_proj_query)))) return rc;
+  // state: prev[2*n1] matched_dist[n2] matches21[n2] matches12[n1] dist12[n1] pushed[n1] nm
+  const size_t N1 = (size_t)std::max(n1, 1), N2 = (size_t)std::max(n2, 1);
+  if ((rc = ensure(ctx, ctx->scratch[SC_STATE], (5 * N1 + 2 * N2 + 4) * 4))) return rc;
+  float* d_prev = (float*)ctx->scratch[SC_STATE].p;
+  float* d_md = d_prev + 2 * N1;
+  int32_t* d_m21 = (int32_t*)(d_md + N2);
+  int32_t* d_m12 = d_m21 + N2;
+  float* d_d12 = (float*)(d_m12 + N1);
+  int32_t* d_push = (int32_t*)(d_d12 + N1);
+  int32_t* d_nm = d_push + N1;
+  if (n1 > 0) {
+    CK(cudaMemcpyAsync(d_prev, prev_matched, (size_t)n1 * 8, cudaMemcpyHostToDevice, ctx->stream));
+    k_init_queries<<<(n1 + 255) / 256, 256, 0, ctx->stream>>>(f1->kps, n1, d_prev, (float)window_size,
+                                                              (asdm_proj_query*)ctx->scratch[SC_QUERY].p);
+    LAUNCHED(ctx);
+  }
+  ProjDev pd;
+  if ((rc = proj_candidates(ctx, f2, n1, f1->desc, nullptr, &ctx->proj_ent_cap, &pd))) return rc;
+  k_init_resolve<<<1, 32, 0, ctx->stream>>>(f1->kps, n1, f2->kps, n2, pd.seg, pd.ent_j, pd.ent_d, nnratio,
+                                            check_ori ? 1 : 0, d_md, d_m21, d_m12, d_d12, d_push, d_prev, d_nm);
+  LAUNCHED(ctx);
+  CK(cudaGetLastError());
+  int32_t nm = 0;
+  if (n1 > 0) {
+    CK(cudaMemcpyAsync(matches12, d_m12, (size_t)n1 * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (dist12) CK(cudaMemcpyAsync(dist12, d_d12, (size_t)n1 * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(prev_matched, d_prev, (size_t)n1 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  CK(cudaMemcpyAsync(&nm, d_nm, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  if (nmatches) *nmatches = nm;
+  return ASDM_OK;
+}
+
+extern "C" int asdm_stereo_row_match(asdm_ctx* ctx, asdm_set* left, asdm_set* right, const float* scale_factors,
+                                     int n_levels, int n_rows, float min_d, float max_d, int32_t* best_r,
+                                     float* best_dist) {
+  if (!ctx || !left || !right || !scale_factors || n_levels <= 0 || n_levels > ASDM_MAX_LEVELS || !best_r)
+    return ASDM_ERR_INVALID;
+  if (!left->has_kps || !right->has_kps) return fail(ctx, ASDM_ERR_INVALID, "sets need keypoints");
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  CK(cudaSetDevice(ctx->device));
+  ctx->stat_launches = 0;
+  const int n_l = left->n;
+  int rc;
+  const size_t NL = (size_t)std::max(n_l, 1);
+  if ((rc = ensure(ctx, ctx->scratch[SC_STATE], (2 * NL + ASDM_MAX_LEVELS) * 4))) return rc;
+  int32_t* d_best = (int32_t*)ctx->scratch[SC_STATE].p;
+  float* d_dist = (float*)(d_best + NL);
+  float* d_sf = d_dist + NL;
+  CK(cudaMemcpyAsync(d_sf, scale_factors, (size_t)n_levels * 4, cudaMemcpyHostToDevice, ctx->stream));
+  if (n_l > 0) {
+    k_stereo_match<<<(n_l * 32 + 255) / 256, 256, 0, ctx->stream>>>(left->desc, left->kps, n_l, right->desc, right->kps,
+                                                                    right->n, d_sf, n_levels, n_rows, min_d, max_d, d_best,
+                                                                    d_dist);
+    LAUNCHED(ctx);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(best_r, d_best, (size_t)n_l * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (best_dist) CK(cudaMemcpyAsync(best_dist, d_dist, (size_t)n_l * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  CK(cudaStreamSynchronize(ctx->stream));
+  return ASDM_OK;
+}

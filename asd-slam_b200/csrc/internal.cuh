@@ -1,0 +1,182 @@
+// internal.cuh -- shared host/device declarations of libasdmatch_cuda.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+#include <atomic>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/asdmatch.h"
+
+#define ASDM_MAX_LEVELS 32
+#define ASDM_BEST_INIT_BOW 256.0f  // ORBmatcher.cc:204-206, 577-579
+
+// A device allocation that only ever grows (scratch reused across calls on one context).
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+};
+
+// ------------------------------------------------------------------------------------------ host structs
+struct asdm_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = true;
+  std::recursive_mutex mu;
+  std::string err;
+  int opt_force_exact = 0;
+  int opt_cand_cap = 8;
+  int opt_list_cap_per_query = 8;  // tensor-core short list slots per query row (grows on overflow)
+  int64_t stat_launches = 0;       // kernels launched by the last call / job run
+  int64_t stat_total_launches = 0;
+  int64_t stat_cand_cap = 0;
+  int64_t stat_retries = 0;
+  int64_t stat_tc_used = 0;
+  int64_t stat_tc_pairs = 0;  // (i,j) pairs emitted by the tensor-core shortlist in the last run
+  int sm_count = 148;
+  void* tmap_encode = nullptr;  // cuTensorMapEncodeTiled, resolved through the runtime
+  // pinned staging for the single-call entry points
+  void* h_pin = nullptr;
+  size_t h_pin_cap = 0;
+  DevBuf scratch[8];
+  int proj_ent_cap = 1 << 16;  // entries of the projection candidate pool (grows on overflow)
+};
+
+struct asdm_set {
+  asdm_ctx* ctx = nullptr;
+  std::atomic<int> ref{1};
+  int n = 0;
+  int n_pad = 0;                     // rows allocated (multiple of 256; padding rows are zero)
+  float* desc = nullptr;             // [n_pad][128] fp32, 512 B rows
+  __nv_bfloat16* desc_bf = nullptr;  // [n_pad][128] bf16 (tensor-core operand, K-major)
+  float* norm2 = nullptr;            // [n_pad] sum of squares of the fp32 row
+  int32_t* d_flags = nullptr;        // [0] = 1 when some row is non-finite or its norm is out of the TC range
+  int tc_ok = -1;                    // -1 unknown (flags not read back yet), 0 no, 1 yes
+  bool has_kps = false, has_grid = false, has_fv = false;
+  asdm_kp* kps = nullptr;  // [n] cv::KeyPoint fields as uploaded (16 B each: one LDG.128 per keypoint)
+  asdm_grid grid{};
+  int32_t* cell_start = nullptr;  // [cols*rows+1]
+  int32_t* cell_items = nullptr;  // [n] insertion (index) order inside a cell
+  uint32_t* node_id = nullptr;    // [n] FeatureVector node of the feature
+  int32_t* fv_pos = nullptr;      // [n] CSR position of the feature in the FeatureVector, -1 if absent
+  std::vector<uint8_t> tmap_bf;   // CUtensorMap (128 B) over desc_bf, built lazily
+};
+
+// --------------------------------------------------------------------------------- device-visible structs
+// One keyframe pair of a BoW-gated dense search (a8 / a9 / a11).
+struct PairDesc {
+  const float* descA;
+  const float* descB;
+  const __nv_bfloat16* bfA;
+  const __nv_bfloat16* bfB;
+  const float* normA;
+  const float* normB;
+  const uint32_t* nodeA;
+  const uint32_t* nodeB;
+  const int32_t* posA;  // query processing order (CSR position); <0 = not in the FeatureVector
+  const int32_t* posB;  // target scan order
+  const uint8_t* maskA;
+  const uint8_t* maskB;
+  const asdm_kp* kpA;
+  const asdm_kp* kpB;
+  int32_t nA, nB;
+  int32_t setA, setB;  // index into the job's tensor-map table
+  float F12[9];
+  float ex, ey;
+};
+
+struct BowParams {
+  int32_t kind;        // KIND_*
+  int32_t mask_sense;  // feature usable iff mask == mask_sense
+  float t_keep;        // keep candidate iff d <= t_keep
+  float th_accept;     // TH_LOW
+  int32_t strict;      // a9: best < TH_LOW (ORBmatcher.cc:609); a8: <= (:231)
+  float nnratio;
+  int32_t check_ori;
+  int32_t n_levels;
+  float scale_factors[ASDM_MAX_LEVELS];
+  float level_sigma2[ASDM_MAX_LEVELS];
+};
+
+#define KIND_BOW_KF_KF 1
+#define KIND_TRIANGULATION 2
+#define KIND_BOW_KF_F 3
+
+struct Cand {
+  int32_t j;
+  float d;
+};
+
+struct TcPair {
+  int32_t i, j;
+};
+
+// ------------------------------------------------------------------------------------------ device helpers
+// ORBmatcher::DescriptorDistance (ORBmatcher.cc:1637-1644): one fp32 accumulator, index ascending,
+// separate sub / mul / add with round-to-nearest -- never contracted into FMA.
+__device__ __forceinline__ float asdm_exact_dist(const float* __restrict__ a, const float* __restrict__ b) {
+  const float4* a4 = reinterpret_cast<const float4*>(a);
+  const float4* b4 = reinterpret_cast<const float4*>(b);
+  float s = 0.f;
+#pragma unroll 8
+  for (int k = 0; k < ASDM_DESC_DIM / 4; k++) {
+    const float4 x = __ldg(a4 + k), y = __ldg(b4 + k);
+    float d;
+    d = __fsub_rn(x.x, y.x); s = __fadd_rn(s, __fmul_rn(d, d));
+    d = __fsub_rn(x.y, y.y); s = __fadd_rn(s, __fmul_rn(d, d));
+    d = __fsub_rn(x.z, y.z); s = __fadd_rn(s, __fmul_rn(d, d));
+    d = __fsub_rn(x.w, y.w); s = __fadd_rn(s, __fmul_rn(d, d));
+  }
+  return s;
+}
+
+// rotation-bin idiom, e.g. ORBmatcher.cc:245-250 (factor = 1.0f/HISTO_LENGTH, so only bins 0..12 occur)
+__device__ __forceinline__ int asdm_rot_bin(float a1, float a2) {
+  const float factor = 1.0f / ASDM_HISTO_LENGTH;
+  float rot = __fsub_rn(a1, a2);
+  if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+  int bin = (int)roundf(__fmul_rn(rot, factor));
+  if (bin == ASDM_HISTO_LENGTH) bin = 0;
+  if (bin < 0 || bin >= ASDM_HISTO_LENGTH) bin = 0;  // the reference asserts here
+  return bin;
+}
+
+// ORBmatcher::ComputeThreeMaxima (ORBmatcher.cc:1584-1625) on bin sizes
+__device__ inline void asdm_three_maxima(const int* sizes, int L, int& ind1, int& ind2, int& ind3) {
+  int max1 = 0, max2 = 0, max3 = 0;
+  ind1 = ind2 = ind3 = -1;
+  for (int i = 0; i < L; i++) {
+    const int s = sizes[i];
+    if (s > max1) {
+      max3 = max2; max2 = max1; max1 = s;
+      ind3 = ind2; ind2 = ind1; ind1 = i;
+    } else if (s > max2) {
+      max3 = max2; max2 = s;
+      ind3 = ind2; ind2 = i;
+    } else if (s > max3) {
+      max3 = s; ind3 = i;
+    }
+  }
+  if ((float)max2 < __fmul_rn(0.1f, (float)max1)) {
+    ind2 = -1; ind3 = -1;
+  } else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) {
+    ind3 = -1;
+  }
+}
+
+// --------------------------------------------------------------------------------------- launch wrappers
+// tc_shortlist.cu: tcgen05/TMA distance contraction that lists every (pair,i,j) whose bf16 distance estimate
+// is within the keep threshold plus the proven error bound.
+struct TcWork {   // one unit of the persistent tensor-core kernel
+  int32_t pair;
+  int32_t n_tile;      // 256-row tile of set B kept resident in shared memory
+  int32_t m_tile0;     // first 128-row tile of set A streamed against it
+  int32_t m_tiles;
+};
+cudaError_t asdm_tc_shortlist_launch(asdm_ctx* ctx, const PairDesc* d_pairs, const void* d_tmaps,
+                                     const TcWork* d_work, int n_work, float t_keep_eff, TcPair* d_list,
+                                     int32_t* d_list_pair, int list_cap, int32_t* d_list_count);
+int asdm_tc_build_tmap(asdm_ctx* ctx, asdm_set* set);

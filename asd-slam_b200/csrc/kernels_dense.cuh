@@ -1,0 +1,361 @@
+// kernels_dense.cuh -- BoW-gated dense search kernels (SearchByBoW x2, SearchForTriangulation).
+//
+//  k_cand_exact   : every gated (i,j) pair in exact fp32 (reference arithmetic), keeps d <= t_keep
+//  k_rerank       : exact fp32 distance of the (i,j) pairs short-listed by the tcgen05 kernel
+//  k_resolve_bow  : replays the reference's greedy query order as a parallel fixed point, ratio test,
+//                   30-bin rotation histogram + ComputeThreeMaxima, writes the match lists
+//  k_resolve_tri  : SearchForTriangulation selection (epipole + epipolar-line gates, last tie wins)
+#pragma once
+#include "internal.cuh"
+
+// gate shared by all candidate producers: both features usable and in the same vocabulary node
+__device__ __forceinline__ bool bow_query_ok(const PairDesc& pd, const BowParams& P, int i) {
+  return pd.maskA[i] == P.mask_sense && pd.posA[i] >= 0;
+}
+__device__ __forceinline__ bool bow_target_ok(const PairDesc& pd, const BowParams& P, int j) {
+  return pd.maskB[j] == P.mask_sense && pd.posB[j] >= 0;
+}
+
+__device__ __forceinline__ void cand_append(int32_t* cnt, Cand* cand, int cap, int qslot, int j, float d,
+                                            int32_t* overflow) {
+  const int s = atomicAdd(cnt + qslot, 1);
+  if (s < cap) {
+    cand[(size_t)qslot * cap + s] = Cand{j, d};
+  } else {
+    *overflow = 1;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Exact dense candidates. Tile 64 queries x 64 targets per CTA, 256 threads, 4x4 pairs per thread; both
+// tiles are staged K-transposed in shared memory so the inner loop is two LDS.128 per 48 fp32 ops. Every
+// pair keeps its own accumulator and walks k = 0..127 in order: bit-identical to ORBmatcher.cc:1637-1644.
+// Algorithmic work: 3*128 flops per pair (sub, mul, add; no FMA).
+#define CE_TM 64
+#define CE_TN 64
+__global__ void __launch_bounds__(256) k_cand_exact(const PairDesc* __restrict__ pairs, BowParams P, int cap,
+                                                    int n_stride, int32_t* __restrict__ cnt,
+                                                    Cand* __restrict__ cand, int32_t* __restrict__ overflow) {
+  extern __shared__ __align__(16) float sm[];
+  float* As = sm;                          // [128][CE_TM]
+  float* Bs = sm + ASDM_DESC_DIM * CE_TM;  // [128][CE_TN]
+  const int pair = blockIdx.z;
+  const PairDesc& pd = pairs[pair];
+  const int i0 = blockIdx.x * CE_TM, j0 = blockIdx.y * CE_TN;
+  if (i0 >= pd.nA || j0 >= pd.nB) return;
+  const int t = threadIdx.x;
+  {
+    const int row = t & 63, kc = t >> 6;  // consecutive threads take consecutive rows: conflict-free smem stores
+    const bool okA = (i0 + row) < pd.nA, okB = (j0 + row) < pd.nB;
+    const float4* ga = reinterpret_cast<const float4*>(pd.descA + (size_t)(i0 + row) * ASDM_DESC_DIM);
+    const float4* gb = reinterpret_cast<const float4*>(pd.descB + (size_t)(j0 + row) * ASDM_DESC_DIM);
+#pragma unroll
+    for (int it = 0; it < 8; it++) {
+      const int k4 = kc + 4 * it;
+      const float4 va = okA ? __ldg(ga + k4) : make_float4(0.f, 0.f, 0.f, 0.f);
+      const float4 vb = okB ? __ldg(gb + k4) : make_float4(0.f, 0.f, 0.f, 0.f);
+      As[(k4 * 4 + 0) * CE_TM + row] = va.x; As[(k4 * 4 + 1) * CE_TM + row] = va.y;
+      As[(k4 * 4 + 2) * CE_TM + row] = va.z; As[(k4 * 4 + 3) * CE_TM + row] = va.w;
+      Bs[(k4 * 4 + 0) * CE_TN + row] = vb.x; Bs[(k4 * 4 + 1) * CE_TN + row] = vb.y;
+      Bs[(k4 * 4 + 2) * CE_TN + row] = vb.z; Bs[(k4 * 4 + 3) * CE_TN + row] = vb.w;
+    }
+  }
+  __syncthreads();
+  const int ty = t >> 4, tx = t & 15;
+  float acc[4][4];
+#pragma unroll
+  for (int r = 0; r < 4; r++)
+#pragma unroll
+    for (int c = 0; c < 4; c++) acc[r][c] = 0.f;
+#pragma unroll 4
+  for (int k = 0; k < ASDM_DESC_DIM; k++) {
+    const float4 a = *reinterpret_cast<const float4*>(As + k * CE_TM + ty * 4);
+    const float4 b = *reinterpret_cast<const float4*>(Bs + k * CE_TN + tx * 4);
+    const float av[4] = {a.x, a.y, a.z, a.w};
+    const float bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int r = 0; r < 4; r++)
+#pragma unroll
+      for (int c = 0; c < 4; c++) {
+        const float d = __fsub_rn(av[r], bv[c]);
+        acc[r][c] = __fadd_rn(acc[r][c], __fmul_rn(d, d));
+      }
+  }
+#pragma unroll
+  for (int r = 0; r < 4; r++) {
+    const int i = i0 + ty * 4 + r;
+    if (i >= pd.nA) continue;
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+      const int j = j0 + tx * 4 + c;
+      if (j >= pd.nB) continue;
+      if (!(acc[r][c] <= P.t_keep)) continue;
+      if (!bow_query_ok(pd, P, i) || !bow_target_ok(pd, P, j)) continue;
+      if (pd.nodeA[i] != pd.nodeB[j]) continue;
+      cand_append(cnt, cand, cap, pair * n_stride + i, j, acc[r][c], overflow);
+    }
+  }
+}
+
+// Exact rerank of the tensor-core short list: one thread per listed (pair, i, j).
+__global__ void __launch_bounds__(256) k_rerank(const PairDesc* __restrict__ pairs, BowParams P, int cap,
+                                                int n_stride, const TcPair* __restrict__ list,
+                                                const int32_t* __restrict__ list_pair,
+                                                const int32_t* __restrict__ list_count, int list_cap,
+                                                int32_t* __restrict__ cnt, Cand* __restrict__ cand,
+                                                int32_t* __restrict__ overflow) {
+  int n = *list_count;
+  if (n > list_cap) {  // the short list itself overflowed: the host falls back to k_cand_exact
+    if (blockIdx.x == 0 && threadIdx.x == 0) overflow[1] = 1;
+    n = list_cap;
+  }
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
+    const int pair = list_pair[e];
+    const PairDesc& pd = pairs[pair];
+    const int i = list[e].i, j = list[e].j;
+    if (i >= pd.nA || j >= pd.nB) continue;
+    if (!bow_query_ok(pd, P, i) || !bow_target_ok(pd, P, j)) continue;
+    if (pd.nodeA[i] != pd.nodeB[j]) continue;
+    const float d = asdm_exact_dist(pd.descA + (size_t)i * ASDM_DESC_DIM, pd.descB + (size_t)j * ASDM_DESC_DIM);
+    if (!(d <= P.t_keep)) continue;
+    cand_append(cnt, cand, cap, pair * n_stride + i, j, d, overflow);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Greedy resolve for SearchByBoW (ORBmatcher.cc:156-297 and :533-666). One CTA per keyframe pair.
+//
+// The reference walks queries in FeatureVector order; an accepted query removes its target from every later
+// query's scan (vpMapPointMatches[realIdxF] / vbMatched2). Let accept(i) be the decision of query i given
+// the targets accepted by queries that precede it. The sequential run is the unique solution of
+//   accept(i) = D_i({accept(i') : pos(i') < pos(i)}).
+// We iterate all queries in parallel against owner[j] = min pos of a query currently accepting j; after
+// iteration t the first t queries are final, and in practice two or three sweeps reach the fixed point.
+// Only candidates with d <= t_keep are listed: a farther second-best cannot fail the ratio test
+// (t_keep is chosen on the host so that nnratio * d > TH_LOW for every d > t_keep).
+__device__ __forceinline__ bool cand_before(const Cand& x, int px, const Cand& y, int py) {
+  return x.d < y.d || (x.d == y.d && px < py);
+}
+
+__global__ void __launch_bounds__(512) k_resolve_bow(const PairDesc* __restrict__ pairs, BowParams P, int cap,
+                                                     int n_stride, int m_stride, int out_stride,
+                                                     const int32_t* __restrict__ cnt, Cand* __restrict__ cand,
+                                                     int32_t* __restrict__ owner, int32_t* __restrict__ acc,
+                                                     int32_t* __restrict__ match, float* __restrict__ dist,
+                                                     int32_t* __restrict__ nmatches) {
+  const int pair = blockIdx.x;
+  const PairDesc& pd = pairs[pair];
+  const int nA = pd.nA, nB = pd.nB;
+  const int32_t* cntp = cnt + (size_t)pair * n_stride;
+  Cand* candp = cand + (size_t)pair * n_stride * cap;
+  int32_t* own0 = owner + (size_t)pair * 2 * m_stride;
+  int32_t* accp = acc + (size_t)pair * n_stride;
+  int32_t* matchp = match + (size_t)pair * out_stride;
+  float* distp = dist + (size_t)pair * out_stride;
+  __shared__ int s_changed;
+  __shared__ int s_hist[ASDM_HISTO_LENGTH];
+  __shared__ int s_keep[3];
+  __shared__ int s_count;
+  const int t = threadIdx.x, nt = blockDim.x;
+
+  // sort each query's list by (distance, target scan position): strict '<' in the reference means the first
+  // candidate in scan order wins ties (ORBmatcher.cc:219-228)
+  for (int i = t; i < nA; i += nt) {
+    const int n = min(cntp[i], cap);
+    Cand* L = candp + (size_t)i * cap;
+    for (int a = 1; a < n; a++) {
+      const Cand x = L[a];
+      const int px = pd.posB[x.j];
+      int b = a - 1;
+      while (b >= 0 && cand_before(x, px, L[b], pd.posB[L[b].j])) {
+        L[b + 1] = L[b];
+        b--;
+      }
+      L[b + 1] = x;
+    }
+    accp[i] = -1;
+  }
+  const int out_n = (P.kind == KIND_BOW_KF_F) ? nB : nA;
+  for (int k = t; k < out_n; k += nt) {
+    matchp[k] = -1;
+    distp[k] = -1.f;
+  }
+  for (int j = t; j < nB; j += nt) own0[j] = INT_MAX;
+  if (t < ASDM_HISTO_LENGTH) s_hist[t] = 0;
+  if (t == 0) s_count = 0;
+  __syncthreads();
+
+  for (int iter = 0;; iter++) {
+    const int32_t* own = own0 + (size_t)(iter & 1) * m_stride;
+    int32_t* own_next = own0 + (size_t)((iter & 1) ^ 1) * m_stride;
+    if (t == 0) s_changed = 0;
+    __syncthreads();
+    for (int i = t; i < nA; i += nt) {
+      const int n = min(cntp[i], cap);
+      if (n == 0) continue;
+      const Cand* L = candp + (size_t)i * cap;
+      const int mypos = pd.posA[i];
+      float d1 = ASDM_BEST_INIT_BOW, d2 = ASDM_BEST_INIT_BOW;
+      int j1 = -1;
+      for (int c = 0; c < n; c++) {
+        const Cand x = L[c];
+        if (!(x.d < ASDM_BEST_INIT_BOW)) break;
+        if (own[x.j] < mypos) continue;  // taken by an earlier query
+        if (j1 < 0) {
+          j1 = x.j;
+          d1 = x.d;
+        } else {
+          d2 = x.d;
+          break;
+        }
+      }
+      const bool pass = P.strict ? (d1 < P.th_accept) : (d1 <= P.th_accept);
+      const int dec = (j1 >= 0 && pass && d1 < __fmul_rn(P.nnratio, d2)) ? j1 : -1;
+      if (dec != accp[i]) {
+        accp[i] = dec;
+        s_changed = 1;
+      }
+    }
+    for (int j = t; j < nB; j += nt) own_next[j] = INT_MAX;
+    __syncthreads();
+    for (int i = t; i < nA; i += nt) {
+      const int a = accp[i];
+      if (a >= 0) atomicMin(own_next + a, pd.posA[i]);
+    }
+    __syncthreads();
+    if (!s_changed) break;
+    __syncthreads();
+  }
+
+  // rotation consistency (ORBmatcher.cc:242-253, 274-294 / :616-626, 645-663)
+  for (int i = t; i < nA; i += nt) {
+    const int j = accp[i];
+    if (j < 0) continue;
+    atomicAdd(&s_count, 1);
+    if (P.check_ori) atomicAdd(&s_hist[asdm_rot_bin(pd.kpA[i].angle, pd.kpB[j].angle)], 1);
+  }
+  __syncthreads();
+  if (t == 0) {
+    if (P.check_ori) {
+      asdm_three_maxima(s_hist, ASDM_HISTO_LENGTH, s_keep[0], s_keep[1], s_keep[2]);
+      int pruned = 0;
+      for (int b = 0; b < ASDM_HISTO_LENGTH; b++)
+        if (b != s_keep[0] && b != s_keep[1] && b != s_keep[2]) pruned += s_hist[b];
+      nmatches[pair] = s_count - pruned;
+    } else {
+      nmatches[pair] = s_count;
+    }
+  }
+  __syncthreads();
+  for (int i = t; i < nA; i += nt) {
+    const int j = accp[i];
+    if (j < 0) continue;
+    if (P.check_ori) {
+      const int b = asdm_rot_bin(pd.kpA[i].angle, pd.kpB[j].angle);
+      if (b != s_keep[0] && b != s_keep[1] && b != s_keep[2]) continue;
+    }
+    const Cand* L = candp + (size_t)i * cap;
+    const int n = min(cntp[i], cap);
+    float d = -1.f;
+    for (int c = 0; c < n; c++)
+      if (L[c].j == j) { d = L[c].d; break; }
+    if (P.kind == KIND_BOW_KF_F) {
+      matchp[j] = i;
+      distp[j] = d;
+    } else {
+      matchp[i] = j;
+      distp[i] = d;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// SearchForTriangulation selection (ORBmatcher.cc:718-774). No cross-query state (vbMatched2 is never set),
+// so each query is independent: among listed candidates (d <= TH_LOW) that pass the epipole gate (:743-747)
+// and CheckDistEpipolarLine (:136-153), the running "dist > bestDist -> continue" keeps the LAST candidate in
+// scan order among equal minima.
+__device__ __forceinline__ bool tri_geo_ok(const PairDesc& pd, const BowParams& P, int i, int j) {
+  const asdm_kp k2 = pd.kpB[j];
+  const float x2 = k2.x, y2 = k2.y;
+  const int o2 = k2.octave;
+  const float distex = __fsub_rn(pd.ex, x2), distey = __fsub_rn(pd.ey, y2);
+  if (__fadd_rn(__fmul_rn(distex, distex), __fmul_rn(distey, distey)) < __fmul_rn(100.f, P.scale_factors[o2]))
+    return false;
+  const float x1 = pd.kpA[i].x, y1 = pd.kpA[i].y;
+  const float* F = pd.F12;
+  const float a = __fadd_rn(__fadd_rn(__fmul_rn(x1, F[0]), __fmul_rn(y1, F[3])), F[6]);
+  const float b = __fadd_rn(__fadd_rn(__fmul_rn(x1, F[1]), __fmul_rn(y1, F[4])), F[7]);
+  const float c = __fadd_rn(__fadd_rn(__fmul_rn(x1, F[2]), __fmul_rn(y1, F[5])), F[8]);
+  const float num = __fadd_rn(__fadd_rn(__fmul_rn(a, x2), __fmul_rn(b, y2)), c);
+  const float den = __fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b));
+  if (den == 0.f) return false;
+  const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+  return (double)dsqr < __dmul_rn(3.84, (double)P.level_sigma2[o2]);
+}
+
+__global__ void __launch_bounds__(512) k_resolve_tri(const PairDesc* __restrict__ pairs, BowParams P, int cap,
+                                                     int n_stride, int out_stride, const int32_t* __restrict__ cnt,
+                                                     const Cand* __restrict__ cand, int32_t* __restrict__ acc,
+                                                     int32_t* __restrict__ match, float* __restrict__ dist,
+                                                     int32_t* __restrict__ nmatches) {
+  const int pair = blockIdx.x;
+  const PairDesc& pd = pairs[pair];
+  const int nA = pd.nA;
+  const int32_t* cntp = cnt + (size_t)pair * n_stride;
+  const Cand* candp = cand + (size_t)pair * n_stride * cap;
+  int32_t* accp = acc + (size_t)pair * n_stride;
+  int32_t* matchp = match + (size_t)pair * out_stride;
+  float* distp = dist + (size_t)pair * out_stride;
+  __shared__ int s_hist[ASDM_HISTO_LENGTH];
+  __shared__ int s_keep[3];
+  __shared__ int s_count;
+  const int t = threadIdx.x, nt = blockDim.x;
+  if (t < ASDM_HISTO_LENGTH) s_hist[t] = 0;
+  if (t == 0) s_count = 0;
+  __syncthreads();
+  for (int i = t; i < nA; i += nt) {
+    const int n = min(cntp[i], cap);
+    const Cand* L = candp + (size_t)i * cap;
+    float best = P.th_accept;  // :718
+    int bj = -1, bpos = -1;
+    for (int c = 0; c < n; c++) {
+      const Cand x = L[c];
+      if (x.d > P.th_accept) continue;
+      const int px = pd.posB[x.j];
+      // running "<=" minimum in scan order == smallest d, largest scan position among equals
+      const bool better = (bj < 0) ? (x.d <= best) : (x.d < best || (x.d == best && px > bpos));
+      if (!better) continue;
+      if (!tri_geo_ok(pd, P, i, x.j)) continue;
+      best = x.d; bj = x.j; bpos = px;
+    }
+    accp[i] = bj;
+    matchp[i] = bj;
+    distp[i] = bj >= 0 ? best : -1.f;
+    if (bj >= 0) {
+      atomicAdd(&s_count, 1);
+      if (P.check_ori) atomicAdd(&s_hist[asdm_rot_bin(pd.kpA[i].angle, pd.kpB[bj].angle)], 1);
+    }
+  }
+  __syncthreads();
+  if (t == 0) {
+    int pruned = 0;
+    if (P.check_ori) {
+      asdm_three_maxima(s_hist, ASDM_HISTO_LENGTH, s_keep[0], s_keep[1], s_keep[2]);
+      for (int b = 0; b < ASDM_HISTO_LENGTH; b++)
+        if (b != s_keep[0] && b != s_keep[1] && b != s_keep[2]) pruned += s_hist[b];
+    }
+    nmatches[pair] = s_count - pruned;
+  }
+  __syncthreads();
+  if (P.check_ori) {
+    for (int i = t; i < nA; i += nt) {
+      const int j = accp[i];
+      if (j < 0) continue;
+      const int b = asdm_rot_bin(pd.kpA[i].angle, pd.kpB[j].angle);
+      if (b != s_keep[0] && b != s_keep[1] && b != s_keep[2]) {
+        matchp[i] = -1;
+        distp[i] = -1.f;
+      }
+    }
+  }
+}

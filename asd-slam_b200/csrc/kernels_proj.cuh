@@ -1,0 +1,427 @@
+// kernels_proj.cuh -- projection-gated searches (K3): the descriptor loops of the four SearchByProjection
+// overloads (ORBmatcher.cc:44-122, 300-413, 1318-1452, 1455-1582), SearchForInitialization (:416-531) and the
+// descriptor stage of Frame::ComputeStereoMatches (Frame.cc:360-444).
+//
+//  k_proj_gather  : Frame/KeyFrame::GetFeaturesInArea (Frame.cc:219-274, KeyFrame.cc:839-878) per query, written
+//                   as CSR segments in the reference's scan order (ix outer, iy inner, insertion order in a cell)
+//  k_proj_dist    : exact fp32 distance of every gathered (query, keypoint) entry
+//  k_proj_resolve : replays the greedy query order as a parallel fixed point (same argument as k_resolve_bow)
+//  k_init_resolve : SearchForInitialization's stealing semantics, replayed in query order by one warp
+//  k_stereo_match : row-band stereo candidates, independent per left keypoint
+#pragma once
+#include "internal.cuh"
+
+struct ProjSeg {
+  int32_t off, cnt;
+};
+
+__device__ __forceinline__ bool area_cells(const asdm_grid& g, float x, float y, float r, int& x0, int& x1, int& y0,
+                                           int& y1) {
+  // Frame.cc:226-240. Float->int conversions are clamped first so that huge windows stay defined.
+  const float fx0 = floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, g.min_x), r), g.inv_w));
+  const float fx1 = ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, g.min_x), r), g.inv_w));
+  const float fy0 = floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, g.min_y), r), g.inv_h));
+  const float fy1 = ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, g.min_y), r), g.inv_h));
+  if (!(fx0 == fx0) || !(fx1 == fx1) || !(fy0 == fy0) || !(fy1 == fy1)) return false;
+  const float lim = 1.0e6f;
+  x0 = max(0, (int)fminf(fmaxf(fx0, -lim), lim));
+  if (x0 >= g.cols) return false;
+  x1 = min(g.cols - 1, (int)fminf(fmaxf(fx1, -lim), lim));
+  if (x1 < 0) return false;
+  y0 = max(0, (int)fminf(fmaxf(fy0, -lim), lim));
+  if (y0 >= g.rows) return false;
+  y1 = min(g.rows - 1, (int)fminf(fmaxf(fy1, -lim), lim));
+  if (y1 < 0) return false;
+  return true;
+}
+
+__device__ __forceinline__ bool area_keep(const asdm_kp& kp, float x, float y, float r, bool check_levels,
+                                          int min_level, int max_level) {
+  if (check_levels) {  // Frame.cc:254-261
+    if (kp.octave < min_level) return false;
+    if (max_level >= 0 && kp.octave > max_level) return false;
+  }
+  const float distx = __fsub_rn(kp.x, x), disty = __fsub_rn(kp.y, y);
+  return fabsf(distx) < r && fabsf(disty) < r;  // Frame.cc:266
+}
+
+// One thread per query. total[0] = entries allocated so far; overflow[0] set when the entry pool is too small.
+__global__ void __launch_bounds__(128) k_proj_gather(const asdm_proj_query* __restrict__ q, int nq,
+                                                     const asdm_kp* __restrict__ kps, asdm_grid g,
+                                                     const int32_t* __restrict__ cell_start,
+                                                     const int32_t* __restrict__ cell_items,
+                                                     ProjSeg* __restrict__ seg, int32_t* __restrict__ ent_j,
+                                                     int32_t* __restrict__ ent_q, int ent_cap,
+                                                     int32_t* __restrict__ total, int32_t* __restrict__ overflow) {
+  const int iq = blockIdx.x * blockDim.x + threadIdx.x;
+  if (iq >= nq) return;
+  const asdm_proj_query Q = q[iq];
+  ProjSeg s{0, 0};
+  int x0, x1, y0, y1;
+  if (Q.valid && area_cells(g, Q.u, Q.v, Q.r, x0, x1, y0, y1)) {
+    const bool check_levels = (Q.min_level > 0) || (Q.max_level >= 0);  // Frame.cc:242
+    int cnt = 0;
+    for (int ix = x0; ix <= x1; ix++)
+      for (int e = cell_start[ix * g.rows + y0]; e < cell_start[ix * g.rows + y1 + 1]; e++)
+        cnt += area_keep(kps[cell_items[e]], Q.u, Q.v, Q.r, check_levels, Q.min_level, Q.max_level) ? 1 : 0;
+    if (cnt > 0) {
+      const int off = atomicAdd(total, cnt);
+      if (off + cnt > ent_cap) {
+        *overflow = 1;
+      } else {
+        s.off = off;
+        s.cnt = cnt;
+        int w = off;
+        // cells (ix, y0..y1) are contiguous in the CSR (cell = ix*rows + iy), so this is the reference's scan order
+        for (int ix = x0; ix <= x1; ix++)
+          for (int e = cell_start[ix * g.rows + y0]; e < cell_start[ix * g.rows + y1 + 1]; e++) {
+            const int j = cell_items[e];
+            if (area_keep(kps[j], Q.u, Q.v, Q.r, check_levels, Q.min_level, Q.max_level)) {
+              ent_j[w] = j;
+              ent_q[w] = iq;
+              w++;
+            }
+          }
+      }
+    }
+  }
+  seg[iq] = s;
+}
+
+// One thread per entry: 2 x 512 B rows, 384 flops. desc_q rows are indexed by q_row[iq] when given (queries that
+// live in a descriptor set, e.g. the last frame), else by iq (map-point descriptors uploaded for this call).
+__global__ void __launch_bounds__(256) k_proj_dist(const float* __restrict__ desc_q,
+                                                   const int32_t* __restrict__ q_row,
+                                                   const float* __restrict__ desc_t,
+                                                   const int32_t* __restrict__ ent_j,
+                                                   const int32_t* __restrict__ ent_q, int ent_cap,
+                                                   const int32_t* __restrict__ total, float* __restrict__ ent_d) {
+  const int n = min(*total, ent_cap);
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
+    const int iq = ent_q[e];
+    const int row = q_row ? q_row[iq] : iq;
+    ent_d[e] = asdm_exact_dist(desc_q + (size_t)row * ASDM_DESC_DIM, desc_t + (size_t)ent_j[e] * ASDM_DESC_DIM);
+  }
+}
+
+struct ProjParamsDev {
+  int32_t mode;  // 0 = best & second with octaves (:44-122), 1 = best only
+  float th_accept;
+  float best_init;
+  float nnratio;
+  int32_t check_ori;
+  int32_t count_twice;
+};
+
+// Single CTA. acc[q] = entry index accepted by query q (or -1); own[2][n_t] = smallest blocking query index that
+// currently accepts keypoint j.
+__global__ void __launch_bounds__(1024) k_proj_resolve(const asdm_proj_query* __restrict__ q, int nq,
+                                                       const asdm_kp* __restrict__ kps_t, int n_t,
+                                                       const uint8_t* __restrict__ blocked0,
+                                                       const ProjSeg* __restrict__ seg,
+                                                       const int32_t* __restrict__ ent_j,
+                                                       const float* __restrict__ ent_d, ProjParamsDev P,
+                                                       int32_t* __restrict__ acc, int32_t* __restrict__ own,
+                                                       int32_t* __restrict__ assign, float* __restrict__ dist_t,
+                                                       int32_t* __restrict__ nmatches) {
+  __shared__ int s_changed, s_count;
+  __shared__ int s_hist[ASDM_HISTO_LENGTH];
+  __shared__ int s_keep[3];
+  const int t = threadIdx.x, nt = blockDim.x;
+  for (int i = t; i < nq; i += nt) acc[i] = -1;
+  for (int j = t; j < n_t; j += nt) {
+    own[j] = INT_MAX;
+    assign[j] = -1;
+    dist_t[j] = -1.f;
+  }
+  if (t < ASDM_HISTO_LENGTH) s_hist[t] = 0;
+  if (t == 0) s_count = 0;
+  __syncthreads();
+
+  for (int iter = 0;; iter++) {
+    const int32_t* cur = own + (size_t)(iter & 1) * n_t;
+    int32_t* nxt = own + (size_t)((iter & 1) ^ 1) * n_t;
+    if (t == 0) s_changed = 0;
+    __syncthreads();
+    for (int i = t; i < nq; i += nt) {
+      const ProjSeg s = seg[i];
+      if (s.cnt == 0) continue;
+      float best = P.best_init, best2 = P.best_init;
+      int lvl = -1, lvl2 = -1, be = -1;
+      for (int e = s.off; e < s.off + s.cnt; e++) {
+        const int j = ent_j[e];
+        if ((blocked0 && blocked0[j]) || cur[j] < i) continue;  // :86-88, :385, :1393-1395, :1524
+        const float d = ent_d[e];
+        if (d < best) {
+          best2 = best; best = d;
+          lvl2 = lvl; lvl = kps_t[j].octave;
+          be = e;
+        } else if (P.mode == 0 && d < best2) {  // :102-106
+          lvl2 = kps_t[j].octave;
+          best2 = d;
+        }
+      }
+      int dec = -1;
+      if (be >= 0 && best <= P.th_accept) {  // :110, :404, :1408, :1538
+        dec = be;
+        if (P.mode == 0 && lvl == lvl2 && best > __fmul_rn(P.nnratio, best2)) dec = -1;  // :112
+      }
+      if (dec != acc[i]) {
+        acc[i] = dec;
+        s_changed = 1;
+      }
+    }
+    for (int j = t; j < n_t; j += nt) nxt[j] = INT_MAX;
+    __syncthreads();
+    for (int i = t; i < nq; i += nt) {
+      const int e = acc[i];
+      if (e >= 0 && q[i].blocks) atomicMin(nxt + ent_j[e], i);
+    }
+    __syncthreads();
+    if (!s_changed) break;
+    __syncthreads();
+  }
+
+  // F.mvpMapPoints[bestIdx] = pMP: the last accepting query owns the keypoint
+  for (int i = t; i < nq; i += nt) {
+    const int e = acc[i];
+    if (e < 0) continue;
+    const int j = ent_j[e];
+    atomicMax(assign + j, i);
+    atomicAdd(&s_count, P.count_twice ? 2 : 1);  // :116-117
+    if (P.check_ori) atomicAdd(&s_hist[asdm_rot_bin(q[i].angle, kps_t[j].angle)], 1);  // :1413-1423
+  }
+  __syncthreads();
+  if (t == 0) {
+    int pruned = 0;
+    if (P.check_ori) {
+      asdm_three_maxima(s_hist, ASDM_HISTO_LENGTH, s_keep[0], s_keep[1], s_keep[2]);
+      for (int b = 0; b < ASDM_HISTO_LENGTH; b++)
+        if (b != s_keep[0] && b != s_keep[1] && b != s_keep[2]) pruned += s_hist[b];
+    }
+    *nmatches = s_count - pruned;
+  }
+  for (int i = t; i < nq; i += nt) {
+    const int e = acc[i];
+    if (e >= 0 && assign[ent_j[e]] == i) dist_t[ent_j[e]] = ent_d[e];
+  }
+  __syncthreads();
+  if (P.check_ori) {  // :1430-1449: every entry pushed into a pruned bin clears its keypoint
+    for (int i = t; i < nq; i += nt) {
+      const int e = acc[i];
+      if (e < 0) continue;
+      const int j = ent_j[e];
+      const int b = asdm_rot_bin(q[i].angle, kps_t[j].angle);
+      if (b != s_keep[0] && b != s_keep[1] && b != s_keep[2]) {
+        assign[j] = -1;
+        dist_t[j] = -1.f;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// SearchForInitialization (ORBmatcher.cc:416-531). Later queries may steal a keypoint from an earlier one
+// (:474-478) and vMatchedDistance gates candidates (:456), so the queries are replayed in order by ONE warp;
+// the 32 lanes share each query's candidate scan (two-minimum reduction with scan-order tie-breaking).
+__device__ __forceinline__ bool two_min_before(float d, int p, float d2, int p2) {
+  return d < d2 || (d == d2 && p < p2);
+}
+
+__global__ void __launch_bounds__(32) k_init_resolve(const asdm_kp* __restrict__ kps1, int n1,
+                                                     const asdm_kp* __restrict__ kps2, int n2,
+                                                     const ProjSeg* __restrict__ seg,
+                                                     const int32_t* __restrict__ ent_j,
+                                                     const float* __restrict__ ent_d, float nnratio, int check_ori,
+                                                     float* __restrict__ matched_dist /* [n2] */,
+                                                     int32_t* __restrict__ matches21 /* [n2] */,
+                                                     int32_t* __restrict__ matches12, float* __restrict__ dist12,
+                                                     int32_t* __restrict__ pushed /* [n1] bin of the push or -1 */,
+                                                     float* __restrict__ prev_matched,
+                                                     int32_t* __restrict__ nmatches_out) {
+  const int lane = threadIdx.x;
+  for (int j = lane; j < n2; j += 32) {
+    matched_dist[j] = 100.f;  // :427
+    matches21[j] = -1;
+  }
+  for (int i = lane; i < n1; i += 32) {
+    matches12[i] = -1;
+    dist12[i] = -1.f;
+    pushed[i] = -1;
+  }
+  __syncwarp();
+  int nmatches;
+  const int BIG = INT_MAX;
+  for (int i1 = 0; i1 < n1; i1++) {
+    const ProjSeg s = seg[i1];
+    if (s.cnt == 0) continue;  // level1 > 0 (:433-435) or empty window (:439)
+    // per-lane two smallest (distance, scan position) among admissible candidates
+    float b1 = 100.f, b2 = 100.f;
+    int p1 = BIG, p2 = BIG, j1 = -1;
+    for (int c = lane; c < s.cnt; c += 32) {
+      const int j = ent_j[s.off + c];
+      const float d = ent_d[s.off + c];
+      if (matched_dist[j] <= d) continue;  // :456
+      if (!(d < 100.f)) continue;          // cannot beat the initial best/second
+      if (two_min_before(d, c, b1, p1)) {
+        b2 = b1; p2 = p1;
+        b1 = d; p1 = c; j1 = j;
+      } else if (two_min_before(d, c, b2, p2)) {
+        b2 = d; p2 = c;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ob1 = __shfl_xor_sync(0xffffffffu, b1, o), ob2 = __shfl_xor_sync(0xffffffffu, b2, o);
+      const int op1 = __shfl_xor_sync(0xffffffffu, p1, o), op2 = __shfl_xor_sync(0xffffffffu, p2, o);
+      const int oj1 = __shfl_xor_sync(0xffffffffu, j1, o);
+      if (two_min_before(ob1, op1, b1, p1)) {
+        // other's best wins; second = min(my best, other's second)
+        if (two_min_before(b1, p1, ob2, op2)) { b2 = b1; p2 = p1; } else { b2 = ob2; p2 = op2; }
+        b1 = ob1; p1 = op1; j1 = oj1;
+      } else {
+        if (two_min_before(ob1, op1, b2, p2)) { b2 = ob1; p2 = op1; }
+      }
+    }
+    // all lanes hold the same (b1, j1, b2)
+    if (j1 >= 0 && b1 <= ASDM_TH_LOW && b1 < __fmul_rn(b2, nnratio)) {  // :470-472
+      if (lane == 0) {
+        const int prev = matches21[j1];
+        if (prev >= 0) {  // :474-478
+          matches12[prev] = -1;
+          dist12[prev] = -1.f;
+        }
+        matches12[i1] = j1;
+        dist12[i1] = b1;
+        matches21[j1] = i1;
+        matched_dist[j1] = b1;
+        if (check_ori) pushed[i1] = asdm_rot_bin(kps1[i1].angle, kps2[j1].angle);  // :486-496
+      }
+    }
+    __syncwarp();
+  }
+  // nmatches after the loop = accepts - steals (:477, :482) = queries that still hold a match
+  int live = 0;
+  for (int i = lane; i < n1; i += 32) live += matches12[i] >= 0 ? 1 : 0;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) live += __shfl_xor_sync(0xffffffffu, live, o);
+  nmatches = live;
+
+  if (check_ori) {  // :500-523
+    __shared__ int s_hist[ASDM_HISTO_LENGTH];
+    __shared__ int s_keep[3];
+    if (lane < ASDM_HISTO_LENGTH) s_hist[lane] = 0;
+    __syncwarp();
+    for (int i = lane; i < n1; i += 32)
+      if (pushed[i] >= 0) atomicAdd(&s_hist[pushed[i]], 1);  // stale entries still count in the bin sizes
+    __syncwarp();
+    if (lane == 0) asdm_three_maxima(s_hist, ASDM_HISTO_LENGTH, s_keep[0], s_keep[1], s_keep[2]);
+    __syncwarp();
+    int removed = 0;
+    for (int i = lane; i < n1; i += 32) {
+      const int b = pushed[i];
+      if (b < 0 || b == s_keep[0] || b == s_keep[1] || b == s_keep[2]) continue;
+      if (matches12[i] >= 0) {  // :515
+        matches12[i] = -1;
+        dist12[i] = -1.f;
+        removed++;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) removed += __shfl_xor_sync(0xffffffffu, removed, o);
+    nmatches -= removed;
+  }
+  __syncwarp();
+  for (int i = lane; i < n1; i += 32)  // :526-528
+    if (matches12[i] >= 0) {
+      prev_matched[2 * i] = kps2[matches12[i]].x;
+      prev_matched[2 * i + 1] = kps2[matches12[i]].y;
+    }
+  if (lane == 0) *nmatches_out = nmatches;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Descriptor stage of Frame::ComputeStereoMatches (Frame.cc:360-444). One warp per left keypoint: lanes test the
+// right keypoints in index order (vRowIndices[row] is filled in ascending iR, Frame.cc:378-388), compute the exact
+// distance of those inside the row band / octave / disparity gates and reduce to the first minimum.
+__global__ void __launch_bounds__(256) k_stereo_match(const float* __restrict__ desc_l,
+                                                      const asdm_kp* __restrict__ kps_l, int n_l,
+                                                      const float* __restrict__ desc_r,
+                                                      const asdm_kp* __restrict__ kps_r, int n_r,
+                                                      const float* __restrict__ scale_factors, int n_levels,
+                                                      int n_rows, float min_d, float max_d,
+                                                      int32_t* __restrict__ best_r, float* __restrict__ best_dist) {
+  const int lane = threadIdx.x & 31;
+  const int iL = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (iL >= n_l) return;
+  const asdm_kp kpL = kps_l[iL];
+  const float vL = kpL.y, uL = kpL.x;
+  int out_idx = -1;
+  float out_d = -1.f;
+  if (vL >= 0.f && vL < (float)n_rows) {
+    const int row = (int)vL;  // vRowIndices[vL] (Frame.cc:406)
+    const float minU = __fsub_rn(uL, max_d), maxU = __fsub_rn(uL, min_d);
+    if (!(maxU < 0.f)) {
+      float bd = ASDM_TH_HIGH;  // :417
+      int bi = INT_MAX;
+      for (int base = 0; base < n_r; base += 32) {
+        const int iR = base + lane;
+        if (iR < n_r) {
+          const asdm_kp kpR = kps_r[iR];
+          const int oc = min(max(kpR.octave, 0), n_levels - 1);
+          const float r = __fmul_rn(2.0f, scale_factors[oc]);
+          const int maxr = (int)ceilf(__fadd_rn(kpR.y, r));
+          const int minr = (int)floorf(__fsub_rn(kpR.y, r));
+          const bool in_band = row >= minr && row <= maxr;
+          const bool lvl_ok = !(kpR.octave < kpL.octave - 1 || kpR.octave > kpL.octave + 1);  // :428
+          if (in_band && lvl_ok && kpR.x >= minU && kpR.x <= maxU) {
+            const float d = asdm_exact_dist(desc_l + (size_t)iL * ASDM_DESC_DIM, desc_r + (size_t)iR * ASDM_DESC_DIM);
+            if (d < bd) {  // per lane indices ascend, so strict '<' keeps the first minimum
+              bd = d;
+              bi = iR;
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float od = __shfl_xor_sync(0xffffffffu, bd, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (od < bd || (od == bd && oi < bi)) {
+          bd = od;
+          bi = oi;
+        }
+      }
+      const int thOrbDist = (int)((ASDM_TH_HIGH + ASDM_TH_LOW) / 2);  // Frame.cc:366 -> 1
+      if (bi != INT_MAX && bd < (float)thOrbDist) {
+        out_idx = bi;
+        out_d = bd;
+      }
+    }
+  }
+  if (lane == 0) {
+    best_r[iL] = out_idx;
+    best_dist[iL] = out_d;
+  }
+}
+
+// Queries of SearchForInitialization: level-0 keypoints of F1 search F2 around their previous match
+// (ORBmatcher.cc:431-437).
+__global__ void __launch_bounds__(256) k_init_queries(const asdm_kp* __restrict__ kps1, int n1,
+                                                      const float* __restrict__ prev_matched, float window,
+                                                      asdm_proj_query* __restrict__ q) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n1) return;
+  const asdm_kp kp = kps1[i];
+  asdm_proj_query Q;
+  Q.valid = kp.octave > 0 ? 0 : 1;
+  Q.blocks = 0;
+  Q.pad = 0;
+  Q.u = prev_matched[2 * i];
+  Q.v = prev_matched[2 * i + 1];
+  Q.r = window;
+  Q.min_level = kp.octave;
+  Q.max_level = kp.octave;
+  Q.angle = kp.angle;
+  q[i] = Q;
+}

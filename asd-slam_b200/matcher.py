@@ -1,0 +1,297 @@
+"""Host-side mirror of the reference matcher interface over the C ABI (include/asdmatch.h).
+
+Names and argument meaning follow ORB_SLAM2::ORBmatcher (reference src/vslam/include/ORBmatcher.h:48-90):
+`ORBmatcher(nnratio, checkOri)` with SearchByBoW / SearchForTriangulation / SearchByProjection /
+SearchForInitialization.  Frame / KeyFrame state is passed as a `DescriptorSet` (device-resident descriptors,
+keypoints, grid, FeatureVector -- uploaded once, reference Frame.h:147 / KeyFrame.h:199) plus the small per-call
+masks the reference reads from MapPoint pointers.  MapPoint* never crosses the boundary: results are index arrays.
+
+Every call goes to libasdmatch_cuda.so; there is no CPU path in this package.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import (ASDM_JOB_BOW_KF_KF, ASDM_JOB_TRIANGULATION, ASDM_PROJ_BEST_ONLY, ASDM_PROJ_RATIO_LEVEL, KP_DTYPE,
+                   PROJ_QUERY_DTYPE, TH_HIGH, TH_LOW, AsdmError, FeatVec, Grid, JobDesc, ProjParams, ptr)
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _u8(a):
+    return np.ascontiguousarray(a, dtype=np.uint8)
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+class Context:
+    """One per GPU (asdm_create). Owns a CUDA stream; calls are serialised inside the library."""
+
+    def __init__(self, device=0):
+        self.lib = _lib.load()
+        h = C.c_void_p()
+        rc = self.lib.asdm_create(int(device), C.byref(h))
+        if rc != 0:
+            raise AsdmError(f"asdm_create(device={device}) failed with {rc}: no usable B200 "
+                            "(the matcher has no CPU fallback)")
+        self.h = h
+        self.device = int(device)
+
+    def check(self, rc):
+        if rc != 0:
+            raise AsdmError(f"libasdmatch_cuda error {rc}: {self.lib.asdm_last_error(self.h).decode()}")
+
+    def set_option(self, key, value):
+        self.check(self.lib.asdm_set_option(self.h, key.encode(), int(value)))
+
+    def stat(self, key):
+        v = C.c_int64()
+        self.check(self.lib.asdm_get_stat(self.h, key.encode(), C.byref(v)))
+        return v.value
+
+    def stream(self):
+        return self.lib.asdm_stream(self.h)
+
+    def set_stream(self, stream_ptr):
+        self.check(self.lib.asdm_set_stream(self.h, C.c_void_p(stream_ptr)))
+
+    def synchronize(self):
+        self.check(self.lib.asdm_synchronize(self.h))
+
+    def close(self):
+        if self.h:
+            self.lib.asdm_destroy(self.h)
+            self.h = None
+
+    def pinned(self, shape, dtype):
+        """numpy array backed by page-locked memory (asdm_host_alloc); keep the returned array alive."""
+        return PinnedArray(self.lib, shape, dtype).a
+
+
+class PinnedArray:
+    def __init__(self, lib, shape, dtype):
+        self.lib = lib
+        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        p = C.c_void_p()
+        if lib.asdm_host_alloc(C.byref(p), max(n, 1)) != 0:
+            raise AsdmError("asdm_host_alloc failed")
+        self.p = p
+        buf = (C.c_char * max(n, 1)).from_address(p.value)
+        self.a = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+        _PINNED.append(self)
+
+
+_PINNED = []  # pinned blocks live for the process (bench/test helper)
+
+
+class DescriptorSet:
+    """Device-resident descriptors (+ keypoints, grid, FeatureVector) of one Frame / KeyFrame / map-point pool."""
+
+    def __init__(self, ctx, desc, kps=None, grid=None, featvec=None):
+        self.ctx = ctx
+        desc = _f32(desc)
+        assert desc.ndim == 2 and desc.shape[1] == 128
+        self.n = desc.shape[0]
+        g = None
+        if grid is not None:
+            g = grid if isinstance(grid, Grid) else Grid(*grid)
+        if kps is not None:
+            kps = np.ascontiguousarray(kps, dtype=KP_DTYPE)
+            assert len(kps) == self.n
+        h = C.c_void_p()
+        ctx.check(ctx.lib.asdm_set_create(ctx.h, ptr(desc), self.n, 0, ptr(kps) if kps is not None else None,
+                                          C.byref(g) if g is not None else None, C.byref(h)))
+        self.h = h
+        if featvec is not None:
+            self.set_featvec(featvec)
+
+    def set_featvec(self, fv):
+        node_ids, off, idx = fv
+        node_ids = np.ascontiguousarray(node_ids, dtype=np.uint32)
+        off, idx = _i32(off), _i32(idx)
+        c = FeatVec(len(node_ids), ptr(node_ids), ptr(off), ptr(idx))
+        self.ctx.check(self.ctx.lib.asdm_set_featvec(self.h, C.byref(c)))
+
+    def read_desc(self, row0=0, n_rows=None):
+        n_rows = self.n - row0 if n_rows is None else n_rows
+        out = np.empty((n_rows, 128), np.float32)
+        self.ctx.check(self.ctx.lib.asdm_set_read_desc(self.h, row0, n_rows, ptr(out)))
+        return out
+
+    def retain(self):
+        self.ctx.lib.asdm_set_retain(self.h)
+
+    def release(self):
+        if self.h:
+            self.ctx.lib.asdm_set_release(self.h)
+            self.h = None
+
+
+class PairJob:
+    """Batched keyframe-pair search whose inputs are resident in HBM (asdm_job_*): the loop bodies of
+    LoopClosing.cc:291-318 (kind BOW_KF_KF) and LocalMapping.cc:335-370 (kind TRIANGULATION)."""
+
+    def __init__(self, ctx, kind, sets, masks, ia, ib, nnratio=0.6, check_ori=True, F12=None, epipoles=None,
+                 scale_factors=None, level_sigma2=None):
+        self.ctx = ctx
+        self.n_pairs = len(ia)
+        n_kf = len(sets)
+        self._keep = dict(masks=[_u8(m) for m in masks], ia=_i32(ia), ib=_i32(ib))
+        k = self._keep
+        set_arr = (C.c_void_p * n_kf)(*[s.h for s in sets])
+        mask_arr = (C.c_void_p * n_kf)(*[m.ctypes.data for m in k["masks"]])
+        d = JobDesc()
+        d.kind, d.n_kf, d.sets, d.masks = kind, n_kf, set_arr, mask_arr
+        d.n_pairs, d.ia, d.ib = self.n_pairs, ptr(k["ia"]), ptr(k["ib"])
+        d.nnratio, d.check_ori = float(nnratio), int(bool(check_ori))
+        if kind == ASDM_JOB_TRIANGULATION:
+            k["F12"], k["ep"] = _f32(F12).reshape(-1), _f32(epipoles).reshape(-1)
+            k["sf"], k["ls"] = _f32(scale_factors), _f32(level_sigma2)
+            d.F12, d.epipoles, d.scale_factors, d.level_sigma2 = ptr(k["F12"]), ptr(k["ep"]), ptr(k["sf"]), ptr(k["ls"])
+            d.n_levels = len(k["sf"])
+        h = C.c_void_p()
+        ctx.check(ctx.lib.asdm_job_prepare(ctx.h, C.byref(d), C.byref(h)))
+        self.h = h
+        self.stride = ctx.lib.asdm_job_out_stride(h)
+
+    def run(self):
+        self.ctx.check(self.ctx.lib.asdm_job_run(self.h))
+
+    def settle(self):
+        self.ctx.check(self.ctx.lib.asdm_job_settle(self.h))
+
+    def fetch(self, match=None, dist=None, nm=None):
+        P, S = self.n_pairs, self.stride
+        match = np.empty((P, S), np.int32) if match is None else match
+        dist = np.empty((P, S), np.float32) if dist is None else dist
+        nm = np.empty(P, np.int32) if nm is None else nm
+        self.ctx.check(self.ctx.lib.asdm_job_fetch(self.h, ptr(match), ptr(dist), ptr(nm)))
+        return nm, match, dist
+
+    def device_outputs(self):
+        m, d, n = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        self.ctx.check(self.ctx.lib.asdm_job_device_outputs(self.h, C.byref(m), C.byref(d), C.byref(n)))
+        return m.value, d.value, n.value
+
+    def destroy(self):
+        if self.h:
+            self.ctx.lib.asdm_job_destroy(self.h)
+            self.h = None
+
+
+class ORBmatcher:
+    """ORB_SLAM2::ORBmatcher(nnratio=0.6, checkOri=true) (reference ORBmatcher.h:45)."""
+
+    TH_LOW = TH_LOW
+    TH_HIGH = TH_HIGH
+
+    def __init__(self, ctx, nnratio=0.6, checkOri=True):
+        self.ctx = ctx
+        self.mfNNratio = float(nnratio)
+        self.mbCheckOrientation = bool(checkOri)
+
+    # -- SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches)            ORBmatcher.cc:156-297
+    def SearchByBoW_KF_F(self, kf, valid_kf, f):
+        valid_kf = _u8(valid_kf)
+        match = np.empty(f.n, np.int32)
+        dist = np.empty(f.n, np.float32)
+        nm = C.c_int32()
+        c = self.ctx
+        c.check(c.lib.asdm_search_by_bow_kf_f(c.h, kf.h, ptr(valid_kf), f.h, self.mfNNratio,
+                                              int(self.mbCheckOrientation), ptr(match), ptr(dist), C.byref(nm)))
+        return nm.value, match, dist
+
+    # -- SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12)               ORBmatcher.cc:533-666
+    def SearchByBoW_KF_KF(self, kf1, valid1, kf2, valid2):
+        valid1, valid2 = _u8(valid1), _u8(valid2)
+        match = np.empty(kf1.n, np.int32)
+        dist = np.empty(kf1.n, np.float32)
+        nm = C.c_int32()
+        c = self.ctx
+        c.check(c.lib.asdm_search_by_bow_kf_kf(c.h, kf1.h, ptr(valid1), kf2.h, ptr(valid2), self.mfNNratio,
+                                               int(self.mbCheckOrientation), ptr(match), ptr(dist), C.byref(nm)))
+        return nm.value, match, dist
+
+    # -- SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo)   ORBmatcher.cc:669-822
+    def SearchForTriangulation(self, kf1, has_mp1, kf2, has_mp2, F12, ex, ey, scale_factors2, level_sigma2_2):
+        has_mp1, has_mp2 = _u8(has_mp1), _u8(has_mp2)
+        F12, sf, ls = _f32(F12).reshape(9), _f32(scale_factors2), _f32(level_sigma2_2)
+        match = np.empty(kf1.n, np.int32)
+        dist = np.empty(kf1.n, np.float32)
+        nm = C.c_int32()
+        c = self.ctx
+        c.check(c.lib.asdm_search_for_triangulation(c.h, kf1.h, ptr(has_mp1), kf2.h, ptr(has_mp2), ptr(F12),
+                                                    float(ex), float(ey), ptr(sf), ptr(ls), len(sf),
+                                                    int(self.mbCheckOrientation), ptr(match), ptr(dist),
+                                                    C.byref(nm)))
+        return nm.value, match, dist
+
+    # -- the descriptor loop shared by the four SearchByProjection overloads
+    def SearchByProjection(self, target, queries, desc_q=None, q_set=None, q_rows=None, blocked0=None,
+                           mode=ASDM_PROJ_BEST_ONLY, th_accept=TH_HIGH, best_init=256.0, count_twice=False,
+                           check_ori=None):
+        queries = np.ascontiguousarray(queries, dtype=PROJ_QUERY_DTYPE)
+        nq = len(queries)
+        dq = _f32(desc_q) if desc_q is not None else None
+        rows = _i32(q_rows) if q_rows is not None else None
+        b0 = _u8(blocked0) if blocked0 is not None else None
+        co = self.mbCheckOrientation if check_ori is None else check_ori
+        p = ProjParams(int(mode), float(th_accept), float(best_init), self.mfNNratio, int(bool(co)),
+                       int(bool(count_twice)))
+        assign = np.empty(target.n, np.int32)
+        dist = np.empty(target.n, np.float32)
+        nm = C.c_int32()
+        c = self.ctx
+        c.check(c.lib.asdm_search_by_projection(c.h, target.h, ptr(queries), nq, ptr(dq),
+                                                q_set.h if q_set is not None else None, ptr(rows), ptr(b0),
+                                                C.byref(p), ptr(assign), ptr(dist), C.byref(nm)))
+        return nm.value, assign, dist
+
+    # -- SearchByProjection(Frame&, vector<MapPoint*>&, th)           ORBmatcher.cc:44-122
+    @staticmethod
+    def RadiusByViewingCos(view_cos):  # ORBmatcher.cc:126-132
+        return np.where(np.asarray(view_cos, np.float32).astype(np.float64) > 0.998, np.float32(2.5), np.float32(4.0))
+
+    def SearchByProjection_LocalMap(self, F, track_in_view, proj_x, proj_y, scale_level, view_cos, blocks, desc_mp,
+                                    scale_factors, th=1.0, blocked0=None):
+        """F: DescriptorSet of the frame; per map point the MapPoint::mTrack* fields (MapPoint.h:95-100)."""
+        n = len(proj_x)
+        q = np.zeros(n, PROJ_QUERY_DTYPE)
+        lvl = _i32(scale_level)
+        r = self.RadiusByViewingCos(view_cos).astype(np.float32)
+        if th != 1.0:
+            r = (r * np.float32(th)).astype(np.float32)
+        q["valid"] = _u8(track_in_view)
+        q["blocks"] = _u8(blocks)
+        q["u"], q["v"] = _f32(proj_x), _f32(proj_y)
+        q["r"] = (r * _f32(scale_factors)[lvl]).astype(np.float32)
+        q["min_level"], q["max_level"] = lvl - 1, lvl
+        return self.SearchByProjection(F, q, desc_q=desc_mp, blocked0=blocked0, mode=ASDM_PROJ_RATIO_LEVEL,
+                                       th_accept=TH_HIGH, best_init=256.0, count_twice=True, check_ori=False)
+
+    # -- SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)   ORBmatcher.cc:416-531
+    def SearchForInitialization(self, F1, F2, vbPrevMatched, windowSize=10):
+        prev = np.array(vbPrevMatched, dtype=np.float32, copy=True).reshape(-1)
+        match = np.empty(F1.n, np.int32)
+        dist = np.empty(F1.n, np.float32)
+        nm = C.c_int32()
+        c = self.ctx
+        c.check(c.lib.asdm_search_for_initialization(c.h, F1.h, F2.h, ptr(prev), int(windowSize), self.mfNNratio,
+                                                     int(self.mbCheckOrientation), ptr(match), ptr(dist),
+                                                     C.byref(nm)))
+        return nm.value, match, dist, prev.reshape(-1, 2)
+
+    # -- descriptor stage of Frame::ComputeStereoMatches              Frame.cc:360-444
+    def StereoRowMatch(self, left, right, scale_factors, n_rows, min_d, max_d):
+        sf = _f32(scale_factors)
+        best = np.empty(left.n, np.int32)
+        dist = np.empty(left.n, np.float32)
+        c = self.ctx
+        c.check(c.lib.asdm_stereo_row_match(c.h, left.h, right.h, ptr(sf), len(sf), int(n_rows), float(min_d),
+                                            float(max_d), ptr(best), ptr(dist)))
+        return best, dist

@@ -1,0 +1,218 @@
+/*
+ * asdmatch.h -- C ABI of libasdmatch_cuda.so: B200-native (sm_100a) ASD descriptor matching.
+ *
+ * Drop-in boundary for the one data-parallel hot path of mataiyuan/ASD-SLAM: the descriptor loops of
+ * ORB_SLAM2::ORBmatcher (reference src/vslam/include/ORBmatcher.h:48-90, src/vslam/src/ORBmatcher.cc).
+ * The reference has no FFI for this path: ORBmatcher is a C++ class inside
+ * libvslam.so.  The C++ adaptor asd-slam_b200/host/ORBmatcher.{h,cc} keeps that class's method names
+ * and argument meaning and marshals Frame / KeyFrame / MapPoint state into the flat calls below;
+ * INTEGRATION.md shows the binding a maintainer adds to the reference.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; no torch / OpenCV types; MapPoint* never crosses the boundary
+ *    (the adaptor maps indices back to pointers);
+ *  - every function returns ASDM_OK (0) or a negative error code and never throws;
+ *    asdm_last_error() gives the message of the last failure on that context;
+ *  - host buffers are caller-owned; device buffers are library-owned (asdm_set, asdm_job);
+ *  - a context owns one CUDA stream; calls on one context are serialised by an internal mutex, so
+ *    the three ORB-SLAM2 threads may share it; use one context per GPU;
+ *  - there is NO CPU fallback: without a CUDA device asdm_create fails with ASDM_ERR_CUDA.
+ *
+ * Result contract: index lists are bit-identical to the reference's CPU matcher on the same inputs;
+ * returned distances are the reference's own fp32 values (sequential index-ascending accumulation of
+ * (a-b)*(a-b), no FMA: ORBmatcher.cc:1637-1644).
+ */
+#ifndef ASDMATCH_H
+#define ASDMATCH_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ASDM_DESC_DIM 128     /* ASD descriptors: N x 128 CV_32FC1 (ORBextractor.cc:1209) */
+#define ASDM_HISTO_LENGTH 30  /* ORBmatcher.cc:39 */
+#define ASDM_TH_LOW 0.5f      /* ORBmatcher.cc:38 */
+#define ASDM_TH_HIGH 1.5f     /* ORBmatcher.cc:37 */
+
+enum {
+  ASDM_OK = 0,
+  ASDM_ERR_INVALID = -1,     /* bad argument */
+  ASDM_ERR_CUDA = -2,        /* CUDA runtime / driver failure (including: no device) */
+  ASDM_ERR_OOM = -3,
+  ASDM_ERR_INTERNAL = -4
+};
+
+typedef struct asdm_ctx asdm_ctx;
+typedef struct asdm_set asdm_set; /* device-resident descriptors + keypoints + grid of one Frame / KeyFrame */
+typedef struct asdm_job asdm_job; /* a prepared batched search whose inputs are resident in HBM */
+
+/* cv::KeyPoint fields the matcher reads (mvKeysUn[i].pt.x, .pt.y, .angle, .octave) */
+typedef struct {
+  float x, y, angle;
+  int32_t octave;
+} asdm_kp;
+
+/* Frame/KeyFrame grid geometry: Frame.h:37-38 (64x48), Frame.cc:34, KeyFrame.h:217-220.
+ * KeyFrame's integer bounds are passed converted to float (exact). */
+typedef struct {
+  float min_x, min_y, max_x, max_y;
+  float inv_w, inv_h;
+  int32_t cols, rows;
+} asdm_grid;
+
+/* DBoW2::FeatureVector (src/dbow2/include/FeatureVector.h:21-22) as CSR: ascending node ids,
+ * idx[off[k]..off[k+1]) = feature indices of node k in insertion order. A feature appears at most once
+ * (TemplatedVocabulary.h:1125-1192 adds each feature to one node, or to none when its word is stopped). */
+typedef struct {
+  int32_t n_nodes;
+  const uint32_t* node_ids;
+  const int32_t* off;
+  const int32_t* idx;
+} asdm_featvec;
+
+/* ---------------------------------------------------------------------------------------- context */
+int asdm_create(int device, asdm_ctx** out);
+int asdm_destroy(asdm_ctx* ctx);
+const char* asdm_last_error(const asdm_ctx* ctx);
+void* asdm_stream(asdm_ctx* ctx); /* the context's cudaStream_t, for event timing by the caller */
+int asdm_synchronize(asdm_ctx* ctx);
+/* run on a caller-owned cudaStream_t instead (e.g. the stream an NCCL all-gather of the results is queued on) */
+int asdm_set_stream(asdm_ctx* ctx, void* stream);
+/* page-locked host memory for inputs / results, so that the copies inside the calls are true async DMA */
+int asdm_host_alloc(void** out, size_t bytes);
+int asdm_host_free(void* p);
+/* options: "force_exact" (1 = skip the tensor-core shortlist and compute every gated pair in exact fp32),
+ *          "cand_cap" (initial per-query candidate slots; grows automatically on overflow) */
+int asdm_set_option(asdm_ctx* ctx, const char* key, int value);
+/* counters of the last call/run on this context: "gpu_launches", "cand_cap", "retries", "tc_used" */
+int asdm_get_stat(asdm_ctx* ctx, const char* key, int64_t* value);
+
+/* ---------------------------------------------------------- descriptor sets (Frame.h:147, KeyFrame.h:199) */
+/* Uploads once: fp32 rows (512 B, padded), the bf16 tensor-core copy and row norms, the keypoint SoA and
+ * the 64x48 grid bucket (PosInGrid/AssignFeaturesToGrid, Frame.cc:123-138, 276-286). kps/grid may be NULL
+ * for a pure descriptor pool (map-point descriptors). Refcounted: Frame copies and KeyFrame clones
+ * (Frame.cc:47, KeyFrame.cc:153) retain instead of re-uploading. */
+int asdm_set_create(asdm_ctx* ctx, const float* desc, int n, int row_stride_bytes, const asdm_kp* kps,
+                    const asdm_grid* grid, asdm_set** out);
+int asdm_set_retain(asdm_set* set);
+int asdm_set_release(asdm_set* set);
+int asdm_set_size(const asdm_set* set);
+/* attaches Frame::mFeatVec / KeyFrame::mFeatVec (after ComputeBoW, Frame.cc:289-296) */
+int asdm_set_featvec(asdm_set* set, const asdm_featvec* fv);
+/* reads rows back (map save / checkpoint: System.cc:296-439 writes descriptors from host Mats) */
+int asdm_set_read_desc(asdm_set* set, int row0, int n_rows, float* out);
+
+/* --------------------------------------------------------------------------- BoW-gated dense search */
+/* ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches)  (ORBmatcher.cc:156-297).
+ * valid_kf[i]: KF feature i holds a map point that is not bad.
+ * match_f[j] (n_f entries): KF feature whose map point is assigned to frame feature j, or -1.
+ * dist_f may be NULL. *nmatches = return value of the reference. */
+int asdm_search_by_bow_kf_f(asdm_ctx* ctx, asdm_set* kf, const uint8_t* valid_kf, asdm_set* f, float nnratio,
+                            int check_ori, int32_t* match_f, float* dist_f, int32_t* nmatches);
+
+/* ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12)  (ORBmatcher.cc:533-666).
+ * match12[i] (n1 entries): feature of KF2 matched to feature i of KF1, or -1. */
+int asdm_search_by_bow_kf_kf(asdm_ctx* ctx, asdm_set* kf1, const uint8_t* valid1, asdm_set* kf2,
+                             const uint8_t* valid2, float nnratio, int check_ori, int32_t* match12, float* dist12,
+                             int32_t* nmatches);
+
+/* ORBmatcher::SearchForTriangulation (ORBmatcher.cc:669-822; CheckDistEpipolarLine :136-153).
+ * has_mp1/2[i]: feature already holds a map point. F12 row-major 3x3; (ex,ey) = epipole in image 2
+ * (:675-682). scale_factors2 / level_sigma2_2: pKF2->mvScaleFactors / mvLevelSigma2 (n_levels entries).
+ * Pairs = {(i, match12[i]) : match12[i] >= 0}, ascending i (:814-819). */
+int asdm_search_for_triangulation(asdm_ctx* ctx, asdm_set* kf1, const uint8_t* has_mp1, asdm_set* kf2,
+                                  const uint8_t* has_mp2, const float* F12, float ex, float ey,
+                                  const float* scale_factors2, const float* level_sigma2_2, int n_levels,
+                                  int check_ori, int32_t* match12, float* dist12, int32_t* nmatches);
+
+/* ----------------------------------------------------------------------- projection-gated searches */
+/* Common descriptor loop of the four ORBmatcher::SearchByProjection overloads (ORBmatcher.cc:44-122, 300-413,
+ * 1318-1452, 1455-1582). The adaptor supplies, per query, what the reference derives from poses and map points
+ * before it reaches GetFeaturesInArea: the window (u, v, r), the octave range handed to Frame::GetFeaturesInArea
+ * (Frame.cc:219-274; KeyFrame::GetFeaturesInArea has none: min_level = max_level = -1), whether the query's map
+ * point blocks the keypoint for later queries (Observations()>0) and the query angle for the histogram. */
+typedef struct {
+  uint8_t valid;  /* query survived the reference's pre-descriptor gates (mbTrackInView, !isBad, in image ...) */
+  uint8_t blocks; /* once assigned, later queries skip that keypoint (:86-88, :1393-1395) */
+  int16_t pad;
+  float u, v, r;
+  int32_t min_level, max_level;
+  float angle;
+} asdm_proj_query;
+
+enum {
+  ASDM_PROJ_RATIO_LEVEL = 0, /* :44-122  best & second with octaves; ratio test only when both share an octave */
+  ASDM_PROJ_BEST_ONLY = 1    /* :300-413, :1318-1452, :1455-1582 */
+};
+
+typedef struct {
+  int32_t mode;
+  float th_accept;     /* accept if best <= th_accept: TH_HIGH (:110, :1408), ORBdist (:1538), TH_LOW (:404) */
+  float best_init;     /* 256 (:75, :380, :1518) or 100 (:1387) */
+  float nnratio;       /* mode RATIO_LEVEL only */
+  int32_t check_ori;   /* rotation histogram (:1413-1449, :1543-1579) */
+  int32_t count_twice; /* :116-117 increments nmatches twice */
+} asdm_proj_params;
+
+/* target: set with keypoints + grid (the Frame / KeyFrame searched). Query descriptors: either desc_q (host,
+ * nq x 128, e.g. MapPoint::GetDescriptor of each local map point) or rows q_rows[i] of the resident set q_set
+ * (q_rows NULL = row i). blocked0[j] (may be NULL): keypoint j unavailable from the start.
+ * assign[j] (target->n entries) = query finally assigned to keypoint j, or -1. *nmatches = reference's return. */
+int asdm_search_by_projection(asdm_ctx* ctx, asdm_set* target, const asdm_proj_query* q, int nq, const float* desc_q,
+                              asdm_set* q_set, const int32_t* q_rows, const uint8_t* blocked0,
+                              const asdm_proj_params* p, int32_t* assign, float* dist_t, int32_t* nmatches);
+
+/* ORBmatcher::SearchForInitialization (ORBmatcher.cc:416-531). prev_matched: 2*n1 floats (x,y), read and rewritten
+ * (:526-528). matches12[i] (n1 entries) = index in F2 or -1. */
+int asdm_search_for_initialization(asdm_ctx* ctx, asdm_set* f1, asdm_set* f2, float* prev_matched, int window_size,
+                                   float nnratio, int check_ori, int32_t* matches12, float* dist12, int32_t* nmatches);
+
+/* Descriptor stage of Frame::ComputeStereoMatches (Frame.cc:360-444): left keypoints = mvKeys, right = mvKeysRight.
+ * best_r[i] = right index when bestDist < thOrbDist, else -1. */
+int asdm_stereo_row_match(asdm_ctx* ctx, asdm_set* left, asdm_set* right, const float* scale_factors, int n_levels,
+                          int n_rows, float min_d, float max_d, int32_t* best_r, float* best_dist);
+
+/* ------------------------------------------------------------------ batched keyframe-pair jobs */
+/* Loop bodies of LoopClosing.cc:291-318 (kind BOW_KF_KF) and LocalMapping.cc:335-370 (kind TRIANGULATION)
+ * over independent keyframe pairs (ia[p], ib[p]) drawn from n_kf keyframes. masks[k] = valid (BoW) or
+ * has_mp (triangulation) of keyframe k. prepare() uploads the per-call inputs; run() launches the kernels
+ * on the context stream without synchronising; fetch() copies results to the host (row stride
+ * asdm_job_out_stride()) and synchronises. Pairs pair_begin..pair_end-1 are processed (sharding by rank). */
+enum { ASDM_JOB_BOW_KF_KF = 1, ASDM_JOB_TRIANGULATION = 2 };
+
+typedef struct {
+  int32_t kind;
+  int32_t n_kf;
+  asdm_set* const* sets;        /* n_kf */
+  const uint8_t* const* masks;  /* n_kf */
+  int32_t n_pairs;
+  const int32_t* ia;
+  const int32_t* ib;
+  float nnratio;                /* BoW */
+  int32_t check_ori;
+  const float* F12;             /* triangulation: 9*n_pairs */
+  const float* epipoles;        /* triangulation: 2*n_pairs */
+  const float* scale_factors;   /* triangulation: n_levels */
+  const float* level_sigma2;    /* triangulation: n_levels */
+  int32_t n_levels;
+} asdm_job_desc;
+
+int asdm_job_prepare(asdm_ctx* ctx, const asdm_job_desc* desc, asdm_job** out);
+int asdm_job_run(asdm_job* job);
+int asdm_job_fetch(asdm_job* job, int32_t* match12, float* dist12, int32_t* nmatches);
+/* waits for the last run and, if a candidate pool overflowed, grows it and runs again; after it returns the device
+ * outputs are final (fetch() calls it) */
+int asdm_job_settle(asdm_job* job);
+int asdm_job_out_stride(const asdm_job* job);
+/* device pointers of the results (match12: n_pairs*stride int32, dist12: same float, nmatches: n_pairs),
+ * e.g. for an NCCL all-gather by the caller */
+int asdm_job_device_outputs(asdm_job* job, void** match12, void** dist12, void** nmatches);
+int asdm_job_destroy(asdm_job* job);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

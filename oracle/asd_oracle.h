@@ -1,0 +1,183 @@
+/*
+ * asd_oracle.h -- CPU ORACLE for the ASD descriptor-matching hot path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Nothing under oracle/ is part of the product: only tests/,
+ * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load this
+ * library, and there only as the checker or the timed CPU baseline.  The product
+ * (libasdmatch_cuda.so) never links, loads or calls it.
+ *
+ * It restates, over flat arrays, the reference matcher of mataiyuan/ASD-SLAM
+ * (src/vslam/src/ORBmatcher.cc, Frame.cc, KeyFrame.cc).  Every function cites the reference
+ * file:line it follows.  Parity status: PINNED against the reference's own ORBmatcher.cc
+ * compiled from where it lies (oracle/_ref, see oracle/Makefile `ref` target and
+ * tests/test_oracle_vs_ref.py).  The reference holds no golden vectors for this path
+ * (SURVEY.md section 4).
+ *
+ * Float environment: the reference was built by GCC 5.4 with only --std=c++11 on x86-64, i.e.
+ * scalar SSE fp32, round-to-nearest, no FMA contraction, no reassociation.  This file must be
+ * compiled with -ffp-contract=off -fno-fast-math (oracle/Makefile does).
+ */
+#ifndef ASD_ORACLE_H
+#define ASD_ORACLE_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORA_DESC_DIM 128
+#define ORA_HISTO_LENGTH 30 /* ORBmatcher.cc:39 */
+
+/* cv::KeyPoint fields the matcher reads: mvKeysUn[i].pt.x/.pt.y/.angle/.octave */
+typedef struct {
+  float x, y, angle;
+  int32_t octave;
+} ora_kp;
+
+/* Frame/KeyFrame grid geometry (Frame.h:37-38; Frame.cc:34; KeyFrame.h:217-220).
+ * KeyFrame keeps integer bounds; they enter every expression converted to float, so a float
+ * copy is exact. */
+typedef struct {
+  float min_x, min_y, max_x, max_y;
+  float inv_w, inv_h; /* mfGridElementWidthInv / HeightInv */
+  int32_t cols, rows; /* 64 x 48 */
+} ora_grid;
+
+/* DBoW2::FeatureVector (src/dbow2/include/FeatureVector.h:21-22) flattened to CSR:
+ * node ids ascending; idx[off[k]..off[k+1]) are the feature indices of node k in
+ * insertion (= ascending feature index) order. */
+typedef struct {
+  int32_t n_nodes;
+  const uint32_t* node_ids;
+  const int32_t* off;
+  const int32_t* idx;
+} ora_featvec;
+
+/* a1: ORBmatcher::DescriptorDistance (ORBmatcher.cc:1629-1650) */
+float ora_descriptor_distance(const float* a, const float* b);
+
+/* a12: ORBmatcher::ComputeThreeMaxima (ORBmatcher.cc:1584-1625) on bin sizes */
+void ora_compute_three_maxima(const int32_t* sizes, int L, int32_t* ind1, int32_t* ind2, int32_t* ind3);
+
+/* rotation-bin idiom (e.g. ORBmatcher.cc:245-252) */
+int ora_rot_bin(float angle1, float angle2);
+
+/* a3: Frame::PosInGrid + AssignFeaturesToGrid (Frame.cc:123-138, 276-286; KeyFrame.cc:116-143).
+ * cell_start has cols*rows+1 entries (cell = ix*rows+iy), cell_items up to n entries,
+ * cell_of[i] = ix*rows+iy or -1 when the keypoint falls outside the grid. */
+void ora_assign_features_to_grid(const ora_kp* kps, int n, const ora_grid* g, int32_t* cell_start,
+                                 int32_t* cell_items, int32_t* cell_of);
+
+/* a3: Frame::GetFeaturesInArea (Frame.cc:219-274).  KeyFrame::GetFeaturesInArea
+ * (KeyFrame.cc:839-878) is the same scan with min_level = max_level = -1.
+ * Returns the number of indices written to out (scan order). */
+int ora_get_features_in_area(const ora_kp* kps, int n, const ora_grid* g, const int32_t* cell_start,
+                             const int32_t* cell_items, float x, float y, float r, int min_level,
+                             int max_level, int32_t* out);
+
+/* a8: SearchByBoW(KeyFrame*, Frame&, out) (ORBmatcher.cc:156-297).
+ * valid_kf[i] = KF feature i holds a map point that is not bad.
+ * match_f[j] (size n_f) = KF feature index whose map point was assigned to frame feature j, or -1.
+ * Returns nmatches. */
+int ora_search_by_bow_kf_f(const float* desc_kf, const ora_kp* kps_kf, int n_kf, const ora_featvec* fv_kf,
+                           const uint8_t* valid_kf, const float* desc_f, const ora_kp* kps_f, int n_f,
+                           const ora_featvec* fv_f, float nnratio, int check_ori, int32_t* match_f,
+                           float* dist_f);
+
+/* a9: SearchByBoW(KeyFrame*, KeyFrame*, out) (ORBmatcher.cc:533-666).
+ * match12[i] (size n1) = feature index in KF2 or -1. Returns nmatches. */
+int ora_search_by_bow_kf_kf(const float* desc1, const ora_kp* kps1, int n1, const ora_featvec* fv1,
+                            const uint8_t* valid1, const float* desc2, const ora_kp* kps2, int n2,
+                            const ora_featvec* fv2, const uint8_t* valid2, float nnratio, int check_ori,
+                            int32_t* match12, float* dist12);
+
+/* a11: SearchForTriangulation (ORBmatcher.cc:669-822) with CheckDistEpipolarLine (:136-153).
+ * has_mp1/2[i] = feature already holds a map point (such features are skipped).
+ * F12 row-major 3x3; (ex,ey) epipole in image 2 (:675-682, computed by the caller);
+ * scale_factors2 / level_sigma2_2 = pKF2->mvScaleFactors / mvLevelSigma2.
+ * match12[i] (size n1) = idx2 or -1. Returns nmatches. */
+int ora_search_for_triangulation(const float* desc1, const ora_kp* kps1, int n1, const ora_featvec* fv1,
+                                 const uint8_t* has_mp1, const float* desc2, const ora_kp* kps2, int n2,
+                                 const ora_featvec* fv2, const uint8_t* has_mp2, const float* F12, float ex,
+                                 float ey, const float* scale_factors2, const float* level_sigma2_2,
+                                 int check_ori, int32_t* match12, float* dist12);
+
+/* Generic projection-gated search: the common body of the four SearchByProjection overloads
+ * (ORBmatcher.cc:44-122, 300-413, 1318-1452, 1455-1582).  The caller supplies, per query, what
+ * the reference derives from poses / map points before it reaches the descriptor loop. */
+enum {
+  ORA_PROJ_RATIO_LEVEL = 0, /* :44-122  best & second with octaves, TH_HIGH, ratio only when same octave */
+  ORA_PROJ_BEST_ONLY = 1    /* :300-413, :1318-1452, :1455-1582  best only */
+};
+typedef struct {
+  int32_t mode;
+  float th_accept;     /* accept if best <= th_accept (TH_HIGH, ORBdist or TH_LOW) */
+  float best_init;     /* 256 (:75, :380, :1518) or 100 (:1387) */
+  float nnratio;       /* mode RATIO_LEVEL only */
+  int32_t check_ori;   /* rotation histogram on (:1413-1449, :1543-1579) */
+  int32_t count_twice; /* :116-117 increments nmatches twice */
+} ora_proj_params;
+
+typedef struct {
+  uint8_t valid;  /* query survived the reference's pre-descriptor gates */
+  uint8_t blocks; /* assigned map point has Observations()>0 (or: any non-null blocks) */
+  int16_t pad;
+  float u, v, r;  /* window centre and half-size handed to GetFeaturesInArea */
+  int32_t min_level, max_level;
+  float angle;    /* query keypoint angle for the rotation histogram */
+} ora_proj_query;
+
+/* blocked0[j] = target keypoint j is unavailable from the start.
+ * assign[j] (size n_t) = query index finally assigned to keypoint j, or -1 if untouched/pruned.
+ * Returns nmatches (doubled when count_twice). */
+int ora_search_by_projection(const float* desc_t, const ora_kp* kps_t, int n_t, const ora_grid* g,
+                             const ora_proj_query* q, const float* desc_q, int n_q, const uint8_t* blocked0,
+                             const ora_proj_params* p, int32_t* assign, float* dist_t);
+
+/* a4 helper: ORBmatcher::RadiusByViewingCos (ORBmatcher.cc:126-132) and the window of :62-68 */
+float ora_radius_by_viewing_cos(float view_cos);
+float ora_local_map_window(float view_cos, float th, float scale_factor);
+
+/* MapPoint::PredictScale (MapPoint.cc:421-453) */
+int ora_predict_scale(float max_distance, float current_dist, float log_scale_factor, int n_levels);
+
+/* a10: SearchForInitialization (ORBmatcher.cc:416-531).
+ * prev_matched (2*n1 floats, x,y interleaved) is read and rewritten (:526-528).
+ * matches12[i] (size n1) = idx2 or -1. Returns nmatches. */
+int ora_search_for_initialization(const float* desc1, const ora_kp* kps1, int n1, const float* desc2,
+                                  const ora_kp* kps2, int n2, const ora_grid* g2, float* prev_matched,
+                                  int window_size, float nnratio, int check_ori, int32_t* matches12,
+                                  float* dist12);
+
+/* Descriptor stage of Frame::ComputeStereoMatches (Frame.cc:360-444; dead code upstream, BASELINE config 3).
+ * kps_l = mvKeys, kps_r = mvKeysRight.  best_r[i] = right index when bestDist < thOrbDist, else -1.
+ * Rows outside [0,n_rows) are skipped (the reference would index out of bounds). */
+void ora_stereo_row_match(const float* desc_l, const ora_kp* kps_l, int n_l, const float* desc_r,
+                          const ora_kp* kps_r, int n_r, const float* scale_factors, int n_rows, float min_d,
+                          float max_d, int32_t* best_r, float* best_dist);
+
+/* Batched drivers for BASELINE configs 4 and 5 (the loop bodies of LocalMapping.cc:335-370 and
+ * LoopClosing.cc:291-318): pair p uses keyframes ia[p], ib[p] out of n_kf keyframes that all
+ * hold n features. threads>1 runs pairs on OpenMP threads (pairs are independent). */
+typedef struct {
+  const float* desc;     /* n x 128 */
+  const ora_kp* kps;     /* n */
+  const ora_featvec* fv;
+  const uint8_t* mask;   /* valid (config 5) or has_mp (config 4) */
+} ora_keyframe;
+
+void ora_batch_bow_kf_kf(const ora_keyframe* kfs, int n, const int32_t* ia, const int32_t* ib, int n_pairs,
+                         float nnratio, int check_ori, int threads, int32_t* match12 /* n_pairs*n */,
+                         float* dist12, int32_t* nmatches /* n_pairs */);
+void ora_batch_triangulation(const ora_keyframe* kfs, int n, const int32_t* ia, const int32_t* ib, int n_pairs,
+                             const float* F12 /* 9*n_pairs */, const float* epipoles /* 2*n_pairs */,
+                             const float* scale_factors, const float* level_sigma2, int check_ori, int threads,
+                             int32_t* match12, float* dist12, int32_t* nmatches);
+
+int ora_max_threads(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,322 @@
+"""GPU parity: libasdmatch_cuda.so (through the C ABI) against the CPU oracle on the same seeded inputs.
+
+Bar (BASELINE.json north_star): match index lists bit-exact; distances are the reference's own fp32 values, so they
+are compared bit-exactly too (tolerance stated: 0, tighter than the 1e-5 relative the north star allows).
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _sets_pair(pkg, ctx, c):
+    A = pkg.DescriptorSet(ctx, c["desc_a"], c["kps_a"], c["grid"], c["fv_a"])
+    B = pkg.DescriptorSet(ctx, c["desc_b"], c["kps_b"], c["grid"], c["fv_b"])
+    return A, B
+
+
+def _eq(a, b, what):
+    a, b = np.asarray(a), np.asarray(b)
+    assert a.shape == b.shape, what
+    bad = np.nonzero(a != b)[0] if a.ndim == 1 else np.argwhere(a != b)
+    assert len(bad) == 0, f"{what}: {len(bad)} mismatches, first at {bad[:5].tolist()}: {a[tuple(bad[0].T)] if a.ndim > 1 else a[bad[:5]]} vs {b[tuple(bad[0].T)] if b.ndim > 1 else b[bad[:5]]}"
+
+
+def _eq_dist(a, b, what):
+    # bit-exact comparison of fp32 distances (tolerance 0)
+    _eq(np.asarray(a, np.float32).view(np.uint32), np.asarray(b, np.float32).view(np.uint32), what)
+
+
+# ------------------------------------------------------------------------------------------------ sets
+def test_set_roundtrip_and_grid(pkg, ctx, oracle):
+    c = pkg.synth.config1(777, 500)
+    A = pkg.DescriptorSet(ctx, c["desc_a"], c["kps_a"], c["grid"], c["fv_a"])
+    assert np.array_equal(A.read_desc(), c["desc_a"])
+    assert np.array_equal(A.read_desc(100, 17), c["desc_a"][100:117])
+    A.release()
+
+
+@pytest.mark.parametrize("force_exact", [1, 0])
+@pytest.mark.parametrize("n,m,nodes,ratio,ori", [(2000, 2000, 1, 0.7, 1), (1500, 2000, 1, 0.75, 0), (2000, 1777, 40, 0.7, 1),
+                                                   (300, 250, 5, 0.9, 1), (64, 64, 1, 0.6, 1), (1, 1, 1, 0.7, 1)])
+def test_c1_search_by_bow_kf_f(pkg, ctx, oracle, n, m, nodes, ratio, ori, force_exact):
+    c = pkg.synth.config1(n, m, n_nodes=nodes)
+    rng = np.random.default_rng(n * 31 + m)
+    valid = (rng.random(n) < 0.9).astype(np.uint8)
+    ctx.set_option("force_exact", force_exact)
+    A, B = _sets_pair(pkg, ctx, c)
+    mt = pkg.ORBmatcher(ctx, ratio, bool(ori))
+    nm, match, dist = mt.SearchByBoW_KF_F(A, valid, B)
+    onm, omatch, odist = oracle.search_by_bow_kf_f(c["desc_a"], c["kps_a"], c["fv_a"], valid, c["desc_b"], c["kps_b"],
+                                                   c["fv_b"], ratio, ori)
+    ctx.set_option("force_exact", 0)
+    _eq(match, omatch, "match_f")
+    _eq_dist(dist, odist, "dist_f")
+    assert nm == onm
+    if n >= 1000:
+        assert nm > n // 4  # the synthetic pair really has matches
+    A.release(); B.release()
+
+
+@pytest.mark.parametrize("force_exact", [1, 0])
+@pytest.mark.parametrize("n,nodes,ratio", [(2000, 1, 0.85), (1200, 25, 0.85), (130, 3, 0.6)])
+def test_search_by_bow_kf_kf(pkg, ctx, oracle, n, nodes, ratio, force_exact):
+    c = pkg.synth.config5(n=n, n_pairs=3, n_kf=4, n_nodes=nodes)
+    kfs = c["kfs"]
+    ctx.set_option("force_exact", force_exact)
+    sets = [pkg.DescriptorSet(ctx, k["desc"], k["kps"], c["grid"], k["fv"]) for k in kfs]
+    mt = pkg.ORBmatcher(ctx, ratio, True)
+    for a, b in [(0, 1), (2, 3), (1, 0)]:
+        nm, match, dist = mt.SearchByBoW_KF_KF(sets[a], kfs[a]["valid"], sets[b], kfs[b]["valid"])
+        onm, omatch, odist = oracle.search_by_bow_kf_kf(kfs[a]["desc"], kfs[a]["kps"], kfs[a]["fv"], kfs[a]["valid"],
+                                                        kfs[b]["desc"], kfs[b]["kps"], kfs[b]["fv"], kfs[b]["valid"],
+                                                        ratio, 1)
+        _eq(match, omatch, "match12")
+        _eq_dist(dist, odist, "dist12")
+        assert nm == onm
+    ctx.set_option("force_exact", 0)
+    for s in sets:
+        s.release()
+
+
+@pytest.mark.parametrize("force_exact", [1, 0])
+def test_exact_ties_and_duplicates(pkg, ctx, oracle, force_exact):
+    """Adversarial: duplicated descriptors give exactly equal distances; scan-order tie-breaking must match
+    (first wins in SearchByBoW, last wins in SearchForTriangulation)."""
+    c = pkg.synth.config1(400, 400, n_nodes=3)
+    rng = np.random.default_rng(5)
+    db = c["desc_b"].copy()
+    src = rng.integers(0, 400, 120)
+    dst = rng.integers(0, 400, 120)
+    db[dst] = db[src]  # exact duplicates inside B
+    da = c["desc_a"].copy()
+    da[rng.integers(0, 400, 60)] = db[rng.integers(0, 400, 60)]  # zero-distance pairs
+    c["desc_a"], c["desc_b"] = da, db
+    ctx.set_option("force_exact", force_exact)
+    A, B = _sets_pair(pkg, ctx, c)
+    valid = np.ones(400, np.uint8)
+    for ratio in (0.7, 1.5):
+        mt = pkg.ORBmatcher(ctx, ratio, True)
+        nm, match, dist = mt.SearchByBoW_KF_F(A, valid, B)
+        onm, omatch, odist = oracle.search_by_bow_kf_f(da, c["kps_a"], c["fv_a"], valid, db, c["kps_b"], c["fv_b"], ratio, 1)
+        _eq(match, omatch, "match_f (ties)")
+        _eq_dist(dist, odist, "dist_f (ties)")
+        assert nm == onm
+        nm, match, dist = mt.SearchByBoW_KF_KF(A, valid, B, valid)
+        onm, omatch, odist = oracle.search_by_bow_kf_kf(da, c["kps_a"], c["fv_a"], valid, db, c["kps_b"], c["fv_b"], valid,
+                                                        ratio, 1)
+        _eq(match, omatch, "match12 (ties)")
+        assert nm == onm
+    # triangulation with wide-open geometry gates so that the tie rule decides
+    F12 = np.array([0, 0, 0, 0, 0, 1, 0, -1, 0.0], np.float32)  # epipolar lines y2 = y1... any; gate opened below
+    sf = pkg.synth.scale_factors()
+    ls = np.full(8, 1e12, np.float32)
+    nomp = np.zeros(400, np.uint8)
+    mt = pkg.ORBmatcher(ctx, 0.6, False)
+    nm, match, dist = mt.SearchForTriangulation(A, nomp, B, nomp, F12, -1e4, -1e4, sf, ls)
+    onm, omatch, odist = oracle.search_for_triangulation(da, c["kps_a"], c["fv_a"], nomp, db, c["kps_b"], c["fv_b"], nomp,
+                                                         F12, -1e4, -1e4, sf, ls, 0)
+    _eq(match, omatch, "triangulation (ties)")
+    _eq_dist(dist, odist, "triangulation dist (ties)")
+    assert nm == onm and nm > 50
+    ctx.set_option("force_exact", 0)
+    A.release(); B.release()
+
+
+@pytest.mark.parametrize("force_exact", [1, 0])
+@pytest.mark.parametrize("n,pairs,nodes,ori", [(2000, 20, 1, 0), (900, 6, 30, 1)])
+def test_c4_triangulation_job(pkg, ctx, oracle, n, pairs, nodes, ori, force_exact):
+    c = pkg.synth.config4(n=n, n_pairs=pairs, n_nodes=nodes)
+    kfs = c["kfs"]
+    ctx.set_option("force_exact", force_exact)
+    sets = [pkg.DescriptorSet(ctx, k["desc"], k["kps"], c["grid"], k["fv"]) for k in kfs]
+    job = pkg.PairJob(ctx, pkg.ASDM_JOB_TRIANGULATION, sets, [k["has_mp"] for k in kfs], c["ia"], c["ib"], 0.6, ori,
+                      c["F12"], c["epipoles"], c["scale_factors"], c["level_sigma2"])
+    job.run()
+    nm, match, dist = job.fetch()
+    assert ctx.stat("gpu_launches") >= 2
+    onm, omatch, odist = oracle.batch_triangulation(kfs, c["ia"], c["ib"], c["F12"], c["epipoles"], c["scale_factors"],
+                                                    c["level_sigma2"], ori, threads=oracle.max_threads())
+    ctx.set_option("force_exact", 0)
+    _eq(match[:, :n], omatch, "triangulation match12")
+    _eq_dist(dist[:, :n], odist, "triangulation dist12")
+    _eq(nm, onm, "nmatches")
+    assert onm.sum() > pairs * n // 50
+    # single-pair entry point agrees with the job
+    mt = pkg.ORBmatcher(ctx, 0.6, bool(ori))
+    p = pairs - 1
+    a, b = c["ia"][p], c["ib"][p]
+    nm1, m1, d1 = mt.SearchForTriangulation(sets[a], kfs[a]["has_mp"], sets[b], kfs[b]["has_mp"], c["F12"][p],
+                                            c["epipoles"][p][0], c["epipoles"][p][1], c["scale_factors"],
+                                            c["level_sigma2"])
+    _eq(m1, omatch[p], "single-pair triangulation")
+    assert nm1 == onm[p]
+    job.destroy()
+    for s in sets:
+        s.release()
+
+
+@pytest.mark.parametrize("force_exact", [1, 0])
+def test_c5_loop_sweep_job(pkg, ctx, oracle, force_exact):
+    n, pairs = 4000, 6
+    c = pkg.synth.config5(n=n, n_pairs=pairs, n_kf=5)
+    kfs = c["kfs"]
+    ctx.set_option("force_exact", force_exact)
+    sets = [pkg.DescriptorSet(ctx, k["desc"], k["kps"], c["grid"], k["fv"]) for k in kfs]
+    job = pkg.PairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, sets, [k["valid"] for k in kfs], c["ia"], c["ib"], c["nnratio"],
+                      c["check_ori"])
+    job.run()
+    nm, match, dist = job.fetch()
+    ctx.set_option("force_exact", 0)
+    onm, omatch, odist = oracle.batch_bow_kf_kf(kfs, c["ia"], c["ib"], c["nnratio"], c["check_ori"],
+                                                threads=oracle.max_threads())
+    _eq(match[:, :n], omatch, "bow match12")
+    _eq_dist(dist[:, :n], odist, "bow dist12")
+    _eq(nm, onm, "nmatches")
+    assert onm.min() > n // 20
+    # properties that hold at any size: one-to-one (vbMatched2), matched targets valid
+    for p in range(pairs):
+        m = match[p, :n]
+        got = m[m >= 0]
+        assert len(np.unique(got)) == len(got)
+        assert kfs[c["ib"][p]]["valid"][got].all() and kfs[c["ia"][p]]["valid"][np.nonzero(m >= 0)[0]].all()
+    job.destroy()
+    for s in sets:
+        s.release()
+
+
+def test_small_cand_cap_retries(pkg, ctx, oracle):
+    """Candidate pools start tiny and must grow transparently (no silent truncation)."""
+    c = pkg.synth.config1(500, 500)
+    db = c["desc_b"].copy()
+    db[:300] = db[0]  # 300 identical targets: hundreds of candidates for some queries
+    c["desc_a"][:50] = db[0]
+    c["desc_b"] = db
+    ctx.set_option("cand_cap", 1)
+    A, B = _sets_pair(pkg, ctx, c)
+    valid = np.ones(500, np.uint8)
+    mt = pkg.ORBmatcher(ctx, 0.7, True)
+    nm, match, dist = mt.SearchByBoW_KF_F(A, valid, B)
+    ctx.set_option("cand_cap", 8)
+    onm, omatch, odist = oracle.search_by_bow_kf_f(c["desc_a"], c["kps_a"], c["fv_a"], valid, db, c["kps_b"], c["fv_b"],
+                                                   0.7, 1)
+    _eq(match, omatch, "match_f after growth")
+    assert nm == onm
+    A.release(); B.release()
+
+
+# ------------------------------------------------------------------------------- projection-gated searches
+@pytest.mark.parametrize("th,nkp,nmp,inview", [(1.0, 2000, 8000, 2000), (5.0, 2000, 8000, 3000), (1.0, 50, 200, 100),
+                                               (3.0, 1, 5, 5)])
+def test_c2_search_by_projection_local_map(pkg, ctx, oracle, th, nkp, nmp, inview):
+    c = pkg.synth.config2(n_kp=nkp, n_mp=nmp, n_in_view=inview, th=th)
+    F = pkg.DescriptorSet(ctx, c["desc_t"], c["kps_t"], c["grid"])
+    mt = pkg.ORBmatcher(ctx, c["nnratio"], True)
+    q = c["queries"]
+    nm, assign, dist = mt.SearchByProjection_LocalMap(F, q["valid"], q["u"], q["v"], c["level"], c["view_cos"], q["blocks"],
+                                                      c["desc_q"], pkg.synth.scale_factors(), th=th,
+                                                      blocked0=c["blocked0"])
+    onm, oassign, odist = oracle.search_by_projection(c["desc_t"], c["kps_t"], c["grid"], q, c["desc_q"], c["blocked0"],
+                                                      c["mode"], c["th_accept"], c["best_init"], c["nnratio"],
+                                                      c["check_ori"], c["count_twice"])
+    _eq(assign, oassign, "assign")
+    _eq_dist(dist, odist, "dist")
+    assert nm == onm
+    if nkp >= 2000:
+        assert (oassign >= 0).sum() > 500
+    F.release()
+
+
+def test_c3_stereo_and_frame_to_frame(pkg, ctx, oracle):
+    c = pkg.synth.config3()
+    s, f = c["stereo"], c["f2f"]
+    L = pkg.DescriptorSet(ctx, s["desc_l"], s["kps_l"], f["grid"])
+    R = pkg.DescriptorSet(ctx, s["desc_r"], s["kps_r"], f["grid"])
+    mt = pkg.ORBmatcher(ctx, 0.8, True)
+    best, dist = mt.StereoRowMatch(L, R, s["scale_factors"], s["n_rows"], s["min_d"], s["max_d"])
+    obest, odist = oracle.stereo_row_match(s["desc_l"], s["kps_l"], s["desc_r"], s["kps_r"], s["scale_factors"],
+                                           s["n_rows"], s["min_d"], s["max_d"])
+    _eq(best, obest, "stereo best_r")
+    _eq_dist(dist, odist, "stereo dist")
+    assert (obest >= 0).sum() > 200
+    # frame-to-frame SearchByProjection(Cur, Last, th=15, mono): queries are rows of the last frame's set
+    Cur = pkg.DescriptorSet(ctx, f["desc_t"], f["kps_t"], f["grid"])
+    nm, assign, dist = mt.SearchByProjection(Cur, f["queries"], q_set=L, blocked0=f["blocked0"],
+                                             mode=pkg.ASDM_PROJ_BEST_ONLY, th_accept=1.5, best_init=100.0)
+    onm, oassign, odist = oracle.search_by_projection(f["desc_t"], f["kps_t"], f["grid"], f["queries"], f["desc_q"],
+                                                      f["blocked0"], f["mode"], f["th_accept"], f["best_init"],
+                                                      f["nnratio"], f["check_ori"], f["count_twice"])
+    _eq(assign, oassign, "f2f assign")
+    _eq_dist(dist, odist, "f2f dist")
+    assert nm == onm and (oassign >= 0).sum() > 200
+    # same through host descriptors and an explicit row map
+    rows = np.arange(len(f["queries"]), dtype=np.int32)
+    nm2, assign2, _ = mt.SearchByProjection(Cur, f["queries"], q_set=L, q_rows=rows, blocked0=f["blocked0"],
+                                            mode=pkg.ASDM_PROJ_BEST_ONLY, th_accept=1.5, best_init=100.0)
+    _eq(assign2, oassign, "f2f assign (row map)")
+    for x in (L, R, Cur):
+        x.release()
+
+
+@pytest.mark.parametrize("n,window", [(4000, 100), (600, 40), (30, 500)])
+def test_search_for_initialization(pkg, ctx, oracle, n, window):
+    c = pkg.synth.config_init(n=n, window=window)
+    F1 = pkg.DescriptorSet(ctx, c["desc1"], c["kps1"], c["grid2"])
+    F2 = pkg.DescriptorSet(ctx, c["desc2"], c["kps2"], c["grid2"])
+    mt = pkg.ORBmatcher(ctx, c["nnratio"], True)
+    nm, match, dist, prev = mt.SearchForInitialization(F1, F2, c["prev_matched"], window)
+    onm, omatch, odist, oprev = oracle.search_for_initialization(c["desc1"], c["kps1"], c["desc2"], c["kps2"], c["grid2"],
+                                                                 c["prev_matched"], window, c["nnratio"], 1)
+    _eq(match, omatch, "matches12")
+    _eq_dist(dist, odist, "dist12")
+    assert nm == onm
+    assert np.array_equal(prev, oprev)
+    if n >= 4000:
+        assert onm > 100
+    F1.release(); F2.release()
+
+
+def test_init_stealing(pkg, ctx, oracle):
+    """Later queries steal a keypoint from an earlier owner (ORBmatcher.cc:474-478): make many F1 keypoints
+    compete for the same F2 keypoints with decreasing distances."""
+    rng = np.random.default_rng(11)
+    S = pkg.synth
+    n = 300
+    W, H = S.KITTI["width"], S.KITTI["height"]
+    d2 = S.make_descriptors(rng, n)
+    k2 = S.make_keypoints(rng, n, W, H)
+    k2["octave"] = 0
+    d1 = np.empty_like(d2)
+    k1 = S.make_keypoints(rng, n, W, H)
+    k1["octave"] = (rng.random(n) < 0.2).astype(np.int32)
+    tgt = rng.integers(0, 40, n)  # 300 queries fight over 40 targets
+    for i in range(n):
+        noise = rng.standard_normal(128).astype(np.float32) * np.float32(0.05 * (1.0 - i / (2 * n)))
+        v = d2[tgt[i]] + noise
+        d1[i] = v / np.sqrt((v * v).sum(dtype=np.float32))
+        k1["x"][i], k1["y"][i] = k2["x"][tgt[i]] + rng.normal(0, 5), k2["y"][tgt[i]] + rng.normal(0, 5)
+    g = S.image_grid(W, H)
+    prev = np.stack([k1["x"], k1["y"]], 1).astype(np.float32)
+    F1 = pkg.DescriptorSet(ctx, d1, k1, g)
+    F2 = pkg.DescriptorSet(ctx, d2, k2, g)
+    mt = pkg.ORBmatcher(ctx, 0.9, True)
+    nm, match, dist, pv = mt.SearchForInitialization(F1, F2, prev, 100)
+    onm, omatch, odist, opv = oracle.search_for_initialization(d1, k1, d2, k2, g, prev, 100, 0.9, 1)
+    _eq(match, omatch, "matches12 (steal)")
+    assert nm == onm and np.array_equal(pv, opv)
+    F1.release(); F2.release()
+
+
+def test_errors_do_not_throw(pkg, ctx):
+    """C ABI error behaviour: negative codes + message, never an exception from native code."""
+    import ctypes as C
+    lib = ctx.lib
+    h = C.c_void_p()
+    assert lib.asdm_set_create(ctx.h, None, 5, 0, None, None, C.byref(h)) == -1
+    c = pkg.synth.config1(10, 10)
+    A = pkg.DescriptorSet(ctx, c["desc_a"], c["kps_a"], c["grid"])  # no FeatureVector
+    mt = pkg.ORBmatcher(ctx)
+    with pytest.raises(pkg.AsdmError):
+        mt.SearchByBoW_KF_KF(A, np.ones(10, np.uint8), A, np.ones(10, np.uint8))
+    assert b"FeatureVector" in lib.asdm_last_error(ctx.h)
+    A.release()
