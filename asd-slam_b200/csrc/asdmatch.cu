@@ -111,6 +111,7 @@ extern "C" int asdm_destroy(asdm_ctx* ctx) {
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   for (auto& b : ctx->scratch) release(b);
+  for (cudaEvent_t e : ctx->ev) cudaEventDestroy(e);
   if (ctx->h_pin) cudaFreeHost(ctx->h_pin);
   if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
@@ -145,6 +146,7 @@ extern "C" int asdm_set_option(asdm_ctx* ctx, const char* key, int value) {
   if (!strcmp(key, "force_exact")) ctx->opt_force_exact = value;
   else if (!strcmp(key, "cand_cap")) ctx->opt_cand_cap = std::max(1, value);
   else if (!strcmp(key, "list_cap_per_query")) ctx->opt_list_cap_per_query = std::max(1, value);
+  else if (!strcmp(key, "time_kernels")) ctx->opt_time_kernels = value;
   else return fail(ctx, ASDM_ERR_INVALID, "unknown option");
   return ASDM_OK;
 }
@@ -159,6 +161,25 @@ extern "C" int asdm_get_stat(asdm_ctx* ctx, const char* key, int64_t* value) {
   else if (!strcmp(key, "tc_used")) *value = ctx->stat_tc_used;
   else if (!strcmp(key, "tc_pairs")) *value = ctx->stat_tc_pairs;
   else if (!strcmp(key, "sm_count")) *value = ctx->sm_count;
+  else if (!strcmp(key, "dist_stage_us") || !strcmp(key, "dist_stage_runs")) {
+    // total device time of the distance stage (tensor-core shortlist, or the exact kernel) over the runs recorded
+    // since the last drain; the caller must have synchronised
+    double us = 0;
+    const int64_t runs = (int64_t)ctx->ev.size() / 2;
+    if (!strcmp(key, "dist_stage_runs")) {
+      *value = runs;
+      return ASDM_OK;
+    }
+    for (size_t i = 0; i + 1 < ctx->ev.size(); i += 2) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, ctx->ev[i], ctx->ev[i + 1]) == cudaSuccess) us += (double)ms * 1000.0;
+      cudaEventDestroy(ctx->ev[i]);
+      cudaEventDestroy(ctx->ev[i + 1]);
+    }
+    cudaGetLastError();
+    ctx->ev.clear();
+    *value = (int64_t)(us + 0.5);
+  }
   else return fail(ctx, ASDM_ERR_INVALID, "unknown stat");
   return ASDM_OK;
 }
@@ -563,10 +584,17 @@ static int job_run(asdm_job* j) {
   int32_t* flags = (int32_t*)j->d_flags.p;
   CK(cudaMemsetAsync(j->d_cnt.p, 0, (size_t)j->n_pairs * j->n_stride * sizeof(int32_t), ctx->stream));
   CK(cudaMemsetAsync(flags, 0, 64, ctx->stream));
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  if (ctx->opt_time_kernels) {
+    CK(cudaEventCreate(&ev0));
+    CK(cudaEventCreate(&ev1));
+    CK(cudaEventRecord(ev0, ctx->stream));
+  }
   if (j->use_tc) {
     CK(asdm_tc_shortlist_launch(ctx, pairs, j->d_tmaps.p, (const TcWork*)j->d_work.p, j->n_work, j->P.t_keep,
                                 (TcPair*)j->d_list.p, (int32_t*)j->d_list_pair.p, j->list_cap, flags + 2));
     LAUNCHED(ctx);
+    if (ev1) CK(cudaEventRecord(ev1, ctx->stream));
     const int blocks = ctx->sm_count * 8;
     k_rerank<<<blocks, 256, 0, ctx->stream>>>(pairs, j->P, j->cap, j->n_stride, (const TcPair*)j->d_list.p,
                                               (const int32_t*)j->d_list_pair.p, flags + 2, j->list_cap,
@@ -578,6 +606,11 @@ static int job_run(asdm_job* j) {
     k_cand_exact<<<grid, 256, ASDM_DESC_DIM * (CE_TM + CE_TN) * sizeof(float), ctx->stream>>>(
         pairs, j->P, j->cap, j->n_stride, (int32_t*)j->d_cnt.p, (Cand*)j->d_cand.p, flags);
     LAUNCHED(ctx);
+    if (ev1) CK(cudaEventRecord(ev1, ctx->stream));
+  }
+  if (ev0) {
+    ctx->ev.push_back(ev0);
+    ctx->ev.push_back(ev1);
   }
   if (j->kind == KIND_TRIANGULATION)
     k_resolve_tri<<<j->n_pairs, 512, 0, ctx->stream>>>(pairs, j->P, j->cap, j->n_stride, j->out_stride,

@@ -42,6 +42,8 @@ struct asdm_ctx {
   void* h_pin = nullptr;
   size_t h_pin_cap = 0;
   DevBuf scratch[8];
+  int opt_time_kernels = 0;     // record CUDA events around the distance stage of every job run
+  std::vector<cudaEvent_t> ev;  // pairs (begin, end), drained by asdm_get_stat("dist_stage_us")
   int proj_ent_cap = 1 << 16;  // entries of the projection candidate pool (grows on overflow)
 };
 

@@ -1,5 +1,343 @@
-// placeholder until the tcgen05 kernel lands
+// tc_shortlist.cu -- K1: the N x M distance matrix of a keyframe pair as a dense contraction on the 5th-gen tensor
+// cores (tcgen05.mma, bf16 operands staged by TMA, fp32 accumulators in TMEM), reduced on the fly to the short list
+// of (i, j) whose squared distance can be <= t_keep.  k_rerank then recomputes those few pairs in the reference's
+// exact fp32 arithmetic, so the tensor-core result is only ever a filter (DESIGN.md "error bound").
+//
+//   ||a-b||^2 = |a|^2 + |b|^2 - 2 a.b ;  acc = bf16(a).bf16(b) in fp32 ;  |acc - a.b| <= 1.25 * 2^-8 * (|a|^2+|b|^2)
+//   d <= t_keep  =>  acc >= KAPPA*(|a|^2 + |b|^2) - t_keep/2 * (1+1e-4),   KAPPA = 0.495
+//
+// Persistent kernel, one CTA per SM, 6 warps: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane),
+// warps 2..5 = epilogue (one per TMEM lane quarter). A work unit keeps one 256-row tile of set B resident in shared
+// memory (double buffered across units) and streams 128-row tiles of set A through a 3-stage ring; accumulators are
+// double buffered in TMEM (2 x 256 columns), so the epilogue of tile t overlaps the MMAs of tile t+1.
+// Per tile: 8 x tcgen05.mma 128x256x16 = 8.39 MFLOP; epilogue = 32768 fp32 reads from TMEM, one max per value.
+#include <cuda.h>
+
 #include "internal.cuh"
-cudaError_t asdm_tc_shortlist_launch(asdm_ctx*, const PairDesc*, const void*, const TcWork*, int, float, TcPair*,
-                                     int32_t*, int, int32_t*) { return cudaErrorNotSupported; }
-int asdm_tc_build_tmap(asdm_ctx*, asdm_set*) { return ASDM_ERR_INTERNAL; }
+
+namespace {
+
+constexpr int TM = 128;        // rows of A per tile (UMMA M)
+constexpr int TN = 256;        // rows of B per tile (UMMA N)
+constexpr int KD = ASDM_DESC_DIM;
+constexpr int A_STAGES = 3;
+constexpr int A_BYTES = TM * KD * 2;   // 32 KB
+constexpr int B_BYTES = TN * KD * 2;   // 64 KB
+constexpr int KBLK_A = TM * 128;       // bytes of one 64-element K block of an A tile (128 B per row)
+constexpr int KBLK_B = TN * 128;
+constexpr int TC_SMEM = 2 * B_BYTES + A_STAGES * A_BYTES + 1024;
+constexpr int TC_THREADS = 192;
+constexpr float KAPPA = 0.495f;
+
+// instruction descriptor (cute::UMMA::InstrDescriptor): D=f32, A=B=bf16, both K-major, N=256, M=128
+constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P1;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+      "@P1 bra DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "DONE:\n\t"
+      "}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const void* tmap, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(dst)),
+      "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+// K-major, 128-byte swizzle: 8-row groups are 1024 B apart (SBO), LBO unused, descriptor version 1 (sm_100)
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
+  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) |
+         ((uint64_t)2 << 61);
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(da), "l"(db), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ float max3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+
+__device__ __forceinline__ float max_of_32(const uint32_t (&v)[32]) {
+  float m[11];
+#pragma unroll
+  for (int k = 0; k < 10; k++)
+    m[k] = max3(__uint_as_float(v[3 * k]), __uint_as_float(v[3 * k + 1]), __uint_as_float(v[3 * k + 2]));
+  m[10] = fmaxf(__uint_as_float(v[30]), __uint_as_float(v[31]));
+  const float a = max3(m[0], m[1], m[2]), b = max3(m[3], m[4], m[5]), c = max3(m[6], m[7], m[8]);
+  return max3(max3(a, b, c), m[9], m[10]);
+}
+
+struct __align__(8) TcBarriers {
+  uint64_t a_full[A_STAGES], a_empty[A_STAGES];
+  uint64_t b_full[2], b_empty[2];
+  uint64_t t_full[2], t_empty[2];
+  uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+k_tc_shortlist(const PairDesc* __restrict__ pairs, const uint8_t* __restrict__ tmaps, const TcWork* __restrict__ work,
+               int n_work, float t_half, int mask_sense, TcPair* __restrict__ list, int32_t* __restrict__ list_pair,
+               int list_cap, int32_t* __restrict__ list_count) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ TcBarriers bars;
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* smB = smem;                  // 2 x 64 KB
+  uint8_t* smA = smem + 2 * B_BYTES;    // A_STAGES x 32 KB
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < A_STAGES; s++) {
+      mbar_init(&bars.a_full[s], 1);
+      mbar_init(&bars.a_empty[s], 1);
+    }
+    for (int s = 0; s < 2; s++) {
+      mbar_init(&bars.b_full[s], 1);
+      mbar_init(&bars.b_empty[s], 1);
+      mbar_init(&bars.t_full[s], 1);
+      mbar_init(&bars.t_empty[s], 4);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&bars.tmem_base)), "n"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars.tmem_base;
+
+  if (warp == 0) {
+    // ================================================================ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t aphase = 0;
+      int ul = 0;
+      for (int u = blockIdx.x; u < n_work; u += gridDim.x, ul++) {
+        const TcWork w = work[u];
+        const PairDesc& pd = pairs[w.pair];
+        const void* tmA = tmaps + (size_t)pd.setA * 128;
+        const void* tmB = tmaps + (size_t)pd.setB * 128;
+        const int bb = ul & 1;
+        mbar_wait(&bars.b_empty[bb], ((ul >> 1) & 1) ^ 1);
+        mbar_expect_tx(&bars.b_full[bb], B_BYTES);
+#pragma unroll
+        for (int kb = 0; kb < 2; kb++)
+#pragma unroll
+          for (int h = 0; h < 2; h++)
+            tma_load_2d(smB + bb * B_BYTES + kb * KBLK_B + h * (128 * 128), tmB, kb * 64, w.n_tile * TN + h * 128,
+                        &bars.b_full[bb]);
+        for (int t = 0; t < w.m_tiles; t++) {
+          mbar_wait(&bars.a_empty[stage], aphase ^ 1);
+          mbar_expect_tx(&bars.a_full[stage], A_BYTES);
+#pragma unroll
+          for (int kb = 0; kb < 2; kb++)
+            tma_load_2d(smA + stage * A_BYTES + kb * KBLK_A, tmA, kb * 64, (w.m_tile0 + t) * TM, &bars.a_full[stage]);
+          if (++stage == A_STAGES) {
+            stage = 0;
+            aphase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================================================ MMA issuer
+    if (lane == 0) {
+      int stage = 0, acc = 0;
+      uint32_t aphase = 0, accphase = 0;
+      int ul = 0;
+      for (int u = blockIdx.x; u < n_work; u += gridDim.x, ul++) {
+        const int m_tiles = work[u].m_tiles;
+        const int bb = ul & 1;
+        mbar_wait(&bars.b_full[bb], (ul >> 1) & 1);
+        const uint32_t b_addr = smem_u32(smB + bb * B_BYTES);
+        for (int t = 0; t < m_tiles; t++) {
+          mbar_wait(&bars.t_empty[acc], accphase ^ 1);
+          mbar_wait(&bars.a_full[stage], aphase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smA + stage * A_BYTES);
+          const uint32_t d_tmem = tmem_base + (uint32_t)acc * TN;
+#pragma unroll
+          for (int kb = 0; kb < 2; kb++)
+#pragma unroll
+            for (int kk = 0; kk < 4; kk++)
+              umma_bf16(d_tmem, umma_desc(a_addr + kb * KBLK_A + kk * 32), umma_desc(b_addr + kb * KBLK_B + kk * 32), IDESC,
+                        (kb | kk) ? 1u : 0u);
+          umma_commit(&bars.a_empty[stage]);  // smem slot reusable once these MMAs have read it
+          umma_commit(&bars.t_full[acc]);     // accumulator ready for the epilogue
+          if (++stage == A_STAGES) {
+            stage = 0;
+            aphase ^= 1;
+          }
+          acc ^= 1;
+          if (acc == 0) accphase ^= 1;
+        }
+        umma_commit(&bars.b_empty[bb]);
+      }
+    }
+  } else {
+    // ================================================================ epilogue: 4 warps, one per TMEM lane quarter
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    int acc = 0;
+    uint32_t accphase = 0;
+    const float INF = __int_as_float(0x7f800000);
+    for (int u = blockIdx.x; u < n_work; u += gridDim.x) {
+      const TcWork w = work[u];
+      const PairDesc& pd = pairs[w.pair];
+      const int nA = pd.nA, nB = pd.nB;
+      const int j0 = w.n_tile * TN;
+      const float* __restrict__ normB = pd.normB;
+      float minb = INF;
+#pragma unroll
+      for (int k = 0; k < TN / 32; k++) {
+        const int j = j0 + k * 32 + lane;
+        if (j < nB) minb = fminf(minb, KAPPA * __ldg(normB + j));
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) minb = fminf(minb, __shfl_xor_sync(0xffffffffu, minb, o));
+      for (int t = 0; t < w.m_tiles; t++) {
+        const int i = (w.m_tile0 + t) * TM + row;
+        const float ai = i < nA ? KAPPA * __ldg(pd.normA + i) : INF;
+        const float thr_row = (ai + minb) - t_half;  // +inf for padding rows / all-padding column tiles
+        mbar_wait(&bars.t_full[acc], accphase);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)acc * TN;
+        uint32_t v[2][32];
+        tmem_ld32(taddr, v[0]);
+#pragma unroll
+        for (int ch = 0; ch < TN / 32; ch++) {
+          tmem_ld_wait();
+          if (ch + 1 < TN / 32) tmem_ld32(taddr + (ch + 1) * 32, v[(ch + 1) & 1]);
+          const uint32_t(&cur)[32] = v[ch & 1];
+          if (max_of_32(cur) >= thr_row) {
+            // rare: some column of this row may be a candidate -- test each against its own bound and the gates
+            if (pd.maskA[i] == mask_sense && pd.posA[i] >= 0) {
+              const uint32_t nodeA = pd.nodeA[i];
+#pragma unroll
+              for (int c = 0; c < 32; c++) {
+                const float x = __uint_as_float(cur[c]);
+                if (x >= thr_row) {
+                  const int j = j0 + ch * 32 + c;
+                  if (j < nB && x >= (ai + KAPPA * __ldg(normB + j)) - t_half && pd.maskB[j] == mask_sense &&
+                      pd.posB[j] >= 0 && pd.nodeB[j] == nodeA) {
+                    const int slot = atomicAdd(list_count, 1);
+                    if (slot < list_cap) {
+                      list[slot] = TcPair{i, j};
+                      list_pair[slot] = w.pair;
+                    }
+                  }
+                }
+              }
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars.t_empty[acc]);
+        acc ^= 1;
+        if (acc == 0) accphase ^= 1;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512));
+  }
+}
+
+}  // namespace
+
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+int asdm_tc_build_tmap(asdm_ctx* ctx, asdm_set* set) {
+  if (!set->tmap_bf.empty()) return ASDM_OK;
+  if (!ctx->tmap_encode) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn) {
+      cudaGetLastError();
+      return ASDM_ERR_CUDA;
+    }
+    ctx->tmap_encode = fn;
+  }
+  CUtensorMap tm;
+  const cuuint64_t dims[2] = {(cuuint64_t)KD, (cuuint64_t)set->n_pad};
+  const cuuint64_t strides[1] = {(cuuint64_t)KD * 2};
+  const cuuint32_t box[2] = {64, 128};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = ((PFN_encodeTiled)ctx->tmap_encode)(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, set->desc_bf, dims, strides,
+                                                         box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return ASDM_ERR_CUDA;
+  set->tmap_bf.resize(128);
+  memcpy(set->tmap_bf.data(), &tm, 128);
+  return ASDM_OK;
+}
+
+cudaError_t asdm_tc_shortlist_launch(asdm_ctx* ctx, const PairDesc* d_pairs, const void* d_tmaps, const TcWork* d_work,
+                                     int n_work, float t_keep, int mask_sense, TcPair* d_list, int32_t* d_list_pair,
+                                     int list_cap, int32_t* d_list_count) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(k_tc_shortlist, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  const float t_half = 0.5f * t_keep * 1.0001f + 1e-6f;
+  const int grid = n_work < ctx->sm_count ? n_work : ctx->sm_count;
+  k_tc_shortlist<<<grid, TC_THREADS, TC_SMEM, ctx->stream>>>(d_pairs, (const uint8_t*)d_tmaps, d_work, n_work, t_half, mask_sense,
+                                                             d_list, d_list_pair, list_cap, d_list_count);
+  return cudaGetLastError();
+}

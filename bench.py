@@ -1,0 +1,336 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the ASD descriptor-matching hot path on B200.
+
+Workload (BASELINE.json configs[4], "C5"): loop-closure verification sweep -- 512 candidate keyframe pairs, each
+4000 x 4000 ASD descriptors (128-d fp32), matched with ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*) semantics
+(ratio 0.85, rotation check; reference ORBmatcher.cc:533-666, LoopClosing.cc:291-318) over 64 distinct keyframes.
+A "step" is one pass of the whole sweep.  Metric: descriptor pairs / s (= pairs * 4000 * 4000 * steps / time).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            our arm (one process per GPU; N>1 under torchrun)
+  python bench.py --impl reference ...                            the reference's CPU matcher (oracle port) timed
+                                                                   on the host cores, same metric / config
+
+N>1 is weak scaling: every rank owns its own 512-pair shard of an N*512-pair sweep over the same 64 keyframes
+(replicated on each GPU), and the match lists are all-gathered over NCCL at the end of every step.
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_DESC = 4000
+N_KF = 64
+N_PAIRS = 512
+NNRATIO = 0.85
+METRIC = "descriptor_pairs_per_sec"
+UNIT = "descriptor pairs/s"
+WORKLOAD = ("C5 loop-closure sweep: 512 keyframe pairs x 4000x4000 ASD descriptors (128-d fp32) per GPU, "
+            "SearchByBoW(KF,KF) ratio 0.85 + rotation histogram, 64 distinct keyframes")
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return dict(bf16=float(d["bf16_tflops_sustained"]), bf16_burst=float(d["bf16_tflops"]), hbm=float(d["hbm_gbs"]),
+                    source="measured")
+    return dict(bf16=1400.0, bf16_burst=1590.0, hbm=6650.0, source="fallback")
+
+
+def make_inputs(pkg, rank, n=N_DESC, n_kf=N_KF, n_pairs=N_PAIRS):
+    c = pkg.synth.config5(n=n, n_pairs=n_pairs, n_kf=n_kf, seed_extra=0)
+    if rank:
+        rng = np.random.default_rng(0xC5 + rank)  # this rank's shard of the sweep: its own candidate pairs
+        ia = rng.integers(0, n_kf, n_pairs).astype(np.int32)
+        c["ia"], c["ib"] = ia, ((ia + 1 + rng.integers(0, n_kf - 1, n_pairs)) % n_kf).astype(np.int32)
+    return c
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.06)
+        self.proc.terminate()
+        sm, mx, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        allrows = []
+        for ts, line in self.rows:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                row = (ts, float(f[0]), float(f[1]), float(f[2]), f[3:7])
+            except ValueError:
+                continue
+            allrows.append(row)
+        inside = [r for r in allrows if t0 <= r[0] <= t1] or allrows[-3:]
+        for ts, a, b, pw, fl in inside:
+            sm.append(a); mx.append(b); power.append(pw)
+            for nme, v in zip(names, fl):
+                if v.lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": float(max(mx)) if mx else None,
+                "power_w_max": float(max(power)) if power else None, "samples": len(inside), "reasons": sorted(reasons)}
+
+
+class DevArray:
+    """Exposes a raw device pointer of the library to torch (zero copy) for the NCCL all-gather."""
+
+    def __init__(self, p, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(p), False), "version": 2}
+
+
+# --------------------------------------------------------------------------------------------- CPU arms
+def cpu_sample(oracle, c, pairs, threads):
+    """Times the CPU oracle (port of the reference matcher) on the first `pairs` pairs of the workload."""
+    ia, ib = c["ia"][:pairs], c["ib"][:pairs]
+    t = time.perf_counter()
+    nm, match, dist = oracle.batch_bow_kf_kf(c["kfs"], ia, ib, c["nnratio"], c["check_ori"], threads=threads)
+    dt = time.perf_counter() - t
+    return dt, nm, match
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    pkg = importlib.import_module("asd-slam_b200")
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_py as oracle  # the one place outside tests/smoke where bench.py executes oracle/: the reference arm
+    oracle.build()
+    threads = oracle.max_threads()
+    c = make_inputs(pkg, 0)
+    n = N_DESC
+    dt1, _, _ = cpu_sample(oracle, c, threads, threads)  # calibration + first warm-up
+    per_pair_wall = dt1 / threads
+    budget = min(1.5, 150.0 / max(1, args.steps + args.warmup))
+    pairs = int(min(N_PAIRS, max(threads, round(budget / per_pair_wall))))
+    for _ in range(max(0, args.warmup - 1)):
+        cpu_sample(oracle, c, pairs, threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_sample(oracle, c, pairs, threads)
+    dt = time.perf_counter() - t0
+    value = pairs * float(n) * n * args.steps / dt
+    sample = f"{pairs} of the {N_PAIRS} keyframe pairs per step (4000x4000 each), {threads} OpenMP threads over pairs"
+    out = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": WORKLOAD, "sample": sample},
+           "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+           "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "keyframe_pairs_per_sec": pairs * args.steps / dt, "gpu_launches": 0}
+    print(json.dumps(out), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------- our arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the matcher has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    pkg = importlib.import_module("asd-slam_b200")
+    ctx = pkg.Context(local)
+    stream = torch.cuda.Stream()
+    ctx.set_stream(stream.cuda_stream)
+    n, P = N_DESC, args.pairs
+    c = make_inputs(pkg, rank, n_pairs=P)
+    kfs = c["kfs"]
+
+    # ---- resident inputs (device-only arm): keyframe sets uploaded once, as the SLAM system would at KF creation
+    sets = [pkg.DescriptorSet(ctx, k["desc"], k["kps"], c["grid"], k["fv"]) for k in kfs]
+    masks = [k["valid"] for k in kfs]
+    job = pkg.PairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, sets, masks, c["ia"], c["ib"], c["nnratio"], c["check_ori"])
+    S = job.stride
+    gathered = None
+    if world > 1:
+        pm, pd_, pn = job.device_outputs()
+        t_match = torch.as_tensor(DevArray(pm, (P * S,), "<i4"), device=f"cuda:{local}")
+        t_dist = torch.as_tensor(DevArray(pd_, (P * S,), "<f4"), device=f"cuda:{local}")
+        gathered = (torch.empty(world * P * S, dtype=torch.int32, device=f"cuda:{local}"),
+                    torch.empty(world * P * S, dtype=torch.float32, device=f"cuda:{local}"))
+
+    def step():
+        job.run()
+        if world > 1:  # results of all shards on every rank (north_star: NCCL all-gather over NVLink)
+            with torch.cuda.stream(stream):
+                dist.all_gather_into_tensor(gathered[0], t_match)
+                dist.all_gather_into_tensor(gathered[1], t_dist)
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+        job.settle()  # grows candidate pools if the first runs overflowed
+    launches_per_step = ctx.stat("gpu_launches")
+    tc_used = ctx.stat("tc_used")
+    ctx.set_option("time_kernels", 1)
+    ctx.stat("dist_stage_us")  # drain
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local) if rank == 0 else None
+    t0 = time.time()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1) if sampler else None
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device=f"cuda:{local}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    dist_us = ctx.stat("dist_stage_us")
+    ctx.set_option("time_kernels", 0)
+    job.settle()
+    assert ctx.stat("retries") == 0, "a candidate pool overflowed inside the timed region"
+    nm, match, _ = job.fetch()
+
+    # ---- e2e arm: the reference-facing call with HOST buffers -- upload the 64 keyframes from pinned host memory,
+    # attach FeatureVectors, prepare the job, run, and read the match lists back, every step
+    h_desc = [ctx.pinned((n, 128), np.float32) for _ in kfs]
+    for h, k in zip(h_desc, kfs):
+        h[...] = k["desc"]
+    h_match, h_dist, h_nm = ctx.pinned((P, S), np.int32), ctx.pinned((P, S), np.float32), ctx.pinned((P,), np.int32)
+
+    def e2e_step():
+        ss = [pkg.DescriptorSet(ctx, h, k["kps"], c["grid"], k["fv"]) for h, k in zip(h_desc, kfs)]
+        jb = pkg.PairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, ss, masks, c["ia"], c["ib"], c["nnratio"], c["check_ori"])
+        jb.run()
+        jb.fetch(h_match, h_dist, h_nm)
+        jb.destroy()
+        for s_ in ss:
+            s_.release()
+
+    e2e_steps = max(3, min(args.steps, 10))
+    e2e_step()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    te = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_ms = 1e3 * (time.perf_counter() - te) / e2e_steps
+    if world > 1:
+        t = torch.tensor([e2e_ms], device=f"cuda:{local}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t.item())
+    assert np.array_equal(h_match, match), "e2e results differ from the resident-input results"
+    h2d = sum(k["desc"].nbytes + k["kps"].nbytes + 8 * len(k["kps"]) + len(k["valid"]) for k in kfs) + 8 * P
+    d2h = h_match.nbytes + h_dist.nbytes + h_nm.nbytes
+
+    if rank == 0:
+        pk = peaks()
+        units = float(P) * n * n  # descriptor pairs per step per GPU
+        value = world * units * args.steps / (ms * 1e-3)
+        flops = 2.0 * units * 128  # 2*N*M*128 per keyframe pair, counted once
+        runs = max(1, args.steps)
+        dist_ms = dist_us * 1e-3 / runs
+        if tc_used:
+            achieved = flops / (dist_ms * 1e-3) / 1e12
+            roof = {"bound": "tensor", "kernel": "k_tc_shortlist", "achieved": achieved, "peak": pk["bf16"],
+                    "unit": "TFLOP/s", "frac": achieved / pk["bf16"], "traffic": None,
+                    "peak_source": f"{pk['source']} bf16 sustained (kernel timed inside a long step)"}
+        else:
+            achieved = 3.0 * units * 128 / (dist_ms * 1e-3) / 1e12  # sub, mul, add per element on the fp32 pipes
+            roof = {"bound": "fp32", "kernel": "k_cand_exact", "achieved": achieved, "peak": None, "unit": "TFLOP/s",
+                    "frac": None, "traffic": None, "note": "exact fp32 CUDA-core path (tensor-core shortlist disabled)"}
+        roof["ms_per_launch"] = dist_ms
+        roof["share_of_step"] = dist_ms / (ms / args.steps)
+
+        # CPU baseline: the oracle port of the reference matcher on this box's host cores, bounded sample
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import oracle_py as oracle  # cpu_baseline leg only
+        oracle.build()
+        threads = oracle.max_threads()
+        c0 = c
+        cpu_pairs = int(min(P, max(threads, 8)))
+        dtc, onm, omatch = cpu_sample(oracle, c0, cpu_pairs, threads)
+        if dtc < 5.0:
+            cpu_pairs = int(min(P, cpu_pairs * max(2, int(10.0 / max(dtc, 1e-3)))))
+            dtc, onm, omatch = cpu_sample(oracle, c0, cpu_pairs, threads)
+        parity = bool(np.array_equal(omatch, match[:cpu_pairs, :n]) and np.array_equal(onm, nm[:cpu_pairs]))
+        cpu_val = cpu_pairs * float(n) * n / dtc
+        out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+               "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+               "dtype": "f32", "data": "synthetic",
+               "config": {"workload": WORKLOAD, "pairs_per_gpu": P, "descriptors_per_keyframe": n,
+                          "l2": "inputs larger than L2 (197 MB of descriptors + candidate pools vs 126 MB); no flush",
+                          "tensor_core_shortlist": bool(tc_used)},
+               "keyframe_pairs_per_sec": world * P * args.steps / (ms * 1e-3),
+               "e2e": {"value": world * units / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+                       "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms,
+                       "what": "asdm_set_create x64 (pinned host descriptors) + featvec + job prepare/run/fetch per step"},
+               "gpu_launches": int(launches_per_step * args.steps),
+               "roofline": roof,
+               "cpu_baseline": {"value": cpu_val, "unit": UNIT, "cores": threads, "kind": "port",
+                                "sample": f"first {cpu_pairs} of the {P} keyframe pairs, {threads} OpenMP threads over pairs",
+                                "parity_on_sample": parity},
+               "clocks": clocks}
+        print(json.dumps(out), flush=True)
+    job.destroy()
+    for s_ in sets:
+        s_.release()
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--pairs", type=int, default=N_PAIRS, help="keyframe pairs per GPU per step (default: the C5 sweep)")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()
