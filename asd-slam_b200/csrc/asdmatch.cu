@@ -591,7 +591,7 @@ static int job_run(asdm_job* j) {
     CK(cudaEventRecord(ev0, ctx->stream));
   }
   if (j->use_tc) {
-    CK(asdm_tc_shortlist_launch(ctx, pairs, j->d_tmaps.p, (const TcWork*)j->d_work.p, j->n_work, j->P.t_keep,
+    CK(asdm_tc_shortlist_launch(ctx, pairs, j->d_tmaps.p, (const TcWork*)j->d_work.p, j->n_work, j->P.t_keep, j->P.mask_sense,
                                 (TcPair*)j->d_list.p, (int32_t*)j->d_list_pair.p, j->list_cap, flags + 2));
     LAUNCHED(ctx);
     if (ev1) CK(cudaEventRecord(ev1, ctx->stream));

@@ -179,6 +179,6 @@ struct TcWork {   // one unit of the persistent tensor-core kernel
   int32_t m_tiles;
 };
 cudaError_t asdm_tc_shortlist_launch(asdm_ctx* ctx, const PairDesc* d_pairs, const void* d_tmaps,
-                                     const TcWork* d_work, int n_work, float t_keep_eff, TcPair* d_list,
+                                     const TcWork* d_work, int n_work, float t_keep, int mask_sense, TcPair* d_list,
                                      int32_t* d_list_pair, int list_cap, int32_t* d_list_count);
 int asdm_tc_build_tmap(asdm_ctx* ctx, asdm_set* set);
