@@ -381,11 +381,12 @@ struct asdm_job {
   std::vector<asdm_set*> sets;  // retained
   std::vector<PairDesc> h_pairs;
   DevBuf d_pairs, d_masks, d_cnt, d_cand, d_owner, d_acc, d_flags, d_match, d_dist, d_nm;
-  DevBuf d_work, d_tmaps, d_list, d_list_pair;
+  DevBuf d_work, d_tmaps, d_list, d_seg_count;
   int cap = 8;
   int use_tc = 0;
   int n_work = 0;
-  int list_cap = 0;
+  int list_cap = 0;  // total hit slots; split evenly into n_seg segments of seg_cap
+  int n_seg = 0, seg_cap = 0;
   float t_keep_tc = 0.f;
   bool ran = false;
   int32_t* h_flags = nullptr;  // pinned, 8 ints: [0] cand overflow, [1] list overflow, [2] list count
@@ -396,7 +397,7 @@ static void job_free(asdm_job* j) {
   cudaSetDevice(j->ctx->device);
   cudaStreamSynchronize(j->ctx->stream);
   DevBuf* bufs[] = {&j->d_pairs, &j->d_masks, &j->d_cnt, &j->d_cand, &j->d_owner, &j->d_acc, &j->d_flags,
-                    &j->d_match, &j->d_dist, &j->d_nm, &j->d_work, &j->d_tmaps, &j->d_list, &j->d_list_pair};
+                    &j->d_match, &j->d_dist, &j->d_nm, &j->d_work, &j->d_tmaps, &j->d_list, &j->d_seg_count};
   for (DevBuf* b : bufs) release(*b);
   if (j->h_flags) cudaFreeHost(j->h_flags);
   for (asdm_set* s : j->sets) asdm_set_release(s);
@@ -416,8 +417,13 @@ static int job_alloc_scratch(asdm_job* j) {
   if ((rc = ensure(ctx, j->d_dist, P * j->out_stride * sizeof(float)))) return rc;
   if ((rc = ensure(ctx, j->d_nm, P * sizeof(int32_t)))) return rc;
   if (j->use_tc) {
-    if ((rc = ensure(ctx, j->d_list, (size_t)j->list_cap * sizeof(TcPair)))) return rc;
-    if ((rc = ensure(ctx, j->d_list_pair, (size_t)j->list_cap * sizeof(int32_t)))) return rc;
+    j->n_seg = ctx->sm_count * ASDM_TC_EPI_WARPS;
+    {  // only the CTAs that get work fill their segments
+      const int active = std::max(1, std::min(j->n_work, ctx->sm_count)) * ASDM_TC_EPI_WARPS;
+      j->seg_cap = std::max(1024, (j->list_cap + active - 1) / active);
+    }
+    if ((rc = ensure(ctx, j->d_list, (size_t)j->seg_cap * j->n_seg * sizeof(TcHit)))) return rc;
+    if ((rc = ensure(ctx, j->d_seg_count, (size_t)j->n_seg * sizeof(int32_t)))) return rc;
   }
   return ASDM_OK;
 }
@@ -591,14 +597,14 @@ static int job_run(asdm_job* j) {
     CK(cudaEventRecord(ev0, ctx->stream));
   }
   if (j->use_tc) {
+    CK(cudaMemsetAsync(j->d_seg_count.p, 0, (size_t)j->n_seg * sizeof(int32_t), ctx->stream));
     CK(asdm_tc_shortlist_launch(ctx, pairs, j->d_tmaps.p, (const TcWork*)j->d_work.p, j->n_work, j->P.t_keep, j->P.mask_sense,
-                                (TcPair*)j->d_list.p, (int32_t*)j->d_list_pair.p, j->list_cap, flags + 2));
+                                (TcHit*)j->d_list.p, j->seg_cap, (int32_t*)j->d_seg_count.p, flags + 2));
     LAUNCHED(ctx);
     if (ev1) CK(cudaEventRecord(ev1, ctx->stream));
-    const int blocks = ctx->sm_count * 8;
-    k_rerank<<<blocks, 256, 0, ctx->stream>>>(pairs, j->P, j->cap, j->n_stride, (const TcPair*)j->d_list.p,
-                                              (const int32_t*)j->d_list_pair.p, flags + 2, j->list_cap,
-                                              (int32_t*)j->d_cnt.p, (Cand*)j->d_cand.p, flags);
+    k_rerank<<<j->n_seg, 256, 0, ctx->stream>>>(pairs, j->P, j->cap, j->n_stride, (const TcHit*)j->d_list.p,
+                                                (const int32_t*)j->d_seg_count.p, j->seg_cap, (int32_t*)j->d_cnt.p,
+                                                (Cand*)j->d_cand.p, flags);
     LAUNCHED(ctx);
   } else {
     dim3 grid((j->n_stride + CE_TM - 1) / CE_TM, (j->m_stride + CE_TN - 1) / CE_TN, j->n_pairs);
@@ -646,7 +652,7 @@ static int job_settle(asdm_job* j) {
     ctx->stat_retries++;
     if (cand_over) j->cap = std::min(std::max(j->cap * 2, 2), std::max(j->m_stride, 2));
     if (list_over) {
-      const long need = std::max<long>((long)j->h_flags[2] + 1024, (long)j->list_cap * 2);
+      const long need = std::max<long>(2 * (long)j->h_flags[2] + 4096, (long)j->list_cap * 2);
       if (need > ((long)1 << 30)) j->use_tc = 0;  // absurdly dense: take the exact kernel
       else j->list_cap = (int)need;
     }

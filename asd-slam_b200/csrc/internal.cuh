@@ -29,7 +29,7 @@ struct asdm_ctx {
   std::string err;
   int opt_force_exact = 0;
   int opt_cand_cap = 8;
-  int opt_list_cap_per_query = 8;  // tensor-core short list slots per query row (grows on overflow)
+  int opt_list_cap_per_query = 4;  // tensor-core short list slots per query row (grows on overflow)
   int64_t stat_launches = 0;       // kernels launched by the last call / job run
   int64_t stat_total_launches = 0;
   int64_t stat_cand_cap = 0;
@@ -112,8 +112,8 @@ struct Cand {
   float d;
 };
 
-struct TcPair {
-  int32_t i, j;
+struct TcHit {  // one (pair, query, target) short-listed by the tensor-core kernel
+  int32_t pair, i, j;
 };
 
 // ------------------------------------------------------------------------------------------ device helpers
@@ -178,7 +178,12 @@ struct TcWork {   // one unit of the persistent tensor-core kernel
   int32_t m_tile0;     // first 128-row tile of set A streamed against it
   int32_t m_tiles;
 };
-cudaError_t asdm_tc_shortlist_launch(asdm_ctx* ctx, const PairDesc* d_pairs, const void* d_tmaps,
-                                     const TcWork* d_work, int n_work, float t_keep, int mask_sense, TcPair* d_list,
-                                     int32_t* d_list_pair, int list_cap, int32_t* d_list_count);
+// The hit list is segmented: epilogue warp e of CTA c appends to list[(c*EPI_WARPS+e)*seg_cap ..) without atomics and
+// leaves its count in seg_count[c*EPI_WARPS+e] (a count above seg_cap means that segment overflowed).
+#ifndef ASDM_TC_EPI_WARPS
+#define ASDM_TC_EPI_WARPS 4
+#endif
+cudaError_t asdm_tc_shortlist_launch(asdm_ctx* ctx, const PairDesc* d_pairs, const void* d_tmaps, const TcWork* d_work,
+                                     int n_work, float t_keep, int mask_sense, TcHit* d_list, int seg_cap,
+                                     int32_t* d_seg_count, int32_t* d_list_total);
 int asdm_tc_build_tmap(asdm_ctx* ctx, asdm_set* set);

@@ -16,6 +16,8 @@ __device__ __forceinline__ bool bow_target_ok(const PairDesc& pd, const BowParam
   return pd.maskB[j] == P.mask_sense && pd.posB[j] >= 0;
 }
 
+__device__ __forceinline__ int pair_slot(int pair, int n_stride, int i) { return pair * n_stride + i; }
+
 __device__ __forceinline__ void cand_append(int32_t* cnt, Cand* cand, int cap, int qslot, int j, float d,
                                             int32_t* overflow) {
   const int s = atomicAdd(cnt + qslot, 1);
@@ -92,33 +94,34 @@ __global__ void __launch_bounds__(256) k_cand_exact(const PairDesc* __restrict__
       if (!(acc[r][c] <= P.t_keep)) continue;
       if (!bow_query_ok(pd, P, i) || !bow_target_ok(pd, P, j)) continue;
       if (pd.nodeA[i] != pd.nodeB[j]) continue;
-      cand_append(cnt, cand, cap, pair * n_stride + i, j, acc[r][c], overflow);
+      cand_append(cnt, cand, cap, pair_slot(pair, n_stride, i), j, acc[r][c], overflow);
     }
   }
 }
 
-// Exact rerank of the tensor-core short list: one thread per listed (pair, i, j).
+// Exact rerank of the tensor-core short list: one CTA per list segment, one thread per listed (pair, i, j).
+// flags[1] is raised when a segment overflowed (the host grows the list and reruns the job).
 __global__ void __launch_bounds__(256) k_rerank(const PairDesc* __restrict__ pairs, BowParams P, int cap,
-                                                int n_stride, const TcPair* __restrict__ list,
-                                                const int32_t* __restrict__ list_pair,
-                                                const int32_t* __restrict__ list_count, int list_cap,
+                                                int n_stride, const TcHit* __restrict__ list,
+                                                const int32_t* __restrict__ seg_count, int seg_cap,
                                                 int32_t* __restrict__ cnt, Cand* __restrict__ cand,
-                                                int32_t* __restrict__ overflow) {
-  int n = *list_count;
-  if (n > list_cap) {  // the short list itself overflowed: the host falls back to k_cand_exact
-    if (blockIdx.x == 0 && threadIdx.x == 0) overflow[1] = 1;
-    n = list_cap;
+                                                int32_t* __restrict__ flags) {
+  int n = seg_count[blockIdx.x];
+  if (n > seg_cap) {
+    if (threadIdx.x == 0) flags[1] = 1;
+    n = seg_cap;
   }
-  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
-    const int pair = list_pair[e];
-    const PairDesc& pd = pairs[pair];
-    const int i = list[e].i, j = list[e].j;
+  const TcHit* __restrict__ seg = list + (size_t)blockIdx.x * seg_cap;
+  for (int e = threadIdx.x; e < n; e += blockDim.x) {
+    const TcHit h = seg[e];
+    const PairDesc& pd = pairs[h.pair];
+    const int i = h.i, j = h.j;
     if (i >= pd.nA || j >= pd.nB) continue;
     if (!bow_query_ok(pd, P, i) || !bow_target_ok(pd, P, j)) continue;
     if (pd.nodeA[i] != pd.nodeB[j]) continue;
     const float d = asdm_exact_dist(pd.descA + (size_t)i * ASDM_DESC_DIM, pd.descB + (size_t)j * ASDM_DESC_DIM);
     if (!(d <= P.t_keep)) continue;
-    cand_append(cnt, cand, cap, pair * n_stride + i, j, d, overflow);
+    cand_append(cnt, cand, cap, pair_slot(h.pair, n_stride, i), j, d, flags);
   }
 }
 

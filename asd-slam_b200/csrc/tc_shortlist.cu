@@ -25,8 +25,10 @@ constexpr int A_BYTES = TM * KD * 2;   // 32 KB
 constexpr int B_BYTES = TN * KD * 2;   // 64 KB
 constexpr int KBLK_A = TM * 128;       // bytes of one 64-element K block of an A tile (128 B per row)
 constexpr int KBLK_B = TN * 128;
-constexpr int TC_SMEM = 2 * B_BYTES + A_STAGES * A_BYTES + 1024;
-constexpr int TC_THREADS = 192;
+constexpr int EPI_WARPS = ASDM_TC_EPI_WARPS;  // 4 or 8 (two warps per TMEM lane quarter split the columns)
+constexpr int EPI_COLS = TN / (EPI_WARPS / 4);
+constexpr int TC_SMEM = 2 * B_BYTES + A_STAGES * A_BYTES + 256;  // tiles + barriers
+constexpr int TC_THREADS = 64 + 32 * EPI_WARPS;
 constexpr float KAPPA = 0.495f;
 
 // instruction descriptor (cute::UMMA::InstrDescriptor): D=f32, A=B=bf16, both K-major, N=256, M=128
@@ -119,18 +121,40 @@ struct __align__(8) TcBarriers {
   uint32_t tmem_base;
 };
 
+// The slow path of the epilogue, entered by a whole warp when some lane of it saw max(32 columns) >= its row bound.
+// Emits (pair, i, j) for every column at or above the row bound; the query-side gates are already folded into the
+// bound (+inf for unusable rows), the target-side gates (mask, node, j < nB) are re-checked by k_rerank.
+__device__ __noinline__ int tc_emit_hits(uint32_t mask, int pair, int i, int jbase, TcHit* __restrict__ seg, int seg_cnt,
+                                         int seg_cap) {
+  const unsigned full = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const unsigned lt = (1u << lane) - 1u;
+  while (__any_sync(full, mask != 0u)) {
+    const bool has = mask != 0u;
+    const int c = __ffs((int)mask) - 1;
+    mask &= mask - 1u;
+    const unsigned b = __ballot_sync(full, has);
+    if (has) {
+      const int pos = seg_cnt + __popc(b & lt);
+      if (pos < seg_cap) seg[pos] = TcHit{pair, i, jbase + c};
+    }
+    seg_cnt += __popc(b);
+  }
+  return seg_cnt;
+}
+
 __global__ void __launch_bounds__(TC_THREADS, 1)
 k_tc_shortlist(const PairDesc* __restrict__ pairs, const uint8_t* __restrict__ tmaps, const TcWork* __restrict__ work,
-               int n_work, float t_half, int mask_sense, TcPair* __restrict__ list, int32_t* __restrict__ list_pair,
-               int list_cap, int32_t* __restrict__ list_count) {
-  extern __shared__ uint8_t smem_raw[];
-  __shared__ TcBarriers bars;
-  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+               int n_work, float t_half, int mask_sense, TcHit* __restrict__ list, int seg_cap,
+               int32_t* __restrict__ seg_count, int32_t* __restrict__ list_total) {
+  extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* smB = smem;                  // 2 x 64 KB
   uint8_t* smA = smem + 2 * B_BYTES;    // A_STAGES x 32 KB
+  TcBarriers& bars = *reinterpret_cast<TcBarriers*>(smem + 2 * B_BYTES + A_STAGES * A_BYTES);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {
+    if (smem_u32(smem) & 1023u) __trap();  // the 128-byte swizzle of the tiles assumes 1024 B alignment
     for (int s = 0; s < A_STAGES; s++) {
       mbar_init(&bars.a_full[s], 1);
       mbar_init(&bars.a_empty[s], 1);
@@ -139,7 +163,7 @@ k_tc_shortlist(const PairDesc* __restrict__ pairs, const uint8_t* __restrict__ t
       mbar_init(&bars.b_full[s], 1);
       mbar_init(&bars.b_empty[s], 1);
       mbar_init(&bars.t_full[s], 1);
-      mbar_init(&bars.t_empty[s], 4);
+      mbar_init(&bars.t_empty[s], EPI_WARPS);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -222,9 +246,15 @@ k_tc_shortlist(const PairDesc* __restrict__ pairs, const uint8_t* __restrict__ t
       }
     }
   } else {
-    // ================================================================ epilogue: 4 warps, one per TMEM lane quarter
+    // ================================================================ epilogue: EPI_WARPS warps; warp e reads TMEM
+    // lanes 32*(warp%4).. (the hardware's lane-quarter rule) and columns [chalf*EPI_COLS, +EPI_COLS)
+    const int ew = warp - 2;
     const int quarter = warp & 3;
+    const int chalf = ew >> 2;
     const int row = quarter * 32 + lane;
+    const int seg_id = blockIdx.x * EPI_WARPS + ew;
+    TcHit* __restrict__ seg = list + (size_t)seg_id * seg_cap;
+    int seg_cnt = 0;
     int acc = 0;
     uint32_t accphase = 0;
     const float INF = __int_as_float(0x7f800000);
@@ -232,50 +262,39 @@ k_tc_shortlist(const PairDesc* __restrict__ pairs, const uint8_t* __restrict__ t
       const TcWork w = work[u];
       const PairDesc& pd = pairs[w.pair];
       const int nA = pd.nA, nB = pd.nB;
-      const int j0 = w.n_tile * TN;
-      const float* __restrict__ normB = pd.normB;
+      const float* __restrict__ normA = pd.normA;
+      const uint8_t* __restrict__ maskA = pd.maskA;
+      const int32_t* __restrict__ posA = pd.posA;
+      const int j0 = w.n_tile * TN + chalf * EPI_COLS;
       float minb = INF;
 #pragma unroll
-      for (int k = 0; k < TN / 32; k++) {
+      for (int k = 0; k < EPI_COLS / 32; k++) {
         const int j = j0 + k * 32 + lane;
-        if (j < nB) minb = fminf(minb, KAPPA * __ldg(normB + j));
+        if (j < nB) minb = fminf(minb, KAPPA * __ldg(pd.normB + j));
       }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) minb = fminf(minb, __shfl_xor_sync(0xffffffffu, minb, o));
+      const float colb = minb - t_half;  // +inf when the whole column range is padding
       for (int t = 0; t < w.m_tiles; t++) {
         const int i = (w.m_tile0 + t) * TM + row;
-        const float ai = i < nA ? KAPPA * __ldg(pd.normA + i) : INF;
-        const float thr_row = (ai + minb) - t_half;  // +inf for padding rows / all-padding column tiles
+        float ai = INF;
+        if (i < nA && maskA[i] == mask_sense && posA[i] >= 0) ai = KAPPA * __ldg(normA + i);
+        const float thr_row = ai + colb;  // +inf for padding / unusable rows
         mbar_wait(&bars.t_full[acc], accphase);
         tc_fence_after();
-        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)acc * TN;
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * TN + chalf * EPI_COLS);
         uint32_t v[2][32];
         tmem_ld32(taddr, v[0]);
-#pragma unroll
-        for (int ch = 0; ch < TN / 32; ch++) {
+#pragma unroll 2
+        for (int ch = 0; ch < EPI_COLS / 32; ch++) {
           tmem_ld_wait();
-          if (ch + 1 < TN / 32) tmem_ld32(taddr + (ch + 1) * 32, v[(ch + 1) & 1]);
+          if (ch + 1 < EPI_COLS / 32) tmem_ld32(taddr + (ch + 1) * 32, v[(ch + 1) & 1]);
           const uint32_t(&cur)[32] = v[ch & 1];
-          if (max_of_32(cur) >= thr_row) {
-            // rare: some column of this row may be a candidate -- test each against its own bound and the gates
-            if (pd.maskA[i] == mask_sense && pd.posA[i] >= 0) {
-              const uint32_t nodeA = pd.nodeA[i];
+          if (__any_sync(0xffffffffu, max_of_32(cur) >= thr_row)) {
+            uint32_t mask = 0;
 #pragma unroll
-              for (int c = 0; c < 32; c++) {
-                const float x = __uint_as_float(cur[c]);
-                if (x >= thr_row) {
-                  const int j = j0 + ch * 32 + c;
-                  if (j < nB && x >= (ai + KAPPA * __ldg(normB + j)) - t_half && pd.maskB[j] == mask_sense &&
-                      pd.posB[j] >= 0 && pd.nodeB[j] == nodeA) {
-                    const int slot = atomicAdd(list_count, 1);
-                    if (slot < list_cap) {
-                      list[slot] = TcPair{i, j};
-                      list_pair[slot] = w.pair;
-                    }
-                  }
-                }
-              }
-            }
+            for (int c = 0; c < 32; c++) mask |= (__uint_as_float(cur[c]) >= thr_row) ? (1u << c) : 0u;
+            seg_cnt = tc_emit_hits(mask, w.pair, i, j0 + ch * 32, seg, seg_cnt, seg_cap);
           }
         }
         tc_fence_before();
@@ -284,6 +303,10 @@ k_tc_shortlist(const PairDesc* __restrict__ pairs, const uint8_t* __restrict__ t
         acc ^= 1;
         if (acc == 0) accphase ^= 1;
       }
+    }
+    if (lane == 0) {
+      seg_count[seg_id] = seg_cnt;  // > seg_cap means this segment overflowed: the host grows the list and reruns
+      if (seg_cnt) atomicAdd(list_total, seg_cnt);
     }
   }
 
@@ -327,8 +350,8 @@ int asdm_tc_build_tmap(asdm_ctx* ctx, asdm_set* set) {
 }
 
 cudaError_t asdm_tc_shortlist_launch(asdm_ctx* ctx, const PairDesc* d_pairs, const void* d_tmaps, const TcWork* d_work,
-                                     int n_work, float t_keep, int mask_sense, TcPair* d_list, int32_t* d_list_pair,
-                                     int list_cap, int32_t* d_list_count) {
+                                     int n_work, float t_keep, int mask_sense, TcHit* d_list, int seg_cap,
+                                     int32_t* d_seg_count, int32_t* d_list_total) {
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(k_tc_shortlist, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM);
@@ -338,6 +361,6 @@ cudaError_t asdm_tc_shortlist_launch(asdm_ctx* ctx, const PairDesc* d_pairs, con
   const float t_half = 0.5f * t_keep * 1.0001f + 1e-6f;
   const int grid = n_work < ctx->sm_count ? n_work : ctx->sm_count;
   k_tc_shortlist<<<grid, TC_THREADS, TC_SMEM, ctx->stream>>>(d_pairs, (const uint8_t*)d_tmaps, d_work, n_work, t_half, mask_sense,
-                                                             d_list, d_list_pair, list_cap, d_list_count);
+                                                             d_list, seg_cap, d_seg_count, d_list_total);
   return cudaGetLastError();
 }
