@@ -147,6 +147,7 @@ extern "C" int asdm_set_option(asdm_ctx* ctx, const char* key, int value) {
   else if (!strcmp(key, "cand_cap")) ctx->opt_cand_cap = std::max(1, value);
   else if (!strcmp(key, "list_cap_per_query")) ctx->opt_list_cap_per_query = std::max(1, value);
   else if (!strcmp(key, "time_kernels")) ctx->opt_time_kernels = value;
+  else if (!strcmp(key, "tc_epi_warps")) ctx->opt_tc_epi_warps = value == 8 ? 8 : 4;
   else return fail(ctx, ASDM_ERR_INVALID, "unknown option");
   return ASDM_OK;
 }
@@ -417,9 +418,9 @@ static int job_alloc_scratch(asdm_job* j) {
   if ((rc = ensure(ctx, j->d_dist, P * j->out_stride * sizeof(float)))) return rc;
   if ((rc = ensure(ctx, j->d_nm, P * sizeof(int32_t)))) return rc;
   if (j->use_tc) {
-    j->n_seg = ctx->sm_count * ASDM_TC_EPI_WARPS;
+    j->n_seg = ctx->sm_count * ASDM_TC_MAX_EPI_WARPS;
     {  // only the CTAs that get work fill their segments
-      const int active = std::max(1, std::min(j->n_work, ctx->sm_count)) * ASDM_TC_EPI_WARPS;
+      const int active = std::max(1, std::min(j->n_work, ctx->sm_count)) * ASDM_TC_MAX_EPI_WARPS;
       j->seg_cap = std::max(1024, (j->list_cap + active - 1) / active);
     }
     if ((rc = ensure(ctx, j->d_list, (size_t)j->seg_cap * j->n_seg * sizeof(TcHit)))) return rc;

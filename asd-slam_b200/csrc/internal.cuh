@@ -29,7 +29,8 @@ struct asdm_ctx {
   std::string err;
   int opt_force_exact = 0;
   int opt_cand_cap = 8;
-  int opt_list_cap_per_query = 4;  // tensor-core short list slots per query row (grows on overflow)
+  int opt_list_cap_per_query = 4;
+  int opt_tc_epi_warps = 8;        // epilogue warps of the tensor-core kernel: 4 or 8  // tensor-core short list slots per query row (grows on overflow)
   int64_t stat_launches = 0;       // kernels launched by the last call / job run
   int64_t stat_total_launches = 0;
   int64_t stat_cand_cap = 0;
@@ -180,9 +181,7 @@ struct TcWork {   // one unit of the persistent tensor-core kernel
 };
 // The hit list is segmented: epilogue warp e of CTA c appends to list[(c*EPI_WARPS+e)*seg_cap ..) without atomics and
 // leaves its count in seg_count[c*EPI_WARPS+e] (a count above seg_cap means that segment overflowed).
-#ifndef ASDM_TC_EPI_WARPS
-#define ASDM_TC_EPI_WARPS 4
-#endif
+#define ASDM_TC_MAX_EPI_WARPS 8
 cudaError_t asdm_tc_shortlist_launch(asdm_ctx* ctx, const PairDesc* d_pairs, const void* d_tmaps, const TcWork* d_work,
                                      int n_work, float t_keep, int mask_sense, TcHit* d_list, int seg_cap,
                                      int32_t* d_seg_count, int32_t* d_list_total);

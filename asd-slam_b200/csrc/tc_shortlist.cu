@@ -25,10 +25,7 @@ constexpr int A_BYTES = TM * KD * 2;   // 32 KB
 constexpr int B_BYTES = TN * KD * 2;   // 64 KB
 constexpr int KBLK_A = TM * 128;       // bytes of one 64-element K block of an A tile (128 B per row)
 constexpr int KBLK_B = TN * 128;
-constexpr int EPI_WARPS = ASDM_TC_EPI_WARPS;  // 4 or 8 (two warps per TMEM lane quarter split the columns)
-constexpr int EPI_COLS = TN / (EPI_WARPS / 4);
 constexpr int TC_SMEM = 2 * B_BYTES + A_STAGES * A_BYTES + 256;  // tiles + barriers
-constexpr int TC_THREADS = 64 + 32 * EPI_WARPS;
 constexpr float KAPPA = 0.495f;
 
 // instruction descriptor (cute::UMMA::InstrDescriptor): D=f32, A=B=bf16, both K-major, N=256, M=128
@@ -143,10 +140,13 @@ __device__ __noinline__ int tc_emit_hits(uint32_t mask, int pair, int i, int jba
   return seg_cnt;
 }
 
-__global__ void __launch_bounds__(TC_THREADS, 1)
+// EPI_WARPS = 4 or 8 (with 8, the two warps of a TMEM lane quarter split the 256 columns)
+template <int EPI_WARPS>
+__global__ void __launch_bounds__(64 + 32 * EPI_WARPS, 1)
 k_tc_shortlist(const PairDesc* __restrict__ pairs, const uint8_t* __restrict__ tmaps, const TcWork* __restrict__ work,
                int n_work, float t_half, int mask_sense, TcHit* __restrict__ list, int seg_cap,
                int32_t* __restrict__ seg_count, int32_t* __restrict__ list_total) {
+  constexpr int EPI_COLS = TN / (EPI_WARPS / 4);
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* smB = smem;                  // 2 x 64 KB
   uint8_t* smA = smem + 2 * B_BYTES;    // A_STAGES x 32 KB
@@ -275,11 +275,18 @@ k_tc_shortlist(const PairDesc* __restrict__ pairs, const uint8_t* __restrict__ t
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) minb = fminf(minb, __shfl_xor_sync(0xffffffffu, minb, o));
       const float colb = minb - t_half;  // +inf when the whole column range is padding
-      for (int t = 0; t < w.m_tiles; t++) {
+      // row bound of the next tile is fetched one tile ahead, so its global-load latency hides behind this tile
+      auto row_bound = [&](int t) -> float {
         const int i = (w.m_tile0 + t) * TM + row;
         float ai = INF;
-        if (i < nA && maskA[i] == mask_sense && posA[i] >= 0) ai = KAPPA * __ldg(normA + i);
-        const float thr_row = ai + colb;  // +inf for padding / unusable rows
+        if (t < w.m_tiles && i < nA && maskA[i] == mask_sense && posA[i] >= 0) ai = KAPPA * __ldg(normA + i);
+        return ai;
+      };
+      float ai_next = row_bound(0);
+      for (int t = 0; t < w.m_tiles; t++) {
+        const int i = (w.m_tile0 + t) * TM + row;
+        const float thr_row = ai_next + colb;  // +inf for padding / unusable rows
+        ai_next = row_bound(t + 1);
         mbar_wait(&bars.t_full[acc], accphase);
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * TN + chalf * EPI_COLS);
@@ -349,18 +356,27 @@ int asdm_tc_build_tmap(asdm_ctx* ctx, asdm_set* set) {
   return ASDM_OK;
 }
 
-cudaError_t asdm_tc_shortlist_launch(asdm_ctx* ctx, const PairDesc* d_pairs, const void* d_tmaps, const TcWork* d_work,
-                                     int n_work, float t_keep, int mask_sense, TcHit* d_list, int seg_cap,
-                                     int32_t* d_seg_count, int32_t* d_list_total) {
+template <int EPI_WARPS>
+static cudaError_t tc_launch(asdm_ctx* ctx, const PairDesc* d_pairs, const void* d_tmaps, const TcWork* d_work, int n_work,
+                             float t_half, int mask_sense, TcHit* d_list, int seg_cap, int32_t* d_seg_count,
+                             int32_t* d_list_total) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(k_tc_shortlist, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(k_tc_shortlist<EPI_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
-  const float t_half = 0.5f * t_keep * 1.0001f + 1e-6f;
   const int grid = n_work < ctx->sm_count ? n_work : ctx->sm_count;
-  k_tc_shortlist<<<grid, TC_THREADS, TC_SMEM, ctx->stream>>>(d_pairs, (const uint8_t*)d_tmaps, d_work, n_work, t_half, mask_sense,
-                                                             d_list, seg_cap, d_seg_count, d_list_total);
+  k_tc_shortlist<EPI_WARPS><<<grid, 64 + 32 * EPI_WARPS, TC_SMEM, ctx->stream>>>(
+      d_pairs, (const uint8_t*)d_tmaps, d_work, n_work, t_half, mask_sense, d_list, seg_cap, d_seg_count, d_list_total);
   return cudaGetLastError();
+}
+
+cudaError_t asdm_tc_shortlist_launch(asdm_ctx* ctx, const PairDesc* d_pairs, const void* d_tmaps, const TcWork* d_work,
+                                     int n_work, float t_keep, int mask_sense, TcHit* d_list, int seg_cap,
+                                     int32_t* d_seg_count, int32_t* d_list_total) {
+  const float t_half = 0.5f * t_keep * 1.0001f + 1e-6f;
+  if (ctx->opt_tc_epi_warps == 8)
+    return tc_launch<8>(ctx, d_pairs, d_tmaps, d_work, n_work, t_half, mask_sense, d_list, seg_cap, d_seg_count, d_list_total);
+  return tc_launch<4>(ctx, d_pairs, d_tmaps, d_work, n_work, t_half, mask_sense, d_list, seg_cap, d_seg_count, d_list_total);
 }

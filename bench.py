@@ -170,6 +170,8 @@ def run_ours(args):
     ctx = pkg.Context(local)
     stream = torch.cuda.Stream()
     ctx.set_stream(stream.cuda_stream)
+    if args.epi_warps:
+        ctx.set_option("tc_epi_warps", args.epi_warps)
     n, P = N_DESC, args.pairs
     c = make_inputs(pkg, rank, n_pairs=P)
     kfs = c["kfs"]
@@ -325,6 +327,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--pairs", type=int, default=N_PAIRS, help="keyframe pairs per GPU per step (default: the C5 sweep)")
+    ap.add_argument("--epi-warps", type=int, default=0, help="tuning: epilogue warps of the tensor-core kernel (4 or 8)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
