@@ -1,0 +1,466 @@
+// ref_driver.cc -- flat C entry points over the reference's OWN matcher, compiled from where it lies:
+//   /root/reference/src/vslam/src/ORBmatcher.cc                  (unmodified, whole file)
+//   Frame.cc / KeyFrame.cc / MapPoint.cc function bodies          (line ranges extracted by oracle/Makefile into
+//                                                                  oracle/_ref/gen/*.inc at build time; not committed)
+// against the from-scratch header shims in oracle/ref_shim (OpenCV 3.2, libtorch, ROS and g2o are not installed).
+// The result, oracle/_ref/libref_orbmatcher.so, exists to PIN the CPU oracle (tests/test_oracle_vs_ref.py) and to
+// generate the golden fixtures under tests/golden/.  TEST INFRASTRUCTURE ONLY: nothing in the product loads it, and
+// it cannot be built on the GPU box (/root/reference does not exist there) -- the prebuilt .so travels instead.
+//
+// Each ref_* function takes the same flat arrays as its ora_* twin in asd_oracle.h, builds shim Frame / KeyFrame /
+// MapPoint objects from them and calls the reference method.  Where an overload derives its search window from
+// poses and 3-D points, the harness picks identity poses, fx=fy=1, cx=cy=0 and points (u, v, 1), so the reference's
+// own projection code yields exactly the (u, v) passed in.
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <memory>
+
+#include "ORBmatcher.h"  // ref_shim/ORBmatcher.h -> the reference's include/ORBmatcher.h
+#include "asd_oracle.h"
+
+namespace ORB_SLAM2 {
+float Frame::fx = 1, Frame::fy = 1, Frame::cx = 0, Frame::cy = 0, Frame::invfx = 1, Frame::invfy = 1;
+float Frame::mfGridElementWidthInv = 0, Frame::mfGridElementHeightInv = 0;
+float Frame::mnMinX = 0, Frame::mnMaxX = 0, Frame::mnMinY = 0, Frame::mnMaxY = 0;
+// the reference's own function bodies (see oracle/Makefile for the line ranges)
+#include "_ref/gen/frame_grid.inc"
+#include "_ref/gen/keyframe_grid.inc"
+#include "_ref/gen/mappoint_scale.inc"
+
+// protected members of the reference class, opened for direct checks
+struct OpenMatcher : public ORBmatcher {
+  OpenMatcher(float r, bool o) : ORBmatcher(r, o) {}
+  using ORBmatcher::CheckDistEpipolarLine;
+  using ORBmatcher::ComputeThreeMaxima;
+  using ORBmatcher::RadiusByViewingCos;
+};
+}  // namespace ORB_SLAM2
+
+using namespace ORB_SLAM2;
+
+namespace {
+
+cv::Mat desc_mat(const float* d, int n) {
+  cv::Mat m(n, ORA_DESC_DIM, CV_32F);
+  if (n > 0) memcpy(m.ptr<float>(0), d, (size_t)n * ORA_DESC_DIM * sizeof(float));
+  return m;
+}
+cv::Mat desc_row(const float* d) { return desc_mat(d, 1); }
+
+std::vector<cv::KeyPoint> keypoints(const ora_kp* k, int n) {
+  std::vector<cv::KeyPoint> v((size_t)n);
+  for (int i = 0; i < n; i++) {
+    v[i].pt.x = k[i].x;
+    v[i].pt.y = k[i].y;
+    v[i].angle = k[i].angle;
+    v[i].octave = k[i].octave;
+  }
+  return v;
+}
+
+void featvec(const ora_featvec* fv, DBoW2::FeatureVector& out) {
+  out.clear();
+  if (!fv) return;
+  for (int k = 0; k < fv->n_nodes; k++)
+    for (int e = fv->off[k]; e < fv->off[k + 1]; e++) out.addFeature(fv->node_ids[k], (unsigned)fv->idx[e]);
+}
+
+cv::Mat eye4() {
+  cv::Mat T(4, 4, CV_32F);
+  for (int i = 0; i < 4; i++) T.at<float>(i, i) = 1.f;
+  return T;
+}
+cv::Mat vec3(float x, float y, float z) {
+  cv::Mat v(3, 1, CV_32F);
+  v.at<float>(0) = x; v.at<float>(1) = y; v.at<float>(2) = z;
+  return v;
+}
+
+void levels(const float* sf, const float* sigma2, int n_levels, float log_scale, std::vector<float>& vsf,
+            std::vector<float>& vs2, std::vector<float>& vis2, int& nl, float& lsf) {
+  vsf.assign(sf, sf + n_levels);
+  vs2.clear(); vis2.clear();
+  for (int l = 0; l < n_levels; l++) {
+    const float s2 = sigma2 ? sigma2[l] : sf[l] * sf[l];
+    vs2.push_back(s2);
+    vis2.push_back(1.0f / s2);
+  }
+  nl = n_levels;
+  lsf = log_scale;
+}
+
+void fill_frame(Frame& F, const float* desc, const ora_kp* kps, int n, const ora_grid* g) {
+  F.N = n;
+  F.mvKeys = F.mvKeysUn = keypoints(kps, n);
+  F.mDescriptors = desc_mat(desc, n);
+  F.mvpMapPoints.assign((size_t)n, nullptr);
+  F.mvbOutlier.assign((size_t)n, false);
+  F.mTcw = eye4();
+  Frame::fx = Frame::fy = 1.f; Frame::cx = Frame::cy = 0.f;
+  if (g) {
+    Frame::mnMinX = g->min_x; Frame::mnMaxX = g->max_x; Frame::mnMinY = g->min_y; Frame::mnMaxY = g->max_y;
+    Frame::mfGridElementWidthInv = g->inv_w; Frame::mfGridElementHeightInv = g->inv_h;
+    F.AssignFeaturesToGrid();
+  }
+}
+
+void fill_keyframe(KeyFrame& K, const float* desc, const ora_kp* kps, int n, const ora_grid* g) {
+  K.N = n;
+  K.mvKeys = K.mvKeysUn = keypoints(kps, n);
+  K.mDescriptors = desc_mat(desc, n);
+  K.mvpMapPoints.assign((size_t)n, nullptr);
+  K.Tcw = eye4();
+  K.Ow = vec3(0, 0, 0);
+  K.fx = K.fy = 1.f; K.cx = K.cy = 0.f; K.invfx = K.invfy = 1.f;
+  if (g) {
+    K.mnMinX = (int)g->min_x; K.mnMaxX = (int)g->max_x; K.mnMinY = (int)g->min_y; K.mnMaxY = (int)g->max_y;
+    K.mfGridElementWidthInv = g->inv_w; K.mfGridElementHeightInv = g->inv_h;
+    K.mnGridCols = g->cols; K.mnGridRows = g->rows;
+    K.mGrid.assign((size_t)g->cols, std::vector<std::vector<size_t> >((size_t)g->rows));
+    K.AssignFeaturesToGrid();
+  }
+}
+
+// one MapPoint per usable feature; unusable features alternate between "no map point" and "bad map point"
+// (the reference treats both alike: `if(!pMP) continue; if(pMP->isBad()) continue;`)
+struct Pool {
+  std::vector<std::unique_ptr<MapPoint> > own;
+  MapPoint* make(int id) {
+    own.emplace_back(new MapPoint());
+    own.back()->id = id;
+    return own.back().get();
+  }
+};
+
+void attach_valid(Pool& pool, KeyFrame& K, const uint8_t* valid, int n) {
+  for (int i = 0; i < n; i++) {
+    if (valid[i]) {
+      K.mvpMapPoints[i] = pool.make(i);
+      K.mvpMapPoints[i]->nObs = 1;
+    } else if (i & 1) {
+      MapPoint* p = pool.make(i);
+      p->mbBad = true;
+      K.mvpMapPoints[i] = p;
+    }
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+// ------------------------------------------------------------------------------------------- scalar pieces
+float ref_descriptor_distance(const float* a, const float* b) {
+  return ORBmatcher::DescriptorDistance(desc_row(a), desc_row(b));  // ORBmatcher.cc:1629-1650
+}
+
+void ref_compute_three_maxima(const int32_t* sizes, int L, int32_t* i1, int32_t* i2, int32_t* i3) {
+  std::vector<std::vector<int> > h((size_t)L);
+  for (int b = 0; b < L; b++) h[b].assign((size_t)sizes[b], 0);
+  OpenMatcher m(0.6f, true);
+  int a = -1, b = -1, c = -1;  // every call site initialises them to -1 (e.g. :276-278)
+  m.ComputeThreeMaxima(h.data(), L, a, b, c);  // :1584-1625
+  *i1 = a; *i2 = b; *i3 = c;
+}
+
+float ref_radius_by_viewing_cos(float view_cos) { return OpenMatcher(0.6f, true).RadiusByViewingCos(view_cos); }
+
+int ref_check_dist_epipolar_line(float x1, float y1, float x2, float y2, int octave2, const float* F12,
+                                 const float* level_sigma2, int n_levels) {
+  KeyFrame K2;
+  K2.mvLevelSigma2.assign(level_sigma2, level_sigma2 + n_levels);
+  cv::Mat F(3, 3, CV_32F);
+  memcpy(F.ptr<float>(0), F12, 9 * sizeof(float));
+  cv::KeyPoint k1, k2;
+  k1.pt.x = x1; k1.pt.y = y1; k2.pt.x = x2; k2.pt.y = y2; k2.octave = octave2;
+  return OpenMatcher(0.6f, true).CheckDistEpipolarLine(k1, k2, F, &K2) ? 1 : 0;  // :136-153
+}
+
+int ref_predict_scale(float max_distance, float current_dist, float log_scale_factor, int n_levels) {
+  MapPoint mp;
+  mp.mfMaxDistance = max_distance;
+  Frame F;
+  F.mfLogScaleFactor = log_scale_factor;
+  F.mnScaleLevels = n_levels;
+  return mp.PredictScale(current_dist, &F);  // MapPoint.cc:438-453
+}
+
+// ------------------------------------------------------------------------------------------- grid
+// Frame::AssignFeaturesToGrid + GetFeaturesInArea (Frame.cc:123-138, 219-286): returns the count written to out
+int ref_frame_features_in_area(const ora_kp* kps, int n, const ora_grid* g, float x, float y, float r, int min_level,
+                               int max_level, int32_t* out) {
+  Frame F;
+  fill_frame(F, nullptr, kps, 0, nullptr);
+  F.N = n;
+  F.mvKeys = F.mvKeysUn = keypoints(kps, n);
+  Frame::mnMinX = g->min_x; Frame::mnMaxX = g->max_x; Frame::mnMinY = g->min_y; Frame::mnMaxY = g->max_y;
+  Frame::mfGridElementWidthInv = g->inv_w; Frame::mfGridElementHeightInv = g->inv_h;
+  F.AssignFeaturesToGrid();
+  const std::vector<size_t> v = F.GetFeaturesInArea(x, y, r, min_level, max_level);
+  for (size_t k = 0; k < v.size(); k++) out[k] = (int32_t)v[k];
+  return (int)v.size();
+}
+
+// KeyFrame::AssignFeaturesToGrid + GetFeaturesInArea (KeyFrame.cc:116-143, 839-878)
+int ref_keyframe_features_in_area(const ora_kp* kps, int n, const ora_grid* g, float x, float y, float r,
+                                  int32_t* out) {
+  KeyFrame K;
+  fill_keyframe(K, nullptr, kps, 0, nullptr);
+  K.N = n;
+  K.mvKeys = K.mvKeysUn = keypoints(kps, n);
+  K.mnMinX = (int)g->min_x; K.mnMaxX = (int)g->max_x; K.mnMinY = (int)g->min_y; K.mnMaxY = (int)g->max_y;
+  K.mfGridElementWidthInv = g->inv_w; K.mfGridElementHeightInv = g->inv_h;
+  K.mnGridCols = g->cols; K.mnGridRows = g->rows;
+  K.mGrid.assign((size_t)g->cols, std::vector<std::vector<size_t> >((size_t)g->rows));
+  K.AssignFeaturesToGrid();
+  const std::vector<size_t> v = K.GetFeaturesInArea(x, y, r);
+  for (size_t k = 0; k < v.size(); k++) out[k] = (int32_t)v[k];
+  return (int)v.size();
+}
+
+// ------------------------------------------------------------------------------------------- BoW-gated searches
+// ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches)  (ORBmatcher.cc:156-297)
+int ref_search_by_bow_kf_f(const float* desc_kf, const ora_kp* kps_kf, int n_kf, const ora_featvec* fv_kf,
+                           const uint8_t* valid_kf, const float* desc_f, const ora_kp* kps_f, int n_f,
+                           const ora_featvec* fv_f, float nnratio, int check_ori, int32_t* match_f) {
+  Pool pool;
+  KeyFrame K;
+  fill_keyframe(K, desc_kf, kps_kf, n_kf, nullptr);
+  featvec(fv_kf, K.mFeatVec);
+  attach_valid(pool, K, valid_kf, n_kf);
+  Frame F;
+  fill_frame(F, desc_f, kps_f, n_f, nullptr);
+  featvec(fv_f, F.mFeatVec);
+  std::vector<MapPoint*> out;
+  ORBmatcher m(nnratio, check_ori != 0);
+  const int nm = m.SearchByBoW(&K, F, out);
+  for (int j = 0; j < n_f; j++) match_f[j] = out[j] ? out[j]->id : -1;
+  return nm;
+}
+
+// ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12)  (ORBmatcher.cc:533-666)
+int ref_search_by_bow_kf_kf(const float* desc1, const ora_kp* kps1, int n1, const ora_featvec* fv1,
+                            const uint8_t* valid1, const float* desc2, const ora_kp* kps2, int n2,
+                            const ora_featvec* fv2, const uint8_t* valid2, float nnratio, int check_ori,
+                            int32_t* match12) {
+  Pool pool;
+  KeyFrame K1, K2;
+  fill_keyframe(K1, desc1, kps1, n1, nullptr);
+  fill_keyframe(K2, desc2, kps2, n2, nullptr);
+  featvec(fv1, K1.mFeatVec);
+  featvec(fv2, K2.mFeatVec);
+  attach_valid(pool, K1, valid1, n1);
+  attach_valid(pool, K2, valid2, n2);
+  std::vector<MapPoint*> out;
+  ORBmatcher m(nnratio, check_ori != 0);
+  const int nm = m.SearchByBoW(&K1, &K2, out);
+  for (int i = 0; i < n1; i++) match12[i] = out[i] ? out[i]->id : -1;  // map point of KF2 feature id
+  return nm;
+}
+
+// ORBmatcher::SearchForTriangulation (ORBmatcher.cc:669-822). The epipole (:675-682) is produced by the reference's
+// own code from Cw = (ex, ey, 1), R2w = I, t2w = 0, fx = fy = 1, cx = cy = 0.
+int ref_search_for_triangulation(const float* desc1, const ora_kp* kps1, int n1, const ora_featvec* fv1,
+                                 const uint8_t* has_mp1, const float* desc2, const ora_kp* kps2, int n2,
+                                 const ora_featvec* fv2, const uint8_t* has_mp2, const float* F12, float ex,
+                                 float ey, const float* scale_factors2, const float* level_sigma2_2, int n_levels,
+                                 int check_ori, int32_t* match12) {
+  Pool pool;
+  KeyFrame K1, K2;
+  fill_keyframe(K1, desc1, kps1, n1, nullptr);
+  fill_keyframe(K2, desc2, kps2, n2, nullptr);
+  featvec(fv1, K1.mFeatVec);
+  featvec(fv2, K2.mFeatVec);
+  for (int i = 0; i < n1; i++)
+    if (has_mp1[i]) K1.mvpMapPoints[i] = pool.make(i);
+  for (int i = 0; i < n2; i++)
+    if (has_mp2[i]) K2.mvpMapPoints[i] = pool.make(i);
+  K1.Ow = vec3(ex, ey, 1.f);
+  float lsf;
+  levels(scale_factors2, level_sigma2_2, n_levels, std::log(1.2f), K2.mvScaleFactors, K2.mvLevelSigma2,
+         K2.mvInvLevelSigma2, K2.mnScaleLevels, lsf);
+  K1.mvScaleFactors = K2.mvScaleFactors; K1.mvLevelSigma2 = K2.mvLevelSigma2;
+  cv::Mat F(3, 3, CV_32F);
+  memcpy(F.ptr<float>(0), F12, 9 * sizeof(float));
+  std::vector<std::pair<size_t, size_t> > pairs;
+  ORBmatcher m(0.6f, check_ori != 0);
+  const int nm = m.SearchForTriangulation(&K1, &K2, F, pairs, false);
+  for (int i = 0; i < n1; i++) match12[i] = -1;
+  for (size_t k = 0; k < pairs.size(); k++) match12[pairs[k].first] = (int32_t)pairs[k].second;
+  return nm;
+}
+
+// ORBmatcher::SearchForInitialization (ORBmatcher.cc:416-531)
+int ref_search_for_initialization(const float* desc1, const ora_kp* kps1, int n1, const float* desc2,
+                                  const ora_kp* kps2, int n2, const ora_grid* g2, float* prev_matched,
+                                  int window_size, float nnratio, int check_ori, int32_t* matches12) {
+  Frame F1, F2;
+  fill_frame(F1, desc1, kps1, n1, nullptr);
+  fill_frame(F2, desc2, kps2, n2, g2);
+  std::vector<cv::Point2f> prev((size_t)n1);
+  for (int i = 0; i < n1; i++) prev[i] = cv::Point2f(prev_matched[2 * i], prev_matched[2 * i + 1]);
+  std::vector<int> out;
+  ORBmatcher m(nnratio, check_ori != 0);
+  const int nm = m.SearchForInitialization(F1, F2, prev, out, window_size);
+  for (int i = 0; i < n1; i++) {
+    matches12[i] = out[i];
+    prev_matched[2 * i] = prev[i].x;
+    prev_matched[2 * i + 1] = prev[i].y;
+  }
+  return nm;
+}
+
+// ------------------------------------------------------------------------------------------- projection searches
+// Shared inputs: q[i].valid / .blocks / .u / .v / .angle as in ora_proj_query (r, min_level, max_level are NOT read:
+// the reference derives them itself from level[i], aux[i] and th), desc_q = one descriptor per query,
+// blocked0[j] = target keypoint j already holds a map point with observations.
+// assign[j] = query whose map point ends up on keypoint j, or -1.
+
+// a4: SearchByProjection(Frame&, vector<MapPoint*>&, th)  (ORBmatcher.cc:44-122); aux = mTrackViewCos
+int ref_sbp_local_map(const float* desc_t, const ora_kp* kps_t, int n_t, const ora_grid* g, const ora_proj_query* q,
+                      const int32_t* level, const float* view_cos, const float* desc_q, int n_q,
+                      const uint8_t* blocked0, const float* scale_factors, int n_levels, float th, float nnratio,
+                      int32_t* assign) {
+  Pool pool;
+  Frame F;
+  fill_frame(F, desc_t, kps_t, n_t, g);
+  F.mvScaleFactors.assign(scale_factors, scale_factors + n_levels);
+  for (int j = 0; j < n_t; j++)
+    if (blocked0 && blocked0[j]) {
+      F.mvpMapPoints[j] = pool.make(-2);
+      F.mvpMapPoints[j]->nObs = 1;
+    }
+  std::vector<MapPoint*> mps((size_t)n_q);
+  for (int i = 0; i < n_q; i++) {
+    MapPoint* p = pool.make(i);
+    p->mbTrackInView = q[i].valid != 0;
+    p->mTrackProjX = q[i].u;
+    p->mTrackProjY = q[i].v;
+    p->mnTrackScaleLevel = level[i];
+    p->mTrackViewCos = view_cos[i];
+    p->nObs = q[i].blocks ? 1 : 0;
+    p->mDescriptor = desc_row(desc_q + (size_t)i * ORA_DESC_DIM);
+    mps[i] = p;
+  }
+  ORBmatcher m(nnratio, true);
+  const int nm = m.SearchByProjection(F, mps, th);
+  for (int j = 0; j < n_t; j++) assign[j] = (F.mvpMapPoints[j] && F.mvpMapPoints[j]->id >= 0) ? F.mvpMapPoints[j]->id : -1;
+  return nm;
+}
+
+// a5: SearchByProjection(Frame& Cur, const Frame& Last, th, bMono=true)  (ORBmatcher.cc:1318-1452);
+// level[i] = LastFrame.mvKeys[i].octave; invalid queries alternate between "no map point" and "outlier"
+int ref_sbp_frame_frame(const float* desc_t, const ora_kp* kps_t, int n_t, const ora_grid* g, const ora_proj_query* q,
+                        const int32_t* level, const float* desc_q, int n_q, const uint8_t* blocked0,
+                        const float* scale_factors, int n_levels, float th, float nnratio, int check_ori,
+                        int32_t* assign) {
+  Pool pool;
+  Frame Cur, Last;
+  fill_frame(Cur, desc_t, kps_t, n_t, g);
+  Cur.mvScaleFactors.assign(scale_factors, scale_factors + n_levels);
+  for (int j = 0; j < n_t; j++)
+    if (blocked0 && blocked0[j]) {
+      Cur.mvpMapPoints[j] = pool.make(-2);
+      Cur.mvpMapPoints[j]->nObs = 1;
+    }
+  Last.N = n_q;
+  Last.mTcw = eye4();
+  Last.mvKeys.resize((size_t)n_q);
+  Last.mvKeysUn.resize((size_t)n_q);
+  Last.mvpMapPoints.assign((size_t)n_q, nullptr);
+  Last.mvbOutlier.assign((size_t)n_q, false);
+  for (int i = 0; i < n_q; i++) {
+    Last.mvKeys[i].octave = Last.mvKeysUn[i].octave = level[i];
+    Last.mvKeys[i].angle = Last.mvKeysUn[i].angle = q[i].angle;
+    if (!q[i].valid && !(i & 1)) continue;
+    MapPoint* p = pool.make(i);
+    p->mWorldPos = vec3(q[i].u, q[i].v, 1.f);
+    p->nObs = q[i].blocks ? 1 : 0;
+    p->mDescriptor = desc_row(desc_q + (size_t)i * ORA_DESC_DIM);
+    Last.mvpMapPoints[i] = p;
+    if (!q[i].valid) Last.mvbOutlier[i] = true;
+  }
+  ORBmatcher m(nnratio, check_ori != 0);
+  const int nm = m.SearchByProjection(Cur, Last, th, true);
+  for (int j = 0; j < n_t; j++) assign[j] = (Cur.mvpMapPoints[j] && Cur.mvpMapPoints[j]->id >= 0) ? Cur.mvpMapPoints[j]->id : -1;
+  return nm;
+}
+
+static void set_distance_for_level(MapPoint* p, float u, float v, int lvl) {
+  // PredictScale (MapPoint.cc:421-453) returns ceil(log(max/dist)/log(1.2)); aim at the middle of the level's bin
+  const float dist = std::sqrt(u * u + v * v + 1.f);
+  p->mfMaxDistance = dist * std::pow(1.2f, (float)lvl - 0.5f);
+  p->mfMinDistance = 0.f;
+}
+
+// a6: SearchByProjection(Frame& Cur, KeyFrame*, sAlreadyFound, th, ORBdist)  (ORBmatcher.cc:1455-1582);
+// level[i] = level PredictScale must return; invalid queries cycle through null / bad / already found
+int ref_sbp_frame_keyframe(const float* desc_t, const ora_kp* kps_t, int n_t, const ora_grid* g,
+                           const ora_proj_query* q, const int32_t* level, const float* desc_q, int n_q,
+                           const uint8_t* blocked0, const float* scale_factors, int n_levels, float th, float orb_dist,
+                           float nnratio, int check_ori, int32_t* assign) {
+  Pool pool;
+  Frame Cur;
+  fill_frame(Cur, desc_t, kps_t, n_t, g);
+  Cur.mvScaleFactors.assign(scale_factors, scale_factors + n_levels);
+  Cur.mnScaleLevels = n_levels;
+  Cur.mfLogScaleFactor = std::log(1.2f);
+  for (int j = 0; j < n_t; j++)
+    if (blocked0 && blocked0[j]) Cur.mvpMapPoints[j] = pool.make(-2);
+  KeyFrame K;
+  K.N = n_q;
+  K.mvKeysUn.resize((size_t)n_q);
+  K.mvpMapPoints.assign((size_t)n_q, nullptr);
+  std::set<MapPoint*> found;
+  for (int i = 0; i < n_q; i++) {
+    K.mvKeysUn[i].angle = q[i].angle;
+    if (!q[i].valid && i % 3 == 0) continue;
+    MapPoint* p = pool.make(i);
+    p->mWorldPos = vec3(q[i].u, q[i].v, 1.f);
+    set_distance_for_level(p, q[i].u, q[i].v, level[i]);
+    p->mDescriptor = desc_row(desc_q + (size_t)i * ORA_DESC_DIM);
+    K.mvpMapPoints[i] = p;
+    if (!q[i].valid) {
+      if (i % 3 == 1) p->mbBad = true;
+      else found.insert(p);
+    }
+  }
+  ORBmatcher m(nnratio, check_ori != 0);
+  const int nm = m.SearchByProjection(Cur, &K, found, th, orb_dist);
+  for (int j = 0; j < n_t; j++) assign[j] = (Cur.mvpMapPoints[j] && Cur.mvpMapPoints[j]->id >= 0) ? Cur.mvpMapPoints[j]->id : -1;
+  return nm;
+}
+
+// a7: SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th)  (ORBmatcher.cc:300-413), Scw = identity
+int ref_sbp_keyframe_sim3(const float* desc_t, const ora_kp* kps_t, int n_t, const ora_grid* g,
+                          const ora_proj_query* q, const int32_t* level, const float* desc_q, int n_q,
+                          const uint8_t* blocked0, const float* scale_factors, int n_levels, int th, float nnratio,
+                          int32_t* assign) {
+  Pool pool;
+  KeyFrame K;
+  fill_keyframe(K, desc_t, kps_t, n_t, g);
+  K.mvScaleFactors.assign(scale_factors, scale_factors + n_levels);
+  K.mnScaleLevels = n_levels;
+  K.mfLogScaleFactor = std::log(1.2f);
+  std::vector<MapPoint*> matched((size_t)n_t, nullptr);
+  for (int j = 0; j < n_t; j++)
+    if (blocked0 && blocked0[j]) matched[j] = pool.make(-2);
+  std::vector<MapPoint*> pts((size_t)n_q);
+  for (int i = 0; i < n_q; i++) {
+    MapPoint* p = pool.make(i);
+    p->mWorldPos = vec3(q[i].u, q[i].v, 1.f);
+    set_distance_for_level(p, q[i].u, q[i].v, level[i]);
+    const float d = std::sqrt(q[i].u * q[i].u + q[i].v * q[i].v + 1.f);
+    p->mNormalVector = vec3(q[i].u / d, q[i].v / d, 1.f / d);
+    p->mDescriptor = desc_row(desc_q + (size_t)i * ORA_DESC_DIM);
+    if (!q[i].valid) p->mbBad = true;
+    pts[i] = p;
+  }
+  ORBmatcher m(nnratio, true);
+  const int nm = m.SearchByProjection(&K, eye4(), pts, matched, th);
+  for (int j = 0; j < n_t; j++) assign[j] = (matched[j] && matched[j]->id >= 0) ? matched[j]->id : -1;
+  return nm;
+}
+
+}  // extern "C"

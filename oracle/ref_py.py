@@ -1,0 +1,178 @@
+"""ctypes wrapper over oracle/_ref/libref_orbmatcher.so -- the reference's OWN ORBmatcher.cc compiled in place
+against header shims (oracle/Makefile `ref`, oracle/ref_driver.cc).  TEST INFRASTRUCTURE ONLY.
+
+Used by tests/test_oracle_vs_ref.py to pin the CPU oracle and by tests/golden/make_golden.py to generate the
+committed fixtures.  The library can only be BUILT where /root/reference exists (this container); the prebuilt .so
+travels to the GPU box.  `available()` says whether it is there.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from oracle_py import FV, Grid, PROJ_QUERY_DTYPE, _f32, _p, _u8, grid_struct
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "_ref", "libref_orbmatcher.so")
+REF_ROOT = "/root/reference/src/vslam"
+
+
+def build():
+    if os.path.isdir(REF_ROOT):
+        subprocess.check_call(["make", "-C", _HERE, "ref"], stdout=subprocess.DEVNULL)
+    return os.path.exists(_LIB)
+
+
+def available():
+    return os.path.exists(_LIB) or build()
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not available():
+            raise RuntimeError("oracle/_ref/libref_orbmatcher.so is missing and /root/reference is not mounted")
+        _lib = C.CDLL(_LIB)
+        _lib.ref_descriptor_distance.restype = C.c_float
+        _lib.ref_radius_by_viewing_cos.restype = C.c_float
+        _lib.ref_radius_by_viewing_cos.argtypes = [C.c_float]
+        _lib.ref_predict_scale.argtypes = [C.c_float, C.c_float, C.c_float, C.c_int]
+        _lib.ref_check_dist_epipolar_line.argtypes = [C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_void_p,
+                                                      C.c_void_p, C.c_int]
+    return _lib
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def descriptor_distance(a, b):
+    a, b = _f32(a), _f32(b)
+    return float(lib().ref_descriptor_distance(_p(a), _p(b)))
+
+
+def compute_three_maxima(sizes):
+    s = _i32(sizes)
+    i1, i2, i3 = C.c_int32(-1), C.c_int32(-1), C.c_int32(-1)
+    lib().ref_compute_three_maxima(_p(s), len(s), C.byref(i1), C.byref(i2), C.byref(i3))
+    return i1.value, i2.value, i3.value
+
+
+def radius_by_viewing_cos(c):
+    return float(lib().ref_radius_by_viewing_cos(float(c)))
+
+
+def predict_scale(max_distance, current_dist, log_scale_factor, n_levels):
+    return int(lib().ref_predict_scale(float(max_distance), float(current_dist), float(log_scale_factor), int(n_levels)))
+
+
+def check_dist_epipolar_line(x1, y1, x2, y2, octave2, F12, level_sigma2):
+    F12, ls = _f32(F12).reshape(9), _f32(level_sigma2)
+    return int(lib().ref_check_dist_epipolar_line(float(x1), float(y1), float(x2), float(y2), int(octave2), _p(F12),
+                                                  _p(ls), len(ls)))
+
+
+def frame_features_in_area(kps, grid, x, y, r, min_level=-1, max_level=-1):
+    g = grid_struct(grid)
+    out = np.zeros(max(len(kps), 1), np.int32)
+    n = lib().ref_frame_features_in_area(_p(kps), len(kps), C.byref(g), C.c_float(x), C.c_float(y), C.c_float(r),
+                                         int(min_level), int(max_level), _p(out))
+    return out[:n].copy()
+
+
+def keyframe_features_in_area(kps, grid, x, y, r):
+    g = grid_struct(grid)
+    out = np.zeros(max(len(kps), 1), np.int32)
+    n = lib().ref_keyframe_features_in_area(_p(kps), len(kps), C.byref(g), C.c_float(x), C.c_float(y), C.c_float(r),
+                                            _p(out))
+    return out[:n].copy()
+
+
+def search_by_bow_kf_f(desc_kf, kps_kf, fv_kf, valid_kf, desc_f, kps_f, fv_f, nnratio, check_ori):
+    desc_kf, desc_f, valid_kf = _f32(desc_kf), _f32(desc_f), _u8(valid_kf)
+    fa, fb = FV.of(fv_kf), FV.of(fv_f)
+    match = np.empty(len(kps_f), np.int32)
+    nm = lib().ref_search_by_bow_kf_f(_p(desc_kf), _p(kps_kf), len(kps_kf), C.byref(fa.c), _p(valid_kf), _p(desc_f),
+                                      _p(kps_f), len(kps_f), C.byref(fb.c), C.c_float(nnratio), int(check_ori),
+                                      _p(match))
+    return nm, match
+
+
+def search_by_bow_kf_kf(desc1, kps1, fv1, valid1, desc2, kps2, fv2, valid2, nnratio, check_ori):
+    desc1, desc2, valid1, valid2 = _f32(desc1), _f32(desc2), _u8(valid1), _u8(valid2)
+    fa, fb = FV.of(fv1), FV.of(fv2)
+    match = np.empty(len(kps1), np.int32)
+    nm = lib().ref_search_by_bow_kf_kf(_p(desc1), _p(kps1), len(kps1), C.byref(fa.c), _p(valid1), _p(desc2), _p(kps2),
+                                       len(kps2), C.byref(fb.c), _p(valid2), C.c_float(nnratio), int(check_ori),
+                                       _p(match))
+    return nm, match
+
+
+def search_for_triangulation(desc1, kps1, fv1, has_mp1, desc2, kps2, fv2, has_mp2, F12, ex, ey, scale_factors2,
+                             level_sigma2_2, check_ori):
+    desc1, desc2, has_mp1, has_mp2 = _f32(desc1), _f32(desc2), _u8(has_mp1), _u8(has_mp2)
+    F12, sf, ls = _f32(F12).reshape(9), _f32(scale_factors2), _f32(level_sigma2_2)
+    fa, fb = FV.of(fv1), FV.of(fv2)
+    match = np.empty(len(kps1), np.int32)
+    nm = lib().ref_search_for_triangulation(_p(desc1), _p(kps1), len(kps1), C.byref(fa.c), _p(has_mp1), _p(desc2),
+                                            _p(kps2), len(kps2), C.byref(fb.c), _p(has_mp2), _p(F12), C.c_float(ex),
+                                            C.c_float(ey), _p(sf), _p(ls), len(sf), int(check_ori), _p(match))
+    return nm, match
+
+
+def search_for_initialization(desc1, kps1, desc2, kps2, grid2, prev_matched, window_size, nnratio, check_ori):
+    desc1, desc2 = _f32(desc1), _f32(desc2)
+    g = grid_struct(grid2)
+    prev = np.array(prev_matched, dtype=np.float32, copy=True).reshape(-1)
+    match = np.empty(len(kps1), np.int32)
+    nm = lib().ref_search_for_initialization(_p(desc1), _p(kps1), len(kps1), _p(desc2), _p(kps2), len(kps2),
+                                             C.byref(g), _p(prev), int(window_size), C.c_float(nnratio),
+                                             int(check_ori), _p(match))
+    return nm, match, prev.reshape(-1, 2)
+
+
+def _proj_common(desc_t, kps_t, grid, queries, level, desc_q, blocked0, scale_factors):
+    desc_t, desc_q, sf = _f32(desc_t), _f32(desc_q), _f32(scale_factors)
+    q = np.ascontiguousarray(queries, dtype=PROJ_QUERY_DTYPE)
+    b0 = None if blocked0 is None else _u8(blocked0)
+    return desc_t, desc_q, sf, q, _i32(level), b0, grid_struct(grid), np.empty(len(kps_t), np.int32)
+
+
+def sbp_local_map(desc_t, kps_t, grid, queries, level, view_cos, desc_q, blocked0, scale_factors, th, nnratio):
+    desc_t, desc_q, sf, q, lvl, b0, g, assign = _proj_common(desc_t, kps_t, grid, queries, level, desc_q, blocked0,
+                                                              scale_factors)
+    vc = _f32(view_cos)
+    nm = lib().ref_sbp_local_map(_p(desc_t), _p(kps_t), len(kps_t), C.byref(g), _p(q), _p(lvl), _p(vc), _p(desc_q),
+                                 len(q), _p(b0), _p(sf), len(sf), C.c_float(th), C.c_float(nnratio), _p(assign))
+    return nm, assign
+
+
+def sbp_frame_frame(desc_t, kps_t, grid, queries, level, desc_q, blocked0, scale_factors, th, nnratio, check_ori):
+    desc_t, desc_q, sf, q, lvl, b0, g, assign = _proj_common(desc_t, kps_t, grid, queries, level, desc_q, blocked0,
+                                                              scale_factors)
+    nm = lib().ref_sbp_frame_frame(_p(desc_t), _p(kps_t), len(kps_t), C.byref(g), _p(q), _p(lvl), _p(desc_q), len(q),
+                                   _p(b0), _p(sf), len(sf), C.c_float(th), C.c_float(nnratio), int(check_ori),
+                                   _p(assign))
+    return nm, assign
+
+
+def sbp_frame_keyframe(desc_t, kps_t, grid, queries, level, desc_q, blocked0, scale_factors, th, orb_dist, nnratio,
+                       check_ori):
+    desc_t, desc_q, sf, q, lvl, b0, g, assign = _proj_common(desc_t, kps_t, grid, queries, level, desc_q, blocked0,
+                                                              scale_factors)
+    nm = lib().ref_sbp_frame_keyframe(_p(desc_t), _p(kps_t), len(kps_t), C.byref(g), _p(q), _p(lvl), _p(desc_q),
+                                      len(q), _p(b0), _p(sf), len(sf), C.c_float(th), C.c_float(orb_dist),
+                                      C.c_float(nnratio), int(check_ori), _p(assign))
+    return nm, assign
+
+
+def sbp_keyframe_sim3(desc_t, kps_t, grid, queries, level, desc_q, blocked0, scale_factors, th, nnratio):
+    desc_t, desc_q, sf, q, lvl, b0, g, assign = _proj_common(desc_t, kps_t, grid, queries, level, desc_q, blocked0,
+                                                              scale_factors)
+    nm = lib().ref_sbp_keyframe_sim3(_p(desc_t), _p(kps_t), len(kps_t), C.byref(g), _p(q), _p(lvl), _p(desc_q), len(q),
+                                     _p(b0), _p(sf), len(sf), int(th), C.c_float(nnratio), _p(assign))
+    return nm, assign

@@ -1,0 +1,241 @@
+"""Pins the CPU oracle (oracle/asd_oracle.cc) against the reference's OWN matcher: /root/reference/src/vslam/src/
+ORBmatcher.cc compiled unmodified against header shims (oracle/_ref, see oracle/Makefile `ref`).  CPU only.
+
+Index lists and counts must be identical; distances are checked through DescriptorDistance (bit-exact, tolerance 0).
+Skipped when oracle/_ref cannot be had (no /root/reference and no prebuilt library).
+"""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+
+
+@pytest.fixture(scope="module")
+def ref(oracle):
+    import ref_py
+    if not ref_py.available():
+        pytest.skip("oracle/_ref/libref_orbmatcher.so unavailable")
+    return ref_py
+
+
+def test_descriptor_distance_bits(pkg, oracle, ref):
+    rng = np.random.default_rng(1)
+    a = pkg.synth.make_descriptors(rng, 300)
+    b = pkg.synth.make_descriptors(rng, 300)
+    b[:50] = a[:50]                       # zero distance
+    b[50:100] = a[50:100] + np.float32(1e-4)
+    a[100] *= np.float32(1e3)             # not unit norm
+    for i in range(300):
+        assert np.float32(oracle.descriptor_distance(a[i], b[i])).view(np.uint32) == \
+            np.float32(ref.descriptor_distance(a[i], b[i])).view(np.uint32)
+
+
+def test_three_maxima_and_small_functions(oracle, ref):
+    rng = np.random.default_rng(2)
+    for _ in range(300):
+        sizes = rng.integers(0, 6, 30) * (rng.random(30) < rng.random())
+        if rng.random() < 0.3:
+            sizes[rng.integers(0, 30)] = 60
+        assert oracle.compute_three_maxima(sizes) == ref.compute_three_maxima(sizes)
+    L = oracle.lib()
+    for c in [0.0, 0.5, 0.998, 0.99800003, 0.9981, 1.0, np.float32(0.998)]:
+        assert L.ora_radius_by_viewing_cos(float(c)) == ref.radius_by_viewing_cos(c)
+    logs = float(np.log(np.float32(1.2)))
+    for _ in range(500):
+        mx, d = float(rng.uniform(0.1, 50)), float(rng.uniform(0.1, 50))
+        assert L.ora_predict_scale(mx, d, logs, 8) == ref.predict_scale(mx, d, logs, 8)
+
+
+def test_grid_functions(pkg, oracle, ref):
+    S = pkg.synth
+    rng = np.random.default_rng(3)
+    for (W, H) in [(1241, 376), (752, 480)]:
+        g = S.image_grid(W, H)
+        kps = S.make_keypoints(rng, 700, W, H)
+        # keypoints on and beyond the border (PosInGrid drops / rounds them)
+        kps["x"][:10] = [0, W, W - 0.001, -3, W + 5, 0.4, W - 9.7, 9.69, 100, 200]
+        kps["y"][:10] = [0, H, H - 0.001, 5, 10, -0.6, H - 3.9, 3.91, H + 2, -8]
+        cs, ci, _ = oracle.assign_features_to_grid(kps, g)
+        for _ in range(250):
+            x, y = rng.uniform(-50, W + 50), rng.uniform(-50, H + 50)
+            r = float(rng.choice([0.5, 3.0, 15.0, 100.0, 2000.0]))
+            lo = int(rng.integers(-1, 8))
+            hi = int(rng.integers(-1, 8))
+            a = oracle.get_features_in_area(kps, g, cs, ci, x, y, r, lo, hi)
+            b = ref.frame_features_in_area(kps, g, x, y, r, lo, hi)
+            assert np.array_equal(a, b), (x, y, r, lo, hi)
+            a = oracle.get_features_in_area(kps, g, cs, ci, x, y, r, -1, -1)
+            b = ref.keyframe_features_in_area(kps, g, x, y, r)
+            assert np.array_equal(a, b), (x, y, r)
+
+
+@pytest.mark.parametrize("n,m,nodes,ratio,ori", [(600, 700, 1, 0.7, 1), (500, 400, 12, 0.75, 0), (300, 300, 3, 0.9, 1),
+                                                   (40, 60, 1, 0.6, 1)])
+def test_search_by_bow(pkg, oracle, ref, n, m, nodes, ratio, ori):
+    c = pkg.synth.config1(n, m, n_nodes=nodes)
+    rng = np.random.default_rng(n + m)
+    va = (rng.random(n) < 0.85).astype(np.uint8)
+    vb = (rng.random(m) < 0.85).astype(np.uint8)
+    # exact duplicates -> equal distances -> scan-order tie-breaking decides
+    db = c["desc_b"].copy()
+    db[rng.integers(0, m, m // 8)] = db[rng.integers(0, m, m // 8)]
+    onm, om, od = oracle.search_by_bow_kf_f(c["desc_a"], c["kps_a"], c["fv_a"], va, db, c["kps_b"], c["fv_b"], ratio, ori)
+    rnm, rm = ref.search_by_bow_kf_f(c["desc_a"], c["kps_a"], c["fv_a"], va, db, c["kps_b"], c["fv_b"], ratio, ori)
+    assert np.array_equal(om, rm) and onm == rnm
+    for j in np.nonzero(om >= 0)[0][:50]:
+        assert np.float32(od[j]).view(np.uint32) == np.float32(ref.descriptor_distance(c["desc_a"][om[j]], db[j])).view(np.uint32)
+    onm, om, od = oracle.search_by_bow_kf_kf(c["desc_a"], c["kps_a"], c["fv_a"], va, db, c["kps_b"], c["fv_b"], vb, ratio, ori)
+    rnm, rm = ref.search_by_bow_kf_kf(c["desc_a"], c["kps_a"], c["fv_a"], va, db, c["kps_b"], c["fv_b"], vb, ratio, ori)
+    assert np.array_equal(om, rm) and onm == rnm
+    if n >= 300:
+        assert onm > n // 10
+
+
+@pytest.mark.parametrize("n,pairs,nodes,ori", [(500, 3, 1, 0), (400, 2, 9, 1)])
+def test_search_for_triangulation(pkg, oracle, ref, n, pairs, nodes, ori):
+    c = pkg.synth.config4(n=n, n_pairs=pairs, n_nodes=nodes)
+    kfs = c["kfs"]
+    tot = 0
+    for p in range(pairs):
+        a, b = kfs[c["ia"][p]], kfs[c["ib"][p]]
+        args = (a["desc"], a["kps"], a["fv"], a["has_mp"], b["desc"], b["kps"], b["fv"], b["has_mp"], c["F12"][p],
+                c["epipoles"][p][0], c["epipoles"][p][1], c["scale_factors"], c["level_sigma2"], ori)
+        onm, om, od = oracle.search_for_triangulation(*args)
+        rnm, rm = ref.search_for_triangulation(*args)
+        assert np.array_equal(om, rm) and onm == rnm
+        tot += onm
+    assert tot > 0
+    # last-tie-wins rule with wide-open geometry gates and duplicated targets
+    a, b = kfs[0], kfs[1]
+    db = b["desc"].copy()
+    db[1::2] = db[0::2][: len(db[1::2])]
+    da = a["desc"].copy()
+    da[:100] = db[:100]
+    F12 = np.array([0, 0, 0, 0, 0, 1, 0, -1, 0.0], np.float32)
+    ls = np.full(8, 1e12, np.float32)
+    nomp = np.zeros(n, np.uint8)
+    args = (da, a["kps"], a["fv"], nomp, db, b["kps"], b["fv"], nomp, F12, -1e4, -1e4, c["scale_factors"], ls, 0)
+    onm, om, _ = oracle.search_for_triangulation(*args)
+    rnm, rm = ref.search_for_triangulation(*args)
+    assert np.array_equal(om, rm) and onm == rnm and onm >= 50
+
+
+def test_check_dist_epipolar_line(pkg, ref, oracle):
+    """CheckDistEpipolarLine alone (ORBmatcher.cc:136-153) on random geometry, via a 1x1 triangulation problem."""
+    rng = np.random.default_rng(9)
+    S = pkg.synth
+    d = S.make_descriptors(rng, 1)
+    fv = S.dense_fv(1)
+    z = np.zeros(1, np.uint8)
+    agree = 0
+    for _ in range(300):
+        F12 = rng.standard_normal(9).astype(np.float32)
+        k1, k2 = S.make_keypoints(rng, 1, 1241, 376), S.make_keypoints(rng, 1, 1241, 376)
+        ls = (S.level_sigma2() * np.float32(rng.choice([1.0, 100.0, 1e4]))).astype(np.float32)
+        r = ref.check_dist_epipolar_line(k1["x"][0], k1["y"][0], k2["x"][0], k2["y"][0], k2["octave"][0], F12, ls)
+        onm, _, _ = oracle.search_for_triangulation(d, k1, fv, z, d, k2, fv, z, F12, -1e6, -1e6, S.scale_factors(), ls, 0)
+        assert onm == r
+        agree += r
+    assert 0 < agree < 300
+
+
+@pytest.mark.parametrize("n,window", [(700, 100), (300, 40), (30, 500)])
+def test_search_for_initialization(pkg, oracle, ref, n, window):
+    c = pkg.synth.config_init(n=n, window=window)
+    onm, om, od, oprev = oracle.search_for_initialization(c["desc1"], c["kps1"], c["desc2"], c["kps2"], c["grid2"],
+                                                          c["prev_matched"], window, c["nnratio"], 1)
+    rnm, rm, rprev = ref.search_for_initialization(c["desc1"], c["kps1"], c["desc2"], c["kps2"], c["grid2"],
+                                                   c["prev_matched"], window, c["nnratio"], 1)
+    assert np.array_equal(om, rm) and onm == rnm and np.array_equal(oprev, rprev)
+
+
+def test_initialization_stealing(pkg, oracle, ref):
+    rng = np.random.default_rng(11)
+    S = pkg.synth
+    n = 300
+    W, H = S.KITTI["width"], S.KITTI["height"]
+    d2 = S.make_descriptors(rng, n)
+    k2 = S.make_keypoints(rng, n, W, H)
+    k2["octave"] = 0
+    d1 = np.empty_like(d2)
+    k1 = S.make_keypoints(rng, n, W, H)
+    k1["octave"] = (rng.random(n) < 0.2).astype(np.int32)
+    tgt = rng.integers(0, 40, n)
+    for i in range(n):
+        v = d2[tgt[i]] + rng.standard_normal(128).astype(np.float32) * np.float32(0.05 * (1.0 - i / (2 * n)))
+        d1[i] = v / np.sqrt((v * v).sum(dtype=np.float32))
+        k1["x"][i], k1["y"][i] = k2["x"][tgt[i]] + rng.normal(0, 5), k2["y"][tgt[i]] + rng.normal(0, 5)
+    g = S.image_grid(W, H)
+    prev = np.stack([k1["x"], k1["y"]], 1).astype(np.float32)
+    onm, om, _, op = oracle.search_for_initialization(d1, k1, d2, k2, g, prev, 100, 0.9, 1)
+    rnm, rm, rp = ref.search_for_initialization(d1, k1, d2, k2, g, prev, 100, 0.9, 1)
+    assert np.array_equal(om, rm) and onm == rnm and np.array_equal(op, rp)
+    assert onm < (k1["octave"] == 0).sum()  # something was stolen or rejected
+
+
+@pytest.mark.parametrize("th", [1.0, 5.0])
+def test_sbp_local_map(pkg, oracle, ref, th):
+    c = pkg.synth.config2(n_kp=600, n_mp=2400, n_in_view=800, th=th)
+    q = c["queries"]
+    onm, oa, _ = oracle.search_by_projection(c["desc_t"], c["kps_t"], c["grid"], q, c["desc_q"], c["blocked0"], 0, 1.5,
+                                             256.0, 0.8, 0, 1)
+    rnm, ra = ref.sbp_local_map(c["desc_t"], c["kps_t"], c["grid"], q, c["level"], c["view_cos"], c["desc_q"],
+                                c["blocked0"], pkg.synth.scale_factors(), th, 0.8)
+    assert np.array_equal(oa, ra) and onm == rnm
+    assert (oa >= 0).sum() > 100
+
+
+def test_sbp_frame_to_frame(pkg, oracle, ref):
+    f = pkg.synth.config3(n=700)["f2f"]
+    q = f["queries"]
+    level = (q["min_level"] + 1).astype(np.int32)
+    onm, oa, _ = oracle.search_by_projection(f["desc_t"], f["kps_t"], f["grid"], q, f["desc_q"], f["blocked0"], 1, 1.5,
+                                             100.0, 0.8, 1, 0)
+    rnm, ra = ref.sbp_frame_frame(f["desc_t"], f["kps_t"], f["grid"], q, level, f["desc_q"], f["blocked0"],
+                                  pkg.synth.scale_factors(), 15.0, 0.8, 1)
+    assert np.array_equal(oa, ra) and onm == rnm
+    assert (oa >= 0).sum() > 100
+
+
+def _reloc_like(pkg, n, th, seed):
+    """Queries for the relocalisation / loop overloads: window th*scale[level], octave range given per overload."""
+    S = pkg.synth
+    f = S.config3(n=n, seed_extra=seed)["f2f"]
+    q = f["queries"].copy()
+    rng = np.random.default_rng(seed)
+    level = rng.integers(0, 8, n).astype(np.int32)
+    q["r"] = (np.float32(th) * S.scale_factors()[level]).astype(np.float32)
+    blocked0 = (rng.random(n) < 0.1).astype(np.uint8)
+    return f, q, level, blocked0
+
+
+@pytest.mark.parametrize("th,orb_dist", [(10.0, 0.7), (3.0, 0.5)])
+def test_sbp_frame_keyframe(pkg, oracle, ref, th, orb_dist):
+    f, q, level, blocked0 = _reloc_like(pkg, 600, th, 5)
+    q["min_level"], q["max_level"] = level - 1, level + 1
+    q["blocks"] = 1  # any occupied keypoint is skipped (ORBmatcher.cc:1524)
+    onm, oa, _ = oracle.search_by_projection(f["desc_t"], f["kps_t"], f["grid"], q, f["desc_q"], blocked0, 1, orb_dist,
+                                             256.0, 0.9, 1, 0)
+    rnm, ra = ref.sbp_frame_keyframe(f["desc_t"], f["kps_t"], f["grid"], q, level, f["desc_q"], blocked0,
+                                     pkg.synth.scale_factors(), th, orb_dist, 0.9, 1)
+    assert np.array_equal(oa, ra) and onm == rnm
+    assert (oa >= 0).sum() > 10
+
+
+def test_sbp_keyframe_sim3(pkg, oracle, ref):
+    f, q, level, blocked0 = _reloc_like(pkg, 600, 10, 6)
+    q["min_level"], q["max_level"] = level - 1, level
+    q["blocks"] = 1
+    # KeyFrame::IsInImage is strict on the upper bounds (KeyFrame.cc:880-883)
+    W, H = pkg.synth.EUROC["width"], pkg.synth.EUROC["height"]
+    q["valid"] &= ((q["u"] >= 0) & (q["u"] < W) & (q["v"] >= 0) & (q["v"] < H)).astype(np.uint8)
+    onm, oa, _ = oracle.search_by_projection(f["desc_t"], f["kps_t"], f["grid"], q, f["desc_q"], blocked0, 1, 0.5, 256.0,
+                                             0.85, 0, 0)
+    rnm, ra = ref.sbp_keyframe_sim3(f["desc_t"], f["kps_t"], f["grid"], q, level, f["desc_q"], blocked0,
+                                    pkg.synth.scale_factors(), 10, 0.85)
+    assert np.array_equal(oa, ra) and onm == rnm
+    assert (oa >= 0).sum() > 10
