@@ -32,7 +32,7 @@ EXPORTS = [
     "asdm_set_create", "asdm_set_retain", "asdm_set_release", "asdm_set_size", "asdm_set_featvec",
     "asdm_set_read_desc",
     "asdm_search_by_bow_kf_f", "asdm_search_by_bow_kf_kf", "asdm_search_for_triangulation",
-    "asdm_search_by_projection", "asdm_search_for_initialization", "asdm_stereo_row_match",
+    "asdm_search_by_projection", "asdm_search_by_projection_q", "asdm_search_for_initialization", "asdm_stereo_row_match",
     "asdm_job_prepare", "asdm_job_run", "asdm_job_fetch", "asdm_job_settle", "asdm_job_out_stride",
     "asdm_job_device_outputs", "asdm_job_destroy",
 ]
@@ -49,7 +49,8 @@ class FeatVec(C.Structure):
 
 class ProjParams(C.Structure):
     _fields_ = [("mode", C.c_int32), ("th_accept", C.c_float), ("best_init", C.c_float), ("nnratio", C.c_float),
-                ("check_ori", C.c_int32), ("count_twice", C.c_int32)]
+                ("check_ori", C.c_int32), ("count_twice", C.c_int32), ("chi2_max", C.c_double), ("n_levels", C.c_int32),
+                ("reserved", C.c_int32), ("inv_level_sigma2", C.c_float * 32)]
 
 
 class JobDesc(C.Structure):
@@ -100,6 +101,8 @@ def load():
                                                   C.POINTER(i32)]
     lib.asdm_search_by_projection.argtypes = [vp, vp, vp, C.c_int, vp, vp, vp, vp, C.POINTER(ProjParams), vp, vp,
                                               C.POINTER(i32)]
+    lib.asdm_search_by_projection_q.argtypes = [vp, vp, vp, C.c_int, vp, vp, vp, vp, C.POINTER(ProjParams), vp, vp,
+                                                C.POINTER(i32)]
     lib.asdm_search_for_initialization.argtypes = [vp, vp, vp, vp, C.c_int, f32, C.c_int, vp, vp, C.POINTER(i32)]
     lib.asdm_stereo_row_match.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, f32, f32, vp, vp]
     lib.asdm_job_prepare.argtypes = [vp, C.POINTER(JobDesc), C.POINTER(vp)]

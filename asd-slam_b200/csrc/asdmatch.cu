@@ -806,7 +806,7 @@ struct ProjDev {
 
 // gather + distance with automatic growth of the entry pool; queries are already on the device
 static int proj_candidates(asdm_ctx* ctx, asdm_set* target, int nq, const float* d_desc_q, const int32_t* d_q_rows,
-                           int* ent_cap_io, ProjDev* out) {
+                           const ProjGate& gate, int* ent_cap_io, ProjDev* out) {
   int ent_cap = std::max(*ent_cap_io, 1 << 14);
   for (int attempt = 0; attempt < 20; attempt++) {
     int rc;
@@ -823,7 +823,7 @@ static int proj_candidates(asdm_ctx* ctx, asdm_set* target, int nq, const float*
     pd.overflow = pd.total + 1;
     CK(cudaMemsetAsync(pd.total, 0, 8, ctx->stream));
     if (nq > 0) {
-      k_proj_gather<<<(nq + 127) / 128, 128, 0, ctx->stream>>>(pd.q, nq, target->kps, target->grid, target->cell_start,
+      k_proj_gather<<<(nq + 127) / 128, 128, 0, ctx->stream>>>(pd.q, nq, target->kps, target->grid, gate, target->cell_start,
                                                                target->cell_items, pd.seg, pd.ent_j, pd.ent_q, ent_cap,
                                                                pd.total, pd.overflow);
       LAUNCHED(ctx);
@@ -849,11 +849,11 @@ static int proj_candidates(asdm_ctx* ctx, asdm_set* target, int nq, const float*
   return fail(ctx, ASDM_ERR_INTERNAL, "projection entry pool kept overflowing");
 }
 
-extern "C" int asdm_search_by_projection(asdm_ctx* ctx, asdm_set* target, const asdm_proj_query* q, int nq,
-                                         const float* desc_q, asdm_set* q_set, const int32_t* q_rows,
-                                         const uint8_t* blocked0, const asdm_proj_params* p, int32_t* assign,
-                                         float* dist_t, int32_t* nmatches) {
-  if (!ctx || !target || nq < 0 || (nq > 0 && !q) || !p || !assign) return ASDM_ERR_INVALID;
+static int search_by_projection_impl(asdm_ctx* ctx, asdm_set* target, const asdm_proj_query* q, int nq,
+                                     const float* desc_q, asdm_set* q_set, const int32_t* q_rows,
+                                     const uint8_t* blocked0, const asdm_proj_params* p, int32_t* assign, float* dist_t,
+                                     int32_t* nmatches, int32_t* query_best, float* query_dist) {
+  if (!ctx || !target || nq < 0 || (nq > 0 && !q) || !p || (!assign && !query_best)) return ASDM_ERR_INVALID;
   if (!target->has_grid) return fail(ctx, ASDM_ERR_INVALID, "target set has no grid");
   if (!desc_q && !q_set) return fail(ctx, ASDM_ERR_INVALID, "query descriptors missing");
   if (p->mode != ASDM_PROJ_RATIO_LEVEL && p->mode != ASDM_PROJ_BEST_ONLY) return fail(ctx, ASDM_ERR_INVALID, "bad mode");
@@ -892,27 +892,59 @@ extern "C" int asdm_search_by_projection(asdm_ctx* ctx, asdm_set* target, const 
     d_blocked = (const uint8_t*)ctx->scratch[SC_BLOCK].p;
   }
   ProjDev pd;
-  if ((rc = proj_candidates(ctx, target, nq, d_desc_q, d_rows, &ctx->proj_ent_cap, &pd))) return rc;
-  // state: acc[nq] own[2*n_t] assign[n_t] dist[n_t] nm[1]
-  const size_t state = ((size_t)std::max(nq, 1) + 4 * (size_t)std::max(n_t, 1) + 4) * 4;
+  ProjGate gate;
+  memset(&gate, 0, sizeof gate);
+  if (p->chi2_max > 0.0) {
+    if (p->n_levels <= 0 || p->n_levels > ASDM_MAX_LEVELS) return fail(ctx, ASDM_ERR_INVALID, "chi2 gate needs 1..32 levels");
+    gate.chi2_max = p->chi2_max;
+    gate.n_levels = p->n_levels;
+    memcpy(gate.inv_level_sigma2, p->inv_level_sigma2, (size_t)p->n_levels * sizeof(float));
+  }
+  if ((rc = proj_candidates(ctx, target, nq, d_desc_q, d_rows, gate, &ctx->proj_ent_cap, &pd))) return rc;
+  // state: acc[nq] own[2*n_t] assign[n_t] dist[n_t] nm[4] qbest[nq] qdist[nq]
+  const size_t state = (3 * (size_t)std::max(nq, 1) + 4 * (size_t)std::max(n_t, 1) + 4) * 4;
   if ((rc = ensure(ctx, ctx->scratch[SC_STATE], state))) return rc;
   int32_t* acc = (int32_t*)ctx->scratch[SC_STATE].p;
   int32_t* own = acc + std::max(nq, 1);
   int32_t* d_assign = own + 2 * (size_t)std::max(n_t, 1);
   float* d_dist = (float*)(d_assign + std::max(n_t, 1));
   int32_t* d_nm = (int32_t*)(d_dist + std::max(n_t, 1));
+  int32_t* d_qbest = d_nm + 4;
+  float* d_qdist = (float*)(d_qbest + std::max(nq, 1));
   ProjParamsDev P{p->mode, p->th_accept, p->best_init, p->nnratio, p->check_ori ? 1 : 0, p->count_twice ? 1 : 0};
   k_proj_resolve<<<1, 1024, 0, ctx->stream>>>(pd.q, nq, target->kps, n_t, d_blocked, pd.seg, pd.ent_j, pd.ent_d, P, acc,
-                                              own, d_assign, d_dist, d_nm);
+                                              own, d_assign, d_dist, d_nm, query_best ? d_qbest : nullptr, d_qdist);
   LAUNCHED(ctx);
   CK(cudaGetLastError());
   int32_t nm = 0;
-  if (n_t > 0) CK(cudaMemcpyAsync(assign, d_assign, (size_t)n_t * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  if (query_best && nq > 0) {
+    CK(cudaMemcpyAsync(query_best, d_qbest, (size_t)nq * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (query_dist) CK(cudaMemcpyAsync(query_dist, d_qdist, (size_t)nq * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  if (assign && n_t > 0) CK(cudaMemcpyAsync(assign, d_assign, (size_t)n_t * 4, cudaMemcpyDeviceToHost, ctx->stream));
   if (dist_t && n_t > 0) CK(cudaMemcpyAsync(dist_t, d_dist, (size_t)n_t * 4, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaMemcpyAsync(&nm, d_nm, 4, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
   if (nmatches) *nmatches = nm;
   return ASDM_OK;
+}
+
+extern "C" int asdm_search_by_projection(asdm_ctx* ctx, asdm_set* target, const asdm_proj_query* q, int nq,
+                                         const float* desc_q, asdm_set* q_set, const int32_t* q_rows,
+                                         const uint8_t* blocked0, const asdm_proj_params* p, int32_t* assign,
+                                         float* dist_t, int32_t* nmatches) {
+  if (!assign) return ASDM_ERR_INVALID;
+  return search_by_projection_impl(ctx, target, q, nq, desc_q, q_set, q_rows, blocked0, p, assign, dist_t, nmatches, nullptr,
+                                   nullptr);
+}
+
+extern "C" int asdm_search_by_projection_q(asdm_ctx* ctx, asdm_set* target, const asdm_proj_query* q, int nq,
+                                           const float* desc_q, asdm_set* q_set, const int32_t* q_rows,
+                                           const uint8_t* blocked0, const asdm_proj_params* p, int32_t* query_best,
+                                           float* query_dist, int32_t* nmatches) {
+  if (!query_best) return ASDM_ERR_INVALID;
+  return search_by_projection_impl(ctx, target, q, nq, desc_q, q_set, q_rows, blocked0, p, nullptr, nullptr, nmatches,
+                                   query_best, query_dist);
 }
 
 extern "C" int asdm_search_for_initialization(asdm_ctx* ctx, asdm_set* f1, asdm_set* f2, float* prev_matched,
@@ -944,7 +976,9 @@ extern "C" int asdm_search_for_initialization(asdm_ctx* ctx, asdm_set* f1, asdm_
     LAUNCHED(ctx);
   }
   ProjDev pd;
-  if ((rc = proj_candidates(ctx, f2, n1, f1->desc, nullptr, &ctx->proj_ent_cap, &pd))) return rc;
+  ProjGate gate;
+  memset(&gate, 0, sizeof gate);
+  if ((rc = proj_candidates(ctx, f2, n1, f1->desc, nullptr, gate, &ctx->proj_ent_cap, &pd))) return rc;
   k_init_resolve<<<1, 32, 0, ctx->stream>>>(f1->kps, n1, f2->kps, n2, pd.seg, pd.ent_j, pd.ent_d, nnratio,
                                             check_ori ? 1 : 0, d_md, d_m21, d_m12, d_d12, d_push, d_prev, d_nm);
   LAUNCHED(ctx);

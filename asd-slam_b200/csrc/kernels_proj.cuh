@@ -35,19 +35,32 @@ __device__ __forceinline__ bool area_cells(const asdm_grid& g, float x, float y,
   return true;
 }
 
+// Fuse's per-keypoint reprojection gate (ORBmatcher.cc:919-926); chi2_max <= 0 switches it off
+struct ProjGate {
+  double chi2_max;
+  int32_t n_levels;
+  float inv_level_sigma2[ASDM_MAX_LEVELS];
+};
+
 __device__ __forceinline__ bool area_keep(const asdm_kp& kp, float x, float y, float r, bool check_levels,
-                                          int min_level, int max_level) {
+                                          int min_level, int max_level, const ProjGate& G) {
   if (check_levels) {  // Frame.cc:254-261
     if (kp.octave < min_level) return false;
     if (max_level >= 0 && kp.octave > max_level) return false;
   }
   const float distx = __fsub_rn(kp.x, x), disty = __fsub_rn(kp.y, y);
-  return fabsf(distx) < r && fabsf(disty) < r;  // Frame.cc:266
+  if (!(fabsf(distx) < r && fabsf(disty) < r)) return false;  // Frame.cc:266
+  if (G.chi2_max > 0.0 && kp.octave >= 0 && kp.octave < G.n_levels) {
+    const float ex = __fsub_rn(x, kp.x), ey = __fsub_rn(y, kp.y);
+    const float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+    if ((double)__fmul_rn(e2, G.inv_level_sigma2[kp.octave]) > G.chi2_max) return false;
+  }
+  return true;
 }
 
 // One thread per query. total[0] = entries allocated so far; overflow[0] set when the entry pool is too small.
 __global__ void __launch_bounds__(128) k_proj_gather(const asdm_proj_query* __restrict__ q, int nq,
-                                                     const asdm_kp* __restrict__ kps, asdm_grid g,
+                                                     const asdm_kp* __restrict__ kps, asdm_grid g, ProjGate G,
                                                      const int32_t* __restrict__ cell_start,
                                                      const int32_t* __restrict__ cell_items,
                                                      ProjSeg* __restrict__ seg, int32_t* __restrict__ ent_j,
@@ -63,7 +76,7 @@ __global__ void __launch_bounds__(128) k_proj_gather(const asdm_proj_query* __re
     int cnt = 0;
     for (int ix = x0; ix <= x1; ix++)
       for (int e = cell_start[ix * g.rows + y0]; e < cell_start[ix * g.rows + y1 + 1]; e++)
-        cnt += area_keep(kps[cell_items[e]], Q.u, Q.v, Q.r, check_levels, Q.min_level, Q.max_level) ? 1 : 0;
+        cnt += area_keep(kps[cell_items[e]], Q.u, Q.v, Q.r, check_levels, Q.min_level, Q.max_level, G) ? 1 : 0;
     if (cnt > 0) {
       const int off = atomicAdd(total, cnt);
       if (off + cnt > ent_cap) {
@@ -76,7 +89,7 @@ __global__ void __launch_bounds__(128) k_proj_gather(const asdm_proj_query* __re
         for (int ix = x0; ix <= x1; ix++)
           for (int e = cell_start[ix * g.rows + y0]; e < cell_start[ix * g.rows + y1 + 1]; e++) {
             const int j = cell_items[e];
-            if (area_keep(kps[j], Q.u, Q.v, Q.r, check_levels, Q.min_level, Q.max_level)) {
+            if (area_keep(kps[j], Q.u, Q.v, Q.r, check_levels, Q.min_level, Q.max_level, G)) {
               ent_j[w] = j;
               ent_q[w] = iq;
               w++;
@@ -123,7 +136,9 @@ __global__ void __launch_bounds__(1024) k_proj_resolve(const asdm_proj_query* __
                                                        const float* __restrict__ ent_d, ProjParamsDev P,
                                                        int32_t* __restrict__ acc, int32_t* __restrict__ own,
                                                        int32_t* __restrict__ assign, float* __restrict__ dist_t,
-                                                       int32_t* __restrict__ nmatches) {
+                                                       int32_t* __restrict__ nmatches,
+                                                       int32_t* __restrict__ qbest /* [nq] or null */,
+                                                       float* __restrict__ qdist /* [nq] or null */) {
   __shared__ int s_changed, s_count;
   __shared__ int s_hist[ASDM_HISTO_LENGTH];
   __shared__ int s_keep[3];
@@ -185,6 +200,10 @@ __global__ void __launch_bounds__(1024) k_proj_resolve(const asdm_proj_query* __
   // F.mvpMapPoints[bestIdx] = pMP: the last accepting query owns the keypoint
   for (int i = t; i < nq; i += nt) {
     const int e = acc[i];
+    if (qbest) {  // per-query view of the same decision (SearchBySim3 / Fuse have no exclusivity)
+      qbest[i] = e >= 0 ? ent_j[e] : -1;
+      qdist[i] = e >= 0 ? ent_d[e] : -1.f;
+    }
     if (e < 0) continue;
     const int j = ent_j[e];
     atomicMax(assign + j, i);
@@ -213,7 +232,7 @@ __global__ void __launch_bounds__(1024) k_proj_resolve(const asdm_proj_query* __
       const int j = ent_j[e];
       const int b = asdm_rot_bin(q[i].angle, kps_t[j].angle);
       if (b != s_keep[0] && b != s_keep[1] && b != s_keep[2]) {
-        assign[j] = -1;
+        assign[j] = -2;  // cleared by the rotation check, as opposed to -1 = never assigned
         dist_t[j] = -1.f;
       }
     }

@@ -234,7 +234,7 @@ class ORBmatcher:
     # -- the descriptor loop shared by the four SearchByProjection overloads
     def SearchByProjection(self, target, queries, desc_q=None, q_set=None, q_rows=None, blocked0=None,
                            mode=ASDM_PROJ_BEST_ONLY, th_accept=TH_HIGH, best_init=256.0, count_twice=False,
-                           check_ori=None):
+                           check_ori=None, chi2_max=0.0, inv_level_sigma2=None):
         queries = np.ascontiguousarray(queries, dtype=PROJ_QUERY_DTYPE)
         nq = len(queries)
         dq = _f32(desc_q) if desc_q is not None else None
@@ -243,6 +243,11 @@ class ORBmatcher:
         co = self.mbCheckOrientation if check_ori is None else check_ori
         p = ProjParams(int(mode), float(th_accept), float(best_init), self.mfNNratio, int(bool(co)),
                        int(bool(count_twice)))
+        if chi2_max > 0:  # Fuse's reprojection gate (ORBmatcher.cc:919-926)
+            inv = _f32(inv_level_sigma2)
+            p.chi2_max, p.n_levels = float(chi2_max), len(inv)
+            for l, v in enumerate(inv):
+                p.inv_level_sigma2[l] = float(v)
         assign = np.empty(target.n, np.int32)
         dist = np.empty(target.n, np.float32)
         nm = C.c_int32()
@@ -251,6 +256,27 @@ class ORBmatcher:
                                                 q_set.h if q_set is not None else None, ptr(rows), ptr(b0),
                                                 C.byref(p), ptr(assign), ptr(dist), C.byref(nm)))
         return nm.value, assign, dist
+
+    # -- per-query view of the same search: the match phase of Fuse (ORBmatcher.cc:825-1086) and each direction of
+    #    SearchBySim3 (:1090-1314), where several queries may choose one keypoint
+    def SearchByProjection_PerQuery(self, target, queries, desc_q, blocked0=None, th_accept=TH_LOW, best_init=256.0,
+                                    chi2_max=0.0, inv_level_sigma2=None):
+        queries = np.ascontiguousarray(queries, dtype=PROJ_QUERY_DTYPE)
+        dq = _f32(desc_q)
+        b0 = _u8(blocked0) if blocked0 is not None else None
+        p = ProjParams(ASDM_PROJ_BEST_ONLY, float(th_accept), float(best_init), self.mfNNratio, 0, 0)
+        if chi2_max > 0:
+            inv = _f32(inv_level_sigma2)
+            p.chi2_max, p.n_levels = float(chi2_max), len(inv)
+            for l, v in enumerate(inv):
+                p.inv_level_sigma2[l] = float(v)
+        best = np.empty(len(queries), np.int32)
+        dist = np.empty(len(queries), np.float32)
+        nm = C.c_int32()
+        c = self.ctx
+        c.check(c.lib.asdm_search_by_projection_q(c.h, target.h, ptr(queries), len(queries), ptr(dq), None, None, ptr(b0),
+                                                  C.byref(p), ptr(best), ptr(dist), C.byref(nm)))
+        return best, dist
 
     # -- SearchByProjection(Frame&, vector<MapPoint*>&, th)           ORBmatcher.cc:44-122
     @staticmethod

@@ -155,15 +155,30 @@ typedef struct {
   float nnratio;       /* mode RATIO_LEVEL only */
   int32_t check_ori;   /* rotation histogram (:1413-1449, :1543-1579) */
   int32_t count_twice; /* :116-117 increments nmatches twice */
+  /* Fuse's reprojection gate (:919-926): when chi2_max > 0 a keypoint is skipped if
+   * e2 * inv_level_sigma2[octave] > chi2_max, e2 = (u-x)^2 + (v-y)^2 in fp32, compared in double (5.99) */
+  double chi2_max;
+  int32_t n_levels;
+  int32_t reserved;
+  float inv_level_sigma2[32];
 } asdm_proj_params;
 
 /* target: set with keypoints + grid (the Frame / KeyFrame searched). Query descriptors: either desc_q (host,
  * nq x 128, e.g. MapPoint::GetDescriptor of each local map point) or rows q_rows[i] of the resident set q_set
  * (q_rows NULL = row i). blocked0[j] (may be NULL): keypoint j unavailable from the start.
- * assign[j] (target->n entries) = query finally assigned to keypoint j, or -1. *nmatches = reference's return. */
+ * assign[j] (target->n entries) = query finally assigned to keypoint j; -1 = never assigned (the caller keeps what
+ * the keypoint held); -2 = assigned and then cleared by the rotation check (the reference stores NULL, :1441). *nmatches = reference's return. */
 int asdm_search_by_projection(asdm_ctx* ctx, asdm_set* target, const asdm_proj_query* q, int nq, const float* desc_q,
                               asdm_set* q_set, const int32_t* q_rows, const uint8_t* blocked0,
                               const asdm_proj_params* p, int32_t* assign, float* dist_t, int32_t* nmatches);
+
+/* Same search seen from the queries: query_best[i] = keypoint chosen by query i (or -1), query_dist[i] its distance.
+ * For the entry points without exclusivity, where several queries may choose one keypoint: SearchBySim3
+ * (ORBmatcher.cc:1090-1314, both directions) and the match phase of Fuse (:825-960, :963-1086; set every
+ * query's `blocks` to 0 and apply the graph mutations on the host in query order). */
+int asdm_search_by_projection_q(asdm_ctx* ctx, asdm_set* target, const asdm_proj_query* q, int nq, const float* desc_q,
+                                asdm_set* q_set, const int32_t* q_rows, const uint8_t* blocked0,
+                                const asdm_proj_params* p, int32_t* query_best, float* query_dist, int32_t* nmatches);
 
 /* ORBmatcher::SearchForInitialization (ORBmatcher.cc:416-531). prev_matched: 2*n1 floats (x,y), read and rewritten
  * (:526-528). matches12[i] (n1 entries) = index in F2 or -1. */

@@ -404,9 +404,35 @@ int ora_predict_scale(float max_distance, float current_dist, float log_scale_fa
   return nScale;
 }
 
+static int search_by_projection_impl(const float* desc_t, const ora_kp* kps_t, int n_t, const ora_grid* g,
+                                     const ora_proj_query* q, const float* desc_q, int n_q, const uint8_t* blocked0,
+                                     const ora_proj_params* p, int32_t* assign, float* dist_t, int32_t* query_best,
+                                     float* query_dist);
+
 int ora_search_by_projection(const float* desc_t, const ora_kp* kps_t, int n_t, const ora_grid* g,
                              const ora_proj_query* q, const float* desc_q, int n_q, const uint8_t* blocked0,
                              const ora_proj_params* p, int32_t* assign, float* dist_t) {
+  return search_by_projection_impl(desc_t, kps_t, n_t, g, q, desc_q, n_q, blocked0, p, assign, dist_t, nullptr, nullptr);
+}
+
+/* per-query view: query_best[i] = keypoint chosen by query i or -1 (match phase of Fuse :825-1086, SearchBySim3 :1090-1314) */
+int ora_search_by_projection_q(const float* desc_t, const ora_kp* kps_t, int n_t, const ora_grid* g,
+                               const ora_proj_query* q, const float* desc_q, int n_q, const uint8_t* blocked0,
+                               const ora_proj_params* p, int32_t* query_best, float* query_dist) {
+  std::vector<int32_t> assign((size_t)(n_t > 0 ? n_t : 1));
+  return search_by_projection_impl(desc_t, kps_t, n_t, g, q, desc_q, n_q, blocked0, p, assign.data(), nullptr, query_best,
+                                   query_dist);
+}
+
+static int search_by_projection_impl(const float* desc_t, const ora_kp* kps_t, int n_t, const ora_grid* g,
+                                     const ora_proj_query* q, const float* desc_q, int n_q, const uint8_t* blocked0,
+                                     const ora_proj_params* p, int32_t* assign, float* dist_t, int32_t* query_best,
+                                     float* query_dist) {
+  if (query_best)
+    for (int i = 0; i < n_q; i++) {
+      query_best[i] = -1;
+      if (query_dist) query_dist[i] = -1.f;
+    }
   Grid G;
   build_grid(kps_t, n_t, *g, G);
   /* occupancy of F.mvpMapPoints[idx] as far as the descriptor loop can see it:
@@ -436,6 +462,13 @@ int ora_search_by_projection(const float* desc_t, const ora_kp* kps_t, int n_t, 
     for (size_t k = 0; k < vIndices.size(); k++) {
       const int idx = vIndices[k];
       if (blocking[idx]) continue; /* :86-88, :385, :1393-1395, :1524 */
+      if (p->chi2_max > 0) { /* Fuse: :919-926 */
+        const float ex = Q.u - kps_t[idx].x;
+        const float ey = Q.v - kps_t[idx].y;
+        const float e2 = ex * ex + ey * ey;
+        const int lvl = kps_t[idx].octave;
+        if (lvl >= 0 && lvl < p->n_levels && e2 * p->inv_level_sigma2[lvl] > p->chi2_max) continue;
+      }
       const float dist = dd(dq, desc_t + (size_t)idx * ORA_DESC_DIM);
       if (dist < bestDist) {
         bestDist2 = bestDist;
@@ -453,6 +486,10 @@ int ora_search_by_projection(const float* desc_t, const ora_kp* kps_t, int n_t, 
         if (bestLevel == bestLevel2 && bestDist > p->nnratio * bestDist2) continue; /* :112 */
       }
       assign[bestIdx] = iq;
+      if (query_best) {
+        query_best[iq] = bestIdx;
+        if (query_dist) query_dist[iq] = bestDist;
+      }
       if (dist_t) dist_t[bestIdx] = bestDist;
       blocking[bestIdx] = Q.blocks;
       nmatches++;
@@ -467,7 +504,7 @@ int ora_search_by_projection(const float* desc_t, const ora_kp* kps_t, int n_t, 
     for (int i = 0; i < HISTO_LENGTH; i++) {
       if (i != ind1 && i != ind2 && i != ind3) {
         for (size_t j = 0; j < rotHist[i].size(); j++) {
-          assign[rotHist[i][j]] = -1;
+          assign[rotHist[i][j]] = -2; /* cleared by the rotation check (set to NULL at :1441), as opposed to -1 = untouched */
           if (dist_t) dist_t[rotHist[i][j]] = -1.f;
           nmatches--;
         }

@@ -117,6 +117,10 @@ typedef struct {
   float nnratio;       /* mode RATIO_LEVEL only */
   int32_t check_ori;   /* rotation histogram on (:1413-1449, :1543-1579) */
   int32_t count_twice; /* :116-117 increments nmatches twice */
+  double chi2_max;     /* > 0: Fuse's gate e2*inv_level_sigma2[octave] > chi2_max -> skip (:919-926) */
+  int32_t n_levels;
+  int32_t reserved;
+  float inv_level_sigma2[32];
 } ora_proj_params;
 
 typedef struct {
@@ -129,11 +133,16 @@ typedef struct {
 } ora_proj_query;
 
 /* blocked0[j] = target keypoint j is unavailable from the start.
- * assign[j] (size n_t) = query index finally assigned to keypoint j, or -1 if untouched/pruned.
+ * assign[j] (size n_t) = query index finally assigned to keypoint j; -1 untouched; -2 cleared by the rotation check.
  * Returns nmatches (doubled when count_twice). */
 int ora_search_by_projection(const float* desc_t, const ora_kp* kps_t, int n_t, const ora_grid* g,
                              const ora_proj_query* q, const float* desc_q, int n_q, const uint8_t* blocked0,
                              const ora_proj_params* p, int32_t* assign, float* dist_t);
+
+/* Same search seen from the queries (no exclusivity needed): query_best[i] = keypoint chosen by query i or -1. */
+int ora_search_by_projection_q(const float* desc_t, const ora_kp* kps_t, int n_t, const ora_grid* g,
+                               const ora_proj_query* q, const float* desc_q, int n_q, const uint8_t* blocked0,
+                               const ora_proj_params* p, int32_t* query_best, float* query_dist);
 
 /* a4 helper: ORBmatcher::RadiusByViewingCos (ORBmatcher.cc:126-132) and the window of :62-68 */
 float ora_radius_by_viewing_cos(float view_cos);

@@ -30,7 +30,8 @@ class FeatVec(C.Structure):
 
 class ProjParams(C.Structure):
     _fields_ = [("mode", C.c_int32), ("th_accept", C.c_float), ("best_init", C.c_float), ("nnratio", C.c_float),
-                ("check_ori", C.c_int32), ("count_twice", C.c_int32)]
+                ("check_ori", C.c_int32), ("count_twice", C.c_int32), ("chi2_max", C.c_double), ("n_levels", C.c_int32),
+                ("reserved", C.c_int32), ("inv_level_sigma2", C.c_float * 32)]
 
 
 class KeyFrame(C.Structure):
@@ -169,18 +170,43 @@ def search_for_triangulation(desc1, kps1, fv1, has_mp1, desc2, kps2, fv2, has_mp
 
 
 def search_by_projection(desc_t, kps_t, grid, queries, desc_q, blocked0, mode, th_accept, best_init, nnratio,
-                         check_ori, count_twice):
+                         check_ori, count_twice, chi2_max=0.0, inv_level_sigma2=None):
     desc_t, desc_q = _f32(desc_t), _f32(desc_q)
     g = grid_struct(grid)
     n_t = len(kps_t)
     queries = np.ascontiguousarray(queries, dtype=PROJ_QUERY_DTYPE)
     b0 = None if blocked0 is None else _u8(blocked0)
     p = ProjParams(int(mode), th_accept, best_init, nnratio, int(check_ori), int(count_twice))
+    if chi2_max > 0:
+        inv = _f32(inv_level_sigma2)
+        p.chi2_max, p.n_levels = float(chi2_max), len(inv)
+        for l, v in enumerate(inv):
+            p.inv_level_sigma2[l] = float(v)
     assign = np.empty(n_t, np.int32)
     dist = np.empty(n_t, np.float32)
     nm = lib().ora_search_by_projection(_p(desc_t), _p(kps_t), n_t, C.byref(g), _p(queries), _p(desc_q), len(queries),
                                         _p(b0), C.byref(p), _p(assign), _p(dist))
     return nm, assign, dist
+
+
+def search_by_projection_q(desc_t, kps_t, grid, queries, desc_q, blocked0, mode, th_accept, best_init, nnratio,
+                           chi2_max=0.0, inv_level_sigma2=None):
+    """Per-query result of the same search: (best keypoint or -1, distance) for every query."""
+    desc_t, desc_q = _f32(desc_t), _f32(desc_q)
+    g = grid_struct(grid)
+    queries = np.ascontiguousarray(queries, dtype=PROJ_QUERY_DTYPE)
+    b0 = None if blocked0 is None else _u8(blocked0)
+    p = ProjParams(int(mode), th_accept, best_init, nnratio, 0, 0)
+    if chi2_max > 0:
+        inv = _f32(inv_level_sigma2)
+        p.chi2_max, p.n_levels = float(chi2_max), len(inv)
+        for l, v in enumerate(inv):
+            p.inv_level_sigma2[l] = float(v)
+    best = np.empty(len(queries), np.int32)
+    dist = np.empty(len(queries), np.float32)
+    lib().ora_search_by_projection_q(_p(desc_t), _p(kps_t), len(kps_t), C.byref(g), _p(queries), _p(desc_q), len(queries),
+                                     _p(b0), C.byref(p), _p(best), _p(dist))
+    return best, dist
 
 
 def search_for_initialization(desc1, kps1, desc2, kps2, grid2, prev_matched, window_size, nnratio, check_ori):

@@ -463,4 +463,138 @@ int ref_sbp_keyframe_sim3(const float* desc_t, const ora_kp* kps_t, int n_t, con
   return nm;
 }
 
+// ------------------------------------------------------------------------------------------- Fuse / SearchBySim3
+// Shared set-up: target keyframe with occupant map points (occ_obs[j] = 0: none, k > 0: a map point with k
+// observations), candidate map points at (u, v, 1) with nObs = mp_obs[i], normal towards the camera.
+namespace {
+struct FuseRig {
+  Pool pool;
+  KeyFrame K;
+  std::vector<MapPoint*> pts;
+  FuseRig(const float* desc_t, const ora_kp* kps_t, int n_t, const ora_grid* g, const ora_proj_query* q,
+          const int32_t* level, const float* desc_q, int n_q, const int32_t* occ_obs, const int32_t* mp_obs,
+          const float* scale_factors, int n_levels) {
+    fill_keyframe(K, desc_t, kps_t, n_t, g);
+    float lsf;
+    levels(scale_factors, nullptr, n_levels, std::log(1.2f), K.mvScaleFactors, K.mvLevelSigma2, K.mvInvLevelSigma2,
+           K.mnScaleLevels, lsf);
+    K.mfLogScaleFactor = lsf;
+    for (int j = 0; j < n_t; j++)
+      if (occ_obs[j] > 0) {
+        K.mvpMapPoints[j] = pool.make(1000000 + j);
+        K.mvpMapPoints[j]->nObs = occ_obs[j];
+        K.mvpMapPoints[j]->mObservations[&K] = (size_t)j;
+      }
+    pts.assign((size_t)n_q, nullptr);
+    for (int i = 0; i < n_q; i++) {
+      if (!q[i].valid && (i % 3) == 0) continue;  // null entry (Fuse(KF, vector) tolerates them)
+      MapPoint* p = pool.make(i);
+      p->mWorldPos = vec3(q[i].u, q[i].v, 1.f);
+      set_distance_for_level(p, q[i].u, q[i].v, level[i]);
+      const float d = std::sqrt(q[i].u * q[i].u + q[i].v * q[i].v + 1.f);
+      p->mNormalVector = vec3(q[i].u / d, q[i].v / d, 1.f / d);
+      p->mDescriptor = desc_row(desc_q + (size_t)i * ORA_DESC_DIM);
+      p->nObs = mp_obs[i];
+      if (!q[i].valid) p->mbBad = true;
+      pts[i] = p;
+    }
+  }
+};
+}  // namespace
+
+// Fuse(KeyFrame*, vpMapPoints, th)  (ORBmatcher.cc:825-960).  action[i]: -1 nothing; 4*idx+0 observation added at
+// keypoint idx; 4*idx+1 candidate replaced by the keypoint's occupant; 4*idx+2 occupant replaced by the candidate.
+int ref_fuse(const float* desc_t, const ora_kp* kps_t, int n_t, const ora_grid* g, const ora_proj_query* q,
+             const int32_t* level, const float* desc_q, int n_q, const int32_t* occ_obs, const int32_t* mp_obs,
+             const float* scale_factors, int n_levels, float th, int32_t* action) {
+  FuseRig R(desc_t, kps_t, n_t, g, q, level, desc_q, n_q, occ_obs, mp_obs, scale_factors, n_levels);
+  ORBmatcher m(0.6f, true);
+  const int nf = m.Fuse(&R.K, R.pts, th);
+  // final state of the graph as seen from every candidate: where it sits in the keyframe (4*idx), whether it was
+  // replaced (4*idx_of_replacer+1, or 4*replacer_candidate+3 when the replacer is another candidate), or nothing
+  for (int i = 0; i < n_q; i++) {
+    action[i] = -1;
+    MapPoint* p = R.pts[i];
+    if (!p) continue;
+    if (p->mObservations.count(&R.K)) action[i] = 4 * (int)p->mObservations[&R.K] + 0;
+    else if (p->mpReplaced) {
+      MapPoint* r = p->mpReplaced;
+      action[i] = r->id >= 1000000 ? 4 * (r->id - 1000000) + 1 : 4 * r->id + 3;
+    }
+  }
+  return nf;
+}
+
+// Fuse(KeyFrame*, Scw, vpPoints, th, vpReplacePoint)  (ORBmatcher.cc:963-1086), Scw = identity.
+// replace[i] = keypoint whose occupant lands in vpReplacePoint[i], added[i] = keypoint that received the candidate.
+int ref_fuse_sim3(const float* desc_t, const ora_kp* kps_t, int n_t, const ora_grid* g, const ora_proj_query* q,
+                  const int32_t* level, const float* desc_q, int n_q, const int32_t* occ_obs, const int32_t* mp_obs,
+                  const float* scale_factors, int n_levels, float th, int32_t* replace, int32_t* added) {
+  FuseRig R(desc_t, kps_t, n_t, g, q, level, desc_q, n_q, occ_obs, mp_obs, scale_factors, n_levels);
+  for (int i = 0; i < n_q; i++)
+    if (!R.pts[i]) {  // this overload dereferences every entry: give the null slots a bad point
+      R.pts[i] = R.pool.make(i);
+      R.pts[i]->mbBad = true;
+    }
+  std::vector<MapPoint*> repl((size_t)n_q, nullptr);
+  ORBmatcher m(0.8f, true);
+  const int nf = m.Fuse(&R.K, eye4(), R.pts, th, repl);
+  for (int i = 0; i < n_q; i++) {
+    replace[i] = repl[i] ? repl[i]->GetIndexInKeyFrame(&R.K) : -1;
+    added[i] = R.pts[i]->mObservations.count(&R.K) ? (int)R.pts[i]->mObservations[&R.K] : -1;
+  }
+  return nf;
+}
+
+// SearchBySim3 (ORBmatcher.cc:1090-1314) with identity poses and s12 = 1, R12 = I, t12 = 0: map point i of KF1 sits
+// at (u1[i], v1[i], 1) (its projection into KF2) and map point j of KF2 at (u2[j], v2[j], 1).
+int ref_search_by_sim3(const float* desc1, const ora_kp* kps1, int n1, const float* desc2, const ora_kp* kps2, int n2,
+                       const ora_grid* g, const uint8_t* valid1, const uint8_t* valid2, const float* uv1,
+                       const float* uv2, const int32_t* level1, const int32_t* level2, const float* mpdesc1,
+                       const float* mpdesc2, const uint8_t* already1, const float* scale_factors, int n_levels, float th,
+                       int32_t* match12) {
+  Pool pool;
+  KeyFrame K1, K2;
+  fill_keyframe(K1, desc1, kps1, n1, g);
+  fill_keyframe(K2, desc2, kps2, n2, g);
+  float lsf;
+  levels(scale_factors, nullptr, n_levels, std::log(1.2f), K1.mvScaleFactors, K1.mvLevelSigma2, K1.mvInvLevelSigma2,
+         K1.mnScaleLevels, lsf);
+  K1.mfLogScaleFactor = lsf;
+  K2.mvScaleFactors = K1.mvScaleFactors; K2.mnScaleLevels = n_levels; K2.mfLogScaleFactor = lsf;
+  for (int i = 0; i < n1; i++)
+    if (valid1[i] || (i & 1)) {
+      MapPoint* p = pool.make(i);
+      p->mbBad = !valid1[i];
+      p->mWorldPos = vec3(uv1[2 * i], uv1[2 * i + 1], 1.f);
+      set_distance_for_level(p, uv1[2 * i], uv1[2 * i + 1], level1[i]);
+      p->mDescriptor = desc_row(mpdesc1 + (size_t)i * ORA_DESC_DIM);
+      K1.mvpMapPoints[i] = p;
+    }
+  for (int j = 0; j < n2; j++)
+    if (valid2[j] || (j & 1)) {
+      MapPoint* p = pool.make(j);
+      p->mbBad = !valid2[j];
+      p->mWorldPos = vec3(uv2[2 * j], uv2[2 * j + 1], 1.f);
+      set_distance_for_level(p, uv2[2 * j], uv2[2 * j + 1], level2[j]);
+      p->mDescriptor = desc_row(mpdesc2 + (size_t)j * ORA_DESC_DIM);
+      p->mObservations[&K2] = (size_t)j;
+      K2.mvpMapPoints[j] = p;
+    }
+  std::vector<MapPoint*> m12((size_t)n1, nullptr);
+  std::vector<MapPoint*> pre;
+  for (int i = 0; i < n1; i++)
+    if (already1[i] && K2.mvpMapPoints[i % n2] && !K2.mvpMapPoints[i % n2]->mbBad) {
+      m12[i] = K2.mvpMapPoints[i % n2];  // an earlier SearchByBoW match (LoopClosing.cc:304)
+      pre.push_back(m12[i]);
+    }
+  cv::Mat R12(3, 3, CV_32F);
+  for (int i = 0; i < 3; i++) R12.at<float>(i, i) = 1.f;
+  ORBmatcher m(0.85f, true);
+  const float s12 = 1.f;
+  const int nf = m.SearchBySim3(&K1, &K2, m12, s12, R12, vec3(0, 0, 0), th);
+  for (int i = 0; i < n1; i++) match12[i] = m12[i] ? m12[i]->id : -1;
+  return nf;
+}
+
 }  // extern "C"

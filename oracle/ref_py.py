@@ -29,14 +29,22 @@ def available():
 
 
 _lib = None
+_path = None  # library the ref_* calls go to; None = the reference build
+
+
+def use(path=None):
+    """Route the ref_* calls to another build of ref_driver.cc: the C++ adaptor under test
+    (asd-slam_b200/host/libadaptor_shim.so = our ORBmatcher_cuda.cc behind the same harness). None = the reference."""
+    global _lib, _path
+    _lib, _path = None, path
 
 
 def lib():
     global _lib
     if _lib is None:
-        if not available():
+        if _path is None and not available():
             raise RuntimeError("oracle/_ref/libref_orbmatcher.so is missing and /root/reference is not mounted")
-        _lib = C.CDLL(_LIB)
+        _lib = C.CDLL(_path or _LIB)
         _lib.ref_descriptor_distance.restype = C.c_float
         _lib.ref_radius_by_viewing_cos.restype = C.c_float
         _lib.ref_radius_by_viewing_cos.argtypes = [C.c_float]
@@ -176,3 +184,34 @@ def sbp_keyframe_sim3(desc_t, kps_t, grid, queries, level, desc_q, blocked0, sca
     nm = lib().ref_sbp_keyframe_sim3(_p(desc_t), _p(kps_t), len(kps_t), C.byref(g), _p(q), _p(lvl), _p(desc_q), len(q),
                                      _p(b0), _p(sf), len(sf), int(th), C.c_float(nnratio), _p(assign))
     return nm, assign
+
+
+def fuse(desc_t, kps_t, grid, queries, level, desc_q, occ_obs, mp_obs, scale_factors, th):
+    desc_t, desc_q, sf, q, lvl, _, g, _ = _proj_common(desc_t, kps_t, grid, queries, level, desc_q, None, scale_factors)
+    occ, mob = _i32(occ_obs), _i32(mp_obs)
+    action = np.empty(len(q), np.int32)
+    nf = lib().ref_fuse(_p(desc_t), _p(kps_t), len(kps_t), C.byref(g), _p(q), _p(lvl), _p(desc_q), len(q), _p(occ), _p(mob),
+                        _p(sf), len(sf), C.c_float(th), _p(action))
+    return nf, action
+
+
+def fuse_sim3(desc_t, kps_t, grid, queries, level, desc_q, occ_obs, mp_obs, scale_factors, th):
+    desc_t, desc_q, sf, q, lvl, _, g, _ = _proj_common(desc_t, kps_t, grid, queries, level, desc_q, None, scale_factors)
+    occ, mob = _i32(occ_obs), _i32(mp_obs)
+    replace, added = np.empty(len(q), np.int32), np.empty(len(q), np.int32)
+    nf = lib().ref_fuse_sim3(_p(desc_t), _p(kps_t), len(kps_t), C.byref(g), _p(q), _p(lvl), _p(desc_q), len(q), _p(occ),
+                             _p(mob), _p(sf), len(sf), C.c_float(th), _p(replace), _p(added))
+    return nf, replace, added
+
+
+def search_by_sim3(desc1, kps1, desc2, kps2, grid, valid1, valid2, uv1, uv2, level1, level2, mpdesc1, mpdesc2, already1,
+                   scale_factors, th):
+    desc1, desc2, mp1, mp2, sf = _f32(desc1), _f32(desc2), _f32(mpdesc1), _f32(mpdesc2), _f32(scale_factors)
+    v1, v2, a1 = _u8(valid1), _u8(valid2), _u8(already1)
+    uv1, uv2, l1, l2 = _f32(uv1), _f32(uv2), _i32(level1), _i32(level2)
+    g = grid_struct(grid)
+    match = np.empty(len(kps1), np.int32)
+    nf = lib().ref_search_by_sim3(_p(desc1), _p(kps1), len(kps1), _p(desc2), _p(kps2), len(kps2), C.byref(g), _p(v1), _p(v2),
+                                  _p(uv1), _p(uv2), _p(l1), _p(l2), _p(mp1), _p(mp2), _p(a1), _p(sf), len(sf),
+                                  C.c_float(th), _p(match))
+    return nf, match

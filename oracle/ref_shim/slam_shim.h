@@ -7,6 +7,7 @@
 #pragma once
 #include <cmath>
 #include <map>
+#include <memory>
 #include <set>
 #include <string>
 #include <vector>
@@ -16,6 +17,8 @@
 
 #define FRAME_GRID_ROWS 48
 #define FRAME_GRID_COLS 64
+
+namespace asdm { struct DeviceSet; }  // asd-slam_b200/host/asdm_device.h; the member the integration adds
 
 using namespace std;  // the reference's headers rely on a using-directive leaked by its own Frame.h / KeyFrame.h
 
@@ -43,9 +46,15 @@ class MapPoint {
   int PredictScale(const float& currentDist, Frame* pF);
   bool IsInKeyFrame(KeyFrame* pKF) { return mObservations.count(pKF); }
   int GetIndexInKeyFrame(KeyFrame* pKF) { return mObservations.count(pKF) ? (int)mObservations[pKF] : -1; }
-  // graph mutations of Fuse are recorded, not performed (the harness replays them)
-  void Replace(MapPoint* pMP) { mpReplaced = pMP; }
-  void AddObservation(KeyFrame* pKF, size_t idx) { mObservations[pKF] = idx; nObs++; }
+  // Graph mutations of Fuse.  Replace follows what the reference's MapPoint::Replace does to the state the matcher
+  // can observe afterwards (MapPoint.cc:205-245): this point turns bad, its observations move to pMP (or are erased
+  // from keyframes that already see pMP).  Defined after KeyFrame below.
+  void Replace(MapPoint* pMP);
+  void AddObservation(KeyFrame* pKF, size_t idx) {
+    if (mObservations.count(pKF)) return;
+    mObservations[pKF] = idx;
+    nObs++;
+  }
 
   bool mbBad = false;
   int nObs = 0;
@@ -78,6 +87,7 @@ class Frame {
   float mfScaleFactor = 0, mfLogScaleFactor = 0;
   vector<float> mvScaleFactors, mvInvScaleFactors, mvLevelSigma2, mvInvLevelSigma2;
   static float mnMinX, mnMaxX, mnMinY, mnMaxY;
+  mutable std::shared_ptr<asdm::DeviceSet> mDev;  // device-resident descriptors, shared by Frame copies
 };
 
 class KeyFrame {
@@ -113,6 +123,24 @@ class KeyFrame {
   std::vector<MapPoint*> mvpMapPoints;
   std::vector<std::vector<std::vector<size_t> > > mGrid;
   cv::Mat Tcw, Ow;
+  mutable std::shared_ptr<asdm::DeviceSet> mDev;  // device-resident descriptors (handed over by the Frame)
 };
+
+inline void MapPoint::Replace(MapPoint* pMP) {
+  if (pMP == this) return;
+  std::map<KeyFrame*, size_t> obs = mObservations;
+  mObservations.clear();
+  mbBad = true;
+  mpReplaced = pMP;
+  for (std::map<KeyFrame*, size_t>::iterator it = obs.begin(); it != obs.end(); ++it) {
+    KeyFrame* pKF = it->first;
+    if (!pMP->IsInKeyFrame(pKF)) {
+      pKF->mvpMapPoints[it->second] = pMP;
+      pMP->AddObservation(pKF, it->second);
+    } else {
+      pKF->mvpMapPoints[it->second] = static_cast<MapPoint*>(NULL);
+    }
+  }
+}
 
 }  // namespace ORB_SLAM2

@@ -90,4 +90,110 @@ def cases():
             q["valid"] &= ((q["u"] >= 0) & (q["u"] < W) & (q["v"] >= 0) & (q["v"] < H)).astype(np.uint8)
         blocked0 = (rng.random(len(f["kps_t"])) < 0.1).astype(np.uint8)
         out.append((name, kind, dict(f=f, q=q, level=level, blocked0=blocked0, th=th, acc=acc)))
+    # Fuse x2 and SearchBySim3: candidates project near keypoints that hold noisy copies of them
+    W, H = S.EUROC["width"], S.EUROC["height"]
+    for name, kind, th in [("fuse", "fuse", 3.0), ("fuse_sim3", "fuse_sim3", 4.0)]:
+        rng = np.random.default_rng(700 + len(out))
+        n = 500
+        desc_q = S.make_descriptors(rng, n)
+        kq = S.make_keypoints(rng, n, W, H)
+        desc_t, kps_t, gt = S.make_matched_set(rng, desc_q, kq, n, W, H, match_frac=0.7, d_lo=0.05, d_hi=0.8, pos_sigma=2.0)
+        q = np.zeros(n, S.PROJ_QUERY_DTYPE)
+        q["valid"] = (rng.random(n) < 0.9).astype(np.uint8)
+        q["u"] = np.clip(kq["x"] + rng.normal(0, 1.0, n), 0, W - 1e-2).astype(np.float32)
+        q["v"] = np.clip(kq["y"] + rng.normal(0, 1.0, n), 0, H - 1e-2).astype(np.float32)
+        level = np.minimum(kq["octave"] + rng.integers(0, 2, n), 7).astype(np.int32)
+        occ_obs = np.where(rng.random(n) < 0.5, rng.integers(1, 6, n), 0).astype(np.int32)
+        mp_obs = rng.integers(1, 6, n).astype(np.int32)
+        # two candidates aimed at the same keypoint: the second sees what the first one changed
+        q["u"][1], q["v"][1], level[1] = q["u"][0], q["v"][0], level[0]
+        desc_q[1] = desc_q[0]
+        out.append((name, kind, dict(desc_t=desc_t, kps_t=kps_t, grid=S.image_grid(W, H), q=q, level=level, desc_q=desc_q,
+                                     occ_obs=occ_obs, mp_obs=mp_obs, th=th)))
+    rng = np.random.default_rng(900)
+    n = 400
+    d1 = S.make_descriptors(rng, n)
+    k1 = S.make_keypoints(rng, n, W, H)
+    d2, k2, gt = S.make_matched_set(rng, d1, k1, n, W, H, match_frac=0.7, d_lo=0.05, d_hi=1.2, pos_sigma=3.0)
+    inv = np.full(n, -1, np.int64)
+    inv[gt[gt >= 0]] = np.nonzero(gt >= 0)[0]
+    uv1 = np.stack([k1["x"], k1["y"]], 1).astype(np.float32)  # where KF1's map points land in KF2
+    has = inv >= 0
+    uv1[has, 0], uv1[has, 1] = k2["x"][inv[has]], k2["y"][inv[has]]
+    uv2 = np.stack([k2["x"], k2["y"]], 1).astype(np.float32)
+    has2 = gt >= 0
+    uv2[has2, 0], uv2[has2, 1] = k1["x"][gt[has2]], k1["y"][gt[has2]]
+    uv1 += rng.normal(0, 1.0, uv1.shape).astype(np.float32)
+    uv2 += rng.normal(0, 1.0, uv2.shape).astype(np.float32)
+    uv1 = np.clip(uv1, 0, [W - 1e-2, H - 1e-2]).astype(np.float32)
+    uv2 = np.clip(uv2, 0, [W - 1e-2, H - 1e-2]).astype(np.float32)
+    out.append(("sim3", "sim3", dict(desc1=d1, kps1=k1, desc2=d2, kps2=k2, grid=S.image_grid(W, H),
+                                     valid1=(rng.random(n) < 0.85).astype(np.uint8), valid2=(rng.random(n) < 0.85).astype(np.uint8),
+                                     uv1=uv1, uv2=uv2, level1=np.minimum(k1["octave"] + rng.integers(0, 2, n), 7).astype(np.int32),
+                                     level2=np.minimum(k2["octave"] + rng.integers(0, 2, n), 7).astype(np.int32),
+                                     already1=(rng.random(n) < 0.1).astype(np.uint8), th=7.5)))
+    return out
+
+
+def pair_dists(ref, da, db, ia, ib):
+    return np.array([ref.descriptor_distance(da[i], db[j]) for i, j in zip(ia, ib)], np.float32)
+
+
+def run_case(ref, name, kind, a):
+    """Runs one case through the flat ref_* harness API (oracle/ref_py.py) -- the reference build for the golden file,
+    or the C++ adaptor build under test -- and returns {name/key: array}."""
+    S = synth()
+    out = {}
+    out[name + "/sha"] = np.frombuffer(bytes.fromhex(digest(a)), np.uint8)
+    if kind == "bow":
+        c = a["c"]
+        nm, m = ref.search_by_bow_kf_f(c["desc_a"], c["kps_a"], c["fv_a"], c["valid_a"], c["desc_b"], c["kps_b"], c["fv_b"], a["ratio"], a["ori"])
+        j = np.nonzero(m >= 0)[0]
+        out[name + "/kf_f_nm"], out[name + "/kf_f_match"] = np.int32(nm), m
+        out[name + "/kf_f_dist"] = pair_dists(ref, c["desc_a"], c["desc_b"], m[j], j)
+        nm, m = ref.search_by_bow_kf_kf(c["desc_a"], c["kps_a"], c["fv_a"], c["valid_a"], c["desc_b"], c["kps_b"], c["fv_b"], c["valid_b"], a["ratio"], a["ori"])
+        i = np.nonzero(m >= 0)[0]
+        out[name + "/kf_kf_nm"], out[name + "/kf_kf_match"] = np.int32(nm), m
+        out[name + "/kf_kf_dist"] = pair_dists(ref, c["desc_a"], c["desc_b"], i, m[i])
+    elif kind == "tri":
+        c = a["c"]
+        kfs = c["kfs"]
+        ms, nms = [], []
+        for p in range(len(c["ia"])):
+            x, y = kfs[c["ia"][p]], kfs[c["ib"][p]]
+            nm, m = ref.search_for_triangulation(x["desc"], x["kps"], x["fv"], x["has_mp"], y["desc"], y["kps"], y["fv"], y["has_mp"],
+                                                 c["F12"][p], c["epipoles"][p][0], c["epipoles"][p][1], c["scale_factors"], c["level_sigma2"], a["ori"])
+            ms.append(m); nms.append(nm)
+        out[name + "/match"], out[name + "/nm"] = np.stack(ms), np.array(nms, np.int32)
+    elif kind == "init":
+        c = a["c"]
+        nm, m, prev = ref.search_for_initialization(c["desc1"], c["kps1"], c["desc2"], c["kps2"], c["grid2"], c["prev_matched"], a["window"], c["nnratio"], 1)
+        out[name + "/nm"], out[name + "/match"], out[name + "/prev"] = np.int32(nm), m, prev
+    elif kind == "proj_localmap":
+        c = a["c"]
+        nm, asg = ref.sbp_local_map(c["desc_t"], c["kps_t"], c["grid"], c["queries"], c["level"], c["view_cos"], c["desc_q"], c["blocked0"], S.scale_factors(), a["th"], 0.8)
+        out[name + "/nm"], out[name + "/assign"] = np.int32(nm), asg
+    elif kind == "proj_f2f":
+        f = a["c"]
+        q = f["queries"]
+        nm, asg = ref.sbp_frame_frame(f["desc_t"], f["kps_t"], f["grid"], q, (q["min_level"] + 1).astype(np.int32), f["desc_q"], f["blocked0"], S.scale_factors(), a["th"], 0.8, 1)
+        out[name + "/nm"], out[name + "/assign"] = np.int32(nm), asg
+    elif kind == "proj_reloc":
+        f = a["f"]
+        nm, asg = ref.sbp_frame_keyframe(f["desc_t"], f["kps_t"], f["grid"], a["q"], a["level"], f["desc_q"], a["blocked0"], S.scale_factors(), a["th"], a["acc"], 0.9, 1)
+        out[name + "/nm"], out[name + "/assign"] = np.int32(nm), asg
+    elif kind == "proj_sim3":
+        f = a["f"]
+        nm, asg = ref.sbp_keyframe_sim3(f["desc_t"], f["kps_t"], f["grid"], a["q"], a["level"], f["desc_q"], a["blocked0"], S.scale_factors(), int(a["th"]), 0.85)
+        out[name + "/nm"], out[name + "/assign"] = np.int32(nm), asg
+    elif kind == "fuse":
+        nf, act = ref.fuse(a["desc_t"], a["kps_t"], a["grid"], a["q"], a["level"], a["desc_q"], a["occ_obs"], a["mp_obs"], S.scale_factors(), a["th"])
+        out[name + "/nf"], out[name + "/action"] = np.int32(nf), act
+    elif kind == "fuse_sim3":
+        nf, rep, add = ref.fuse_sim3(a["desc_t"], a["kps_t"], a["grid"], a["q"], a["level"], a["desc_q"], a["occ_obs"], a["mp_obs"], S.scale_factors(), a["th"])
+        out[name + "/nf"], out[name + "/replace"], out[name + "/added"] = np.int32(nf), rep, add
+    elif kind == "sim3":
+        nf, m = ref.search_by_sim3(a["desc1"], a["kps1"], a["desc2"], a["kps2"], a["grid"], a["valid1"], a["valid2"], a["uv1"], a["uv2"],
+                                   a["level1"], a["level2"], a["desc1"], a["desc2"], a["already1"], S.scale_factors(), a["th"])
+        out[name + "/nf"], out[name + "/match"] = np.int32(nf), m
     return out

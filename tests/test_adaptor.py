@@ -1,0 +1,46 @@
+"""The C++ adaptor (asd-slam_b200/host/ORBmatcher_cuda.cc: the reference's ORBmatcher class re-implemented over
+libasdmatch_cuda.so, same header, same method signatures) against the reference's own ORBmatcher.cc.
+
+Both are built behind the same flat harness (oracle/ref_driver.cc) with the same Frame/KeyFrame/MapPoint shims, so the
+identical inputs reach `ORB_SLAM2::ORBmatcher::Search*` / `Fuse` in both; the reference's outputs are the committed
+golden file.  GPU only (the adaptor has no CPU path).  Everything is compared with tolerance 0."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+sys.path.insert(0, os.path.join(HERE, "golden"))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+import cases as C  # noqa: E402
+
+ADAPTOR = os.path.join(ROOT, "asd-slam_b200", "host", "libadaptor_shim.so")
+GOLD = np.load(os.path.join(HERE, "golden", "ref_golden.npz"))
+CASES = C.cases()
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def adaptor(ctx):
+    if not os.path.exists(ADAPTOR):
+        pytest.skip("libadaptor_shim.so not built (needs /root/reference at build time)")
+    import ref_py
+    ref_py.use(ADAPTOR)
+    yield ref_py
+    ref_py.use(None)
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_adaptor_matches_reference(case, adaptor):
+    name, kind, a = case
+    got = C.run_case(adaptor, name, kind, a)
+    assert got, "no outputs"
+    for k, v in got.items():
+        want = GOLD[k]
+        if v.dtype == np.float32:
+            assert np.array_equal(v.view(np.uint32), want.view(np.uint32)), k
+        else:
+            assert np.array_equal(v, want), f"{k}: {np.argwhere(np.asarray(v) != np.asarray(want))[:5].tolist()}"

