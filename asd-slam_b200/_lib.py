@@ -29,7 +29,7 @@ HISTO_LENGTH = 30
 EXPORTS = [
     "asdm_create", "asdm_destroy", "asdm_last_error", "asdm_stream", "asdm_synchronize", "asdm_set_stream",
     "asdm_host_alloc", "asdm_host_free", "asdm_set_option", "asdm_get_stat",
-    "asdm_set_create", "asdm_set_retain", "asdm_set_release", "asdm_set_size", "asdm_set_featvec",
+    "asdm_set_create", "asdm_set_create_async", "asdm_set_retain", "asdm_set_release", "asdm_set_size", "asdm_set_featvec",
     "asdm_set_read_desc",
     "asdm_search_by_bow_kf_f", "asdm_search_by_bow_kf_kf", "asdm_search_for_triangulation",
     "asdm_search_by_projection", "asdm_search_by_projection_q", "asdm_search_for_initialization", "asdm_stereo_row_match",
@@ -90,6 +90,7 @@ def load():
     lib.asdm_set_option.argtypes = [vp, C.c_char_p, C.c_int]
     lib.asdm_get_stat.argtypes = [vp, C.c_char_p, C.POINTER(C.c_int64)]
     lib.asdm_set_create.argtypes = [vp, vp, C.c_int, C.c_int, vp, C.POINTER(Grid), C.POINTER(vp)]
+    lib.asdm_set_create_async.argtypes = lib.asdm_set_create.argtypes
     lib.asdm_set_retain.argtypes = [vp]
     lib.asdm_set_release.argtypes = [vp]
     lib.asdm_set_size.argtypes = [vp]

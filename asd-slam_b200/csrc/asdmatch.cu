@@ -39,28 +39,88 @@ static int fail(asdm_ctx* ctx, int code, const char* what, cudaError_t e = cudaS
     (ctx)->stat_total_launches++; \
   } while (0)
 
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// Device memory comes from the device's stream-ordered pool (cudaMallocAsync) with the release threshold lifted in
+// asdm_create: allocation and free are ordered on the context stream, never synchronise the device, and the memory
+// of released sets / jobs is recycled by the next ones (keyframes come and go at frame rate in the SLAM system).
+static cudaError_t dev_alloc(asdm_ctx* ctx, void** p, size_t bytes) { return cudaMallocAsync(p, bytes, ctx->stream); }
+static void dev_free(asdm_ctx* ctx, void* p) {
+  if (p && cudaFreeAsync(p, ctx->stream) != cudaSuccess) cudaGetLastError();
+}
+
 static int ensure(asdm_ctx* ctx, DevBuf& b, size_t bytes) {
   if (bytes <= b.cap) return ASDM_OK;
-  if (b.p) {
-    CK(cudaStreamSynchronize(ctx->stream));
-    CK(cudaFree(b.p));
-    b.p = nullptr;
-    b.cap = 0;
-  }
+  dev_free(ctx, b.p);  // stream-ordered: kernels already queued on the old buffer finish first
+  b.p = nullptr;
+  b.cap = 0;
   size_t want = std::max(bytes, (size_t)4096);
   want = (want + 255) & ~(size_t)255;
-  CK(cudaMalloc(&b.p, want));
+  CK(dev_alloc(ctx, &b.p, want));
   b.cap = want;
   return ASDM_OK;
 }
 
-static void release(DevBuf& b) {
-  if (b.p) cudaFree(b.p);
+static void release(asdm_ctx* ctx, DevBuf& b) {
+  dev_free(ctx, b.p);
   b.p = nullptr;
   b.cap = 0;
 }
 
-static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+// the library synchronised the stream: everything staged so far has been consumed
+static inline void synced(asdm_ctx* ctx) { ctx->stage_off = 0; }
+
+static int stage_alloc(asdm_ctx* ctx, size_t bytes, void** out) {
+  bytes = align_up(std::max(bytes, (size_t)1), 256);
+  if (ctx->stage_off + bytes > ctx->stage_cap) {
+    CK(cudaStreamSynchronize(ctx->stream));
+    synced(ctx);
+    if (bytes > ctx->stage_cap) {
+      if (ctx->stage) cudaFreeHost(ctx->stage);
+      ctx->stage = nullptr;
+      ctx->stage_cap = 0;
+      const size_t want = std::max(bytes * 2, (size_t)16 << 20);
+      CK(cudaHostAlloc((void**)&ctx->stage, want, cudaHostAllocDefault));
+      ctx->stage_cap = want;
+    }
+  }
+  *out = ctx->stage + ctx->stage_off;
+  ctx->stage_off += bytes;
+  return ASDM_OK;
+}
+
+// host -> device through the staging arena: returns at once, the caller's buffer is free on return
+static int stage_upload(asdm_ctx* ctx, void* dst, const void* src, size_t bytes) {
+  if (!bytes) return ASDM_OK;
+  void* h = nullptr;
+  int rc = stage_alloc(ctx, bytes, &h);
+  if (rc) return rc;
+  memcpy(h, src, bytes);
+  CK(cudaMemcpyAsync(dst, h, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  return ASDM_OK;
+}
+
+enum { SLOT_BYTES = 64, SLOT_COUNT = 4096 };
+static int32_t* slot_get(asdm_ctx* ctx) {
+  if (!ctx->slot_slab) {
+    if (cudaHostAlloc((void**)&ctx->slot_slab, (size_t)SLOT_BYTES * SLOT_COUNT, cudaHostAllocDefault) != cudaSuccess) {
+      cudaGetLastError();
+      ctx->slot_slab = nullptr;
+      return nullptr;
+    }
+    ctx->slot_free.reserve(SLOT_COUNT);
+    for (int i = SLOT_COUNT - 1; i >= 0; i--) ctx->slot_free.push_back(i);
+  }
+  if (ctx->slot_free.empty()) return nullptr;
+  const int i = ctx->slot_free.back();
+  ctx->slot_free.pop_back();
+  int32_t* p = (int32_t*)(ctx->slot_slab + (size_t)i * SLOT_BYTES);
+  memset(p, 0, SLOT_BYTES);
+  return p;
+}
+static void slot_put(asdm_ctx* ctx, int32_t* p) {
+  if (p) ctx->slot_free.push_back((int)(((char*)p - ctx->slot_slab) / SLOT_BYTES));
+}
 
 // Smallest keep threshold t such that a candidate farther than t can neither be accepted (d > TH_LOW) nor make
 // the ratio test fail as second best: for every fp32 d > t, fl(nnratio*d) > th_accept >= best1.
@@ -102,6 +162,17 @@ extern "C" int asdm_create(int device, asdm_ctx** out) {
   }
   cudaFuncSetAttribute(k_cand_exact, cudaFuncAttributeMaxDynamicSharedMemorySize,
                        (int)(ASDM_DESC_DIM * (CE_TM + CE_TN) * sizeof(float)));
+  {  // keep freed blocks in the pool instead of returning them to the driver at every synchronisation
+    cudaMemPool_t pool = nullptr;
+    uint64_t keep = UINT64_MAX;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) != cudaSuccess ||
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep) != cudaSuccess) {
+      cudaGetLastError();
+      cudaStreamDestroy(ctx->stream);
+      delete ctx;
+      return ASDM_ERR_CUDA;
+    }
+  }
   *out = ctx;
   return ASDM_OK;
 }
@@ -109,10 +180,11 @@ extern "C" int asdm_create(int device, asdm_ctx** out) {
 extern "C" int asdm_destroy(asdm_ctx* ctx) {
   if (!ctx) return ASDM_ERR_INVALID;
   cudaSetDevice(ctx->device);
+  for (auto& b : ctx->scratch) release(ctx, b);
   cudaStreamSynchronize(ctx->stream);
-  for (auto& b : ctx->scratch) release(b);
   for (cudaEvent_t e : ctx->ev) cudaEventDestroy(e);
-  if (ctx->h_pin) cudaFreeHost(ctx->h_pin);
+  if (ctx->stage) cudaFreeHost(ctx->stage);
+  if (ctx->slot_slab) cudaFreeHost(ctx->slot_slab);
   if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
   return ASDM_OK;
@@ -126,6 +198,7 @@ extern "C" int asdm_set_stream(asdm_ctx* ctx, void* stream) {
   std::lock_guard<std::recursive_mutex> lk(ctx->mu);
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
+  synced(ctx);
   if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
   ctx->stream = (cudaStream_t)stream;
   ctx->own_stream = false;
@@ -137,6 +210,7 @@ extern "C" int asdm_synchronize(asdm_ctx* ctx) {
   std::lock_guard<std::recursive_mutex> lk(ctx->mu);
   CK(cudaSetDevice(ctx->device));
   CK(cudaStreamSynchronize(ctx->stream));
+  synced(ctx);
   return ASDM_OK;
 }
 
@@ -201,31 +275,36 @@ extern "C" int asdm_host_free(void* p) {
   return ASDM_OK;
 }
 
-static int pin_reserve(asdm_ctx* ctx, size_t bytes) {
-  if (bytes <= ctx->h_pin_cap) return ASDM_OK;
-  if (ctx->h_pin) {
-    CK(cudaStreamSynchronize(ctx->stream));
-    cudaFreeHost(ctx->h_pin);
-    ctx->h_pin = nullptr;
-    ctx->h_pin_cap = 0;
-  }
-  size_t want = align_up(std::max(bytes, (size_t)1 << 16), 4096);
-  CK(cudaHostAlloc(&ctx->h_pin, want, cudaHostAllocDefault));
-  ctx->h_pin_cap = want;
-  return ASDM_OK;
-}
-
 // --------------------------------------------------------------------------------------- descriptor sets
 static void set_free(asdm_set* s) {
   if (!s) return;
-  cudaSetDevice(s->ctx->device);
-  if (s->desc) cudaFree(s->desc);  // one arena: every other device pointer lives inside it
-  if (s->node_id) cudaFree(s->node_id);
+  asdm_ctx* ctx = s->ctx;
+  cudaSetDevice(ctx->device);
+  dev_free(ctx, s->desc);  // one arena: every other device pointer lives inside it
+  dev_free(ctx, s->fv_mem);
+  slot_put(ctx, s->h_flag);
   delete s;
 }
 
-extern "C" int asdm_set_create(asdm_ctx* ctx, const float* desc, int n, int row_stride_bytes, const asdm_kp* kps,
-                               const asdm_grid* grid, asdm_set** out) {
+// reads the tensor-core range flags of sets whose flag copy is still in flight (one stream wait for all of them)
+static int resolve_tc_flags(asdm_ctx* ctx, asdm_set* const* sets, int n) {
+  bool pending = false;
+  for (int k = 0; k < n; k++) pending |= sets[k]->tc_ok < 0;
+  if (!pending) return ASDM_OK;
+  CK(cudaStreamSynchronize(ctx->stream));
+  synced(ctx);
+  for (int k = 0; k < n; k++) {
+    asdm_set* s = sets[k];
+    if (s->tc_ok >= 0) continue;
+    s->tc_ok = (s->h_flag && *s->h_flag == 0) ? 1 : 0;
+    slot_put(ctx, s->h_flag);
+    s->h_flag = nullptr;
+  }
+  return ASDM_OK;
+}
+
+static int set_create_impl(asdm_ctx* ctx, const float* desc, int n, int row_stride_bytes, const asdm_kp* kps,
+                           const asdm_grid* grid, asdm_set** out, bool wait) {
   if (!ctx || !out || n < 0 || (n > 0 && !desc)) return ASDM_ERR_INVALID;
   *out = nullptr;
   if (row_stride_bytes == 0) row_stride_bytes = ASDM_DESC_DIM * sizeof(float);
@@ -251,16 +330,15 @@ extern "C" int asdm_set_create(asdm_ctx* ctx, const float* desc, int n, int row_
   const size_t o_ci = off;   off += grid ? align_up((size_t)s->n_pad * sizeof(int32_t), 256) : 0;
   const size_t o_tmp = off;  off += grid ? align_up((size_t)s->n_pad * sizeof(int32_t), 256) : 0;
   char* base = nullptr;
-  cudaError_t e = cudaMalloc(&base, off);
+  cudaError_t e = dev_alloc(ctx, (void**)&base, off);
   if (e != cudaSuccess) {
     delete s;
-    return fail(ctx, ASDM_ERR_OOM, "cudaMalloc(set)", e);
+    return fail(ctx, ASDM_ERR_OOM, "cudaMallocAsync(set)", e);
   }
   s->desc = (float*)(base + o_desc);
   s->desc_bf = (__nv_bfloat16*)(base + o_bf);
   s->norm2 = (float*)(base + o_norm);
   s->d_flags = (int32_t*)(base + o_flags);
-  int rc = ASDM_OK;
   auto bail = [&](int code) {
     set_free(s);
     return code;
@@ -272,6 +350,7 @@ extern "C" int asdm_set_create(asdm_ctx* ctx, const float* desc, int n, int row_
   } while (0)
   CKS(cudaMemsetAsync(s->d_flags, 0, 256, ctx->stream));
   if (n > 0) {
+    // descriptors are DMA'd straight from the caller's buffer (true async when it is page-locked)
     if (row_stride_bytes == (int)(ASDM_DESC_DIM * sizeof(float)))
       CKS(cudaMemcpyAsync(s->desc, desc, (size_t)n * ASDM_DESC_DIM * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
     else
@@ -284,10 +363,15 @@ extern "C" int asdm_set_create(asdm_ctx* ctx, const float* desc, int n, int row_
   ctx->stat_launches = 0;
   k_pack_desc<<<(s->n_pad * 32 + 255) / 256, 256, 0, ctx->stream>>>(s->desc, n, s->n_pad, s->desc_bf, s->norm2, s->d_flags);
   LAUNCHED(ctx);
+  s->h_flag = slot_get(ctx);  // the range flag travels back behind the kernel; read when a job first needs it
+  if (s->h_flag) CKS(cudaMemcpyAsync(s->h_flag, s->d_flags, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
   if (kps) {
     s->kps = (asdm_kp*)(base + o_kps);
     s->has_kps = true;
-    if (n > 0) CKS(cudaMemcpyAsync(s->kps, kps, (size_t)n * sizeof(asdm_kp), cudaMemcpyHostToDevice, ctx->stream));
+    if (n > 0) {
+      const int rc = stage_upload(ctx, s->kps, kps, (size_t)n * sizeof(asdm_kp));
+      if (rc) return bail(rc);
+    }
   }
   if (grid) {
     s->grid = *grid;
@@ -300,12 +384,28 @@ extern "C" int asdm_set_create(asdm_ctx* ctx, const float* desc, int n, int row_
     LAUNCHED(ctx);
   }
   CKS(cudaGetLastError());
-  // the caller's host buffers may be reused as soon as we return
-  CKS(cudaStreamSynchronize(ctx->stream));
+  if (wait || !s->h_flag) {  // the caller's descriptor buffer may be reused as soon as we return
+    CKS(cudaStreamSynchronize(ctx->stream));
+    synced(ctx);
+    if (!s->h_flag) {
+      int32_t f = 1;
+      CKS(cudaMemcpy(&f, s->d_flags, sizeof f, cudaMemcpyDeviceToHost));
+      s->tc_ok = f ? 0 : 1;
+    }
+  }
 #undef CKS
-  (void)rc;
   *out = s;
   return ASDM_OK;
+}
+
+extern "C" int asdm_set_create(asdm_ctx* ctx, const float* desc, int n, int row_stride_bytes, const asdm_kp* kps,
+                               const asdm_grid* grid, asdm_set** out) {
+  return set_create_impl(ctx, desc, n, row_stride_bytes, kps, grid, out, true);
+}
+
+extern "C" int asdm_set_create_async(asdm_ctx* ctx, const float* desc, int n, int row_stride_bytes, const asdm_kp* kps,
+                                     const asdm_grid* grid, asdm_set** out) {
+  return set_create_impl(ctx, desc, n, row_stride_bytes, kps, grid, out, false);
 }
 
 extern "C" int asdm_set_retain(asdm_set* s) {
@@ -319,9 +419,7 @@ extern "C" int asdm_set_release(asdm_set* s) {
   if (s->ref.fetch_sub(1) == 1) {
     asdm_ctx* ctx = s->ctx;
     std::lock_guard<std::recursive_mutex> lk(ctx->mu);
-    cudaSetDevice(ctx->device);
-    cudaStreamSynchronize(ctx->stream);
-    set_free(s);
+    set_free(s);  // stream-ordered free: searches already queued on this set finish first
   }
   return ASDM_OK;
 }
@@ -333,9 +431,15 @@ extern "C" int asdm_set_featvec(asdm_set* s, const asdm_featvec* fv) {
   asdm_ctx* ctx = s->ctx;
   std::lock_guard<std::recursive_mutex> lk(ctx->mu);
   CK(cudaSetDevice(ctx->device));
-  // per-feature node id and scan position: the flattening of DBoW2::FeatureVector the kernels gate on
-  std::vector<uint32_t> node((size_t)s->n_pad, 0u);
-  std::vector<int32_t> pos((size_t)s->n_pad, -1);
+  // per-feature node id and scan position: the flattening of DBoW2::FeatureVector the kernels gate on, written
+  // straight into the pinned staging arena
+  void* h = nullptr;
+  int rc = stage_alloc(ctx, (size_t)s->n_pad * 8, &h);
+  if (rc) return rc;
+  uint32_t* node = (uint32_t*)h;
+  int32_t* pos = (int32_t*)(node + s->n_pad);
+  memset(node, 0, (size_t)s->n_pad * 4);
+  memset(pos, 0xff, (size_t)s->n_pad * 4);
   for (int k = 0; k < fv->n_nodes; k++) {
     if (k > 0 && !(fv->node_ids[k] > fv->node_ids[k - 1])) return fail(ctx, ASDM_ERR_INVALID, "node ids not ascending");
     for (int e = fv->off[k]; e < fv->off[k + 1]; e++) {
@@ -346,15 +450,12 @@ extern "C" int asdm_set_featvec(asdm_set* s, const asdm_featvec* fv) {
       pos[i] = e;
     }
   }
-  if (!s->node_id) {
-    void* p = nullptr;
-    CK(cudaMalloc(&p, (size_t)s->n_pad * 8));
-    s->node_id = (uint32_t*)p;
-    s->fv_pos = (int32_t*)((char*)p + (size_t)s->n_pad * 4);
+  if (!s->fv_mem) {
+    CK(dev_alloc(ctx, &s->fv_mem, (size_t)s->n_pad * 8));
+    s->node_id = (uint32_t*)s->fv_mem;
+    s->fv_pos = (int32_t*)((char*)s->fv_mem + (size_t)s->n_pad * 4);
   }
-  CK(cudaMemcpyAsync(s->node_id, node.data(), (size_t)s->n_pad * 4, cudaMemcpyHostToDevice, ctx->stream));
-  CK(cudaMemcpyAsync(s->fv_pos, pos.data(), (size_t)s->n_pad * 4, cudaMemcpyHostToDevice, ctx->stream));
-  CK(cudaStreamSynchronize(ctx->stream));
+  CK(cudaMemcpyAsync(s->fv_mem, h, (size_t)s->n_pad * 8, cudaMemcpyHostToDevice, ctx->stream));
   s->has_fv = true;
   return ASDM_OK;
 }
@@ -367,6 +468,7 @@ extern "C" int asdm_set_read_desc(asdm_set* s, int row0, int n_rows, float* out)
   CK(cudaMemcpyAsync(out, s->desc + (size_t)row0 * ASDM_DESC_DIM, (size_t)n_rows * ASDM_DESC_DIM * sizeof(float),
                      cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
+  synced(ctx);
   return ASDM_OK;
 }
 
@@ -391,16 +493,23 @@ struct asdm_job {
   float t_keep_tc = 0.f;
   bool ran = false;
   int32_t* h_flags = nullptr;  // pinned, 8 ints: [0] cand overflow, [1] list overflow, [2] list count
+  bool h_flags_owned = false;  // true when the context's slot slab was exhausted and the job allocated its own
 };
 
 static void job_free(asdm_job* j) {
   if (!j) return;
-  cudaSetDevice(j->ctx->device);
-  cudaStreamSynchronize(j->ctx->stream);
+  asdm_ctx* ctx = j->ctx;
+  cudaSetDevice(ctx->device);
   DevBuf* bufs[] = {&j->d_pairs, &j->d_masks, &j->d_cnt, &j->d_cand, &j->d_owner, &j->d_acc, &j->d_flags,
                     &j->d_match, &j->d_dist, &j->d_nm, &j->d_work, &j->d_tmaps, &j->d_list, &j->d_seg_count};
-  for (DevBuf* b : bufs) release(*b);
-  if (j->h_flags) cudaFreeHost(j->h_flags);
+  for (DevBuf* b : bufs) release(ctx, *b);  // stream-ordered: a run still in flight completes first
+  if (j->h_flags_owned) {
+    cudaStreamSynchronize(ctx->stream);
+    synced(ctx);
+    cudaFreeHost(j->h_flags);
+  } else {
+    slot_put(ctx, j->h_flags);
+  }
   for (asdm_set* s : j->sets) asdm_set_release(s);
   delete j;
 }
@@ -467,11 +576,13 @@ static int job_prepare(asdm_ctx* ctx, const asdm_job_desc* d, int kind_internal,
   }
   int rc;
   if ((rc = ensure(ctx, j->d_masks, mtot))) return bail(rc);
-  if ((rc = pin_reserve(ctx, mtot))) return bail(rc);
-  for (int k = 0; k < d->n_kf; k++) memcpy((char*)ctx->h_pin + mask_off[k], d->masks[k], (size_t)d->sets[k]->n);
-  if (cudaMemcpyAsync(j->d_masks.p, ctx->h_pin, mtot, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess)
-    return bail(fail(ctx, ASDM_ERR_CUDA, "mask upload"));
-  if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) return bail(fail(ctx, ASDM_ERR_CUDA, "mask upload sync"));
+  {
+    void* h = nullptr;
+    if ((rc = stage_alloc(ctx, mtot, &h))) return bail(rc);
+    for (int k = 0; k < d->n_kf; k++) memcpy((char*)h + mask_off[k], d->masks[k], (size_t)d->sets[k]->n);
+    if (cudaMemcpyAsync(j->d_masks.p, h, mtot, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess)
+      return bail(fail(ctx, ASDM_ERR_CUDA, "mask upload"));
+  }
 
   BowParams& P = j->P;
   memset(&P, 0, sizeof P);
@@ -526,17 +637,8 @@ static int job_prepare(asdm_ctx* ctx, const asdm_job_desc* d, int kind_internal,
 
   // tensor-core shortlist only when every set passed the range check of k_pack_desc
   if (!ctx->opt_force_exact && d->n_pairs > 0) {
-    for (int k = 0; k < d->n_kf; k++) {
-      asdm_set* s = d->sets[k];
-      if (s->tc_ok < 0) {
-        int32_t f = 1;
-        if (cudaMemcpyAsync(&f, s->d_flags, sizeof f, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
-            cudaStreamSynchronize(ctx->stream) != cudaSuccess)
-          return bail(fail(ctx, ASDM_ERR_CUDA, "flag readback"));
-        s->tc_ok = f ? 0 : 1;
-      }
-      all_tc &= s->tc_ok;
-    }
+    if ((rc = resolve_tc_flags(ctx, d->sets, d->n_kf))) return bail(rc);
+    for (int k = 0; k < d->n_kf; k++) all_tc &= d->sets[k]->tc_ok;
     if (all_tc) {
       // work units: one resident 256-row B tile x a run of 128-row A tiles; split runs until the grid is full
       std::vector<TcWork> work;
@@ -559,9 +661,9 @@ static int job_prepare(asdm_ctx* ctx, const asdm_job_desc* d, int kind_internal,
         if ((rc = ensure(ctx, j->d_tmaps, (size_t)d->n_kf * 128))) return bail(rc);
         std::vector<uint8_t> maps((size_t)d->n_kf * 128);
         for (int k = 0; k < d->n_kf; k++) memcpy(maps.data() + (size_t)k * 128, d->sets[k]->tmap_bf.data(), 128);
-        if (cudaMemcpy(j->d_work.p, work.data(), work.size() * sizeof(TcWork), cudaMemcpyHostToDevice) != cudaSuccess ||
-            cudaMemcpy(j->d_tmaps.p, maps.data(), maps.size(), cudaMemcpyHostToDevice) != cudaSuccess)
-          return bail(fail(ctx, ASDM_ERR_CUDA, "work upload"));
+        if ((rc = stage_upload(ctx, j->d_work.p, work.data(), work.size() * sizeof(TcWork))) ||
+            (rc = stage_upload(ctx, j->d_tmaps.p, maps.data(), maps.size())))
+          return bail(rc);
         long q = 0;
         for (int p = 0; p < d->n_pairs; p++) q += j->h_pairs[p].nA;
         j->list_cap = (int)std::min<long>((long)1 << 30, std::max<long>(4096, q * ctx->opt_list_cap_per_query));
@@ -569,12 +671,14 @@ static int job_prepare(asdm_ctx* ctx, const asdm_job_desc* d, int kind_internal,
     }
   }
   if ((rc = ensure(ctx, j->d_pairs, std::max<size_t>(1, j->h_pairs.size()) * sizeof(PairDesc)))) return bail(rc);
-  if (!j->h_pairs.empty() &&
-      cudaMemcpy(j->d_pairs.p, j->h_pairs.data(), j->h_pairs.size() * sizeof(PairDesc), cudaMemcpyHostToDevice) != cudaSuccess)
-    return bail(fail(ctx, ASDM_ERR_CUDA, "pair upload"));
+  if ((rc = stage_upload(ctx, j->d_pairs.p, j->h_pairs.data(), j->h_pairs.size() * sizeof(PairDesc)))) return bail(rc);
   if ((rc = job_alloc_scratch(j))) return bail(rc);
-  if (cudaHostAlloc((void**)&j->h_flags, 64, cudaHostAllocDefault) != cudaSuccess)
-    return bail(fail(ctx, ASDM_ERR_OOM, "pinned flags"));
+  j->h_flags = slot_get(ctx);
+  if (!j->h_flags) {
+    if (cudaHostAlloc((void**)&j->h_flags, 64, cudaHostAllocDefault) != cudaSuccess)
+      return bail(fail(ctx, ASDM_ERR_OOM, "pinned flags"));
+    j->h_flags_owned = true;
+  }
   *out = j;
   return ASDM_OK;
 }
@@ -647,6 +751,7 @@ static int job_settle(asdm_job* j) {
   for (int attempt = 0; attempt < 24; attempt++) {
     CK(cudaMemcpyAsync(j->h_flags, j->d_flags.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    synced(ctx);
     const bool cand_over = j->h_flags[0] != 0, list_over = j->h_flags[1] != 0;
     ctx->stat_tc_pairs = j->use_tc ? j->h_flags[2] : 0;
     if (!cand_over && !list_over) return ASDM_OK;
@@ -692,6 +797,7 @@ extern "C" int asdm_job_fetch(asdm_job* j, int32_t* match12, float* dist12, int3
   if (nmatches && j->n_pairs)
     CK(cudaMemcpyAsync(nmatches, j->d_nm.p, (size_t)j->n_pairs * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
+  synced(ctx);
   return ASDM_OK;
 }
 
@@ -831,6 +937,7 @@ static int proj_candidates(asdm_ctx* ctx, asdm_set* target, int nq, const float*
     int32_t h[2] = {0, 0};
     CK(cudaMemcpyAsync(h, pd.total, 8, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    synced(ctx);
     if (h[1]) {  // pool too small: h[0] is the exact demand
       ent_cap = std::max(ent_cap * 2, h[0] + 1024);
       ctx->stat_retries++;
@@ -925,6 +1032,7 @@ static int search_by_projection_impl(asdm_ctx* ctx, asdm_set* target, const asdm
   if (dist_t && n_t > 0) CK(cudaMemcpyAsync(dist_t, d_dist, (size_t)n_t * 4, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaMemcpyAsync(&nm, d_nm, 4, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
+  synced(ctx);
   if (nmatches) *nmatches = nm;
   return ASDM_OK;
 }
@@ -991,6 +1099,7 @@ extern "C" int asdm_search_for_initialization(asdm_ctx* ctx, asdm_set* f1, asdm_
   }
   CK(cudaMemcpyAsync(&nm, d_nm, 4, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
+  synced(ctx);
   if (nmatches) *nmatches = nm;
   return ASDM_OK;
 }
@@ -1022,5 +1131,6 @@ extern "C" int asdm_stereo_row_match(asdm_ctx* ctx, asdm_set* left, asdm_set* ri
     if (best_dist) CK(cudaMemcpyAsync(best_dist, d_dist, (size_t)n_l * 4, cudaMemcpyDeviceToHost, ctx->stream));
   }
   CK(cudaStreamSynchronize(ctx->stream));
+  synced(ctx);
   return ASDM_OK;
 }

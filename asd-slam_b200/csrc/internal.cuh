@@ -29,8 +29,8 @@ struct asdm_ctx {
   std::string err;
   int opt_force_exact = 0;
   int opt_cand_cap = 8;
-  int opt_list_cap_per_query = 4;
-  int opt_tc_epi_warps = 8;        // epilogue warps of the tensor-core kernel: 4 or 8  // tensor-core short list slots per query row (grows on overflow)
+  int opt_list_cap_per_query = 4;  // tensor-core short list slots per query row (grows on overflow)
+  int opt_tc_epi_warps = 8;        // epilogue warps of the tensor-core kernel: 4 or 8
   int64_t stat_launches = 0;       // kernels launched by the last call / job run
   int64_t stat_total_launches = 0;
   int64_t stat_cand_cap = 0;
@@ -39,9 +39,14 @@ struct asdm_ctx {
   int64_t stat_tc_pairs = 0;  // (i,j) pairs emitted by the tensor-core shortlist in the last run
   int sm_count = 148;
   void* tmap_encode = nullptr;  // cuTensorMapEncodeTiled, resolved through the runtime
-  // pinned staging for the single-call entry points
-  void* h_pin = nullptr;
-  size_t h_pin_cap = 0;
+  // Pinned staging arena (bump allocator): small per-call inputs (keypoints, masks, FeatureVector flattening, work
+  // lists) are written here and DMA'd from here, so no call has to wait for its own upload. Everything staged is
+  // consumed in stream order; the arena rewinds whenever the library synchronises the stream.
+  char* stage = nullptr;
+  size_t stage_cap = 0, stage_off = 0;
+  // Pinned 64-byte slots with object lifetime (per-job overflow flags, per-set tensor-core range flag)
+  char* slot_slab = nullptr;
+  std::vector<int> slot_free;
   DevBuf scratch[8];
   int opt_time_kernels = 0;     // record CUDA events around the distance stage of every job run
   std::vector<cudaEvent_t> ev;  // pairs (begin, end), drained by asdm_get_stat("dist_stage_us")
@@ -58,6 +63,8 @@ struct asdm_set {
   float* norm2 = nullptr;            // [n_pad] sum of squares of the fp32 row
   int32_t* d_flags = nullptr;        // [0] = 1 when some row is non-finite or its norm is out of the TC range
   int tc_ok = -1;                    // -1 unknown (flags not read back yet), 0 no, 1 yes
+  int32_t* h_flag = nullptr;         // pinned slot the flag is copied to right after k_pack_desc (resolved lazily)
+  void* fv_mem = nullptr;            // allocation holding node_id / fv_pos
   bool has_kps = false, has_grid = false, has_fv = false;
   asdm_kp* kps = nullptr;  // [n] cv::KeyPoint fields as uploaded (16 B each: one LDG.128 per keypoint)
   asdm_grid grid{};

@@ -92,7 +92,9 @@ _PINNED = []  # pinned blocks live for the process (bench/test helper)
 class DescriptorSet:
     """Device-resident descriptors (+ keypoints, grid, FeatureVector) of one Frame / KeyFrame / map-point pool."""
 
-    def __init__(self, ctx, desc, kps=None, grid=None, featvec=None):
+    def __init__(self, ctx, desc, kps=None, grid=None, featvec=None, async_upload=False):
+        """async_upload: asdm_set_create_async -- `desc` must stay alive and unmodified until the next synchronising
+        call on the context (use Context.pinned() memory for a true async DMA)."""
         self.ctx = ctx
         desc = _f32(desc)
         assert desc.ndim == 2 and desc.shape[1] == 128
@@ -104,8 +106,10 @@ class DescriptorSet:
             kps = np.ascontiguousarray(kps, dtype=KP_DTYPE)
             assert len(kps) == self.n
         h = C.c_void_p()
-        ctx.check(ctx.lib.asdm_set_create(ctx.h, ptr(desc), self.n, 0, ptr(kps) if kps is not None else None,
-                                          C.byref(g) if g is not None else None, C.byref(h)))
+        create = ctx.lib.asdm_set_create_async if async_upload else ctx.lib.asdm_set_create
+        self._desc_keepalive = desc if async_upload else None
+        ctx.check(create(ctx.h, ptr(desc), self.n, 0, ptr(kps) if kps is not None else None,
+                         C.byref(g) if g is not None else None, C.byref(h)))
         self.h = h
         if featvec is not None:
             self.set_featvec(featvec)

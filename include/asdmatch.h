@@ -13,7 +13,8 @@
  *    (the adaptor maps indices back to pointers);
  *  - every function returns ASDM_OK (0) or a negative error code and never throws;
  *    asdm_last_error() gives the message of the last failure on that context;
- *  - host buffers are caller-owned; device buffers are library-owned (asdm_set, asdm_job);
+ *  - host buffers are caller-owned; device buffers are library-owned (asdm_set, asdm_job) and come from the
+ *    device's stream-ordered memory pool, so creating / releasing sets and jobs never synchronises the device;
  *  - a context owns one CUDA stream; calls on one context are serialised by an internal mutex, so
  *    the three ORB-SLAM2 threads may share it; use one context per GPU;
  *  - there is NO CPU fallback: without a CUDA device asdm_create fails with ASDM_ERR_CUDA.
@@ -97,6 +98,12 @@ int asdm_get_stat(asdm_ctx* ctx, const char* key, int64_t* value);
  * (Frame.cc:47, KeyFrame.cc:153) retain instead of re-uploading. */
 int asdm_set_create(asdm_ctx* ctx, const float* desc, int n, int row_stride_bytes, const asdm_kp* kps,
                     const asdm_grid* grid, asdm_set** out);
+/* Same, but returns without waiting for the descriptor upload: `desc` must stay valid and unmodified until the next
+ * call on this context that synchronises (asdm_synchronize, any search / fetch that returns results). kps / grid are
+ * staged and may be reused at once. With page-locked `desc` (asdm_host_alloc) the copy is a true async DMA, so the
+ * uploads of a batch of keyframes queue back to back and overlap the host-side preparation of the job that uses them. */
+int asdm_set_create_async(asdm_ctx* ctx, const float* desc, int n, int row_stride_bytes, const asdm_kp* kps,
+                          const asdm_grid* grid, asdm_set** out);
 int asdm_set_retain(asdm_set* set);
 int asdm_set_release(asdm_set* set);
 int asdm_set_size(const asdm_set* set);
