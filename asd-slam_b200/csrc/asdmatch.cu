@@ -90,13 +90,13 @@ static int stage_alloc(asdm_ctx* ctx, size_t bytes, void** out) {
 }
 
 // host -> device through the staging arena: returns at once, the caller's buffer is free on return
-static int stage_upload(asdm_ctx* ctx, void* dst, const void* src, size_t bytes) {
+static int stage_upload(asdm_ctx* ctx, void* dst, const void* src, size_t bytes, cudaStream_t stream = nullptr) {
   if (!bytes) return ASDM_OK;
   void* h = nullptr;
   int rc = stage_alloc(ctx, bytes, &h);
   if (rc) return rc;
   memcpy(h, src, bytes);
-  CK(cudaMemcpyAsync(dst, h, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemcpyAsync(dst, h, bytes, cudaMemcpyHostToDevice, stream ? stream : ctx->stream));
   return ASDM_OK;
 }
 
@@ -146,7 +146,9 @@ extern "C" int asdm_create(int device, asdm_ctx** out) {
   asdm_ctx* ctx = new (std::nothrow) asdm_ctx();
   if (!ctx) return ASDM_ERR_OOM;
   ctx->device = device;
-  if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+  if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&ctx->upload_stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&ctx->upload_done, cudaEventDisableTiming) != cudaSuccess) {
     cudaGetLastError();
     delete ctx;
     return ASDM_ERR_CUDA;
@@ -186,6 +188,8 @@ extern "C" int asdm_destroy(asdm_ctx* ctx) {
   if (ctx->stage) cudaFreeHost(ctx->stage);
   if (ctx->slot_slab) cudaFreeHost(ctx->slot_slab);
   if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+  if (ctx->upload_stream) cudaStreamDestroy(ctx->upload_stream);
+  if (ctx->upload_done) cudaEventDestroy(ctx->upload_done);
   delete ctx;
   return ASDM_OK;
 }
@@ -329,8 +333,9 @@ static int set_create_impl(asdm_ctx* ctx, const float* desc, int n, int row_stri
   const size_t o_cs = off;   off += grid ? align_up((size_t)(nc + 1) * sizeof(int32_t), 256) : 0;
   const size_t o_ci = off;   off += grid ? align_up((size_t)s->n_pad * sizeof(int32_t), 256) : 0;
   const size_t o_tmp = off;  off += grid ? align_up((size_t)s->n_pad * sizeof(int32_t), 256) : 0;
+  // allocated on the upload stream (the pool orders the reuse of blocks freed on the main stream by itself)
   char* base = nullptr;
-  cudaError_t e = dev_alloc(ctx, (void**)&base, off);
+  cudaError_t e = cudaMallocAsync((void**)&base, off, ctx->upload_stream);
   if (e != cudaSuccess) {
     delete s;
     return fail(ctx, ASDM_ERR_OOM, "cudaMallocAsync(set)", e);
@@ -348,15 +353,29 @@ static int set_create_impl(asdm_ctx* ctx, const float* desc, int n, int row_stri
     cudaError_t e__ = (call);                                  \
     if (e__ != cudaSuccess) return bail(fail(ctx, ASDM_ERR_CUDA, #call, e__)); \
   } while (0)
-  CKS(cudaMemsetAsync(s->d_flags, 0, 256, ctx->stream));
+  // All host->device traffic of a set rides the upload stream: a small copy queued on the main stream would sit in
+  // the copy engine's FIFO behind its own stream dependencies (pack kernel <- this upload) and stall the next
+  // keyframe's descriptor DMA behind it (measured: 26 GB/s instead of 48 GB/s over 64 keyframes).
+  if (kps) {
+    s->kps = (asdm_kp*)(base + o_kps);
+    s->has_kps = true;
+    if (n > 0) {
+      const int rc = stage_upload(ctx, s->kps, kps, (size_t)n * sizeof(asdm_kp), ctx->upload_stream);
+      if (rc) return bail(rc);
+    }
+  }
   if (n > 0) {
     // descriptors are DMA'd straight from the caller's buffer (true async when it is page-locked)
     if (row_stride_bytes == (int)(ASDM_DESC_DIM * sizeof(float)))
-      CKS(cudaMemcpyAsync(s->desc, desc, (size_t)n * ASDM_DESC_DIM * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+      CKS(cudaMemcpyAsync(s->desc, desc, (size_t)n * ASDM_DESC_DIM * sizeof(float), cudaMemcpyHostToDevice,
+                          ctx->upload_stream));
     else
       CKS(cudaMemcpy2DAsync(s->desc, ASDM_DESC_DIM * sizeof(float), desc, row_stride_bytes,
-                            ASDM_DESC_DIM * sizeof(float), n, cudaMemcpyHostToDevice, ctx->stream));
+                            ASDM_DESC_DIM * sizeof(float), n, cudaMemcpyHostToDevice, ctx->upload_stream));
   }
+  CKS(cudaEventRecord(ctx->upload_done, ctx->upload_stream));
+  CKS(cudaStreamWaitEvent(ctx->stream, ctx->upload_done, 0));  // everything below is ordered after the upload
+  CKS(cudaMemsetAsync(s->d_flags, 0, 256, ctx->stream));
   if (s->n_pad > n)
     CKS(cudaMemsetAsync(s->desc + (size_t)n * ASDM_DESC_DIM, 0, (size_t)(s->n_pad - n) * ASDM_DESC_DIM * sizeof(float),
                         ctx->stream));
@@ -365,14 +384,6 @@ static int set_create_impl(asdm_ctx* ctx, const float* desc, int n, int row_stri
   LAUNCHED(ctx);
   s->h_flag = slot_get(ctx);  // the range flag travels back behind the kernel; read when a job first needs it
   if (s->h_flag) CKS(cudaMemcpyAsync(s->h_flag, s->d_flags, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
-  if (kps) {
-    s->kps = (asdm_kp*)(base + o_kps);
-    s->has_kps = true;
-    if (n > 0) {
-      const int rc = stage_upload(ctx, s->kps, kps, (size_t)n * sizeof(asdm_kp));
-      if (rc) return bail(rc);
-    }
-  }
   if (grid) {
     s->grid = *grid;
     s->has_grid = true;
@@ -451,11 +462,17 @@ extern "C" int asdm_set_featvec(asdm_set* s, const asdm_featvec* fv) {
     }
   }
   if (!s->fv_mem) {
-    CK(dev_alloc(ctx, &s->fv_mem, (size_t)s->n_pad * 8));
+    CK(cudaMallocAsync(&s->fv_mem, (size_t)s->n_pad * 8, ctx->upload_stream));
     s->node_id = (uint32_t*)s->fv_mem;
     s->fv_pos = (int32_t*)((char*)s->fv_mem + (size_t)s->n_pad * 4);
+  } else {
+    // replacing a FeatureVector: searches already queued on the main stream must have read the old one
+    CK(cudaEventRecord(ctx->upload_done, ctx->stream));
+    CK(cudaStreamWaitEvent(ctx->upload_stream, ctx->upload_done, 0));
   }
-  CK(cudaMemcpyAsync(s->fv_mem, h, (size_t)s->n_pad * 8, cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemcpyAsync(s->fv_mem, h, (size_t)s->n_pad * 8, cudaMemcpyHostToDevice, ctx->upload_stream));
+  CK(cudaEventRecord(ctx->upload_done, ctx->upload_stream));
+  CK(cudaStreamWaitEvent(ctx->stream, ctx->upload_done, 0));
   s->has_fv = true;
   return ASDM_OK;
 }

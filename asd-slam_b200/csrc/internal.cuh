@@ -25,6 +25,9 @@ struct asdm_ctx {
   int device = 0;
   cudaStream_t stream = nullptr;
   bool own_stream = true;
+  // descriptor uploads ride their own stream so the DMA of keyframe k+1 overlaps the pack / grid kernels of keyframe k
+  cudaStream_t upload_stream = nullptr;
+  cudaEvent_t upload_done = nullptr;
   std::recursive_mutex mu;
   std::string err;
   int opt_force_exact = 0;
