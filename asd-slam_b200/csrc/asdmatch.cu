@@ -501,7 +501,7 @@ struct asdm_job {
   std::vector<asdm_set*> sets;  // retained
   std::vector<PairDesc> h_pairs;
   DevBuf d_pairs, d_masks, d_cnt, d_cand, d_owner, d_acc, d_flags, d_match, d_dist, d_nm;
-  DevBuf d_work, d_tmaps, d_list, d_seg_count;
+  DevBuf d_work, d_tmaps, d_list, d_seg_count, d_rb, d_cmin, d_setdesc;
   int cap = 8;
   int use_tc = 0;
   int n_work = 0;
@@ -518,7 +518,8 @@ static void job_free(asdm_job* j) {
   asdm_ctx* ctx = j->ctx;
   cudaSetDevice(ctx->device);
   DevBuf* bufs[] = {&j->d_pairs, &j->d_masks, &j->d_cnt, &j->d_cand, &j->d_owner, &j->d_acc, &j->d_flags,
-                    &j->d_match, &j->d_dist, &j->d_nm, &j->d_work, &j->d_tmaps, &j->d_list, &j->d_seg_count};
+                    &j->d_match, &j->d_dist, &j->d_nm, &j->d_work, &j->d_tmaps, &j->d_list, &j->d_seg_count,
+                    &j->d_rb, &j->d_cmin, &j->d_setdesc};
   for (DevBuf* b : bufs) release(ctx, *b);  // stream-ordered: a run still in flight completes first
   if (j->h_flags_owned) {
     cudaStreamSynchronize(ctx->stream);
@@ -681,6 +682,33 @@ static int job_prepare(asdm_ctx* ctx, const asdm_job_desc* d, int kind_internal,
         if ((rc = stage_upload(ctx, j->d_work.p, work.data(), work.size() * sizeof(TcWork))) ||
             (rc = stage_upload(ctx, j->d_tmaps.p, maps.data(), maps.size())))
           return bail(rc);
+        // per-keyframe filter bounds (k_tc_row_bounds): one launch over all 128-row chunks of all keyframes
+        {
+          std::vector<TcSetDesc> sd((size_t)d->n_kf);
+          std::vector<int32_t> chunk_set;
+          for (int k = 0; k < d->n_kf; k++) {
+            const asdm_set* S = d->sets[k];
+            sd[k] = TcSetDesc{S->norm2, (const uint8_t*)j->d_masks.p + mask_off[k], S->fv_pos, S->n, (int32_t)chunk_set.size()};
+            chunk_set.insert(chunk_set.end(), (size_t)S->n_pad / 128, k);
+          }
+          const size_t nch = chunk_set.size();
+          if ((rc = ensure(ctx, j->d_rb, nch * 128 * sizeof(float))) || (rc = ensure(ctx, j->d_cmin, nch * sizeof(float))) ||
+              (rc = ensure(ctx, j->d_setdesc, sd.size() * sizeof(TcSetDesc) + nch * sizeof(int32_t))))
+            return bail(rc);
+          int32_t* d_chunk_set = (int32_t*)((char*)j->d_setdesc.p + sd.size() * sizeof(TcSetDesc));
+          if ((rc = stage_upload(ctx, j->d_setdesc.p, sd.data(), sd.size() * sizeof(TcSetDesc))) ||
+              (rc = stage_upload(ctx, d_chunk_set, chunk_set.data(), nch * sizeof(int32_t))))
+            return bail(rc);
+          if (asdm_tc_row_bounds_launch(ctx, (const TcSetDesc*)j->d_setdesc.p, d_chunk_set, (int)nch, P.mask_sense,
+                                        (float*)j->d_rb.p, (float*)j->d_cmin.p) != cudaSuccess)
+            return bail(fail(ctx, ASDM_ERR_CUDA, "row-bound launch"));
+          ctx->stat_total_launches++;
+          for (int p = 0; p < d->n_pairs; p++) {
+            PairDesc& pd = j->h_pairs[p];
+            pd.rbA = (const float*)j->d_rb.p + (size_t)sd[pd.setA].chunk0 * 128;
+            pd.cminB = (const float*)j->d_cmin.p + sd[pd.setB].chunk0;
+          }
+        }
         long q = 0;
         for (int p = 0; p < d->n_pairs; p++) q += j->h_pairs[p].nA;
         j->list_cap = (int)std::min<long>((long)1 << 30, std::max<long>(4096, q * ctx->opt_list_cap_per_query));
@@ -720,7 +748,7 @@ static int job_run(asdm_job* j) {
   }
   if (j->use_tc) {
     CK(cudaMemsetAsync(j->d_seg_count.p, 0, (size_t)j->n_seg * sizeof(int32_t), ctx->stream));
-    CK(asdm_tc_shortlist_launch(ctx, pairs, j->d_tmaps.p, (const TcWork*)j->d_work.p, j->n_work, j->P.t_keep, j->P.mask_sense,
+    CK(asdm_tc_shortlist_launch(ctx, pairs, j->d_tmaps.p, (const TcWork*)j->d_work.p, j->n_work, j->P.t_keep,
                                 (TcHit*)j->d_list.p, j->seg_cap, (int32_t*)j->d_seg_count.p, flags + 2));
     LAUNCHED(ctx);
     if (ev1) CK(cudaEventRecord(ev1, ctx->stream));

@@ -97,6 +97,9 @@ struct PairDesc {
   const asdm_kp* kpB;
   int32_t nA, nB;
   int32_t setA, setB;  // index into the job's tensor-map table
+  // tensor-core shortlist gates, precomputed per keyframe by k_tc_row_bounds (tc_shortlist.cu):
+  const float* rbA;    // [n_pad] KAPPA*|a_i|^2 when query i is usable (mask, FeatureVector membership), else +inf
+  const float* cminB;  // [n_pad/128] min over each 128-row chunk of the same bound on the target side
   float F12[9];
   float ex, ey;
 };
@@ -193,6 +196,16 @@ struct TcWork {   // one unit of the persistent tensor-core kernel
 // leaves its count in seg_count[c*EPI_WARPS+e] (a count above seg_cap means that segment overflowed).
 #define ASDM_TC_MAX_EPI_WARPS 8
 cudaError_t asdm_tc_shortlist_launch(asdm_ctx* ctx, const PairDesc* d_pairs, const void* d_tmaps, const TcWork* d_work,
-                                     int n_work, float t_keep, int mask_sense, TcHit* d_list, int seg_cap,
-                                     int32_t* d_seg_count, int32_t* d_list_total);
+                                     int n_work, float t_keep, TcHit* d_list, int seg_cap, int32_t* d_seg_count,
+                                     int32_t* d_list_total);
+// per-keyframe row bounds for the shortlist: one launch over every 128-row chunk of every keyframe of a job
+struct TcSetDesc {
+  const float* norm2;
+  const uint8_t* mask;
+  const int32_t* pos;
+  int32_t n;
+  int32_t chunk0;  // first chunk of this keyframe in rb / cmin
+};
+cudaError_t asdm_tc_row_bounds_launch(asdm_ctx* ctx, const TcSetDesc* d_sets, const int32_t* d_chunk_set, int n_chunks,
+                                      int mask_sense, float* d_rb, float* d_cmin);
 int asdm_tc_build_tmap(asdm_ctx* ctx, asdm_set* set);

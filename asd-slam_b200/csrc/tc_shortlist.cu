@@ -6,8 +6,8 @@
 //   ||a-b||^2 = |a|^2 + |b|^2 - 2 a.b ;  acc = bf16(a).bf16(b) in fp32 ;  |acc - a.b| <= 1.25 * 2^-8 * (|a|^2+|b|^2)
 //   d <= t_keep  =>  acc >= KAPPA*(|a|^2 + |b|^2) - t_keep/2 * (1+1e-4),   KAPPA = 0.495
 //
-// Persistent kernel, one CTA per SM, 6 warps: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane),
-// warps 2..5 = epilogue (one per TMEM lane quarter). A work unit keeps one 256-row tile of set B resident in shared
+// Persistent kernel, one CTA per SM, 10 warps: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane),
+// warps 2..9 = epilogue (two per TMEM lane quarter, 128 columns each). A work unit keeps one 256-row tile of set B resident in shared
 // memory (double buffered across units) and streams 128-row tiles of set A through a 3-stage ring; accumulators are
 // double buffered in TMEM (2 x 256 columns), so the epilogue of tile t overlaps the MMAs of tile t+1.
 // Per tile: 8 x tcgen05.mma 128x256x16 = 8.39 MFLOP; epilogue = 32768 fp32 reads from TMEM, one max per value.
@@ -140,12 +140,33 @@ __device__ __noinline__ int tc_emit_hits(uint32_t mask, int pair, int i, int jba
   return seg_cnt;
 }
 
+// Row / column bounds of the filter, once per keyframe of a job: rb[i] = KAPPA*|x_i|^2 for a usable feature (mask ==
+// mask_sense and present in the FeatureVector), +inf otherwise; cmin[c] = min of rb over the 128-row chunk c. The
+// epilogue then needs ONE independent load per tile (a dependent mask -> pos -> norm chain cost three L2 round
+// trips per tile and kept the tensor pipe at 50 %: profiles/r01d).
+__global__ void __launch_bounds__(128) k_tc_row_bounds(const TcSetDesc* __restrict__ sets,
+                                                       const int32_t* __restrict__ chunk_set, int mask_sense,
+                                                       float* __restrict__ rb, float* __restrict__ cmin) {
+  const TcSetDesc sd = sets[chunk_set[blockIdx.x]];
+  const int i = (blockIdx.x - sd.chunk0) * 128 + threadIdx.x;
+  float v = __int_as_float(0x7f800000);
+  if (i < sd.n && sd.mask[i] == mask_sense && sd.pos[i] >= 0) v = KAPPA * sd.norm2[i];
+  rb[(size_t)blockIdx.x * 128 + threadIdx.x] = v;
+  __shared__ float s_min[4];
+  float m = v;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fminf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0) s_min[threadIdx.x >> 5] = m;
+  __syncthreads();
+  if (threadIdx.x == 0) cmin[blockIdx.x] = fminf(fminf(s_min[0], s_min[1]), fminf(s_min[2], s_min[3]));
+}
+
 // EPI_WARPS = 4 or 8 (with 8, the two warps of a TMEM lane quarter split the 256 columns)
 template <int EPI_WARPS>
 __global__ void __launch_bounds__(64 + 32 * EPI_WARPS, 1)
 k_tc_shortlist(const PairDesc* __restrict__ pairs, const uint8_t* __restrict__ tmaps, const TcWork* __restrict__ work,
-               int n_work, float t_half, int mask_sense, TcHit* __restrict__ list, int seg_cap,
-               int32_t* __restrict__ seg_count, int32_t* __restrict__ list_total) {
+               int n_work, float t_half, TcHit* __restrict__ list, int seg_cap, int32_t* __restrict__ seg_count,
+               int32_t* __restrict__ list_total) {
   constexpr int EPI_COLS = TN / (EPI_WARPS / 4);
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* smB = smem;                  // 2 x 64 KB
@@ -261,32 +282,19 @@ k_tc_shortlist(const PairDesc* __restrict__ pairs, const uint8_t* __restrict__ t
     for (int u = blockIdx.x; u < n_work; u += gridDim.x) {
       const TcWork w = work[u];
       const PairDesc& pd = pairs[w.pair];
-      const int nA = pd.nA, nB = pd.nB;
-      const float* __restrict__ normA = pd.normA;
-      const uint8_t* __restrict__ maskA = pd.maskA;
-      const int32_t* __restrict__ posA = pd.posA;
+      const float* __restrict__ rbA = pd.rbA + (size_t)w.m_tile0 * TM + row;
       const int j0 = w.n_tile * TN + chalf * EPI_COLS;
-      float minb = INF;
-#pragma unroll
-      for (int k = 0; k < EPI_COLS / 32; k++) {
-        const int j = j0 + k * 32 + lane;
-        if (j < nB) minb = fminf(minb, KAPPA * __ldg(pd.normB + j));
-      }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) minb = fminf(minb, __shfl_xor_sync(0xffffffffu, minb, o));
-      const float colb = minb - t_half;  // +inf when the whole column range is padding
-      // row bound of the next tile is fetched one tile ahead, so its global-load latency hides behind this tile
-      auto row_bound = [&](int t) -> float {
-        const int i = (w.m_tile0 + t) * TM + row;
-        float ai = INF;
-        if (t < w.m_tiles && i < nA && maskA[i] == mask_sense && posA[i] >= 0) ai = KAPPA * __ldg(normA + i);
-        return ai;
-      };
-      float ai_next = row_bound(0);
+      const int c0 = j0 >> 7;
+      float minb = __ldg(pd.cminB + c0);
+      if (EPI_COLS == 256) minb = fminf(minb, __ldg(pd.cminB + c0 + 1));
+      const float colb = minb - t_half;  // +inf when no column of the range is usable
+      // the row bound of the next tile is fetched one tile ahead: a single independent load whose latency hides
+      // behind this tile's TMEM reads
+      float ai_next = __ldg(rbA);
       for (int t = 0; t < w.m_tiles; t++) {
         const int i = (w.m_tile0 + t) * TM + row;
         const float thr_row = ai_next + colb;  // +inf for padding / unusable rows
-        ai_next = row_bound(t + 1);
+        ai_next = (t + 1 < w.m_tiles) ? __ldg(rbA + (size_t)(t + 1) * TM) : INF;
         mbar_wait(&bars.t_full[acc], accphase);
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * TN + chalf * EPI_COLS);
@@ -356,10 +364,16 @@ int asdm_tc_build_tmap(asdm_ctx* ctx, asdm_set* set) {
   return ASDM_OK;
 }
 
+cudaError_t asdm_tc_row_bounds_launch(asdm_ctx* ctx, const TcSetDesc* d_sets, const int32_t* d_chunk_set, int n_chunks,
+                                      int mask_sense, float* d_rb, float* d_cmin) {
+  if (n_chunks <= 0) return cudaSuccess;
+  k_tc_row_bounds<<<n_chunks, 128, 0, ctx->stream>>>(d_sets, d_chunk_set, mask_sense, d_rb, d_cmin);
+  return cudaGetLastError();
+}
+
 template <int EPI_WARPS>
 static cudaError_t tc_launch(asdm_ctx* ctx, const PairDesc* d_pairs, const void* d_tmaps, const TcWork* d_work, int n_work,
-                             float t_half, int mask_sense, TcHit* d_list, int seg_cap, int32_t* d_seg_count,
-                             int32_t* d_list_total) {
+                             float t_half, TcHit* d_list, int seg_cap, int32_t* d_seg_count, int32_t* d_list_total) {
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(k_tc_shortlist<EPI_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM);
@@ -368,15 +382,15 @@ static cudaError_t tc_launch(asdm_ctx* ctx, const PairDesc* d_pairs, const void*
   }
   const int grid = n_work < ctx->sm_count ? n_work : ctx->sm_count;
   k_tc_shortlist<EPI_WARPS><<<grid, 64 + 32 * EPI_WARPS, TC_SMEM, ctx->stream>>>(
-      d_pairs, (const uint8_t*)d_tmaps, d_work, n_work, t_half, mask_sense, d_list, seg_cap, d_seg_count, d_list_total);
+      d_pairs, (const uint8_t*)d_tmaps, d_work, n_work, t_half, d_list, seg_cap, d_seg_count, d_list_total);
   return cudaGetLastError();
 }
 
 cudaError_t asdm_tc_shortlist_launch(asdm_ctx* ctx, const PairDesc* d_pairs, const void* d_tmaps, const TcWork* d_work,
-                                     int n_work, float t_keep, int mask_sense, TcHit* d_list, int seg_cap,
-                                     int32_t* d_seg_count, int32_t* d_list_total) {
+                                     int n_work, float t_keep, TcHit* d_list, int seg_cap, int32_t* d_seg_count,
+                                     int32_t* d_list_total) {
   const float t_half = 0.5f * t_keep * 1.0001f + 1e-6f;
   if (ctx->opt_tc_epi_warps == 8)
-    return tc_launch<8>(ctx, d_pairs, d_tmaps, d_work, n_work, t_half, mask_sense, d_list, seg_cap, d_seg_count, d_list_total);
-  return tc_launch<4>(ctx, d_pairs, d_tmaps, d_work, n_work, t_half, mask_sense, d_list, seg_cap, d_seg_count, d_list_total);
+    return tc_launch<8>(ctx, d_pairs, d_tmaps, d_work, n_work, t_half, d_list, seg_cap, d_seg_count, d_list_total);
+  return tc_launch<4>(ctx, d_pairs, d_tmaps, d_work, n_work, t_half, d_list, seg_cap, d_seg_count, d_list_total);
 }

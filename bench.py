@@ -272,9 +272,14 @@ def run_ours(args):
         dist_ms = dist_us * 1e-3 / runs
         if tc_used:
             achieved = flops / (dist_ms * 1e-3) / 1e12
-            roof = {"bound": "tensor", "kernel": "k_tc_shortlist", "achieved": achieved, "peak": pk["bf16"],
-                    "unit": "TFLOP/s", "frac": achieved / pk["bf16"], "traffic": None,
-                    "peak_source": f"{pk['source']} bf16 sustained (kernel timed inside a long step)"}
+            # the timed region is a fraction of a second (clocks stay at boost, no power cap): the burst figure applies
+            long_run = ms * 1e-3 > 2.0
+            peak = pk["bf16"] if long_run else pk["bf16_burst"]
+            roof = {"bound": "tensor", "kernel": "k_tc_shortlist", "achieved": achieved, "peak": peak,
+                    "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
+                    "peak_source": f"{pk['source']} dense bf16 cuBLAS, " + ("sustained (timed region > 2 s)" if long_run else
+                                   "burst (timed region < 2 s at boost clocks)"),
+                    "frac_of_sustained_peak": achieved / pk["bf16"]}
         else:
             achieved = 3.0 * units * 128 / (dist_ms * 1e-3) / 1e12  # sub, mul, add per element on the fp32 pipes
             roof = {"bound": "fp32", "kernel": "k_cand_exact", "achieved": achieved, "peak": None, "unit": "TFLOP/s",
@@ -323,7 +328,7 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--pairs", type=int, default=N_PAIRS, help="keyframe pairs per GPU per step (default: the C5 sweep)")
