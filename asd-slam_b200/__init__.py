@@ -3,11 +3,13 @@ mataiyuan/ASD-SLAM (reference src/vslam/src/ORBmatcher.cc) behind a C ABI (inclu
 
 The directory name carries a hyphen, so import it with
     importlib.import_module("asd-slam_b200")
-(see tests/conftest.py).  `matcher` mirrors the reference's ORBmatcher interface; `synth` builds the seeded
-inputs of the five BASELINE configs.  Importing the package does not load the CUDA library; creating a
+(see tests/conftest.py).  `matcher` mirrors the reference's ORBmatcher interface; `shard` deals batched
+keyframe-pair searches over the ranks of a torch.distributed group; `synth` builds the seeded inputs of the five
+BASELINE configs.  Importing the package does not load the CUDA library; creating a
 `Context` does, and raises when the library or a B200 is missing (no CPU fallback).
 """
 from . import _lib, synth  # noqa: F401
 from ._lib import (ASDM_JOB_BOW_KF_KF, ASDM_JOB_TRIANGULATION, ASDM_PROJ_BEST_ONLY, ASDM_PROJ_RATIO_LEVEL,  # noqa: F401
                    KP_DTYPE, PROJ_QUERY_DTYPE, AsdmError)
 from .matcher import Context, DescriptorSet, ORBmatcher, PairJob  # noqa: F401
+from .shard import PairShards, ShardedPairJob, all_gather_results  # noqa: F401

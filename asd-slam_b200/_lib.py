@@ -57,7 +57,8 @@ class JobDesc(C.Structure):
     _fields_ = [("kind", C.c_int32), ("n_kf", C.c_int32), ("sets", C.POINTER(C.c_void_p)),
                 ("masks", C.POINTER(C.c_void_p)), ("n_pairs", C.c_int32), ("ia", C.c_void_p), ("ib", C.c_void_p),
                 ("nnratio", C.c_float), ("check_ori", C.c_int32), ("F12", C.c_void_p), ("epipoles", C.c_void_p),
-                ("scale_factors", C.c_void_p), ("level_sigma2", C.c_void_p), ("n_levels", C.c_int32)]
+                ("scale_factors", C.c_void_p), ("level_sigma2", C.c_void_p), ("n_levels", C.c_int32),
+                ("row_begin", C.c_void_p), ("row_end", C.c_void_p)]
 
 
 class AsdmError(RuntimeError):

@@ -204,8 +204,14 @@ extern "C" int asdm_set_stream(asdm_ctx* ctx, void* stream) {
   cudaStreamSynchronize(ctx->stream);
   synced(ctx);
   if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
-  ctx->stream = (cudaStream_t)stream;
-  ctx->own_stream = false;
+  if (stream) {
+    ctx->stream = (cudaStream_t)stream;
+    ctx->own_stream = false;
+  } else {  // back to a stream of our own
+    ctx->stream = nullptr;
+    ctx->own_stream = true;
+    CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  }
   return ASDM_OK;
 }
 
@@ -564,6 +570,8 @@ static int job_prepare(asdm_ctx* ctx, const asdm_job_desc* d, int kind_internal,
   if (kind_internal == KIND_TRIANGULATION &&
       (!d->F12 || !d->epipoles || !d->scale_factors || !d->level_sigma2 || d->n_levels <= 0 || d->n_levels > ASDM_MAX_LEVELS))
     return fail(ctx, ASDM_ERR_INVALID, "triangulation job needs F12, epipoles and level tables");
+  if ((d->row_begin || d->row_end) && (kind_internal != KIND_TRIANGULATION || d->check_ori || !d->row_begin || !d->row_end))
+    return fail(ctx, ASDM_ERR_INVALID, "row ranges need both arrays and a triangulation job without rotation check");
   for (int k = 0; k < d->n_kf; k++) {
     const asdm_set* s = d->sets[k];
     if (!s || s->ctx != ctx || !d->masks[k]) return fail(ctx, ASDM_ERR_INVALID, "bad keyframe set / mask");
@@ -639,6 +647,13 @@ static int job_prepare(asdm_ctx* ctx, const asdm_job_desc* d, int kind_internal,
     pd.maskB = (const uint8_t*)j->d_masks.p + mask_off[b];
     pd.kpA = A->kps; pd.kpB = B->kps;
     pd.nA = A->n; pd.nB = B->n;
+    pd.rowA0 = 0; pd.rowA1 = A->n;
+    if (d->row_begin) {
+      if (d->row_begin[p] < 0 || d->row_end[p] < d->row_begin[p] || d->row_end[p] > A->n)
+        return bail(fail(ctx, ASDM_ERR_INVALID, "row range out of bounds"));
+      pd.rowA0 = d->row_begin[p];
+      pd.rowA1 = d->row_end[p];
+    }
     pd.setA = a; pd.setB = b;
     if (kind_internal == KIND_TRIANGULATION) {
       memcpy(pd.F12, d->F12 + 9 * (size_t)p, 9 * sizeof(float));
@@ -661,14 +676,23 @@ static int job_prepare(asdm_ctx* ctx, const asdm_job_desc* d, int kind_internal,
       // work units: one resident 256-row B tile x a run of 128-row A tiles; split runs until the grid is full
       std::vector<TcWork> work;
       long tiles = 0;
-      for (int p = 0; p < d->n_pairs; p++)
-        tiles += (long)((j->h_pairs[p].nB + 255) / 256) * ((j->h_pairs[p].nA + 127) / 128);
+      auto m_range = [&](int p, int& m_lo, int& m_hi) {  // 128-row tiles of set A that hold this unit's query rows
+        m_lo = j->h_pairs[p].rowA0 / 128;
+        m_hi = j->h_pairs[p].rowA1 > j->h_pairs[p].rowA0 ? (j->h_pairs[p].rowA1 + 127) / 128 : m_lo;
+      };
+      for (int p = 0; p < d->n_pairs; p++) {
+        int m_lo, m_hi;
+        m_range(p, m_lo, m_hi);
+        tiles += (long)((j->h_pairs[p].nB + 255) / 256) * (m_hi - m_lo);
+      }
       const long target_units = (long)ctx->sm_count * 4;
       int run = (int)std::max<long>(1, std::min<long>(32, tiles / std::max<long>(1, target_units)));
       for (int p = 0; p < d->n_pairs; p++) {
-        const int nt_n = (j->h_pairs[p].nB + 255) / 256, nt_m = (j->h_pairs[p].nA + 127) / 128;
+        const int nt_n = (j->h_pairs[p].nB + 255) / 256;
+        int m_lo, m_hi;
+        m_range(p, m_lo, m_hi);
         for (int tn = 0; tn < nt_n; tn++)
-          for (int m0 = 0; m0 < nt_m; m0 += run) work.push_back(TcWork{p, tn, m0, std::min(run, nt_m - m0)});
+          for (int m0 = m_lo; m0 < m_hi; m0 += run) work.push_back(TcWork{p, tn, m0, std::min(run, m_hi - m0)});
       }
       bool maps_ok = true;
       for (int k = 0; k < d->n_kf && maps_ok; k++) maps_ok = asdm_tc_build_tmap(ctx, d->sets[k]) == ASDM_OK;

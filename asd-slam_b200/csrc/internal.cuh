@@ -96,7 +96,8 @@ struct PairDesc {
   const asdm_kp* kpA;
   const asdm_kp* kpB;
   int32_t nA, nB;
-  int32_t setA, setB;  // index into the job's tensor-map table
+  int32_t rowA0, rowA1;  // query rows [rowA0, rowA1) of set A belong to this unit (whole set: 0, nA)
+  int32_t setA, setB;    // index into the job's tensor-map table
   // tensor-core shortlist gates, precomputed per keyframe by k_tc_row_bounds (tc_shortlist.cu):
   const float* rbA;    // [n_pad] KAPPA*|a_i|^2 when query i is usable (mask, FeatureVector membership), else +inf
   const float* cminB;  // [n_pad/128] min over each 128-row chunk of the same bound on the target side

@@ -10,7 +10,7 @@
 
 // gate shared by all candidate producers: both features usable and in the same vocabulary node
 __device__ __forceinline__ bool bow_query_ok(const PairDesc& pd, const BowParams& P, int i) {
-  return pd.maskA[i] == P.mask_sense && pd.posA[i] >= 0;
+  return i >= pd.rowA0 && i < pd.rowA1 && pd.maskA[i] == P.mask_sense && pd.posA[i] >= 0;
 }
 __device__ __forceinline__ bool bow_target_ok(const PairDesc& pd, const BowParams& P, int j) {
   return pd.maskB[j] == P.mask_sense && pd.posB[j] >= 0;
@@ -44,7 +44,7 @@ __global__ void __launch_bounds__(256) k_cand_exact(const PairDesc* __restrict__
   const int pair = blockIdx.z;
   const PairDesc& pd = pairs[pair];
   const int i0 = blockIdx.x * CE_TM, j0 = blockIdx.y * CE_TN;
-  if (i0 >= pd.nA || j0 >= pd.nB) return;
+  if (i0 >= pd.rowA1 || i0 + CE_TM <= pd.rowA0 || j0 >= pd.nB) return;
   const int t = threadIdx.x;
   {
     const int row = t & 63, kc = t >> 6;  // consecutive threads take consecutive rows: conflict-free smem stores

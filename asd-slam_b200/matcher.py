@@ -141,7 +141,7 @@ class PairJob:
     LoopClosing.cc:291-318 (kind BOW_KF_KF) and LocalMapping.cc:335-370 (kind TRIANGULATION)."""
 
     def __init__(self, ctx, kind, sets, masks, ia, ib, nnratio=0.6, check_ori=True, F12=None, epipoles=None,
-                 scale_factors=None, level_sigma2=None):
+                 scale_factors=None, level_sigma2=None, row_begin=None, row_end=None):
         self.ctx = ctx
         self.n_pairs = len(ia)
         n_kf = len(sets)
@@ -158,6 +158,9 @@ class PairJob:
             k["sf"], k["ls"] = _f32(scale_factors), _f32(level_sigma2)
             d.F12, d.epipoles, d.scale_factors, d.level_sigma2 = ptr(k["F12"]), ptr(k["ep"]), ptr(k["sf"]), ptr(k["ls"])
             d.n_levels = len(k["sf"])
+        if row_begin is not None:  # row-block units of a pair (triangulation without rotation check only)
+            k["rb"], k["re"] = _i32(row_begin), _i32(row_end)
+            d.row_begin, d.row_end = ptr(k["rb"]), ptr(k["re"])
         h = C.c_void_p()
         ctx.check(ctx.lib.asdm_job_prepare(ctx.h, C.byref(d), C.byref(h)))
         self.h = h

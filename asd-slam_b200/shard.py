@@ -1,0 +1,208 @@
+"""Sharding of batched keyframe-pair searches over GPUs.
+
+The units of the two batched workloads are independent: the loop bodies of LocalMapping.cc:335-370 (one
+SearchForTriangulation per covisible keyframe, "C4") and LoopClosing.cc:291-318 (one SearchByBoW per loop candidate,
+"C5").  Keyframe descriptor sets are replicated on every GPU (about 3 MB per 4000-keypoint keyframe), the units are
+dealt round-robin to the ranks, every rank writes fixed-stride records (int32 index + fp32 distance per query row, one
+count per unit) and ONE all-gather per result array makes the whole batch visible on every rank.  There is no other
+data-path collective.
+
+SearchForTriangulation has no cross-query state (vbMatched2 is never set, ORBmatcher.cc:669-822) and its only caller
+switches the rotation check off (LocalMapping.cc:309), so a pair may also be split into 128-row-aligned query
+row-blocks: 20 covisible pairs become >= 40 units and divide evenly over 8 GPUs.  The BoW searches are greedy and are
+sharded by whole pairs only.
+
+`PairShards` is pure host logic (numpy); `all_gather_results` works on CPU tensors over gloo and on CUDA tensors over
+NCCL; `ShardedPairJob` ties both to the device-resident `PairJob` (zero-copy all-gather of the library's outputs).
+"""
+import numpy as np
+
+from ._lib import ASDM_JOB_TRIANGULATION
+
+
+class PairShards:
+    """Static round-robin partition of (pair, row-block) units over `world` ranks.
+
+    n_rows: number of query rows of each pair (len n_pairs) -- keyframe sizes of sets[ia[p]].
+    blocks_per_pair > 1 splits every pair into that many row blocks whose boundaries are multiples of `align` rows
+    (the tensor-core tile height), so no tile is computed twice.
+    """
+
+    def __init__(self, n_rows, world, blocks_per_pair=1, align=128):
+        n_rows = np.asarray(n_rows, dtype=np.int64).reshape(-1)
+        self.n_pairs = len(n_rows)
+        self.world = int(world)
+        assert self.world >= 1 and blocks_per_pair >= 1
+        up, r0, r1 = [], [], []
+        for p, n in enumerate(n_rows):
+            tiles = -(-int(n) // align)
+            nb = max(1, min(blocks_per_pair, tiles))
+            cuts = [(tiles * b // nb) * align for b in range(nb)] + [int(n)]
+            for b in range(nb):
+                up.append(p)
+                r0.append(min(cuts[b], int(n)))
+                r1.append(min(cuts[b + 1], int(n)))
+        self.unit_pair = np.asarray(up, np.int32)
+        self.unit_r0 = np.asarray(r0, np.int32)
+        self.unit_r1 = np.asarray(r1, np.int32)
+        self.n_units = len(up)
+        self.per_rank = -(-self.n_units // self.world) if self.n_units else 0
+        self.split_rows = blocks_per_pair > 1
+
+    def local_units(self, rank):
+        """Global unit ids owned by `rank`, in local order (unit u lives at rank u % world, slot u // world)."""
+        return np.arange(rank, self.n_units, self.world, dtype=np.int64)
+
+    def merge(self, g_match, g_dist, g_nm):
+        """Rank-major gathered records -> per-pair results.
+
+        g_match, g_dist: [world, per_rank, stride]; g_nm: [world, per_rank].  Returns (nm[n_pairs], match[n_pairs,
+        stride], dist[n_pairs, stride]) exactly as a single un-sharded job over all pairs would report them.
+        """
+        g_match = np.asarray(g_match).reshape(self.world, self.per_rank, -1)
+        g_dist = np.asarray(g_dist).reshape(self.world, self.per_rank, -1)
+        g_nm = np.asarray(g_nm).reshape(self.world, self.per_rank)
+        stride = g_match.shape[2]
+        match = np.full((self.n_pairs, stride), -1, np.int32)
+        dist = np.full((self.n_pairs, stride), -1.0, np.float32)
+        nm = np.zeros(self.n_pairs, np.int32)
+        for u in range(self.n_units):
+            r, s, p = u % self.world, u // self.world, self.unit_pair[u]
+            a, b = (int(self.unit_r0[u]), int(self.unit_r1[u])) if self.split_rows else (0, stride)
+            match[p, a:b] = g_match[r, s, a:b]
+            dist[p, a:b] = g_dist[r, s, a:b]
+            nm[p] += g_nm[r, s]
+        return nm, match, dist
+
+
+def all_gather_results(local, per_rank, group=None, out=None):
+    """All-gathers one fixed-stride record array.  local: torch tensor [n_local, ...] (CPU over gloo, CUDA over NCCL),
+    n_local <= per_rank (ragged tails are padded with -1).  Returns a tensor [world, per_rank, ...] on every rank."""
+    import torch
+    import torch.distributed as dist
+
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if local.shape[0] != per_rank:
+        padded = torch.full((per_rank,) + tuple(local.shape[1:]), -1, dtype=local.dtype, device=local.device)
+        padded[:local.shape[0]] = local
+        local = padded
+    local = local.contiguous()
+    if out is None:
+        out = torch.empty((world,) + tuple(local.shape), dtype=local.dtype, device=local.device)
+    if world == 1:
+        out[0].copy_(local)
+    else:
+        dist.all_gather_into_tensor(out.view(-1), local.view(-1), group=group)
+    return out
+
+
+class _DevArray:
+    """Exposes a raw device pointer of the library to torch (zero copy)."""
+
+    def __init__(self, p, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(p), False), "version": 2}
+
+
+class ShardedPairJob:
+    """A batched keyframe-pair search whose units are dealt over the ranks of a torch.distributed group.
+
+    Every rank passes the SAME global description (sets replicated on its own GPU, the same ia / ib / F12 / epipoles);
+    the rank prepares a device-resident PairJob for its own units only.  run() launches the local kernels, gather()
+    queues the all-gathers behind them on the context's stream (NCCL over NVLink), fetch() returns the merged per-pair
+    results on the host.
+    """
+
+    def __init__(self, ctx, kind, sets, masks, ia, ib, nnratio=0.6, check_ori=True, F12=None, epipoles=None,
+                 scale_factors=None, level_sigma2=None, rank=0, world=1, group=None, blocks_per_pair=1):
+        import torch
+        from .matcher import PairJob
+
+        ia, ib = np.asarray(ia, np.int32), np.asarray(ib, np.int32)
+        if blocks_per_pair > 1 and (kind != ASDM_JOB_TRIANGULATION or check_ori):
+            raise ValueError("row-block units need a triangulation job without rotation check")
+        self.ctx, self.rank, self.world, self.group = ctx, rank, world, group
+        self.shards = PairShards([sets[a].n for a in ia], world, blocks_per_pair)
+        mine = self.shards.local_units(rank)
+        up = self.shards.unit_pair[mine]
+        kw = {}
+        if kind == ASDM_JOB_TRIANGULATION:
+            kw = dict(F12=np.asarray(F12, np.float32).reshape(-1, 9)[up], epipoles=np.asarray(epipoles, np.float32).reshape(-1, 2)[up],
+                      scale_factors=scale_factors, level_sigma2=level_sigma2)
+            if blocks_per_pair > 1:
+                kw.update(row_begin=self.shards.unit_r0[mine], row_end=self.shards.unit_r1[mine])
+        self.job = PairJob(ctx, kind, sets, masks, ia[up], ib[up], nnratio, check_ori, **kw)
+        self.n_local = len(mine)
+        # one stride for every rank: the largest query set of the batch (jobs size theirs from their own units)
+        self.stride = max([sets[a].n for a in ia], default=1)
+        assert self.job.stride <= self.stride
+        dev = torch.device("cuda", ctx.device)
+        self._torch = torch
+        pr = self.shards.per_rank
+        self.g_match = torch.empty((world, pr, self.stride), dtype=torch.int32, device=dev)
+        self.g_dist = torch.empty((world, pr, self.stride), dtype=torch.float32, device=dev)
+        self.g_nm = torch.empty((world, pr), dtype=torch.int32, device=dev)
+        self._direct = self.n_local == pr and self.job.stride == self.stride and pr > 0
+        if self._direct:
+            pm, pd_, pn = self.job.device_outputs()
+            self.l_match = torch.as_tensor(_DevArray(pm, (pr, self.stride), "<i4"), device=dev)
+            self.l_dist = torch.as_tensor(_DevArray(pd_, (pr, self.stride), "<f4"), device=dev)
+            self.l_nm = torch.as_tensor(_DevArray(pn, (pr,), "<i4"), device=dev)
+
+    def run(self):
+        self.job.run()
+
+    def settle(self):
+        self.job.settle()
+
+    def _locals(self):
+        if self._direct:
+            return self.l_match, self.l_dist, self.l_nm
+        torch = self._torch
+        dev = self.g_match.device
+        m = torch.full((self.n_local, self.stride), -1, dtype=torch.int32, device=dev)
+        d = torch.full((self.n_local, self.stride), -1.0, dtype=torch.float32, device=dev)
+        n = torch.zeros((self.n_local,), dtype=torch.int32, device=dev)
+        if self.n_local:
+            pm, pd_, pn = self.job.device_outputs()
+            js = self.job.stride
+            m[:, :js] = torch.as_tensor(_DevArray(pm, (self.n_local, js), "<i4"), device=dev)
+            d[:, :js] = torch.as_tensor(_DevArray(pd_, (self.n_local, js), "<f4"), device=dev)
+            n.copy_(torch.as_tensor(_DevArray(pn, (self.n_local,), "<i4"), device=dev))
+        return m, d, n
+
+    def _stream(self):
+        p = self.ctx.stream()
+        if getattr(self, "_ext", None) is None or self._ext[0] != p:
+            self._ext = (p, self._torch.cuda.ExternalStream(p, device=self.g_match.device))
+        return self._ext[1]
+
+    def gather(self):
+        """Queues the all-gathers on the stream the job ran on (set with Context.set_stream to a torch stream)."""
+        torch = self._torch
+        with torch.cuda.stream(self._stream()):
+            m, d, n = self._locals()
+            pr = self.shards.per_rank
+            all_gather_results(m, pr, self.group, self.g_match)
+            all_gather_results(d, pr, self.group, self.g_dist)
+            all_gather_results(n, pr, self.group, self.g_nm)
+
+    def fetch(self):
+        """Merged per-pair results on the host (every rank gets the whole batch)."""
+        self.job.settle()
+        self.gather()
+        self.ctx.synchronize()
+        return self.shards.merge(self.g_match.cpu().numpy(), self.g_dist.cpu().numpy(), self.g_nm.cpu().numpy())
+
+    def fetch_gathered(self, h_match, h_dist, h_nm):
+        """gather() + device->host copies of the rank-major records into caller-provided pinned torch tensors
+        ([world, per_rank, stride] / [world, per_rank]); `shards.merge` turns them into per-pair results."""
+        self.job.settle()
+        self.gather()
+        with self._torch.cuda.stream(self._stream()):
+            h_match.copy_(self.g_match, non_blocking=True)
+            h_dist.copy_(self.g_dist, non_blocking=True)
+            h_nm.copy_(self.g_nm, non_blocking=True)
+        self.ctx.synchronize()
+
+    def destroy(self):
+        self.job.destroy()

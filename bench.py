@@ -10,8 +10,9 @@ A "step" is one pass of the whole sweep.  Metric: descriptor pairs / s (= pairs 
   python bench.py --impl reference ...                            the reference's CPU matcher (oracle port) timed
                                                                    on the host cores, same metric / config
 
-N>1 is weak scaling: every rank owns its own 512-pair shard of an N*512-pair sweep over the same 64 keyframes
-(replicated on each GPU), and the match lists are all-gathered over NCCL at the end of every step.
+N>1 is weak scaling: an N*512-pair sweep over the same 64 keyframes (replicated on each GPU) is dealt round-robin
+to the ranks by asd-slam_b200/shard.py (512 pairs each, no data-path collective), and the match lists are all-gathered
+over NCCL at the end of every step.
 """
 import argparse
 import importlib
@@ -54,6 +55,19 @@ def make_inputs(pkg, rank, n=N_DESC, n_kf=N_KF, n_pairs=N_PAIRS):
         ia = rng.integers(0, n_kf, n_pairs).astype(np.int32)
         c["ia"], c["ib"] = ia, ((ia + 1 + rng.integers(0, n_kf - 1, n_pairs)) % n_kf).astype(np.int32)
     return c
+
+
+def global_sweep(pkg, world, n_pairs):
+    """The world*n_pairs candidate pairs of the whole job, interleaved so that the round-robin deal of shard.py hands
+    rank r exactly make_inputs(rank=r)'s pairs (rank 0's shard is the N=1 workload)."""
+    c = make_inputs(pkg, 0, n_pairs=n_pairs)
+    ia = np.empty(world * n_pairs, np.int32)
+    ib = np.empty(world * n_pairs, np.int32)
+    ia[0::world], ib[0::world] = c["ia"], c["ib"]
+    for r in range(1, world):
+        cr = make_inputs(pkg, r, n_pairs=n_pairs)
+        ia[r::world], ib[r::world] = cr["ia"], cr["ib"]
+    return c, ia, ib
 
 
 class ClockSampler:
@@ -100,13 +114,6 @@ class ClockSampler:
                     reasons.add(nme)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": float(max(mx)) if mx else None,
                 "power_w_max": float(max(power)) if power else None, "samples": len(inside), "reasons": sorted(reasons)}
-
-
-class DevArray:
-    """Exposes a raw device pointer of the library to torch (zero copy) for the NCCL all-gather."""
-
-    def __init__(self, p, shape, typestr):
-        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(p), False), "version": 2}
 
 
 # --------------------------------------------------------------------------------------------- CPU arms
@@ -173,28 +180,20 @@ def run_ours(args):
     if args.epi_warps:
         ctx.set_option("tc_epi_warps", args.epi_warps)
     n, P = N_DESC, args.pairs
-    c = make_inputs(pkg, rank, n_pairs=P)
+    c, g_ia, g_ib = global_sweep(pkg, world, P)  # every rank describes the whole job; shard.py deals the units
     kfs = c["kfs"]
 
     # ---- resident inputs (device-only arm): keyframe sets uploaded once, as the SLAM system would at KF creation
     sets = [pkg.DescriptorSet(ctx, k["desc"], k["kps"], c["grid"], k["fv"]) for k in kfs]
     masks = [k["valid"] for k in kfs]
-    job = pkg.PairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, sets, masks, c["ia"], c["ib"], c["nnratio"], c["check_ori"])
+    job = pkg.ShardedPairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, sets, masks, g_ia, g_ib, c["nnratio"], c["check_ori"],
+                             rank=rank, world=world)
     S = job.stride
-    gathered = None
-    if world > 1:
-        pm, pd_, pn = job.device_outputs()
-        t_match = torch.as_tensor(DevArray(pm, (P * S,), "<i4"), device=f"cuda:{local}")
-        t_dist = torch.as_tensor(DevArray(pd_, (P * S,), "<f4"), device=f"cuda:{local}")
-        gathered = (torch.empty(world * P * S, dtype=torch.int32, device=f"cuda:{local}"),
-                    torch.empty(world * P * S, dtype=torch.float32, device=f"cuda:{local}"))
 
     def step():
         job.run()
         if world > 1:  # results of all shards on every rank (north_star: NCCL all-gather over NVLink)
-            with torch.cuda.stream(stream):
-                dist.all_gather_into_tensor(gathered[0], t_match)
-                dist.all_gather_into_tensor(gathered[1], t_dist)
+            job.gather()
 
     for _ in range(max(args.warmup, 3)):
         step()
@@ -227,20 +226,32 @@ def run_ours(args):
     ctx.set_option("time_kernels", 0)
     job.settle()
     assert ctx.stat("retries") == 0, "a candidate pool overflowed inside the timed region"
-    nm, match, _ = job.fetch()
+    shortlist_hits = ctx.stat("tc_pairs")
+    nm, match, _ = job.fetch()  # merged: all world*P pairs, in global order
 
     # ---- e2e arm: the reference-facing call with HOST buffers -- upload the 64 keyframes from pinned host memory,
     # attach FeatureVectors, prepare the job, run, and read the match lists back, every step
     h_desc = [ctx.pinned((n, 128), np.float32) for _ in kfs]
     for h, k in zip(h_desc, kfs):
         h[...] = k["desc"]
-    h_match, h_dist, h_nm = ctx.pinned((P, S), np.int32), ctx.pinned((P, S), np.float32), ctx.pinned((P,), np.int32)
+    if world == 1:
+        h_match, h_dist, h_nm = ctx.pinned((P, S), np.int32), ctx.pinned((P, S), np.float32), ctx.pinned((P,), np.int32)
+    else:  # rank-major gathered records of the whole job
+        h_match = torch.empty((world, P, S), dtype=torch.int32).pin_memory()
+        h_dist = torch.empty((world, P, S), dtype=torch.float32).pin_memory()
+        h_nm = torch.empty((world, P), dtype=torch.int32).pin_memory()
 
     def e2e_step():
         ss = [pkg.DescriptorSet(ctx, h, k["kps"], c["grid"], k["fv"], async_upload=True) for h, k in zip(h_desc, kfs)]
-        jb = pkg.PairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, ss, masks, c["ia"], c["ib"], c["nnratio"], c["check_ori"])
-        jb.run()
-        jb.fetch(h_match, h_dist, h_nm)
+        if world == 1:
+            jb = pkg.PairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, ss, masks, g_ia, g_ib, c["nnratio"], c["check_ori"])
+            jb.run()
+            jb.fetch(h_match, h_dist, h_nm)
+        else:
+            jb = pkg.ShardedPairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, ss, masks, g_ia, g_ib, c["nnratio"], c["check_ori"],
+                                    rank=rank, world=world)
+            jb.run()
+            jb.fetch_gathered(h_match, h_dist, h_nm)
         jb.destroy()
         for s_ in ss:
             s_.release()
@@ -259,9 +270,14 @@ def run_ours(args):
         t = torch.tensor([e2e_ms], device=f"cuda:{local}")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
-    assert np.array_equal(h_match, match), "e2e results differ from the resident-input results"
+    if world == 1:
+        e2e_same = np.array_equal(h_match, match)
+    else:
+        e2e_same = np.array_equal(job.shards.merge(h_match.numpy(), h_dist.numpy(), h_nm.numpy())[1], match)
+    assert e2e_same, "e2e results differ from the resident-input results"
     h2d = sum(k["desc"].nbytes + k["kps"].nbytes + 8 * len(k["kps"]) + len(k["valid"]) for k in kfs) + 8 * P
-    d2h = h_match.nbytes + h_dist.nbytes + h_nm.nbytes
+    d2h = (h_match.nbytes + h_dist.nbytes + h_nm.nbytes) if world == 1 else \
+        (h_match.numel() + h_dist.numel() + h_nm.numel()) * 4
 
     if rank == 0:
         pk = peaks()
@@ -292,7 +308,7 @@ def run_ours(args):
         import oracle_py as oracle  # cpu_baseline leg only
         oracle.build()
         threads = oracle.max_threads()
-        c0 = c
+        c0 = dict(c, ia=g_ia, ib=g_ib)  # the first pairs of the GLOBAL sweep: at N>1 they belong to different ranks
         cpu_pairs = int(min(P, max(threads, 8)))
         dtc, onm, omatch = cpu_sample(oracle, c0, cpu_pairs, threads)
         if dtc < 5.0:
@@ -305,7 +321,9 @@ def run_ours(args):
                "dtype": "f32", "data": "synthetic",
                "config": {"workload": WORKLOAD, "pairs_per_gpu": P, "descriptors_per_keyframe": n,
                           "l2": "inputs larger than L2 (197 MB of descriptors + candidate pools vs 126 MB); no flush",
-                          "tensor_core_shortlist": bool(tc_used)},
+                          "tensor_core_shortlist": bool(tc_used), "shortlist_hits_per_step": int(shortlist_hits),
+                          "sharding": "round-robin pairs over ranks, NCCL all-gather of match/dist/count records"
+                                      if world > 1 else "single GPU"},
                "keyframe_pairs_per_sec": world * P * args.steps / (ms * 1e-3),
                "e2e": {"value": world * units / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                        "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms,
@@ -313,7 +331,7 @@ def run_ours(args):
                "gpu_launches": int(launches_per_step * args.steps),
                "roofline": roof,
                "cpu_baseline": {"value": cpu_val, "unit": UNIT, "cores": threads, "kind": "port",
-                                "sample": f"first {cpu_pairs} of the {P} keyframe pairs, {threads} OpenMP threads over pairs",
+                                "sample": f"first {cpu_pairs} of the {world * P} keyframe pairs, {threads} OpenMP threads over pairs",
                                 "parity_on_sample": parity},
                "clocks": clocks}
         print(json.dumps(out), flush=True)

@@ -80,7 +80,8 @@ int asdm_destroy(asdm_ctx* ctx);
 const char* asdm_last_error(const asdm_ctx* ctx);
 void* asdm_stream(asdm_ctx* ctx); /* the context's cudaStream_t, for event timing by the caller */
 int asdm_synchronize(asdm_ctx* ctx);
-/* run on a caller-owned cudaStream_t instead (e.g. the stream an NCCL all-gather of the results is queued on) */
+/* run on a caller-owned cudaStream_t instead (e.g. the stream an NCCL all-gather of the results is queued on);
+ * NULL switches back to a stream owned by the context */
 int asdm_set_stream(asdm_ctx* ctx, void* stream);
 /* page-locked host memory for inputs / results, so that the copies inside the calls are true async DMA */
 int asdm_host_alloc(void** out, size_t bytes);
@@ -220,6 +221,12 @@ typedef struct {
   const float* scale_factors;   /* triangulation: n_levels */
   const float* level_sigma2;    /* triangulation: n_levels */
   int32_t n_levels;
+  /* Optional (NULL = whole keyframe): pair p only searches query rows [row_begin[p], row_end[p]) of sets[ia[p]], so a
+   * pair can be split into row-block units across GPUs. Triangulation with check_ori == 0 only: that search has no
+   * cross-query state (vbMatched2 is never set, ORBmatcher.cc:669-822), the BoW searches are greedy and the rotation
+   * histogram is per pair. Rows outside the range come back as -1. Multiples of 128 avoid wasted tensor-core tiles. */
+  const int32_t* row_begin;
+  const int32_t* row_end;
 } asdm_job_desc;
 
 int asdm_job_prepare(asdm_ctx* ctx, const asdm_job_desc* desc, asdm_job** out);
