@@ -370,7 +370,15 @@ static int set_create_impl(asdm_ctx* ctx, const float* desc, int n, int row_stri
       if (rc) return bail(rc);
     }
   }
+  // `desc` may also be device memory (e.g. keyframes replicated over NVLink by an all-gather that the caller queued on
+  // the context stream): that copy is ordered on the context stream instead.
+  bool desc_on_device = false;
   if (n > 0) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, desc) == cudaSuccess) desc_on_device = at.type == cudaMemoryTypeDevice;
+    else cudaGetLastError();
+  }
+  if (n > 0 && !desc_on_device) {
     // descriptors are DMA'd straight from the caller's buffer (true async when it is page-locked)
     if (row_stride_bytes == (int)(ASDM_DESC_DIM * sizeof(float)))
       CKS(cudaMemcpyAsync(s->desc, desc, (size_t)n * ASDM_DESC_DIM * sizeof(float), cudaMemcpyHostToDevice,
@@ -381,6 +389,9 @@ static int set_create_impl(asdm_ctx* ctx, const float* desc, int n, int row_stri
   }
   CKS(cudaEventRecord(ctx->upload_done, ctx->upload_stream));
   CKS(cudaStreamWaitEvent(ctx->stream, ctx->upload_done, 0));  // everything below is ordered after the upload
+  if (n > 0 && desc_on_device)
+    CKS(cudaMemcpy2DAsync(s->desc, ASDM_DESC_DIM * sizeof(float), desc, row_stride_bytes, ASDM_DESC_DIM * sizeof(float), n,
+                          cudaMemcpyDeviceToDevice, ctx->stream));
   CKS(cudaMemsetAsync(s->d_flags, 0, 256, ctx->stream));
   if (s->n_pad > n)
     CKS(cudaMemsetAsync(s->desc + (size_t)n * ASDM_DESC_DIM, 0, (size_t)(s->n_pad - n) * ASDM_DESC_DIM * sizeof(float),

@@ -96,9 +96,16 @@ class DescriptorSet:
         """async_upload: asdm_set_create_async -- `desc` must stay alive and unmodified until the next synchronising
         call on the context (use Context.pinned() memory for a true async DMA)."""
         self.ctx = ctx
-        desc = _f32(desc)
-        assert desc.ndim == 2 and desc.shape[1] == 128
-        self.n = desc.shape[0]
+        dev_ptr = None
+        if hasattr(desc, "__cuda_array_interface__"):  # device-resident rows (e.g. a torch CUDA tensor): D2D, stream-ordered
+            cai = desc.__cuda_array_interface__
+            assert cai["typestr"] == "<f4" and len(cai["shape"]) == 2 and cai["shape"][1] == 128 and not cai.get("strides")
+            dev_ptr, self.n = C.c_void_p(cai["data"][0]), int(cai["shape"][0])
+            async_upload = True
+        else:
+            desc = _f32(desc)
+            assert desc.ndim == 2 and desc.shape[1] == 128
+            self.n = desc.shape[0]
         g = None
         if grid is not None:
             g = grid if isinstance(grid, Grid) else Grid(*grid)
@@ -108,7 +115,7 @@ class DescriptorSet:
         h = C.c_void_p()
         create = ctx.lib.asdm_set_create_async if async_upload else ctx.lib.asdm_set_create
         self._desc_keepalive = desc if async_upload else None
-        ctx.check(create(ctx.h, ptr(desc), self.n, 0, ptr(kps) if kps is not None else None,
+        ctx.check(create(ctx.h, dev_ptr if dev_ptr is not None else ptr(desc), self.n, 0, ptr(kps) if kps is not None else None,
                          C.byref(g) if g is not None else None, C.byref(h)))
         self.h = h
         if featvec is not None:

@@ -96,6 +96,44 @@ def all_gather_results(local, per_rank, group=None, out=None):
     return out
 
 
+class ReplicatedDescriptors:
+    """Keyframe descriptors replicated on every GPU of the group ("replicate each keyframe's device
+    descriptor set to all GPUs once at keyframe creation") without sending them N times over PCIe: rank r uploads the
+    keyframes k = r (mod world) from its pinned host buffers, one all-gather over NVLink hands every rank all of them.
+    `rows(k)` is then a device view to create the local DescriptorSet from (device-to-device, stream-ordered).
+    """
+
+    def __init__(self, ctx, n_kf, n_max, rank=0, world=1, group=None):
+        import torch
+        self._torch, self.ctx, self.rank, self.world, self.group = torch, ctx, rank, world, group
+        self.n_kf, self.n_max = n_kf, n_max
+        self.per_rank = -(-n_kf // world)
+        dev = torch.device("cuda", ctx.device)
+        self.slab = torch.zeros((world, self.per_rank, n_max, 128), dtype=torch.float32, device=dev)
+        self.mine = torch.zeros((self.per_rank, n_max, 128), dtype=torch.float32, device=dev) if world > 1 else self.slab[0]
+        self._ext = None
+
+    def _stream(self):
+        p = self.ctx.stream()
+        if self._ext is None or self._ext[0] != p:
+            self._ext = (p, self._torch.cuda.ExternalStream(p, device=self.slab.device))
+        return self._ext[1]
+
+    def upload(self, h_desc):
+        """h_desc[k]: pinned host torch tensor [n_k, 128] fp32 of keyframe k (only this rank's are read).  Queued on
+        the context stream: H2D of the local keyframes, then the NVLink all-gather."""
+        torch = self._torch
+        with torch.cuda.stream(self._stream()):
+            for k in range(self.rank, self.n_kf, self.world):
+                self.mine[k // self.world, :h_desc[k].shape[0]].copy_(h_desc[k], non_blocking=True)
+            if self.world > 1:
+                import torch.distributed as dist
+                dist.all_gather_into_tensor(self.slab.view(-1), self.mine.view(-1), group=self.group)
+
+    def rows(self, k, n):
+        return self.slab[k % self.world, k // self.world, :n]
+
+
 class _DevArray:
     """Exposes a raw device pointer of the library to torch (zero copy)."""
 
@@ -195,12 +233,16 @@ class ShardedPairJob:
 
     def fetch_gathered(self, h_match, h_dist, h_nm):
         """gather() + device->host copies of the rank-major records into caller-provided pinned torch tensors
-        ([world, per_rank, stride] / [world, per_rank]); `shards.merge` turns them into per-pair results."""
+        ([world, per_rank, stride] / [world, per_rank]); `shards.merge` turns them into per-pair results.
+        h_match / h_dist may be None on ranks whose host only needs the per-pair counts (worker ranks: the match lists
+        stay on the GPU, the consumer process reads them on its own rank)."""
         self.job.settle()
         self.gather()
         with self._torch.cuda.stream(self._stream()):
-            h_match.copy_(self.g_match, non_blocking=True)
-            h_dist.copy_(self.g_dist, non_blocking=True)
+            if h_match is not None:
+                h_match.copy_(self.g_match, non_blocking=True)
+            if h_dist is not None:
+                h_dist.copy_(self.g_dist, non_blocking=True)
             h_nm.copy_(self.g_nm, non_blocking=True)
         self.ctx.synchronize()
 

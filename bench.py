@@ -231,23 +231,31 @@ def run_ours(args):
 
     # ---- e2e arm: the reference-facing call with HOST buffers -- upload the 64 keyframes from pinned host memory,
     # attach FeatureVectors, prepare the job, run, and read the match lists back, every step
-    h_desc = [ctx.pinned((n, 128), np.float32) for _ in kfs]
+    # N>1: every keyframe crosses PCIe once (rank k % N uploads keyframe k) and is replicated over NVLink by one
+    # all-gather; rank 0 -- the GPU of the SLAM process that consumes the loop candidates -- reads back the match
+    # lists of the whole job, the worker ranks only the per-pair counts.
+    h_desc_t = [torch.empty((n, 128), dtype=torch.float32).pin_memory() for _ in kfs]
+    h_desc = [t.numpy() for t in h_desc_t]
     for h, k in zip(h_desc, kfs):
         h[...] = k["desc"]
     if world == 1:
         h_match, h_dist, h_nm = ctx.pinned((P, S), np.int32), ctx.pinned((P, S), np.float32), ctx.pinned((P,), np.int32)
+        rep_desc = None
     else:  # rank-major gathered records of the whole job
-        h_match = torch.empty((world, P, S), dtype=torch.int32).pin_memory()
-        h_dist = torch.empty((world, P, S), dtype=torch.float32).pin_memory()
+        h_match = torch.empty((world, P, S), dtype=torch.int32).pin_memory() if rank == 0 else None
+        h_dist = torch.empty((world, P, S), dtype=torch.float32).pin_memory() if rank == 0 else None
         h_nm = torch.empty((world, P), dtype=torch.int32).pin_memory()
+        rep_desc = pkg.ReplicatedDescriptors(ctx, len(kfs), n, rank, world)
 
     def e2e_step():
-        ss = [pkg.DescriptorSet(ctx, h, k["kps"], c["grid"], k["fv"], async_upload=True) for h, k in zip(h_desc, kfs)]
         if world == 1:
+            ss = [pkg.DescriptorSet(ctx, h, k["kps"], c["grid"], k["fv"], async_upload=True) for h, k in zip(h_desc, kfs)]
             jb = pkg.PairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, ss, masks, g_ia, g_ib, c["nnratio"], c["check_ori"])
             jb.run()
             jb.fetch(h_match, h_dist, h_nm)
         else:
+            rep_desc.upload(h_desc_t)
+            ss = [pkg.DescriptorSet(ctx, rep_desc.rows(i, n), k["kps"], c["grid"], k["fv"]) for i, k in enumerate(kfs)]
             jb = pkg.ShardedPairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, ss, masks, g_ia, g_ib, c["nnratio"], c["check_ori"],
                                     rank=rank, world=world)
             jb.run()
@@ -272,12 +280,17 @@ def run_ours(args):
         e2e_ms = float(t.item())
     if world == 1:
         e2e_same = np.array_equal(h_match, match)
-    else:
+    elif rank == 0:
         e2e_same = np.array_equal(job.shards.merge(h_match.numpy(), h_dist.numpy(), h_nm.numpy())[1], match)
+    else:
+        e2e_same = np.array_equal(job.shards.merge(np.zeros((world, P, 1), np.int32), np.zeros((world, P, 1), np.float32),
+                                                   h_nm.numpy())[0], nm)
     assert e2e_same, "e2e results differ from the resident-input results"
-    h2d = sum(k["desc"].nbytes + k["kps"].nbytes + 8 * len(k["kps"]) + len(k["valid"]) for k in kfs) + 8 * P
-    d2h = (h_match.nbytes + h_dist.nbytes + h_nm.nbytes) if world == 1 else \
-        (h_match.numel() + h_dist.numel() + h_nm.numel()) * 4
+    # whole-job bytes per step: descriptors cross PCIe once in total; keypoints, FeatureVectors, masks and pair lists
+    # go to every rank; rank 0 reads all match lists back, the other ranks the counts
+    side = sum(k["kps"].nbytes + 8 * len(k["kps"]) + len(k["valid"]) for k in kfs) + 8 * P
+    h2d = sum(k["desc"].nbytes for k in kfs) + world * side
+    d2h = world * P * S * 8 + world * (world * P * 4)
 
     if rank == 0:
         pk = peaks()
@@ -327,7 +340,10 @@ def run_ours(args):
                "keyframe_pairs_per_sec": world * P * args.steps / (ms * 1e-3),
                "e2e": {"value": world * units / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                        "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms,
-                       "what": "asdm_set_create_async x64 (pinned host descriptors) + featvec + job prepare/run/fetch per step"},
+                       "what": "asdm_set_create_async x64 (pinned host descriptors) + featvec + job prepare/run/fetch per step"
+                               if world == 1 else
+                               "per step: each keyframe uploaded once (rank k%N) + NVLink all-gather of descriptors, 64 device-"
+                               "side set creates per rank, sharded job, NCCL all-gather of results, rank 0 reads all match lists"},
                "gpu_launches": int(launches_per_step * args.steps),
                "roofline": roof,
                "cpu_baseline": {"value": cpu_val, "unit": UNIT, "cores": threads, "kind": "port",

@@ -99,6 +99,9 @@ int asdm_get_stat(asdm_ctx* ctx, const char* key, int64_t* value);
  * (Frame.cc:47, KeyFrame.cc:153) retain instead of re-uploading. */
 int asdm_set_create(asdm_ctx* ctx, const float* desc, int n, int row_stride_bytes, const asdm_kp* kps,
                     const asdm_grid* grid, asdm_set** out);
+/* `desc` may also point to memory of the context's device (descriptors produced on the GPU, or keyframes replicated
+ * to every GPU over NVLink by an all-gather): the rows are then copied device-to-device, ordered on the context
+ * stream, so the producer must have been queued on that stream (asdm_set_stream). kps stay host pointers. */
 /* Same, but returns without waiting for the descriptor upload: `desc` must stay valid and unmodified until the next
  * call on this context that synchronises (asdm_synchronize, any search / fetch that returns results). kps / grid are
  * staged and may be reused at once. With page-locked `desc` (asdm_host_alloc) the copy is a true async DMA, so the

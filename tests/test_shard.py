@@ -226,3 +226,33 @@ def test_sharded_job_world1(pkg, ctx, oracle, kind):
     finally:
         ctx.synchronize()
         ctx.set_stream(None)
+
+
+@pytest.mark.gpu
+def test_sets_from_replicated_device_rows(pkg, ctx, oracle):
+    """Keyframes uploaded into a device slab (ReplicatedDescriptors, world 1) and turned into sets device-to-device
+    behave exactly like sets uploaded from the host."""
+    import torch
+    stream = torch.cuda.Stream()
+    ctx.set_stream(stream.cuda_stream)
+    try:
+        n = 600
+        c = pkg.synth.config5(n=n, n_pairs=4, n_kf=3)
+        kfs = c["kfs"]
+        h = [torch.from_numpy(k["desc"]).pin_memory() for k in kfs]
+        rep = pkg.ReplicatedDescriptors(ctx, len(kfs), n)
+        rep.upload(h)
+        sets = [pkg.DescriptorSet(ctx, rep.rows(i, n), k["kps"], c["grid"], k["fv"]) for i, k in enumerate(kfs)]
+        for s, k in zip(sets, kfs):
+            assert np.array_equal(s.read_desc(), k["desc"])
+        job = pkg.PairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, sets, [k["valid"] for k in kfs], c["ia"], c["ib"], c["nnratio"], 1)
+        job.run()
+        nm, match, dist = job.fetch()
+        onm, om, od = oracle.batch_bow_kf_kf(kfs, c["ia"], c["ib"], c["nnratio"], 1)
+        assert np.array_equal(match[:, :n], om) and np.array_equal(nm, onm)
+        job.destroy()
+        for s in sets:
+            s.release()
+    finally:
+        ctx.synchronize()
+        ctx.set_stream(None)
