@@ -34,6 +34,7 @@ struct asdm_ctx {
   int opt_cand_cap = 8;
   int opt_list_cap_per_query = 4;  // tensor-core short list slots per query row (grows on overflow)
   int opt_tc_epi_warps = 8;        // epilogue warps of the tensor-core kernel: 4 or 8
+  int opt_tc_variant = 0;          // pipeline-shape experiments of the tensor-core kernel (tc_shortlist.cu)
   int64_t stat_launches = 0;       // kernels launched by the last call / job run
   int64_t stat_total_launches = 0;
   int64_t stat_cand_cap = 0;

@@ -9,7 +9,10 @@
 // Persistent kernel, one CTA per SM, 10 warps: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane),
 // warps 2..9 = epilogue (two per TMEM lane quarter, 128 columns each). A work unit keeps one 256-row tile of set B resident in shared
 // memory (double buffered across units) and streams 128-row tiles of set A through a 3-stage ring; accumulators are
-// double buffered in TMEM (2 x 256 columns), so the epilogue of tile t overlaps the MMAs of tile t+1.
+// double buffered in TMEM (2 x 256 columns), so the epilogue of tile t overlaps the MMAs of tile t+1. Each epilogue
+// warp pulls its 32 lanes x 128 columns into registers with four back-to-back tcgen05.ld, waits once, and hands the
+// accumulator back to the MMA warp BEFORE it looks at the values, so TMEM is held for one load latency per tile
+// (1437 -> 1632 TFLOP/s on C5; without that the MMA warp stalled on t_empty: profiles/r01e vs r01f).
 // Per tile: 8 x tcgen05.mma 128x256x16 = 8.39 MFLOP; epilogue = 32768 fp32 reads from TMEM, one max per value.
 #include <cuda.h>
 
@@ -20,12 +23,12 @@ namespace {
 constexpr int TM = 128;        // rows of A per tile (UMMA M)
 constexpr int TN = 256;        // rows of B per tile (UMMA N)
 constexpr int KD = ASDM_DESC_DIM;
-constexpr int A_STAGES = 3;
+constexpr int MAX_A_STAGES = 6;
 constexpr int A_BYTES = TM * KD * 2;   // 32 KB
 constexpr int B_BYTES = TN * KD * 2;   // 64 KB
 constexpr int KBLK_A = TM * 128;       // bytes of one 64-element K block of an A tile (128 B per row)
 constexpr int KBLK_B = TN * 128;
-constexpr int TC_SMEM = 2 * B_BYTES + A_STAGES * A_BYTES + 256;  // tiles + barriers
+constexpr int tc_smem(int a_stages, int b_bufs) { return b_bufs * B_BYTES + a_stages * A_BYTES + 256; }  // tiles + barriers
 constexpr float KAPPA = 0.495f;
 
 // instruction descriptor (cute::UMMA::InstrDescriptor): D=f32, A=B=bf16, both K-major, N=256, M=128
@@ -112,7 +115,7 @@ __device__ __forceinline__ float max_of_32(const uint32_t (&v)[32]) {
 }
 
 struct __align__(8) TcBarriers {
-  uint64_t a_full[A_STAGES], a_empty[A_STAGES];
+  uint64_t a_full[MAX_A_STAGES], a_empty[MAX_A_STAGES];
   uint64_t b_full[2], b_empty[2];
   uint64_t t_full[2], t_empty[2];
   uint32_t tmem_base;
@@ -161,17 +164,18 @@ __global__ void __launch_bounds__(128) k_tc_row_bounds(const TcSetDesc* __restri
   if (threadIdx.x == 0) cmin[blockIdx.x] = fminf(fminf(s_min[0], s_min[1]), fminf(s_min[2], s_min[3]));
 }
 
-// EPI_WARPS = 4 or 8 (with 8, the two warps of a TMEM lane quarter split the 256 columns)
-template <int EPI_WARPS>
+// EPI_WARPS = 4 or 8 (with 8, the two warps of a TMEM lane quarter split the 256 columns); A_STAGES x 32 KB ring of
+// streamed A tiles, B_BUFS x 64 KB resident B tiles; NO_EPI (timing experiments only) skips the TMEM reads.
+template <int EPI_WARPS, int A_STAGES, int B_BUFS, bool NO_EPI, bool EARLY>
 __global__ void __launch_bounds__(64 + 32 * EPI_WARPS, 1)
 k_tc_shortlist(const PairDesc* __restrict__ pairs, const uint8_t* __restrict__ tmaps, const TcWork* __restrict__ work,
                int n_work, float t_half, TcHit* __restrict__ list, int seg_cap, int32_t* __restrict__ seg_count,
                int32_t* __restrict__ list_total) {
   constexpr int EPI_COLS = TN / (EPI_WARPS / 4);
   extern __shared__ __align__(1024) uint8_t smem[];
-  uint8_t* smB = smem;                  // 2 x 64 KB
-  uint8_t* smA = smem + 2 * B_BYTES;    // A_STAGES x 32 KB
-  TcBarriers& bars = *reinterpret_cast<TcBarriers*>(smem + 2 * B_BYTES + A_STAGES * A_BYTES);
+  uint8_t* smB = smem;                      // B_BUFS x 64 KB
+  uint8_t* smA = smem + B_BUFS * B_BYTES;   // A_STAGES x 32 KB
+  TcBarriers& bars = *reinterpret_cast<TcBarriers*>(smem + B_BUFS * B_BYTES + A_STAGES * A_BYTES);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {
@@ -209,8 +213,8 @@ k_tc_shortlist(const PairDesc* __restrict__ pairs, const uint8_t* __restrict__ t
         const PairDesc& pd = pairs[w.pair];
         const void* tmA = tmaps + (size_t)pd.setA * 128;
         const void* tmB = tmaps + (size_t)pd.setB * 128;
-        const int bb = ul & 1;
-        mbar_wait(&bars.b_empty[bb], ((ul >> 1) & 1) ^ 1);
+        const int bb = ul % B_BUFS;
+        mbar_wait(&bars.b_empty[bb], ((ul / B_BUFS) & 1) ^ 1);
         mbar_expect_tx(&bars.b_full[bb], B_BYTES);
 #pragma unroll
         for (int kb = 0; kb < 2; kb++)
@@ -239,8 +243,8 @@ k_tc_shortlist(const PairDesc* __restrict__ pairs, const uint8_t* __restrict__ t
       int ul = 0;
       for (int u = blockIdx.x; u < n_work; u += gridDim.x, ul++) {
         const int m_tiles = work[u].m_tiles;
-        const int bb = ul & 1;
-        mbar_wait(&bars.b_full[bb], (ul >> 1) & 1);
+        const int bb = ul % B_BUFS;
+        mbar_wait(&bars.b_full[bb], (ul / B_BUFS) & 1);
         const uint32_t b_addr = smem_u32(smB + bb * B_BYTES);
         for (int t = 0; t < m_tiles; t++) {
           mbar_wait(&bars.t_empty[acc], accphase ^ 1);
@@ -298,23 +302,45 @@ k_tc_shortlist(const PairDesc* __restrict__ pairs, const uint8_t* __restrict__ t
         mbar_wait(&bars.t_full[acc], accphase);
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * TN + chalf * EPI_COLS);
-        uint32_t v[2][32];
-        tmem_ld32(taddr, v[0]);
-#pragma unroll 2
-        for (int ch = 0; ch < EPI_COLS / 32; ch++) {
-          tmem_ld_wait();
-          if (ch + 1 < EPI_COLS / 32) tmem_ld32(taddr + (ch + 1) * 32, v[(ch + 1) & 1]);
-          const uint32_t(&cur)[32] = v[ch & 1];
-          if (__any_sync(0xffffffffu, max_of_32(cur) >= thr_row)) {
-            uint32_t mask = 0;
+        if (EARLY) {
+          // all 128 columns of this warp into registers at once, then hand the accumulator back to the MMA warp
+          // BEFORE looking at the values: TMEM is held for one load latency per tile instead of the whole epilogue
+          static_assert(!EARLY || EPI_COLS == 128, "early release keeps 128 columns in registers");
+          uint32_t v[4][32];
 #pragma unroll
-            for (int c = 0; c < 32; c++) mask |= (__uint_as_float(cur[c]) >= thr_row) ? (1u << c) : 0u;
-            seg_cnt = tc_emit_hits(mask, w.pair, i, j0 + ch * 32, seg, seg_cnt, seg_cap);
+          for (int ch = 0; ch < 4; ch++) tmem_ld32(taddr + ch * 32, v[ch]);
+          tmem_ld_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&bars.t_empty[acc]);
+#pragma unroll
+          for (int ch = 0; ch < 4; ch++) {
+            if (__any_sync(0xffffffffu, max_of_32(v[ch]) >= thr_row)) {
+              uint32_t mask = 0;
+#pragma unroll
+              for (int c = 0; c < 32; c++) mask |= (__uint_as_float(v[ch][c]) >= thr_row) ? (1u << c) : 0u;
+              seg_cnt = tc_emit_hits(mask, w.pair, i, j0 + ch * 32, seg, seg_cnt, seg_cap);
+            }
           }
+        } else {
+          uint32_t v[2][32];
+          if (!NO_EPI) tmem_ld32(taddr, v[0]);
+#pragma unroll 2
+          for (int ch = 0; ch < (NO_EPI ? 0 : EPI_COLS / 32); ch++) {
+            tmem_ld_wait();
+            if (ch + 1 < EPI_COLS / 32) tmem_ld32(taddr + (ch + 1) * 32, v[(ch + 1) & 1]);
+            const uint32_t(&cur)[32] = v[ch & 1];
+            if (__any_sync(0xffffffffu, max_of_32(cur) >= thr_row)) {
+              uint32_t mask = 0;
+#pragma unroll
+              for (int c = 0; c < 32; c++) mask |= (__uint_as_float(cur[c]) >= thr_row) ? (1u << c) : 0u;
+              seg_cnt = tc_emit_hits(mask, w.pair, i, j0 + ch * 32, seg, seg_cnt, seg_cap);
+            }
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&bars.t_empty[acc]);
         }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&bars.t_empty[acc]);
         acc ^= 1;
         if (acc == 0) accphase ^= 1;
       }
@@ -371,17 +397,18 @@ cudaError_t asdm_tc_row_bounds_launch(asdm_ctx* ctx, const TcSetDesc* d_sets, co
   return cudaGetLastError();
 }
 
-template <int EPI_WARPS>
+template <int EPI_WARPS, int A_STAGES, int B_BUFS, bool NO_EPI, bool EARLY>
 static cudaError_t tc_launch(asdm_ctx* ctx, const PairDesc* d_pairs, const void* d_tmaps, const TcWork* d_work, int n_work,
                              float t_half, TcHit* d_list, int seg_cap, int32_t* d_seg_count, int32_t* d_list_total) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(k_tc_shortlist<EPI_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(k_tc_shortlist<EPI_WARPS, A_STAGES, B_BUFS, NO_EPI, EARLY>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem(A_STAGES, B_BUFS));
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
   const int grid = n_work < ctx->sm_count ? n_work : ctx->sm_count;
-  k_tc_shortlist<EPI_WARPS><<<grid, 64 + 32 * EPI_WARPS, TC_SMEM, ctx->stream>>>(
+  k_tc_shortlist<EPI_WARPS, A_STAGES, B_BUFS, NO_EPI, EARLY><<<grid, 64 + 32 * EPI_WARPS, tc_smem(A_STAGES, B_BUFS), ctx->stream>>>(
       d_pairs, (const uint8_t*)d_tmaps, d_work, n_work, t_half, d_list, seg_cap, d_seg_count, d_list_total);
   return cudaGetLastError();
 }
@@ -390,7 +417,15 @@ cudaError_t asdm_tc_shortlist_launch(asdm_ctx* ctx, const PairDesc* d_pairs, con
                                      int n_work, float t_keep, TcHit* d_list, int seg_cap, int32_t* d_seg_count,
                                      int32_t* d_list_total) {
   const float t_half = 0.5f * t_keep * 1.0001f + 1e-6f;
-  if (ctx->opt_tc_epi_warps == 8)
-    return tc_launch<8>(ctx, d_pairs, d_tmaps, d_work, n_work, t_half, d_list, seg_cap, d_seg_count, d_list_total);
-  return tc_launch<4>(ctx, d_pairs, d_tmaps, d_work, n_work, t_half, d_list, seg_cap, d_seg_count, d_list_total);
+#define TC_ARGS ctx, d_pairs, d_tmaps, d_work, n_work, t_half, d_list, seg_cap, d_seg_count, d_list_total
+  switch (ctx->opt_tc_variant) {  // tuning experiments (asdm_set_option "tc_variant"); 0 is the shipped configuration
+    case 1: return tc_launch<8, 5, 1, false, false>(TC_ARGS);
+    case 2: return tc_launch<8, 2, 2, false, false>(TC_ARGS);
+    case 3: return tc_launch<8, 3, 2, true, false>(TC_ARGS);  // no epilogue: timing of the TMA + MMA pipeline only
+    case 5: return tc_launch<8, 3, 2, false, false>(TC_ARGS);  // accumulator released after the whole epilogue
+    default: break;
+  }
+  if (ctx->opt_tc_epi_warps == 8) return tc_launch<8, 3, 2, false, true>(TC_ARGS);
+  return tc_launch<4, 3, 2, false, false>(TC_ARGS);
+#undef TC_ARGS
 }

@@ -48,6 +48,24 @@ def peaks():
     return dict(bf16=1400.0, bf16_burst=1590.0, hbm=6650.0, source="fallback")
 
 
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one k_tc_shortlist launch on this workload, from the newest
+    committed `ncu --set full` summary under profiles/ (tools/ncu_summary.py); None when there is none."""
+    import glob
+    import re
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_tc_shortlist*.txt")))
+    if not files:
+        return None, None
+    mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    tot = 0.0
+    with open(files[-1]) as f:
+        for line in f:
+            m = re.match(r"\s*dram__bytes_(read|write)\.sum\s+([0-9.]+)\s+(\w+)", line)
+            if m:
+                tot += float(m.group(2)) * mult.get(m.group(3), 1.0)
+    return (tot or None), os.path.relpath(files[-1], ROOT)
+
+
 def make_inputs(pkg, rank, n=N_DESC, n_kf=N_KF, n_pairs=N_PAIRS):
     c = pkg.synth.config5(n=n, n_pairs=n_pairs, n_kf=n_kf, seed_extra=0)
     if rank:
@@ -179,6 +197,8 @@ def run_ours(args):
     ctx.set_stream(stream.cuda_stream)
     if args.epi_warps:
         ctx.set_option("tc_epi_warps", args.epi_warps)
+    if args.tc_variant:
+        ctx.set_option("tc_variant", args.tc_variant)
     n, P = N_DESC, args.pairs
     c, g_ia, g_ib = global_sweep(pkg, world, P)  # every rank describes the whole job; shard.py deals the units
     kfs = c["kfs"]
@@ -313,6 +333,9 @@ def run_ours(args):
             achieved = 3.0 * units * 128 / (dist_ms * 1e-3) / 1e12  # sub, mul, add per element on the fp32 pipes
             roof = {"bound": "fp32", "kernel": "k_cand_exact", "achieved": achieved, "peak": None, "unit": "TFLOP/s",
                     "frac": None, "traffic": None, "note": "exact fp32 CUDA-core path (tensor-core shortlist disabled)"}
+        if tc_used and P == N_PAIRS:
+            roof["traffic"], roof["traffic_source"] = ncu_traffic()
+            roof["traffic_unit"] = "bytes of DRAM read+write per launch (algorithmic: 64 keyframes x 1.024 MB bf16 read once)"
         roof["ms_per_launch"] = dist_ms
         roof["share_of_step"] = dist_ms / (ms / args.steps)
 
@@ -366,6 +389,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--pairs", type=int, default=N_PAIRS, help="keyframe pairs per GPU per step (default: the C5 sweep)")
+    ap.add_argument("--tc-variant", type=int, default=0, help="tuning: pipeline shape of the tensor-core kernel")
     ap.add_argument("--epi-warps", type=int, default=0, help="tuning: epilogue warps of the tensor-core kernel (4 or 8)")
     args = ap.parse_args()
     if args.impl == "reference":
