@@ -35,6 +35,7 @@ EXPORTS = [
     "asdm_search_by_projection", "asdm_search_by_projection_q", "asdm_search_for_initialization", "asdm_stereo_row_match",
     "asdm_job_prepare", "asdm_job_run", "asdm_job_fetch", "asdm_job_settle", "asdm_job_out_stride",
     "asdm_job_device_outputs", "asdm_job_destroy",
+    "asdm_distinctive_descriptors",
 ]
 
 
@@ -114,6 +115,7 @@ def load():
     lib.asdm_job_out_stride.argtypes = [vp]
     lib.asdm_job_device_outputs.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
     lib.asdm_job_destroy.argtypes = [vp]
+    lib.asdm_distinctive_descriptors.argtypes = [vp, C.POINTER(vp), C.c_int, C.c_int, vp, vp, vp, vp, vp]
     _lib = lib
     return lib
 

@@ -51,7 +51,7 @@ struct asdm_ctx {
   // Pinned 64-byte slots with object lifetime (per-job overflow flags, per-set tensor-core range flag)
   char* slot_slab = nullptr;
   std::vector<int> slot_free;
-  DevBuf scratch[8];
+  DevBuf scratch[12];
   int opt_time_kernels = 0;     // record CUDA events around the distance stage of every job run
   std::vector<cudaEvent_t> ev;  // pairs (begin, end), drained by asdm_get_stat("dist_stage_us")
   int proj_ent_cap = 1 << 16;  // entries of the projection candidate pool (grows on overflow)

@@ -335,3 +335,18 @@ class ORBmatcher:
         c.check(c.lib.asdm_stereo_row_match(c.h, left.h, right.h, ptr(sf), len(sf), int(n_rows), float(min_d),
                                             float(max_d), ptr(best), ptr(dist)))
         return best, dist
+
+
+def ComputeDistinctiveDescriptors(ctx, sets, obs_off, obs_set, obs_row):
+    """MapPoint::ComputeDistinctiveDescriptors (reference MapPoint.cc:271-338) for a batch of map points.
+
+    sets: DescriptorSets of the keyframes; point p is observed at rows (sets[obs_set[e]], obs_row[e]) for e in
+    [obs_off[p], obs_off[p+1]), in the reference's iteration order.  Returns (best, median): position within each
+    point's list of the descriptor that becomes MapPoint::mDescriptor (-1: no observation) and its median distance."""
+    off, st, row = _i32(obs_off), _i32(obs_set), _i32(obs_row)
+    n = len(off) - 1
+    best = np.empty(n, np.int32)
+    med = np.empty(n, np.float32)
+    arr = (C.c_void_p * max(len(sets), 1))(*[s.h for s in sets])
+    ctx.check(ctx.lib.asdm_distinctive_descriptors(ctx.h, arr, len(sets), n, ptr(off), ptr(st), ptr(row), ptr(best), ptr(med)))
+    return best, med

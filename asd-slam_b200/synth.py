@@ -337,3 +337,37 @@ def config_init(n=4000, seed_extra=0, window=100):
     prev = np.stack([kps1["x"], kps1["y"]], axis=1).astype(np.float32)  # Tracking.cc:404-406
     return dict(desc1=desc1, kps1=kps1, desc2=desc2, kps2=kps2, grid2=image_grid(W, H), prev_matched=prev,
                 window=window, nnratio=0.9, check_ori=1, gt=gt)
+
+
+def config_distinctive(n_kf=12, n=600, n_points=900, seed_extra=0, max_obs=None, dup_frac=0.05):
+    """MapPoint::ComputeDistinctiveDescriptors inputs (SURVEY 8f.2): `n_points` map points, each observed in 1..max_obs
+    keyframes (a few in none), observation descriptors = a per-point base descriptor + noise; some observations are
+    exact duplicates so that medians tie.  Observations are listed per point in ascending keyframe order, one per
+    keyframe (the reference iterates a std::map<KeyFrame*, size_t>)."""
+    rng = rng_for(7, seed_extra)
+    max_obs = n_kf if max_obs is None else min(max_obs, n_kf)
+    descs = [make_descriptors(rng, n) for _ in range(n_kf)]
+    next_row = np.zeros(n_kf, np.int64)
+    off, okf, orow = [0], [], []
+    for p in range(n_points):
+        r = rng.random()
+        k = 0 if r < 0.02 else (1 if r < 0.07 else int(rng.integers(2, max_obs + 1)))
+        cand = [kf for kf in range(n_kf) if next_row[kf] < n]
+        kfs = sorted(rng.choice(cand, size=min(k, len(cand)), replace=False).tolist()) if cand and k else []
+        base = make_descriptors(rng, 1)[0]
+        prev = None
+        for kf in kfs:
+            row = int(next_row[kf])
+            next_row[kf] += 1
+            if prev is not None and rng.random() < dup_frac:
+                d = prev.copy()
+            else:
+                d = base + rng.normal(0, rng.uniform(0.01, 0.08), DESC_DIM).astype(np.float32)
+                d = (d / np.sqrt((d * d).sum(dtype=np.float32))).astype(np.float32)
+            descs[kf][row] = d
+            prev = d
+            okf.append(kf)
+            orow.append(row)
+        off.append(len(okf))
+    return dict(descs=descs, obs_off=np.asarray(off, np.int32), obs_kf=np.asarray(okf, np.int32),
+                obs_row=np.asarray(orow, np.int32))

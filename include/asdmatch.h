@@ -244,6 +244,16 @@ int asdm_job_out_stride(const asdm_job* job);
 int asdm_job_device_outputs(asdm_job* job, void** match12, void** dist12, void** nmatches);
 int asdm_job_destroy(asdm_job* job);
 
+/* ------------------------------------------------------------------ map-point descriptor maintenance */
+/* MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:271-338) for a batch of map points, e.g. all points matched by
+ * a new keyframe (LocalMapping.cc:245, 535, 628). Observations of point p are rows (sets[obs_set[e]], obs_row[e]),
+ * e in [obs_off[p], obs_off[p+1]), listed in the reference's iteration order (its std::map<KeyFrame*, size_t>), bad
+ * keyframes already dropped (:296). best[p] = position in the point's list of the descriptor to become mDescriptor
+ * (least median distance to the rest, first wins, :321-334), or -1 when the point has no observation (the reference
+ * returns without touching mDescriptor). best_median may be NULL. */
+int asdm_distinctive_descriptors(asdm_ctx* ctx, asdm_set* const* sets, int n_sets, int n_points, const int32_t* obs_off,
+                                 const int32_t* obs_set, const int32_t* obs_row, int32_t* best, float* best_median);
+
 #ifdef __cplusplus
 }
 #endif

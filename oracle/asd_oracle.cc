@@ -677,6 +677,44 @@ void ora_batch_triangulation(const ora_keyframe* kfs, int n, const int32_t* ia, 
   }
 }
 
+// MapPoint.cc:271-338
+void ora_distinctive(const float* const* kf_desc, int n_points, const int32_t* obs_off, const int32_t* obs_kf,
+                     const int32_t* obs_row, int32_t* best, float* best_median) {
+  for (int p = 0; p < n_points; p++) {
+    const int N = obs_off[p + 1] - obs_off[p];
+    best[p] = -1;
+    if (best_median) best_median[p] = 100.f;
+    if (N <= 0) continue;  // :285-286 / :300-301: mDescriptor is left alone
+    std::vector<const float*> row((size_t)N);
+    for (int i = 0; i < N; i++) {
+      const int e = obs_off[p] + i;
+      row[i] = kf_desc[obs_kf[e]] + (size_t)obs_row[e] * ORA_DESC_DIM;
+    }
+    std::vector<float> D((size_t)N * N);
+    for (int i = 0; i < N; i++) {  // :306-318
+      D[(size_t)i * N + i] = 0;
+      for (int j = i + 1; j < N; j++) {
+        const float d = ora_descriptor_distance(row[i], row[j]);
+        D[(size_t)i * N + j] = d;
+        D[(size_t)j * N + i] = d;
+      }
+    }
+    float best_med = 100;  // :321
+    int best_idx = 0;
+    for (int i = 0; i < N; i++) {  // :323-334
+      std::vector<float> v(D.begin() + (size_t)i * N, D.begin() + (size_t)(i + 1) * N);
+      std::sort(v.begin(), v.end());
+      const float median = v[(size_t)(0.5 * (N - 1))];
+      if (median < best_med) {
+        best_med = median;
+        best_idx = i;
+      }
+    }
+    best[p] = best_idx;
+    if (best_median) best_median[p] = best_med;
+  }
+}
+
 int ora_max_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();

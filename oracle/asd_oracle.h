@@ -184,6 +184,15 @@ void ora_batch_triangulation(const ora_keyframe* kfs, int n, const int32_t* ia, 
                              const float* scale_factors, const float* level_sigma2, int check_ori, int threads,
                              int32_t* match12, float* dist12, int32_t* nmatches);
 
+/* MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:271-338), batched over map points: all-pairs
+ * DescriptorDistance between the point's observed descriptors (:306-318), per observation the median
+ * vDists[0.5*(N-1)] of its sorted row INCLUDING the zero self distance (:323-327), the first observation with the
+ * smallest median below 100 wins (:329-333; BestIdx stays 0 otherwise). Observations (obs_kf[e], obs_row[e]),
+ * e in [obs_off[p], obs_off[p+1]), are given in the reference's iteration order (std::map<KeyFrame*, size_t>).
+ * best[p] = position within the point's list, -1 when it has no observation (:285-286, :300-301). */
+void ora_distinctive(const float* const* kf_desc, int n_points, const int32_t* obs_off, const int32_t* obs_kf,
+                     const int32_t* obs_row, int32_t* best, float* best_median);
+
 int ora_max_threads(void);
 
 #ifdef __cplusplus

@@ -274,3 +274,22 @@ def batch_triangulation(kfs, ia, ib, F12, epipoles, scale_factors, level_sigma2,
 
 def max_threads():
     return int(lib().ora_max_threads())
+
+
+def _obs_arrays(kf_descs, obs_off, obs_kf, obs_row):
+    descs = [_f32(d) for d in kf_descs]
+    ptrs = (C.c_void_p * len(descs))(*[d.ctypes.data for d in descs])
+    off = np.ascontiguousarray(obs_off, np.int32)
+    kf = np.ascontiguousarray(obs_kf, np.int32)
+    row = np.ascontiguousarray(obs_row, np.int32)
+    return descs, ptrs, off, kf, row
+
+
+def distinctive(kf_descs, obs_off, obs_kf, obs_row):
+    """MapPoint::ComputeDistinctiveDescriptors over a batch of map points (MapPoint.cc:271-338)."""
+    descs, ptrs, off, kf, row = _obs_arrays(kf_descs, obs_off, obs_kf, obs_row)
+    n = len(off) - 1
+    best = np.empty(n, np.int32)
+    med = np.empty(n, np.float32)
+    lib().ora_distinctive(ptrs, n, _p(off), _p(kf), _p(row), _p(best), _p(med))
+    return best, med

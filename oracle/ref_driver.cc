@@ -11,6 +11,7 @@
 // MapPoint objects from them and calls the reference method.  Where an overload derives its search window from
 // poses and 3-D points, the harness picks identity poses, fx=fy=1, cx=cy=0 and points (u, v, 1), so the reference's
 // own projection code yields exactly the (u, v) passed in.
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -23,10 +24,12 @@ namespace ORB_SLAM2 {
 float Frame::fx = 1, Frame::fy = 1, Frame::cx = 0, Frame::cy = 0, Frame::invfx = 1, Frame::invfy = 1;
 float Frame::mfGridElementWidthInv = 0, Frame::mfGridElementHeightInv = 0;
 float Frame::mnMinX = 0, Frame::mnMaxX = 0, Frame::mnMinY = 0, Frame::mnMaxY = 0;
-// the reference's own function bodies (see oracle/Makefile for the line ranges)
+// the reference's own function bodies (see oracle/Makefile for the line ranges); MapPoint.cc relies on `using namespace std`
+using std::sort;
 #include "_ref/gen/frame_grid.inc"
 #include "_ref/gen/keyframe_grid.inc"
 #include "_ref/gen/mappoint_scale.inc"
+#include "_ref/gen/mappoint_distinct.inc"
 
 // protected members of the reference class, opened for direct checks
 struct OpenMatcher : public ORBmatcher {
@@ -595,6 +598,22 @@ int ref_search_by_sim3(const float* desc1, const ora_kp* kps1, int n1, const flo
   const int nf = m.SearchBySim3(&K1, &K2, m12, s12, R12, vec3(0, 0, 0), th);
   for (int i = 0; i < n1; i++) match12[i] = m12[i] ? m12[i]->id : -1;
   return nf;
+}
+
+// MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:271-338) over a batch of map points. Observations of point p
+// are (obs_kf[e], obs_row[e]) for e in [obs_off[p], obs_off[p+1]), ascending and unique in obs_kf -- the reference
+// walks a std::map<KeyFrame*, size_t>, and the keyframes live in one array here so pointer order is index order.
+// out_desc: the 128 floats the reference leaves in mDescriptor (untouched rows when a point has no observation).
+void ref_distinctive(const float* const* kf_desc, const int32_t* kf_n, int n_kf, int n_points, const int32_t* obs_off,
+                     const int32_t* obs_kf, const int32_t* obs_row, float* out_desc) {
+  std::vector<KeyFrame> kfs((size_t)n_kf);
+  for (int k = 0; k < n_kf; k++) kfs[k].mDescriptors = desc_mat(kf_desc[k], kf_n[k]);
+  for (int p = 0; p < n_points; p++) {
+    MapPoint mp;
+    for (int e = obs_off[p]; e < obs_off[p + 1]; e++) mp.mObservations[&kfs[obs_kf[e]]] = (size_t)obs_row[e];
+    mp.ComputeDistinctiveDescriptors();
+    if (!mp.mDescriptor.empty()) memcpy(out_desc + (size_t)p * ORA_DESC_DIM, mp.mDescriptor.ptr<float>(0), ORA_DESC_DIM * sizeof(float));
+  }
 }
 
 }  // extern "C"

@@ -215,3 +215,16 @@ def search_by_sim3(desc1, kps1, desc2, kps2, grid, valid1, valid2, uv1, uv2, lev
                                   _p(uv1), _p(uv2), _p(l1), _p(l2), _p(mp1), _p(mp2), _p(a1), _p(sf), len(sf),
                                   C.c_float(th), _p(match))
     return nf, match
+
+
+def distinctive(kf_descs, obs_off, obs_kf, obs_row):
+    """The reference's own MapPoint::ComputeDistinctiveDescriptors; returns the chosen descriptor of every point
+    (NaN rows for points without observations, which the reference leaves untouched)."""
+    descs = [_f32(d) for d in kf_descs]
+    ptrs = (C.c_void_p * len(descs))(*[d.ctypes.data for d in descs])
+    ns = _i32([len(d) for d in descs])
+    off, kf, row = _i32(obs_off), _i32(obs_kf), _i32(obs_row)
+    n = len(off) - 1
+    out = np.full((n, 128), np.nan, np.float32)
+    lib().ref_distinctive(ptrs, _p(ns), len(descs), n, _p(off), _p(kf), _p(row), _p(out))
+    return out

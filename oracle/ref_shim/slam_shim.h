@@ -40,6 +40,7 @@ class MapPoint {
   cv::Mat GetDescriptor() { return mDescriptor.clone(); }
   cv::Mat GetWorldPos() { return mWorldPos.clone(); }
   cv::Mat GetNormal() { return mNormalVector.clone(); }
+  void ComputeDistinctiveDescriptors();  // body: the reference's MapPoint.cc:271-338 (oracle/_ref/gen)
   float GetMinDistanceInvariance();
   float GetMaxDistanceInvariance();
   int PredictScale(const float& currentDist, KeyFrame* pKF);
@@ -61,6 +62,7 @@ class MapPoint {
   cv::Mat mDescriptor, mWorldPos, mNormalVector;
   float mfMinDistance = 0, mfMaxDistance = 0;
   std::map<KeyFrame*, size_t> mObservations;
+  std::vector<cv::Mat> mappointAllDescriptors;  // MapPoint.h: side buffer the fork fills in ComputeDistinctiveDescriptors
   MapPoint* mpReplaced = nullptr;
   int id = -1;
 };
@@ -96,6 +98,8 @@ class KeyFrame {
   void AssignFeaturesToGrid();
   std::vector<size_t> GetFeaturesInArea(const float& x, const float& y, const float& r) const;
   bool IsInImage(const float& x, const float& y) const;
+  bool isBad() { return mbBad; }
+  bool mbBad = false;
   std::vector<MapPoint*> GetMapPointMatches() { return mvpMapPoints; }
   MapPoint* GetMapPoint(const size_t& idx) { return mvpMapPoints[idx]; }
   std::set<MapPoint*> GetMapPoints() {

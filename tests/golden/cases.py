@@ -132,6 +132,33 @@ def cases():
                                      uv1=uv1, uv2=uv2, level1=np.minimum(k1["octave"] + rng.integers(0, 2, n), 7).astype(np.int32),
                                      level2=np.minimum(k2["octave"] + rng.integers(0, 2, n), 7).astype(np.int32),
                                      already1=(rng.random(n) < 0.1).astype(np.uint8), th=7.5)))
+    # MapPoint::ComputeDistinctiveDescriptors: few observations per point, and points seen from > 32 keyframes
+    out.append(("distinct", "distinct", dict(c=S.config_distinctive(n_kf=10, n=200, n_points=300, seed_extra=1))))
+    out.append(("distinct_many_obs", "distinct", dict(c=S.config_distinctive(n_kf=44, n=60, n_points=50, seed_extra=2, dup_frac=0.1))))
+    return out
+
+
+def first_equal_observation(c, chosen):
+    """Position, within each point's observation list, of the first observation whose descriptor equals `chosen[p]`
+    bit for bit (-1 for points without observations: the reference leaves their descriptor untouched)."""
+    off, okf, orow = c["obs_off"], c["obs_kf"], c["obs_row"]
+    out = np.full(len(off) - 1, -1, np.int32)
+    for p in range(len(off) - 1):
+        for e in range(off[p], off[p + 1]):
+            if np.array_equal(c["descs"][okf[e]][orow[e]].view(np.uint32), chosen[p].view(np.uint32)):
+                out[p] = e - off[p]
+                break
+        assert out[p] >= 0 or off[p] == off[p + 1], "the reference chose a descriptor that is not among the observations"
+    return out
+
+
+def chosen_descriptors(c, best):
+    """Rows picked by `best` (positions within each point's list); NaN rows where best < 0."""
+    out = np.full((len(best), 128), np.nan, np.float32)
+    for p, b in enumerate(best):
+        if b >= 0:
+            e = c["obs_off"][p] + b
+            out[p] = c["descs"][c["obs_kf"][e]][c["obs_row"][e]]
     return out
 
 
@@ -192,6 +219,9 @@ def run_case(ref, name, kind, a):
     elif kind == "fuse_sim3":
         nf, rep, add = ref.fuse_sim3(a["desc_t"], a["kps_t"], a["grid"], a["q"], a["level"], a["desc_q"], a["occ_obs"], a["mp_obs"], S.scale_factors(), a["th"])
         out[name + "/nf"], out[name + "/replace"], out[name + "/added"] = np.int32(nf), rep, add
+    elif kind == "distinct":
+        c = a["c"]
+        out[name + "/best"] = first_equal_observation(c, ref.distinctive(c["descs"], c["obs_off"], c["obs_kf"], c["obs_row"]))
     elif kind == "sim3":
         nf, m = ref.search_by_sim3(a["desc1"], a["kps1"], a["desc2"], a["kps2"], a["grid"], a["valid1"], a["valid2"], a["uv1"], a["uv2"],
                                    a["level1"], a["level2"], a["desc1"], a["desc2"], a["already1"], S.scale_factors(), a["th"])

@@ -320,3 +320,25 @@ def test_errors_do_not_throw(pkg, ctx):
         mt.SearchByBoW_KF_KF(A, np.ones(10, np.uint8), A, np.ones(10, np.uint8))
     assert b"FeatureVector" in lib.asdm_last_error(ctx.h)
     A.release()
+
+
+# ------------------------------------------------------------------ MapPoint::ComputeDistinctiveDescriptors
+@pytest.mark.parametrize("n_kf,n,n_points,max_obs", [(20, 2000, 6000, 12), (48, 300, 200, 48), (2, 10, 5, 2)])
+def test_compute_distinctive_descriptors(pkg, ctx, oracle, n_kf, n, n_points, max_obs):
+    c = pkg.synth.config_distinctive(n_kf=n_kf, n=n, n_points=n_points, max_obs=max_obs, dup_frac=0.1)
+    sets = [pkg.DescriptorSet(ctx, d) for d in c["descs"]]
+    best, med = pkg.ComputeDistinctiveDescriptors(ctx, sets, c["obs_off"], c["obs_kf"], c["obs_row"])
+    assert ctx.stat("gpu_launches") >= 1
+    obest, omed = oracle.distinctive(c["descs"], c["obs_off"], c["obs_kf"], c["obs_row"])
+    _eq(best, obest, "best observation")
+    has = obest >= 0
+    _eq_dist(med[has], omed[has], "best median")
+    if max_obs > 32:
+        assert (np.diff(c["obs_off"]) > 32).sum() > 10  # the large-point kernel ran
+    # empty batch and points without observations
+    b0, _ = pkg.ComputeDistinctiveDescriptors(ctx, sets, [0, 0, 0], [], [])
+    assert list(b0) == [-1, -1]
+    with pytest.raises(pkg.AsdmError):
+        pkg.ComputeDistinctiveDescriptors(ctx, sets, [0, 1], [len(sets)], [0])
+    for s in sets:
+        s.release()

@@ -243,3 +243,21 @@ def test_sbp_keyframe_sim3(pkg, oracle, ref):
     oa = np.where(oa == -2, -1, oa)  # the harness cannot tell 'cleared by the rotation check' from 'untouched'
     assert np.array_equal(oa, ra) and onm == rnm
     assert (oa >= 0).sum() > 10
+
+
+@pytest.mark.parametrize("n_kf,n,n_points,max_obs", [(12, 600, 900, None), (44, 60, 50, 44), (3, 50, 40, 3)])
+def test_compute_distinctive_descriptors(pkg, oracle, ref, n_kf, n, n_points, max_obs):
+    """MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:271-338): the descriptor the reference stores."""
+    sys_path_golden = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    if sys_path_golden not in sys.path:
+        sys.path.insert(0, sys_path_golden)
+    import cases as C
+    c = pkg.synth.config_distinctive(n_kf=n_kf, n=n, n_points=n_points, max_obs=max_obs, dup_frac=0.1)
+    best, med = oracle.distinctive(c["descs"], c["obs_off"], c["obs_kf"], c["obs_row"])
+    want = ref.distinctive(c["descs"], c["obs_off"], c["obs_kf"], c["obs_row"])
+    got = C.chosen_descriptors(c, best)
+    nobs = np.diff(c["obs_off"])
+    assert np.array_equal(best < 0, nobs == 0)
+    assert np.array_equal(np.isnan(want[:, 0]), nobs == 0)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    assert (best > 0).sum() > 0
