@@ -36,6 +36,7 @@ EXPORTS = [
     "asdm_job_prepare", "asdm_job_run", "asdm_job_fetch", "asdm_job_settle", "asdm_job_out_stride",
     "asdm_job_device_outputs", "asdm_job_destroy",
     "asdm_distinctive_descriptors",
+    "asdm_vocab_create", "asdm_vocab_release", "asdm_vocab_transform",
 ]
 
 
@@ -60,6 +61,12 @@ class JobDesc(C.Structure):
                 ("nnratio", C.c_float), ("check_ori", C.c_int32), ("F12", C.c_void_p), ("epipoles", C.c_void_p),
                 ("scale_factors", C.c_void_p), ("level_sigma2", C.c_void_p), ("n_levels", C.c_int32),
                 ("row_begin", C.c_void_p), ("row_end", C.c_void_p)]
+
+
+class VocabDesc(C.Structure):
+    _fields_ = [("k", C.c_int32), ("L", C.c_int32), ("weighting", C.c_int32), ("scoring", C.c_int32),
+                ("n_nodes", C.c_int32), ("child_off", C.c_void_p), ("child_idx", C.c_void_p), ("desc", C.c_void_p),
+                ("weight", C.c_void_p), ("word_id", C.c_void_p)]
 
 
 class AsdmError(RuntimeError):
@@ -116,6 +123,9 @@ def load():
     lib.asdm_job_device_outputs.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
     lib.asdm_job_destroy.argtypes = [vp]
     lib.asdm_distinctive_descriptors.argtypes = [vp, C.POINTER(vp), C.c_int, C.c_int, vp, vp, vp, vp, vp]
+    lib.asdm_vocab_create.argtypes = [vp, C.POINTER(VocabDesc), C.POINTER(vp)]
+    lib.asdm_vocab_release.argtypes = [vp]
+    lib.asdm_vocab_transform.argtypes = [vp, vp, vp, C.c_int, vp, vp, vp, C.POINTER(i32), vp, vp]
     _lib = lib
     return lib
 

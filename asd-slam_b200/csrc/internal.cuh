@@ -79,6 +79,20 @@ struct asdm_set {
   std::vector<uint8_t> tmap_bf;   // CUtensorMap (128 B) over desc_bf, built lazily
 };
 
+// DBoW2 vocabulary tree resident on the device (kernels_vocab.cuh) plus the host copies of what the BowVector needs
+struct asdm_vocab {
+  asdm_ctx* ctx = nullptr;
+  int k = 0, L = 0, weighting = 0, scoring = 0, n_nodes = 0;
+  int G = 1;               // lanes per feature in k_voc_descend
+  void* mem = nullptr;     // one arena: child_off | child_idx | weight | blk
+  int32_t* child_off = nullptr;
+  int32_t* child_idx = nullptr;
+  double* weight = nullptr;
+  float* blk = nullptr;
+  std::vector<double> h_weight;
+  std::vector<int32_t> h_word;
+};
+
 // --------------------------------------------------------------------------------- device-visible structs
 // One keyframe pair of a BoW-gated dense search (a8 / a9 / a11).
 struct PairDesc {

@@ -14,7 +14,7 @@ import numpy as np
 
 from . import _lib
 from ._lib import (ASDM_JOB_BOW_KF_KF, ASDM_JOB_TRIANGULATION, ASDM_PROJ_BEST_ONLY, ASDM_PROJ_RATIO_LEVEL, KP_DTYPE,
-                   PROJ_QUERY_DTYPE, TH_HIGH, TH_LOW, AsdmError, FeatVec, Grid, JobDesc, ProjParams, ptr)
+                   PROJ_QUERY_DTYPE, TH_HIGH, TH_LOW, AsdmError, FeatVec, Grid, JobDesc, ProjParams, VocabDesc, ptr)
 
 
 def _f32(a):
@@ -350,3 +350,49 @@ def ComputeDistinctiveDescriptors(ctx, sets, obs_off, obs_set, obs_row):
     arr = (C.c_void_p * max(len(sets), 1))(*[s.h for s in sets])
     ctx.check(ctx.lib.asdm_distinctive_descriptors(ctx.h, arr, len(sets), n, ptr(off), ptr(st), ptr(row), ptr(best), ptr(med)))
     return best, med
+
+
+# DBoW2 enums (src/dbow2/include/BowVector.h:36-53)
+TF_IDF, TF, IDF, BINARY = 0, 1, 2, 3
+L1_NORM, L2_NORM, CHI_SQUARE, KL, BHATTACHARYYA, DOT_PRODUCT = 0, 1, 2, 3, 4, 5
+
+
+class ORBVocabulary:
+    """DBoW2::TemplatedVocabulary<FSift::TDescriptor, FSift> (reference src/vslam/include/ORBVocabulary.h:34) resident
+    on the device. `tree` holds the flat arrays of include/asdmatch.h asdm_vocab_desc: k, L, weighting, scoring,
+    child_off, child_idx, desc (n_nodes x 128), weight (float64), word_id."""
+
+    def __init__(self, ctx, tree):
+        self.ctx = ctx
+        self._keep = (_i32(tree["child_off"]), _i32(tree["child_idx"]), _f32(tree["desc"]),
+                      np.ascontiguousarray(tree["weight"], np.float64), _i32(tree["word_id"]))
+        off, idx, desc, w, word = self._keep
+        d = VocabDesc(int(tree["k"]), int(tree["L"]), int(tree["weighting"]), int(tree["scoring"]), len(w), ptr(off),
+                      ptr(idx), ptr(desc), ptr(w), ptr(word))
+        h = C.c_void_p()
+        ctx.check(ctx.lib.asdm_vocab_create(ctx.h, C.byref(d), C.byref(h)))
+        self.h = h
+
+    def transform(self, dset, levelsup=4, host=True):
+        """transform(features, BowVector&, FeatureVector&, levelsup) (TemplatedVocabulary.h:1125-1192) over the rows of
+        `dset`; attaches the FeatureVector to the set on the device. Returns dict(word_id, node_id, in_fv, bow_id,
+        bow_val), or None with host=False (nothing comes back, the call stays asynchronous)."""
+        ctx = self.ctx
+        if not host:
+            ctx.check(ctx.lib.asdm_vocab_transform(ctx.h, self.h, dset.h, int(levelsup), None, None, None, None, None, None))
+            return None
+        n = dset.n
+        word = np.empty(n, np.int32)
+        node = np.empty(n, np.int32)
+        inc = np.empty(n, np.uint8)
+        bid = np.empty(max(n, 1), np.uint32)
+        bval = np.empty(max(n, 1), np.float64)
+        nb = C.c_int32()
+        ctx.check(ctx.lib.asdm_vocab_transform(ctx.h, self.h, dset.h, int(levelsup), ptr(word), ptr(node), ptr(inc),
+                                               C.byref(nb), ptr(bid), ptr(bval)))
+        return dict(word_id=word, node_id=node, in_fv=inc, bow_id=bid[:nb.value].copy(), bow_val=bval[:nb.value].copy())
+
+    def release(self):
+        if self.h:
+            self.ctx.lib.asdm_vocab_release(self.h)
+            self.h = None

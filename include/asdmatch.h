@@ -254,6 +254,40 @@ int asdm_job_destroy(asdm_job* job);
 int asdm_distinctive_descriptors(asdm_ctx* ctx, asdm_set* const* sets, int n_sets, int n_points, const int32_t* obs_off,
                                  const int32_t* obs_set, const int32_t* obs_row, int32_t* best, float* best_median);
 
+/* ------------------------------------------------------------------ vocabulary tree (DBoW2) on the device */
+/* TemplatedVocabulary<FSift::TDescriptor, FSift> (src/dbow2/include/TemplatedVocabulary.h; the ORBVocabulary typedef,
+ * src/vslam/include/ORBVocabulary.h:34) as flat arrays, in the state TemplatedVocabulary::load leaves it (:1455-1504):
+ * node 0 is the root, children of a node are listed in push_back order (:1486), desc holds Node::descriptor
+ * (FSift::fromString), weight Node::weight, word_id Node::word_id of the leaves (ignored for inner nodes). */
+typedef struct asdm_vocab asdm_vocab;
+typedef struct {
+  int32_t k, L;             /* m_k, m_L */
+  int32_t weighting;        /* DBoW2::WeightingType: 0 TF_IDF, 1 TF, 2 IDF, 3 BINARY (BowVector.h:36-42) */
+  int32_t scoring;          /* DBoW2::ScoringType: 0 L1_NORM, 1 L2_NORM, 2 CHI_SQUARE, 3 KL, 4 BHATTACHARYYA, 5 DOT_PRODUCT */
+  int32_t n_nodes;          /* including the root */
+  const int32_t* child_off; /* n_nodes + 1 */
+  const int32_t* child_idx; /* child_off[n_nodes] node ids */
+  const float* desc;        /* n_nodes x 128 (row 0, the root, is not read) */
+  const double* weight;     /* n_nodes */
+  const int32_t* word_id;   /* n_nodes */
+} asdm_vocab_desc;
+
+int asdm_vocab_create(asdm_ctx* ctx, const asdm_vocab_desc* desc, asdm_vocab** out);
+int asdm_vocab_release(asdm_vocab* voc);
+
+/* TemplatedVocabulary::transform(features, BowVector&, FeatureVector&, levelsup) (:1125-1192) over the rows of `set`,
+ * as called by Frame::ComputeBoW (Frame.cc:289-296) and KeyFrame::ComputeBoW (KeyFrame.cc:203-219) with levelsup = 4.
+ * The tree descent (:1216-1257, FSift::distance in double, FSift.cpp:86-101) runs on the device and the resulting
+ * FeatureVector is attached to the set there (as asdm_set_featvec would), so the gating data of the BoW searches never
+ * crosses PCIe. Returned to the host for the caller's mBowVec / mFeatVec:
+ *   word_id[i]  word of feature i (n entries);  node_id[i]  its node levelsup levels above the leaves (0 = root);
+ *   in_fv[i]    1 when the word is not stopped (weight > 0, :1155) -- only those features enter either vector;
+ *   bow_id / bow_val (capacity n; *bow_n entries, ascending word id) = the BowVector after weighting and
+ *   normalisation (:1137-1189, BowVector.cpp:61-84), bit-identical doubles.
+ * Any output pointer may be NULL. An empty vocabulary cannot be created, so the early return of :1132 does not arise. */
+int asdm_vocab_transform(asdm_ctx* ctx, asdm_vocab* voc, asdm_set* set, int levelsup, int32_t* word_id,
+                         int32_t* node_id, uint8_t* in_fv, int32_t* bow_n, uint32_t* bow_id, double* bow_val);
+
 #ifdef __cplusplus
 }
 #endif

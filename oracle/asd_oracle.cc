@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <map>
 #include <utility>
 #include <vector>
 #ifdef _OPENMP
@@ -713,6 +714,88 @@ void ora_distinctive(const float* const* kf_desc, int n_points, const int32_t* o
     best[p] = best_idx;
     if (best_median) best_median[p] = best_med;
   }
+}
+
+// FSift::distance (src/dbow2/DBoW2/FSift.cpp:86-101): float difference, float product, double running sum
+static double fsift_distance(const float* a, const float* b) {
+  double sqd = 0.;
+  for (int i = 0; i < ORA_DESC_DIM; i++) {
+    const float d = a[i] - b[i];
+    const float p = d * d;
+    sqd += p;
+  }
+  return sqd;
+}
+
+int ora_voc_transform(int L, int weighting, int scoring, int n_nodes, const int32_t* child_off, const int32_t* child_idx,
+                      const float* node_desc, const double* weight, const int32_t* word_of_node, const float* desc, int n,
+                      int levelsup, int32_t* word_id, int32_t* node_id, uint8_t* in_fv, uint32_t* bow_id, double* bow_val) {
+  (void)n_nodes;
+  std::map<uint32_t, double> v;  // DBoW2::BowVector
+  const int nid_level = L - levelsup;  // TemplatedVocabulary.h:1224
+  for (int f = 0; f < n; f++) {
+    const float* feat = desc + (size_t)f * ORA_DESC_DIM;
+    int nid = 0;
+    bool nid_set = nid_level <= 0;  // :1225
+    int final_id = 0, level = 0;
+    do {  // :1230-1251
+      ++level;
+      const int off = child_off[final_id], kp = child_off[final_id + 1] - off;
+      final_id = child_idx[off];
+      double best_d = fsift_distance(feat, node_desc + (size_t)final_id * ORA_DESC_DIM);
+      for (int c = 1; c < kp; c++) {
+        const int id = child_idx[off + c];
+        const double d = fsift_distance(feat, node_desc + (size_t)id * ORA_DESC_DIM);
+        if (d < best_d) {
+          best_d = d;
+          final_id = id;
+        }
+      }
+      if (level == nid_level) {
+        nid = final_id;
+        nid_set = true;
+      }
+    } while (child_off[final_id + 1] != child_off[final_id]);
+    if (!nid_set) nid = final_id;
+    const double w = weight[final_id];
+    const uint32_t id = (uint32_t)word_of_node[final_id];
+    if (word_id) word_id[f] = (int32_t)id;
+    if (node_id) node_id[f] = nid;
+    if (in_fv) in_fv[f] = w > 0;
+    if (w > 0) {  // :1155 / :1183
+      auto it = v.lower_bound(id);
+      const bool exists = it != v.end() && !(id < it->first);
+      if (weighting == 0 || weighting == 1) {  // TF_IDF, TF: addWeight
+        if (exists) it->second += w;
+        else v.insert(it, std::make_pair(id, w));
+      } else if (!exists) {  // IDF, BINARY: addIfNotExist
+        v.insert(it, std::make_pair(id, w));
+      }
+    }
+  }
+  const bool must = scoring != 5;  // every scoring object but DotProductScoring normalises (ScoringObject.h:72-89)
+  if ((weighting == 0 || weighting == 1) && !v.empty() && !must) {  // :1163-1169
+    const double nd = v.size();
+    for (auto& e : v) e.second /= nd;
+  }
+  if (must) {  // BowVector::normalize (BowVector.cpp:61-84); L2Scoring alone asks for L2
+    double norm = 0.0;
+    if (scoring != 1) {
+      for (auto& e : v) norm += fabs(e.second);
+    } else {
+      for (auto& e : v) norm += e.second * e.second;
+      norm = sqrt(norm);
+    }
+    if (norm > 0.0)
+      for (auto& e : v) e.second /= norm;
+  }
+  int k = 0;
+  for (auto& e : v) {
+    if (bow_id) bow_id[k] = e.first;
+    if (bow_val) bow_val[k] = e.second;
+    k++;
+  }
+  return k;
 }
 
 int ora_max_threads(void) {

@@ -193,6 +193,18 @@ void ora_batch_triangulation(const ora_keyframe* kfs, int n, const int32_t* ia, 
 void ora_distinctive(const float* const* kf_desc, int n_points, const int32_t* obs_off, const int32_t* obs_kf,
                      const int32_t* obs_row, int32_t* best, float* best_median);
 
+/* DBoW2 vocabulary tree: TemplatedVocabulary<FSift::TDescriptor, FSift>::transform(features, BowVector&,
+ * FeatureVector&, levelsup) (src/dbow2/include/TemplatedVocabulary.h:1125-1192) with the per-feature descent of
+ * :1216-1257 and FSift::distance (src/dbow2/DBoW2/FSift.cpp:86-101; fp32 products added to a double in index order).
+ * The tree is given flat, in the state TemplatedVocabulary::load leaves it (:1455-1504): node 0 = root, children in
+ * push_back order. Outputs: word_id / node_id / in_fv per feature (node_id at level L - levelsup, 0 = root; when a
+ * branch ends above that level the reference reads an uninitialised NodeId (:1148) and this restatement reports the
+ * leaf), and the BowVector (ascending word id) after BowVector::addWeight / addIfNotExist and normalize
+ * (BowVector.cpp:35-84). Returns the BowVector size. */
+int ora_voc_transform(int L, int weighting, int scoring, int n_nodes, const int32_t* child_off, const int32_t* child_idx,
+                      const float* node_desc, const double* weight, const int32_t* word_of_node, const float* desc, int n,
+                      int levelsup, int32_t* word_id, int32_t* node_id, uint8_t* in_fv, uint32_t* bow_id, double* bow_val);
+
 int ora_max_threads(void);
 
 #ifdef __cplusplus

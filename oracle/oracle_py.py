@@ -293,3 +293,26 @@ def distinctive(kf_descs, obs_off, obs_kf, obs_row):
     med = np.empty(n, np.float32)
     lib().ora_distinctive(ptrs, n, _p(off), _p(kf), _p(row), _p(best), _p(med))
     return best, med
+
+
+def voc_transform(tree, desc, levelsup=4):
+    """TemplatedVocabulary::transform(features, BowVector&, FeatureVector&, levelsup) (TemplatedVocabulary.h:1125-1192,
+    1216-1257; FSift.cpp:86-101) on the flat tree `tree` (keys as asdm_vocab_desc)."""
+    desc = _f32(desc)
+    n = len(desc)
+    off = np.ascontiguousarray(tree["child_off"], np.int32)
+    idx = np.ascontiguousarray(tree["child_idx"], np.int32)
+    nd = _f32(tree["desc"])
+    w = np.ascontiguousarray(tree["weight"], np.float64)
+    word = np.ascontiguousarray(tree["word_id"], np.int32)
+    word_id = np.empty(n, np.int32)
+    node_id = np.empty(n, np.int32)
+    inc = np.empty(n, np.uint8)
+    bid = np.empty(max(n, 1), np.uint32)
+    bval = np.empty(max(n, 1), np.float64)
+    f = lib().ora_voc_transform
+    f.restype = C.c_int
+    nb = f(C.c_int(int(tree["L"])), C.c_int(int(tree["weighting"])), C.c_int(int(tree["scoring"])), C.c_int(len(w)),
+           _p(off), _p(idx), _p(nd), _p(w), _p(word), _p(desc), C.c_int(n), C.c_int(int(levelsup)), _p(word_id),
+           _p(node_id), _p(inc), _p(bid), _p(bval))
+    return dict(word_id=word_id, node_id=node_id, in_fv=inc, bow_id=bid[:nb].copy(), bow_val=bval[:nb].copy())

@@ -228,3 +228,82 @@ def distinctive(kf_descs, obs_off, obs_kf, obs_row):
     out = np.full((n, 128), np.nan, np.float32)
     lib().ref_distinctive(ptrs, _p(ns), len(descs), n, _p(off), _p(kf), _p(row), _p(out))
     return out
+
+
+# ------------------------------------------------------------------ vocabulary tree (oracle/ref_voc_driver.cc)
+_VLIB = os.path.join(_HERE, "_ref", "libref_vocab.so")
+_vlib = None
+
+
+def voc_available():
+    return os.path.exists(_VLIB) or (build() and os.path.exists(_VLIB))
+
+
+def vlib():
+    global _vlib
+    if _vlib is None:
+        if not voc_available():
+            raise RuntimeError("oracle/_ref/libref_vocab.so is missing and /root/reference is not mounted")
+        _vlib = C.CDLL(_VLIB)
+        _vlib.ref_voc_train.restype = C.c_void_p
+        _vlib.ref_voc_load.restype = C.c_void_p
+        _vlib.ref_fsift_distance.restype = C.c_double
+    return _vlib
+
+
+class RefVocabulary:
+    """The reference's own TemplatedVocabulary<FSift::TDescriptor, FSift> behind a handle."""
+
+    def __init__(self, h):
+        self.h = C.c_void_p(h)
+
+    @classmethod
+    def train(cls, desc, n_images, k, L, weighting=0, scoring=0, seed=1):
+        desc = _f32(desc)
+        return cls(vlib().ref_voc_train(_p(desc), len(desc), n_images, k, L, weighting, scoring, C.c_uint(seed)))
+
+    @classmethod
+    def load(cls, tree):
+        """tree: flat arrays as asdm_vocab_desc; goes through the reference's load() (text descriptors)."""
+        off, idx = _i32(tree["child_off"]), _i32(tree["child_idx"])
+        nn = len(off) - 1
+        parent = np.zeros(nn, np.int32)
+        for p in range(nn):
+            parent[idx[off[p]:off[p + 1]]] = p
+        desc, w, word = _f32(tree["desc"]), np.ascontiguousarray(tree["weight"], np.float64), _i32(tree["word_id"])
+        leaves = np.nonzero(off[1:] == off[:-1])[0]
+        word_node = np.zeros(len(leaves), np.int32)
+        word_node[word[leaves]] = leaves
+        return cls(vlib().ref_voc_load(int(tree["k"]), int(tree["L"]), int(tree["weighting"]), int(tree["scoring"]), nn,
+                                       _p(parent), _p(desc), _p(w), len(leaves), _p(word_node)))
+
+    def export(self):
+        sizes = np.zeros(6, np.int32)
+        vlib().ref_voc_sizes(self.h, _p(sizes))
+        nn = int(sizes[0])
+        off, idx = np.zeros(nn + 1, np.int32), np.zeros(max(nn - 1, 1), np.int32)
+        desc, w, word = np.zeros((nn, 128), np.float32), np.zeros(nn, np.float64), np.zeros(nn, np.int32)
+        vlib().ref_voc_export(self.h, _p(off), _p(idx), _p(desc), _p(w), _p(word))
+        return dict(k=int(sizes[1]), L=int(sizes[2]), weighting=int(sizes[3]), scoring=int(sizes[4]), child_off=off,
+                    child_idx=idx[:nn - 1], desc=desc, weight=w, word_id=word)
+
+    def transform(self, desc, levelsup=4):
+        desc = _f32(desc)
+        n = len(desc)
+        word, node, order = np.empty(n, np.int32), np.empty(n, np.int32), np.empty(max(n, 1), np.int32)
+        bid, bval = np.empty(max(n, 1), np.uint32), np.empty(max(n, 1), np.float64)
+        nfv = C.c_int32()
+        nb = vlib().ref_voc_transform(self.h, _p(desc), n, levelsup, _p(word), _p(node), _p(order), C.byref(nfv), _p(bid),
+                                      _p(bval))
+        return dict(word_id=word, fv_node=node, fv_order=order[:nfv.value].copy(), bow_id=bid[:nb].copy(),
+                    bow_val=bval[:nb].copy())
+
+    def free(self):
+        if self.h:
+            vlib().ref_voc_free(self.h)
+            self.h = None
+
+
+def fsift_distance(a, b):
+    a, b = _f32(a), _f32(b)
+    return vlib().ref_fsift_distance(_p(a), _p(b))

@@ -8,6 +8,7 @@
 #pragma once
 #include <cassert>
 #include <cmath>
+#include <limits>
 #include <cstring>
 #include <vector>
 
@@ -46,6 +47,8 @@ class Mat {
   }
   int type() const { return type_; }
   bool empty() const { return rows == 0 || cols == 0; }
+  void release() { create(0, 0, type_); }
+  static Mat zeros(int r, int c, int type) { return Mat(r, c, type); }  // create() zero-fills
   Mat clone() const { return *this; }
   template <typename T> T& at(int i, int j) { return data<T>()[(size_t)i * cols + j]; }
   template <typename T> const T& at(int i, int j) const { return data<T>()[(size_t)i * cols + j]; }
@@ -160,3 +163,5 @@ inline Mat operator/(const Mat& a, double s) { return scale(a, 1.0 / s); }
 inline double norm(const Mat& a) { return std::sqrt(a.dot(a)); }
 
 }  // namespace cv
+
+#include "cv_fs_shim.h"
