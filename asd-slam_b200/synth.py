@@ -371,3 +371,59 @@ def config_distinctive(n_kf=12, n=600, n_points=900, seed_extra=0, max_obs=None,
         off.append(len(okf))
     return dict(descs=descs, obs_off=np.asarray(off, np.int32), obs_kf=np.asarray(okf, np.int32),
                 obs_row=np.asarray(orow, np.int32))
+
+
+def vocab_tree(k=10, L=5, seed_extra=0, ragged=0.0, stop_frac=0.05, weighting=0, scoring=0, dup_children=False):
+    """Synthetic DBoW2 vocabulary (flat arrays of include/asdmatch.h asdm_vocab_desc) shaped like the output of
+    TemplatedVocabulary::create (TemplatedVocabulary.h:557-600): a k-ary tree of depth L whose node descriptors are
+    unit-norm perturbations of their parent's, node ids in creation (depth-first) order, word ids over the leaves in
+    ascending node id (createWords, :813-835). ragged: probability that an inner node above level L stays a leaf or
+    loses some children (k-means leaves clusters with one feature unsplit, :700-716); stop_frac: share of words with
+    weight 0 (idf of a word seen in every image); dup_children: some siblings share one descriptor (exact ties)."""
+    rng = rng_for(9, seed_extra)
+    parent, level, desc = [0], [0], [np.zeros(DESC_DIM, np.float32)]
+    children = [[]]
+    stack = [0]
+    while stack:
+        p = stack.pop()
+        if level[p] >= L:
+            continue
+        kp = k
+        if p != 0 and ragged > 0 and rng.random() < ragged:
+            kp = int(rng.integers(0, k))  # 0 = stays a leaf
+        first = None
+        for c in range(kp):
+            nid = len(parent)
+            base = desc[p] if p else np.zeros(DESC_DIM, np.float32)
+            d = base + rng.standard_normal(DESC_DIM).astype(np.float32) * np.float32(0.6 ** level[p])
+            d = (d / np.sqrt((d * d).sum(dtype=np.float32))).astype(np.float32)
+            if dup_children and first is not None and rng.random() < 0.2:
+                d = first.copy()
+            if first is None:
+                first = d
+            parent.append(p); level.append(level[p] + 1); desc.append(d); children.append([])
+            children[p].append(nid)
+        stack.extend(reversed(children[p]))
+    nn = len(parent)
+    off = np.zeros(nn + 1, np.int32)
+    for p in range(nn):
+        off[p + 1] = off[p] + len(children[p])
+    idx = np.array([c for ch in children for c in ch], np.int32)
+    leaves = np.nonzero(off[1:] == off[:-1])[0]
+    word = np.zeros(nn, np.int32)
+    word[leaves] = np.arange(len(leaves), dtype=np.int32)
+    w = np.zeros(nn, np.float64)
+    w[leaves] = rng.uniform(0.1, 5.0, len(leaves))
+    w[leaves[rng.random(len(leaves)) < stop_frac]] = 0.0
+    return dict(k=k, L=L, weighting=weighting, scoring=scoring, child_off=off, child_idx=idx,
+                desc=np.ascontiguousarray(np.stack(desc), np.float32), weight=w, word_id=word)
+
+
+def vocab_queries(tree, n, seed_extra=0, sigma=0.05):
+    """Descriptors near random leaves of `tree` (so the descent has near-ties at every level), unit norm."""
+    rng = rng_for(10, seed_extra)
+    off = tree["child_off"]
+    leaves = np.nonzero(off[1:] == off[:-1])[0]
+    d = tree["desc"][rng.choice(leaves, n)] + rng.standard_normal((n, DESC_DIM)).astype(np.float32) * np.float32(sigma)
+    d /= np.sqrt((d * d).sum(axis=1, keepdims=True, dtype=np.float32))
+    return np.ascontiguousarray(d, np.float32)
