@@ -233,6 +233,14 @@ def distinctive(kf_descs, obs_off, obs_kf, obs_row):
 # ------------------------------------------------------------------ vocabulary tree (oracle/ref_voc_driver.cc)
 _VLIB = os.path.join(_HERE, "_ref", "libref_vocab.so")
 _vlib = None
+_vpath = None
+
+
+def use_voc(path=None):
+    """Route the ref_voc_* calls to another build of ref_voc_driver.cc: the drop-in DeviceVocabulary under test
+    (asd-slam_b200/host/libadaptor_vocab_shim.so). None = the reference."""
+    global _vlib, _vpath
+    _vlib, _vpath = None, path
 
 
 def voc_available():
@@ -242,9 +250,9 @@ def voc_available():
 def vlib():
     global _vlib
     if _vlib is None:
-        if not voc_available():
+        if _vpath is None and not voc_available():
             raise RuntimeError("oracle/_ref/libref_vocab.so is missing and /root/reference is not mounted")
-        _vlib = C.CDLL(_VLIB)
+        _vlib = C.CDLL(_vpath or _VLIB)
         _vlib.ref_voc_train.restype = C.c_void_p
         _vlib.ref_voc_load.restype = C.c_void_p
         _vlib.ref_fsift_distance.restype = C.c_double

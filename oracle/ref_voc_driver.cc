@@ -17,7 +17,14 @@
 #include "TemplatedVocabulary.h"
 #include "FSift.h"
 
+#ifdef ASD_VOC_ADAPTOR
+// the same harness around the product's drop-in vocabulary (asd-slam_b200/host/asdm_vocabulary.h): transform() then
+// runs on the GPU through the C ABI, everything else is still the reference's code
+#include "asdm_vocabulary.h"
+typedef asdm::DeviceVocabulary<DBoW2::FSift::TDescriptor, DBoW2::FSift> RefVocabulary;
+#else
 typedef DBoW2::TemplatedVocabulary<DBoW2::FSift::TDescriptor, DBoW2::FSift> RefVocabulary;  // ORBVocabulary.h:34
+#endif
 
 namespace {
 

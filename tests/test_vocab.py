@@ -197,3 +197,34 @@ def test_vocab_rejects_bad_trees(pkg, ctx):
     assert len(got["word_id"]) == 0 and len(got["bow_id"]) == 0
     s.release()
     voc.release()
+
+
+ADAPTOR = os.path.join(os.path.dirname(HERE), "asd-slam_b200", "host", "libadaptor_vocab_shim.so")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("i", range(len(ALL)), ids=IDS)
+def test_device_vocabulary_adaptor_vs_golden(ctx, i):
+    """asd-slam_b200/host/asdm_vocabulary.h (DeviceVocabulary: the drop-in for `new ORBVocabulary()`, System.cc:114)
+    behind the harness the goldens were made with: the reference's load() fills the tree, the virtual
+    transform(features, BowVector&, FeatureVector&, levelsup) runs on the GPU and fills the caller's std::maps."""
+    if not os.path.exists(ADAPTOR):
+        pytest.skip("libadaptor_vocab_shim.so not built (needs /root/reference at build time)")
+    sys.path.insert(0, os.path.join(os.path.dirname(HERE), "oracle"))
+    import ref_py
+    ref_py.use_voc(ADAPTOR)
+    try:
+        name, tree, q, levels = case_inputs(i)
+        voc = ref_py.RefVocabulary.load(tree)
+        for lu in levels:
+            r = voc.transform(q, lu)
+            g = {k: GOLD[f"{name}/{lu}/{k}"] for k in ("word_id", "fv_node", "fv_order", "bow_id", "bow_val")}
+            assert np.array_equal(r["bow_id"], g["bow_id"]) and np.array_equal(bits64(r["bow_val"]), bits64(g["bow_val"]))
+            assert np.array_equal(r["fv_node"] >= 0, g["fv_node"] >= 0)
+            ok = (g["fv_node"] >= 0) & V.leaf_depth_reaches(tree, g["word_id"], int(tree["L"]) - lu)
+            assert np.array_equal(r["fv_node"][ok], g["fv_node"][ok])
+            if ok.sum() == (g["fv_node"] >= 0).sum():
+                assert np.array_equal(r["fv_order"], g["fv_order"])
+        voc.free()
+    finally:
+        ref_py.use_voc(None)

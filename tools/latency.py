@@ -132,6 +132,20 @@ def measure(pkg, ctx, reps=200, cpu=True, oracle=None):
                                                                            c["prev_matched"], c["window"], 0.9, 1), n=1)
     out["init_SearchForInitialization_4000_w100"] = r
     F1.release(); F2.release()
+
+    # ---- Frame::ComputeBoW: vocabulary transform of 2000 / 4000 features, k=10 L=5 (DBoW2 default shape), levelsup 4
+    tree = syn.vocab_tree(k=10, L=5, seed_extra=30)
+    voc = pkg.ORBVocabulary(ctx, tree)
+    for n in (2000, 4000):
+        qd = syn.vocab_queries(tree, n, seed_extra=31, sigma=0.08)
+        S = pkg.DescriptorSet(ctx, qd)
+        r = timeit(lambda: voc.transform(S, 4), reps)
+        r["launches"] = ctx.stat("gpu_launches")
+        r["device_only_ms"] = timeit(lambda: (voc.transform(S, 4, host=False), ctx.synchronize()), reps)["median_ms"]
+        r["cpu_oracle_ms"] = cpu_time(lambda: oracle.voc_transform(tree, qd, 4))
+        out[f"ComputeBoW_transform_{n}_k10_L5"] = r
+        S.release()
+    voc.release()
     return out
 
 
