@@ -30,7 +30,7 @@ EXPORTS = [
     "asdm_create", "asdm_destroy", "asdm_last_error", "asdm_stream", "asdm_synchronize", "asdm_set_stream",
     "asdm_host_alloc", "asdm_host_free", "asdm_set_option", "asdm_get_stat",
     "asdm_set_create", "asdm_set_create_async", "asdm_set_retain", "asdm_set_release", "asdm_set_size", "asdm_set_featvec",
-    "asdm_set_read_desc",
+    "asdm_set_read_desc", "asdm_desc_block_bytes", "asdm_set_save_blocks", "asdm_set_load_block",
     "asdm_search_by_bow_kf_f", "asdm_search_by_bow_kf_kf", "asdm_search_for_triangulation",
     "asdm_search_by_projection", "asdm_search_by_projection_q", "asdm_search_for_initialization", "asdm_stereo_row_match",
     "asdm_job_prepare", "asdm_job_run", "asdm_job_fetch", "asdm_job_settle", "asdm_job_out_stride",
@@ -123,6 +123,10 @@ def load():
     lib.asdm_job_device_outputs.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
     lib.asdm_job_destroy.argtypes = [vp]
     lib.asdm_distinctive_descriptors.argtypes = [vp, C.POINTER(vp), C.c_int, C.c_int, vp, vp, vp, vp, vp]
+    lib.asdm_desc_block_bytes.argtypes = [C.c_int]
+    lib.asdm_desc_block_bytes.restype = C.c_size_t
+    lib.asdm_set_save_blocks.argtypes = [vp, C.POINTER(vp), C.c_int, vp, C.c_size_t, vp]
+    lib.asdm_set_load_block.argtypes = [vp, vp, C.c_size_t, vp, C.POINTER(Grid), C.POINTER(vp), C.POINTER(C.c_size_t)]
     lib.asdm_vocab_create.argtypes = [vp, C.POINTER(VocabDesc), C.POINTER(vp)]
     lib.asdm_vocab_release.argtypes = [vp]
     lib.asdm_vocab_transform.argtypes = [vp, vp, vp, C.c_int, vp, vp, vp, C.POINTER(i32), vp, vp]

@@ -509,6 +509,53 @@ extern "C" int asdm_set_read_desc(asdm_set* s, int row0, int n_rows, float* out)
   return ASDM_OK;
 }
 
+// chamo.map descriptor blocks (visual_map_seri.cc:134-146 / :272-285): [int32 128][int32 n][n x 128 fp32]
+extern "C" size_t asdm_desc_block_bytes(int n) {
+  return n < 0 ? 0 : 8 + (size_t)n * ASDM_DESC_DIM * sizeof(float);
+}
+
+extern "C" int asdm_set_save_blocks(asdm_ctx* ctx, asdm_set* const* sets, int n_sets, void* out, size_t cap,
+                                    size_t* offsets) {
+  if (!ctx || n_sets < 0 || (n_sets > 0 && (!sets || !out))) return ASDM_ERR_INVALID;
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  CK(cudaSetDevice(ctx->device));
+  size_t off = 0;
+  for (int k = 0; k < n_sets; k++) {
+    if (!sets[k] || sets[k]->ctx != ctx) return fail(ctx, ASDM_ERR_INVALID, "set of another context");
+    off += asdm_desc_block_bytes(sets[k]->n);
+  }
+  if (off > cap) return fail(ctx, ASDM_ERR_INVALID, "output buffer too small for the descriptor blocks");
+  off = 0;
+  for (int k = 0; k < n_sets; k++) {
+    const asdm_set* s = sets[k];
+    if (offsets) offsets[k] = off;
+    const int32_t hdr[2] = {ASDM_DESC_DIM, s->n};
+    memcpy((char*)out + off, hdr, 8);
+    if (s->n)
+      CK(cudaMemcpyAsync((char*)out + off + 8, s->desc, (size_t)s->n * ASDM_DESC_DIM * sizeof(float), cudaMemcpyDeviceToHost,
+                         ctx->stream));
+    off += asdm_desc_block_bytes(s->n);
+  }
+  if (offsets) offsets[n_sets] = off;
+  CK(cudaStreamSynchronize(ctx->stream));
+  synced(ctx);
+  return ASDM_OK;
+}
+
+extern "C" int asdm_set_load_block(asdm_ctx* ctx, const void* block, size_t bytes, const asdm_kp* kps,
+                                   const asdm_grid* grid, asdm_set** out, size_t* consumed) {
+  if (!ctx || !block || !out) return ASDM_ERR_INVALID;
+  if (bytes < 8) return fail(ctx, ASDM_ERR_INVALID, "descriptor block truncated (no header)");
+  int32_t hdr[2];
+  memcpy(hdr, block, 8);
+  if (hdr[0] != ASDM_DESC_DIM) return fail(ctx, ASDM_ERR_INVALID, "descriptor block is not 128 floats wide (not an ASD map)");
+  if (hdr[1] < 0 || asdm_desc_block_bytes(hdr[1]) > bytes) return fail(ctx, ASDM_ERR_INVALID, "descriptor block truncated");
+  // the payload starts 8 bytes into the block: rows are only 4-byte aligned in the file, which the copy engine accepts
+  const int rc = set_create_impl(ctx, (const float*)((const char*)block + 8), hdr[1], 0, kps, grid, out, false);
+  if (rc == ASDM_OK && consumed) *consumed = asdm_desc_block_bytes(hdr[1]);
+  return rc;
+}
+
 // ------------------------------------------------------------------------------- batched keyframe-pair jobs
 struct asdm_job {
   asdm_ctx* ctx = nullptr;

@@ -134,6 +134,25 @@ class DescriptorSet:
         self.ctx.check(self.ctx.lib.asdm_set_read_desc(self.h, row0, n_rows, ptr(out)))
         return out
 
+    @classmethod
+    def from_map_block(cls, ctx, block, kps=None, grid=None):
+        """Set from the descriptor block of a chamo.map frame (visual_map_seri.cc:272-285). Returns (set, bytes used).
+        `block`: uint8 array starting at the block; it must stay alive until the next synchronising call."""
+        self = cls.__new__(cls)
+        self.ctx = ctx
+        block = np.ascontiguousarray(block, np.uint8)
+        g = None
+        if grid is not None:
+            g = grid if isinstance(grid, Grid) else Grid(*grid)
+        if kps is not None:
+            kps = np.ascontiguousarray(kps, dtype=KP_DTYPE)
+        h, used = C.c_void_p(), C.c_size_t()
+        ctx.check(ctx.lib.asdm_set_load_block(ctx.h, ptr(block), block.nbytes, ptr(kps) if kps is not None else None,
+                                              C.byref(g) if g is not None else None, C.byref(h), C.byref(used)))
+        self.h, self._desc_keepalive = h, block
+        self.n = ctx.lib.asdm_set_size(h)
+        return self, used.value
+
     def retain(self):
         self.ctx.lib.asdm_set_retain(self.h)
 
@@ -350,6 +369,17 @@ def ComputeDistinctiveDescriptors(ctx, sets, obs_off, obs_set, obs_row):
     arr = (C.c_void_p * max(len(sets), 1))(*[s.h for s in sets])
     ctx.check(ctx.lib.asdm_distinctive_descriptors(ctx.h, arr, len(sets), n, ptr(off), ptr(st), ptr(row), ptr(best), ptr(med)))
     return best, med
+
+
+def save_map_blocks(ctx, sets):
+    """Descriptor blocks of `sets`, back to back, as vm::save_visual_map writes them (visual_map_seri.cc:134-146).
+    Returns (uint8 array, offsets)."""
+    total = sum(ctx.lib.asdm_desc_block_bytes(s.n) for s in sets)
+    out = np.empty(total, np.uint8)
+    offs = np.zeros(len(sets) + 1, np.uint64)
+    hs = (C.c_void_p * len(sets))(*[s.h for s in sets])
+    ctx.check(ctx.lib.asdm_set_save_blocks(ctx.h, hs, len(sets), ptr(out), total, ptr(offs)))
+    return out, offs.astype(np.int64)
 
 
 # DBoW2 enums (src/dbow2/include/BowVector.h:36-53)

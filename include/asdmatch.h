@@ -116,6 +116,23 @@ int asdm_set_featvec(asdm_set* set, const asdm_featvec* fv);
 /* reads rows back (map save / checkpoint: System.cc:296-439 writes descriptors from host Mats) */
 int asdm_set_read_desc(asdm_set* set, int row0, int n_rows, float* out);
 
+/* Map save / load. The descriptor block of one frame inside the reference's binary map file `chamo.map`
+ * (vm::save_visual_map, src/visual_map/src/visual_map_seri.cc:134-146; vm::loader_visual_map, :272-285) is
+ *     int32 desc_width (= 128)   int32 desc_count (= N)   N x 128 fp32, descriptor after descriptor
+ * (System::saveToVisualMap fills the column-major Eigen D x N matrix from mDescriptors, System.cc:335-343): byte for
+ * byte the resident rows, so saving is one device-to-host copy behind an 8-byte header and loading is one upload.
+ * asdm_set_save_blocks writes the blocks of n_sets sets back to back into `out` (all copies queued, one wait);
+ * offsets[k] (n_sets + 1 entries, may be NULL) receives where block k starts. Returns ASDM_ERR_INVALID when cap is too
+ * small (asdm_desc_block_bytes says how much a set of n descriptors needs). */
+size_t asdm_desc_block_bytes(int n);
+int asdm_set_save_blocks(asdm_ctx* ctx, asdm_set* const* sets, int n_sets, void* out, size_t cap, size_t* offsets);
+/* Creates a set from one block (the float descriptors System::LoadORBMap should hand to KeyFrame::setData; the
+ * reference converts them to CV_8UC1 there, System.cc:64-69, which is stale ORB code). *consumed = bytes of the block.
+ * Fails with ASDM_ERR_INVALID on a truncated block or desc_width != 128. Asynchronous like asdm_set_create_async:
+ * `block` must stay valid until the next synchronising call. */
+int asdm_set_load_block(asdm_ctx* ctx, const void* block, size_t bytes, const asdm_kp* kps, const asdm_grid* grid,
+                        asdm_set** out, size_t* consumed);
+
 /* --------------------------------------------------------------------------- BoW-gated dense search */
 /* ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches)  (ORBmatcher.cc:156-297).
  * valid_kf[i]: KF feature i holds a map point that is not bad.

@@ -798,6 +798,40 @@ int ora_voc_transform(int L, int weighting, int scoring, int n_nodes, const int3
   return k;
 }
 
+long ora_map_write_block(const float* desc, int n, int d, uint8_t* out) {
+  // System.cc:337-343: descriptors(j, k) = mDescriptors.at<float>(k, j) into a column-major D x N matrix
+  std::vector<float> m((size_t)d * n);
+  for (int j = 0; j < d; j++)
+    for (int k = 0; k < n; k++) m[(size_t)j + (size_t)k * d] = desc[(size_t)k * d + j];
+  // visual_map_seri.cc:134-146
+  long pos = 0;
+  const int32_t width = d, count = n;
+  memcpy(out + pos, &width, 4); pos += 4;
+  memcpy(out + pos, &count, 4); pos += 4;
+  for (int j = 0; j < count; j++)
+    for (int k = 0; k < width; k++) {
+      memcpy(out + pos, &m[(size_t)k + (size_t)j * d], 4);
+      pos += 4;
+    }
+  return pos;
+}
+
+int ora_map_read_block(const uint8_t* block, long bytes, float* rows, int cap_rows, int* width) {
+  if (bytes < 8) return -1;
+  int32_t w, c;  // visual_map_seri.cc:272-273
+  memcpy(&w, block, 4);
+  memcpy(&c, block + 4, 4);
+  if (w < 0 || c < 0 || 8 + (long)w * c * 4 > bytes) return -1;
+  *width = w;
+  long pos = 8;
+  for (int j = 0; j < c; j++)  // :275-285
+    for (int k = 0; k < w; k++) {
+      if (j < cap_rows) memcpy(&rows[(size_t)j * w + k], block + pos, 4);
+      pos += 4;
+    }
+  return c;
+}
+
 int ora_max_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();

@@ -205,6 +205,14 @@ int ora_voc_transform(int L, int weighting, int scoring, int n_nodes, const int3
                       const float* node_desc, const double* weight, const int32_t* word_of_node, const float* desc, int n,
                       int levelsup, int32_t* word_id, int32_t* node_id, uint8_t* in_fv, uint32_t* bow_id, double* bow_val);
 
+/* chamo.map descriptor block of one frame: System::saveToVisualMap (System.cc:333-343) copies mDescriptors (N x 128
+ * CV_32F) into the column-major Eigen matrix descriptors(D, N); vm::save_visual_map writes int32 rows() (= D), int32
+ * cols() (= N) and then descriptors(k, j) for j outer, k inner (visual_map_seri.cc:134-146); vm::loader_visual_map
+ * reads the same back (:272-285). ora_map_write_block returns the bytes written (8 + 512 N); ora_map_read_block
+ * returns N (or -1 when the block is truncated) and stores D in *width; rows[j*D + k] = descriptors(k, j). */
+long ora_map_write_block(const float* desc, int n, int d, uint8_t* out);
+int ora_map_read_block(const uint8_t* block, long bytes, float* rows, int cap_rows, int* width);
+
 int ora_max_threads(void);
 
 #ifdef __cplusplus

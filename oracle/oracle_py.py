@@ -316,3 +316,28 @@ def voc_transform(tree, desc, levelsup=4):
            _p(off), _p(idx), _p(nd), _p(w), _p(word), _p(desc), C.c_int(n), C.c_int(int(levelsup)), _p(word_id),
            _p(node_id), _p(inc), _p(bid), _p(bval))
     return dict(word_id=word_id, node_id=node_id, in_fv=inc, bow_id=bid[:nb].copy(), bow_val=bval[:nb].copy())
+
+
+def map_write_block(desc):
+    """Descriptor block of one frame in chamo.map (System.cc:333-343 + visual_map_seri.cc:134-146) as bytes."""
+    desc = _f32(desc)
+    n, d = desc.shape
+    out = np.empty(8 + n * d * 4, np.uint8)
+    f = lib().ora_map_write_block
+    f.restype = C.c_long
+    nb = f(_p(desc), C.c_int(n), C.c_int(d), _p(out))
+    assert nb == len(out)
+    return out
+
+
+def map_read_block(block):
+    """vm::loader_visual_map's descriptor block reader (visual_map_seri.cc:272-285): returns the N x D float rows."""
+    block = np.ascontiguousarray(block, np.uint8)
+    w = C.c_int()
+    f = lib().ora_map_read_block
+    n = f(_p(block), C.c_long(len(block)), None, C.c_int(0), C.byref(w))
+    if n < 0:
+        return None
+    rows = np.empty((n, w.value), np.float32)
+    f(_p(block), C.c_long(len(block)), _p(rows), C.c_int(n), C.byref(w))
+    return rows

@@ -315,3 +315,30 @@ class RefVocabulary:
 def fsift_distance(a, b):
     a, b = _f32(a), _f32(b)
     return vlib().ref_fsift_distance(_p(a), _p(b))
+
+
+# ------------------------------------------------------------------ chamo.map descriptor blocks (oracle/ref_map_driver.cc)
+_MLIB = os.path.join(_HERE, "_ref", "libref_map.so")
+
+
+def map_available():
+    return os.path.exists(_MLIB) or (build() and os.path.exists(_MLIB))
+
+
+def map_write_block(desc, path):
+    """System::saveToVisualMap + vm::save_visual_map, the reference's own loops; returns the file's bytes."""
+    desc = _f32(desc)
+    m = C.CDLL(_MLIB)
+    m.ref_map_write_block.restype = C.c_long
+    nb = m.ref_map_write_block(_p(desc), len(desc), path.encode())
+    data = np.fromfile(path, np.uint8)
+    assert nb == len(data)
+    return data
+
+
+def map_read_block(path, cap_rows):
+    m = C.CDLL(_MLIB)
+    rows = np.zeros((max(cap_rows, 1), 128), np.float32)
+    dims = np.zeros(2, np.int32)
+    n = m.ref_map_read_block(path.encode(), _p(rows), cap_rows, _p(dims))
+    return rows[:n], dims
