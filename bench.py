@@ -135,6 +135,15 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------------------------- CPU arms
+def host_threads():
+    """Host cores this process may use. torchrun exports OMP_NUM_THREADS=1 to every rank, which would throttle the
+    CPU arm to one thread at N>1; only rank 0 runs CPU work, so it takes the whole affinity mask."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_sample(oracle, c, pairs, threads):
     """Times the CPU oracle (port of the reference matcher) on the first `pairs` pairs of the workload."""
     ia, ib = c["ia"][:pairs], c["ib"][:pairs]
@@ -152,7 +161,7 @@ def run_reference(args):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle_py as oracle  # the one place outside tests/smoke where bench.py executes oracle/: the reference arm
     oracle.build()
-    threads = oracle.max_threads()
+    threads = host_threads()
     c = make_inputs(pkg, 0)
     n = N_DESC
     dt1, _, _ = cpu_sample(oracle, c, threads, threads)  # calibration + first warm-up
@@ -343,7 +352,7 @@ def run_ours(args):
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
         import oracle_py as oracle  # cpu_baseline leg only
         oracle.build()
-        threads = oracle.max_threads()
+        threads = host_threads()
         c0 = dict(c, ia=g_ia, ib=g_ib)  # the first pairs of the GLOBAL sweep: at N>1 they belong to different ranks
         cpu_pairs = int(min(P, max(threads, 8)))
         dtc, onm, omatch = cpu_sample(oracle, c0, cpu_pairs, threads)
