@@ -51,20 +51,63 @@ static void dev_free(asdm_ctx* ctx, void* p) {
   if (p && cudaFreeAsync(p, ctx->stream) != cudaSuccess) cudaGetLastError();
 }
 
+// size classes of the block cache: 4 per octave (waste <= 25 %), at least 4 KB
+static size_t block_class(size_t bytes) {
+  size_t c = 4096;
+  while (c < bytes) {
+    const size_t q = c / 4;
+    for (int k = 1; k <= 4; k++)
+      if (c + q * k >= bytes) return c + q * k;
+    c *= 2;
+  }
+  return c;
+}
+static const size_t BLOCK_CACHE_LIMIT = (size_t)8 << 30;
+
+static void block_put(asdm_ctx* ctx, void* p, size_t cap) {
+  if (!p) return;
+  if (ctx->block_cache_bytes + cap > BLOCK_CACHE_LIMIT) {
+    dev_free(ctx, p);
+    return;
+  }
+  ctx->block_cache[cap].push_back(p);
+  ctx->block_cache_bytes += cap;
+}
+
+static void block_cache_flush(asdm_ctx* ctx) {
+  for (auto& kv : ctx->block_cache)
+    for (void* p : kv.second) dev_free(ctx, p);
+  ctx->block_cache.clear();
+  ctx->block_cache_bytes = 0;
+}
+
 static int ensure(asdm_ctx* ctx, DevBuf& b, size_t bytes) {
   if (bytes <= b.cap) return ASDM_OK;
-  dev_free(ctx, b.p);  // stream-ordered: kernels already queued on the old buffer finish first
+  block_put(ctx, b.p, b.cap);  // stream order: kernels already queued on the old block finish before any reuse
   b.p = nullptr;
   b.cap = 0;
-  size_t want = std::max(bytes, (size_t)4096);
-  want = (want + 255) & ~(size_t)255;
-  CK(dev_alloc(ctx, &b.p, want));
+  const size_t want = block_class(std::max(bytes, (size_t)4096));
+  auto it = ctx->block_cache.find(want);
+  if (it != ctx->block_cache.end() && !it->second.empty()) {
+    b.p = it->second.back();
+    it->second.pop_back();
+    ctx->block_cache_bytes -= want;
+    b.cap = want;
+    return ASDM_OK;
+  }
+  cudaError_t e = dev_alloc(ctx, &b.p, want);
+  if (e == cudaErrorMemoryAllocation) {  // give the cached blocks back and try once more
+    cudaGetLastError();
+    block_cache_flush(ctx);
+    e = dev_alloc(ctx, &b.p, want);
+  }
+  CK(e);
   b.cap = want;
   return ASDM_OK;
 }
 
 static void release(asdm_ctx* ctx, DevBuf& b) {
-  dev_free(ctx, b.p);
+  block_put(ctx, b.p, b.cap);
   b.p = nullptr;
   b.cap = 0;
 }
@@ -150,7 +193,9 @@ extern "C" int asdm_create(int device, asdm_ctx** out) {
   ctx->device = device;
   if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaStreamCreateWithFlags(&ctx->upload_stream, cudaStreamNonBlocking) != cudaSuccess ||
-      cudaEventCreateWithFlags(&ctx->upload_done, cudaEventDisableTiming) != cudaSuccess) {
+      cudaStreamCreateWithFlags(&ctx->prep_stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&ctx->upload_done, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&ctx->prep_done, cudaEventDisableTiming) != cudaSuccess) {
     cudaGetLastError();
     delete ctx;
     return ASDM_ERR_CUDA;
@@ -185,6 +230,7 @@ extern "C" int asdm_destroy(asdm_ctx* ctx) {
   if (!ctx) return ASDM_ERR_INVALID;
   cudaSetDevice(ctx->device);
   for (auto& b : ctx->scratch) release(ctx, b);
+  block_cache_flush(ctx);
   cudaStreamSynchronize(ctx->stream);
   for (cudaEvent_t e : ctx->ev) cudaEventDestroy(e);
   if (ctx->stage) cudaFreeHost(ctx->stage);
@@ -192,6 +238,8 @@ extern "C" int asdm_destroy(asdm_ctx* ctx) {
   if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
   if (ctx->upload_stream) cudaStreamDestroy(ctx->upload_stream);
   if (ctx->upload_done) cudaEventDestroy(ctx->upload_done);
+  if (ctx->prep_stream) cudaStreamDestroy(ctx->prep_stream);
+  if (ctx->prep_done) cudaEventDestroy(ctx->prep_done);
   delete ctx;
   return ASDM_OK;
 }
@@ -299,6 +347,20 @@ static void set_free(asdm_set* s) {
   delete s;
 }
 
+// Frame::AssignFeaturesToGrid (Frame.cc:123-138) on the device, on first use: only the projection-gated searches read
+// the bucket, so keyframes that only ever meet BoW-gated searches (loop-closure sweeps) never pay for it.
+static int ensure_grid(asdm_ctx* ctx, asdm_set* s) {
+  if (!s->has_grid || s->grid_built) return ASDM_OK;
+  const int nc = s->grid.cols * s->grid.rows;
+  const size_t smem = (size_t)(nc + 1) * sizeof(int32_t);
+  if (smem > 48 * 1024) cudaFuncSetAttribute(k_build_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  k_build_grid<<<1, 1024, smem, ctx->stream>>>(s->kps, s->n, s->grid, s->cell_tmp, s->cell_start, s->cell_items);
+  LAUNCHED(ctx);
+  CK(cudaGetLastError());
+  s->grid_built = true;
+  return ASDM_OK;
+}
+
 // reads the tensor-core range flags of sets whose flag copy is still in flight (one stream wait for all of them)
 static int resolve_tc_flags(asdm_ctx* ctx, asdm_set* const* sets, int n) {
   bool pending = false;
@@ -390,29 +452,33 @@ static int set_create_impl(asdm_ctx* ctx, const float* desc, int n, int row_stri
       CKS(cudaMemcpy2DAsync(s->desc, ASDM_DESC_DIM * sizeof(float), desc, row_stride_bytes,
                             ASDM_DESC_DIM * sizeof(float), n, cudaMemcpyHostToDevice, ctx->upload_stream));
   }
+  // Preparation (bf16 copy, norms, range flag) runs on its own stream behind the upload, so the copy engine moves on
+  // to the next keyframe at once and searches already queued on the main stream are not in its way.
   CKS(cudaEventRecord(ctx->upload_done, ctx->upload_stream));
-  CKS(cudaStreamWaitEvent(ctx->stream, ctx->upload_done, 0));  // everything below is ordered after the upload
-  if (n > 0 && desc_on_device)
+  CKS(cudaStreamWaitEvent(ctx->prep_stream, ctx->upload_done, 0));
+  if (n > 0 && desc_on_device) {  // the producer of device-resident rows was queued on the main stream
+    CKS(cudaEventRecord(ctx->prep_done, ctx->stream));
+    CKS(cudaStreamWaitEvent(ctx->prep_stream, ctx->prep_done, 0));
     CKS(cudaMemcpy2DAsync(s->desc, ASDM_DESC_DIM * sizeof(float), desc, row_stride_bytes, ASDM_DESC_DIM * sizeof(float), n,
-                          cudaMemcpyDeviceToDevice, ctx->stream));
-  CKS(cudaMemsetAsync(s->d_flags, 0, 256, ctx->stream));
+                          cudaMemcpyDeviceToDevice, ctx->prep_stream));
+  }
+  CKS(cudaMemsetAsync(s->d_flags, 0, 256, ctx->prep_stream));
   if (s->n_pad > n)
     CKS(cudaMemsetAsync(s->desc + (size_t)n * ASDM_DESC_DIM, 0, (size_t)(s->n_pad - n) * ASDM_DESC_DIM * sizeof(float),
-                        ctx->stream));
+                        ctx->prep_stream));
   ctx->stat_launches = 0;
-  k_pack_desc<<<(s->n_pad * 32 + 255) / 256, 256, 0, ctx->stream>>>(s->desc, n, s->n_pad, s->desc_bf, s->norm2, s->d_flags);
+  k_pack_desc<<<(s->n_pad * 32 + 255) / 256, 256, 0, ctx->prep_stream>>>(s->desc, n, s->n_pad, s->desc_bf, s->norm2, s->d_flags);
   LAUNCHED(ctx);
   s->h_flag = slot_get(ctx);  // the range flag travels back behind the kernel; read when a job first needs it
-  if (s->h_flag) CKS(cudaMemcpyAsync(s->h_flag, s->d_flags, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
-  if (grid) {
+  if (s->h_flag) CKS(cudaMemcpyAsync(s->h_flag, s->d_flags, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->prep_stream));
+  CKS(cudaEventRecord(ctx->prep_done, ctx->prep_stream));
+  CKS(cudaStreamWaitEvent(ctx->stream, ctx->prep_done, 0));  // whatever is queued on the main stream from here on sees the set
+  if (grid) {  // the grid bucket itself is built by the first projection-gated search (ensure_grid)
     s->grid = *grid;
     s->has_grid = true;
     s->cell_start = (int32_t*)(base + o_cs);
     s->cell_items = (int32_t*)(base + o_ci);
-    const size_t smem = (size_t)(nc + 1) * sizeof(int32_t);
-    if (smem > 48 * 1024) cudaFuncSetAttribute(k_build_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_build_grid<<<1, 1024, smem, ctx->stream>>>(s->kps, n, *grid, (int32_t*)(base + o_tmp), s->cell_start, s->cell_items);
-    LAUNCHED(ctx);
+    s->cell_tmp = (int32_t*)(base + o_tmp);
   }
   CKS(cudaGetLastError());
   if (wait || !s->h_flag) {  // the caller's descriptor buffer may be reused as soon as we return
@@ -576,6 +642,7 @@ struct asdm_job {
   int n_seg = 0, seg_cap = 0;
   float t_keep_tc = 0.f;
   bool ran = false;
+  bool tc_pending = false;     // tensor-core route taken before every set's range flag was back (validated in settle)
   int32_t* h_flags = nullptr;  // pinned, 8 ints: [0] cand overflow, [1] list overflow, [2] list count
   bool h_flags_owned = false;  // true when the context's slot slab was exhausted and the job allocated its own
 };
@@ -731,8 +798,20 @@ static int job_prepare(asdm_ctx* ctx, const asdm_job_desc* d, int kind_internal,
 
   // tensor-core shortlist only when every set passed the range check of k_pack_desc
   if (!ctx->opt_force_exact && d->n_pairs > 0) {
-    if ((rc = resolve_tc_flags(ctx, d->sets, d->n_kf))) return bail(rc);
-    for (int k = 0; k < d->n_kf; k++) all_tc &= d->sets[k]->tc_ok;
+    // The range flag of a set travels back behind its k_pack_desc. When some flags are still in flight (keyframes
+    // uploaded asynchronously just before this call) the job does not wait for them: it takes the tensor-core route
+    // speculatively and job_settle() checks the flags once the run has finished anyway (a raised flag = rerun on the
+    // exact route; results are only ever taken from a validated run). So preparing and launching a job never blocks
+    // on uploads that are still crossing PCIe -- later keyframes keep streaming in while this job computes.
+    bool pending = false;
+    for (int k = 0; k < d->n_kf; k++) pending |= d->sets[k]->tc_ok < 0;
+    if (pending && cudaStreamQuery(ctx->stream) == cudaSuccess) {  // nothing in flight: the flags are already here
+      if ((rc = resolve_tc_flags(ctx, d->sets, d->n_kf))) return bail(rc);
+      pending = false;
+    }
+    cudaGetLastError();  // cudaErrorNotReady from the query is not an error
+    for (int k = 0; k < d->n_kf; k++) all_tc &= d->sets[k]->tc_ok != 0;
+    j->tc_pending = pending && all_tc;
     if (all_tc) {
       // work units: one resident 256-row B tile x a run of 128-row A tiles; split runs until the grid is full
       std::vector<TcWork> work;
@@ -882,6 +961,19 @@ static int job_settle(asdm_job* j) {
     CK(cudaMemcpyAsync(j->h_flags, j->d_flags.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     synced(ctx);
+    if (j->tc_pending) {  // the stream is idle now, so every set's flag copy has landed
+      j->tc_pending = false;
+      int rc = resolve_tc_flags(ctx, j->sets.data(), (int)j->sets.size());
+      if (rc) return rc;
+      bool all_tc = true;
+      for (asdm_set* s : j->sets) all_tc &= s->tc_ok != 0;
+      if (!all_tc && j->use_tc) {  // speculation failed: some descriptors are outside the shortlist's proven range
+        j->use_tc = 0;
+        ctx->stat_retries++;
+        if ((rc = job_alloc_scratch(j)) || (rc = job_run(j))) return rc;
+        continue;
+      }
+    }
     const bool cand_over = j->h_flags[0] != 0, list_over = j->h_flags[1] != 0;
     ctx->stat_tc_pairs = j->use_tc ? j->h_flags[2] : 0;
     if (!cand_over && !list_over) return ASDM_OK;
@@ -1044,6 +1136,10 @@ struct ProjDev {
 static int proj_candidates(asdm_ctx* ctx, asdm_set* target, int nq, const float* d_desc_q, const int32_t* d_q_rows,
                            const ProjGate& gate, int* ent_cap_io, ProjDev* out) {
   int ent_cap = std::max(*ent_cap_io, 1 << 14);
+  {
+    const int rc = ensure_grid(ctx, target);
+    if (rc) return rc;
+  }
   for (int attempt = 0; attempt < 20; attempt++) {
     int rc;
     if ((rc = ensure(ctx, ctx->scratch[SC_SEG], (size_t)std::max(nq, 1) * sizeof(ProjSeg)))) return rc;

@@ -5,6 +5,7 @@
 #include <stdint.h>
 
 #include <atomic>
+#include <map>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -28,6 +29,17 @@ struct asdm_ctx {
   // descriptor uploads ride their own stream so the DMA of keyframe k+1 overlaps the pack / grid kernels of keyframe k
   cudaStream_t upload_stream = nullptr;
   cudaEvent_t upload_done = nullptr;
+  // ... and the per-set preparation (bf16 copy, norms, range flag) a third one, so that neither the copy engine nor the
+  // search kernels on the main stream wait behind it: searches of earlier keyframes overlap the upload AND the packing
+  // of later ones (StreamedPairSweep). The main stream waits for prep_done of every set at creation time, so any
+  // search queued later is ordered after the sets it may touch.
+  cudaStream_t prep_stream = nullptr;
+  cudaEvent_t prep_done = nullptr;
+  // Scratch blocks of jobs / calls (DevBuf) are recycled through this cache instead of going back to the driver pool:
+  // they are only ever touched on the context stream, so stream order makes the reuse safe, and a job costs no
+  // cudaMallocAsync / cudaFreeAsync calls in steady state. Keyed by size class.
+  std::map<size_t, std::vector<void*>> block_cache;
+  size_t block_cache_bytes = 0;
   std::recursive_mutex mu;
   std::string err;
   int opt_force_exact = 0;
@@ -74,6 +86,8 @@ struct asdm_set {
   asdm_grid grid{};
   int32_t* cell_start = nullptr;  // [cols*rows+1]
   int32_t* cell_items = nullptr;  // [n] insertion (index) order inside a cell
+  int32_t* cell_tmp = nullptr;    // [n] scratch of k_build_grid
+  bool grid_built = false;        // the grid bucket is built by the first projection-gated search that needs it
   uint32_t* node_id = nullptr;    // [n] FeatureVector node of the feature
   int32_t* fv_pos = nullptr;      // [n] CSR position of the feature in the FeatureVector, -1 if absent
   std::vector<uint8_t> tmap_bf;   // CUtensorMap (128 B) over desc_bf, built lazily

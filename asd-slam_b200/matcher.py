@@ -217,6 +217,53 @@ class PairJob:
             self.h = None
 
 
+class StreamedPairSweep:
+    """Keyframe-pair sweep over keyframes that are NOT yet resident (a cold loop-closure sweep, or a map being loaded):
+    keyframes are uploaded in index order and pairs are searched in readiness order, so the search of the pairs whose
+    keyframes have arrived overlaps the PCIe upload of the later ones. Pairs are dealt into waves by max(ia, ib):
+    wave w holds the pairs whose later keyframe lies in [bounds[w-1], bounds[w]) and is launched as soon as those
+    keyframes are queued (asdm_job_prepare never waits for uploads in flight). Results come back in readiness order:
+    row r of the outputs belongs to pair `order[r]` (the caller indexes, nothing is permuted on the host)."""
+
+    def __init__(self, ctx, kind, n_kf, ia, ib, nnratio=0.6, check_ori=True, bounds=None, **job_kw):
+        self.ctx, self.kind, self.n_kf = ctx, kind, int(n_kf)
+        self.ia, self.ib = _i32(ia), _i32(ib)
+        self.nnratio, self.check_ori, self.job_kw = nnratio, check_ori, job_kw
+        if bounds is None:
+            # waves shrink towards the end: the last one (after the last upload) is all that is not hidden.
+            # pairs with max < b are a (b/n)^2 share of a uniform sweep
+            bounds = sorted({max(2, int(round(self.n_kf * f))) for f in (0.42, 0.62, 0.77, 0.88, 0.95, 1.0)})
+        self.bounds = [int(b) for b in bounds]
+        assert self.bounds[-1] == self.n_kf
+        later = np.maximum(self.ia, self.ib)
+        self.order = np.argsort(later, kind="stable").astype(np.int64)
+        cuts = np.searchsorted(later[self.order], self.bounds, side="left")
+        self.slices = [(int(a), int(b)) for a, b in zip(np.concatenate(([0], cuts[:-1])), cuts)]
+        self._per_pair = {k: (np.asarray(v).reshape(len(self.ia), -1) if k in ("F12", "epipoles", "row_begin", "row_end") else v)
+                          for k, v in job_kw.items()}
+
+    def run(self, make_set, masks, match, dist, nm):
+        """make_set(k) -> DescriptorSet of keyframe k with its FeatureVector attached (uploaded asynchronously).
+        match / dist: (n_pairs, stride) arrays, nm: (n_pairs,), ideally page-locked. Returns the sets (caller releases)."""
+        sets, jobs, done = [], [], 0
+        for (a, b), bound in zip(self.slices, self.bounds):
+            while done < bound:
+                sets.append(make_set(done))
+                done += 1
+            if b <= a:
+                continue
+            sel = self.order[a:b]
+            kw = {k: (v[sel] if k in ("F12", "epipoles", "row_begin", "row_end") else v) for k, v in self._per_pair.items()}
+            jb = PairJob(self.ctx, self.kind, sets[:bound], masks[:bound], self.ia[sel], self.ib[sel], self.nnratio,
+                         self.check_ori, **kw)
+            jb.run()
+            jobs.append((jb, a, b))
+        for jb, a, b in jobs:  # waves finish in launch order; each fetch drains one
+            jb.fetch(match[a:b], dist[a:b], nm[a:b])
+            jb.destroy()
+        return sets
+
+
 class ORBmatcher:
     """ORB_SLAM2::ORBmatcher(nnratio=0.6, checkOri=true) (reference ORBmatcher.h:45)."""
 

@@ -276,8 +276,17 @@ def run_ours(args):
         h_nm = torch.empty((world, P), dtype=torch.int32).pin_memory()
         rep_desc = pkg.ReplicatedDescriptors(ctx, len(kfs), n, rank, world)
 
+    # N=1: the keyframes stream in over PCIe and the pairs are searched in readiness order (StreamedPairSweep), so the
+    # upload of the later keyframes overlaps the search of the earlier pairs; row r of the outputs = pair sweep.order[r]
+    sweep = pkg.StreamedPairSweep(ctx, pkg.ASDM_JOB_BOW_KF_KF, len(kfs), g_ia, g_ib, c["nnratio"], c["check_ori"]) \
+        if world == 1 and not args.no_stream else None
+
     def e2e_step():
-        if world == 1:
+        if sweep is not None:
+            ss = sweep.run(lambda i: pkg.DescriptorSet(ctx, h_desc[i], kfs[i]["kps"], c["grid"], kfs[i]["fv"], async_upload=True),
+                           masks, h_match, h_dist, h_nm)
+            jb = None
+        elif world == 1:
             ss = [pkg.DescriptorSet(ctx, h, k["kps"], c["grid"], k["fv"], async_upload=True) for h, k in zip(h_desc, kfs)]
             jb = pkg.PairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, ss, masks, g_ia, g_ib, c["nnratio"], c["check_ori"])
             jb.run()
@@ -289,7 +298,8 @@ def run_ours(args):
                                     rank=rank, world=world)
             jb.run()
             jb.fetch_gathered(h_match, h_dist, h_nm)
-        jb.destroy()
+        if jb is not None:
+            jb.destroy()
         for s_ in ss:
             s_.release()
 
@@ -307,7 +317,9 @@ def run_ours(args):
         t = torch.tensor([e2e_ms], device=f"cuda:{local}")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
-    if world == 1:
+    if sweep is not None:
+        e2e_same = np.array_equal(h_match, match[sweep.order]) and np.array_equal(h_nm, nm[sweep.order])
+    elif world == 1:
         e2e_same = np.array_equal(h_match, match)
     elif rank == 0:
         e2e_same = np.array_equal(job.shards.merge(h_match.numpy(), h_dist.numpy(), h_nm.numpy())[1], match)
@@ -319,6 +331,8 @@ def run_ours(args):
     # go to every rank; rank 0 reads all match lists back, the other ranks the counts
     side = sum(k["kps"].nbytes + 8 * len(k["kps"]) + len(k["valid"]) for k in kfs) + 8 * P
     h2d = sum(k["desc"].nbytes for k in kfs) + world * side
+    if sweep is not None:  # every wave re-sends the masks of the keyframes it may touch
+        h2d += sum(sum(len(k["valid"]) for k in kfs[:b]) for b in sweep.bounds[:-1])
     d2h = world * P * S * 8 + world * (world * P * 4)
 
     if rank == 0:
@@ -372,7 +386,10 @@ def run_ours(args):
                "keyframe_pairs_per_sec": world * P * args.steps / (ms * 1e-3),
                "e2e": {"value": world * units / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                        "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms,
-                       "what": "asdm_set_create_async x64 (pinned host descriptors) + featvec + job prepare/run/fetch per step"
+                       "what": (f"per step: 64 keyframes uploaded from pinned host memory (asdm_set_create_async + featvec), pairs "
+                                f"searched in {len(sweep.bounds)} readiness waves (keyframe bounds {sweep.bounds}) that overlap the "
+                                "uploads, all match lists read back" if sweep is not None else
+                                "asdm_set_create_async x64 (pinned host descriptors) + featvec + job prepare/run/fetch per step")
                                if world == 1 else
                                "per step: each keyframe uploaded once (rank k%N) + NVLink all-gather of descriptors, 64 device-"
                                "side set creates per rank, sharded job, NCCL all-gather of results, rank 0 reads all match lists"},
@@ -397,6 +414,7 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-stream", action="store_true", help="e2e at N=1: upload everything, then one job (no overlap)")
     ap.add_argument("--pairs", type=int, default=N_PAIRS, help="keyframe pairs per GPU per step (default: the C5 sweep)")
     ap.add_argument("--tc-variant", type=int, default=0, help="tuning: pipeline shape of the tensor-core kernel")
     ap.add_argument("--epi-warps", type=int, default=0, help="tuning: epilogue warps of the tensor-core kernel (4 or 8)")

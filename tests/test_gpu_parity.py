@@ -342,3 +342,44 @@ def test_compute_distinctive_descriptors(pkg, ctx, oracle, n_kf, n, n_points, ma
         pkg.ComputeDistinctiveDescriptors(ctx, sets, [0, 1], [len(sets)], [0])
     for s in sets:
         s.release()
+
+
+@pytest.mark.parametrize("bad", [False, True])
+def test_streamed_sweep_and_speculative_tensor_route(pkg, ctx, oracle, bad):
+    """StreamedPairSweep: keyframes uploaded asynchronously, pairs searched in readiness waves while later keyframes are
+    still crossing PCIe. The jobs take the tensor-core route before the range flags of their sets are back; with
+    `bad` one keyframe holds rows outside the shortlist's proven norm range (x 3000), so the speculation fails and the
+    settle step must rerun that wave on the exact route. Either way: the oracle's lists, bit for bit."""
+    n, pairs, n_kf = 1500, 40, 9
+    c = pkg.synth.config5(n=n, n_pairs=pairs, n_kf=n_kf, n_nodes=6)
+    kfs = c["kfs"]
+    if bad:
+        kfs[3]["desc"][::7] *= np.float32(3000.0)
+    host = [ctx.pinned((n, 128), np.float32) for _ in kfs]
+    for h, k in zip(host, kfs):
+        h[...] = k["desc"]
+    sweep = pkg.StreamedPairSweep(ctx, pkg.ASDM_JOB_BOW_KF_KF, n_kf, c["ia"], c["ib"], c["nnratio"], c["check_ori"],
+                                  bounds=[3, 5, 7, 9])
+    match, dist, nm = ctx.pinned((pairs, n), np.int32), ctx.pinned((pairs, n), np.float32), ctx.pinned((pairs,), np.int32)
+    retries = []
+
+    def make(i):
+        return pkg.DescriptorSet(ctx, host[i], kfs[i]["kps"], c["grid"], kfs[i]["fv"], async_upload=True)
+    sets = sweep.run(make, [k["valid"] for k in kfs], match, dist, nm)
+    retries.append(ctx.stat("retries"))
+    onm, omatch, odist = oracle.batch_bow_kf_kf(kfs, c["ia"], c["ib"], c["nnratio"], c["check_ori"], threads=oracle.max_threads())
+    o = sweep.order
+    assert sorted(o.tolist()) == list(range(pairs))
+    _eq(match, omatch[o], "streamed match12")
+    _eq_dist(dist, odist[o], "streamed dist12")
+    _eq(nm, onm[o], "streamed nmatches")
+    assert onm.max() > n // 20
+    # the same pairs as one job on the (now flag-resolved) sets: the exact route is chosen up front when `bad`
+    job = pkg.PairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, sets, [k["valid"] for k in kfs], c["ia"], c["ib"], c["nnratio"], c["check_ori"])
+    job.run()
+    nm2, match2, _ = job.fetch()
+    assert ctx.stat("tc_used") == (0 if bad else 1)
+    _eq(match2[:, :n], omatch, "one-job match12")
+    job.destroy()
+    for s in sets:
+        s.release()

@@ -40,3 +40,35 @@ for it in range(8):
     tick("TOTAL", t_all)
 for k, v in T.items():
     print(f"{k:40s} {1e3 * np.median(v[2:]):8.3f} ms   (first {1e3 * v[0]:8.3f})")
+
+# ---- streamed sweep (pairs searched in readiness waves while later keyframes upload): host time per phase
+print("\nstreamed sweep")
+sw = pkg.StreamedPairSweep(ctx, pkg.ASDM_JOB_BOW_KF_KF, len(kfs), c["ia"], c["ib"], c["nnratio"], c["check_ori"])
+T.clear()
+for it in range(8):
+    ctx.synchronize()
+    t_all = time.perf_counter()
+    sets, jobs, done = [], [], 0
+    for (a, b), bound in zip(sw.slices, sw.bounds):
+        t = time.perf_counter()
+        while done < bound:
+            sets.append(pkg.DescriptorSet(ctx, h_desc[done], kfs[done]["kps"], c["grid"], kfs[done]["fv"], async_upload=True))
+            done += 1
+        tick("sets (create + featvec)", t); t = time.perf_counter()
+        sel = sw.order[a:b]
+        jb = pkg.PairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, sets[:bound], masks[:bound], sw.ia[sel], sw.ib[sel], c["nnratio"], c["check_ori"])
+        tick(f"prepare wave<{bound}", t); t = time.perf_counter()
+        jb.run()
+        tick("run", t)
+        jobs.append((jb, a, b))
+    for jb, a, b in jobs:
+        t = time.perf_counter()
+        jb.fetch(h_match[a:b], h_dist[a:b], h_nm[a:b])
+        tick(f"fetch {a}:{b}", t)
+        jb.destroy()
+    for s_ in sets:
+        s_.release()
+    tick("TOTAL", t_all)
+for k, v in T.items():
+    v = np.asarray(v).reshape(8, -1).sum(axis=1) if len(v) > 8 else np.asarray(v)
+    print(f"{k:40s} {1e3 * np.median(v[2:]):8.3f} ms")
