@@ -29,11 +29,11 @@ HISTO_LENGTH = 30
 EXPORTS = [
     "asdm_create", "asdm_destroy", "asdm_last_error", "asdm_stream", "asdm_synchronize", "asdm_set_stream",
     "asdm_host_alloc", "asdm_host_free", "asdm_set_option", "asdm_get_stat",
-    "asdm_set_create", "asdm_set_create_async", "asdm_set_retain", "asdm_set_release", "asdm_set_size", "asdm_set_featvec",
+    "asdm_set_create", "asdm_set_create_async", "asdm_set_create_batch", "asdm_set_retain", "asdm_set_release", "asdm_set_size", "asdm_set_featvec",
     "asdm_set_read_desc", "asdm_desc_block_bytes", "asdm_set_save_blocks", "asdm_set_load_block",
     "asdm_search_by_bow_kf_f", "asdm_search_by_bow_kf_kf", "asdm_search_for_triangulation",
     "asdm_search_by_projection", "asdm_search_by_projection_q", "asdm_search_for_initialization", "asdm_stereo_row_match",
-    "asdm_job_prepare", "asdm_job_run", "asdm_job_fetch", "asdm_job_settle", "asdm_job_out_stride",
+    "asdm_job_prepare", "asdm_job_run", "asdm_job_fetch", "asdm_job_fetch_async", "asdm_job_settle", "asdm_job_out_stride",
     "asdm_job_device_outputs", "asdm_job_destroy",
     "asdm_distinctive_descriptors",
     "asdm_vocab_create", "asdm_vocab_release", "asdm_vocab_transform",
@@ -47,6 +47,11 @@ class Grid(C.Structure):
 
 class FeatVec(C.Structure):
     _fields_ = [("n_nodes", C.c_int32), ("node_ids", C.c_void_p), ("off", C.c_void_p), ("idx", C.c_void_p)]
+
+
+class SetDesc(C.Structure):
+    _fields_ = [("desc", C.c_void_p), ("n", C.c_int32), ("row_stride_bytes", C.c_int32), ("kps", C.c_void_p),
+                ("grid", C.POINTER(Grid)), ("featvec", C.POINTER(FeatVec))]
 
 
 class ProjParams(C.Structure):
@@ -100,6 +105,7 @@ def load():
     lib.asdm_get_stat.argtypes = [vp, C.c_char_p, C.POINTER(C.c_int64)]
     lib.asdm_set_create.argtypes = [vp, vp, C.c_int, C.c_int, vp, C.POINTER(Grid), C.POINTER(vp)]
     lib.asdm_set_create_async.argtypes = lib.asdm_set_create.argtypes
+    lib.asdm_set_create_batch.argtypes = [vp, C.POINTER(SetDesc), C.c_int, C.POINTER(vp)]
     lib.asdm_set_retain.argtypes = [vp]
     lib.asdm_set_release.argtypes = [vp]
     lib.asdm_set_size.argtypes = [vp]
@@ -118,6 +124,7 @@ def load():
     lib.asdm_job_prepare.argtypes = [vp, C.POINTER(JobDesc), C.POINTER(vp)]
     lib.asdm_job_run.argtypes = [vp]
     lib.asdm_job_fetch.argtypes = [vp, vp, vp, vp]
+    lib.asdm_job_fetch_async.argtypes = [vp, vp, vp, vp]
     lib.asdm_job_settle.argtypes = [vp]
     lib.asdm_job_out_stride.argtypes = [vp]
     lib.asdm_job_device_outputs.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]

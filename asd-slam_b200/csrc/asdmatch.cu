@@ -43,6 +43,10 @@ static int fail(asdm_ctx* ctx, int code, const char* what, cudaError_t e = cudaS
 
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// slots of asdm_ctx::scratch
+enum { SC_QUERY = 0, SC_QDESC = 1, SC_SEG = 2, SC_ENT = 3, SC_STATE = 4, SC_BLOCK = 5, SC_MISC = 6, SC_MP_ARGS = 7, SC_MP_DIST = 8, SC_VOC = 9 };
+static int flatten_featvec(asdm_ctx* ctx, const asdm_featvec* fv, int n, int n_pad, uint32_t* node, int32_t* pos);
+
 // Device memory comes from the device's stream-ordered pool (cudaMallocAsync) with the release threshold lifted in
 // asdm_create: allocation and free are ordered on the context stream, never synchronise the device, and the memory
 // of released sets / jobs is recycled by the next ones (keyframes come and go at frame rate in the SLAM system).
@@ -125,12 +129,52 @@ static int stage_alloc(asdm_ctx* ctx, size_t bytes, void** out) {
       ctx->stage = nullptr;
       ctx->stage_cap = 0;
       const size_t want = std::max(bytes * 2, (size_t)16 << 20);
-      CK(cudaHostAlloc((void**)&ctx->stage, want, cudaHostAllocDefault));
+      CK(cudaHostAlloc((void**)&ctx->stage, want, cudaHostAllocMapped));
       ctx->stage_cap = want;
     }
   }
   *out = ctx->stage + ctx->stage_off;
   ctx->stage_off += bytes;
+  return ASDM_OK;
+}
+
+// Small inputs of a search reach the device through a COPY KERNEL that reads the page-locked staging arena over PCIe
+// (zero-copy loads), not through the copy engine: the engine serves a stream's backlog in long slices, so a 4 KB
+// work list queued behind a burst of 2 MB keyframe uploads (another stream, same engine) would only arrive when the
+// burst has drained -- measured: the first wave of a streamed sweep finished together with the LAST upload.
+__global__ void __launch_bounds__(256) k_pull16(uint4* __restrict__ dst, const uint4* __restrict__ src, size_t n16) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x) dst[i] = src[i];
+}
+__global__ void __launch_bounds__(256) k_pull4(uint32_t* __restrict__ dst, const uint32_t* __restrict__ src, size_t n4) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) dst[i] = src[i];
+}
+
+// zero fill by kernel, for the same reason (cudaMemsetAsync may be served by the copy engine)
+__global__ void __launch_bounds__(256) k_zero16(uint4* __restrict__ dst, size_t n16) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x)
+    dst[i] = make_uint4(0u, 0u, 0u, 0u);
+}
+static int zero_device(asdm_ctx* ctx, void* dst, size_t bytes) {  // dst 16-byte aligned; rounds bytes up to 16
+  const size_t n = (bytes + 15) / 16;
+  if (!n) return ASDM_OK;
+  k_zero16<<<(int)std::min<size_t>((n + 255) / 256, 1184), 256, 0, ctx->stream>>>((uint4*)dst, n);
+  CK(cudaGetLastError());
+  return ASDM_OK;
+}
+
+// `h` lies in the staging arena (page-locked, device-visible under UVA); queued on the main stream
+static int pull_to_device(asdm_ctx* ctx, void* dst, const void* h, size_t bytes) {
+  if (!bytes) return ASDM_OK;
+  const bool a16 = (((uintptr_t)dst | (uintptr_t)h | bytes) & 15) == 0, a4 = (((uintptr_t)dst | (uintptr_t)h | bytes) & 3) == 0;
+  if (!a4 || bytes > ((size_t)8 << 20)) {  // odd sizes / big blocks: the copy engine
+    CK(cudaMemcpyAsync(dst, h, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    return ASDM_OK;
+  }
+  const size_t n = a16 ? bytes / 16 : bytes / 4;
+  const int blocks = (int)std::min<size_t>((n + 255) / 256, 64);
+  if (a16) k_pull16<<<blocks, 256, 0, ctx->stream>>>((uint4*)dst, (const uint4*)h, n);
+  else k_pull4<<<blocks, 256, 0, ctx->stream>>>((uint32_t*)dst, (const uint32_t*)h, n);
+  CK(cudaGetLastError());
   return ASDM_OK;
 }
 
@@ -141,14 +185,15 @@ static int stage_upload(asdm_ctx* ctx, void* dst, const void* src, size_t bytes,
   int rc = stage_alloc(ctx, bytes, &h);
   if (rc) return rc;
   memcpy(h, src, bytes);
-  CK(cudaMemcpyAsync(dst, h, bytes, cudaMemcpyHostToDevice, stream ? stream : ctx->stream));
+  if (!stream || stream == ctx->stream) return pull_to_device(ctx, dst, h, bytes);
+  CK(cudaMemcpyAsync(dst, h, bytes, cudaMemcpyHostToDevice, stream));
   return ASDM_OK;
 }
 
 enum { SLOT_BYTES = 64, SLOT_COUNT = 4096 };
 static int32_t* slot_get(asdm_ctx* ctx) {
   if (!ctx->slot_slab) {
-    if (cudaHostAlloc((void**)&ctx->slot_slab, (size_t)SLOT_BYTES * SLOT_COUNT, cudaHostAllocDefault) != cudaSuccess) {
+    if (cudaHostAlloc((void**)&ctx->slot_slab, (size_t)SLOT_BYTES * SLOT_COUNT, cudaHostAllocMapped) != cudaSuccess) {
       cudaGetLastError();
       ctx->slot_slab = nullptr;
       return nullptr;
@@ -194,6 +239,8 @@ extern "C" int asdm_create(int device, asdm_ctx** out) {
   if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaStreamCreateWithFlags(&ctx->upload_stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaStreamCreateWithFlags(&ctx->prep_stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&ctx->download_stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&ctx->run_done, cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreateWithFlags(&ctx->upload_done, cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreateWithFlags(&ctx->prep_done, cudaEventDisableTiming) != cudaSuccess) {
     cudaGetLastError();
@@ -240,6 +287,8 @@ extern "C" int asdm_destroy(asdm_ctx* ctx) {
   if (ctx->upload_done) cudaEventDestroy(ctx->upload_done);
   if (ctx->prep_stream) cudaStreamDestroy(ctx->prep_stream);
   if (ctx->prep_done) cudaEventDestroy(ctx->prep_done);
+  if (ctx->download_stream) cudaStreamDestroy(ctx->download_stream);
+  if (ctx->run_done) cudaEventDestroy(ctx->run_done);
   delete ctx;
   return ASDM_OK;
 }
@@ -341,8 +390,12 @@ static void set_free(asdm_set* s) {
   if (!s) return;
   asdm_ctx* ctx = s->ctx;
   cudaSetDevice(ctx->device);
-  dev_free(ctx, s->desc);  // one arena: every other device pointer lives inside it
+  dev_free(ctx, s->desc);  // one arena: every other device pointer lives inside it (or in the batch's side block)
   dev_free(ctx, s->fv_mem);
+  if (s->side && --s->side->ref == 0) {
+    dev_free(ctx, s->side->p);
+    delete s->side;
+  }
   slot_put(ctx, s->h_flag);
   delete s;
 }
@@ -505,6 +558,151 @@ extern "C" int asdm_set_create_async(asdm_ctx* ctx, const float* desc, int n, in
   return set_create_impl(ctx, desc, n, row_stride_bytes, kps, grid, out, false);
 }
 
+// A batch of sets (asdmatch.h). Copy-engine work per batch: the pack table, ONE copy with the small arrays of every
+// set (range flag | keypoints | FeatureVector, into a side block the sets share), then the descriptor DMAs back to
+// back; one pack launch on the preparation stream.
+extern "C" int asdm_set_create_batch(asdm_ctx* ctx, const asdm_set_desc* descs, int n_sets, asdm_set** out) {
+  if (!ctx || n_sets < 0 || (n_sets > 0 && (!descs || !out))) return ASDM_ERR_INVALID;
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  CK(cudaSetDevice(ctx->device));
+  for (int k = 0; k < n_sets; k++) out[k] = nullptr;
+  size_t side_bytes = 0;
+  std::vector<size_t> side_off((size_t)n_sets);
+  for (int k = 0; k < n_sets; k++) {
+    const asdm_set_desc& d = descs[k];
+    if (d.n < 0 || (d.n > 0 && !d.desc)) return fail(ctx, ASDM_ERR_INVALID, "bad set description");
+    if (d.row_stride_bytes != 0 && d.row_stride_bytes < (int)(ASDM_DESC_DIM * sizeof(float)))
+      return fail(ctx, ASDM_ERR_INVALID, "row stride < 512 B");
+    if (d.grid && (!d.kps || d.grid->cols <= 0 || d.grid->rows <= 0 || (int64_t)d.grid->cols * d.grid->rows > (1 << 20)))
+      return fail(ctx, ASDM_ERR_INVALID, "bad grid");
+    if (d.featvec && d.featvec->n_nodes < 0) return fail(ctx, ASDM_ERR_INVALID, "bad FeatureVector");
+    const size_t n_pad = align_up((size_t)std::max(d.n, 1), 256);
+    side_off[k] = side_bytes;
+    side_bytes += 256 + (d.kps ? n_pad * sizeof(asdm_kp) : 0) + (d.featvec ? n_pad * 8 : 0);
+  }
+  if (n_sets == 0) return ASDM_OK;
+  SideBlock* side = new (std::nothrow) SideBlock;
+  if (!side) return fail(ctx, ASDM_ERR_OOM, "host allocation");
+  auto bail = [&](int code) {
+    for (int k = 0; k < n_sets; k++) {
+      if (out[k]) set_free(out[k]);
+      out[k] = nullptr;
+    }
+    if (side->ref == 0) {  // no set took a share yet
+      dev_free(ctx, side->p);
+      delete side;
+    }
+    return code;
+  };
+  const size_t table_bytes = align_up((size_t)n_sets * sizeof(PackItem), 256);
+  void* h_stage = nullptr;
+  int rc = stage_alloc(ctx, table_bytes + side_bytes, &h_stage);
+  if (rc) return bail(rc);
+  PackItem* items = (PackItem*)h_stage;
+  char* h_side = (char*)h_stage + table_bytes;
+  // the table sits in front of the side block on the device as well: one copy brings both
+  cudaError_t e = cudaMallocAsync(&side->p, table_bytes + side_bytes, ctx->upload_stream);
+  if (e != cudaSuccess) return bail(fail(ctx, ASDM_ERR_OOM, "cudaMallocAsync(side block)", e));
+  char* d_side = (char*)side->p + table_bytes;
+  int max_pad = 0;
+  for (int k = 0; k < n_sets; k++) {
+    const asdm_set_desc& d = descs[k];
+    asdm_set* s = new (std::nothrow) asdm_set();
+    if (!s) return bail(fail(ctx, ASDM_ERR_OOM, "host allocation"));
+    out[k] = s;
+    s->ctx = ctx;
+    s->side = side;
+    side->ref++;
+    s->n = d.n;
+    s->n_pad = (int)align_up((size_t)std::max(d.n, 1), 256);
+    max_pad = std::max(max_pad, s->n_pad);
+    const int nc = d.grid ? d.grid->cols * d.grid->rows : 0;
+    size_t off = 0;
+    const size_t o_desc = off; off += align_up((size_t)s->n_pad * ASDM_DESC_DIM * sizeof(float), 1024);
+    const size_t o_bf = off;   off += align_up((size_t)s->n_pad * ASDM_DESC_DIM * sizeof(__nv_bfloat16), 1024);
+    const size_t o_norm = off; off += align_up((size_t)s->n_pad * sizeof(float), 256);
+    const size_t o_cs = off;   off += d.grid ? align_up((size_t)(nc + 1) * sizeof(int32_t), 256) : 0;
+    const size_t o_ci = off;   off += d.grid ? align_up((size_t)s->n_pad * sizeof(int32_t), 256) : 0;
+    const size_t o_tmp = off;  off += d.grid ? align_up((size_t)s->n_pad * sizeof(int32_t), 256) : 0;
+    char* base = nullptr;
+    e = cudaMallocAsync((void**)&base, off, ctx->upload_stream);
+    if (e != cudaSuccess) return bail(fail(ctx, ASDM_ERR_OOM, "cudaMallocAsync(set)", e));
+    s->desc = (float*)(base + o_desc);
+    s->desc_bf = (__nv_bfloat16*)(base + o_bf);
+    s->norm2 = (float*)(base + o_norm);
+    if (d.grid) {
+      s->grid = *d.grid;
+      s->has_grid = true;
+      s->cell_start = (int32_t*)(base + o_cs);
+      s->cell_items = (int32_t*)(base + o_ci);
+      s->cell_tmp = (int32_t*)(base + o_tmp);
+    }
+    // the descriptors start crossing PCIe at once; the small arrays are staged below, while the copy engine works
+    if (d.n > 0) {
+      const int stride = d.row_stride_bytes ? d.row_stride_bytes : (int)(ASDM_DESC_DIM * sizeof(float));
+      if (stride == (int)(ASDM_DESC_DIM * sizeof(float)))
+        e = cudaMemcpyAsync(s->desc, d.desc, (size_t)d.n * ASDM_DESC_DIM * sizeof(float), cudaMemcpyHostToDevice, ctx->upload_stream);
+      else
+        e = cudaMemcpy2DAsync(s->desc, ASDM_DESC_DIM * sizeof(float), d.desc, stride, ASDM_DESC_DIM * sizeof(float), d.n,
+                              cudaMemcpyHostToDevice, ctx->upload_stream);
+      if (e != cudaSuccess) return bail(fail(ctx, ASDM_ERR_CUDA, "descriptor upload", e));
+    }
+  }
+  for (int k = 0; k < n_sets; k++) {
+    const asdm_set_desc& d = descs[k];
+    asdm_set* s = out[k];
+    // side block share: flags | keypoints | node ids | FeatureVector positions
+    size_t so = side_off[k];
+    s->d_flags = (int32_t*)(d_side + so);
+    memset(h_side + so, 0, 256);
+    so += 256;
+    if (d.kps) {
+      s->kps = (asdm_kp*)(d_side + so);
+      s->has_kps = true;
+      memcpy(h_side + so, d.kps, (size_t)d.n * sizeof(asdm_kp));
+      memset(h_side + so + (size_t)d.n * sizeof(asdm_kp), 0, (size_t)(s->n_pad - d.n) * sizeof(asdm_kp));
+      so += (size_t)s->n_pad * sizeof(asdm_kp);
+    }
+    if (d.featvec) {
+      s->node_id = (uint32_t*)(d_side + so);
+      s->fv_pos = (int32_t*)(d_side + so + (size_t)s->n_pad * 4);
+      uint32_t* hn = (uint32_t*)(h_side + so);
+      if ((rc = flatten_featvec(ctx, d.featvec, d.n, s->n_pad, hn, (int32_t*)(hn + s->n_pad)))) return bail(rc);
+      s->has_fv = true;
+    }
+    s->h_flag = slot_get(ctx);
+    items[k] = PackItem{s->desc, s->desc_bf, s->norm2, s->d_flags, s->n, s->n_pad, s->h_flag};
+  }
+#define CKB(call)                                              \
+  do {                                                         \
+    cudaError_t e__ = (call);                                  \
+    if (e__ != cudaSuccess) return bail(fail(ctx, ASDM_ERR_CUDA, #call, e__)); \
+  } while (0)
+  CKB(cudaMemcpyAsync(side->p, h_stage, table_bytes + side_bytes, cudaMemcpyHostToDevice, ctx->upload_stream));
+  CKB(cudaEventRecord(ctx->upload_done, ctx->upload_stream));
+  CKB(cudaStreamWaitEvent(ctx->prep_stream, ctx->upload_done, 0));
+  ctx->stat_launches = 0;
+  k_pack_batch<<<dim3(std::min((max_pad * 32 + 255) / 256, 64), n_sets), 256, 0, ctx->prep_stream>>>((const PackItem*)side->p);
+  LAUNCHED(ctx);
+  CKB(cudaEventRecord(ctx->prep_done, ctx->prep_stream));
+  CKB(cudaStreamWaitEvent(ctx->stream, ctx->prep_done, 0));
+  CKB(cudaGetLastError());
+  bool need_sync = false;
+  for (int k = 0; k < n_sets; k++) need_sync |= !out[k]->h_flag;
+  if (need_sync) {  // pinned flag slots exhausted: read the flags now
+    CKB(cudaStreamSynchronize(ctx->stream));
+    synced(ctx);
+    for (int k = 0; k < n_sets; k++)
+      if (!out[k]->h_flag) {
+        int32_t f = 1;
+        CKB(cudaMemcpy(&f, out[k]->d_flags, sizeof f, cudaMemcpyDeviceToHost));
+        out[k]->tc_ok = f ? 0 : 1;
+      }
+  }
+#undef CKB
+  return ASDM_OK;
+}
+
 extern "C" int asdm_set_retain(asdm_set* s) {
   if (!s) return ASDM_ERR_INVALID;
   s->ref.fetch_add(1);
@@ -523,6 +721,23 @@ extern "C" int asdm_set_release(asdm_set* s) {
 
 extern "C" int asdm_set_size(const asdm_set* s) { return s ? s->n : ASDM_ERR_INVALID; }
 
+// DBoW2::FeatureVector -> per-feature node id + CSR position (-1 = not in the vector)
+static int flatten_featvec(asdm_ctx* ctx, const asdm_featvec* fv, int n, int n_pad, uint32_t* node, int32_t* pos) {
+  memset(node, 0, (size_t)n_pad * 4);
+  memset(pos, 0xff, (size_t)n_pad * 4);
+  for (int k = 0; k < fv->n_nodes; k++) {
+    if (k > 0 && !(fv->node_ids[k] > fv->node_ids[k - 1])) return fail(ctx, ASDM_ERR_INVALID, "node ids not ascending");
+    for (int e = fv->off[k]; e < fv->off[k + 1]; e++) {
+      const int i = fv->idx[e];
+      if (i < 0 || i >= n) return fail(ctx, ASDM_ERR_INVALID, "feature index out of range");
+      if (pos[i] >= 0) return fail(ctx, ASDM_ERR_INVALID, "feature listed twice in the FeatureVector");
+      node[i] = fv->node_ids[k];
+      pos[i] = e;
+    }
+  }
+  return ASDM_OK;
+}
+
 extern "C" int asdm_set_featvec(asdm_set* s, const asdm_featvec* fv) {
   if (!s || !fv || fv->n_nodes < 0) return ASDM_ERR_INVALID;
   asdm_ctx* ctx = s->ctx;
@@ -533,21 +748,8 @@ extern "C" int asdm_set_featvec(asdm_set* s, const asdm_featvec* fv) {
   void* h = nullptr;
   int rc = stage_alloc(ctx, (size_t)s->n_pad * 8, &h);
   if (rc) return rc;
-  uint32_t* node = (uint32_t*)h;
-  int32_t* pos = (int32_t*)(node + s->n_pad);
-  memset(node, 0, (size_t)s->n_pad * 4);
-  memset(pos, 0xff, (size_t)s->n_pad * 4);
-  for (int k = 0; k < fv->n_nodes; k++) {
-    if (k > 0 && !(fv->node_ids[k] > fv->node_ids[k - 1])) return fail(ctx, ASDM_ERR_INVALID, "node ids not ascending");
-    for (int e = fv->off[k]; e < fv->off[k + 1]; e++) {
-      const int i = fv->idx[e];
-      if (i < 0 || i >= s->n) return fail(ctx, ASDM_ERR_INVALID, "feature index out of range");
-      if (pos[i] >= 0) return fail(ctx, ASDM_ERR_INVALID, "feature listed twice in the FeatureVector");
-      node[i] = fv->node_ids[k];
-      pos[i] = e;
-    }
-  }
-  if (!s->fv_mem) {
+  if ((rc = flatten_featvec(ctx, fv, s->n, s->n_pad, (uint32_t*)h, (int32_t*)((uint32_t*)h + s->n_pad)))) return rc;
+  if (!s->node_id) {
     CK(cudaMallocAsync(&s->fv_mem, (size_t)s->n_pad * 8, ctx->upload_stream));
     s->node_id = (uint32_t*)s->fv_mem;
     s->fv_pos = (int32_t*)((char*)s->fv_mem + (size_t)s->n_pad * 4);
@@ -556,7 +758,7 @@ extern "C" int asdm_set_featvec(asdm_set* s, const asdm_featvec* fv) {
     CK(cudaEventRecord(ctx->upload_done, ctx->stream));
     CK(cudaStreamWaitEvent(ctx->upload_stream, ctx->upload_done, 0));
   }
-  CK(cudaMemcpyAsync(s->fv_mem, h, (size_t)s->n_pad * 8, cudaMemcpyHostToDevice, ctx->upload_stream));
+  CK(cudaMemcpyAsync(s->node_id, h, (size_t)s->n_pad * 8, cudaMemcpyHostToDevice, ctx->upload_stream));
   CK(cudaEventRecord(ctx->upload_done, ctx->upload_stream));
   CK(cudaStreamWaitEvent(ctx->stream, ctx->upload_done, 0));
   s->has_fv = true;
@@ -642,6 +844,8 @@ struct asdm_job {
   int n_seg = 0, seg_cap = 0;
   float t_keep_tc = 0.f;
   bool ran = false;
+  void* prefetched[3] = {nullptr, nullptr, nullptr};  // destinations of asdm_job_fetch_async
+  bool prefetch_valid = false;
   bool tc_pending = false;     // tensor-core route taken before every set's range flag was back (validated in settle)
   int32_t* h_flags = nullptr;  // pinned, 8 ints: [0] cand overflow, [1] list overflow, [2] list count
   bool h_flags_owned = false;  // true when the context's slot slab was exhausted and the job allocated its own
@@ -651,6 +855,10 @@ static void job_free(asdm_job* j) {
   if (!j) return;
   asdm_ctx* ctx = j->ctx;
   cudaSetDevice(ctx->device);
+  if (j->prefetch_valid && ctx->downloads_pending) {  // destroyed between fetch_async and fetch
+    cudaStreamSynchronize(ctx->download_stream);
+    ctx->downloads_pending = false;
+  }
   DevBuf* bufs[] = {&j->d_pairs, &j->d_masks, &j->d_cnt, &j->d_cand, &j->d_owner, &j->d_acc, &j->d_flags,
                     &j->d_match, &j->d_dist, &j->d_nm, &j->d_work, &j->d_tmaps, &j->d_list, &j->d_seg_count,
                     &j->d_rb, &j->d_cmin, &j->d_setdesc};
@@ -734,8 +942,7 @@ static int job_prepare(asdm_ctx* ctx, const asdm_job_desc* d, int kind_internal,
     void* h = nullptr;
     if ((rc = stage_alloc(ctx, mtot, &h))) return bail(rc);
     for (int k = 0; k < d->n_kf; k++) memcpy((char*)h + mask_off[k], d->masks[k], (size_t)d->sets[k]->n);
-    if (cudaMemcpyAsync(j->d_masks.p, h, mtot, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess)
-      return bail(fail(ctx, ASDM_ERR_CUDA, "mask upload"));
+    if ((rc = pull_to_device(ctx, j->d_masks.p, h, mtot))) return bail(rc);
   }
 
   BowParams& P = j->P;
@@ -902,8 +1109,12 @@ static int job_run(asdm_job* j) {
   if (j->n_pairs == 0) return ASDM_OK;
   const PairDesc* pairs = (const PairDesc*)j->d_pairs.p;
   int32_t* flags = (int32_t*)j->d_flags.p;
-  CK(cudaMemsetAsync(j->d_cnt.p, 0, (size_t)j->n_pairs * j->n_stride * sizeof(int32_t), ctx->stream));
-  CK(cudaMemsetAsync(flags, 0, 64, ctx->stream));
+  {  // (buffers come from ensure(): at least 4 KB, so rounding the fill up to 16 bytes stays inside)
+    int rc;
+    if ((rc = zero_device(ctx, j->d_cnt.p, (size_t)j->n_pairs * j->n_stride * sizeof(int32_t))) ||
+        (rc = zero_device(ctx, flags, 64)))
+      return rc;
+  }
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   if (ctx->opt_time_kernels) {
     CK(cudaEventCreate(&ev0));
@@ -911,7 +1122,10 @@ static int job_run(asdm_job* j) {
     CK(cudaEventRecord(ev0, ctx->stream));
   }
   if (j->use_tc) {
-    CK(cudaMemsetAsync(j->d_seg_count.p, 0, (size_t)j->n_seg * sizeof(int32_t), ctx->stream));
+    {
+      const int rc = zero_device(ctx, j->d_seg_count.p, (size_t)j->n_seg * sizeof(int32_t));
+      if (rc) return rc;
+    }
     CK(asdm_tc_shortlist_launch(ctx, pairs, j->d_tmaps.p, (const TcWork*)j->d_work.p, j->n_work, j->P.t_keep,
                                 (TcHit*)j->d_list.p, j->seg_cap, (int32_t*)j->d_seg_count.p, flags + 2));
     LAUNCHED(ctx);
@@ -1011,8 +1225,17 @@ extern "C" int asdm_job_fetch(asdm_job* j, int32_t* match12, float* dist12, int3
   asdm_ctx* ctx = j->ctx;
   std::lock_guard<std::recursive_mutex> lk(ctx->mu);
   CK(cudaSetDevice(ctx->device));
+  const bool had_prefetch = j->prefetch_valid && j->prefetched[0] == match12 && j->prefetched[1] == dist12 &&
+                            j->prefetched[2] == nmatches;
+  j->prefetch_valid = false;
   int rc = job_settle(j);
   if (rc) return rc;
+  // results queued by asdm_job_fetch_async stand when the run they were copied from was the validated one
+  if (ctx->downloads_pending) {  // also before copying again: the two must not race on the destination
+    CK(cudaStreamSynchronize(ctx->download_stream));
+    ctx->downloads_pending = false;
+  }
+  if (had_prefetch && ctx->stat_retries == 0) return ASDM_OK;
   const size_t n = (size_t)j->n_pairs * j->out_stride;
   if (match12 && n) CK(cudaMemcpyAsync(match12, j->d_match.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
   if (dist12 && n) CK(cudaMemcpyAsync(dist12, j->d_dist.p, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
@@ -1020,6 +1243,29 @@ extern "C" int asdm_job_fetch(asdm_job* j, int32_t* match12, float* dist12, int3
     CK(cudaMemcpyAsync(nmatches, j->d_nm.p, (size_t)j->n_pairs * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
   synced(ctx);
+  return ASDM_OK;
+}
+
+extern "C" int asdm_job_fetch_async(asdm_job* j, int32_t* match12, float* dist12, int32_t* nmatches) {
+  if (!j) return ASDM_ERR_INVALID;
+  asdm_ctx* ctx = j->ctx;
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  CK(cudaSetDevice(ctx->device));
+  if (!j->ran) {
+    const int rc = job_run(j);
+    if (rc) return rc;
+  }
+  const size_t n = (size_t)j->n_pairs * j->out_stride;
+  cudaStream_t ds = ctx->download_stream;
+  CK(cudaEventRecord(ctx->run_done, ctx->stream));
+  CK(cudaStreamWaitEvent(ds, ctx->run_done, 0));
+  if (match12 && n) CK(cudaMemcpyAsync(match12, j->d_match.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, ds));
+  if (dist12 && n) CK(cudaMemcpyAsync(dist12, j->d_dist.p, n * sizeof(float), cudaMemcpyDeviceToHost, ds));
+  if (nmatches && j->n_pairs)
+    CK(cudaMemcpyAsync(nmatches, j->d_nm.p, (size_t)j->n_pairs * sizeof(int32_t), cudaMemcpyDeviceToHost, ds));
+  ctx->downloads_pending = true;
+  j->prefetched[0] = match12; j->prefetched[1] = dist12; j->prefetched[2] = nmatches;
+  j->prefetch_valid = true;
   return ASDM_OK;
 }
 
@@ -1122,7 +1368,6 @@ extern "C" int asdm_search_for_triangulation(asdm_ctx* ctx, asdm_set* kf1, const
 
 // ------------------------------------------------------------------------- projection-gated entry points
 // scratch slots of the context
-enum { SC_QUERY = 0, SC_QDESC = 1, SC_SEG = 2, SC_ENT = 3, SC_STATE = 4, SC_BLOCK = 5, SC_MISC = 6, SC_MP_ARGS = 7, SC_MP_DIST = 8, SC_VOC = 9 };
 
 struct ProjDev {
   asdm_proj_query* q;
@@ -1560,7 +1805,7 @@ extern "C" int asdm_vocab_transform(asdm_ctx* ctx, asdm_vocab* voc, asdm_set* s,
   ctx->stat_launches = 0;
   if (bow_n) *bow_n = 0;
   const int n = s->n;
-  if (!s->fv_mem) {
+  if (!s->node_id) {
     CK(dev_alloc(ctx, &s->fv_mem, (size_t)s->n_pad * 8));
     s->node_id = (uint32_t*)s->fv_mem;
     s->fv_pos = (int32_t*)((char*)s->fv_mem + (size_t)s->n_pad * 4);

@@ -35,6 +35,10 @@ struct asdm_ctx {
   // search queued later is ordered after the sets it may touch.
   cudaStream_t prep_stream = nullptr;
   cudaEvent_t prep_done = nullptr;
+  // results queued by asdm_job_fetch_async leave on a fourth stream, so the copies of one wave overlap the next wave
+  cudaStream_t download_stream = nullptr;
+  cudaEvent_t run_done = nullptr;
+  bool downloads_pending = false;
   // Scratch blocks of jobs / calls (DevBuf) are recycled through this cache instead of going back to the driver pool:
   // they are only ever touched on the context stream, so stream order makes the reuse safe, and a job costs no
   // cudaMallocAsync / cudaFreeAsync calls in steady state. Keyed by size class.
@@ -69,8 +73,16 @@ struct asdm_ctx {
   int proj_ent_cap = 1 << 16;  // entries of the projection candidate pool (grows on overflow)
 };
 
+// small per-set arrays (range flag | keypoints | FeatureVector) of a batch of sets live in ONE device block, filled by
+// one copy (asdm_set_create_batch); the sets of the batch share it
+struct SideBlock {
+  void* p = nullptr;
+  int ref = 0;  // guarded by the context mutex
+};
+
 struct asdm_set {
   asdm_ctx* ctx = nullptr;
+  SideBlock* side = nullptr;
   std::atomic<int> ref{1};
   int n = 0;
   int n_pad = 0;                     // rows allocated (multiple of 256; padding rows are zero)

@@ -110,3 +110,43 @@ __global__ void __launch_bounds__(1024) k_build_grid(const asdm_kp* __restrict__
     }
   }
 }
+
+// Batched k_pack_desc for asdm_set_create_batch: one launch packs every set of a batch (a wave of keyframes that
+// arrived together). blockIdx.y = set; rows beyond n are zeroed here (desc, bf16 copy, norm), so the batch needs no
+// memset per set.
+struct PackItem {
+  float* desc;
+  __nv_bfloat16* bf;
+  float* norm2;
+  int32_t* flags;
+  int32_t n, n_pad;
+  int32_t* h_flag;  // page-locked, device-visible copy of flags[0] (written straight over PCIe: no copy-back per set)
+};
+
+__global__ void __launch_bounds__(256) k_pack_batch(const PackItem* __restrict__ items) {
+  const PackItem it = items[blockIdx.y];
+  const int lane = threadIdx.x & 31;
+  for (int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; row < it.n_pad; row += (gridDim.x * blockDim.x) >> 5) {
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    float4* src = reinterpret_cast<float4*>(it.desc + (size_t)row * ASDM_DESC_DIM) + lane;
+    if (row < it.n) v = *src;
+    else *src = v;
+    float s = v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y);
+    __nv_bfloat162 hi = __floats2bfloat162_rn(v.z, v.w);
+    uint2 packed;
+    packed.x = *reinterpret_cast<uint32_t*>(&lo);
+    packed.y = *reinterpret_cast<uint32_t*>(&hi);
+    *reinterpret_cast<uint2*>(it.bf + (size_t)row * ASDM_DESC_DIM + lane * 4) = packed;
+    if (lane == 0) {
+      it.norm2[row] = s;
+      const bool ok = (s == 0.f) || (s >= 9.5367431640625e-07f && s <= 1048576.f);  // [2^-20, 2^20], as k_pack_desc
+      if (!ok) {
+        it.flags[0] = 1;
+        if (it.h_flag) *it.h_flag = 1;
+      }
+    }
+  }
+}

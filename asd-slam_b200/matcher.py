@@ -14,7 +14,7 @@ import numpy as np
 
 from . import _lib
 from ._lib import (ASDM_JOB_BOW_KF_KF, ASDM_JOB_TRIANGULATION, ASDM_PROJ_BEST_ONLY, ASDM_PROJ_RATIO_LEVEL, KP_DTYPE,
-                   PROJ_QUERY_DTYPE, TH_HIGH, TH_LOW, AsdmError, FeatVec, Grid, JobDesc, ProjParams, VocabDesc, ptr)
+                   PROJ_QUERY_DTYPE, TH_HIGH, TH_LOW, AsdmError, FeatVec, Grid, JobDesc, ProjParams, SetDesc, VocabDesc, ptr)
 
 
 def _f32(a):
@@ -135,6 +135,44 @@ class DescriptorSet:
         return out
 
     @classmethod
+    def create_batch(cls, ctx, descs, kps=None, grid=None, featvecs=None):
+        """asdm_set_create_batch: the sets of a batch of keyframes in one call (asynchronous uploads: every `descs[k]`
+        must stay alive and unmodified until the next synchronising call; page-locked memory gives a true async DMA).
+        kps: list of KP_DTYPE arrays, featvecs: list of (node_ids, off, idx) -- or None."""
+        m = len(descs)
+        g = None
+        if grid is not None:
+            g = grid if isinstance(grid, Grid) else Grid(*grid)
+        arr = (SetDesc * m)()
+        keep = []
+        for k in range(m):
+            d = descs[k]
+            assert d.dtype == np.float32 and d.ndim == 2 and d.shape[1] == 128 and d.flags["C_CONTIGUOUS"]
+            a = arr[k]
+            a.desc, a.n, a.row_stride_bytes = d.ctypes.data, d.shape[0], 0
+            if kps is not None:
+                kp = np.ascontiguousarray(kps[k], dtype=KP_DTYPE)
+                assert len(kp) == d.shape[0]
+                a.kps = kp.ctypes.data
+                keep.append(kp)
+                if g is not None:
+                    a.grid = C.pointer(g)
+            if featvecs is not None:
+                node_ids, off, idx = featvecs[k]
+                node_ids, off, idx = np.ascontiguousarray(node_ids, dtype=np.uint32), _i32(off), _i32(idx)
+                fv = FeatVec(len(node_ids), ptr(node_ids), ptr(off), ptr(idx))
+                a.featvec = C.pointer(fv)
+                keep.append((node_ids, off, idx, fv))
+        hs = (C.c_void_p * m)()
+        ctx.check(ctx.lib.asdm_set_create_batch(ctx.h, arr, m, hs))
+        out = []
+        for k in range(m):
+            self = cls.__new__(cls)
+            self.ctx, self.h, self.n, self._desc_keepalive = ctx, C.c_void_p(hs[k]), descs[k].shape[0], descs[k]
+            out.append(self)
+        return out
+
+    @classmethod
     def from_map_block(cls, ctx, block, kps=None, grid=None):
         """Set from the descriptor block of a chamo.map frame (visual_map_seri.cc:272-285). Returns (set, bytes used).
         `block`: uint8 array starting at the block; it must stay alive until the next synchronising call."""
@@ -206,6 +244,10 @@ class PairJob:
         self.ctx.check(self.ctx.lib.asdm_job_fetch(self.h, ptr(match), ptr(dist), ptr(nm)))
         return nm, match, dist
 
+    def fetch_async(self, match, dist, nm):
+        """Queues the result copies behind the run; `fetch` on the same arrays later validates (and finishes) them."""
+        self.ctx.check(self.ctx.lib.asdm_job_fetch_async(self.h, ptr(match), ptr(dist), ptr(nm)))
+
     def device_outputs(self):
         m, d, n = C.c_void_p(), C.c_void_p(), C.c_void_p()
         self.ctx.check(self.ctx.lib.asdm_job_device_outputs(self.h, C.byref(m), C.byref(d), C.byref(n)))
@@ -232,7 +274,9 @@ class StreamedPairSweep:
         if bounds is None:
             # waves shrink towards the end: the last one (after the last upload) is all that is not hidden.
             # pairs with max < b are a (b/n)^2 share of a uniform sweep
-            bounds = sorted({max(2, int(round(self.n_kf * f))) for f in (0.42, 0.62, 0.77, 0.88, 0.95, 1.0)})
+            # (measured on C5, B200: 4 waves at 1/2, 3/4, 9/10 of the keyframes; every wave costs ~0.13 ms of fixed
+            # kernel tails, so more waves stop paying once the searches, not the uploads, are the long pole)
+            bounds = sorted({max(2, int(round(self.n_kf * f))) for f in (0.5, 0.75, 0.9, 1.0)})
         self.bounds = [int(b) for b in bounds]
         assert self.bounds[-1] == self.n_kf
         later = np.maximum(self.ia, self.ib)
@@ -242,14 +286,15 @@ class StreamedPairSweep:
         self._per_pair = {k: (np.asarray(v).reshape(len(self.ia), -1) if k in ("F12", "epipoles", "row_begin", "row_end") else v)
                           for k, v in job_kw.items()}
 
-    def run(self, make_set, masks, match, dist, nm):
-        """make_set(k) -> DescriptorSet of keyframe k with its FeatureVector attached (uploaded asynchronously).
-        match / dist: (n_pairs, stride) arrays, nm: (n_pairs,), ideally page-locked. Returns the sets (caller releases)."""
+    def run(self, make_sets, masks, match, dist, nm):
+        """make_sets(lo, hi) -> list of DescriptorSets of keyframes lo..hi-1 with their FeatureVectors attached, uploaded
+        asynchronously (DescriptorSet.create_batch). match / dist: (n_pairs, stride) arrays, nm: (n_pairs,), page-locked.
+        Returns the sets (the caller releases them)."""
         sets, jobs, done = [], [], 0
         for (a, b), bound in zip(self.slices, self.bounds):
-            while done < bound:
-                sets.append(make_set(done))
-                done += 1
+            if bound > done:
+                sets.extend(make_sets(done, bound))
+                done = bound
             if b <= a:
                 continue
             sel = self.order[a:b]
@@ -257,8 +302,9 @@ class StreamedPairSweep:
             jb = PairJob(self.ctx, self.kind, sets[:bound], masks[:bound], self.ia[sel], self.ib[sel], self.nnratio,
                          self.check_ori, **kw)
             jb.run()
+            jb.fetch_async(match[a:b], dist[a:b], nm[a:b])  # the copies of this wave overlap the next wave's kernels
             jobs.append((jb, a, b))
-        for jb, a, b in jobs:  # waves finish in launch order; each fetch drains one
+        for jb, a, b in jobs:  # validates each wave; copies again only if a wave had to be rerun
             jb.fetch(match[a:b], dist[a:b], nm[a:b])
             jb.destroy()
         return sets

@@ -281,9 +281,11 @@ def run_ours(args):
     sweep = pkg.StreamedPairSweep(ctx, pkg.ASDM_JOB_BOW_KF_KF, len(kfs), g_ia, g_ib, c["nnratio"], c["check_ori"]) \
         if world == 1 and not args.no_stream else None
 
+    kps_all, fv_all = [k["kps"] for k in kfs], [k["fv"] for k in kfs]
+
     def e2e_step():
         if sweep is not None:
-            ss = sweep.run(lambda i: pkg.DescriptorSet(ctx, h_desc[i], kfs[i]["kps"], c["grid"], kfs[i]["fv"], async_upload=True),
+            ss = sweep.run(lambda lo, hi: pkg.DescriptorSet.create_batch(ctx, h_desc[lo:hi], kps_all[lo:hi], c["grid"], fv_all[lo:hi]),
                            masks, h_match, h_dist, h_nm)
             jb = None
         elif world == 1:
@@ -386,7 +388,7 @@ def run_ours(args):
                "keyframe_pairs_per_sec": world * P * args.steps / (ms * 1e-3),
                "e2e": {"value": world * units / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                        "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms,
-                       "what": (f"per step: 64 keyframes uploaded from pinned host memory (asdm_set_create_async + featvec), pairs "
+                       "what": (f"per step: 64 keyframes uploaded from pinned host memory (asdm_set_create_batch per wave), pairs "
                                 f"searched in {len(sweep.bounds)} readiness waves (keyframe bounds {sweep.bounds}) that overlap the "
                                 "uploads, all match lists read back" if sweep is not None else
                                 "asdm_set_create_async x64 (pinned host descriptors) + featvec + job prepare/run/fetch per step")

@@ -108,6 +108,19 @@ int asdm_set_create(asdm_ctx* ctx, const float* desc, int n, int row_stride_byte
  * uploads of a batch of keyframes queue back to back and overlap the host-side preparation of the job that uses them. */
 int asdm_set_create_async(asdm_ctx* ctx, const float* desc, int n, int row_stride_bytes, const asdm_kp* kps,
                           const asdm_grid* grid, asdm_set** out);
+/* A batch of sets in one call (keyframes that arrive together: a map being loaded, a cold loop-closure sweep). Same
+ * result as asdm_set_create_async + asdm_set_featvec per set, but the small inputs of each set (keypoints, FeatureVector)
+ * travel in one copy, one kernel launch prepares the whole batch, and the call costs a few microseconds of host time
+ * per set -- so the host keeps up with the PCIe copy engine (2 MB of descriptors per 43 us). featvec may be NULL. */
+typedef struct {
+  const float* desc;
+  int32_t n;
+  int32_t row_stride_bytes; /* 0 = 512 */
+  const asdm_kp* kps;
+  const asdm_grid* grid;
+  const asdm_featvec* featvec;
+} asdm_set_desc;
+int asdm_set_create_batch(asdm_ctx* ctx, const asdm_set_desc* descs, int n_sets, asdm_set** out);
 int asdm_set_retain(asdm_set* set);
 int asdm_set_release(asdm_set* set);
 int asdm_set_size(const asdm_set* set);
@@ -252,6 +265,11 @@ typedef struct {
 int asdm_job_prepare(asdm_ctx* ctx, const asdm_job_desc* desc, asdm_job** out);
 int asdm_job_run(asdm_job* job);
 int asdm_job_fetch(asdm_job* job, int32_t* match12, float* dist12, int32_t* nmatches);
+/* Queues the device-to-host copies of the results behind the run and returns at once, so the copies of one job overlap
+ * the kernels of the next (page-locked destinations). The buffers hold the results only after asdm_job_fetch on the same
+ * pointers returned: it validates the run (candidate pools, speculative tensor-core route) and copies again only if the
+ * job had to be rerun. */
+int asdm_job_fetch_async(asdm_job* job, int32_t* match12, float* dist12, int32_t* nmatches);
 /* waits for the last run and, if a candidate pool overflowed, grows it and runs again; after it returns the device
  * outputs are final (fetch() calls it) */
 int asdm_job_settle(asdm_job* job);

@@ -363,8 +363,11 @@ def test_streamed_sweep_and_speculative_tensor_route(pkg, ctx, oracle, bad):
     match, dist, nm = ctx.pinned((pairs, n), np.int32), ctx.pinned((pairs, n), np.float32), ctx.pinned((pairs,), np.int32)
     retries = []
 
-    def make(i):
-        return pkg.DescriptorSet(ctx, host[i], kfs[i]["kps"], c["grid"], kfs[i]["fv"], async_upload=True)
+    def make(lo, hi):
+        if lo == 0:  # first wave one set at a time, the others as batches: both creation paths feed the same searches
+            return [pkg.DescriptorSet(ctx, host[i], kfs[i]["kps"], c["grid"], kfs[i]["fv"], async_upload=True) for i in range(lo, hi)]
+        return pkg.DescriptorSet.create_batch(ctx, host[lo:hi], [k["kps"] for k in kfs[lo:hi]], c["grid"],
+                                              [k["fv"] for k in kfs[lo:hi]])
     sets = sweep.run(make, [k["valid"] for k in kfs], match, dist, nm)
     retries.append(ctx.stat("retries"))
     onm, omatch, odist = oracle.batch_bow_kf_kf(kfs, c["ia"], c["ib"], c["nnratio"], c["check_ori"], threads=oracle.max_threads())
@@ -383,3 +386,27 @@ def test_streamed_sweep_and_speculative_tensor_route(pkg, ctx, oracle, bad):
     job.destroy()
     for s in sets:
         s.release()
+
+
+def test_batch_created_sets_in_projection_search(pkg, ctx, oracle):
+    """asdm_set_create_batch (keypoints + FeatureVector in one copy, one pack launch, grid built by the first projection
+    search): the sets behave exactly like individually created ones -- rows, padding, grid scan order."""
+    cs = [pkg.synth.config2(n_kp=n, n_mp=4 * n, n_in_view=n, th=2.0, seed_extra=e) for e, n in enumerate((1999, 300, 1))]
+    descs = [np.ascontiguousarray(c["desc_t"], np.float32) for c in cs]
+    sets = pkg.DescriptorSet.create_batch(ctx, descs, [c["kps_t"] for c in cs], cs[0]["grid"])
+    for c, F, d in zip(cs, sets, descs):
+        assert np.array_equal(F.read_desc().view(np.uint32), d.view(np.uint32))
+        q = c["queries"]
+        mt = pkg.ORBmatcher(ctx, c["nnratio"], True)
+        for _ in range(2):  # second call: grid already built
+            nm, assign, dist = mt.SearchByProjection_LocalMap(F, q["valid"], q["u"], q["v"], c["level"], c["view_cos"],
+                                                              q["blocks"], c["desc_q"], pkg.synth.scale_factors(), th=2.0,
+                                                              blocked0=c["blocked0"])
+            onm, oassign, odist = oracle.search_by_projection(c["desc_t"], c["kps_t"], c["grid"], q, c["desc_q"], c["blocked0"],
+                                                              c["mode"], c["th_accept"], c["best_init"], c["nnratio"],
+                                                              c["check_ori"], c["count_twice"])
+            _eq(assign, oassign, "assign")
+            _eq_dist(dist, odist, "dist")
+            assert nm == onm
+    for F in sets:
+        F.release()

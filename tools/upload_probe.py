@@ -33,3 +33,30 @@ def desc_only():
 run("desc + kps + grid + featvec", full)
 run("desc + kps + grid", nofv)
 run("desc only (pack kernel)", desc_only)
+kps_all, fv_all = [k["kps"] for k in kfs], [k["fv"] for k in kfs]
+def batch():
+    ss = pkg.DescriptorSet.create_batch(ctx, h_desc, kps_all, c["grid"], fv_all)
+    return ss, time.perf_counter()
+def batch_desc_only():
+    ss = pkg.DescriptorSet.create_batch(ctx, h_desc)
+    return ss, time.perf_counter()
+def batch4x16():
+    ss = []
+    for a in range(0, 64, 16):
+        ss += pkg.DescriptorSet.create_batch(ctx, h_desc[a:a + 16], kps_all[a:a + 16], c["grid"], fv_all[a:a + 16])
+    return ss, time.perf_counter()
+run("create_batch(64)", batch)
+run("create_batch(64) desc only", batch_desc_only)
+run("create_batch 4 x 16", batch4x16)
+# raw DMA: 64 cudaMemcpyAsync of 2 MB pinned -> device on one torch stream
+import torch
+dev = [torch.empty((n, 128), dtype=torch.float32, device="cuda") for _ in kfs]
+pin = [torch.from_numpy(h) for h in h_desc]
+st = torch.cuda.Stream()
+for rep in range(5):
+    torch.cuda.synchronize(); t = time.perf_counter()
+    with torch.cuda.stream(st):
+        for d, p in zip(dev, pin):
+            d.copy_(p, non_blocking=True)
+    ti = time.perf_counter(); torch.cuda.synchronize(); tt = time.perf_counter() - t
+print(f"{'raw torch copies (pinned? ' + str(pin[0].is_pinned()) + ')':44s} issue {1e3*(ti-t):6.3f} ms  done {1e3*tt:6.3f} ms  -> {131.072e6/tt/1e9:5.1f} GB/s")
