@@ -44,7 +44,7 @@ static int fail(asdm_ctx* ctx, int code, const char* what, cudaError_t e = cudaS
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // slots of asdm_ctx::scratch
-enum { SC_QUERY = 0, SC_QDESC = 1, SC_SEG = 2, SC_ENT = 3, SC_STATE = 4, SC_BLOCK = 5, SC_MISC = 6, SC_MP_ARGS = 7, SC_MP_DIST = 8, SC_VOC = 9 };
+enum { SC_QUERY = 0, SC_QDESC = 1, SC_SEG = 2, SC_ENT = 3, SC_STATE = 4, SC_BLOCK = 5, SC_MISC = 6, SC_MP_ARGS = 7, SC_MP_DIST = 8, SC_VOC = 9, SC_INIT = 10 };
 static int flatten_featvec(asdm_ctx* ctx, const asdm_featvec* fv, int n, int n_pad, uint32_t* node, int32_t* pos);
 
 // Device memory comes from the device's stream-ordered pool (cudaMallocAsync) with the release threshold lifted in
@@ -327,6 +327,7 @@ extern "C" int asdm_set_option(asdm_ctx* ctx, const char* key, int value) {
   if (!ctx || !key) return ASDM_ERR_INVALID;
   std::lock_guard<std::recursive_mutex> lk(ctx->mu);
   if (!strcmp(key, "force_exact")) ctx->opt_force_exact = value;
+  else if (!strcmp(key, "init_serial")) ctx->opt_init_serial = value;
   else if (!strcmp(key, "cand_cap")) ctx->opt_cand_cap = std::max(1, value);
   else if (!strcmp(key, "list_cap_per_query")) ctx->opt_list_cap_per_query = std::max(1, value);
   else if (!strcmp(key, "time_kernels")) ctx->opt_time_kernels = value;
@@ -343,6 +344,7 @@ extern "C" int asdm_get_stat(asdm_ctx* ctx, const char* key, int64_t* value) {
   else if (!strcmp(key, "total_launches")) *value = ctx->stat_total_launches;
   else if (!strcmp(key, "cand_cap")) *value = ctx->stat_cand_cap;
   else if (!strcmp(key, "retries")) *value = ctx->stat_retries;
+  else if (!strcmp(key, "init_sweeps")) *value = ctx->stat_init_sweeps;
   else if (!strcmp(key, "tc_used")) *value = ctx->stat_tc_used;
   else if (!strcmp(key, "tc_pairs")) *value = ctx->stat_tc_pairs;
   else if (!strcmp(key, "sm_count")) *value = ctx->sm_count;
@@ -1379,7 +1381,7 @@ struct ProjDev {
 
 // gather + distance with automatic growth of the entry pool; queries are already on the device
 static int proj_candidates(asdm_ctx* ctx, asdm_set* target, int nq, const float* d_desc_q, const int32_t* d_q_rows,
-                           const ProjGate& gate, int* ent_cap_io, ProjDev* out) {
+                           const ProjGate& gate, int* ent_cap_io, ProjDev* out, bool large_windows = false) {
   int ent_cap = std::max(*ent_cap_io, 1 << 14);
   {
     const int rc = ensure_grid(ctx, target);
@@ -1400,9 +1402,14 @@ static int proj_candidates(asdm_ctx* ctx, asdm_set* target, int nq, const float*
     pd.overflow = pd.total + 1;
     CK(cudaMemsetAsync(pd.total, 0, 8, ctx->stream));
     if (nq > 0) {
-      k_proj_gather<<<(nq + 127) / 128, 128, 0, ctx->stream>>>(pd.q, nq, target->kps, target->grid, gate, target->cell_start,
-                                                               target->cell_items, pd.seg, pd.ent_j, pd.ent_q, ent_cap,
-                                                               pd.total, pd.overflow);
+      if (large_windows)
+        k_proj_gather_warp<<<(nq * 32 + 255) / 256, 256, 0, ctx->stream>>>(pd.q, nq, target->kps, target->grid, gate,
+                                                                          target->cell_start, target->cell_items, pd.seg,
+                                                                          pd.ent_j, pd.ent_q, ent_cap, pd.total, pd.overflow);
+      else
+        k_proj_gather<<<(nq + 127) / 128, 128, 0, ctx->stream>>>(pd.q, nq, target->kps, target->grid, gate, target->cell_start,
+                                                                 target->cell_items, pd.seg, pd.ent_j, pd.ent_q, ent_cap,
+                                                                 pd.total, pd.overflow);
       LAUNCHED(ctx);
     }
     int32_t h[2] = {0, 0};
@@ -1572,10 +1579,55 @@ extern "C" int asdm_search_for_initialization(asdm_ctx* ctx, asdm_set* f1, asdm_
   ProjDev pd;
   ProjGate gate;
   memset(&gate, 0, sizeof gate);
-  if ((rc = proj_candidates(ctx, f2, n1, f1->desc, nullptr, gate, &ctx->proj_ent_cap, &pd))) return rc;
-  k_init_resolve<<<1, 32, 0, ctx->stream>>>(f1->kps, n1, f2->kps, n2, pd.seg, pd.ent_j, pd.ent_d, nnratio,
-                                            check_ori ? 1 : 0, d_md, d_m21, d_m12, d_d12, d_push, d_prev, d_nm);
-  LAUNCHED(ctx);
+  if ((rc = proj_candidates(ctx, f2, n1, f1->desc, nullptr, gate, &ctx->proj_ent_cap, &pd, window_size >= 30))) return rc;
+  // Jacobi sweeps to the fixed point of the serial replay (k_init_sweep); the serial kernel remains as the fallback
+  // for pathological inputs (more than INIT_K accepts of one keypoint, or no convergence within the sweep budget)
+  bool resolved = false;
+  ctx->stat_init_sweeps = 0;
+  if (n1 > 0 && !ctx->opt_init_serial) {
+    const int SWEEPS_PER_ROUND = 8, MAX_SWEEPS = 96;
+    const size_t per_buf = align_up(N1 * 8 + N2 * 4 + N2 * INIT_K * 8, 256);
+    const size_t state_bytes = align_up((size_t)(INIT_STATE_CHG + MAX_SWEEPS + 2) * 4, 256);
+    if ((rc = ensure(ctx, ctx->scratch[SC_INIT], state_bytes + 3 * per_buf))) return rc;
+    char* base = (char*)ctx->scratch[SC_INIT].p;
+    int32_t* d_state = (int32_t*)base;
+    InitBuf B[3];
+    for (int b = 0; b < 3; b++) {
+      char* p = base + state_bytes + (size_t)b * per_buf;
+      B[b].dec_j = (int32_t*)p;
+      B[b].dec_d = (float*)(p + N1 * 4);
+      B[b].cnt = (int32_t*)(p + N1 * 8);
+      B[b].lst_i = (int32_t*)(p + N1 * 8 + N2 * 4);
+      B[b].lst_d = (float*)(p + N1 * 8 + N2 * 4 + N2 * INIT_K * 4);
+    }
+    if ((rc = zero_device(ctx, base, state_bytes + 3 * per_buf))) return rc;
+    CK(cudaMemsetAsync(B[0].dec_j, 0xff, N1 * 4, ctx->stream));  // sweep 0: nobody has accepted anything
+    int32_t h_state[4] = {0, 0, 0, 0};
+    for (int t0 = 1; t0 + SWEEPS_PER_ROUND <= MAX_SWEEPS && !h_state[0] && !h_state[2]; t0 += SWEEPS_PER_ROUND) {
+      for (int t = t0; t < t0 + SWEEPS_PER_ROUND; t++) {
+        k_init_sweep<<<(n1 * 32 + 255) / 256, 256, 0, ctx->stream>>>(t, n1, n2, pd.seg, pd.ent_j, pd.ent_d, nnratio,
+                                                                     B[(t - 1) % 3], B[t % 3], B[(t + 1) % 3], d_state);
+        LAUNCHED(ctx);
+      }
+      // an empty launch in the next slot notices a last sweep of the round that changed nothing
+      k_init_sweep<<<1, 32, 0, ctx->stream>>>(t0 + SWEEPS_PER_ROUND, 0, 0, pd.seg, pd.ent_j, pd.ent_d, nnratio, B[0], B[0], B[0],
+                                              d_state);
+      k_init_finalize<<<1, 1024, 0, ctx->stream>>>(f1->kps, n1, f2->kps, check_ori ? 1 : 0, B[0], B[1], B[2], d_state, d_m12,
+                                                   d_d12, d_prev, d_nm);
+      LAUNCHED(ctx);
+      CK(cudaGetLastError());
+      CK(cudaMemcpyAsync(h_state, d_state, 16, cudaMemcpyDeviceToHost, ctx->stream));
+      CK(cudaStreamSynchronize(ctx->stream));
+      if (!h_state[0] && !h_state[2]) ctx->stat_retries++;  // another round of sweeps
+    }
+    resolved = h_state[0] && !h_state[2];
+    ctx->stat_init_sweeps = resolved ? 1 : 0;
+  }
+  if (!resolved) {
+    k_init_resolve<<<1, 32, 0, ctx->stream>>>(f1->kps, n1, f2->kps, n2, pd.seg, pd.ent_j, pd.ent_d, nnratio,
+                                              check_ori ? 1 : 0, d_md, d_m21, d_m12, d_d12, d_push, d_prev, d_nm);
+    LAUNCHED(ctx);
+  }
   CK(cudaGetLastError());
   int32_t nm = 0;
   if (n1 > 0) {

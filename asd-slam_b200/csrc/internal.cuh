@@ -50,6 +50,8 @@ struct asdm_ctx {
   int opt_cand_cap = 8;
   int opt_list_cap_per_query = 4;  // tensor-core short list slots per query row (grows on overflow)
   int opt_tc_epi_warps = 8;        // epilogue warps of the tensor-core kernel: 4 or 8
+  int opt_init_serial = 0;         // SearchForInitialization: 1 = the serial replay kernel instead of the Jacobi sweeps
+  int64_t stat_init_sweeps = 0;    // 1 when the last SearchForInitialization was resolved by the sweeps
   int opt_tc_variant = 0;          // pipeline-shape experiments of the tensor-core kernel (tc_shortlist.cu)
   int64_t stat_launches = 0;       // kernels launched by the last call / job run
   int64_t stat_total_launches = 0;

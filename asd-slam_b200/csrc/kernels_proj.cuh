@@ -444,3 +444,213 @@ __global__ void __launch_bounds__(256) k_init_queries(const asdm_kp* __restrict_
   Q.angle = kp.angle;
   q[i] = Q;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Warp-per-query variant of k_proj_gather for LARGE windows (SearchForInitialization: 200 px windows, hundreds of
+// candidates per query): the 32 lanes share each column's contiguous CSR range and compact the kept keypoints with
+// ballots, which preserves the reference's scan order exactly as the thread-per-query kernel does.
+__global__ void __launch_bounds__(256) k_proj_gather_warp(const asdm_proj_query* __restrict__ q, int nq,
+                                                          const asdm_kp* __restrict__ kps, asdm_grid g, ProjGate G,
+                                                          const int32_t* __restrict__ cell_start,
+                                                          const int32_t* __restrict__ cell_items,
+                                                          ProjSeg* __restrict__ seg, int32_t* __restrict__ ent_j,
+                                                          int32_t* __restrict__ ent_q, int ent_cap,
+                                                          int32_t* __restrict__ total, int32_t* __restrict__ overflow) {
+  const int lane = threadIdx.x & 31;
+  const int iq = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (iq >= nq) return;
+  const asdm_proj_query Q = q[iq];
+  ProjSeg s{0, 0};
+  int x0, x1, y0, y1;
+  if (Q.valid && area_cells(g, Q.u, Q.v, Q.r, x0, x1, y0, y1)) {
+    const bool check_levels = (Q.min_level > 0) || (Q.max_level >= 0);  // Frame.cc:242
+    int cnt = 0;
+    for (int ix = x0; ix <= x1; ix++) {
+      const int b = cell_start[ix * g.rows + y0], e = cell_start[ix * g.rows + y1 + 1];
+      for (int p = b; p < e; p += 32) {
+        const bool keep = p + lane < e &&
+                          area_keep(kps[cell_items[p + lane]], Q.u, Q.v, Q.r, check_levels, Q.min_level, Q.max_level, G);
+        cnt += __popc(__ballot_sync(0xffffffffu, keep));
+      }
+    }
+    if (cnt > 0) {
+      int off = 0;
+      if (lane == 0) off = atomicAdd(total, cnt);
+      off = __shfl_sync(0xffffffffu, off, 0);
+      if (off + cnt > ent_cap) {
+        if (lane == 0) *overflow = 1;
+      } else {
+        s.off = off;
+        s.cnt = cnt;
+        int w = off;
+        for (int ix = x0; ix <= x1; ix++) {
+          const int b = cell_start[ix * g.rows + y0], e = cell_start[ix * g.rows + y1 + 1];
+          for (int p = b; p < e; p += 32) {
+            int j = -1;
+            bool keep = false;
+            if (p + lane < e) {
+              j = cell_items[p + lane];
+              keep = area_keep(kps[j], Q.u, Q.v, Q.r, check_levels, Q.min_level, Q.max_level, G);
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, keep);
+            if (keep) {
+              const int at = w + __popc(m & ((1u << lane) - 1u));
+              ent_j[at] = j;
+              ent_q[at] = iq;
+            }
+            w += __popc(m);
+          }
+        }
+      }
+    }
+  }
+  if (lane == 0) seg[iq] = s;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// SearchForInitialization (ORBmatcher.cc:416-531) without the serial replay. The decision of query i1 (which
+// keypoint it accepts, at what distance) depends on earlier queries only through vMatchedDistance (:456), and
+// vMatchedDistance[j] at the time of i1 = the smallest accepted distance among earlier queries that took j (every
+// accept lowers it, :456 + :480). So the decisions are the unique fixed point of  D(i) = f(D(i') : i' < i);  Jacobi
+// sweeps over all queries in parallel reach it (after sweep t the first t queries are final; in practice a handful of
+// sweeps), and a sweep that changes nothing proves it. Steals (:474-478) do not feed back into decisions: they only
+// decide which accept survives, resolved at the end (the last accept of a keypoint wins).
+#define INIT_K 8  // accepts remembered per keypoint and sweep; more -> overflow flag -> the serial kernel takes over
+struct InitBuf {
+  int32_t* dec_j;  // [n1] keypoint accepted by query i, -1 = none
+  float* dec_d;    // [n1]
+  int32_t* cnt;    // [n2] accepts of keypoint j in this sweep
+  int32_t* lst_i;  // [n2][INIT_K] accepting queries (unordered)
+  float* lst_d;    // [n2][INIT_K] their distances
+};
+// state: [0] converged, [1] buffer holding the fixed point, [2] overflow, [4 + t] sweep t changed a decision
+#define INIT_STATE_CHG 4
+
+__global__ void __launch_bounds__(256) k_init_sweep(int t, int n1, int n2, const ProjSeg* __restrict__ seg,
+                                                    const int32_t* __restrict__ ent_j, const float* __restrict__ ent_d,
+                                                    float nnratio, InitBuf prev, InitBuf cur, InitBuf next,
+                                                    int32_t* __restrict__ state) {
+  if (state[0]) return;
+  if (t >= 2 && state[INIT_STATE_CHG + t - 1] == 0) {  // the previous sweep changed nothing: fixed point
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      state[1] = (t - 1) % 3;
+      __threadfence();
+      state[0] = 1;
+    }
+    return;
+  }
+  for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n2; j += gridDim.x * blockDim.x) next.cnt[j] = 0;
+  const int lane = threadIdx.x & 31;
+  const int i1 = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (i1 >= n1) return;
+  const ProjSeg s = seg[i1];
+  const int BIG = INT_MAX;
+  float b1 = 100.f, b2 = 100.f;
+  int p1 = BIG, p2 = BIG, j1 = -1;
+  for (int c = lane; c < s.cnt; c += 32) {
+    const int j = ent_j[s.off + c];
+    const float d = ent_d[s.off + c];
+    if (!(d < 100.f)) continue;
+    // vMatchedDistance[j] as query i1 would find it (:456)
+    float md = 100.f;
+    const int na = min(prev.cnt[j], INIT_K);
+    for (int a = 0; a < na; a++)
+      if (prev.lst_i[j * INIT_K + a] < i1) md = fminf(md, prev.lst_d[j * INIT_K + a]);
+    if (md <= d) continue;
+    if (two_min_before(d, c, b1, p1)) {
+      b2 = b1; p2 = p1;
+      b1 = d; p1 = c; j1 = j;
+    } else if (two_min_before(d, c, b2, p2)) {
+      b2 = d; p2 = c;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ob1 = __shfl_xor_sync(0xffffffffu, b1, o), ob2 = __shfl_xor_sync(0xffffffffu, b2, o);
+    const int op1 = __shfl_xor_sync(0xffffffffu, p1, o), op2 = __shfl_xor_sync(0xffffffffu, p2, o);
+    const int oj1 = __shfl_xor_sync(0xffffffffu, j1, o);
+    if (two_min_before(ob1, op1, b1, p1)) {
+      if (two_min_before(b1, p1, ob2, op2)) { b2 = b1; p2 = p1; } else { b2 = ob2; p2 = op2; }
+      b1 = ob1; p1 = op1; j1 = oj1;
+    } else {
+      if (two_min_before(ob1, op1, b2, p2)) { b2 = ob1; p2 = op1; }
+    }
+  }
+  if (lane == 0) {
+    const bool accept = j1 >= 0 && b1 <= ASDM_TH_LOW && b1 < __fmul_rn(b2, nnratio);  // :470-472
+    const int dj = accept ? j1 : -1;
+    const float dd = accept ? b1 : -1.f;
+    if (dj != prev.dec_j[i1] || __float_as_int(dd) != __float_as_int(prev.dec_d[i1])) state[INIT_STATE_CHG + t] = 1;
+    cur.dec_j[i1] = dj;
+    cur.dec_d[i1] = dd;
+    if (accept) {
+      const int slot = atomicAdd(&cur.cnt[j1], 1);
+      if (slot < INIT_K) {
+        cur.lst_i[j1 * INIT_K + slot] = i1;
+        cur.lst_d[j1 * INIT_K + slot] = b1;
+      } else {
+        state[2] = 1;
+      }
+    }
+  }
+}
+
+// Tail of SearchForInitialization on the fixed point: which accept of every keypoint survives (the last one, :474-482),
+// the rotation histogram over ALL accepts including stolen ones (:486-496, :515), nmatches and vbPrevMatched (:526-528).
+__global__ void __launch_bounds__(1024) k_init_finalize(const asdm_kp* __restrict__ kps1, int n1,
+                                                        const asdm_kp* __restrict__ kps2, int check_ori, InitBuf b0,
+                                                        InitBuf b1, InitBuf b2, const int32_t* __restrict__ state,
+                                                        int32_t* __restrict__ matches12, float* __restrict__ dist12,
+                                                        float* __restrict__ prev_matched,
+                                                        int32_t* __restrict__ nmatches_out) {
+  if (!state[0] || state[2]) return;  // not converged yet / overflow: the host continues or falls back
+  const InitBuf B = state[1] == 0 ? b0 : (state[1] == 1 ? b1 : b2);
+  __shared__ int s_hist[ASDM_HISTO_LENGTH];
+  __shared__ int s_keep[3];
+  __shared__ int s_live, s_removed;
+  const int t = threadIdx.x, nt = blockDim.x;
+  if (t < ASDM_HISTO_LENGTH) s_hist[t] = 0;
+  if (t == 0) { s_live = 0; s_removed = 0; }
+  __syncthreads();
+  int live = 0;
+  for (int i = t; i < n1; i += nt) {
+    const int j = B.dec_j[i];
+    int m = -1;
+    float d = -1.f;
+    if (j >= 0) {
+      bool last = true;  // no later query accepted j
+      const int na = min(B.cnt[j], INIT_K);
+      for (int a = 0; a < na; a++) last &= B.lst_i[j * INIT_K + a] <= i;
+      if (last) { m = j; d = B.dec_d[i]; live++; }
+      if (check_ori) atomicAdd(&s_hist[asdm_rot_bin(kps1[i].angle, kps2[j].angle)], 1);
+    }
+    matches12[i] = m;
+    dist12[i] = d;
+  }
+  atomicAdd(&s_live, live);
+  __syncthreads();
+  if (check_ori) {  // :500-523
+    if (t == 0) asdm_three_maxima(s_hist, ASDM_HISTO_LENGTH, s_keep[0], s_keep[1], s_keep[2]);
+    __syncthreads();
+    int removed = 0;
+    for (int i = t; i < n1; i += nt) {
+      const int j = B.dec_j[i];
+      if (j < 0) continue;
+      const int b = asdm_rot_bin(kps1[i].angle, kps2[j].angle);
+      if (b == s_keep[0] || b == s_keep[1] || b == s_keep[2]) continue;
+      if (matches12[i] >= 0) {  // :515
+        matches12[i] = -1;
+        dist12[i] = -1.f;
+        removed++;
+      }
+    }
+    atomicAdd(&s_removed, removed);
+  }
+  __syncthreads();
+  for (int i = t; i < n1; i += nt)  // :526-528
+    if (matches12[i] >= 0) {
+      prev_matched[2 * i] = kps2[matches12[i]].x;
+      prev_matched[2 * i + 1] = kps2[matches12[i]].y;
+    }
+  if (t == 0) *nmatches_out = s_live - s_removed;
+}

@@ -258,13 +258,20 @@ def test_c3_stereo_and_frame_to_frame(pkg, ctx, oracle):
         x.release()
 
 
-@pytest.mark.parametrize("n,window", [(4000, 100), (600, 40), (30, 500)])
-def test_search_for_initialization(pkg, ctx, oracle, n, window):
+@pytest.mark.parametrize("serial", [0, 1])
+@pytest.mark.parametrize("n,window", [(4000, 100), (600, 40), (30, 500), (900, 12)])
+def test_search_for_initialization(pkg, ctx, oracle, n, window, serial):
+    """serial=0: Jacobi sweeps to the fixed point of the reference's serial replay (k_init_sweep); serial=1: the serial
+    replay kernel itself (the fallback). Both must give the reference's lists."""
     c = pkg.synth.config_init(n=n, window=window)
     F1 = pkg.DescriptorSet(ctx, c["desc1"], c["kps1"], c["grid2"])
     F2 = pkg.DescriptorSet(ctx, c["desc2"], c["kps2"], c["grid2"])
     mt = pkg.ORBmatcher(ctx, c["nnratio"], True)
+    ctx.set_option("init_serial", serial)
     nm, match, dist, prev = mt.SearchForInitialization(F1, F2, c["prev_matched"], window)
+    ctx.set_option("init_serial", 0)
+    if n >= 600:
+        assert ctx.stat("init_sweeps") == 1 - serial
     onm, omatch, odist, oprev = oracle.search_for_initialization(c["desc1"], c["kps1"], c["desc2"], c["kps2"], c["grid2"],
                                                                  c["prev_matched"], window, c["nnratio"], 1)
     _eq(match, omatch, "matches12")
