@@ -1381,7 +1381,10 @@ struct ProjDev {
 
 // gather + distance with automatic growth of the entry pool; queries are already on the device
 static int proj_candidates(asdm_ctx* ctx, asdm_set* target, int nq, const float* d_desc_q, const int32_t* d_q_rows,
-                           const ProjGate& gate, int* ent_cap_io, ProjDev* out, bool large_windows = false) {
+                           const ProjGate& gate, int* ent_cap_io, ProjDev* out, bool large_windows = false,
+                           bool defer_check = false) {
+  // defer_check: no wait for the entry count -- the distance kernel sizes itself from the device counter and the caller
+  // reads (total, overflow) back together with its results, growing the pool and repeating the search if needed
   int ent_cap = std::max(*ent_cap_io, 1 << 14);
   {
     const int rc = ensure_grid(ctx, target);
@@ -1411,6 +1414,16 @@ static int proj_candidates(asdm_ctx* ctx, asdm_set* target, int nq, const float*
                                                                  target->cell_items, pd.seg, pd.ent_j, pd.ent_q, ent_cap,
                                                                  pd.total, pd.overflow);
       LAUNCHED(ctx);
+    }
+    if (defer_check) {
+      if (nq > 0) {
+        k_proj_dist<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(d_desc_q, d_q_rows, target->desc, pd.ent_j, pd.ent_q, ent_cap,
+                                                               pd.total, pd.ent_d);
+        LAUNCHED(ctx);
+      }
+      *ent_cap_io = ent_cap;
+      *out = pd;
+      return ASDM_OK;
     }
     int32_t h[2] = {0, 0};
     CK(cudaMemcpyAsync(h, pd.total, 8, cudaMemcpyDeviceToHost, ctx->stream));
@@ -1449,7 +1462,8 @@ static int search_by_projection_impl(asdm_ctx* ctx, asdm_set* target, const asdm
   const int n_t = target->n;
   int rc;
   if ((rc = ensure(ctx, ctx->scratch[SC_QUERY], (size_t)std::max(nq, 1) * sizeof(asdm_proj_query)))) return rc;
-  if (nq > 0) CK(cudaMemcpyAsync(ctx->scratch[SC_QUERY].p, q, (size_t)nq * sizeof(asdm_proj_query), cudaMemcpyHostToDevice, ctx->stream));
+  // queries, masks and row maps are caller memory (pageable): staged through the pinned arena so nothing blocks
+  if (nq > 0 && (rc = stage_upload(ctx, ctx->scratch[SC_QUERY].p, q, (size_t)nq * sizeof(asdm_proj_query)))) return rc;
   const float* d_desc_q = nullptr;
   const int32_t* d_rows = nullptr;
   if (desc_q) {
@@ -1479,7 +1493,7 @@ static int search_by_projection_impl(asdm_ctx* ctx, asdm_set* target, const asdm
       for (int i = 0; i < nq; i++)
         if (q[i].valid && (q_rows[i] < 0 || q_rows[i] >= q_set->n)) return fail(ctx, ASDM_ERR_INVALID, "query row out of range");
       if ((rc = ensure(ctx, ctx->scratch[SC_QDESC], (size_t)std::max(nq, 1) * sizeof(int32_t)))) return rc;
-      if (nq > 0) CK(cudaMemcpyAsync(ctx->scratch[SC_QDESC].p, q_rows, (size_t)nq * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+      if (nq > 0 && (rc = stage_upload(ctx, ctx->scratch[SC_QDESC].p, q_rows, (size_t)nq * sizeof(int32_t)))) return rc;
       d_rows = (const int32_t*)ctx->scratch[SC_QDESC].p;
     } else if (nq > q_set->n) {
       return fail(ctx, ASDM_ERR_INVALID, "more queries than rows in the query set");
@@ -1488,7 +1502,7 @@ static int search_by_projection_impl(asdm_ctx* ctx, asdm_set* target, const asdm
   const uint8_t* d_blocked = nullptr;
   if (blocked0) {
     if ((rc = ensure(ctx, ctx->scratch[SC_BLOCK], (size_t)std::max(n_t, 1)))) return rc;
-    if (n_t > 0) CK(cudaMemcpyAsync(ctx->scratch[SC_BLOCK].p, blocked0, (size_t)n_t, cudaMemcpyHostToDevice, ctx->stream));
+    if (n_t > 0 && (rc = stage_upload(ctx, ctx->scratch[SC_BLOCK].p, blocked0, (size_t)n_t))) return rc;
     d_blocked = (const uint8_t*)ctx->scratch[SC_BLOCK].p;
   }
   ProjDev pd;
@@ -1500,31 +1514,58 @@ static int search_by_projection_impl(asdm_ctx* ctx, asdm_set* target, const asdm
     gate.n_levels = p->n_levels;
     memcpy(gate.inv_level_sigma2, p->inv_level_sigma2, (size_t)p->n_levels * sizeof(float));
   }
-  if ((rc = proj_candidates(ctx, target, nq, d_desc_q, d_rows, gate, &ctx->proj_ent_cap, &pd))) return rc;
   // state: acc[nq] own[2*n_t] assign[n_t] dist[n_t] nm[4] qbest[nq] qdist[nq]
-  const size_t state = (3 * (size_t)std::max(nq, 1) + 4 * (size_t)std::max(n_t, 1) + 4) * 4;
+  const size_t NQ = (size_t)std::max(nq, 1), NT = (size_t)std::max(n_t, 1);
+  const size_t state = (3 * NQ + 4 * NT + 4) * 4;
   if ((rc = ensure(ctx, ctx->scratch[SC_STATE], state))) return rc;
   int32_t* acc = (int32_t*)ctx->scratch[SC_STATE].p;
-  int32_t* own = acc + std::max(nq, 1);
-  int32_t* d_assign = own + 2 * (size_t)std::max(n_t, 1);
-  float* d_dist = (float*)(d_assign + std::max(n_t, 1));
-  int32_t* d_nm = (int32_t*)(d_dist + std::max(n_t, 1));
+  int32_t* own = acc + NQ;
+  int32_t* d_assign = own + 2 * NT;
+  float* d_dist = (float*)(d_assign + NT);
+  int32_t* d_nm = (int32_t*)(d_dist + NT);
   int32_t* d_qbest = d_nm + 4;
-  float* d_qdist = (float*)(d_qbest + std::max(nq, 1));
+  float* d_qdist = (float*)(d_qbest + NQ);
   ProjParamsDev P{p->mode, p->th_accept, p->best_init, p->nnratio, p->check_ori ? 1 : 0, p->count_twice ? 1 : 0};
-  k_proj_resolve<<<1, 1024, 0, ctx->stream>>>(pd.q, nq, target->kps, n_t, d_blocked, pd.seg, pd.ent_j, pd.ent_d, P, acc,
-                                              own, d_assign, d_dist, d_nm, query_best ? d_qbest : nullptr, d_qdist);
-  LAUNCHED(ctx);
-  CK(cudaGetLastError());
   int32_t nm = 0;
-  if (query_best && nq > 0) {
-    CK(cudaMemcpyAsync(query_best, d_qbest, (size_t)nq * 4, cudaMemcpyDeviceToHost, ctx->stream));
-    if (query_dist) CK(cudaMemcpyAsync(query_dist, d_qdist, (size_t)nq * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  for (int attempt = 0;; attempt++) {
+    if (attempt >= 20) return fail(ctx, ASDM_ERR_INTERNAL, "projection entry pool kept overflowing");
+    // gather -> distances -> resolve back to back; the entry pool is checked with the results (one wait per call)
+    if ((rc = proj_candidates(ctx, target, nq, d_desc_q, d_rows, gate, &ctx->proj_ent_cap, &pd, false, true))) return rc;
+    k_proj_resolve<<<1, 1024, 0, ctx->stream>>>(pd.q, nq, target->kps, n_t, d_blocked, pd.seg, pd.ent_j, pd.ent_d, P, acc,
+                                                own, d_assign, d_dist, d_nm, query_best ? d_qbest : nullptr, d_qdist);
+    LAUNCHED(ctx);
+    CK(cudaGetLastError());
+    // results land in the pinned arena (the caller's arrays are pageable) and are handed over after the wait
+    void* ho = nullptr;
+    if ((rc = stage_alloc(ctx, (2 * NQ + 2 * NT + 8) * 4, &ho))) return rc;
+    int32_t* h_pool = (int32_t*)ho;  // total, overflow, nm
+    int32_t* h_assign = h_pool + 8;
+    float* h_dist = (float*)(h_assign + NT);
+    int32_t* h_qbest = (int32_t*)(h_dist + NT);
+    float* h_qdist = (float*)(h_qbest + NQ);
+    CK(cudaMemcpyAsync(h_pool, pd.total, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(h_pool + 2, d_nm, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (query_best && nq > 0) {
+      CK(cudaMemcpyAsync(h_qbest, d_qbest, (size_t)nq * 4, cudaMemcpyDeviceToHost, ctx->stream));
+      if (query_dist) CK(cudaMemcpyAsync(h_qdist, d_qdist, (size_t)nq * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    if ((assign || dist_t) && n_t > 0)  // assign and dist are adjacent on both sides: one copy
+      CK(cudaMemcpyAsync(h_assign, d_assign, (size_t)n_t * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (h_pool[1]) {  // pool too small: h_pool[0] is the exact demand. Inputs are still resident: search again
+      ctx->proj_ent_cap = std::max(ctx->proj_ent_cap * 2, h_pool[0] + 1024);
+      ctx->stat_retries++;
+      continue;
+    }
+    nm = h_pool[2];
+    if (query_best && nq > 0) {
+      memcpy(query_best, h_qbest, (size_t)nq * 4);
+      if (query_dist) memcpy(query_dist, h_qdist, (size_t)nq * 4);
+    }
+    if (assign && n_t > 0) memcpy(assign, h_assign, (size_t)n_t * 4);
+    if (dist_t && n_t > 0) memcpy(dist_t, h_dist, (size_t)n_t * 4);
+    break;
   }
-  if (assign && n_t > 0) CK(cudaMemcpyAsync(assign, d_assign, (size_t)n_t * 4, cudaMemcpyDeviceToHost, ctx->stream));
-  if (dist_t && n_t > 0) CK(cudaMemcpyAsync(dist_t, d_dist, (size_t)n_t * 4, cudaMemcpyDeviceToHost, ctx->stream));
-  CK(cudaMemcpyAsync(&nm, d_nm, 4, cudaMemcpyDeviceToHost, ctx->stream));
-  CK(cudaStreamSynchronize(ctx->stream));
   synced(ctx);
   if (nmatches) *nmatches = nm;
   return ASDM_OK;

@@ -72,6 +72,21 @@ def measure(pkg, ctx, reps=200, cpu=True, oracle=None):
     r = timeit(lambda: mt.SearchByProjection_LocalMap(F, q["valid"], q["u"], q["v"], c["level"], c["view_cos"], q["blocks"],
                                                       c["desc_q"], sf, th=1.0, blocked0=c["blocked0"]), reps)
     r["launches"] = ctx.stat("gpu_launches")
+    # the C-ABI call alone, on the query records a C++ adaptor would have filled (asdm_proj_query array built beforehand)
+    r["abi_call_ms"] = timeit(lambda: mt.SearchByProjection(F, q, desc_q=c["desc_q"], blocked0=c["blocked0"], mode=pkg.ASDM_PROJ_RATIO_LEVEL,
+                                                            th_accept=1.5, best_init=256.0, count_twice=True, check_ori=False), reps)["median_ms"]
+    # map-point descriptors resident in a device pool (they only change in ComputeDistinctiveDescriptors): no descriptor
+    # crosses PCIe per frame, the call ships the 8000 query records only
+    pool = pkg.DescriptorSet(ctx, c["desc_q"])
+    res_pool = mt.SearchByProjection(F, q, q_set=pool, blocked0=c["blocked0"], mode=pkg.ASDM_PROJ_RATIO_LEVEL, th_accept=1.5,
+                                     best_init=256.0, count_twice=True, check_ori=False)
+    res_host = mt.SearchByProjection(F, q, desc_q=c["desc_q"], blocked0=c["blocked0"], mode=pkg.ASDM_PROJ_RATIO_LEVEL,
+                                     th_accept=1.5, best_init=256.0, count_twice=True, check_ori=False)
+    assert res_pool[0] == res_host[0] and np.array_equal(res_pool[1], res_host[1])
+    r["abi_call_resident_pool_ms"] = timeit(lambda: mt.SearchByProjection(F, q, q_set=pool, blocked0=c["blocked0"],
+                                                                          mode=pkg.ASDM_PROJ_RATIO_LEVEL, th_accept=1.5, best_init=256.0,
+                                                                          count_twice=True, check_ori=False), reps)["median_ms"]
+    pool.release()
     r["cpu_oracle_ms"] = cpu_time(lambda: oracle.search_by_projection(c["desc_t"], c["kps_t"], c["grid"], q, c["desc_q"], c["blocked0"],
                                                                       c["mode"], c["th_accept"], c["best_init"], c["nnratio"],
                                                                       c["check_ori"], c["count_twice"]))
