@@ -583,6 +583,18 @@ extern "C" int asdm_set_create_batch(asdm_ctx* ctx, const asdm_set_desc* descs, 
     side_bytes += 256 + (d.kps ? n_pad * sizeof(asdm_kp) : 0) + (d.featvec ? n_pad * 8 : 0);
   }
   if (n_sets == 0) return ASDM_OK;
+  // rows that already live on this GPU (keyframes replicated over NVLink by an all-gather queued on the main stream):
+  // the "upload" is then a device-to-device copy, ordered behind whatever the main stream holds so far
+  bool any_on_device = false;
+  for (int k = 0; k < n_sets && !any_on_device; k++) {
+    cudaPointerAttributes at;
+    if (descs[k].n > 0 && cudaPointerGetAttributes(&at, descs[k].desc) == cudaSuccess) any_on_device = at.type == cudaMemoryTypeDevice;
+    else cudaGetLastError();
+  }
+  if (any_on_device) {
+    CK(cudaEventRecord(ctx->prep_done, ctx->stream));
+    CK(cudaStreamWaitEvent(ctx->upload_stream, ctx->prep_done, 0));
+  }
   SideBlock* side = new (std::nothrow) SideBlock;
   if (!side) return fail(ctx, ASDM_ERR_OOM, "host allocation");
   auto bail = [&](int code) {
@@ -643,10 +655,10 @@ extern "C" int asdm_set_create_batch(asdm_ctx* ctx, const asdm_set_desc* descs, 
     if (d.n > 0) {
       const int stride = d.row_stride_bytes ? d.row_stride_bytes : (int)(ASDM_DESC_DIM * sizeof(float));
       if (stride == (int)(ASDM_DESC_DIM * sizeof(float)))
-        e = cudaMemcpyAsync(s->desc, d.desc, (size_t)d.n * ASDM_DESC_DIM * sizeof(float), cudaMemcpyHostToDevice, ctx->upload_stream);
+        e = cudaMemcpyAsync(s->desc, d.desc, (size_t)d.n * ASDM_DESC_DIM * sizeof(float), cudaMemcpyDefault, ctx->upload_stream);
       else
         e = cudaMemcpy2DAsync(s->desc, ASDM_DESC_DIM * sizeof(float), d.desc, stride, ASDM_DESC_DIM * sizeof(float), d.n,
-                              cudaMemcpyHostToDevice, ctx->upload_stream);
+                              cudaMemcpyDefault, ctx->upload_stream);
       if (e != cudaSuccess) return bail(fail(ctx, ASDM_ERR_CUDA, "descriptor upload", e));
     }
   }

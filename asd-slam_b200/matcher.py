@@ -147,12 +147,17 @@ class DescriptorSet:
         keep = []
         for k in range(m):
             d = descs[k]
-            assert d.dtype == np.float32 and d.ndim == 2 and d.shape[1] == 128 and d.flags["C_CONTIGUOUS"]
             a = arr[k]
-            a.desc, a.n, a.row_stride_bytes = d.ctypes.data, d.shape[0], 0
+            if hasattr(d, "__cuda_array_interface__"):  # rows already on this GPU (e.g. a torch CUDA tensor): device-to-device
+                cai = d.__cuda_array_interface__
+                assert cai["typestr"] == "<f4" and len(cai["shape"]) == 2 and cai["shape"][1] == 128 and not cai.get("strides")
+                a.desc, a.n, a.row_stride_bytes = cai["data"][0], int(cai["shape"][0]), 0
+            else:
+                assert d.dtype == np.float32 and d.ndim == 2 and d.shape[1] == 128 and d.flags["C_CONTIGUOUS"]
+                a.desc, a.n, a.row_stride_bytes = d.ctypes.data, d.shape[0], 0
             if kps is not None:
                 kp = np.ascontiguousarray(kps[k], dtype=KP_DTYPE)
-                assert len(kp) == d.shape[0]
+                assert len(kp) == a.n
                 a.kps = kp.ctypes.data
                 keep.append(kp)
                 if g is not None:
@@ -168,7 +173,7 @@ class DescriptorSet:
         out = []
         for k in range(m):
             self = cls.__new__(cls)
-            self.ctx, self.h, self.n, self._desc_keepalive = ctx, C.c_void_p(hs[k]), descs[k].shape[0], descs[k]
+            self.ctx, self.h, self.n, self._desc_keepalive = ctx, C.c_void_p(hs[k]), int(arr[k].n), descs[k]
             out.append(self)
         return out
 

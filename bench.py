@@ -295,7 +295,7 @@ def run_ours(args):
             jb.fetch(h_match, h_dist, h_nm)
         else:
             rep_desc.upload(h_desc_t)
-            ss = [pkg.DescriptorSet(ctx, rep_desc.rows(i, n), k["kps"], c["grid"], k["fv"]) for i, k in enumerate(kfs)]
+            ss = pkg.DescriptorSet.create_batch(ctx, [rep_desc.rows(i, n) for i in range(len(kfs))], kps_all, c["grid"], fv_all)
             jb = pkg.ShardedPairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, ss, masks, g_ia, g_ib, c["nnratio"], c["check_ori"],
                                     rank=rank, world=world)
             jb.run()

@@ -229,7 +229,8 @@ def test_sharded_job_world1(pkg, ctx, oracle, kind):
 
 
 @pytest.mark.gpu
-def test_sets_from_replicated_device_rows(pkg, ctx, oracle):
+@pytest.mark.parametrize("batch", [False, True])
+def test_sets_from_replicated_device_rows(pkg, ctx, oracle, batch):
     """Keyframes uploaded into a device slab (ReplicatedDescriptors, world 1) and turned into sets device-to-device
     behave exactly like sets uploaded from the host."""
     import torch
@@ -242,7 +243,11 @@ def test_sets_from_replicated_device_rows(pkg, ctx, oracle):
         h = [torch.from_numpy(k["desc"]).pin_memory() for k in kfs]
         rep = pkg.ReplicatedDescriptors(ctx, len(kfs), n)
         rep.upload(h)
-        sets = [pkg.DescriptorSet(ctx, rep.rows(i, n), k["kps"], c["grid"], k["fv"]) for i, k in enumerate(kfs)]
+        if batch:  # asdm_set_create_batch on device rows: one round of copies, ordered behind the all-gather
+            sets = pkg.DescriptorSet.create_batch(ctx, [rep.rows(i, n) for i in range(len(kfs))], [k["kps"] for k in kfs],
+                                                  c["grid"], [k["fv"] for k in kfs])
+        else:
+            sets = [pkg.DescriptorSet(ctx, rep.rows(i, n), k["kps"], c["grid"], k["fv"]) for i, k in enumerate(kfs)]
         for s, k in zip(sets, kfs):
             assert np.array_equal(s.read_desc(), k["desc"])
         job = pkg.PairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, sets, [k["valid"] for k in kfs], c["ia"], c["ib"], c["nnratio"], 1)
