@@ -111,7 +111,7 @@ static int ensure(asdm_ctx* ctx, DevBuf& b, size_t bytes) {
 }
 
 static void release(asdm_ctx* ctx, DevBuf& b) {
-  block_put(ctx, b.p, b.cap);
+  if (b.cap) block_put(ctx, b.p, b.cap);  // cap == 0: a view into another block (job input / zero arenas)
   b.p = nullptr;
   b.cap = 0;
 }
@@ -158,6 +158,7 @@ static int zero_device(asdm_ctx* ctx, void* dst, size_t bytes) {  // dst 16-byte
   const size_t n = (bytes + 15) / 16;
   if (!n) return ASDM_OK;
   k_zero16<<<(int)std::min<size_t>((n + 255) / 256, 1184), 256, 0, ctx->stream>>>((uint4*)dst, n);
+  LAUNCHED(ctx);
   CK(cudaGetLastError());
   return ASDM_OK;
 }
@@ -174,6 +175,7 @@ static int pull_to_device(asdm_ctx* ctx, void* dst, const void* h, size_t bytes)
   const int blocks = (int)std::min<size_t>((n + 255) / 256, 64);
   if (a16) k_pull16<<<blocks, 256, 0, ctx->stream>>>((uint4*)dst, (const uint4*)h, n);
   else k_pull4<<<blocks, 256, 0, ctx->stream>>>((uint32_t*)dst, (const uint32_t*)h, n);
+  LAUNCHED(ctx);
   CK(cudaGetLastError());
   return ASDM_OK;
 }
@@ -851,6 +853,10 @@ struct asdm_job {
   std::vector<PairDesc> h_pairs;
   DevBuf d_pairs, d_masks, d_cnt, d_cand, d_owner, d_acc, d_flags, d_match, d_dist, d_nm;
   DevBuf d_work, d_tmaps, d_list, d_seg_count, d_rb, d_cmin, d_setdesc;
+  // d_masks / d_pairs / d_work / d_tmaps / d_setdesc are views into d_in (every input of the job, brought over by ONE
+  // pull); d_flags / d_seg_count / d_cnt are views into d_zero (everything a run has to clear, ONE fill)
+  DevBuf d_in, d_zero;
+  size_t zero_bytes = 0;
   int cap = 8;
   int use_tc = 0;
   int n_work = 0;
@@ -875,7 +881,7 @@ static void job_free(asdm_job* j) {
   }
   DevBuf* bufs[] = {&j->d_pairs, &j->d_masks, &j->d_cnt, &j->d_cand, &j->d_owner, &j->d_acc, &j->d_flags,
                     &j->d_match, &j->d_dist, &j->d_nm, &j->d_work, &j->d_tmaps, &j->d_list, &j->d_seg_count,
-                    &j->d_rb, &j->d_cmin, &j->d_setdesc};
+                    &j->d_rb, &j->d_cmin, &j->d_setdesc, &j->d_in, &j->d_zero};
   for (DevBuf* b : bufs) release(ctx, *b);  // stream-ordered: a run still in flight completes first
   if (j->h_flags_owned) {
     cudaStreamSynchronize(ctx->stream);
@@ -892,22 +898,28 @@ static int job_alloc_scratch(asdm_job* j) {
   asdm_ctx* ctx = j->ctx;
   const size_t P = (size_t)j->n_pairs;
   int rc;
-  if ((rc = ensure(ctx, j->d_cnt, P * j->n_stride * sizeof(int32_t)))) return rc;
+  if (j->use_tc) j->n_seg = ctx->sm_count * ASDM_TC_MAX_EPI_WARPS;
+  {
+    const size_t o_seg = 256, o_cnt = o_seg + align_up((size_t)(j->use_tc ? j->n_seg : 0) * sizeof(int32_t), 256);
+    j->zero_bytes = o_cnt + align_up(P * j->n_stride * sizeof(int32_t), 256);
+    if ((rc = ensure(ctx, j->d_zero, j->zero_bytes))) return rc;
+    char* z = (char*)j->d_zero.p;
+    j->d_flags = DevBuf{z, 0};
+    j->d_seg_count = DevBuf{z + o_seg, 0};
+    j->d_cnt = DevBuf{z + o_cnt, 0};
+  }
   if ((rc = ensure(ctx, j->d_cand, P * j->n_stride * (size_t)j->cap * sizeof(Cand)))) return rc;
   if ((rc = ensure(ctx, j->d_owner, P * 2 * j->m_stride * sizeof(int32_t)))) return rc;
   if ((rc = ensure(ctx, j->d_acc, P * j->n_stride * sizeof(int32_t)))) return rc;
-  if ((rc = ensure(ctx, j->d_flags, 64))) return rc;
   if ((rc = ensure(ctx, j->d_match, P * j->out_stride * sizeof(int32_t)))) return rc;
   if ((rc = ensure(ctx, j->d_dist, P * j->out_stride * sizeof(float)))) return rc;
   if ((rc = ensure(ctx, j->d_nm, P * sizeof(int32_t)))) return rc;
   if (j->use_tc) {
-    j->n_seg = ctx->sm_count * ASDM_TC_MAX_EPI_WARPS;
     {  // only the CTAs that get work fill their segments
       const int active = std::max(1, std::min(j->n_work, ctx->sm_count)) * ASDM_TC_MAX_EPI_WARPS;
       j->seg_cap = std::max(1024, (j->list_cap + active - 1) / active);
     }
     if ((rc = ensure(ctx, j->d_list, (size_t)j->seg_cap * j->n_seg * sizeof(TcHit)))) return rc;
-    if ((rc = ensure(ctx, j->d_seg_count, (size_t)j->n_seg * sizeof(int32_t)))) return rc;
   }
   return ASDM_OK;
 }
@@ -951,13 +963,52 @@ static int job_prepare(asdm_ctx* ctx, const asdm_job_desc* d, int kind_internal,
     mtot += align_up((size_t)std::max(d->sets[k]->n, 1), 16);
   }
   int rc;
-  if ((rc = ensure(ctx, j->d_masks, mtot))) return bail(rc);
-  {
-    void* h = nullptr;
-    if ((rc = stage_alloc(ctx, mtot, &h))) return bail(rc);
-    for (int k = 0; k < d->n_kf; k++) memcpy((char*)h + mask_off[k], d->masks[k], (size_t)d->sets[k]->n);
-    if ((rc = pull_to_device(ctx, j->d_masks.p, h, mtot))) return bail(rc);
+  // Every input of the job lives in ONE device block (d_in) that is filled by ONE pull from the staging arena:
+  // masks | pair table | tensor maps | per-keyframe bound descriptors | chunk -> keyframe map | work list.
+  // Sizes are known after a pre-pass over the pairs (the work list is the only data-dependent one).
+  const long target_units = (long)ctx->sm_count * 4;
+  long tc_tiles = 0;
+  auto m_range_of = [&](int p, int& m_lo, int& m_hi) {  // 128-row tiles of set A that hold this unit's query rows
+    const int nA = d->sets[d->ia[p]]->n;
+    const int r0 = d->row_begin ? d->row_begin[p] : 0, r1 = d->row_end ? d->row_end[p] : nA;
+    m_lo = r0 / 128;
+    m_hi = r1 > r0 ? (r1 + 127) / 128 : m_lo;
+  };
+  for (int p = 0; p < d->n_pairs; p++) {
+    const int a = d->ia[p], b = d->ib[p];
+    if (a < 0 || a >= d->n_kf || b < 0 || b >= d->n_kf) return bail(fail(ctx, ASDM_ERR_INVALID, "pair index out of range"));
+    if (d->row_begin && (d->row_begin[p] < 0 || d->row_end[p] < d->row_begin[p] || d->row_end[p] > d->sets[a]->n))
+      return bail(fail(ctx, ASDM_ERR_INVALID, "row range out of bounds"));
+    int m_lo, m_hi;
+    m_range_of(p, m_lo, m_hi);
+    tc_tiles += (long)((d->sets[b]->n + 255) / 256) * (m_hi - m_lo);
   }
+  const int tc_run = (int)std::max<long>(1, std::min<long>(32, tc_tiles / std::max<long>(1, target_units)));
+  size_t work_bound = 0, n_chunks = 0;
+  for (int p = 0; p < d->n_pairs; p++) {
+    int m_lo, m_hi;
+    m_range_of(p, m_lo, m_hi);
+    work_bound += (size_t)((d->sets[d->ib[p]]->n + 255) / 256) * (size_t)((m_hi - m_lo + tc_run - 1) / tc_run);
+  }
+  for (int k = 0; k < d->n_kf; k++) n_chunks += (size_t)d->sets[k]->n_pad / 128;
+  size_t in_off = 0;
+  auto carve = [&](size_t bytes) { const size_t o = in_off; in_off += align_up(std::max(bytes, (size_t)1), 256); return o; };
+  const size_t o_masks = carve(mtot), o_pairs = carve((size_t)d->n_pairs * sizeof(PairDesc)),
+               o_tmaps = carve((size_t)d->n_kf * 128), o_sd = carve((size_t)d->n_kf * sizeof(TcSetDesc)),
+               o_chunk = carve(n_chunks * sizeof(int32_t)), o_work = carve(work_bound * sizeof(TcWork));
+  if ((rc = ensure(ctx, j->d_in, in_off))) return bail(rc);
+  void* h_in_v = nullptr;
+  if ((rc = stage_alloc(ctx, in_off, &h_in_v))) return bail(rc);
+  char* h_in = (char*)h_in_v;
+  char* d_in = (char*)j->d_in.p;
+  j->d_masks = DevBuf{d_in + o_masks, 0};
+  j->d_pairs = DevBuf{d_in + o_pairs, 0};
+  j->d_tmaps = DevBuf{d_in + o_tmaps, 0};
+  j->d_setdesc = DevBuf{d_in + o_sd, 0};
+  j->d_work = DevBuf{d_in + o_work, 0};
+  for (int k = 0; k < d->n_kf; k++) memcpy(h_in + o_masks + mask_off[k], d->masks[k], (size_t)d->sets[k]->n);
+  size_t in_used = o_tmaps;  // masks + pairs always travel; the tensor-core tables only when that route is taken
+  size_t row_bound_chunks = 0;
 
   BowParams& P = j->P;
   memset(&P, 0, sizeof P);
@@ -1035,73 +1086,55 @@ static int job_prepare(asdm_ctx* ctx, const asdm_job_desc* d, int kind_internal,
     j->tc_pending = pending && all_tc;
     if (all_tc) {
       // work units: one resident 256-row B tile x a run of 128-row A tiles; split runs until the grid is full
-      std::vector<TcWork> work;
-      long tiles = 0;
-      auto m_range = [&](int p, int& m_lo, int& m_hi) {  // 128-row tiles of set A that hold this unit's query rows
-        m_lo = j->h_pairs[p].rowA0 / 128;
-        m_hi = j->h_pairs[p].rowA1 > j->h_pairs[p].rowA0 ? (j->h_pairs[p].rowA1 + 127) / 128 : m_lo;
-      };
-      for (int p = 0; p < d->n_pairs; p++) {
-        int m_lo, m_hi;
-        m_range(p, m_lo, m_hi);
-        tiles += (long)((j->h_pairs[p].nB + 255) / 256) * (m_hi - m_lo);
-      }
-      const long target_units = (long)ctx->sm_count * 4;
-      int run = (int)std::max<long>(1, std::min<long>(32, tiles / std::max<long>(1, target_units)));
+      TcWork* work = (TcWork*)(h_in + o_work);
+      size_t n_work = 0;
       for (int p = 0; p < d->n_pairs; p++) {
         const int nt_n = (j->h_pairs[p].nB + 255) / 256;
         int m_lo, m_hi;
-        m_range(p, m_lo, m_hi);
+        m_range_of(p, m_lo, m_hi);
         for (int tn = 0; tn < nt_n; tn++)
-          for (int m0 = m_lo; m0 < m_hi; m0 += run) work.push_back(TcWork{p, tn, m0, std::min(run, m_hi - m0)});
+          for (int m0 = m_lo; m0 < m_hi; m0 += tc_run) work[n_work++] = TcWork{p, tn, m0, std::min(tc_run, m_hi - m0)};
       }
       bool maps_ok = true;
       for (int k = 0; k < d->n_kf && maps_ok; k++) maps_ok = asdm_tc_build_tmap(ctx, d->sets[k]) == ASDM_OK;
-      if (maps_ok && !work.empty()) {
+      if (maps_ok && n_work > 0) {
         j->use_tc = 1;
-        j->n_work = (int)work.size();
-        if ((rc = ensure(ctx, j->d_work, work.size() * sizeof(TcWork)))) return bail(rc);
-        if ((rc = ensure(ctx, j->d_tmaps, (size_t)d->n_kf * 128))) return bail(rc);
-        std::vector<uint8_t> maps((size_t)d->n_kf * 128);
-        for (int k = 0; k < d->n_kf; k++) memcpy(maps.data() + (size_t)k * 128, d->sets[k]->tmap_bf.data(), 128);
-        if ((rc = stage_upload(ctx, j->d_work.p, work.data(), work.size() * sizeof(TcWork))) ||
-            (rc = stage_upload(ctx, j->d_tmaps.p, maps.data(), maps.size())))
-          return bail(rc);
+        j->n_work = (int)n_work;
+        for (int k = 0; k < d->n_kf; k++) memcpy(h_in + o_tmaps + (size_t)k * 128, d->sets[k]->tmap_bf.data(), 128);
         // per-keyframe filter bounds (k_tc_row_bounds): one launch over all 128-row chunks of all keyframes
         {
-          std::vector<TcSetDesc> sd((size_t)d->n_kf);
-          std::vector<int32_t> chunk_set;
+          TcSetDesc* sd = (TcSetDesc*)(h_in + o_sd);
+          int32_t* chunk_set = (int32_t*)(h_in + o_chunk);
+          size_t nch = 0;
           for (int k = 0; k < d->n_kf; k++) {
             const asdm_set* S = d->sets[k];
-            sd[k] = TcSetDesc{S->norm2, (const uint8_t*)j->d_masks.p + mask_off[k], S->fv_pos, S->n, (int32_t)chunk_set.size()};
-            chunk_set.insert(chunk_set.end(), (size_t)S->n_pad / 128, k);
+            sd[k] = TcSetDesc{S->norm2, (const uint8_t*)j->d_masks.p + mask_off[k], S->fv_pos, S->n, (int32_t)nch};
+            for (size_t c = 0; c < (size_t)S->n_pad / 128; c++) chunk_set[nch++] = k;
           }
-          const size_t nch = chunk_set.size();
-          if ((rc = ensure(ctx, j->d_rb, nch * 128 * sizeof(float))) || (rc = ensure(ctx, j->d_cmin, nch * sizeof(float))) ||
-              (rc = ensure(ctx, j->d_setdesc, sd.size() * sizeof(TcSetDesc) + nch * sizeof(int32_t))))
+          if ((rc = ensure(ctx, j->d_rb, nch * 128 * sizeof(float))) || (rc = ensure(ctx, j->d_cmin, nch * sizeof(float))))
             return bail(rc);
-          int32_t* d_chunk_set = (int32_t*)((char*)j->d_setdesc.p + sd.size() * sizeof(TcSetDesc));
-          if ((rc = stage_upload(ctx, j->d_setdesc.p, sd.data(), sd.size() * sizeof(TcSetDesc))) ||
-              (rc = stage_upload(ctx, d_chunk_set, chunk_set.data(), nch * sizeof(int32_t))))
-            return bail(rc);
-          if (asdm_tc_row_bounds_launch(ctx, (const TcSetDesc*)j->d_setdesc.p, d_chunk_set, (int)nch, P.mask_sense,
-                                        (float*)j->d_rb.p, (float*)j->d_cmin.p) != cudaSuccess)
-            return bail(fail(ctx, ASDM_ERR_CUDA, "row-bound launch"));
-          ctx->stat_total_launches++;
+          row_bound_chunks = nch;  // launched below, once the inputs are on the device
           for (int p = 0; p < d->n_pairs; p++) {
             PairDesc& pd = j->h_pairs[p];
             pd.rbA = (const float*)j->d_rb.p + (size_t)sd[pd.setA].chunk0 * 128;
             pd.cminB = (const float*)j->d_cmin.p + sd[pd.setB].chunk0;
           }
         }
+        in_used = o_work + align_up(n_work * sizeof(TcWork), 256);
         long q = 0;
         for (int p = 0; p < d->n_pairs; p++) q += j->h_pairs[p].nA;
         j->list_cap = (int)std::min<long>((long)1 << 30, std::max<long>(4096, q * ctx->opt_list_cap_per_query));
       }
     }
   }
-  if ((rc = ensure(ctx, j->d_pairs, std::max<size_t>(1, j->h_pairs.size()) * sizeof(PairDesc)))) return bail(rc);
-  if ((rc = stage_upload(ctx, j->d_pairs.p, j->h_pairs.data(), j->h_pairs.size() * sizeof(PairDesc)))) return bail(rc);
+  if (!j->h_pairs.empty()) memcpy(h_in + o_pairs, j->h_pairs.data(), j->h_pairs.size() * sizeof(PairDesc));
+  if ((rc = pull_to_device(ctx, d_in, h_in, in_used))) return bail(rc);
+  if (row_bound_chunks) {
+    if (asdm_tc_row_bounds_launch(ctx, (const TcSetDesc*)j->d_setdesc.p, (const int32_t*)(d_in + o_chunk), (int)row_bound_chunks,
+                                  P.mask_sense, (float*)j->d_rb.p, (float*)j->d_cmin.p) != cudaSuccess)
+      return bail(fail(ctx, ASDM_ERR_CUDA, "row-bound launch"));
+    ctx->stat_total_launches++;
+  }
   if ((rc = job_alloc_scratch(j))) return bail(rc);
   j->h_flags = slot_get(ctx);
   if (!j->h_flags) {
@@ -1123,11 +1156,9 @@ static int job_run(asdm_job* j) {
   if (j->n_pairs == 0) return ASDM_OK;
   const PairDesc* pairs = (const PairDesc*)j->d_pairs.p;
   int32_t* flags = (int32_t*)j->d_flags.p;
-  {  // (buffers come from ensure(): at least 4 KB, so rounding the fill up to 16 bytes stays inside)
-    int rc;
-    if ((rc = zero_device(ctx, j->d_cnt.p, (size_t)j->n_pairs * j->n_stride * sizeof(int32_t))) ||
-        (rc = zero_device(ctx, flags, 64)))
-      return rc;
+  {
+    const int rc = zero_device(ctx, j->d_zero.p, j->zero_bytes);  // flags | hit-list segment counts | candidate counts
+    if (rc) return rc;
   }
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   if (ctx->opt_time_kernels) {
@@ -1136,10 +1167,6 @@ static int job_run(asdm_job* j) {
     CK(cudaEventRecord(ev0, ctx->stream));
   }
   if (j->use_tc) {
-    {
-      const int rc = zero_device(ctx, j->d_seg_count.p, (size_t)j->n_seg * sizeof(int32_t));
-      if (rc) return rc;
-    }
     CK(asdm_tc_shortlist_launch(ctx, pairs, j->d_tmaps.p, (const TcWork*)j->d_work.p, j->n_work, j->P.t_keep,
                                 (TcHit*)j->d_list.p, j->seg_cap, (int32_t*)j->d_seg_count.p, flags + 2));
     LAUNCHED(ctx);
