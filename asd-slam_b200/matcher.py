@@ -279,9 +279,9 @@ class StreamedPairSweep:
         if bounds is None:
             # waves shrink towards the end: the last one (after the last upload) is all that is not hidden.
             # pairs with max < b are a (b/n)^2 share of a uniform sweep
-            # (measured on C5, B200: 4 waves at 1/2, 3/4, 9/10 of the keyframes; every wave costs ~0.13 ms of fixed
-            # kernel tails, so more waves stop paying once the searches, not the uploads, are the long pole)
-            bounds = sorted({max(2, int(round(self.n_kf * f))) for f in (0.5, 0.75, 0.9, 1.0)})
+            # (measured on C5, B200 with tools/stream_timeline.py: 4 to 7 waves all land within 5 %; every wave costs
+            # ~0.1 ms of fixed kernel tails, so more waves stop paying once the searches, not the uploads, are the long pole)
+            bounds = sorted({max(2, int(round(self.n_kf * f))) for f in (0.375, 0.5625, 0.72, 0.845, 0.94, 1.0)})
         self.bounds = [int(b) for b in bounds]
         assert self.bounds[-1] == self.n_kf
         later = np.maximum(self.ia, self.ib)
