@@ -330,6 +330,8 @@ extern "C" int asdm_set_option(asdm_ctx* ctx, const char* key, int value) {
   std::lock_guard<std::recursive_mutex> lk(ctx->mu);
   if (!strcmp(key, "force_exact")) ctx->opt_force_exact = value;
   else if (!strcmp(key, "init_serial")) ctx->opt_init_serial = value;
+  else if (!strcmp(key, "voc_direct")) ctx->opt_voc_direct = value;
+  else if (!strcmp(key, "voc_exact")) ctx->opt_voc_exact = value;
   else if (!strcmp(key, "cand_cap")) ctx->opt_cand_cap = std::max(1, value);
   else if (!strcmp(key, "list_cap_per_query")) ctx->opt_list_cap_per_query = std::max(1, value);
   else if (!strcmp(key, "time_kernels")) ctx->opt_time_kernels = value;
@@ -347,6 +349,7 @@ extern "C" int asdm_get_stat(asdm_ctx* ctx, const char* key, int64_t* value) {
   else if (!strcmp(key, "cand_cap")) *value = ctx->stat_cand_cap;
   else if (!strcmp(key, "retries")) *value = ctx->stat_retries;
   else if (!strcmp(key, "init_sweeps")) *value = ctx->stat_init_sweeps;
+  else if (!strcmp(key, "voc_exact_levels")) *value = ctx->stat_voc_exact;
   else if (!strcmp(key, "tc_used")) *value = ctx->stat_tc_used;
   else if (!strcmp(key, "tc_pairs")) *value = ctx->stat_tc_pairs;
   else if (!strcmp(key, "sm_count")) *value = ctx->sm_count;
@@ -1885,22 +1888,18 @@ extern "C" int asdm_vocab_create(asdm_ctx* ctx, const asdm_vocab_desc* d, asdm_v
   v->ctx = ctx;
   v->k = d->k; v->L = d->L; v->weighting = d->weighting; v->scoring = d->scoring; v->n_nodes = nn;
   v->G = std::min(std::max(kmax, 1), 32);
+  v->kmax = kmax;
   v->h_weight.assign(d->weight, d->weight + nn);
   v->h_word.assign(d->word_id, d->word_id + nn);
-  const size_t o_off = 0, o_idx = align_up((size_t)(nn + 1) * 4, 256), o_w = o_idx + align_up((size_t)(nn - 1) * 4, 256),
-               o_blk = o_w + align_up((size_t)nn * 8, 256), total = o_blk + (size_t)(nn - 1) * ASDM_DESC_DIM * 4;
-  // dimension-major child blocks, built on the host once (vocabulary load time) and uploaded in one copy
+  // one descriptor row and one record per child slot, built on the host once (vocabulary load time), one upload
+  const size_t ns = (size_t)nn - 1, o_meta = 0, o_rows = align_up(ns * sizeof(int4), 512), total = o_rows + ns * ASDM_DESC_DIM * 4;
   std::vector<char> hb(total, 0);
-  memcpy(hb.data() + o_off, d->child_off, (size_t)(nn + 1) * 4);
-  memcpy(hb.data() + o_idx, d->child_idx, (size_t)(nn - 1) * 4);
-  memcpy(hb.data() + o_w, d->weight, (size_t)nn * 8);
-  float* blk = (float*)(hb.data() + o_blk);
-  for (int p = 0; p < nn; p++) {
-    const int off = d->child_off[p], kp = d->child_off[p + 1] - off;
-    for (int c = 0; c < kp; c++) {
-      const float* src = d->desc + (size_t)d->child_idx[off + c] * ASDM_DESC_DIM;
-      for (int i = 0; i < ASDM_DESC_DIM; i++) blk[(size_t)off * ASDM_DESC_DIM + (size_t)i * kp + c] = src[i];
-    }
+  int4* meta = (int4*)(hb.data() + o_meta);
+  float* rows = (float*)(hb.data() + o_rows);
+  for (size_t sl = 0; sl < ns; sl++) {
+    const int c = d->child_idx[sl];
+    meta[sl] = make_int4(c, d->child_off[c], d->child_off[c + 1] - d->child_off[c], d->weight[c] > 0.0 ? 1 : 0);
+    memcpy(rows + sl * ASDM_DESC_DIM, d->desc + (size_t)c * ASDM_DESC_DIM, ASDM_DESC_DIM * 4);
   }
   cudaError_t e = dev_alloc(ctx, &v->mem, total);
   if (e == cudaSuccess) e = cudaMemcpyAsync(v->mem, hb.data(), total, cudaMemcpyHostToDevice, ctx->stream);
@@ -1911,10 +1910,9 @@ extern "C" int asdm_vocab_create(asdm_ctx* ctx, const asdm_vocab_desc* d, asdm_v
     return fail(ctx, e == cudaErrorMemoryAllocation ? ASDM_ERR_OOM : ASDM_ERR_CUDA, "vocabulary upload", e);
   }
   synced(ctx);
-  v->child_off = (int32_t*)((char*)v->mem + o_off);
-  v->child_idx = (int32_t*)((char*)v->mem + o_idx);
-  v->weight = (double*)((char*)v->mem + o_w);
-  v->blk = (float*)((char*)v->mem + o_blk);
+  v->meta = (int4*)((char*)v->mem + o_meta);
+  v->rows = (float*)((char*)v->mem + o_rows);
+  v->root_k = d->child_off[1];
   *out = v;
   return ASDM_OK;
 }
@@ -1948,14 +1946,29 @@ extern "C" int asdm_vocab_transform(asdm_ctx* ctx, asdm_vocab* voc, asdm_set* s,
   s->has_fv = true;
   if (n == 0) return ASDM_OK;
   int rc;
-  const size_t o_key = 0, o_leaf = align_up((size_t)n * 8, 256), sc_bytes = o_leaf + (size_t)n * 4;
+  const size_t o_key = 0, o_leaf = align_up((size_t)n * 8, 256), o_cnt = o_leaf + align_up((size_t)n * 4, 256), sc_bytes = o_cnt + 256;
   if ((rc = ensure(ctx, ctx->scratch[SC_VOC], sc_bytes))) return rc;
   unsigned long long* d_key = (unsigned long long*)((char*)ctx->scratch[SC_VOC].p + o_key);
   int32_t* d_leaf = (int32_t*)((char*)ctx->scratch[SC_VOC].p + o_leaf);
-  VocDev vd{voc->child_off, voc->child_idx, voc->blk, voc->weight, voc->n_nodes, voc->G};
-  const int fpw = 32 / voc->G, per_cta = VOC_WARPS * fpw;
-  k_voc_descend<<<(n + per_cta - 1) / per_cta, VOC_WARPS * 32, (size_t)per_cta * ASDM_DESC_DIM * 4, ctx->stream>>>(
-      vd, s->desc, n, voc->L - levelsup, d_leaf, s->node_id, s->fv_pos, d_key);
+  int32_t* d_cnt = (int32_t*)((char*)ctx->scratch[SC_VOC].p + o_cnt);
+  VocDev vd{voc->rows, voc->meta, voc->root_k, voc->G};
+  const int fpw = 32 / voc->G;
+  bool staged = false;
+  if (voc->kmax <= 32 && !ctx->opt_voc_direct) {  // child blocks staged through shared memory (cp.async)
+    const int per_cta = VOC_WARPS * fpw;
+    const size_t smem = (size_t)VOC_WARPS * voc_warp_words(voc->G) * sizeof(float);
+    if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_voc_descend_staged, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // several CTAs per SM must fit (the descent is latency bound): ask for the largest shared-memory carve-out
+    CK(cudaFuncSetAttribute(k_voc_descend_staged, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CK(cudaMemsetAsync(d_cnt, 0, 4, ctx->stream));
+    k_voc_descend_staged<<<(n + per_cta - 1) / per_cta, VOC_WARPS * 32, smem, ctx->stream>>>(
+        vd, s->desc, n, voc->L - levelsup, d_leaf, s->node_id, s->fv_pos, d_key, ctx->opt_voc_exact, d_cnt);
+    staged = true;
+  } else {
+    const int per_cta = VOC_WARPS_DIRECT * fpw;
+    k_voc_descend<<<(n + per_cta - 1) / per_cta, VOC_WARPS_DIRECT * 32, (size_t)per_cta * ASDM_DESC_DIM * 4, ctx->stream>>>(
+        vd, s->desc, n, voc->L - levelsup, d_leaf, s->node_id, s->fv_pos, d_key);
+  }
   LAUNCHED(ctx);
   k_fv_rank<<<dim3((n + 127) / 128, (n + FV_JT - 1) / FV_JT), 128, 0, ctx->stream>>>(d_key, n, s->fv_pos);
   LAUNCHED(ctx);
@@ -1963,12 +1976,16 @@ extern "C" int asdm_vocab_transform(asdm_ctx* ctx, asdm_vocab* voc, asdm_set* s,
   const bool want_host = word_id || node_id || in_fv || bow_n || bow_id || bow_val;
   if (!want_host) return ASDM_OK;  // stays asynchronous: the searches that follow are ordered on the same stream
   void* h = nullptr;
-  if ((rc = stage_alloc(ctx, (size_t)n * 8, &h))) return rc;
+  if ((rc = stage_alloc(ctx, (size_t)n * 8 + 4, &h))) return rc;
   int32_t* h_leaf = (int32_t*)h;
   uint32_t* h_nid = (uint32_t*)h + n;
+  int32_t* h_cnt = (int32_t*)h + 2 * (size_t)n;
+  *h_cnt = 0;
   CK(cudaMemcpyAsync(h_leaf, d_leaf, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaMemcpyAsync(h_nid, s->node_id, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  if (staged) CK(cudaMemcpyAsync(h_cnt, d_cnt, 4, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
+  ctx->stat_voc_exact = *h_cnt;
   // marshalling for the caller's std::map containers: per-feature ids, then the BowVector in map (ascending word) order
   std::vector<std::pair<uint32_t, double>> words;  // (word, weight) of the features that count, in feature order
   words.reserve(n);

@@ -50,6 +50,9 @@ struct asdm_ctx {
   int opt_cand_cap = 8;
   int opt_list_cap_per_query = 4;  // tensor-core short list slots per query row (grows on overflow)
   int opt_tc_epi_warps = 8;        // epilogue warps of the tensor-core kernel: 4 or 8
+  int opt_voc_direct = 0;          // vocabulary descent: 1 = children read straight from global memory (no staging)
+  int opt_voc_exact = 0;           // vocabulary descent: 1 = always run the exact double chain (no fp32 fast pass)
+  int64_t stat_voc_exact = 0;      // (feature, level) decisions of the last transform that needed the exact chain
   int opt_init_serial = 0;         // SearchForInitialization: 1 = the serial replay kernel instead of the Jacobi sweeps
   int64_t stat_init_sweeps = 0;    // 1 when the last SearchForInitialization was resolved by the sweeps
   int opt_tc_variant = 0;          // pipeline-shape experiments of the tensor-core kernel (tc_shortlist.cu)
@@ -112,11 +115,11 @@ struct asdm_vocab {
   asdm_ctx* ctx = nullptr;
   int k = 0, L = 0, weighting = 0, scoring = 0, n_nodes = 0;
   int G = 1;               // lanes per feature in k_voc_descend
-  void* mem = nullptr;     // one arena: child_off | child_idx | weight | blk
-  int32_t* child_off = nullptr;
-  int32_t* child_idx = nullptr;
-  double* weight = nullptr;
-  float* blk = nullptr;
+  int kmax = 1;            // widest fan-out of the tree
+  void* mem = nullptr;     // one arena: slot records | slot rows (kernels_vocab.cuh)
+  int4* meta = nullptr;
+  float* rows = nullptr;
+  int root_k = 0;
   std::vector<double> h_weight;
   std::vector<int32_t> h_word;
 };

@@ -107,19 +107,59 @@ def test_fsift_distance_vs_ref(oracle, ref):
 
 # ------------------------------------------------------------------------------------------------ GPU: product
 @pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["fast", "exact", "direct"])
 @pytest.mark.parametrize("i", range(len(ALL)), ids=IDS)
-def test_cuda_vs_golden(pkg, ctx, oracle, i):
+def test_cuda_vs_golden(pkg, ctx, oracle, i, mode):
+    """fast: child blocks staged through shared memory with cp.async (fan-out <= 32), fp32 pass + exact chain where the
+    margin is too small to call; exact: the same kernel, exact chain at every level; direct: the kernel that reads the
+    children straight from global memory (also the one that handles fan-outs above 32, case k40L2)."""
     name, tree, q, levels = case_inputs(i)
     voc = pkg.ORBVocabulary(ctx, tree)
     s = pkg.DescriptorSet(ctx, q)
     for lu in levels:
+        ctx.set_option("voc_direct", mode == "direct")
+        ctx.set_option("voc_exact", mode == "exact")
         got = voc.transform(s, lu)
+        ctx.set_option("voc_direct", 0)
+        ctx.set_option("voc_exact", 0)
         assert ctx.stat("gpu_launches") == 2
         check_against_gold(name, tree, lu, got)
         o = oracle.voc_transform(tree, q, lu)
         for k in ("word_id", "node_id", "in_fv", "bow_id"):
             assert np.array_equal(got[k], o[k]), k
         assert np.array_equal(bits64(got["bow_val"]), bits64(o["bow_val"]))
+    s.release()
+    voc.release()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("rel", [0.0, 1e-9, 1e-7, 3e-6, 1e-4])
+def test_cuda_near_ties_take_the_exact_chain(pkg, ctx, oracle, rel):
+    """Siblings that are copies of one centre up to a relative perturbation `rel` (0 = exact duplicates, first child
+    wins): the fp32 pass cannot separate them below its margin (2^-16), so the decision must come from the reference's
+    fp32-product / double-sum chain -- and the answer must still be the oracle's, word for word."""
+    tree = dict(pkg.synth.vocab_tree(k=8, L=3, seed_extra=77))
+    rng = np.random.default_rng(771)
+    desc = tree["desc"].copy()
+    off, idx = tree["child_off"], tree["child_idx"]
+    for p in range(len(off) - 1):
+        ch = idx[off[p]:off[p + 1]]
+        if len(ch) > 1:
+            jit = 1.0 + rel * rng.standard_normal((len(ch) - 1, 128))
+            desc[ch[1:]] = (desc[ch[0]][None, :] * jit).astype(np.float32)
+    tree["desc"] = desc
+    q = pkg.synth.vocab_queries(tree, 600, seed_extra=78, sigma=0.05)
+    voc = pkg.ORBVocabulary(ctx, tree)
+    s = pkg.DescriptorSet(ctx, q)
+    got, o = voc.transform(s, 2), oracle.voc_transform(tree, q, 2)
+    n_exact = ctx.stat("voc_exact_levels")
+    for k in ("word_id", "node_id", "in_fv", "bow_id"):
+        assert np.array_equal(got[k], o[k]), k
+    assert np.array_equal(bits64(got["bow_val"]), bits64(o["bow_val"]))
+    if rel <= 1e-7:
+        assert n_exact >= 600  # every feature met at least one level it could not call in fp32
+    if rel == 0.0:
+        assert len(np.unique(got["word_id"])) == 1  # strict <: the first of the identical siblings wins at every level
     s.release()
     voc.release()
 
@@ -172,6 +212,7 @@ def test_cuda_full_size_tree(pkg, ctx, oracle):
         assert np.array_equal(got[k], o[k]), k
     assert np.array_equal(bits64(got["bow_val"]), bits64(o["bow_val"]))
     assert len(np.unique(got["node_id"])) == 10 and len(got["bow_id"]) > 2000
+    assert ctx.stat("voc_exact_levels") < 200  # of 20 000 decisions: the fp32 pass settles the rest
     s.release()
     voc.release()
 

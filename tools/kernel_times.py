@@ -24,8 +24,11 @@ for _ in range(2):
 tree = syn.vocab_tree(k=10, L=5, seed_extra=30)
 voc = pkg.ORBVocabulary(ctx, tree)
 S = pkg.DescriptorSet(ctx, syn.vocab_queries(tree, 4000, seed_extra=31, sigma=0.08))
-for _ in range(2):
-    voc.transform(S, 4)
+for direct in (0, 1):  # both descent kernels (option "voc_direct")
+    ctx.set_option("voc_direct", direct)
+    for _ in range(2):
+        voc.transform(S, 4)
+ctx.set_option("voc_direct", 0)
 c = syn.config1()
 A = pkg.DescriptorSet(ctx, c["desc_a"], c["kps_a"], c["grid"], c["fv_a"])
 B = pkg.DescriptorSet(ctx, c["desc_b"], c["kps_b"], c["grid"], c["fv_b"])
