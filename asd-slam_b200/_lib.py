@@ -35,6 +35,7 @@ EXPORTS = [
     "asdm_search_by_projection", "asdm_search_by_projection_q", "asdm_search_for_initialization", "asdm_stereo_row_match",
     "asdm_job_prepare", "asdm_job_run", "asdm_job_fetch", "asdm_job_fetch_async", "asdm_job_settle", "asdm_job_out_stride",
     "asdm_job_device_outputs", "asdm_job_destroy",
+    "asdm_shared_alloc", "asdm_shared_open", "asdm_shared_close", "asdm_shared_free", "asdm_job_set_publish",
     "asdm_distinctive_descriptors",
     "asdm_vocab_create", "asdm_vocab_release", "asdm_vocab_transform",
 ]
@@ -128,6 +129,11 @@ def load():
     lib.asdm_job_settle.argtypes = [vp]
     lib.asdm_job_out_stride.argtypes = [vp]
     lib.asdm_job_device_outputs.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
+    lib.asdm_shared_alloc.argtypes = [vp, C.c_size_t, C.POINTER(vp), vp]
+    lib.asdm_shared_open.argtypes = [vp, vp, C.POINTER(vp)]
+    lib.asdm_shared_close.argtypes = [vp, vp]
+    lib.asdm_shared_free.argtypes = [vp, vp]
+    lib.asdm_job_set_publish.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.c_int, C.c_int]
     lib.asdm_job_destroy.argtypes = [vp]
     lib.asdm_distinctive_descriptors.argtypes = [vp, C.POINTER(vp), C.c_int, C.c_int, vp, vp, vp, vp, vp]
     lib.asdm_desc_block_bytes.argtypes = [C.c_int]

@@ -851,6 +851,7 @@ struct asdm_job {
   int n_stride = 0;    // max nA over pairs (query slots per pair)
   int m_stride = 0;    // max nB over pairs
   int out_stride = 0;  // entries per pair in match12 / dist12
+  PublishArgs pub{};   // gathered arrays of every rank the resolve kernel also stores into (asdm_job_set_publish)
   BowParams P{};
   std::vector<asdm_set*> sets;  // retained
   std::vector<PairDesc> h_pairs;
@@ -1194,13 +1195,13 @@ static int job_run(asdm_job* j) {
     k_resolve_tri<<<j->n_pairs, 512, 0, ctx->stream>>>(pairs, j->P, j->cap, j->n_stride, j->out_stride,
                                                        (const int32_t*)j->d_cnt.p, (const Cand*)j->d_cand.p,
                                                        (int32_t*)j->d_acc.p, (int32_t*)j->d_match.p,
-                                                       (float*)j->d_dist.p, (int32_t*)j->d_nm.p);
+                                                       (float*)j->d_dist.p, (int32_t*)j->d_nm.p, j->pub);
   else
     k_resolve_bow<<<j->n_pairs, 512, 0, ctx->stream>>>(pairs, j->P, j->cap, j->n_stride, j->m_stride, j->out_stride,
                                                        (const int32_t*)j->d_cnt.p, (Cand*)j->d_cand.p,
                                                        (int32_t*)j->d_owner.p, (int32_t*)j->d_acc.p,
                                                        (int32_t*)j->d_match.p, (float*)j->d_dist.p,
-                                                       (int32_t*)j->d_nm.p);
+                                                       (int32_t*)j->d_nm.p, j->pub);
   LAUNCHED(ctx);
   CK(cudaGetLastError());
   return ASDM_OK;
@@ -1324,6 +1325,82 @@ extern "C" int asdm_job_device_outputs(asdm_job* j, void** match12, void** dist1
   if (match12) *match12 = j->d_match.p;
   if (dist12) *dist12 = j->d_dist.p;
   if (nmatches) *nmatches = j->d_nm.p;
+  return ASDM_OK;
+}
+
+// --------------------------------------------------------------- results published to every rank
+extern "C" int asdm_shared_alloc(asdm_ctx* ctx, size_t bytes, void** dptr, uint8_t handle[ASDM_SHARED_HANDLE_BYTES]) {
+  if (!ctx || !dptr || !handle || bytes == 0) return ASDM_ERR_INVALID;
+  static_assert(sizeof(cudaIpcMemHandle_t) == ASDM_SHARED_HANDLE_BYTES, "handle size");
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  CK(cudaSetDevice(ctx->device));
+  void* p = nullptr;
+  cudaError_t e = cudaMalloc(&p, bytes);  // not from the context's block cache: IPC handles name whole allocations
+  if (e != cudaSuccess) return fail(ctx, ASDM_ERR_OOM, "shared allocation", e);
+  cudaIpcMemHandle_t h;
+  e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    return fail(ctx, ASDM_ERR_CUDA, "cudaIpcGetMemHandle", e);
+  }
+  memcpy(handle, &h, sizeof h);
+  *dptr = p;
+  return ASDM_OK;
+}
+
+extern "C" int asdm_shared_open(asdm_ctx* ctx, const uint8_t handle[ASDM_SHARED_HANDLE_BYTES], void** dptr) {
+  if (!ctx || !dptr || !handle) return ASDM_ERR_INVALID;
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  CK(cudaSetDevice(ctx->device));
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof h);
+  void* p = nullptr;
+  cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+  if (e != cudaSuccess) return fail(ctx, ASDM_ERR_CUDA, "cudaIpcOpenMemHandle (no peer access between these GPUs?)", e);
+  *dptr = p;
+  return ASDM_OK;
+}
+
+extern "C" int asdm_shared_close(asdm_ctx* ctx, void* dptr) {
+  if (!ctx || !dptr) return ASDM_ERR_INVALID;
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaStreamSynchronize(ctx->stream));
+  CK(cudaIpcCloseMemHandle(dptr));
+  return ASDM_OK;
+}
+
+extern "C" int asdm_shared_free(asdm_ctx* ctx, void* dptr) {
+  if (!ctx || !dptr) return ASDM_ERR_INVALID;
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaStreamSynchronize(ctx->stream));
+  CK(cudaFree(dptr));
+  return ASDM_OK;
+}
+
+extern "C" int asdm_job_set_publish(asdm_job* j, int n_ranks, void* const* match, void* const* dist, void* const* nmatches,
+                                    int row0, int stride) {
+  if (!j) return ASDM_ERR_INVALID;
+  asdm_ctx* ctx = j->ctx;
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  if (n_ranks == 0) {
+    j->pub.n = 0;
+    return ASDM_OK;
+  }
+  if (n_ranks < 0 || n_ranks > ASDM_MAX_PEERS || !match || !dist || !nmatches || row0 < 0)
+    return fail(ctx, ASDM_ERR_INVALID, "publish: 1..16 destinations");
+  if (stride < j->out_stride) return fail(ctx, ASDM_ERR_INVALID, "publish: gathered stride below the job's row length");
+  for (int r = 0; r < n_ranks; r++)
+    if (!match[r] || !dist[r] || !nmatches[r]) return fail(ctx, ASDM_ERR_INVALID, "publish: null destination");
+  j->pub.n = n_ranks;
+  j->pub.row0 = row0;
+  j->pub.stride = stride;
+  for (int r = 0; r < n_ranks; r++) {
+    j->pub.match[r] = (int32_t*)match[r];
+    j->pub.dist[r] = (float*)dist[r];
+    j->pub.nm[r] = (int32_t*)nmatches[r];
+  }
   return ASDM_OK;
 }
 

@@ -125,6 +125,19 @@ struct asdm_vocab {
 };
 
 // --------------------------------------------------------------------------------- device-visible structs
+// Where a sharded job publishes its results: the rank-major gathered record arrays of every rank of the
+// group -- this GPU's own and its NVLink peers' (cudaIpc mappings) -- so that the all-gather of the match lists is the
+// epilogue of the resolve kernel: each CTA stores its pair's finished row into all of them.
+#define ASDM_MAX_PEERS 16
+struct PublishArgs {
+  int n = 0;                        // 0 = the job keeps its results local
+  int row0 = 0;                     // first row of this rank's records (rank * per_rank)
+  int stride = 0;                   // entries per row of the gathered arrays
+  int32_t* match[ASDM_MAX_PEERS];   // [world * per_rank][stride]
+  float* dist[ASDM_MAX_PEERS];
+  int32_t* nm[ASDM_MAX_PEERS];      // [world * per_rank]
+};
+
 // One keyframe pair of a BoW-gated dense search (a8 / a9 / a11).
 struct PairDesc {
   const float* descA;

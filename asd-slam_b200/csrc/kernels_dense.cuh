@@ -140,12 +140,53 @@ __device__ __forceinline__ bool cand_before(const Cand& x, int px, const Cand& y
   return x.d < y.d || (x.d == y.d && px < py);
 }
 
+// Epilogue of the resolve kernels when the job publishes (PublishArgs): the CTA's finished row -- out_n entries, the
+// rest of the gathered stride padded with -1 -- goes to the same slot of every rank's gathered arrays. Peer stores
+// travel over NVLink while the other CTAs are still resolving their pairs. 16-byte stores when the rows allow it.
+__device__ __forceinline__ void publish_row(const PublishArgs& pub, int pair, const int32_t* __restrict__ matchp,
+                                            const float* __restrict__ distp, int out_n, int nm) {
+  const int t = threadIdx.x, nt = blockDim.x;
+  const size_t row = (size_t)(pub.row0 + pair);
+  const bool vec = (pub.stride & 3) == 0 && ((reinterpret_cast<uintptr_t>(matchp) | reinterpret_cast<uintptr_t>(distp)) & 15) == 0;
+  if (vec) {
+    const int n4 = pub.stride >> 2;
+    for (int k = t; k < n4; k += nt) {
+      int4 m = make_int4(-1, -1, -1, -1);
+      float4 d = make_float4(-1.f, -1.f, -1.f, -1.f);
+      const int e = k * 4;
+      if (e + 3 < out_n) {
+        m = *reinterpret_cast<const int4*>(matchp + e);
+        d = *reinterpret_cast<const float4*>(distp + e);
+      } else if (e < out_n) {
+        m.x = matchp[e]; d.x = distp[e];
+        if (e + 1 < out_n) { m.y = matchp[e + 1]; d.y = distp[e + 1]; }
+        if (e + 2 < out_n) { m.z = matchp[e + 2]; d.z = distp[e + 2]; }
+      }
+      for (int p = 0; p < pub.n; p++) {
+        reinterpret_cast<int4*>(pub.match[p] + row * pub.stride)[k] = m;
+        reinterpret_cast<float4*>(pub.dist[p] + row * pub.stride)[k] = d;
+      }
+    }
+  } else {
+    for (int k = t; k < pub.stride; k += nt) {
+      const int m = k < out_n ? matchp[k] : -1;
+      const float d = k < out_n ? distp[k] : -1.f;
+      for (int p = 0; p < pub.n; p++) {
+        pub.match[p][row * pub.stride + k] = m;
+        pub.dist[p][row * pub.stride + k] = d;
+      }
+    }
+  }
+  if (t == 0)
+    for (int p = 0; p < pub.n; p++) pub.nm[p][row] = nm;
+}
+
 __global__ void __launch_bounds__(512) k_resolve_bow(const PairDesc* __restrict__ pairs, BowParams P, int cap,
                                                      int n_stride, int m_stride, int out_stride,
                                                      const int32_t* __restrict__ cnt, Cand* __restrict__ cand,
                                                      int32_t* __restrict__ owner, int32_t* __restrict__ acc,
                                                      int32_t* __restrict__ match, float* __restrict__ dist,
-                                                     int32_t* __restrict__ nmatches) {
+                                                     int32_t* __restrict__ nmatches, const PublishArgs pub) {
   const int pair = blockIdx.x;
   const PairDesc& pd = pairs[pair];
   const int nA = pd.nA, nB = pd.nB;
@@ -244,10 +285,9 @@ __global__ void __launch_bounds__(512) k_resolve_bow(const PairDesc* __restrict_
       int pruned = 0;
       for (int b = 0; b < ASDM_HISTO_LENGTH; b++)
         if (b != s_keep[0] && b != s_keep[1] && b != s_keep[2]) pruned += s_hist[b];
-      nmatches[pair] = s_count - pruned;
-    } else {
-      nmatches[pair] = s_count;
+      s_count -= pruned;
     }
+    nmatches[pair] = s_count;
   }
   __syncthreads();
   for (int i = t; i < nA; i += nt) {
@@ -269,6 +309,10 @@ __global__ void __launch_bounds__(512) k_resolve_bow(const PairDesc* __restrict_
       matchp[i] = j;
       distp[i] = d;
     }
+  }
+  if (pub.n) {
+    __syncthreads();  // the row is complete (block-wide) before it is copied out
+    publish_row(pub, pair, matchp, distp, out_n, s_count);
   }
 }
 
@@ -300,7 +344,7 @@ __global__ void __launch_bounds__(512) k_resolve_tri(const PairDesc* __restrict_
                                                      int n_stride, int out_stride, const int32_t* __restrict__ cnt,
                                                      const Cand* __restrict__ cand, int32_t* __restrict__ acc,
                                                      int32_t* __restrict__ match, float* __restrict__ dist,
-                                                     int32_t* __restrict__ nmatches) {
+                                                     int32_t* __restrict__ nmatches, const PublishArgs pub) {
   const int pair = blockIdx.x;
   const PairDesc& pd = pairs[pair];
   const int nA = pd.nA;
@@ -347,7 +391,8 @@ __global__ void __launch_bounds__(512) k_resolve_tri(const PairDesc* __restrict_
       for (int b = 0; b < ASDM_HISTO_LENGTH; b++)
         if (b != s_keep[0] && b != s_keep[1] && b != s_keep[2]) pruned += s_hist[b];
     }
-    nmatches[pair] = s_count - pruned;
+    s_count -= pruned;
+    nmatches[pair] = s_count;
   }
   __syncthreads();
   if (P.check_ori) {
@@ -360,5 +405,9 @@ __global__ void __launch_bounds__(512) k_resolve_tri(const PairDesc* __restrict_
         distp[i] = -1.f;
       }
     }
+  }
+  if (pub.n) {
+    __syncthreads();
+    publish_row(pub, pair, matchp, distp, nA, s_count);
   }
 }

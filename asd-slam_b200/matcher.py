@@ -68,6 +68,23 @@ class Context:
             self.lib.asdm_destroy(self.h)
             self.h = None
 
+    def shared_alloc(self, nbytes):
+        """Device memory other processes of the node can map (asdm_shared_alloc): (pointer, 64-byte handle)."""
+        p, h = C.c_void_p(), (C.c_uint8 * 64)()
+        self.check(self.lib.asdm_shared_alloc(self.h, nbytes, C.byref(p), h))
+        return p.value, bytes(h)
+
+    def shared_open(self, handle):
+        p, h = C.c_void_p(), (C.c_uint8 * 64).from_buffer_copy(handle)
+        self.check(self.lib.asdm_shared_open(self.h, h, C.byref(p)))
+        return p.value
+
+    def shared_close(self, p):
+        self.check(self.lib.asdm_shared_close(self.h, C.c_void_p(p)))
+
+    def shared_free(self, p):
+        self.check(self.lib.asdm_shared_free(self.h, C.c_void_p(p)))
+
     def pinned(self, shape, dtype):
         """numpy array backed by page-locked memory (asdm_host_alloc); keep the returned array alive."""
         return PinnedArray(self.lib, shape, dtype).a
@@ -257,6 +274,13 @@ class PairJob:
         m, d, n = C.c_void_p(), C.c_void_p(), C.c_void_p()
         self.ctx.check(self.ctx.lib.asdm_job_device_outputs(self.h, C.byref(m), C.byref(d), C.byref(n)))
         return m.value, d.value, n.value
+
+    def set_publish(self, match_ptrs, dist_ptrs, nm_ptrs, row0, stride):
+        """The job's resolve kernel also stores every finished row into these rank-major gathered arrays (device
+        pointers: this GPU's and its peers', see shard.GatheredResults); an empty list switches it off."""
+        n = len(match_ptrs)
+        arr = lambda ps: (C.c_void_p * max(n, 1))(*ps)
+        self.ctx.check(self.ctx.lib.asdm_job_set_publish(self.h, n, arr(match_ptrs), arr(dist_ptrs), arr(nm_ptrs), row0, stride))
 
     def destroy(self):
         if self.h:

@@ -13,7 +13,10 @@ row-blocks: 20 covisible pairs become >= 40 units and divide evenly over 8 GPUs.
 sharded by whole pairs only.
 
 `PairShards` is pure host logic (numpy); `all_gather_results` works on CPU tensors over gloo and on CUDA tensors over
-NCCL; `ShardedPairJob` ties both to the device-resident `PairJob` (zero-copy all-gather of the library's outputs).
+NCCL; `ShardedPairJob` ties both to the device-resident `PairJob`.  On GPUs the exchange is fused into the job:
+`GatheredResults` maps every rank's gathered arrays into every other rank (cudaIpc over NVLink) and the job's resolve
+kernel stores each finished row into all of them (asdm_job_set_publish), so what remains behind the kernels is a
+one-word barrier instead of three all-gathers of 16 MB per rank.
 """
 import numpy as np
 
@@ -140,6 +143,91 @@ class ReplicatedDescriptors:
         return self.slab[k % self.world, k // self.world, :n]
 
 
+class GatheredResults:
+    """Rank-major gathered record arrays ([world, per_rank, stride] match / dist, [world, per_rank] counts) of a
+    sharded job, allocated on every rank with asdm_shared_alloc and mapped into every other rank of the node
+    (cudaIpc; peer stores travel over NVLink).  Two generations alternate from run to run: a rank that is one step
+    ahead (it cannot be more, every step ends with a barrier of the group) never overwrites what a slower rank is still
+    reading.  Create once, hand to every ShardedPairJob of the sweep; collective (all ranks must construct it).
+    """
+
+    GENERATIONS = 2
+
+    def __init__(self, ctx, rank, world, per_rank, stride, group=None):
+        import torch
+        import torch.distributed as dist
+
+        self.ctx, self.rank, self.world, self.group = ctx, rank, world, group
+        self.per_rank, self.stride = per_rank, stride
+        rows = world * per_rank
+        al = lambda x: (x + 255) & ~255
+        self._o_dist = al(rows * stride * 4)
+        self._o_nm = self._o_dist + al(rows * stride * 4)
+        self._gen_bytes = self._o_nm + al(rows * 4)
+        total = self.GENERATIONS * self._gen_bytes
+        self.base, handle = ctx.shared_alloc(total)
+        handles = [None] * world
+        if world > 1:
+            dist.all_gather_object(handles, handle, group=group)
+        self.bases = [self.base if r == rank else ctx.shared_open(handles[r]) for r in range(world)]
+        dev = torch.device("cuda", ctx.device)
+        self._torch = torch
+        whole = torch.as_tensor(_DevArray(self.base, (total // 4,), "<i4"), device=dev)
+        whole.fill_(-1)  # rows no unit is dealt to stay "no match"; their counts are zeroed below
+        self.views = []
+        for g in range(self.GENERATIONS):
+            b = self.base + g * self._gen_bytes
+            m = torch.as_tensor(_DevArray(b, (world, per_rank, stride), "<i4"), device=dev)
+            d = torch.as_tensor(_DevArray(b + self._o_dist, (world, per_rank, stride), "<f4"), device=dev)
+            n = torch.as_tensor(_DevArray(b + self._o_nm, (world, per_rank), "<i4"), device=dev)
+            d.fill_(-1.0)
+            n.zero_()
+            self.views.append((m, d, n))
+        self._token = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.gen = self.GENERATIONS - 1
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier(group=group)  # every mapping exists and is initialised before anyone publishes
+
+    def next_generation(self):
+        self.gen = (self.gen + 1) % self.GENERATIONS
+        return self.gen
+
+    def ptrs(self, gen):
+        """(match, dist, nm) device pointers of generation `gen` on every rank, rank order."""
+        o = gen * self._gen_bytes
+        return ([b + o for b in self.bases], [b + o + self._o_dist for b in self.bases], [b + o + self._o_nm for b in self.bases])
+
+    def current(self):
+        return self.views[self.gen]
+
+    def barrier(self, stream):
+        """Stream-ordered barrier of the group: once it has run here, every rank's kernels queued before its own
+        barrier -- hence all their stores into this rank's arrays -- are complete."""
+        if self.world > 1:
+            import torch.distributed as dist
+            if dist.get_backend(self.group) == "nccl":
+                with self._torch.cuda.stream(stream):
+                    dist.all_reduce(self._token, group=self.group)
+            else:  # host-side group (tests: two ranks on one GPU over gloo)
+                self.ctx.synchronize()
+                dist.barrier(group=self.group)
+
+    def close(self):
+        if self.base is None:
+            return
+        self.ctx.synchronize()
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.barrier(group=self.group)  # nobody is still storing into a mapping that is about to go away
+        for r, b in enumerate(self.bases):
+            if r != self.rank:
+                self.ctx.shared_close(b)
+        self.views = []
+        self.ctx.shared_free(self.base)
+        self.base = None
+
+
 class _DevArray:
     """Exposes a raw device pointer of the library to torch (zero copy)."""
 
@@ -157,7 +245,9 @@ class ShardedPairJob:
     """
 
     def __init__(self, ctx, kind, sets, masks, ia, ib, nnratio=0.6, check_ori=True, F12=None, epipoles=None,
-                 scale_factors=None, level_sigma2=None, rank=0, world=1, group=None, blocks_per_pair=1):
+                 scale_factors=None, level_sigma2=None, rank=0, world=1, group=None, blocks_per_pair=1, gathered=None):
+        """gathered: a GatheredResults of matching shape -- the job then publishes its rows into every rank's arrays
+        from its own resolve kernel and gather() is a barrier; None: NCCL / gloo all-gathers of the local outputs."""
         import torch
         from .matcher import PairJob
 
@@ -183,6 +273,13 @@ class ShardedPairJob:
         dev = torch.device("cuda", ctx.device)
         self._torch = torch
         pr = self.shards.per_rank
+        self.gathered = gathered
+        if gathered is not None:
+            if (gathered.world, gathered.per_rank) != (world, pr) or gathered.stride < self.stride:
+                raise ValueError("GatheredResults shaped for another job")
+            self.stride = gathered.stride
+            self.g_match, self.g_dist, self.g_nm = gathered.current()
+            return
         self.g_match = torch.empty((world, pr, self.stride), dtype=torch.int32, device=dev)
         self.g_dist = torch.empty((world, pr, self.stride), dtype=torch.float32, device=dev)
         self.g_nm = torch.empty((world, pr), dtype=torch.int32, device=dev)
@@ -194,6 +291,13 @@ class ShardedPairJob:
             self.l_nm = torch.as_tensor(_DevArray(pn, (pr,), "<i4"), device=dev)
 
     def run(self):
+        g = self.gathered
+        if g is not None:  # the rows go out from the resolve kernel itself, into the next generation of arrays
+            gen = g.next_generation()
+            self.g_match, self.g_dist, self.g_nm = g.current()
+            if self.n_local:
+                pm, pd_, pn = g.ptrs(gen)
+                self.job.set_publish(pm, pd_, pn, self.rank * g.per_rank, g.stride)
         self.job.run()
 
     def settle(self):
@@ -222,8 +326,12 @@ class ShardedPairJob:
         return self._ext[1]
 
     def gather(self):
-        """Queues the all-gathers on the stream the job ran on (set with Context.set_stream to a torch stream)."""
+        """Queues the exchange on the stream the job ran on (set with Context.set_stream to a torch stream): a barrier
+        when the job publishes its rows itself, the all-gathers of the local outputs otherwise."""
         torch = self._torch
+        if self.gathered is not None:
+            self.gathered.barrier(self._stream())
+            return
         with torch.cuda.stream(self._stream()):
             m, d, n = self._locals()
             pr = self.shards.per_rank

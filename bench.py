@@ -215,13 +215,16 @@ def run_ours(args):
     # ---- resident inputs (device-only arm): keyframe sets uploaded once, as the SLAM system would at KF creation
     sets = [pkg.DescriptorSet(ctx, k["desc"], k["kps"], c["grid"], k["fv"]) for k in kfs]
     masks = [k["valid"] for k in kfs]
+    # N>1: every rank's gathered record arrays are mapped into every other rank (cudaIpc over NVLink) and the job's
+    # resolve kernel stores each finished row into all of them; --gather nccl keeps three ncclAllGather calls instead
+    gathered = pkg.GatheredResults(ctx, rank, world, P, n) if world > 1 and args.gather == "push" else None
     job = pkg.ShardedPairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, sets, masks, g_ia, g_ib, c["nnratio"], c["check_ori"],
-                             rank=rank, world=world)
+                             rank=rank, world=world, gathered=gathered)
     S = job.stride
 
     def step():
         job.run()
-        if world > 1:  # results of all shards on every rank (north_star: NCCL all-gather over NVLink)
+        if world > 1:  # results of all shards on every rank (north_star: all-gather over NVLink)
             job.gather()
 
     for _ in range(max(args.warmup, 3)):
@@ -297,7 +300,7 @@ def run_ours(args):
             rep_desc.upload(h_desc_t)
             ss = pkg.DescriptorSet.create_batch(ctx, [rep_desc.rows(i, n) for i in range(len(kfs))], kps_all, c["grid"], fv_all)
             jb = pkg.ShardedPairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, ss, masks, g_ia, g_ib, c["nnratio"], c["check_ori"],
-                                    rank=rank, world=world)
+                                    rank=rank, world=world, gathered=gathered)
             jb.run()
             jb.fetch_gathered(h_match, h_dist, h_nm)
         if jb is not None:
@@ -383,8 +386,10 @@ def run_ours(args):
                "config": {"workload": WORKLOAD, "pairs_per_gpu": P, "descriptors_per_keyframe": n,
                           "l2": "inputs larger than L2 (197 MB of descriptors + candidate pools vs 126 MB); no flush",
                           "tensor_core_shortlist": bool(tc_used), "shortlist_hits_per_step": int(shortlist_hits),
-                          "sharding": "round-robin pairs over ranks, NCCL all-gather of match/dist/count records"
-                                      if world > 1 else "single GPU"},
+                          "sharding": ("round-robin pairs over ranks; " +
+                                       ("match/dist/count rows stored into every rank's gathered arrays by the resolve kernel "
+                                        "(cudaIpc peer memory over NVLink) + one-word NCCL barrier" if gathered is not None else
+                                        "NCCL all-gather of match/dist/count records")) if world > 1 else "single GPU"},
                "keyframe_pairs_per_sec": world * P * args.steps / (ms * 1e-3),
                "e2e": {"value": world * units / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                        "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms,
@@ -394,7 +399,9 @@ def run_ours(args):
                                 "asdm_set_create_async x64 (pinned host descriptors) + featvec + job prepare/run/fetch per step")
                                if world == 1 else
                                "per step: each keyframe uploaded once (rank k%N) + NVLink all-gather of descriptors, 64 device-"
-                               "side set creates per rank, sharded job, NCCL all-gather of results, rank 0 reads all match lists"},
+                               "side set creates per rank, sharded job, " + ("results published to every rank by the resolve kernel"
+                                                                      if gathered is not None else "NCCL all-gather of results") +
+                               ", rank 0 reads all match lists"},
                "gpu_launches": int(launches_per_step * args.steps),
                "roofline": roof,
                "cpu_baseline": {"value": cpu_val, "unit": UNIT, "cores": threads, "kind": "port",
@@ -416,6 +423,8 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--gather", default="push", choices=["push", "nccl"],
+                    help="N>1: results stored into every rank's arrays by the resolve kernel (push) or ncclAllGather calls")
     ap.add_argument("--no-stream", action="store_true", help="e2e at N=1: upload everything, then one job (no overlap)")
     ap.add_argument("--pairs", type=int, default=N_PAIRS, help="keyframe pairs per GPU per step (default: the C5 sweep)")
     ap.add_argument("--tc-variant", type=int, default=0, help="tuning: pipeline shape of the tensor-core kernel")

@@ -279,6 +279,25 @@ int asdm_job_out_stride(const asdm_job* job);
 int asdm_job_device_outputs(asdm_job* job, void** match12, void** dist12, void** nmatches);
 int asdm_job_destroy(asdm_job* job);
 
+/* ---- results published into every rank's gathered arrays by the job itself (one process per GPU) ----
+ * The exchange step of a sharded sweep -- every rank ends up with the match lists of all ranks -- as the epilogue of the
+ * job's last kernel instead of a collective call behind it: each rank allocates its gathered record arrays with
+ * asdm_shared_alloc, hands the 64-byte handle to the other processes of the node (any transport: torch.distributed
+ * object all-gather, a pipe), opens theirs with asdm_shared_open (cudaIpc mapping, NVLink peer access) and tells its job
+ * where row `row0 + pair` of every rank's arrays is. From then on asdm_job_run stores each finished row into all of
+ * them; a barrier of the group on the same stream (e.g. a one-word NCCL all-reduce) is all that is left for the caller
+ * before reading. Replaces the three ncclAllGather calls of the north-star design, not a reference function. */
+#define ASDM_SHARED_HANDLE_BYTES 64
+int asdm_shared_alloc(asdm_ctx* ctx, size_t bytes, void** dptr, uint8_t handle[ASDM_SHARED_HANDLE_BYTES]);
+int asdm_shared_open(asdm_ctx* ctx, const uint8_t handle[ASDM_SHARED_HANDLE_BYTES], void** dptr);
+int asdm_shared_close(asdm_ctx* ctx, void* dptr); /* a pointer from asdm_shared_open */
+int asdm_shared_free(asdm_ctx* ctx, void* dptr);  /* a pointer from asdm_shared_alloc */
+/* n_ranks <= 16 destinations (this rank's own arrays included; 0 switches publishing off). match / dist: [rows][stride]
+ * int32 / fp32 with stride >= asdm_job_out_stride (the tail of a row is filled with -1), nmatches: [rows] int32. May be
+ * called between runs (e.g. to alternate between two generations of arrays). */
+int asdm_job_set_publish(asdm_job* job, int n_ranks, void* const* match, void* const* dist, void* const* nmatches,
+                         int row0, int stride);
+
 /* ------------------------------------------------------------------ map-point descriptor maintenance */
 /* MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:271-338) for a batch of map points, e.g. all points matched by
  * a new keyframe (LocalMapping.cc:245, 535, 628). Observations of point p are rows (sets[obs_set[e]], obs_row[e]),

@@ -228,6 +228,87 @@ def test_sharded_job_world1(pkg, ctx, oracle, kind):
         ctx.set_stream(None)
 
 
+def _publish_worker(rank, world, port, kind, n, q):
+    """One rank of a two-process group that shares GPU 0: the gathered arrays of each process are mapped into the other
+    (cudaIpc works between processes on one device too), the job publishes its rows from the resolve kernel."""
+    try:
+        import torch
+        import torch.distributed as dist
+        sys.path.insert(0, ROOT)
+        pkg = importlib.import_module("asd-slam_b200")
+        sh = importlib.import_module("asd-slam_b200.shard")
+        dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+        torch.cuda.set_device(0)
+        ctx = pkg.Context(0)
+        stream = torch.cuda.Stream()
+        ctx.set_stream(stream.cuda_stream)
+        if kind == "tri":
+            pairs, blocks = 5, 2
+            c = pkg.synth.config4(n=n, n_pairs=pairs)
+            sets = [pkg.DescriptorSet(ctx, k["desc"], k["kps"], c["grid"], k["fv"]) for k in c["kfs"]]
+            masks = [k["has_mp"] for k in c["kfs"]]
+            args = (0.6, 0, c["F12"], c["epipoles"], c["scale_factors"], c["level_sigma2"])
+            job_kind = pkg.ASDM_JOB_TRIANGULATION
+        else:
+            pairs, blocks = 9, 1
+            c = pkg.synth.config5(n=n, n_pairs=pairs, n_kf=5)
+            sets = [pkg.DescriptorSet(ctx, k["desc"], k["kps"], c["grid"], k["fv"]) for k in c["kfs"]]
+            masks = [k["valid"] for k in c["kfs"]]
+            args = (c["nnratio"], c["check_ori"])
+            job_kind = pkg.ASDM_JOB_BOW_KF_KF
+        per_rank = sh.PairShards([n] * pairs, world, blocks).per_rank
+        gathered = sh.GatheredResults(ctx, rank, world, per_rank, n)
+        outs = []
+        for step in range(3):  # a new job per step on the same arrays: the generations alternate
+            job = sh.ShardedPairJob(ctx, job_kind, sets, masks, c["ia"], c["ib"], *args, rank=rank, world=world,
+                                    blocks_per_pair=blocks, gathered=gathered)
+            job.run()
+            outs.append(job.fetch())
+            job.destroy()
+        gathered.close()
+        for s in sets:
+            s.release()
+        ctx.close()
+        dist.barrier()
+        dist.destroy_process_group()
+        q.put((rank, True, [tuple(np.ascontiguousarray(x) for x in o) for o in outs]))
+    except Exception as e:  # pragma: no cover
+        import traceback
+        q.put((rank, False, traceback.format_exc()))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind,n", [("bow", 700), ("bow", 701), ("tri", 900)])
+def test_world2_rows_published_by_the_resolve_kernel(pkg, oracle, kind, n):
+    """SURVEY 8e on the GPU: two ranks (two processes sharing GPU 0, gloo for the handle exchange and the barrier), the
+    match lists reach both ranks through asdm_job_set_publish -- no all-gather call -- and equal the unsharded oracle.
+    n = 701: rows that cannot take 16-byte stores; 9 pairs over 2 ranks: a rank with an empty last slot."""
+    import torch.multiprocessing as mp
+    mctx = mp.get_context("spawn")
+    q = mctx.Queue()
+    port = _free_port()
+    procs = [mctx.Process(target=_publish_worker, args=(r, 2, port, kind, n, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(ok for _, ok, _ in res), [r for r in res if not r[1]]
+    if kind == "tri":
+        c = pkg.synth.config4(n=n, n_pairs=5)
+        ref = oracle.batch_triangulation(c["kfs"], c["ia"], c["ib"], c["F12"], c["epipoles"], c["scale_factors"],
+                                         c["level_sigma2"], 0, threads=oracle.max_threads())
+    else:
+        c = pkg.synth.config5(n=n, n_pairs=9, n_kf=5)
+        ref = oracle.batch_bow_kf_kf(c["kfs"], c["ia"], c["ib"], c["nnratio"], c["check_ori"], threads=oracle.max_threads())
+    assert ref[0].sum() > 0
+    for _, _, outs in res:  # every rank, every step
+        for nm, match, dist_ in outs:
+            assert np.array_equal(nm, ref[0])
+            assert np.array_equal(match[:, :n], ref[1])
+            assert np.array_equal(dist_[:, :n].view(np.uint32), ref[2].view(np.uint32))
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("batch", [False, True])
 def test_sets_from_replicated_device_rows(pkg, ctx, oracle, batch):
