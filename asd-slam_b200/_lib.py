@@ -133,7 +133,7 @@ def load():
     lib.asdm_shared_open.argtypes = [vp, vp, C.POINTER(vp)]
     lib.asdm_shared_close.argtypes = [vp, vp]
     lib.asdm_shared_free.argtypes = [vp, vp]
-    lib.asdm_job_set_publish.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.c_int, C.c_int]
+    lib.asdm_job_set_publish.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.c_int, C.c_int, C.c_int]
     lib.asdm_job_destroy.argtypes = [vp]
     lib.asdm_distinctive_descriptors.argtypes = [vp, C.POINTER(vp), C.c_int, C.c_int, vp, vp, vp, vp, vp]
     lib.asdm_desc_block_bytes.argtypes = [C.c_int]

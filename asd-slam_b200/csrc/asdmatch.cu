@@ -1380,7 +1380,7 @@ extern "C" int asdm_shared_free(asdm_ctx* ctx, void* dptr) {
 }
 
 extern "C" int asdm_job_set_publish(asdm_job* j, int n_ranks, void* const* match, void* const* dist, void* const* nmatches,
-                                    int row0, int stride) {
+                                    int row0, int stride, int flags) {
   if (!j) return ASDM_ERR_INVALID;
   asdm_ctx* ctx = j->ctx;
   std::lock_guard<std::recursive_mutex> lk(ctx->mu);
@@ -1396,6 +1396,7 @@ extern "C" int asdm_job_set_publish(asdm_job* j, int n_ranks, void* const* match
   j->pub.n = n_ranks;
   j->pub.row0 = row0;
   j->pub.stride = stride;
+  j->pub.multicast = (flags & ASDM_PUBLISH_MULTICAST) ? 1 : 0;
   for (int r = 0; r < n_ranks; r++) {
     j->pub.match[r] = (int32_t*)match[r];
     j->pub.dist[r] = (float*)dist[r];

@@ -143,10 +143,28 @@ __device__ __forceinline__ bool cand_before(const Cand& x, int px, const Cand& y
 // Epilogue of the resolve kernels when the job publishes (PublishArgs): the CTA's finished row -- out_n entries, the
 // rest of the gathered stride padded with -1 -- goes to the same slot of every rank's gathered arrays. Peer stores
 // travel over NVLink while the other CTAs are still resolving their pairs. 16-byte stores when the rows allow it.
+// Multicast destinations (an NVSwitch multicast mapping that every rank's array is bound to) take multimem.st: the
+// row leaves this GPU once and the switch replicates it, so the egress is 1/N of the unicast version's.
+__device__ __forceinline__ void pub_store4(void* p, int4 v, bool mc) {
+  if (mc)
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(__int_as_float(v.x)),
+                 "f"(__int_as_float(v.y)), "f"(__int_as_float(v.z)), "f"(__int_as_float(v.w))
+                 : "memory");
+  else
+    *reinterpret_cast<int4*>(p) = v;
+}
+__device__ __forceinline__ void pub_store1(void* p, int v, bool mc) {
+  if (mc)
+    asm volatile("multimem.st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+  else
+    *reinterpret_cast<int*>(p) = v;
+}
+
 __device__ __forceinline__ void publish_row(const PublishArgs& pub, int pair, const int32_t* __restrict__ matchp,
                                             const float* __restrict__ distp, int out_n, int nm) {
   const int t = threadIdx.x, nt = blockDim.x;
   const size_t row = (size_t)(pub.row0 + pair);
+  const bool mc = pub.multicast != 0;
   const bool vec = (pub.stride & 3) == 0 && ((reinterpret_cast<uintptr_t>(matchp) | reinterpret_cast<uintptr_t>(distp)) & 15) == 0;
   if (vec) {
     const int n4 = pub.stride >> 2;
@@ -162,9 +180,10 @@ __device__ __forceinline__ void publish_row(const PublishArgs& pub, int pair, co
         if (e + 1 < out_n) { m.y = matchp[e + 1]; d.y = distp[e + 1]; }
         if (e + 2 < out_n) { m.z = matchp[e + 2]; d.z = distp[e + 2]; }
       }
+      const int4 di = make_int4(__float_as_int(d.x), __float_as_int(d.y), __float_as_int(d.z), __float_as_int(d.w));
       for (int p = 0; p < pub.n; p++) {
-        reinterpret_cast<int4*>(pub.match[p] + row * pub.stride)[k] = m;
-        reinterpret_cast<float4*>(pub.dist[p] + row * pub.stride)[k] = d;
+        pub_store4(pub.match[p] + row * pub.stride + e, m, mc);
+        pub_store4(pub.dist[p] + row * pub.stride + e, di, mc);
       }
     }
   } else {
@@ -172,13 +191,14 @@ __device__ __forceinline__ void publish_row(const PublishArgs& pub, int pair, co
       const int m = k < out_n ? matchp[k] : -1;
       const float d = k < out_n ? distp[k] : -1.f;
       for (int p = 0; p < pub.n; p++) {
-        pub.match[p][row * pub.stride + k] = m;
-        pub.dist[p][row * pub.stride + k] = d;
+        pub_store1(pub.match[p] + row * pub.stride + k, m, mc);
+        pub_store1(pub.dist[p] + row * pub.stride + k, __float_as_int(d), mc);
       }
     }
   }
   if (t == 0)
-    for (int p = 0; p < pub.n; p++) pub.nm[p][row] = nm;
+    for (int p = 0; p < pub.n; p++) pub_store1(pub.nm[p] + row, nm, mc);
+  __threadfence_system();  // the stores are on their way to the other GPUs before this CTA retires
 }
 
 __global__ void __launch_bounds__(512) k_resolve_bow(const PairDesc* __restrict__ pairs, BowParams P, int cap,

@@ -275,12 +275,14 @@ class PairJob:
         self.ctx.check(self.ctx.lib.asdm_job_device_outputs(self.h, C.byref(m), C.byref(d), C.byref(n)))
         return m.value, d.value, n.value
 
-    def set_publish(self, match_ptrs, dist_ptrs, nm_ptrs, row0, stride):
+    def set_publish(self, match_ptrs, dist_ptrs, nm_ptrs, row0, stride, multicast=False):
         """The job's resolve kernel also stores every finished row into these rank-major gathered arrays (device
-        pointers: this GPU's and its peers', see shard.GatheredResults); an empty list switches it off."""
+        pointers: this GPU's and its peers', or one NVSwitch multicast mapping of them all -- see
+        shard.GatheredResults); an empty list switches it off."""
         n = len(match_ptrs)
         arr = lambda ps: (C.c_void_p * max(n, 1))(*ps)
-        self.ctx.check(self.ctx.lib.asdm_job_set_publish(self.h, n, arr(match_ptrs), arr(dist_ptrs), arr(nm_ptrs), row0, stride))
+        self.ctx.check(self.ctx.lib.asdm_job_set_publish(self.h, n, arr(match_ptrs), arr(dist_ptrs), arr(nm_ptrs), row0, stride,
+                                                         1 if multicast else 0))
 
     def destroy(self):
         if self.h:

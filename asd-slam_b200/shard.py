@@ -145,15 +145,21 @@ class ReplicatedDescriptors:
 
 class GatheredResults:
     """Rank-major gathered record arrays ([world, per_rank, stride] match / dist, [world, per_rank] counts) of a
-    sharded job, allocated on every rank with asdm_shared_alloc and mapped into every other rank of the node
-    (cudaIpc; peer stores travel over NVLink).  Two generations alternate from run to run: a rank that is one step
-    ahead (it cannot be more, every step ends with a barrier of the group) never overwrites what a slower rank is still
-    reading.  Create once, hand to every ShardedPairJob of the sweep; collective (all ranks must construct it).
+    sharded job on every rank, writable by every other rank of the node.  Two transports:
+
+      * "multicast": torch symmetric memory (CUDA VMM allocations bound to one NVSwitch multicast object, NVLS); the
+        job stores a row ONCE to the multicast address and the switch delivers it to all ranks, its own included;
+      * "peer": asdm_shared_alloc + cudaIpc mappings; the job stores the row to every rank's array over NVLink.
+
+    "auto" takes multicast when the group is NCCL, the rows allow 16-byte stores and the rendezvous yields a multicast
+    mapping, peer otherwise.  Two generations alternate from run to run: a rank that is one step ahead (it cannot be
+    more, every step ends with a barrier of the group) never overwrites what a slower rank is still reading.  Create
+    once, hand to every ShardedPairJob of the sweep; collective (all ranks must construct it).
     """
 
     GENERATIONS = 2
 
-    def __init__(self, ctx, rank, world, per_rank, stride, group=None):
+    def __init__(self, ctx, rank, world, per_rank, stride, group=None, transport="auto"):
         import torch
         import torch.distributed as dist
 
@@ -165,21 +171,41 @@ class GatheredResults:
         self._o_nm = self._o_dist + al(rows * stride * 4)
         self._gen_bytes = self._o_nm + al(rows * 4)
         total = self.GENERATIONS * self._gen_bytes
-        self.base, handle = ctx.shared_alloc(total)
-        handles = [None] * world
-        if world > 1:
-            dist.all_gather_object(handles, handle, group=group)
-        self.bases = [self.base if r == rank else ctx.shared_open(handles[r]) for r in range(world)]
         dev = torch.device("cuda", ctx.device)
         self._torch = torch
-        whole = torch.as_tensor(_DevArray(self.base, (total // 4,), "<i4"), device=dev)
+        self.base = self.mc_base = self._symm = None
+        want_mc = transport == "multicast" or (transport == "auto" and world > 1 and stride % 4 == 0 and
+                                               dist.get_backend(group) == "nccl")
+        if want_mc:
+            try:
+                import torch.distributed._symmetric_memory as symm_mem
+                t = symm_mem.empty(total // 4, dtype=torch.int32, device=dev)
+                h = symm_mem.rendezvous(t, group=group if group is not None else dist.group.WORLD)
+                ok = torch.tensor([1 if h.multicast_ptr else 0], dtype=torch.int32, device=dev)
+                dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+                if int(ok.item()):
+                    self._symm, self.mc_base, whole = (t, h), int(h.multicast_ptr), t
+            except Exception:
+                if transport == "multicast":
+                    raise
+        if self.mc_base is None:
+            if transport == "multicast":
+                raise RuntimeError("no NVLink multicast mapping on this system")
+            self.base, handle = ctx.shared_alloc(total)
+            handles = [None] * world
+            if world > 1:
+                dist.all_gather_object(handles, handle, group=group)
+            self.bases = [self.base if r == rank else ctx.shared_open(handles[r]) for r in range(world)]
+            whole = torch.as_tensor(_DevArray(self.base, (total // 4,), "<i4"), device=dev)
+        self.transport = "multicast" if self.mc_base is not None else "peer"
         whole.fill_(-1)  # rows no unit is dealt to stay "no match"; their counts are zeroed below
         self.views = []
+        n_md = rows * stride
         for g in range(self.GENERATIONS):
-            b = self.base + g * self._gen_bytes
-            m = torch.as_tensor(_DevArray(b, (world, per_rank, stride), "<i4"), device=dev)
-            d = torch.as_tensor(_DevArray(b + self._o_dist, (world, per_rank, stride), "<f4"), device=dev)
-            n = torch.as_tensor(_DevArray(b + self._o_nm, (world, per_rank), "<i4"), device=dev)
+            o = g * self._gen_bytes // 4
+            m = whole[o:o + n_md].view(world, per_rank, stride)
+            d = whole[o + self._o_dist // 4:o + self._o_dist // 4 + n_md].view(torch.float32).view(world, per_rank, stride)
+            n = whole[o + self._o_nm // 4:o + self._o_nm // 4 + rows].view(world, per_rank)
             d.fill_(-1.0)
             n.zero_()
             self.views.append((m, d, n))
@@ -194,9 +220,10 @@ class GatheredResults:
         return self.gen
 
     def ptrs(self, gen):
-        """(match, dist, nm) device pointers of generation `gen` on every rank, rank order."""
+        """(match, dist, nm) destination pointers of generation `gen`: one multicast address each, or one per rank."""
         o = gen * self._gen_bytes
-        return ([b + o for b in self.bases], [b + o + self._o_dist for b in self.bases], [b + o + self._o_nm for b in self.bases])
+        bases = [self.mc_base] if self.mc_base is not None else self.bases
+        return ([b + o for b in bases], [b + o + self._o_dist for b in bases], [b + o + self._o_nm for b in bases])
 
     def current(self):
         return self.views[self.gen]
@@ -214,16 +241,19 @@ class GatheredResults:
                 dist.barrier(group=self.group)
 
     def close(self):
-        if self.base is None:
+        if self.base is None and self._symm is None:
             return
         self.ctx.synchronize()
         if self.world > 1:
             import torch.distributed as dist
             dist.barrier(group=self.group)  # nobody is still storing into a mapping that is about to go away
+        self.views = []
+        if self._symm is not None:
+            self._symm = self.mc_base = None
+            return
         for r, b in enumerate(self.bases):
             if r != self.rank:
                 self.ctx.shared_close(b)
-        self.views = []
         self.ctx.shared_free(self.base)
         self.base = None
 
@@ -297,7 +327,7 @@ class ShardedPairJob:
             self.g_match, self.g_dist, self.g_nm = g.current()
             if self.n_local:
                 pm, pd_, pn = g.ptrs(gen)
-                self.job.set_publish(pm, pd_, pn, self.rank * g.per_rank, g.stride)
+                self.job.set_publish(pm, pd_, pn, self.rank * g.per_rank, g.stride, multicast=g.transport == "multicast")
         self.job.run()
 
     def settle(self):

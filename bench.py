@@ -217,7 +217,8 @@ def run_ours(args):
     masks = [k["valid"] for k in kfs]
     # N>1: every rank's gathered record arrays are mapped into every other rank (cudaIpc over NVLink) and the job's
     # resolve kernel stores each finished row into all of them; --gather nccl keeps three ncclAllGather calls instead
-    gathered = pkg.GatheredResults(ctx, rank, world, P, n) if world > 1 and args.gather == "push" else None
+    gathered = pkg.GatheredResults(ctx, rank, world, P, n, transport={"push": "auto", "peer": "peer"}.get(args.gather, "auto")) \
+        if world > 1 and args.gather != "nccl" else None
     job = pkg.ShardedPairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, sets, masks, g_ia, g_ib, c["nnratio"], c["check_ori"],
                              rank=rank, world=world, gathered=gathered)
     S = job.stride
@@ -275,7 +276,7 @@ def run_ours(args):
         rep_desc = None
     else:  # rank-major gathered records of the whole job
         h_match = torch.empty((world, P, S), dtype=torch.int32).pin_memory() if rank == 0 else None
-        h_dist = torch.empty((world, P, S), dtype=torch.float32).pin_memory() if rank == 0 else None
+        h_dist = None  # the reference call returns vpMatches12 only (ORBmatcher.cc:533); distances stay on the GPUs
         h_nm = torch.empty((world, P), dtype=torch.int32).pin_memory()
         rep_desc = pkg.ReplicatedDescriptors(ctx, len(kfs), n, rank, world)
 
@@ -327,7 +328,8 @@ def run_ours(args):
     elif world == 1:
         e2e_same = np.array_equal(h_match, match)
     elif rank == 0:
-        e2e_same = np.array_equal(job.shards.merge(h_match.numpy(), h_dist.numpy(), h_nm.numpy())[1], match)
+        mm = job.shards.merge(h_match.numpy(), np.zeros(h_match.shape, np.float32), h_nm.numpy())
+        e2e_same = np.array_equal(mm[1], match) and np.array_equal(mm[0], nm)
     else:
         e2e_same = np.array_equal(job.shards.merge(np.zeros((world, P, 1), np.int32), np.zeros((world, P, 1), np.float32),
                                                    h_nm.numpy())[0], nm)
@@ -338,7 +340,7 @@ def run_ours(args):
     h2d = sum(k["desc"].nbytes for k in kfs) + world * side
     if sweep is not None:  # every wave re-sends the masks of the keyframes it may touch
         h2d += sum(sum(len(k["valid"]) for k in kfs[:b]) for b in sweep.bounds[:-1])
-    d2h = world * P * S * 8 + world * (world * P * 4)
+    d2h = world * P * S * (8 if world == 1 else 4) + world * (world * P * 4)
 
     if rank == 0:
         pk = peaks()
@@ -387,8 +389,9 @@ def run_ours(args):
                           "l2": "inputs larger than L2 (197 MB of descriptors + candidate pools vs 126 MB); no flush",
                           "tensor_core_shortlist": bool(tc_used), "shortlist_hits_per_step": int(shortlist_hits),
                           "sharding": ("round-robin pairs over ranks; " +
-                                       ("match/dist/count rows stored into every rank's gathered arrays by the resolve kernel "
-                                        "(cudaIpc peer memory over NVLink) + one-word NCCL barrier" if gathered is not None else
+                                       ("match/dist/count rows stored into every rank's gathered arrays by the resolve kernel (" +
+                                        ("one multimem.st per 16 bytes to an NVSwitch multicast mapping" if gathered.transport == "multicast"
+                                         else "cudaIpc peer memory over NVLink") + ") + one-word NCCL barrier" if gathered is not None else
                                         "NCCL all-gather of match/dist/count records")) if world > 1 else "single GPU"},
                "keyframe_pairs_per_sec": world * P * args.steps / (ms * 1e-3),
                "e2e": {"value": world * units / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
@@ -401,7 +404,7 @@ def run_ours(args):
                                "per step: each keyframe uploaded once (rank k%N) + NVLink all-gather of descriptors, 64 device-"
                                "side set creates per rank, sharded job, " + ("results published to every rank by the resolve kernel"
                                                                       if gathered is not None else "NCCL all-gather of results") +
-                               ", rank 0 reads all match lists"},
+                               ", rank 0 reads all match lists (indices + counts)"},
                "gpu_launches": int(launches_per_step * args.steps),
                "roofline": roof,
                "cpu_baseline": {"value": cpu_val, "unit": UNIT, "cores": threads, "kind": "port",
@@ -423,8 +426,9 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--gather", default="push", choices=["push", "nccl"],
-                    help="N>1: results stored into every rank's arrays by the resolve kernel (push) or ncclAllGather calls")
+    ap.add_argument("--gather", default="push", choices=["push", "peer", "nccl"],
+                    help="N>1: results stored into every rank's arrays by the resolve kernel -- push: NVSwitch multicast "
+                         "when available, else peer stores; peer: peer stores -- or three ncclAllGather calls (nccl)")
     ap.add_argument("--no-stream", action="store_true", help="e2e at N=1: upload everything, then one job (no overlap)")
     ap.add_argument("--pairs", type=int, default=N_PAIRS, help="keyframe pairs per GPU per step (default: the C5 sweep)")
     ap.add_argument("--tc-variant", type=int, default=0, help="tuning: pipeline shape of the tensor-core kernel")

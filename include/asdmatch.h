@@ -295,8 +295,10 @@ int asdm_shared_free(asdm_ctx* ctx, void* dptr);  /* a pointer from asdm_shared_
 /* n_ranks <= 16 destinations (this rank's own arrays included; 0 switches publishing off). match / dist: [rows][stride]
  * int32 / fp32 with stride >= asdm_job_out_stride (the tail of a row is filled with -1), nmatches: [rows] int32. May be
  * called between runs (e.g. to alternate between two generations of arrays). */
+#define ASDM_PUBLISH_MULTICAST 1 /* the destinations are NVSwitch multicast mappings (e.g. torch symmetric memory's
+                                  * multicast_ptr + offset): one store reaches every rank bound to them, n_ranks = 1 */
 int asdm_job_set_publish(asdm_job* job, int n_ranks, void* const* match, void* const* dist, void* const* nmatches,
-                         int row0, int stride);
+                         int row0, int stride, int flags);
 
 /* ------------------------------------------------------------------ map-point descriptor maintenance */
 /* MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:271-338) for a batch of map points, e.g. all points matched by
