@@ -231,7 +231,7 @@ def run_ours(args):
     for _ in range(max(args.warmup, 3)):
         step()
         job.settle()  # grows candidate pools if the first runs overflowed
-    launches_per_step = ctx.stat("gpu_launches")
+    launches_per_step = job.launches  # all sub-jobs of the step
     tc_used = ctx.stat("tc_used")
     ctx.set_option("time_kernels", 1)
     ctx.stat("dist_stage_us")  # drain
@@ -258,8 +258,8 @@ def run_ours(args):
     dist_us = ctx.stat("dist_stage_us")
     ctx.set_option("time_kernels", 0)
     job.settle()
-    assert ctx.stat("retries") == 0, "a candidate pool overflowed inside the timed region"
-    shortlist_hits = ctx.stat("tc_pairs")
+    assert job.retries == 0, "a candidate pool overflowed inside the timed region"
+    shortlist_hits = job.tc_pairs
     nm, match, _ = job.fetch()  # merged: all world*P pairs, in global order
 
     # ---- e2e arm: the reference-facing call with HOST buffers -- upload the 64 keyframes from pinned host memory,
