@@ -261,7 +261,7 @@ def _publish_worker(rank, world, port, kind, n, q):
         outs = []
         for step in range(3):  # a new job per step on the same arrays: the generations alternate
             job = sh.ShardedPairJob(ctx, job_kind, sets, masks, c["ia"], c["ib"], *args, rank=rank, world=world,
-                                    blocks_per_pair=blocks, gathered=gathered)
+                                    blocks_per_pair=blocks, gathered=gathered, chunks=3 if kind == "tri" else 1)
             job.run()
             outs.append(job.fetch())
             job.destroy()
