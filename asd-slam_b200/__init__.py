@@ -11,6 +11,6 @@ BASELINE configs.  Importing the package does not load the CUDA library; creatin
 from . import _lib, synth  # noqa: F401
 from ._lib import (ASDM_JOB_BOW_KF_KF, ASDM_JOB_TRIANGULATION, ASDM_PROJ_BEST_ONLY, ASDM_PROJ_RATIO_LEVEL,  # noqa: F401
                    KP_DTYPE, PROJ_QUERY_DTYPE, AsdmError)
-from .matcher import (ComputeDistinctiveDescriptors, Context, DescriptorSet, ORBmatcher, ORBVocabulary,  # noqa: F401
+from .matcher import (ComputeDistinctiveDescriptors, Context, DescriptorSet, KeyFrameDatabase, ORBmatcher, ORBVocabulary,  # noqa: F401
                       PairJob, StreamedPairSweep, save_map_blocks)
 from .shard import GatheredResults, PairShards, ReplicatedDescriptors, ShardedPairJob, all_gather_results  # noqa: F401

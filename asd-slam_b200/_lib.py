@@ -38,7 +38,14 @@ EXPORTS = [
     "asdm_shared_alloc", "asdm_shared_open", "asdm_shared_close", "asdm_shared_free", "asdm_job_set_publish",
     "asdm_distinctive_descriptors",
     "asdm_vocab_create", "asdm_vocab_release", "asdm_vocab_transform",
+    "asdm_bowdb_create", "asdm_bowdb_release", "asdm_bowdb_add", "asdm_bowdb_erase", "asdm_bowdb_clear", "asdm_bowdb_size",
+    "asdm_bowdb_query", "asdm_bowdb_detect_loop", "asdm_bowdb_detect_reloc", "asdm_bowdb_reloc_scores",
 ]
+
+
+class BowdbGates(C.Structure):
+    _fields_ = [("connected", C.c_void_p), ("global_flag", C.c_void_p), ("neigh_off", C.c_void_p), ("neigh_slot", C.c_void_p),
+                ("min_score", C.c_float), ("only_global_map", C.c_int32)]
 
 
 class Grid(C.Structure):
@@ -143,6 +150,16 @@ def load():
     lib.asdm_vocab_create.argtypes = [vp, C.POINTER(VocabDesc), C.POINTER(vp)]
     lib.asdm_vocab_release.argtypes = [vp]
     lib.asdm_vocab_transform.argtypes = [vp, vp, vp, C.c_int, vp, vp, vp, C.POINTER(i32), vp, vp]
+    lib.asdm_bowdb_create.argtypes = [vp, C.POINTER(vp)]
+    lib.asdm_bowdb_release.argtypes = [vp]
+    lib.asdm_bowdb_add.argtypes = [vp, vp, vp, C.c_int, C.POINTER(i32)]
+    lib.asdm_bowdb_erase.argtypes = [vp, C.c_int32]
+    lib.asdm_bowdb_clear.argtypes = [vp]
+    lib.asdm_bowdb_size.argtypes = [vp]
+    lib.asdm_bowdb_query.argtypes = [vp, vp, vp, C.c_int, vp, vp, vp]
+    lib.asdm_bowdb_detect_loop.argtypes = [vp, vp, vp, C.c_int, C.POINTER(BowdbGates), vp, C.c_int, C.POINTER(i32)]
+    lib.asdm_bowdb_detect_reloc.argtypes = [vp, vp, vp, C.c_int, C.POINTER(BowdbGates), vp, C.c_int, C.POINTER(i32)]
+    lib.asdm_bowdb_reloc_scores.argtypes = [vp, vp]
     _lib = lib
     return lib
 

@@ -134,6 +134,7 @@ struct PublishArgs {
   int row0 = 0;                     // first row of this rank's records (rank * per_rank)
   int stride = 0;                   // entries per row of the gathered arrays
   int multicast = 0;                // destinations are NVLink multicast (NVLS) addresses: one store reaches every rank
+  int no_dist = 0;                  // publish index lists + counts only (what the reference calls return); distances stay local
   int32_t* match[ASDM_MAX_PEERS];   // [world * per_rank][stride]
   float* dist[ASDM_MAX_PEERS];
   int32_t* nm[ASDM_MAX_PEERS];      // [world * per_rank]

@@ -165,6 +165,7 @@ __device__ __forceinline__ void publish_row(const PublishArgs& pub, int pair, co
   const int t = threadIdx.x, nt = blockDim.x;
   const size_t row = (size_t)(pub.row0 + pair);
   const bool mc = pub.multicast != 0;
+  const bool wd = pub.no_dist == 0;
   const bool vec = (pub.stride & 3) == 0 && ((reinterpret_cast<uintptr_t>(matchp) | reinterpret_cast<uintptr_t>(distp)) & 15) == 0;
   if (vec) {
     const int n4 = pub.stride >> 2;
@@ -183,7 +184,7 @@ __device__ __forceinline__ void publish_row(const PublishArgs& pub, int pair, co
       const int4 di = make_int4(__float_as_int(d.x), __float_as_int(d.y), __float_as_int(d.z), __float_as_int(d.w));
       for (int p = 0; p < pub.n; p++) {
         pub_store4(pub.match[p] + row * pub.stride + e, m, mc);
-        pub_store4(pub.dist[p] + row * pub.stride + e, di, mc);
+        if (wd) pub_store4(pub.dist[p] + row * pub.stride + e, di, mc);
       }
     }
   } else {
@@ -192,7 +193,7 @@ __device__ __forceinline__ void publish_row(const PublishArgs& pub, int pair, co
       const float d = k < out_n ? distp[k] : -1.f;
       for (int p = 0; p < pub.n; p++) {
         pub_store1(pub.match[p] + row * pub.stride + k, m, mc);
-        pub_store1(pub.dist[p] + row * pub.stride + k, __float_as_int(d), mc);
+        if (wd) pub_store1(pub.dist[p] + row * pub.stride + k, __float_as_int(d), mc);
       }
     }
   }

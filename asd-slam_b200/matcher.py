@@ -14,7 +14,8 @@ import numpy as np
 
 from . import _lib
 from ._lib import (ASDM_JOB_BOW_KF_KF, ASDM_JOB_TRIANGULATION, ASDM_PROJ_BEST_ONLY, ASDM_PROJ_RATIO_LEVEL, KP_DTYPE,
-                   PROJ_QUERY_DTYPE, TH_HIGH, TH_LOW, AsdmError, FeatVec, Grid, JobDesc, ProjParams, SetDesc, VocabDesc, ptr)
+                   PROJ_QUERY_DTYPE, TH_HIGH, TH_LOW, AsdmError, BowdbGates, FeatVec, Grid, JobDesc, ProjParams, SetDesc, VocabDesc,
+                   ptr)
 
 
 def _f32(a):
@@ -275,14 +276,15 @@ class PairJob:
         self.ctx.check(self.ctx.lib.asdm_job_device_outputs(self.h, C.byref(m), C.byref(d), C.byref(n)))
         return m.value, d.value, n.value
 
-    def set_publish(self, match_ptrs, dist_ptrs, nm_ptrs, row0, stride, multicast=False):
+    def set_publish(self, match_ptrs, dist_ptrs, nm_ptrs, row0, stride, multicast=False, dist=True):
         """The job's resolve kernel also stores every finished row into these rank-major gathered arrays (device
         pointers: this GPU's and its peers', or one NVSwitch multicast mapping of them all -- see
-        shard.GatheredResults); an empty list switches it off."""
+        shard.GatheredResults); an empty list switches it off. dist=False publishes index lists and counts only (the
+        reference's calls return no distances); the distance rows then stay in the job's local outputs."""
         n = len(match_ptrs)
         arr = lambda ps: (C.c_void_p * max(n, 1))(*ps)
         self.ctx.check(self.ctx.lib.asdm_job_set_publish(self.h, n, arr(match_ptrs), arr(dist_ptrs), arr(nm_ptrs), row0, stride,
-                                                         1 if multicast else 0))
+                                                         (1 if multicast else 0) | (0 if dist else 2)))
 
     def destroy(self):
         if self.h:
@@ -549,4 +551,85 @@ class ORBVocabulary:
     def release(self):
         if self.h:
             self.ctx.lib.asdm_vocab_release(self.h)
+            self.h = None
+
+
+class KeyFrameDatabase:
+    """ORB_SLAM2::KeyFrameDatabase (reference src/vslam/include/KeyFrameDatabase.h:40-62, KeyFrameDatabase.cc:34-320) with
+    the BowVectors of all keyframes resident on the device. Keyframes are named by slot = the value add() returns (add
+    order = their order inside the reference's inverted lists). BowVectors are (ascending word ids, values) arrays."""
+
+    def __init__(self, ctx):
+        self.ctx = ctx
+        h = C.c_void_p()
+        ctx.check(ctx.lib.asdm_bowdb_create(ctx.h, C.byref(h)))
+        self.h = h
+
+    def __len__(self):
+        return int(self.ctx.lib.asdm_bowdb_size(self.h))
+
+    @staticmethod
+    def _bow(word, val):
+        return np.ascontiguousarray(word, np.uint32), np.ascontiguousarray(val, np.float64)
+
+    def add(self, word, val):
+        """KeyFrameDatabase::add(pKF) (:41-47); returns the keyframe's slot."""
+        w, v = self._bow(word, val)
+        slot = C.c_int32(-1)
+        self.ctx.check(self.ctx.lib.asdm_bowdb_add(self.h, ptr(w), ptr(v), len(w), C.byref(slot)))
+        return slot.value
+
+    def erase(self, slot):
+        """KeyFrameDatabase::erase(pKF) (:49-70)."""
+        self.ctx.check(self.ctx.lib.asdm_bowdb_erase(self.h, int(slot)))
+
+    def clear(self):
+        """KeyFrameDatabase::clear() (:72-76)."""
+        self.ctx.check(self.ctx.lib.asdm_bowdb_clear(self.h))
+
+    def query(self, word, val):
+        """The device pass alone: (common words, smallest common word, L1 score as float) for every slot."""
+        w, v = self._bow(word, val)
+        n = len(self)
+        common, first, score = np.zeros(n, np.int32), np.zeros(n, np.uint32), np.zeros(n, np.float32)
+        self.ctx.check(self.ctx.lib.asdm_bowdb_query(self.h, ptr(w), ptr(v), len(w), ptr(common), ptr(first), ptr(score)))
+        return common, first, score
+
+    def _detect(self, fn, word, val, connected, global_flag, neigh_off, neigh_slot, min_score, only_global_map):
+        w, v = self._bow(word, val)
+        n = len(self)
+        keep = [None if a is None else np.ascontiguousarray(a, dt) for a, dt in
+                ((connected, np.uint8), (global_flag, np.uint8), (neigh_off, np.int32), (neigh_slot, np.int32))]
+        for a, want in zip(keep[:3], (n, n, n + 1)):
+            if a is not None and len(a) != want:
+                raise ValueError("gate arrays must cover every slot of the database")
+        g = BowdbGates(ptr(keep[0]), ptr(keep[1]), ptr(keep[2]), ptr(keep[3]), float(min_score), int(bool(only_global_map)))
+        out = np.empty(max(n, 1), np.int32)
+        k = C.c_int32(0)
+        self.ctx.check(fn(self.h, ptr(w), ptr(v), len(w), C.byref(g), ptr(out), n, C.byref(k)))
+        return out[:k.value].copy()
+
+    def DetectLoopCandidates(self, word, val, connected, min_score, only_global_map=False, global_flag=None,
+                             neigh_off=None, neigh_slot=None):
+        """DetectLoopCandidates(pKF, minScore, only_global_map) (:80-216): word/val = pKF->mBowVec, connected[slot] =
+        membership in pKF->GetConnectedKeyFrames(), neigh_* = CSR of GetBestCovisibilityKeyFrames(10) per slot.
+        Returns the candidate slots in the reference's order."""
+        return self._detect(self.ctx.lib.asdm_bowdb_detect_loop, word, val, connected, global_flag, neigh_off, neigh_slot,
+                            min_score, only_global_map)
+
+    def DetectRelocalizationCandidates(self, word, val, only_global_map=False, global_flag=None, neigh_off=None,
+                                       neigh_slot=None):
+        """DetectRelocalizationCandidates(F, only_global_map) (:219-320); word/val = F->mBowVec."""
+        return self._detect(self.ctx.lib.asdm_bowdb_detect_reloc, word, val, None, global_flag, neigh_off, neigh_slot, 0.0,
+                            only_global_map)
+
+    def reloc_scores(self):
+        """KeyFrame::mRelocScore of every slot as the queries so far left it."""
+        s = np.zeros(len(self), np.float32)
+        self.ctx.check(self.ctx.lib.asdm_bowdb_reloc_scores(self.h, ptr(s)))
+        return s
+
+    def release(self):
+        if self.h:
+            self.ctx.lib.asdm_bowdb_release(self.h)
             self.h = None

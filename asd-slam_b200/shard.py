@@ -276,7 +276,7 @@ class ShardedPairJob:
 
     def __init__(self, ctx, kind, sets, masks, ia, ib, nnratio=0.6, check_ori=True, F12=None, epipoles=None,
                  scale_factors=None, level_sigma2=None, rank=0, world=1, group=None, blocks_per_pair=1, gathered=None,
-                 chunks=1):
+                 chunks=1, publish_dist=True):
         """gathered: a GatheredResults of matching shape -- the job then publishes its rows into every rank's arrays
         from its own resolve kernel (in `chunks` sub-jobs, see below) and gather() is a barrier; None: NCCL / gloo
         all-gathers of the local outputs."""
@@ -287,6 +287,7 @@ class ShardedPairJob:
         if blocks_per_pair > 1 and (kind != ASDM_JOB_TRIANGULATION or check_ori):
             raise ValueError("row-block units need a triangulation job without rotation check")
         self.ctx, self.rank, self.world, self.group = ctx, rank, world, group
+        self.publish_dist = bool(publish_dist)  # False: only index lists + counts cross NVLink (g_dist rows are stale)
         set_n = np.array([s.n for s in sets], np.int64)
         self.shards = PairShards(set_n[ia], world, blocks_per_pair)
         mine = self.shards.local_units(rank)
@@ -341,7 +342,8 @@ class ShardedPairJob:
             pm, pd_, pn = g.ptrs(gen)
         for jb, r0 in zip(self.jobs, self.chunk_row0):
             if g is not None and self.n_local:
-                jb.set_publish(pm, pd_, pn, self.rank * g.per_rank + r0, g.stride, multicast=g.transport == "multicast")
+                jb.set_publish(pm, pd_, pn, self.rank * g.per_rank + r0, g.stride, multicast=g.transport == "multicast",
+                               dist=self.publish_dist)
             jb.run()
             self.launches += self.ctx.stat("gpu_launches")
 

@@ -427,3 +427,52 @@ def vocab_queries(tree, n, seed_extra=0, sigma=0.05):
     d = tree["desc"][rng.choice(leaves, n)] + rng.standard_normal((n, DESC_DIM)).astype(np.float32) * np.float32(sigma)
     d /= np.sqrt((d * d).sum(axis=1, keepdims=True, dtype=np.float32))
     return np.ascontiguousarray(d, np.float32)
+
+
+def config_kfdb(n_kf=300, n_words=100000, words_per_kf=900, n_places=60, seed_extra=0, erase_frac=0.05, global_frac=0.7):
+    """A keyframe database for KeyFrameDatabase::DetectLoopCandidates / DetectRelocalizationCandidates
+    (KeyFrameDatabase.cc:80-320): a trajectory that visits `n_places` places (consecutive keyframes share a place's
+    word distribution, the end of the trajectory revisits the start), BowVectors = ascending word ids with
+    L1-normalised tf-idf-like doubles, GetBestCovisibilityKeyFrames(10) = the nearest keyframes along the trajectory,
+    a few erased keyframes, a global-map flag, and queries (BowVector + connected set) taken near the revisit."""
+    rng = rng_for(9, seed_extra)
+    per_place = max(1, n_kf // n_places)
+    place_words = [rng.choice(n_words, size=3 * words_per_kf, replace=False) for _ in range(n_places)]
+    common_pool = rng.choice(n_words, size=words_per_kf, replace=False)  # stop-word-like: seen everywhere
+
+    def bow(place):
+        k = int(words_per_kf * rng.uniform(0.7, 1.0))
+        w = np.concatenate([rng.choice(place_words[place], size=int(0.7 * k), replace=False),
+                            rng.choice(common_pool, size=int(0.2 * k), replace=False),
+                            rng.integers(0, n_words, size=k - int(0.7 * k) - int(0.2 * k))])
+        w = np.unique(w).astype(np.uint32)
+        v = rng.gamma(2.0, 1.0, size=len(w))
+        v = v / v.sum()  # L1 norm (BowVector::normalize); the exact values are arbitrary doubles
+        return w, v.astype(np.float64)
+
+    place_of = np.minimum(np.arange(n_kf) // per_place, n_places - 1)
+    place_of[-2 * per_place:] = place_of[:2 * per_place]  # the loop: the trajectory ends where it began
+    bows = [bow(int(p)) for p in place_of]
+    off = np.zeros(n_kf + 1, np.int32)
+    off[1:] = np.cumsum([len(w) for w, _ in bows])
+    word = np.concatenate([w for w, _ in bows]).astype(np.uint32)
+    val = np.concatenate([v for _, v in bows]).astype(np.float64)
+    alive = (rng.uniform(size=n_kf) >= erase_frac).astype(np.uint8)
+    glob = (rng.uniform(size=n_kf) < global_frac).astype(np.uint8)
+    neigh_off = np.zeros(n_kf + 1, np.int32)
+    neigh = []
+    for s in range(n_kf):
+        cand = [s + d for d in (1, -1, 2, -2, 3, -3, 4, -4, 5, -5, 6, -6) if 0 <= s + d < n_kf]
+        k = int(rng.integers(0, 11))
+        neigh.extend(cand[:k])
+        neigh_off[s + 1] = len(neigh)
+    neigh = np.asarray(neigh, np.int32)
+    queries = []
+    for qi in range(6):
+        src = n_kf - 1 - qi * 3  # a keyframe at the end of the trajectory looks for the beginning
+        qw, qv = bow(int(place_of[src]))
+        conn = np.zeros(n_kf, np.uint8)
+        conn[max(0, src - 15):] = 1  # its covisibility neighbourhood: never a loop candidate
+        queries.append(dict(word=qw, val=qv, connected=conn, min_score=float(rng.uniform(0.005, 0.05))))
+    return dict(n_kf=n_kf, n_words=n_words, bow_off=off, bow_word=word, bow_val=val, alive=alive, global_flag=glob,
+                neigh_off=neigh_off, neigh_slot=neigh, queries=queries)

@@ -297,6 +297,8 @@ int asdm_shared_free(asdm_ctx* ctx, void* dptr);  /* a pointer from asdm_shared_
  * called between runs (e.g. to alternate between two generations of arrays). */
 #define ASDM_PUBLISH_MULTICAST 1 /* the destinations are NVSwitch multicast mappings (e.g. torch symmetric memory's
                                   * multicast_ptr + offset): one store reaches every rank bound to them, n_ranks = 1 */
+#define ASDM_PUBLISH_NO_DIST 2   /* publish match indices + counts only -- what the reference's calls return (vpMatches12,
+                                  * vMatchedPairs); the distance rows stay in the job's local outputs */
 int asdm_job_set_publish(asdm_job* job, int n_ranks, void* const* match, void* const* dist, void* const* nmatches,
                          int row0, int stride, int flags);
 
@@ -343,6 +345,45 @@ int asdm_vocab_release(asdm_vocab* voc);
  * Any output pointer may be NULL. An empty vocabulary cannot be created, so the early return of :1132 does not arise. */
 int asdm_vocab_transform(asdm_ctx* ctx, asdm_vocab* voc, asdm_set* set, int levelsup, int32_t* word_id,
                          int32_t* node_id, uint8_t* in_fv, int32_t* bow_n, uint32_t* bow_id, double* bow_val);
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * Keyframe database: BoW candidate detection -- replaces ORB_SLAM2::KeyFrameDatabase (reference
+ * src/vslam/include/KeyFrameDatabase.h:40-62, src/vslam/src/KeyFrameDatabase.cc:34-320) with the L1 scoring of the
+ * vocabulary (DBoW2::L1Scoring::score, src/dbow2/DBoW2/ScoringObject.cpp:24-61). The BowVectors of all keyframes stay
+ * resident on the device; one kernel counts the common words and scores every keyframe against the query
+ * (k_bowdb_query), the list logic of the reference (gates, covisibility-group accumulation, order) is finished on the
+ * host inside the call. Keyframes are named by SLOT = the order of asdm_bowdb_add (= their order inside every inverted
+ * list of the reference); slots are never reused.
+ * ------------------------------------------------------------------------------------------------------------------ */
+typedef struct asdm_bowdb asdm_bowdb;
+int asdm_bowdb_create(asdm_ctx* ctx, asdm_bowdb** out);                  /* KeyFrameDatabase(voc) :34-38 */
+int asdm_bowdb_release(asdm_bowdb* db);
+/* KeyFrameDatabase::add (:41-47): word ids ascending (std::map order) with their values; *slot receives the new slot */
+int asdm_bowdb_add(asdm_bowdb* db, const uint32_t* word_id, const double* value, int n_words, int32_t* slot);
+int asdm_bowdb_erase(asdm_bowdb* db, int32_t slot);                       /* KeyFrameDatabase::erase :49-70 */
+int asdm_bowdb_clear(asdm_bowdb* db);                                     /* KeyFrameDatabase::clear :72-76 */
+int asdm_bowdb_size(asdm_bowdb* db);                                      /* slots handed out so far (erased included) */
+/* The device pass alone: for every slot the number of words shared with the query, the smallest shared word
+ * (0xffffffff if none) and the L1 score as the reference's float. Arrays of asdm_bowdb_size entries; erased slots: 0. */
+int asdm_bowdb_query(asdm_bowdb* db, const uint32_t* word_id, const double* value, int n_words, int32_t* common,
+                     uint32_t* first_word, float* score);
+typedef struct {
+  const uint8_t* connected;   /* [size] pKF->GetConnectedKeyFrames() membership (loop detection only), may be NULL */
+  const uint8_t* global_flag; /* [size] KeyFrame::GetGlobalMapFlag(), may be NULL when only_global_map == 0 */
+  const int32_t* neigh_off;   /* [size + 1] CSR of GetBestCovisibilityKeyFrames(10) per slot, may be NULL (no neighbours) */
+  const int32_t* neigh_slot;
+  float min_score;            /* loop detection: minScore */
+  int32_t only_global_map;
+} asdm_bowdb_gates;
+/* KeyFrameDatabase::DetectLoopCandidates(pKF, minScore, only_global_map) :80-216. out: candidate slots in the
+ * reference's order; ASDM_ERR_INVALID if more than cap. */
+int asdm_bowdb_detect_loop(asdm_bowdb* db, const uint32_t* word_id, const double* value, int n_words,
+                           const asdm_bowdb_gates* gates, int32_t* out, int cap, int32_t* n_out);
+/* KeyFrameDatabase::DetectRelocalizationCandidates(F, only_global_map) :219-320. The keyframes' mRelocScore persists
+ * between calls as in the reference (it starts at 0 here; the reference leaves it uninitialised, KeyFrame.cc:150). */
+int asdm_bowdb_detect_reloc(asdm_bowdb* db, const uint32_t* word_id, const double* value, int n_words,
+                            const asdm_bowdb_gates* gates, int32_t* out, int cap, int32_t* n_out);
+int asdm_bowdb_reloc_scores(asdm_bowdb* db, float* score);               /* [size] the persistent mRelocScore values */
 
 #ifdef __cplusplus
 }

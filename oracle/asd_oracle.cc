@@ -832,6 +832,193 @@ int ora_map_read_block(const uint8_t* block, long bytes, float* rows, int cap_ro
   return c;
 }
 
+// ============================================================================ KeyFrameDatabase (BoW candidates)
+// DBoW2::L1Scoring::score, ScoringObject.cpp:24-61. lower_bound on a sorted array == std::map::lower_bound.
+double ora_bow_score_l1(const uint32_t* w1, const double* v1, int n1, const uint32_t* w2, const double* v2, int n2) {
+  int i = 0, j = 0;
+  double score = 0;
+  while (i < n1 && j < n2) {
+    const double vi = v1[i], wi = v2[j];
+    if (w1[i] == w2[j]) {
+      score += fabs(vi - wi) - fabs(vi) - fabs(wi);  // :41
+      ++i;
+      ++j;
+    } else if (w1[i] < w2[j]) {
+      i = (int)(std::lower_bound(w1 + i, w1 + n1, w2[j]) - w1);  // :48
+    } else {
+      j = (int)(std::lower_bound(w2 + j, w2 + n2, w1[i]) - w2);  // :52
+    }
+  }
+  score = -score / 2.0;  // :56
+  return score;
+}
+
+namespace {
+// the inverted file as KeyFrameDatabase::add builds it (:41-47): word -> keyframes in add order, erased ones absent
+std::map<uint32_t, std::vector<int> > inverted_file(int n_kf, const int32_t* bow_off, const uint32_t* bow_word,
+                                                    const uint8_t* alive) {
+  std::map<uint32_t, std::vector<int> > inv;
+  for (int s = 0; s < n_kf; s++) {
+    if (alive && !alive[s]) continue;
+    for (int e = bow_off[s]; e < bow_off[s + 1]; e++) inv[bow_word[e]].push_back(s);
+  }
+  return inv;
+}
+}  // namespace
+
+int ora_detect_loop_candidates(int n_kf, const int32_t* bow_off, const uint32_t* bow_word, const double* bow_val,
+                               const uint8_t* alive, const uint32_t* q_word, const double* q_val, int nq,
+                               const uint8_t* connected, const uint8_t* global_flag, const int32_t* neigh_off,
+                               const int32_t* neigh_slot, float min_score, int only_global_map, int32_t* out,
+                               int32_t* common, float* score) {
+  const std::map<uint32_t, std::vector<int> > inv = inverted_file(n_kf, bow_off, bow_word, alive);
+  std::vector<uint8_t> queried(n_kf, 0);  // mnLoopQuery == pKF->mnId
+  std::vector<int> words(n_kf, 0);        // mnLoopWords
+  std::vector<float> loop_score(n_kf, 0.f);
+  std::vector<int> sharing;               // lKFsSharingWords
+  for (int q = 0; q < nq; q++) {          // :93-113
+    std::map<uint32_t, std::vector<int> >::const_iterator it = inv.find(q_word[q]);
+    if (it == inv.end()) continue;
+    for (size_t k = 0; k < it->second.size(); k++) {
+      const int s = it->second[k];
+      if (!queried[s]) {
+        words[s] = 0;
+        if (!(connected && connected[s])) {
+          queried[s] = 1;
+          sharing.push_back(s);
+        }
+      }
+      words[s]++;
+    }
+  }
+  if (common)
+    for (int s = 0; s < n_kf; s++) common[s] = queried[s] ? words[s] : 0;
+  if (score)
+    for (int s = 0; s < n_kf; s++) score[s] = -1.f;
+  if (sharing.empty()) return 0;  // :114-115
+  int maxCommonWords = 0;         // :121-126
+  for (size_t k = 0; k < sharing.size(); k++)
+    if (words[sharing[k]] > maxCommonWords) maxCommonWords = words[sharing[k]];
+  const int minCommonWords = maxCommonWords * 0.6f;  // :128
+  std::vector<std::pair<float, int> > scoreAndMatch;
+  for (size_t k = 0; k < sharing.size(); k++) {  // :133-150
+    const int s = sharing[k];
+    if (words[s] > minCommonWords) {
+      const float si = (float)ora_bow_score_l1(q_word, q_val, nq, bow_word + bow_off[s], bow_val + bow_off[s],
+                                               bow_off[s + 1] - bow_off[s]);
+      loop_score[s] = si;
+      if (score) score[s] = si;
+      if (si >= min_score)
+        if ((only_global_map && global_flag && global_flag[s]) || !only_global_map) scoreAndMatch.push_back(std::make_pair(si, s));
+    }
+  }
+  if (scoreAndMatch.empty()) return 0;  // :151-152
+  std::vector<std::pair<float, int> > accScoreAndMatch;
+  float bestAccScore = min_score;  // :155
+  for (size_t k = 0; k < scoreAndMatch.size(); k++) {  // :156-181
+    const int s = scoreAndMatch[k].second;
+    float bestScore = scoreAndMatch[k].first;
+    float accScore = scoreAndMatch[k].first;
+    int best = s;
+    for (int e = neigh_off ? neigh_off[s] : 0; e < (neigh_off ? neigh_off[s + 1] : 0); e++) {
+      const int s2 = neigh_slot[e];
+      if (queried[s2] && words[s2] > minCommonWords) {  // :168
+        accScore += loop_score[s2];
+        if (loop_score[s2] > bestScore) {
+          best = s2;
+          bestScore = loop_score[s2];
+        }
+      }
+    }
+    accScoreAndMatch.push_back(std::make_pair(accScore, best));
+    if (accScore > bestAccScore) bestAccScore = accScore;
+  }
+  const float minScoreToRetain = 0.55f * bestAccScore;  // :184
+  std::vector<uint8_t> added(n_kf, 0);
+  int n_out = 0;
+  for (size_t k = 0; k < accScoreAndMatch.size(); k++)  // :189-200
+    if (accScoreAndMatch[k].first > minScoreToRetain) {
+      const int s = accScoreAndMatch[k].second;
+      if (!added[s]) {
+        out[n_out++] = s;
+        added[s] = 1;
+      }
+    }
+  return n_out;
+}
+
+int ora_detect_reloc_candidates(int n_kf, const int32_t* bow_off, const uint32_t* bow_word, const double* bow_val,
+                                const uint8_t* alive, const uint32_t* q_word, const double* q_val, int nq,
+                                const uint8_t* global_flag, const int32_t* neigh_off, const int32_t* neigh_slot,
+                                int only_global_map, float* reloc_score, int32_t* out, int32_t* common) {
+  const std::map<uint32_t, std::vector<int> > inv = inverted_file(n_kf, bow_off, bow_word, alive);
+  std::vector<uint8_t> queried(n_kf, 0);  // mnRelocQuery == F->mnId
+  std::vector<int> words(n_kf, 0);        // mnRelocWords
+  std::vector<int> sharing;
+  for (int q = 0; q < nq; q++) {  // :226-243
+    std::map<uint32_t, std::vector<int> >::const_iterator it = inv.find(q_word[q]);
+    if (it == inv.end()) continue;
+    for (size_t k = 0; k < it->second.size(); k++) {
+      const int s = it->second[k];
+      if (!queried[s]) {
+        words[s] = 0;
+        queried[s] = 1;
+        if ((only_global_map && global_flag && global_flag[s]) || !only_global_map) sharing.push_back(s);
+      }
+      words[s]++;
+    }
+  }
+  if (common)
+    for (int s = 0; s < n_kf; s++) common[s] = words[s];
+  if (sharing.empty()) return 0;
+  int maxCommonWords = 0;  // :249-254
+  for (size_t k = 0; k < sharing.size(); k++)
+    if (words[sharing[k]] > maxCommonWords) maxCommonWords = words[sharing[k]];
+  const int minCommonWords = maxCommonWords * 0.8f;  // :256
+  std::vector<std::pair<float, int> > scoreAndMatch;
+  for (size_t k = 0; k < sharing.size(); k++) {  // :262-274
+    const int s = sharing[k];
+    if (words[s] > minCommonWords) {
+      const float si = (float)ora_bow_score_l1(q_word, q_val, nq, bow_word + bow_off[s], bow_val + bow_off[s],
+                                               bow_off[s + 1] - bow_off[s]);
+      reloc_score[s] = si;
+      scoreAndMatch.push_back(std::make_pair(si, s));
+    }
+  }
+  if (scoreAndMatch.empty()) return 0;
+  std::vector<std::pair<float, int> > accScoreAndMatch;
+  float bestAccScore = 0;  // :280
+  for (size_t k = 0; k < scoreAndMatch.size(); k++) {  // :282-303
+    const int s = scoreAndMatch[k].second;
+    float bestScore = scoreAndMatch[k].first;
+    float accScore = bestScore;
+    int best = s;
+    for (int e = neigh_off ? neigh_off[s] : 0; e < (neigh_off ? neigh_off[s + 1] : 0); e++) {
+      const int s2 = neigh_slot[e];
+      if (!queried[s2]) continue;    // :291-292
+      accScore += reloc_score[s2];   // :294 -- whatever score the neighbour last received
+      if (reloc_score[s2] > bestScore) {
+        best = s2;
+        bestScore = reloc_score[s2];
+      }
+    }
+    accScoreAndMatch.push_back(std::make_pair(accScore, best));
+    if (accScore > bestAccScore) bestAccScore = accScore;
+  }
+  const float minScoreToRetain = 0.75f * bestAccScore;  // :305
+  std::vector<uint8_t> added(n_kf, 0);
+  int n_out = 0;
+  for (size_t k = 0; k < accScoreAndMatch.size(); k++)
+    if (accScoreAndMatch[k].first > minScoreToRetain) {
+      const int s = accScoreAndMatch[k].second;
+      if (!added[s]) {
+        out[n_out++] = s;
+        added[s] = 1;
+      }
+    }
+  return n_out;
+}
+
 int ora_max_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();

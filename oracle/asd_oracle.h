@@ -213,6 +213,34 @@ int ora_voc_transform(int L, int weighting, int scoring, int n_nodes, const int3
 long ora_map_write_block(const float* desc, int n, int d, uint8_t* out);
 int ora_map_read_block(const uint8_t* block, long bytes, float* rows, int cap_rows, int* width);
 
+/* ---- KeyFrameDatabase: BoW candidate detection, the caller that produces the loop-closure sweep's candidate pairs ----
+ * The database is given flat, in KeyFrameDatabase::add order (KeyFrameDatabase.cc:41-47): keyframe slot s owns the
+ * BowVector entries [bow_off[s], bow_off[s+1]) (ascending word id, as std::map iterates); alive[s] = 0 after
+ * KeyFrameDatabase::erase (:49-70).  Every inverted list holds its keyframes in add order.
+ * ora_bow_score_l1: DBoW2::L1Scoring::score (src/dbow2/DBoW2/ScoringObject.cpp:24-61): merge of the two vectors,
+ * score += fabs(vi - wi) - fabs(vi) - fabs(wi) over the common words in ascending word order, result -score / 2. */
+double ora_bow_score_l1(const uint32_t* w1, const double* v1, int n1, const uint32_t* w2, const double* v2, int n2);
+
+/* KeyFrameDatabase::DetectLoopCandidates (KeyFrameDatabase.cc:80-216): walk of the inverted file over the query's words
+ * (:93-113; connected keyframes never enter the list), maxCommonWords (:121-126), minCommonWords = max * 0.6f (:128),
+ * L1 scores of the keyframes above it and the minScore / only_global_map gates (:133-150), accumulation over
+ * GetBestCovisibilityKeyFrames(10) (neigh_off / neigh_slot, CSR per slot) in float (:156-181), 0.55f * best (:184),
+ * unique best keyframes in list order (:189-200).  common / score (may be NULL) receive mnLoopWords / mLoopScore of every
+ * listed keyframe (score only where it was computed; others -1).  Returns the number of candidates written to out. */
+int ora_detect_loop_candidates(int n_kf, const int32_t* bow_off, const uint32_t* bow_word, const double* bow_val,
+                               const uint8_t* alive, const uint32_t* q_word, const double* q_val, int nq,
+                               const uint8_t* connected, const uint8_t* global_flag, const int32_t* neigh_off,
+                               const int32_t* neigh_slot, float min_score, int only_global_map, int32_t* out,
+                               int32_t* common, float* score);
+/* KeyFrameDatabase::DetectRelocalizationCandidates (:219-320): 0.8f common-word gate (:253), no minScore, bestAccScore
+ * from 0 (:276), 0.75f (:303).  The neighbour accumulation (:286-296) reads mRelocScore of EVERY neighbour that shares a
+ * word with the frame, scored in this query or not: reloc_score[n_kf] is that persistent member (in/out; the reference
+ * leaves it uninitialised at construction, KeyFrame.cc:150 -- this restatement starts it at what the caller passes). */
+int ora_detect_reloc_candidates(int n_kf, const int32_t* bow_off, const uint32_t* bow_word, const double* bow_val,
+                                const uint8_t* alive, const uint32_t* q_word, const double* q_val, int nq,
+                                const uint8_t* global_flag, const int32_t* neigh_off, const int32_t* neigh_slot,
+                                int only_global_map, float* reloc_score, int32_t* out, int32_t* common);
+
 int ora_max_threads(void);
 
 #ifdef __cplusplus

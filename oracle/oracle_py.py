@@ -341,3 +341,56 @@ def map_read_block(block):
     rows = np.empty((n, w.value), np.float32)
     f(_p(block), C.c_long(len(block)), _p(rows), C.c_int(n), C.byref(w))
     return rows
+
+
+def _db_args(db):
+    return (C.c_int(int(db["n_kf"])), _p(np.ascontiguousarray(db["bow_off"], np.int32)),
+            _p(np.ascontiguousarray(db["bow_word"], np.uint32)), _p(np.ascontiguousarray(db["bow_val"], np.float64)),
+            _p(np.ascontiguousarray(db["alive"], np.uint8)))
+
+
+def bow_score_l1(w1, v1, w2, v2, _lib=None):
+    """DBoW2::L1Scoring::score (ScoringObject.cpp:24-61) of two BowVectors given as ascending (word, value) arrays."""
+    w1, w2 = np.ascontiguousarray(w1, np.uint32), np.ascontiguousarray(w2, np.uint32)
+    v1, v2 = np.ascontiguousarray(v1, np.float64), np.ascontiguousarray(v2, np.float64)
+    f = (_lib or lib()).ora_bow_score_l1 if _lib is None else _lib.ref_bow_score_l1
+    f.restype = C.c_double
+    return float(f(_p(w1), _p(v1), C.c_int(len(w1)), _p(w2), _p(v2), C.c_int(len(w2))))
+
+
+def detect_loop_candidates(db, q_word, q_val, connected, min_score, only_global_map=False, _ref=None):
+    """KeyFrameDatabase::DetectLoopCandidates (KeyFrameDatabase.cc:80-216) over the flat database `db`
+    (synth.config_kfdb keys).  Returns (candidate slots in the reference's order, mnLoopWords, mLoopScore)."""
+    n = int(db["n_kf"])
+    qw, qv = np.ascontiguousarray(q_word, np.uint32), np.ascontiguousarray(q_val, np.float64)
+    conn, glob = np.ascontiguousarray(connected, np.uint8), np.ascontiguousarray(db["global_flag"], np.uint8)
+    no, ns = np.ascontiguousarray(db["neigh_off"], np.int32), np.ascontiguousarray(db["neigh_slot"], np.int32)
+    out, common, score = np.empty(max(n, 1), np.int32), np.empty(max(n, 1), np.int32), np.empty(max(n, 1), np.float32)
+    tail = (_p(out), _p(common), _p(score))
+    if _ref is None:
+        k = lib().ora_detect_loop_candidates(*_db_args(db), _p(qw), _p(qv), C.c_int(len(qw)), _p(conn), _p(glob), _p(no), _p(ns),
+                                             C.c_float(min_score), C.c_int(int(only_global_map)), *tail)
+    else:
+        k = _ref.ref_detect_loop_candidates(*_db_args(db), _p(qw), _p(qv), C.c_int(len(qw)), _p(conn), _p(glob), _p(no), _p(ns),
+                                            C.c_float(min_score), C.c_int(int(only_global_map)), C.c_uint(int(db["n_words"])),
+                                            *tail)
+    return out[:k].copy(), common[:n], score[:n]
+
+
+def detect_reloc_candidates(db, q_word, q_val, reloc_score, only_global_map=False, _ref=None):
+    """KeyFrameDatabase::DetectRelocalizationCandidates (KeyFrameDatabase.cc:219-320). reloc_score: the keyframes'
+    persistent mRelocScore (float32 [n_kf], updated in place).  Returns (candidate slots, mnRelocWords)."""
+    n = int(db["n_kf"])
+    assert reloc_score.dtype == np.float32 and reloc_score.flags["C_CONTIGUOUS"] and len(reloc_score) == n
+    qw, qv = np.ascontiguousarray(q_word, np.uint32), np.ascontiguousarray(q_val, np.float64)
+    glob = np.ascontiguousarray(db["global_flag"], np.uint8)
+    no, ns = np.ascontiguousarray(db["neigh_off"], np.int32), np.ascontiguousarray(db["neigh_slot"], np.int32)
+    out, common = np.empty(max(n, 1), np.int32), np.empty(max(n, 1), np.int32)
+    if _ref is None:
+        k = lib().ora_detect_reloc_candidates(*_db_args(db), _p(qw), _p(qv), C.c_int(len(qw)), _p(glob), _p(no), _p(ns),
+                                              C.c_int(int(only_global_map)), _p(reloc_score), _p(out), _p(common))
+    else:
+        k = _ref.ref_detect_reloc_candidates(*_db_args(db), _p(qw), _p(qv), C.c_int(len(qw)), _p(glob), _p(no), _p(ns),
+                                             C.c_int(int(only_global_map)), C.c_uint(int(db["n_words"])), _p(reloc_score),
+                                             _p(out), _p(common))
+    return out[:k].copy(), common[:n]

@@ -342,3 +342,36 @@ def map_read_block(path, cap_rows):
     dims = np.zeros(2, np.int32)
     n = m.ref_map_read_block(path.encode(), _p(rows), cap_rows, _p(dims))
     return rows[:n], dims
+
+
+# ---------------------------------------------------------------- KeyFrameDatabase.cc (oracle/_ref/libref_kfdb.so)
+_KLIB = os.path.join(_HERE, "_ref", "libref_kfdb.so")
+_klib = None
+
+
+def kfdb_available():
+    return os.path.exists(_KLIB) or (build() and os.path.exists(_KLIB))
+
+
+def klib():
+    global _klib
+    if _klib is None:
+        if not kfdb_available():
+            raise RuntimeError("oracle/_ref/libref_kfdb.so is missing and /root/reference is not mounted")
+        _klib = C.CDLL(_KLIB)
+    return _klib
+
+
+def bow_score_l1(w1, v1, w2, v2):
+    import oracle_py
+    return oracle_py.bow_score_l1(w1, v1, w2, v2, _lib=klib())
+
+
+def detect_loop_candidates(db, q_word, q_val, connected, min_score, only_global_map=False):
+    import oracle_py
+    return oracle_py.detect_loop_candidates(db, q_word, q_val, connected, min_score, only_global_map, _ref=klib())
+
+
+def detect_reloc_candidates(db, q_word, q_val, reloc_score, only_global_map=False):
+    import oracle_py
+    return oracle_py.detect_reloc_candidates(db, q_word, q_val, reloc_score, only_global_map, _ref=klib())
