@@ -40,6 +40,7 @@ EXPORTS = [
     "asdm_vocab_create", "asdm_vocab_release", "asdm_vocab_transform",
     "asdm_bowdb_create", "asdm_bowdb_release", "asdm_bowdb_add", "asdm_bowdb_erase", "asdm_bowdb_clear", "asdm_bowdb_size",
     "asdm_bowdb_query", "asdm_bowdb_detect_loop", "asdm_bowdb_detect_reloc", "asdm_bowdb_reloc_scores",
+    "asdm_bowdb_detect_loop_full", "asdm_bowdb_detect_reloc_full", "asdm_bowdb_set_reloc_scores",
 ]
 
 
@@ -160,6 +161,9 @@ def load():
     lib.asdm_bowdb_detect_loop.argtypes = [vp, vp, vp, C.c_int, C.POINTER(BowdbGates), vp, C.c_int, C.POINTER(i32)]
     lib.asdm_bowdb_detect_reloc.argtypes = [vp, vp, vp, C.c_int, C.POINTER(BowdbGates), vp, C.c_int, C.POINTER(i32)]
     lib.asdm_bowdb_reloc_scores.argtypes = [vp, vp]
+    lib.asdm_bowdb_set_reloc_scores.argtypes = [vp, vp]
+    lib.asdm_bowdb_detect_loop_full.argtypes = [vp, vp, vp, C.c_int, C.POINTER(BowdbGates), vp, C.c_int, C.POINTER(i32), vp, vp, vp]
+    lib.asdm_bowdb_detect_reloc_full.argtypes = [vp, vp, vp, C.c_int, C.POINTER(BowdbGates), vp, C.c_int, C.POINTER(i32), vp, vp, vp]
     _lib = lib
     return lib
 

@@ -2323,7 +2323,8 @@ static void bowdb_sharing_list(const asdm_bowdb* db, const int32_t* common, cons
 }
 
 static int bowdb_detect(asdm_bowdb* db, bool reloc, const uint32_t* word_id, const double* value, int n,
-                        const asdm_bowdb_gates* g, int32_t* out, int cap, int32_t* n_out) {
+                        const asdm_bowdb_gates* g, int32_t* out, int cap, int32_t* n_out, int32_t* common_out = nullptr,
+                        uint32_t* first_out = nullptr, float* score_out = nullptr) {
   if (!db || !g || !n_out || n < 0 || (n > 0 && (!word_id || !value)) || cap < 0 || (cap > 0 && !out)) return ASDM_ERR_INVALID;
   asdm_ctx* ctx = db->ctx;
   std::lock_guard<std::recursive_mutex> lk(ctx->mu);
@@ -2344,6 +2345,9 @@ static int bowdb_detect(asdm_bowdb* db, bool reloc, const uint32_t* word_id, con
   const float* score;
   int rc;
   if ((rc = bowdb_run(db, word_id, value, n, &common, &first_word, &score))) return rc;
+  if (common_out) memcpy(common_out, common, (size_t)ns * 4);
+  if (first_out) memcpy(first_out, first_word, (size_t)ns * 4);
+  if (score_out) memcpy(score_out, score, (size_t)ns * 4);
   const uint8_t* glob = g->only_global_map ? g->global_flag : nullptr;
   std::vector<int32_t> sharing;
   // loop: connected keyframes never enter the list (:104); relocalisation: the global-map gate sits on the list (:236)
@@ -2417,6 +2421,25 @@ extern "C" int asdm_bowdb_detect_loop(asdm_bowdb* db, const uint32_t* word_id, c
 extern "C" int asdm_bowdb_detect_reloc(asdm_bowdb* db, const uint32_t* word_id, const double* value, int n,
                                        const asdm_bowdb_gates* g, int32_t* out, int cap, int32_t* n_out) {
   return bowdb_detect(db, true, word_id, value, n, g, out, cap, n_out);
+}
+
+extern "C" int asdm_bowdb_detect_loop_full(asdm_bowdb* db, const uint32_t* word_id, const double* value, int n,
+                                           const asdm_bowdb_gates* g, int32_t* out, int cap, int32_t* n_out,
+                                           int32_t* common, uint32_t* first_word, float* score) {
+  return bowdb_detect(db, false, word_id, value, n, g, out, cap, n_out, common, first_word, score);
+}
+
+extern "C" int asdm_bowdb_detect_reloc_full(asdm_bowdb* db, const uint32_t* word_id, const double* value, int n,
+                                            const asdm_bowdb_gates* g, int32_t* out, int cap, int32_t* n_out,
+                                            int32_t* common, uint32_t* first_word, float* score) {
+  return bowdb_detect(db, true, word_id, value, n, g, out, cap, n_out, common, first_word, score);
+}
+
+extern "C" int asdm_bowdb_set_reloc_scores(asdm_bowdb* db, const float* score) {
+  if (!db || (!score && !db->reloc_score.empty())) return ASDM_ERR_INVALID;
+  std::lock_guard<std::recursive_mutex> lk(db->ctx->mu);
+  if (!db->reloc_score.empty()) memcpy(db->reloc_score.data(), score, db->reloc_score.size() * sizeof(float));
+  return ASDM_OK;
 }
 
 extern "C" int asdm_bowdb_reloc_scores(asdm_bowdb* db, float* score) {

@@ -384,6 +384,17 @@ int asdm_bowdb_detect_loop(asdm_bowdb* db, const uint32_t* word_id, const double
 int asdm_bowdb_detect_reloc(asdm_bowdb* db, const uint32_t* word_id, const double* value, int n_words,
                             const asdm_bowdb_gates* gates, int32_t* out, int cap, int32_t* n_out);
 int asdm_bowdb_reloc_scores(asdm_bowdb* db, float* score);               /* [size] the persistent mRelocScore values */
+/* The C++ drop-in (host/KeyFrameDatabase_cuda.cc) keeps the reference's bookkeeping fields on its KeyFrames
+ * (KeyFrame.h:175-180: mnLoopWords / mLoopScore / mnRelocWords / mRelocScore): the same two calls that also hand back the
+ * per-slot arrays of the device pass (as asdm_bowdb_query; any of the three may be NULL), and a setter for mRelocScore so
+ * that the KeyFrame member stays the source of truth. */
+int asdm_bowdb_detect_loop_full(asdm_bowdb* db, const uint32_t* word_id, const double* value, int n_words,
+                                const asdm_bowdb_gates* gates, int32_t* out, int cap, int32_t* n_out, int32_t* common,
+                                uint32_t* first_word, float* score);
+int asdm_bowdb_detect_reloc_full(asdm_bowdb* db, const uint32_t* word_id, const double* value, int n_words,
+                                 const asdm_bowdb_gates* gates, int32_t* out, int cap, int32_t* n_out, int32_t* common,
+                                 uint32_t* first_word, float* score);
+int asdm_bowdb_set_reloc_scores(asdm_bowdb* db, const float* score);     /* [size] */
 
 #ifdef __cplusplus
 }
