@@ -156,3 +156,42 @@ def test_gpu_bookkeeping_and_errors(pkg, ctx):
     with pytest.raises(pkg.AsdmError):  # only_global_map without flags
         kdb.DetectRelocalizationCandidates(w, v, only_global_map=True)
     kdb.release()
+
+
+# ------------------------------------------------------------------------------------------------ GPU: the C++ drop-in
+ADAPTOR = os.path.join(ROOT, "asd-slam_b200", "host", "libadaptor_kfdb_shim.so")
+
+
+class _Adaptor:
+    """host/KeyFrameDatabase_cuda.cc (our bodies of ORB_SLAM2::KeyFrameDatabase, compiled against the reference's own
+    KeyFrameDatabase.h) behind the flat harness that drives the reference's KeyFrameDatabase.cc (oracle/ref_kfdb_driver.cc):
+    add / erase per keyframe, the detections, and the bookkeeping members they leave on the KeyFrames."""
+
+    def __init__(self, oracle):
+        import ctypes
+        self.oracle, self.lib = oracle, ctypes.CDLL(ADAPTOR)
+
+    def detect_loop_candidates(self, db, w, v, connected, min_score, only_global):
+        return self.oracle.detect_loop_candidates(db, w, v, connected, min_score, only_global, _ref=self.lib)
+
+    def detect_reloc_candidates(self, db, w, v, rs, only_global):
+        return self.oracle.detect_reloc_candidates(db, w, v, rs, only_global, _ref=self.lib)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", sorted(kfdb_cases.CASES))
+def test_adaptor_vs_reference_golden(pkg, ctx, oracle, name):
+    if not os.path.exists(ADAPTOR):
+        pytest.skip("libadaptor_kfdb_shim.so not built (needs /root/reference at build time)")
+    db = kfdb_cases.build(pkg, name)
+    _check(name, make_kfdb_golden.run(_Adaptor(oracle), db))
+
+
+@pytest.mark.gpu
+def test_adaptor_vs_oracle_large(pkg, ctx, oracle):
+    if not os.path.exists(ADAPTOR):
+        pytest.skip("libadaptor_kfdb_shim.so not built (needs /root/reference at build time)")
+    db = pkg.synth.config_kfdb(n_kf=1500, n_words=100000, words_per_kf=800, n_places=150, seed_extra=33, erase_frac=0.1)
+    a, b = make_kfdb_golden.run(oracle, db), make_kfdb_golden.run(_Adaptor(oracle), db)
+    for k in a:
+        assert np.array_equal(a[k], b[k]), k
