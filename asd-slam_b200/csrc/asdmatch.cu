@@ -333,6 +333,7 @@ extern "C" int asdm_set_option(asdm_ctx* ctx, const char* key, int value) {
   else if (!strcmp(key, "init_serial")) ctx->opt_init_serial = value;
   else if (!strcmp(key, "voc_direct")) ctx->opt_voc_direct = value;
   else if (!strcmp(key, "voc_exact")) ctx->opt_voc_exact = value;
+  else if (!strcmp(key, "bowdb_search")) ctx->opt_bowdb_search = value;
   else if (!strcmp(key, "cand_cap")) ctx->opt_cand_cap = std::max(1, value);
   else if (!strcmp(key, "list_cap_per_query")) ctx->opt_list_cap_per_query = std::max(1, value);
   else if (!strcmp(key, "time_kernels")) ctx->opt_time_kernels = value;
@@ -2134,7 +2135,8 @@ struct asdm_bowdb {
 static int bowdb_reserve(asdm_bowdb* db, size_t entries, int n_slots) {
   asdm_ctx* ctx = db->ctx;
   if (entries > db->cap_entries) {
-    const size_t want = std::max(std::max(entries, db->cap_entries * 2), (size_t)1 << 20);
+    // multiple of 64 entries: k_bowdb_query_hash reads whole 16-byte quads, up to 3 words past a keyframe's last entry
+    const size_t want = align_up(std::max(std::max(entries, db->cap_entries * 2), (size_t)1 << 20), 64);
     void *w = nullptr, *v = nullptr;
     CK(dev_alloc(ctx, &w, want * sizeof(uint32_t)));
     CK(dev_alloc(ctx, &v, want * sizeof(double)));
@@ -2263,7 +2265,7 @@ static int bowdb_run(asdm_bowdb* db, const uint32_t* word_id, const double* valu
   const size_t rb = align_up((size_t)std::max(ns, 1) * 4, 256);
   int rc;
   if ((rc = ensure(ctx, db->query, wb + vb))) return rc;
-  if ((rc = ensure(ctx, db->result, 3 * rb))) return rc;
+  if ((rc = ensure(ctx, db->result, 3 * rb + 256))) return rc;  // common | first word | score | slot counter
   void* h = nullptr;
   if ((rc = stage_alloc(ctx, wb + vb + 3 * rb, &h))) return rc;
   char* hb = (char*)h;
@@ -2276,9 +2278,28 @@ static int bowdb_run(asdm_bowdb* db, const uint32_t* word_id, const double* valu
   char* dr = (char*)db->result.p;
   char* hr = hb + wb + vb;
   if (ns) {
-    k_bowdb_query<<<(ns + BOWDB_WARPS - 1) / BOWDB_WARPS, BOWDB_WARPS * 32, 0, ctx->stream>>>(
-        db->d_slot, ns, db->d_word, db->d_val, (const uint32_t*)dq, (const double*)(dq + wb), n, (int32_t*)dr,
-        (uint32_t*)(dr + rb), (float*)(dr + 2 * rb));
+    // the query as a shared-memory hash table (load factor <= 1/2) when it fits and no word collides with the empty mark
+    int log2cap = 6;
+    while ((1 << log2cap) < 2 * n) log2cap++;
+    const size_t tab_bytes = (size_t)8 << log2cap;
+    if (!ctx->opt_bowdb_search && n > 0 && tab_bytes <= (size_t)200 * 1024 && word_id[n - 1] != 0xffffffffu) {
+      static bool attr_set = false;
+      if (!attr_set) {
+        CK(cudaFuncSetAttribute(k_bowdb_query_hash, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_set = true;
+      }
+      int per_sm = 1;
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bowdb_query_hash, BOWDB_WARPS * 32, tab_bytes));
+      const int grid = std::min((ns + BOWDB_WARPS - 1) / BOWDB_WARPS, std::max(per_sm, 1) * ctx->sm_count);
+      CK(cudaMemsetAsync(dr + 3 * rb, 0, 4, ctx->stream));
+      k_bowdb_query_hash<<<grid, BOWDB_WARPS * 32, tab_bytes, ctx->stream>>>(
+          db->d_slot, ns, db->d_word, db->d_val, (const uint32_t*)dq, (const double*)(dq + wb), n, log2cap, (int32_t*)dr,
+          (uint32_t*)(dr + rb), (float*)(dr + 2 * rb), (int*)(dr + 3 * rb));
+    } else {
+      k_bowdb_query<<<(ns + BOWDB_WARPS - 1) / BOWDB_WARPS, BOWDB_WARPS * 32, 0, ctx->stream>>>(
+          db->d_slot, ns, db->d_word, db->d_val, (const uint32_t*)dq, (const double*)(dq + wb), n, (int32_t*)dr,
+          (uint32_t*)(dr + rb), (float*)(dr + 2 * rb));
+    }
     LAUNCHED(ctx);
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(hr, dr, 3 * rb, cudaMemcpyDeviceToHost, ctx->stream));

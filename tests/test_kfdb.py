@@ -101,13 +101,50 @@ class _Device:
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("search", [0, 1], ids=["hash", "bsearch"])
 @pytest.mark.parametrize("name", sorted(kfdb_cases.CASES))
-def test_gpu_vs_reference_golden(pkg, ctx, name):
+def test_gpu_vs_reference_golden(pkg, ctx, name, search):
+    """both device passes: the shared-memory hash table (k_bowdb_query_hash) and the binary search (k_bowdb_query)"""
     db = kfdb_cases.build(pkg, name)
-    dev = _Device(pkg, ctx, db)
-    _check(name, make_kfdb_golden.run(dev, db))
-    assert ctx.stat("gpu_launches") == 1
-    dev.kdb.release()
+    ctx.set_option("bowdb_search", search)
+    try:
+        dev = _Device(pkg, ctx, db)
+        _check(name, make_kfdb_golden.run(dev, db))
+        assert ctx.stat("gpu_launches") == 1
+        dev.kdb.release()
+    finally:
+        ctx.set_option("bowdb_search", 0)
+
+
+@pytest.mark.gpu
+def test_gpu_hash_equals_bsearch_and_fallbacks(pkg, ctx):
+    """The two kernels agree bit for bit on every slot; queries the table cannot serve (word id 0xffffffff = the empty
+    mark, or too many words for shared memory) take the binary search and still answer correctly."""
+    rng = np.random.default_rng(77)
+    kdb = pkg.KeyFrameDatabase(ctx)
+    kfs = []
+    for s in range(700):
+        w = np.unique(rng.integers(0, 60000, int(rng.integers(1, 900)))).astype(np.uint32)
+        if s % 50 == 0:
+            w = np.unique(np.concatenate([w, [0xffffffff, 0xfffffffe]])).astype(np.uint32)
+        v = rng.random(len(w))
+        kdb.add(w, v)
+        kfs.append((w, v))
+    kdb.erase(13)
+    queries = [kfs[5], kfs[50], kfs[699], (np.zeros(0, np.uint32), np.zeros(0)),
+               (np.array([7], np.uint32), np.array([1.0])),
+               (np.unique(rng.integers(0, 60000, 20000)).astype(np.uint32),) * 1]
+    queries[-1] = (queries[-1][0], rng.random(len(queries[-1][0])))  # > 12800 words: no table
+    for w, v in queries:
+        ctx.set_option("bowdb_search", 1)
+        a = kdb.query(w, v)
+        ctx.set_option("bowdb_search", 0)
+        b = kdb.query(w, v)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and np.array_equal(a[2].view(np.uint32), b[2].view(np.uint32))
+    # a keyframe queried against the database finds itself with all its words
+    common, first, score = kdb.query(*kfs[50])
+    assert common[50] == len(kfs[50][0]) and first[50] == kfs[50][0][0] and common[13] == 0
+    kdb.release()
 
 
 @pytest.mark.gpu
