@@ -2332,12 +2332,25 @@ extern "C" int asdm_bowdb_query(asdm_bowdb* db, const uint32_t* word_id, const d
 }
 
 // lKFsSharingWords (:93-113 / :226-243): a keyframe enters the list at the smallest word it shares with the query, and the
-// keyframes of one inverted list stand in add order -> sort by (first common word, slot)
+// keyframes of one inverted list stand in add order -> sort by (first common word, slot).  Only the members above the
+// common-word gate are ever looked at in list order (:137 / :264), and the gate itself (the maximum over the list) does
+// not depend on the order, so the gate is found in one pass over all members and only the survivors are sorted.
 static void bowdb_sharing_list(const asdm_bowdb* db, const int32_t* common, const uint32_t* first_word, const uint8_t* skip,
-                               const uint8_t* need, std::vector<int32_t>& list) {
+                               const uint8_t* need, float gate_factor, std::vector<int32_t>& list, int* min_common) {
   list.clear();
-  for (int s = 0; s < (int)db->slots.size(); s++)
-    if (db->slots[s].alive && common[s] > 0 && !(skip && skip[s]) && (!need || need[s])) list.push_back(s);
+  const int ns = (int)db->slots.size();
+  auto member = [&](int s) { return db->slots[s].alive && common[s] > 0 && !(skip && skip[s]) && (!need || need[s]); };
+  int maxCommonWords = 0;
+  bool any = false;
+  for (int s = 0; s < ns; s++)
+    if (member(s)) {
+      any = true;
+      maxCommonWords = std::max(maxCommonWords, common[s]);
+    }
+  *min_common = (int)(maxCommonWords * gate_factor);  // :128 / :256 (int * float -> float, truncated)
+  if (!any) return;
+  for (int s = 0; s < ns; s++)
+    if (member(s) && common[s] > *min_common) list.push_back(s);
   std::sort(list.begin(), list.end(), [&](int32_t a, int32_t b) {
     return first_word[a] != first_word[b] ? first_word[a] < first_word[b] : a < b;
   });
@@ -2370,14 +2383,13 @@ static int bowdb_detect(asdm_bowdb* db, bool reloc, const uint32_t* word_id, con
   if (first_out) memcpy(first_out, first_word, (size_t)ns * 4);
   if (score_out) memcpy(score_out, score, (size_t)ns * 4);
   const uint8_t* glob = g->only_global_map ? g->global_flag : nullptr;
-  std::vector<int32_t> sharing;
+  std::vector<int32_t> sharing;  // the members of lKFsSharingWords above the common-word gate, in list order
+  int minCommonWords = 0;
   // loop: connected keyframes never enter the list (:104); relocalisation: the global-map gate sits on the list (:236)
-  bowdb_sharing_list(db, common, first_word, reloc ? nullptr : g->connected, reloc ? glob : nullptr, sharing);
+  bowdb_sharing_list(db, common, first_word, reloc ? nullptr : g->connected, reloc ? glob : nullptr, reloc ? 0.8f : 0.6f,
+                     sharing, &minCommonWords);
   synced(ctx);  // (the staging block stays valid: nothing else is staged before this call returns)
   if (sharing.empty()) return ASDM_OK;
-  int maxCommonWords = 0;
-  for (int32_t s : sharing) maxCommonWords = std::max(maxCommonWords, common[s]);
-  const int minCommonWords = maxCommonWords * (reloc ? 0.8f : 0.6f);  // :128 / :256
   // "listed": mnLoopQuery == pKF->mnId (the sharing list) / mnRelocQuery == F->mnId (every alive keyframe sharing a word)
   auto listed = [&](int s2) {
     if (!db->slots[s2].alive || common[s2] <= 0) return false;
