@@ -334,6 +334,7 @@ extern "C" int asdm_set_option(asdm_ctx* ctx, const char* key, int value) {
   else if (!strcmp(key, "voc_direct")) ctx->opt_voc_direct = value;
   else if (!strcmp(key, "voc_exact")) ctx->opt_voc_exact = value;
   else if (!strcmp(key, "bowdb_search")) ctx->opt_bowdb_search = value;
+  else if (!strcmp(key, "bowdb_filter_bits")) ctx->opt_bowdb_filter_bits = std::min(std::max(value, 8), 1024);
   else if (!strcmp(key, "cand_cap")) ctx->opt_cand_cap = std::max(1, value);
   else if (!strcmp(key, "list_cap_per_query")) ctx->opt_list_cap_per_query = std::max(1, value);
   else if (!strcmp(key, "time_kernels")) ctx->opt_time_kernels = value;
@@ -2278,10 +2279,12 @@ static int bowdb_run(asdm_bowdb* db, const uint32_t* word_id, const double* valu
   char* dr = (char*)db->result.p;
   char* hr = hb + wb + vb;
   if (ns) {
-    // the query as a shared-memory hash table (load factor <= 1/2) when it fits and no word collides with the empty mark
+    // the query as a shared-memory hash table + Bloom filter when they fit and no word collides with the empty mark
     int log2cap = 6;
-    while ((1 << log2cap) < 2 * n) log2cap++;
-    const size_t tab_bytes = (size_t)8 << log2cap;
+    while ((1 << log2cap) * 2 < 3 * n) log2cap++;  // load factor <= 2/3 (the filter in front keeps probes rare)
+    int log2bits = 15;  // Bloom filter in front of the table: >= 128 bits per query word, 4 KB .. 64 KB
+    while (log2bits < 19 && (1 << log2bits) < ctx->opt_bowdb_filter_bits * n) log2bits++;
+    const size_t tab_bytes = ((size_t)8 << log2cap) + ((size_t)1 << (log2bits - 3));
     if (!ctx->opt_bowdb_search && n > 0 && tab_bytes <= (size_t)200 * 1024 && word_id[n - 1] != 0xffffffffu) {
       static bool attr_set = false;
       if (!attr_set) {
@@ -2289,12 +2292,12 @@ static int bowdb_run(asdm_bowdb* db, const uint32_t* word_id, const double* valu
         attr_set = true;
       }
       int per_sm = 1;
-      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bowdb_query_hash, BOWDB_WARPS * 32, tab_bytes));
-      const int grid = std::min((ns + BOWDB_WARPS - 1) / BOWDB_WARPS, std::max(per_sm, 1) * ctx->sm_count);
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bowdb_query_hash, BOWDB_HASH_WARPS * 32, tab_bytes));
+      const int grid = std::min((ns + BOWDB_HASH_WARPS - 1) / BOWDB_HASH_WARPS, std::max(per_sm, 1) * ctx->sm_count);
       CK(cudaMemsetAsync(dr + 3 * rb, 0, 4, ctx->stream));
-      k_bowdb_query_hash<<<grid, BOWDB_WARPS * 32, tab_bytes, ctx->stream>>>(
-          db->d_slot, ns, db->d_word, db->d_val, (const uint32_t*)dq, (const double*)(dq + wb), n, log2cap, (int32_t*)dr,
-          (uint32_t*)(dr + rb), (float*)(dr + 2 * rb), (int*)(dr + 3 * rb));
+      k_bowdb_query_hash<<<grid, BOWDB_HASH_WARPS * 32, tab_bytes, ctx->stream>>>(
+          db->d_slot, ns, db->d_word, db->d_val, (const uint32_t*)dq, (const double*)(dq + wb), n, log2cap, log2bits,
+          (int32_t*)dr, (uint32_t*)(dr + rb), (float*)(dr + 2 * rb), (int*)(dr + 3 * rb));
     } else {
       k_bowdb_query<<<(ns + BOWDB_WARPS - 1) / BOWDB_WARPS, BOWDB_WARPS * 32, 0, ctx->stream>>>(
           db->d_slot, ns, db->d_word, db->d_val, (const uint32_t*)dq, (const double*)(dq + wb), n, (int32_t*)dr,

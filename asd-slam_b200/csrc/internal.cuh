@@ -51,6 +51,7 @@ struct asdm_ctx {
   int opt_list_cap_per_query = 4;  // tensor-core short list slots per query row (grows on overflow)
   int opt_tc_epi_warps = 8;        // epilogue warps of the tensor-core kernel: 4 or 8
   int opt_voc_direct = 0;          // vocabulary descent: 1 = children read straight from global memory (no staging)
+  int opt_bowdb_filter_bits = 128; // keyframe database: Bloom filter bits per query word (rounded up to a power of two overall)
   int opt_bowdb_search = 0;        // keyframe database: 1 = binary-search kernel instead of the shared-memory hash table
   int opt_voc_exact = 0;           // vocabulary descent: 1 = always run the exact double chain (no fp32 fast pass)
   int64_t stat_voc_exact = 0;      // (feature, level) decisions of the last transform that needed the exact chain

@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--vocab", type=int, default=1000000)
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--cpu", action="store_true")
+    ap.add_argument("--filter-bits", type=int, default=0, help="Bloom filter bits per query word (0: library default)")
     ap.add_argument("--bsearch", action="store_true", help="the binary-search kernel instead of the shared-memory hash table")
     a = ap.parse_args()
     pkg = importlib.import_module("asd-slam_b200")
@@ -32,6 +33,8 @@ def main():
     ctx = pkg.Context(0)
     kdb = pkg.KeyFrameDatabase(ctx)
     ctx.set_option("bowdb_search", int(a.bsearch))
+    if a.filter_bits:
+        ctx.set_option("bowdb_filter_bits", a.filter_bits)
     # keyframes of one "place" share most of their words: 100 keyframes per place
     n_places = max(a.kf // 100, 1)
     place_words = [np.unique(rng.integers(0, a.vocab, int(a.words * 1.3))) for _ in range(n_places)]
@@ -61,7 +64,7 @@ def main():
         c = kdb.DetectLoopCandidates(words[s], vals[s], connected, 0.05, False, None, neigh_off, neigh_slot)
         tl.append(time.perf_counter() - t0)
         cands.append(c)
-    out = {"tool": "kfdb_probe", "kernel": "k_bowdb_query" if a.bsearch else "k_bowdb_query_hash", "keyframes": a.kf, "entries": int(entries), "vocabulary_words": a.vocab,
+    out = {"tool": "kfdb_probe", "kernel": "k_bowdb_query" if a.bsearch else "k_bowdb_query_hash", "filter_bits_per_word": a.filter_bits or "default", "keyframes": a.kf, "entries": int(entries), "vocabulary_words": a.vocab,
            "algorithmic_bytes_per_query": int(entries) * 12, "add_us_per_keyframe": 1e6 * t_add / a.kf,
            "query_call_ms_median": 1e3 * float(np.median(tq)), "query_call_ms_min": 1e3 * float(np.min(tq)),
            "detect_loop_call_ms_median": 1e3 * float(np.median(tl)),
