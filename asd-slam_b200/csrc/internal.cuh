@@ -78,6 +78,8 @@ struct asdm_ctx {
   int opt_time_kernels = 0;     // record CUDA events around the distance stage of every job run
   std::vector<cudaEvent_t> ev;  // pairs (begin, end), drained by asdm_get_stat("dist_stage_us")
   int proj_ent_cap = 1 << 16;  // entries of the projection candidate pool (grows on overflow)
+  int opt_proj_legacy = 0;     // 1 = the three-kernel projection search (gather / dist / resolve) instead of k_proj_fused
+  void* proj_ctl = nullptr;    // ProjCtl of k_proj_fused: zero between calls (the kernel's last CTA resets it)
 };
 
 // small per-set arrays (range flag | keypoints | FeatureVector) of a batch of sets live in ONE device block, filled by
@@ -106,6 +108,7 @@ struct asdm_set {
   int32_t* cell_start = nullptr;  // [cols*rows+1]
   int32_t* cell_items = nullptr;  // [n] insertion (index) order inside a cell
   int32_t* cell_tmp = nullptr;    // [n] scratch of k_build_grid
+  int4* cell_kp = nullptr;        // [n] keypoints in cell order: {x bits, y bits, octave, index} (one LDG.128 per candidate)
   bool grid_built = false;        // the grid bucket is built by the first projection-gated search that needs it
   uint32_t* node_id = nullptr;    // [n] FeatureVector node of the feature
   int32_t* fv_pos = nullptr;      // [n] CSR position of the feature in the FeatureVector, -1 if absent

@@ -109,6 +109,10 @@ __global__ void __launch_bounds__(256) k_proj_dist(const float* __restrict__ des
                                                    const int32_t* __restrict__ ent_j,
                                                    const int32_t* __restrict__ ent_q, int ent_cap,
                                                    const int32_t* __restrict__ total, float* __restrict__ ent_d) {
+  // total[1] = overflow: a query that did not fit left a hole of unwritten entries behind it (the gather still advances
+  // total[0] so that the host learns the exact demand) -- nothing may be dereferenced, the host grows the pool and
+  // searches again
+  if (total[1]) return;
   const int n = min(*total, ent_cap);
   for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
     const int iq = ent_q[e];
@@ -363,11 +367,14 @@ __global__ void __launch_bounds__(32) k_init_resolve(const asdm_kp* __restrict__
 // Descriptor stage of Frame::ComputeStereoMatches (Frame.cc:360-444). One warp per left keypoint: lanes test the
 // right keypoints in index order (vRowIndices[row] is filled in ascending iR, Frame.cc:378-388), compute the exact
 // distance of those inside the row band / octave / disparity gates and reduce to the first minimum.
+struct StereoLevels {  // mvScaleFactors by value: no upload, no extra launch
+  float v[ASDM_MAX_LEVELS];
+};
 __global__ void __launch_bounds__(256) k_stereo_match(const float* __restrict__ desc_l,
                                                       const asdm_kp* __restrict__ kps_l, int n_l,
                                                       const float* __restrict__ desc_r,
                                                       const asdm_kp* __restrict__ kps_r, int n_r,
-                                                      const float* __restrict__ scale_factors, int n_levels,
+                                                      const StereoLevels scale_factors, int n_levels,
                                                       int n_rows, float min_d, float max_d,
                                                       int32_t* __restrict__ best_r, float* __restrict__ best_dist) {
   const int lane = threadIdx.x & 31;
@@ -388,7 +395,7 @@ __global__ void __launch_bounds__(256) k_stereo_match(const float* __restrict__ 
         if (iR < n_r) {
           const asdm_kp kpR = kps_r[iR];
           const int oc = min(max(kpR.octave, 0), n_levels - 1);
-          const float r = __fmul_rn(2.0f, scale_factors[oc]);
+          const float r = __fmul_rn(2.0f, scale_factors.v[oc]);
           const int maxr = (int)ceilf(__fadd_rn(kpR.y, r));
           const int minr = (int)floorf(__fsub_rn(kpR.y, r));
           const bool in_band = row >= minr && row <= maxr;

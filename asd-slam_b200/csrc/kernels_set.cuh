@@ -36,7 +36,7 @@ __global__ void __launch_bounds__(256) k_pack_desc(const float* __restrict__ des
 __global__ void __launch_bounds__(1024) k_build_grid(const asdm_kp* __restrict__ kps, int n, asdm_grid g,
                                                      int32_t* __restrict__ cell_of_tmp,
                                                      int32_t* __restrict__ cell_start,
-                                                     int32_t* __restrict__ cell_items) {
+                                                     int32_t* __restrict__ cell_items, int4* __restrict__ cell_kp) {
   extern __shared__ int32_t s_cnt[];  // [nc + 1]
   __shared__ int32_t s_warp[32];
   const int nc = g.cols * g.rows;
@@ -108,6 +108,13 @@ __global__ void __launch_bounds__(1024) k_build_grid(const asdm_kp* __restrict__
       }
       cell_items[k + 1] = x;
     }
+  }
+  __syncthreads();
+  // the same bucket with the keypoint fields inline (k_proj_fused reads one 16-byte record per candidate)
+  for (int a = t; a < carry; a += nt) {
+    const int i = cell_items[a];
+    const asdm_kp kp = kps[i];
+    cell_kp[a] = make_int4(__float_as_int(kp.x), __float_as_int(kp.y), kp.octave, i);
   }
 }
 

@@ -206,9 +206,17 @@ def test_small_cand_cap_retries(pkg, ctx, oracle):
 
 
 # ------------------------------------------------------------------------------- projection-gated searches
+@pytest.fixture(params=[0, 1], ids=["fused", "legacy"])
+def proj_path(request, ctx):
+    """Both projection-search implementations must equal the oracle: k_proj_fused (default) and the three-kernel path."""
+    ctx.set_option("proj_legacy", request.param)
+    yield request.param
+    ctx.set_option("proj_legacy", 0)
+
+
 @pytest.mark.parametrize("th,nkp,nmp,inview", [(1.0, 2000, 8000, 2000), (5.0, 2000, 8000, 3000), (1.0, 50, 200, 100),
                                                (3.0, 1, 5, 5)])
-def test_c2_search_by_projection_local_map(pkg, ctx, oracle, th, nkp, nmp, inview):
+def test_c2_search_by_projection_local_map(pkg, ctx, oracle, th, nkp, nmp, inview, proj_path):
     c = pkg.synth.config2(n_kp=nkp, n_mp=nmp, n_in_view=inview, th=th)
     F = pkg.DescriptorSet(ctx, c["desc_t"], c["kps_t"], c["grid"])
     mt = pkg.ORBmatcher(ctx, c["nnratio"], True)
@@ -216,6 +224,8 @@ def test_c2_search_by_projection_local_map(pkg, ctx, oracle, th, nkp, nmp, invie
     nm, assign, dist = mt.SearchByProjection_LocalMap(F, q["valid"], q["u"], q["v"], c["level"], c["view_cos"], q["blocks"],
                                                       c["desc_q"], pkg.synth.scale_factors(), th=th,
                                                       blocked0=c["blocked0"])
+    if proj_path == 0:  # fused: one launch per call (+ the grid bucket on the first search of a set)
+        assert ctx.stat("gpu_launches") <= 2
     onm, oassign, odist = oracle.search_by_projection(c["desc_t"], c["kps_t"], c["grid"], q, c["desc_q"], c["blocked0"],
                                                       c["mode"], c["th_accept"], c["best_init"], c["nnratio"],
                                                       c["check_ori"], c["count_twice"])
@@ -227,7 +237,7 @@ def test_c2_search_by_projection_local_map(pkg, ctx, oracle, th, nkp, nmp, invie
     F.release()
 
 
-def test_c3_stereo_and_frame_to_frame(pkg, ctx, oracle):
+def test_c3_stereo_and_frame_to_frame(pkg, ctx, oracle, proj_path):
     c = pkg.synth.config3()
     s, f = c["stereo"], c["f2f"]
     L = pkg.DescriptorSet(ctx, s["desc_l"], s["kps_l"], f["grid"])
@@ -256,6 +266,80 @@ def test_c3_stereo_and_frame_to_frame(pkg, ctx, oracle):
     _eq(assign2, oassign, "f2f assign (row map)")
     for x in (L, R, Cur):
         x.release()
+
+
+def test_projection_entry_pool_overflow_is_retried(pkg, ctx, oracle, proj_path):
+    """The candidate pool starts far too small: the search must notice, grow it and repeat -- never walk the hole an
+    overflowing query leaves in the pool (kernels_proj.cuh:112) and never truncate silently."""
+    f = pkg.synth.config3()["f2f"]
+    s = pkg.synth.config3()["stereo"]
+    L = pkg.DescriptorSet(ctx, s["desc_l"], s["kps_l"], f["grid"])
+    Cur = pkg.DescriptorSet(ctx, f["desc_t"], f["kps_t"], f["grid"])
+    onm, oassign, odist = oracle.search_by_projection(f["desc_t"], f["kps_t"], f["grid"], f["queries"], f["desc_q"],
+                                                      f["blocked0"], f["mode"], f["th_accept"], f["best_init"],
+                                                      f["nnratio"], f["check_ori"], f["count_twice"])
+    mt = pkg.ORBmatcher(ctx, 0.8, True)
+    ctx.set_option("proj_ent_cap", 64)
+    try:
+        for rep in range(2):  # the second call starts from the grown pool
+            nm, assign, dist = mt.SearchByProjection(Cur, f["queries"], q_set=L, blocked0=f["blocked0"],
+                                                     mode=pkg.ASDM_PROJ_BEST_ONLY, th_accept=1.5, best_init=100.0)
+            if rep == 0:
+                assert ctx.stat("retries") >= 1
+            _eq(assign, oassign, "f2f assign after pool growth")
+            _eq_dist(dist, odist, "f2f dist after pool growth")
+            assert nm == onm
+    finally:
+        ctx.set_option("proj_ent_cap", 1 << 16)
+    L.release(); Cur.release()
+
+
+def test_projection_query_descriptor_sources(pkg, ctx, oracle):
+    """Host descriptors are read in place when they are page-locked (asdm_host_alloc) and staged when pageable; both
+    equal the oracle, and so does the per-query view of the same search."""
+    c = pkg.synth.config2(n_kp=700, n_mp=2500, n_in_view=900, th=1.0)
+    F = pkg.DescriptorSet(ctx, c["desc_t"], c["kps_t"], c["grid"])
+    mt = pkg.ORBmatcher(ctx, c["nnratio"], True)
+    q = c["queries"]
+    onm, oassign, odist = oracle.search_by_projection(c["desc_t"], c["kps_t"], c["grid"], q, c["desc_q"], c["blocked0"],
+                                                      c["mode"], c["th_accept"], c["best_init"], c["nnratio"],
+                                                      c["check_ori"], c["count_twice"])
+    pinned = ctx.pinned(c["desc_q"].shape, np.float32)
+    pinned[...] = c["desc_q"]
+    for dq in (c["desc_q"], pinned):
+        nm, assign, dist = mt.SearchByProjection_LocalMap(F, q["valid"], q["u"], q["v"], c["level"], c["view_cos"], q["blocks"],
+                                                          dq, pkg.synth.scale_factors(), th=1.0, blocked0=c["blocked0"])
+        _eq(assign, oassign, "assign")
+        _eq_dist(dist, odist, "dist")
+        assert nm == onm
+    F.release()
+
+
+def test_empty_jobs_settle_and_fetch(pkg, ctx, oracle):
+    """A job without pairs (a rank that was dealt no unit) must settle and fetch without touching the device flags
+    (asdmatch.cu:1163)."""
+    c = pkg.synth.config5(n=300, n_pairs=2, n_kf=3, n_nodes=4)
+    kfs = c["kfs"]
+    sets = [pkg.DescriptorSet(ctx, k["desc"], k["kps"], c["grid"], k["fv"]) for k in kfs]
+    masks = [k["valid"] for k in kfs]
+    # poison the block cache so that recycled scratch is not accidentally zero
+    big = pkg.PairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, sets, masks, c["ia"], c["ib"], 0.85, True)
+    big.run(); big.fetch(); big.destroy()
+    job = pkg.PairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, sets, masks, np.zeros(0, np.int32), np.zeros(0, np.int32), 0.85, True)
+    job.run()
+    job.settle()
+    nm, match, dist = job.fetch()
+    assert nm.shape == (0,) and match.shape[0] == 0
+    job.destroy()
+    # world larger than the number of pairs: ranks 2 and 3 own nothing
+    for rank in (0, 3):
+        sj = pkg.ShardedPairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, sets, masks, c["ia"], c["ib"], 0.85, True, rank=rank, world=4)
+        sj.run()
+        sj.settle()
+        assert sj.n_local == (1 if rank == 0 else 0)
+        sj.destroy()
+    for s in sets:
+        s.release()
 
 
 @pytest.mark.parametrize("serial", [0, 1])
