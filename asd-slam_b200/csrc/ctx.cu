@@ -320,6 +320,8 @@ extern "C" int asdm_get_stat(asdm_ctx* ctx, const char* key, int64_t* value) {
   else if (!strcmp(key, "tc_used")) *value = ctx->stat_tc_used;
   else if (!strcmp(key, "tc_pairs")) *value = ctx->stat_tc_pairs;
   else if (!strcmp(key, "sm_count")) *value = ctx->sm_count;
+  else if (!strncmp(key, "proj_host_ns_", 13) && key[13] >= '0' && key[13] <= '2' && !key[14]) *value = ctx->stat_proj_host_ns[key[13] - '0'];
+  else if (!strncmp(key, "proj_ns_", 8) && key[8] >= '0' && key[8] <= '5' && !key[9]) *value = ctx->stat_proj_ns[key[8] - '0'];
   else if (!strcmp(key, "dist_stage_us") || !strcmp(key, "dist_stage_runs")) {
     // total device time of the distance stage (tensor-core shortlist, or the exact kernel) over the runs recorded
     // since the last drain; the caller must have synchronised

@@ -79,6 +79,8 @@ struct asdm_ctx {
   std::vector<cudaEvent_t> ev;  // pairs (begin, end), drained by asdm_get_stat("dist_stage_us")
   int proj_ent_cap = 1 << 16;  // entries of the projection candidate pool (grows on overflow)
   int opt_proj_legacy = 0;     // 1 = the three-kernel projection search (gather / dist / resolve) instead of k_proj_fused
+  int32_t stat_proj_ns[6] = {0, 0, 0, 0, 0, 0};  // k_proj_fused of the last call: phase durations (ns) and sweeps
+  int32_t stat_proj_host_ns[3] = {0, 0, 0};      // host side of the same call: staging | launch | wait
   void* proj_ctl = nullptr;    // ProjCtl of k_proj_fused: zero between calls (the kernel's last CTA resets it)
 };
 

@@ -364,51 +364,118 @@ __global__ void __launch_bounds__(32) k_init_resolve(const asdm_kp* __restrict__
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Descriptor stage of Frame::ComputeStereoMatches (Frame.cc:360-444). One warp per left keypoint: lanes test the
-// right keypoints in index order (vRowIndices[row] is filled in ascending iR, Frame.cc:378-388), compute the exact
-// distance of those inside the row band / octave / disparity gates and reduce to the first minimum.
+// Descriptor stage of Frame::ComputeStereoMatches (Frame.cc:360-444). One warp per left keypoint: the lanes test the
+// right keypoints in index order (vRowIndices[row] is filled in ascending iR, Frame.cc:378-388) against the row band /
+// octave / disparity gates and compact the survivors with ballots; every STEREO_BATCH survivors the warp computes their
+// exact distances together -- the left row sits in registers, each right row is read by one coalesced 512-byte load,
+// the squared differences go through shared memory and lane c adds candidate c's 128 terms in index order
+// (ORBmatcher.cc:1637-1644) -- and keeps the first minimum (strict '<' in ascending iR, Frame.cc:438).
 struct StereoLevels {  // mvScaleFactors by value: no upload, no extra launch
   float v[ASDM_MAX_LEVELS];
 };
-__global__ void __launch_bounds__(256) k_stereo_match(const float* __restrict__ desc_l,
+#define STEREO_WARPS 8
+#define STEREO_BATCH 8
+#define STEREO_ROW 132
+__global__ void __launch_bounds__(STEREO_WARPS * 32) k_stereo_match(const float* __restrict__ desc_l,
                                                       const asdm_kp* __restrict__ kps_l, int n_l,
                                                       const float* __restrict__ desc_r,
                                                       const asdm_kp* __restrict__ kps_r, int n_r,
                                                       const StereoLevels scale_factors, int n_levels,
                                                       int n_rows, float min_d, float max_d,
-                                                      int32_t* __restrict__ best_r, float* __restrict__ best_dist) {
-  const int lane = threadIdx.x & 31;
+                                                      int32_t* __restrict__ best_r, float* __restrict__ best_dist,
+                                                      uint32_t* __restrict__ ticket, int4* __restrict__ host_out) {
+  // best_r | best_dist are one device array [2 * n_l (padded to 4)]; the CTA that takes the last ticket copies it to the
+  // page-locked block in 16-byte pieces (1500 scattered 4-byte stores over PCIe cost more than the whole search)
+  __shared__ __align__(16) float s_sq[STEREO_WARPS][STEREO_BATCH * STEREO_ROW];
+  __shared__ int s_pend[STEREO_WARPS][64];
+  // Per right keypoint {first row, last row of its band (Frame.cc:381-385), octave, x}: computed once per CTA into
+  // shared memory (the level table is a kernel parameter: indexing it per candidate would cost a chain of constant
+  // loads), so a step of the scan is one LDS.128 and four compares per lane.
+  extern __shared__ __align__(16) int4 s_band[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int iR = threadIdx.x; iR < n_r; iR += blockDim.x) {
+    const asdm_kp kpR = kps_r[iR];
+    const int oc = min(max(kpR.octave, 0), n_levels - 1);
+    float sfv = 0.f;
+#pragma unroll
+    for (int l = 0; l < ASDM_MAX_LEVELS; l++) sfv = l == oc ? scale_factors.v[l] : sfv;
+    const float r = __fmul_rn(2.0f, sfv);
+    s_band[iR] = make_int4((int)floorf(__fsub_rn(kpR.y, r)), (int)ceilf(__fadd_rn(kpR.y, r)), kpR.octave, __float_as_int(kpR.x));
+  }
+  __syncthreads();
   const int iL = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (iL >= n_l) return;
-  const asdm_kp kpL = kps_l[iL];
+  const bool live = iL < n_l;
+  const asdm_kp kpL = live ? kps_l[iL] : asdm_kp{0.f, -1.f, 0.f, 0};
   const float vL = kpL.y, uL = kpL.x;
   int out_idx = -1;
   float out_d = -1.f;
-  if (vL >= 0.f && vL < (float)n_rows) {
+  if (live && vL >= 0.f && vL < (float)n_rows) {
     const int row = (int)vL;  // vRowIndices[vL] (Frame.cc:406)
     const float minU = __fsub_rn(uL, max_d), maxU = __fsub_rn(uL, min_d);
     if (!(maxU < 0.f)) {
+      const float4 l4 = __ldg(reinterpret_cast<const float4*>(desc_l + (size_t)iL * ASDM_DESC_DIM) + lane);
       float bd = ASDM_TH_HIGH;  // :417
       int bi = INT_MAX;
-      for (int base = 0; base < n_r; base += 32) {
-        const int iR = base + lane;
-        if (iR < n_r) {
-          const asdm_kp kpR = kps_r[iR];
-          const int oc = min(max(kpR.octave, 0), n_levels - 1);
-          const float r = __fmul_rn(2.0f, scale_factors.v[oc]);
-          const int maxr = (int)ceilf(__fadd_rn(kpR.y, r));
-          const int minr = (int)floorf(__fsub_rn(kpR.y, r));
-          const bool in_band = row >= minr && row <= maxr;
-          const bool lvl_ok = !(kpR.octave < kpL.octave - 1 || kpR.octave > kpL.octave + 1);  // :428
-          if (in_band && lvl_ok && kpR.x >= minU && kpR.x <= maxU) {
-            const float d = asdm_exact_dist(desc_l + (size_t)iL * ASDM_DESC_DIM, desc_r + (size_t)iR * ASDM_DESC_DIM);
-            if (d < bd) {  // per lane indices ascend, so strict '<' keeps the first minimum
-              bd = d;
-              bi = iR;
-            }
+      int np = 0;  // pending survivors in s_pend[warp][0..np)
+      float* sq = s_sq[warp];
+      int* pend = s_pend[warp];
+      // distances of the first `nb` pending survivors (ascending iR); lane c < nb ends up with candidate c's distance
+      auto flush = [&](int nb) {
+        for (int c = 0; c < nb; c++) {
+          const int iR = pend[c];
+          const float4 r4 = __ldg(reinterpret_cast<const float4*>(desc_r + (size_t)iR * ASDM_DESC_DIM) + lane);
+          float4 s;
+          float d;
+          d = __fsub_rn(l4.x, r4.x); s.x = __fmul_rn(d, d);
+          d = __fsub_rn(l4.y, r4.y); s.y = __fmul_rn(d, d);
+          d = __fsub_rn(l4.z, r4.z); s.z = __fmul_rn(d, d);
+          d = __fsub_rn(l4.w, r4.w); s.w = __fmul_rn(d, d);
+          *reinterpret_cast<float4*>(sq + c * STEREO_ROW + 4 * lane) = s;
+        }
+        __syncwarp();
+        if (lane < nb) {
+          const float4* rowp = reinterpret_cast<const float4*>(sq + lane * STEREO_ROW);
+          float acc = 0.f;
+#pragma unroll 8
+          for (int k = 0; k < ASDM_DESC_DIM / 4; k++) {
+            const float4 x = rowp[k];
+            acc = __fadd_rn(acc, x.x); acc = __fadd_rn(acc, x.y); acc = __fadd_rn(acc, x.z); acc = __fadd_rn(acc, x.w);
+          }
+          const int iR = pend[lane];
+          if (acc < bd || (acc == bd && iR < bi)) {  // first minimum in ascending iR
+            bd = acc;
+            bi = iR;
           }
         }
+        __syncwarp();
+        // the survivors behind the batch move to the front
+        const int rest = np - nb;
+        int mv = 0;
+        if (lane < rest) mv = pend[nb + lane];
+        __syncwarp();
+        if (lane < rest) pend[lane] = mv;
+        np = rest;
+        __syncwarp();
+      };
+      for (int base = 0; base < n_r; base += 32) {
+        const int iR = base + lane;
+        bool keep = false;
+        if (iR < n_r) {
+          const int4 B = s_band[iR];
+          const float xR = __int_as_float(B.w);
+          const bool in_band = row >= B.x && row <= B.y;
+          const bool lvl_ok = !(B.z < kpL.octave - 1 || B.z > kpL.octave + 1);  // :428
+          keep = in_band && lvl_ok && xR >= minU && xR <= maxU;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, keep);
+        if (m) {
+          if (keep) pend[np + __popc(m & ((1u << lane) - 1u))] = iR;  // np < STEREO_BATCH here, so at most 39 entries
+          np += __popc(m);
+          __syncwarp();
+          while (np >= STEREO_BATCH) flush(STEREO_BATCH);
+        }
       }
+      if (np > 0) flush(np);
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
         const float od = __shfl_xor_sync(0xffffffffu, bd, o);
@@ -425,10 +492,21 @@ __global__ void __launch_bounds__(256) k_stereo_match(const float* __restrict__ 
       }
     }
   }
-  if (lane == 0) {
+  if (live && lane == 0) {
     best_r[iL] = out_idx;
     best_dist[iL] = out_d;
   }
+  __shared__ int s_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = atomicAdd(ticket, 1u) == gridDim.x - 1 ? 1 : 0;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const int n16 = (2 * ((n_l + 3) & ~3)) / 4;
+  const int4* src = reinterpret_cast<const int4*>(best_r);
+  for (int k = threadIdx.x; k < n16; k += blockDim.x) host_out[k] = __ldcg(src + k);
+  if (threadIdx.x == 0) *ticket = 0u;
 }
 
 // Queries of SearchForInitialization: level-0 keypoints of F1 search F2 around their previous match

@@ -7,7 +7,15 @@
 #include <new>
 
 #include "host_util.cuh"
+#include <time.h>
+
 #include "kernels_proj_fused.cuh"
+
+static inline int64_t host_ns() {
+  timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  return (int64_t)ts.tv_sec * 1000000000 + ts.tv_nsec;
+}
 
 // ------------------------------------------------------------------------- projection-gated entry points
 // scratch slots of the context
@@ -26,7 +34,7 @@ static int proj_candidates(asdm_ctx* ctx, asdm_set* target, int nq, const float*
                            bool defer_check = false) {
   // defer_check: no wait for the entry count -- the distance kernel sizes itself from the device counter and the caller
   // reads (total, overflow) back together with its results, growing the pool and repeating the search if needed
-  int ent_cap = std::max(*ent_cap_io, 1 << 14);
+  int ent_cap = std::max(*ent_cap_io, 64);
   {
     const int rc = ensure_grid(ctx, target);
     if (rc) return rc;
@@ -218,7 +226,9 @@ static int search_by_projection_legacy(asdm_ctx* ctx, asdm_set* target, const as
 // page-locked host memory (asdm_host_alloc) or on the device are read in place. Results are stored by the kernel into a
 // page-locked block and handed to the caller's arrays after the wait.
 void proj_init_device() {
-  cudaFuncSetAttribute(k_proj_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  cudaFuncSetAttribute(k_stereo_match, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+  cudaFuncSetAttribute(k_proj_fused<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  cudaFuncSetAttribute(k_proj_fused<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
 }
 
 static int search_by_projection_impl(asdm_ctx* ctx, asdm_set* target, const asdm_proj_query* q, int nq,
@@ -235,6 +245,7 @@ static int search_by_projection_impl(asdm_ctx* ctx, asdm_set* target, const asdm
   if (target->n >= (1 << 24)) return fail(ctx, ASDM_ERR_INVALID, "target set too large for the projection search");
   std::lock_guard<std::recursive_mutex> lk(ctx->mu);
   CK(cudaSetDevice(ctx->device));
+  const int64_t hn0 = host_ns();
   ctx->stat_launches = 0;
   ctx->stat_retries = 0;
   const int n_t = target->n;
@@ -304,12 +315,14 @@ static int search_by_projection_impl(asdm_ctx* ctx, asdm_set* target, const asdm
     CK(cudaMemsetAsync(ctx->proj_ctl, 0, 256, ctx->stream));
   }
   const int n_cells = target->grid.cols * target->grid.rows;
-  const size_t smem1 = pf_phase1_smem(n_cells), smem2 = pf_phase2_smem(n_t, nv);
+  const size_t smem1 = pf_phase1_smem(n_cells), bytes2 = pf_phase2_bytes(n_t, nv);
   if (smem1 > 200 * 1024) return fail(ctx, ASDM_ERR_INVALID, "grid too fine for the projection search");
-  A.smem2 = smem2 <= 200 * 1024 ? 1 : 0;
-  const size_t smem = A.smem2 ? std::max(smem1, smem2) : smem1;
-  if (!A.smem2 && (rc = ensure(ctx, ctx->scratch[SC_STATE], smem2))) return rc;
-  if ((rc = ensure(ctx, ctx->scratch[SC_SEG], NV * 20))) return rc;
+  A.smem2 = bytes2 <= 200 * 1024 ? 1 : 0;
+  const size_t smem = A.smem2 ? std::max(smem1, bytes2) : smem1;
+  if (!A.smem2 && (rc = ensure(ctx, ctx->scratch[SC_STATE], bytes2))) return rc;
+  if ((rc = ensure(ctx, ctx->scratch[SC_SEG], NV * sizeof(ProjRec)))) return rc;
+  if (query_best && (rc = ensure(ctx, ctx->scratch[SC_QDESC], NQ * 8))) return rc;
+  if (blocked0 && (rc = ensure(ctx, ctx->scratch[SC_BLOCK], align_up(NT, 16)))) return rc;
   A.q = hq;
   A.nv = nv;
   A.nq = nq;
@@ -320,8 +333,9 @@ static int search_by_projection_impl(asdm_ctx* ctx, asdm_set* target, const asdm
   A.g = target->grid;
   A.n_t = n_t;
   A.blocked0 = blocked0 ? (const uint8_t*)(h + o_blk) : nullptr;
-  A.act = (int4*)ctx->scratch[SC_SEG].p;
-  A.act_angle = (float*)((char*)ctx->scratch[SC_SEG].p + NV * 16);
+  A.g_blk = blocked0 ? (uint32_t*)ctx->scratch[SC_BLOCK].p : nullptr;
+  A.rec = (ProjRec*)ctx->scratch[SC_SEG].p;
+  A.g_q = query_best ? (int32_t*)ctx->scratch[SC_QDESC].p : nullptr;
   A.ctl = (ProjCtl*)ctx->proj_ctl;
   A.g_state = A.smem2 ? nullptr : (int32_t*)ctx->scratch[SC_STATE].p;
   A.want_q = query_best ? 1 : 0;
@@ -339,16 +353,24 @@ static int search_by_projection_impl(asdm_ctx* ctx, asdm_set* target, const asdm
     A.ent = (int2*)ctx->scratch[SC_ENT].p;
     A.ent_cap = ctx->proj_ent_cap;
     A.r_hdr[0] = A.r_hdr[1] = A.r_hdr[2] = 0;
-    k_proj_fused<<<grid_x, PF_WARPS * 32, smem, ctx->stream>>>(A);
+    const int64_t hn1 = host_ns();
+    if (A.smem2) k_proj_fused<true><<<grid_x, PF_WARPS * 32, smem, ctx->stream>>>(A);
+    else k_proj_fused<false><<<grid_x, PF_WARPS * 32, smem, ctx->stream>>>(A);
     LAUNCHED(ctx);
     CK(cudaGetLastError());
+    const int64_t hn2 = host_ns();
     CK(cudaStreamSynchronize(ctx->stream));
+    const int64_t hn3 = host_ns();
+    ctx->stat_proj_host_ns[0] = (int32_t)(hn1 - hn0);  // staging
+    ctx->stat_proj_host_ns[1] = (int32_t)(hn2 - hn1);  // launch
+    ctx->stat_proj_host_ns[2] = (int32_t)(hn3 - hn2);  // wait
     if (A.r_hdr[1]) {  // pool too small: hdr[0] is the exact demand. The staged inputs are still in place: search again
       ctx->proj_ent_cap = std::max(ctx->proj_ent_cap * 2, A.r_hdr[0] + 1024);
       ctx->stat_retries++;
       continue;
     }
     nm = A.r_hdr[2];
+    for (int k = 0; k < 6; k++) ctx->stat_proj_ns[k] = A.r_hdr[8 + k];
     break;
   }
   if (query_best && nq > 0) {
@@ -488,21 +510,31 @@ extern "C" int asdm_stereo_row_match(asdm_ctx* ctx, asdm_set* left, asdm_set* ri
   int rc;
   // one launch and one wait: the level table rides in the kernel parameters, the results are stored by the kernel into
   // the page-locked arena (zero-copy) and handed to the caller's arrays after the wait
-  const size_t NL = (size_t)n_l;
+  const size_t NL = ((size_t)n_l + 3) & ~(size_t)3;  // best_r | best_dist, each padded to 16 bytes
   void* hv = nullptr;
   if ((rc = stage_alloc(ctx, 2 * NL * 4, &hv))) return rc;
+  if ((rc = ensure(ctx, ctx->scratch[SC_STATE], 2 * NL * 4))) return rc;
+  if (!ctx->proj_ctl) {
+    CK(cudaMalloc(&ctx->proj_ctl, 256));
+    CK(cudaMemsetAsync(ctx->proj_ctl, 0, 256, ctx->stream));
+  }
+  int32_t* d_best = (int32_t*)ctx->scratch[SC_STATE].p;
+  float* d_dist = (float*)(d_best + NL);
   int32_t* h_best = (int32_t*)hv;
   float* h_dist = (float*)(h_best + NL);
   StereoLevels sf;
   memset(&sf, 0, sizeof sf);
   memcpy(sf.v, scale_factors, (size_t)n_levels * 4);
-  k_stereo_match<<<(n_l * 32 + 255) / 256, 256, 0, ctx->stream>>>(left->desc, left->kps, n_l, right->desc, right->kps, right->n, sf,
-                                                                  n_levels, n_rows, min_d, max_d, h_best, h_dist);
+  const size_t band_bytes = (size_t)std::max(right->n, 1) * sizeof(int4);
+  if (band_bytes > 160 * 1024) return fail(ctx, ASDM_ERR_INVALID, "right image has too many keypoints for the stereo search (10240)");
+  k_stereo_match<<<(n_l + STEREO_WARPS - 1) / STEREO_WARPS, STEREO_WARPS * 32, band_bytes, ctx->stream>>>(
+      left->desc, left->kps, n_l, right->desc, right->kps, right->n, sf, n_levels, n_rows, min_d, max_d, d_best, d_dist,
+      (uint32_t*)ctx->proj_ctl + 8, (int4*)hv);
   LAUNCHED(ctx);
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(ctx->stream));
-  memcpy(best_r, h_best, NL * 4);
-  if (best_dist) memcpy(best_dist, h_dist, NL * 4);
+  memcpy(best_r, h_best, (size_t)n_l * 4);
+  if (best_dist) memcpy(best_dist, h_dist, (size_t)n_l * 4);
   synced(ctx);
   return ASDM_OK;
 }

@@ -30,6 +30,31 @@ def timeit(fn, reps, warm=5):
     return {"median_ms": float(np.median(ts)), "p10_ms": float(np.percentile(ts, 10)), "p90_ms": float(np.percentile(ts, 90))}
 
 
+def abi_closure(fn, *args):
+    """The C-ABI call alone: arguments converted once (what a C++ caller passes), only `fn(*args)` is timed."""
+    def call():
+        rc = fn(*args)
+        if rc != 0:
+            raise RuntimeError(f"ABI call failed with {rc}")
+    return call
+
+
+def abi_proj(pkg, ctx, target, q, desc_q=None, q_set=None, blocked0=None, mode=1, th_accept=1.5, best_init=256.0, nnratio=0.8,
+             check_ori=False, count_twice=False):
+    import ctypes as C
+    L = pkg._lib
+    q = np.ascontiguousarray(q, dtype=L.PROJ_QUERY_DTYPE)
+    p = L.ProjParams(int(mode), float(th_accept), float(best_init), float(nnratio), int(check_ori), int(count_twice))
+    assign, dist, nm = np.empty(target.n, np.int32), np.empty(target.n, np.float32), C.c_int32()
+    keep = (q, p, assign, dist, nm, desc_q, blocked0)
+    call = abi_closure(ctx.lib.asdm_search_by_projection, ctx.h, target.h, L.ptr(q), len(q), L.ptr(desc_q),
+                       q_set.h if q_set is not None else None, None, L.ptr(blocked0), C.byref(p), L.ptr(assign), L.ptr(dist),
+                       C.byref(nm))
+    call.keep = keep
+    call.result = lambda: (nm.value, assign, dist)
+    return call
+
+
 def measure(pkg, ctx, reps=200, cpu=True, oracle=None):
     syn = pkg.synth
     out = {}
@@ -52,6 +77,12 @@ def measure(pkg, ctx, reps=200, cpu=True, oracle=None):
     mt = pkg.ORBmatcher(ctx, 0.7, True)
     r = timeit(lambda: mt.SearchByBoW_KF_F(A, c["valid_a"], B), reps)
     r["launches"] = ctx.stat("gpu_launches")
+    import ctypes as C
+    L_ = pkg._lib
+    va = np.ascontiguousarray(c["valid_a"], np.uint8)
+    m1, d1, n1 = np.empty(B.n, np.int32), np.empty(B.n, np.float32), C.c_int32()
+    r["abi_call_ms"] = timeit(abi_closure(ctx.lib.asdm_search_by_bow_kf_f, ctx.h, A.h, L_.ptr(va), B.h, 0.7, 1, L_.ptr(m1), L_.ptr(d1),
+                                          C.byref(n1)), reps)["median_ms"]
     r["cpu_oracle_ms"] = cpu_time(lambda: oracle.search_by_bow_kf_f(c["desc_a"], c["kps_a"], c["fv_a"], c["valid_a"], c["desc_b"],
                                                                     c["kps_b"], c["fv_b"], 0.7, 1))
     # including the per-frame upload of the current frame (asdm_set_create + featvec), as Tracking would pay it
@@ -73,8 +104,16 @@ def measure(pkg, ctx, reps=200, cpu=True, oracle=None):
                                                       c["desc_q"], sf, th=1.0, blocked0=c["blocked0"]), reps)
     r["launches"] = ctx.stat("gpu_launches")
     # the C-ABI call alone, on the query records a C++ adaptor would have filled (asdm_proj_query array built beforehand)
-    r["abi_call_ms"] = timeit(lambda: mt.SearchByProjection(F, q, desc_q=c["desc_q"], blocked0=c["blocked0"], mode=pkg.ASDM_PROJ_RATIO_LEVEL,
-                                                            th_accept=1.5, best_init=256.0, count_twice=True, check_ori=False), reps)["median_ms"]
+    kw2 = dict(blocked0=c["blocked0"], mode=pkg.ASDM_PROJ_RATIO_LEVEL, th_accept=1.5, best_init=256.0, nnratio=c["nnratio"],
+               count_twice=True, check_ori=False)
+    r["abi_call_ms"] = timeit(abi_proj(pkg, ctx, F, q, desc_q=c["desc_q"], **kw2), reps)["median_ms"]
+    # the same with the map-point descriptors gathered by the adaptor into page-locked memory (asdm_host_alloc): the
+    # kernel reads the rows in place over PCIe, nothing is staged
+    pinned_q = ctx.pinned(c["desc_q"].shape, np.float32)
+    pinned_q[...] = c["desc_q"]
+    call = abi_proj(pkg, ctx, F, q, desc_q=pinned_q, **kw2)
+    r["abi_call_pinned_desc_ms"] = timeit(call, reps)["median_ms"]
+    res_pin = call.result()
     # map-point descriptors resident in a device pool (they only change in ComputeDistinctiveDescriptors): no descriptor
     # crosses PCIe per frame, the call ships the 8000 query records only
     pool = pkg.DescriptorSet(ctx, c["desc_q"])
@@ -83,9 +122,12 @@ def measure(pkg, ctx, reps=200, cpu=True, oracle=None):
     res_host = mt.SearchByProjection(F, q, desc_q=c["desc_q"], blocked0=c["blocked0"], mode=pkg.ASDM_PROJ_RATIO_LEVEL,
                                      th_accept=1.5, best_init=256.0, count_twice=True, check_ori=False)
     assert res_pool[0] == res_host[0] and np.array_equal(res_pool[1], res_host[1])
-    r["abi_call_resident_pool_ms"] = timeit(lambda: mt.SearchByProjection(F, q, q_set=pool, blocked0=c["blocked0"],
-                                                                          mode=pkg.ASDM_PROJ_RATIO_LEVEL, th_accept=1.5, best_init=256.0,
-                                                                          count_twice=True, check_ori=False), reps)["median_ms"]
+    assert res_pin[0] == res_host[0] and np.array_equal(res_pin[1], res_host[1])
+    r["abi_call_resident_pool_ms"] = timeit(abi_proj(pkg, ctx, F, q, q_set=pool, **kw2), reps)["median_ms"]
+    # k_proj_fused of the last call: [phase 1 of the resolving CTA, ticket, phase-2 set-up, sweeps, selection] ns + sweeps
+    r["kernel_phases_ns"] = [ctx.stat(f"proj_ns_{k}") for k in range(6)]
+    r["host_phases_ns"] = [ctx.stat(f"proj_host_ns_{k}") for k in range(3)]  # staging | launch | wait
+    r["algorithmic_bytes"] = int(8000 * 512 + 2000 * 512 + 2000 * 16 + (64 * 48 * 4 + 2000 * 4) + 8000 * 24 + 2000 * 8)
     pool.release()
     r["cpu_oracle_ms"] = cpu_time(lambda: oracle.search_by_projection(c["desc_t"], c["kps_t"], c["grid"], q, c["desc_q"], c["blocked0"],
                                                                       c["mode"], c["th_accept"], c["best_init"], c["nnratio"],
@@ -104,6 +146,10 @@ def measure(pkg, ctx, reps=200, cpu=True, oracle=None):
     r["launches"] = ctx.stat("gpu_launches")
     r["cpu_oracle_ms"] = cpu_time(lambda: oracle.stereo_row_match(s["desc_l"], s["kps_l"], s["desc_r"], s["kps_r"], s["scale_factors"],
                                                                   s["n_rows"], s["min_d"], s["max_d"]))
+    sfa = np.ascontiguousarray(s["scale_factors"], np.float32)
+    bs, ds = np.empty(L.n, np.int32), np.empty(L.n, np.float32)
+    r["abi_call_ms"] = timeit(abi_closure(ctx.lib.asdm_stereo_row_match, ctx.h, L.h, R.h, L_.ptr(sfa), len(sfa), int(s["n_rows"]),
+                                          float(s["min_d"]), float(s["max_d"]), L_.ptr(bs), L_.ptr(ds)), reps)["median_ms"]
     out["C3_stereo_row_match_1500"] = r
     r = timeit(lambda: mt.SearchByProjection(Cur, f["queries"], q_set=L, blocked0=f["blocked0"], mode=pkg.ASDM_PROJ_BEST_ONLY,
                                              th_accept=1.5, best_init=100.0), reps)
@@ -111,6 +157,10 @@ def measure(pkg, ctx, reps=200, cpu=True, oracle=None):
     r["cpu_oracle_ms"] = cpu_time(lambda: oracle.search_by_projection(f["desc_t"], f["kps_t"], f["grid"], f["queries"], f["desc_q"],
                                                                       f["blocked0"], f["mode"], f["th_accept"], f["best_init"],
                                                                       f["nnratio"], f["check_ori"], f["count_twice"]))
+    r["abi_call_ms"] = timeit(abi_proj(pkg, ctx, Cur, f["queries"], q_set=L, blocked0=f["blocked0"], mode=pkg.ASDM_PROJ_BEST_ONLY,
+                                       th_accept=1.5, best_init=100.0, nnratio=0.8, check_ori=True), reps)["median_ms"]
+    r["kernel_phases_ns"] = [ctx.stat(f"proj_ns_{k}") for k in range(6)]
+    r["host_phases_ns"] = [ctx.stat(f"proj_host_ns_{k}") for k in range(3)]
     out["C3_frame_to_frame_projection_1500_th15"] = r
     for x in (L, R, Cur):
         x.release()
