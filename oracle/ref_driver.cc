@@ -600,6 +600,38 @@ int ref_search_by_sim3(const float* desc1, const ora_kp* kps1, int n1, const flo
   return nf;
 }
 
+// Descriptor stage of Frame::ComputeStereoMatches (Frame.cc:360-447; dead code upstream, BASELINE config 3). The
+// reference's own text runs here (oracle/Makefile extracts :366-397, :399-444 and :447): this function only supplies the
+// members it names as locals. minD = 0 and maxD = mbf / mb in the reference (:391-393): mb = 1, mbf = max_d gives
+// maxD = max_d exactly. Right keypoints must keep their row bands inside the image (the reference indexes vRowIndices
+// without a bounds check, :384-387; its extractor keeps keypoints 19 px off the border).
+void ref_stereo_row_match(const float* desc_l, const ora_kp* kps_l, int n_l, const float* desc_r, const ora_kp* kps_r,
+                          int n_r, const float* scale_factors, int n_levels, int n_rows, float max_d, int32_t* best_r,
+                          float* best_dist) {
+  using namespace std;
+  struct Level0 { int rows; };
+  struct Extractor { vector<Level0> mvImagePyramid; } extractor;
+  extractor.mvImagePyramid.push_back(Level0{n_rows});
+  Extractor* mpORBextractorLeft = &extractor;
+  const int N = n_l;
+  vector<cv::KeyPoint> mvKeys = keypoints(kps_l, n_l), mvKeysRight = keypoints(kps_r, n_r);
+  vector<float> mvScaleFactors(scale_factors, scale_factors + n_levels);
+  cv::Mat mDescriptors = desc_mat(desc_l, n_l), mDescriptorsRight = desc_mat(desc_r, n_r);
+  const float mb = 1.0f, mbf = max_d;
+  for (int i = 0; i < n_l; i++) {
+    best_r[i] = -1;
+    best_dist[i] = -1.f;
+  }
+#include "_ref/gen/frame_stereo_a.inc"
+#include "_ref/gen/frame_stereo_b.inc"
+#include "_ref/gen/frame_stereo_c.inc"
+        {
+            best_r[iL] = (int32_t)bestIdxR;
+            best_dist[iL] = bestDist;
+        }
+    }
+}
+
 // MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:271-338) over a batch of map points. Observations of point p
 // are (obs_kf[e], obs_row[e]) for e in [obs_off[p], obs_off[p+1]), ascending and unique in obs_kf -- the reference
 // walks a std::map<KeyFrame*, size_t>, and the keyframes live in one array here so pointer order is index order.

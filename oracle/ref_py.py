@@ -375,3 +375,13 @@ def detect_loop_candidates(db, q_word, q_val, connected, min_score, only_global_
 def detect_reloc_candidates(db, q_word, q_val, reloc_score, only_global_map=False):
     import oracle_py
     return oracle_py.detect_reloc_candidates(db, q_word, q_val, reloc_score, only_global_map, _ref=klib())
+
+
+def stereo_row_match(desc_l, kps_l, desc_r, kps_r, scale_factors, n_rows, max_d):
+    """Descriptor stage of the reference's Frame::ComputeStereoMatches (Frame.cc:366-447, its own text): (best_r, dist)."""
+    desc_l, desc_r, sf = _f32(desc_l), _f32(desc_r), _f32(scale_factors)
+    best = np.empty(len(kps_l), np.int32)
+    dist = np.empty(len(kps_l), np.float32)
+    lib().ref_stereo_row_match(_p(desc_l), _p(kps_l), len(kps_l), _p(desc_r), _p(kps_r), len(kps_r), _p(sf), len(sf),
+                               int(n_rows), C.c_float(max_d), _p(best), _p(dist))
+    return best, dist

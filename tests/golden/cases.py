@@ -135,6 +135,26 @@ def cases():
     # MapPoint::ComputeDistinctiveDescriptors: few observations per point, and points seen from > 32 keyframes
     out.append(("distinct", "distinct", dict(c=S.config_distinctive(n_kf=10, n=200, n_points=300, seed_extra=1))))
     out.append(("distinct_many_obs", "distinct", dict(c=S.config_distinctive(n_kf=44, n=60, n_points=50, seed_extra=2, dup_frac=0.1))))
+    # ---- round 2 (appended: the cases above keep their seeds) -----------------------------------------------------
+    # Descriptor stage of Frame::ComputeStereoMatches (Frame.cc:366-447, a14 / BASELINE config 3). The reference indexes
+    # its row table without a bounds check, so right keypoints stay 8 px off the top and bottom (its extractor keeps 19).
+    # stereo_a: clean matches, many best distances in [0.5, 1.0) -- accepted only because thOrbDist is int((1.5+0.5)/2) = 1;
+    # stereo_b: noisier right descriptors, best distances on both sides of 1.0 and of TH_HIGH.
+    for name, n, noise in [("stereo_a", 700, 0.0), ("stereo_b", 500, 0.06)]:
+        s = dict(S.config3(n=n, seed_extra=40 + len(out))["stereo"])
+        kr = s["kps_r"].copy()
+        kr["y"] = np.clip(kr["y"], 8.0, s["n_rows"] - 9.0).astype(np.float32)
+        s["kps_r"] = kr
+        if noise:
+            rng = np.random.default_rng(41 + len(out))
+            s["desc_r"] = (s["desc_r"] + rng.normal(0, noise, s["desc_r"].shape)).astype(np.float32)
+        out.append((name, "stereo", dict(s=s)))
+    # One keyframe pair of each batched workload at FULL size, run through the reference itself (15-40 s each at
+    # generation time): C5 = SearchByBoW(KF, KF) 4000 x 4000 (0.85, rotation check), C4 = SearchForTriangulation 2000 x 2000.
+    c5 = S.config5(n=4000, n_pairs=1, n_kf=2, seed_extra=50)
+    out.append(("c5_full_pair", "bow_kfkf_full", dict(a=c5["kfs"][0], b=c5["kfs"][1], ratio=0.85, ori=1)))
+    c4 = S.config4(n=2000, n_pairs=1, seed_extra=51)
+    out.append(("c4_full_pair", "tri", dict(c=c4, ori=0)))
     return out
 
 
@@ -222,6 +242,16 @@ def run_case(ref, name, kind, a):
     elif kind == "distinct":
         c = a["c"]
         out[name + "/best"] = first_equal_observation(c, ref.distinctive(c["descs"], c["obs_off"], c["obs_kf"], c["obs_row"]))
+    elif kind == "stereo":
+        s = a["s"]
+        best, dist = ref.stereo_row_match(s["desc_l"], s["kps_l"], s["desc_r"], s["kps_r"], s["scale_factors"], s["n_rows"], s["max_d"])
+        out[name + "/best"], out[name + "/dist"] = best, dist
+    elif kind == "bow_kfkf_full":
+        x, y = a["a"], a["b"]
+        nm, m = ref.search_by_bow_kf_kf(x["desc"], x["kps"], x["fv"], x["valid"], y["desc"], y["kps"], y["fv"], y["valid"], a["ratio"], a["ori"])
+        i = np.nonzero(m >= 0)[0]
+        out[name + "/nm"], out[name + "/match"] = np.int32(nm), m
+        out[name + "/dist"] = pair_dists(ref, x["desc"], y["desc"], i, m[i])
     elif kind == "sim3":
         nf, m = ref.search_by_sim3(a["desc1"], a["kps1"], a["desc2"], a["kps2"], a["grid"], a["valid1"], a["valid2"], a["uv1"], a["uv2"],
                                    a["level1"], a["level2"], a["desc1"], a["desc2"], a["already1"], S.scale_factors(), a["th"])

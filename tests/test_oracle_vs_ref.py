@@ -261,3 +261,22 @@ def test_compute_distinctive_descriptors(pkg, oracle, ref, n_kf, n, n_points, ma
     assert np.array_equal(np.isnan(want[:, 0]), nobs == 0)
     assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
     assert (best > 0).sum() > 0
+
+
+@pytest.mark.parametrize("n,seed,noise", [(900, 1, 0.0), (300, 2, 0.05), (40, 3, 0.0), (1, 4, 0.0)])
+def test_stereo_row_match_against_the_reference_text(pkg, oracle, ref, n, seed, noise):
+    """a14: the oracle's restatement of Frame::ComputeStereoMatches' descriptor stage against the reference's own lines
+    (Frame.cc:366-447, extracted by oracle/Makefile). Right keypoints keep their row bands inside the image: the
+    reference indexes vRowIndices without a bounds check."""
+    s = pkg.synth.config3(n=n, seed_extra=seed)["stereo"]
+    kr = s["kps_r"].copy()
+    kr["y"] = np.clip(kr["y"], 8.0, s["n_rows"] - 9.0).astype(np.float32)
+    dr = s["desc_r"]
+    if noise:
+        dr = (dr + np.random.default_rng(seed).normal(0, noise, dr.shape)).astype(np.float32)
+    ob, od = oracle.stereo_row_match(s["desc_l"], s["kps_l"], dr, kr, s["scale_factors"], s["n_rows"], 0.0, s["max_d"])
+    rb, rd = ref.stereo_row_match(s["desc_l"], s["kps_l"], dr, kr, s["scale_factors"], s["n_rows"], s["max_d"])
+    assert np.array_equal(ob, rb)
+    assert np.array_equal(od.view(np.uint32), rd.view(np.uint32))
+    if n >= 300:
+        assert (rb >= 0).sum() > n // 4
