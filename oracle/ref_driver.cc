@@ -80,6 +80,115 @@ cv::Mat vec3(float x, float y, float z) {
   return v;
 }
 
+// ---- scene: where the harness puts cameras and map points -------------------------------------------------------
+// mode 0 (default): identity poses, fx = fy = 1, cx = cy = 0, points (u, v, 1): every projection is exact in any
+// arithmetic, so the flat oracle (which takes windows, not poses) can be compared with the reference bit for bit.
+// mode 1 (ref_set_scene): EuRoC intrinsics, a random SE3 pose (a second one for the other frame / keyframe), a Sim3
+// scale != 1, per-point depths 1.5 .. 11.5 m with ~6 % of the points BEHIND the camera, ~15 % outside the distance-
+// invariance band (above and below), ~15 % of the normals beyond the 60 degree viewing gate. A point meant to project
+// at (u, v) is placed at T^-1 * backproject(u, v, z); the reference's own arithmetic (shim cv::Mat products) then
+// lands within rounding of (u, v). Used for the adaptor-level goldens: reference and adaptor see identical objects.
+struct Scene {
+  int mode = 0;
+  uint32_t seed = 0;
+  float fx = 1, fy = 1, cx = 0, cy = 0;
+  double R[2][9] = {{1, 0, 0, 0, 1, 0, 0, 0, 1}, {1, 0, 0, 0, 1, 0, 0, 0, 1}}, t[2][3] = {{0, 0, 0}, {0, 0, 0}};
+  double s = 1.0;  // scale of the Sim3 overloads (Scw = [sR | st])
+} g_scene;
+
+double hash01(uint32_t i, uint32_t salt) {
+  uint32_t x = i * 2654435761u ^ (salt * 40503u + g_scene.seed * 69069u + 12345u);
+  x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+  return (x >> 8) * (1.0 / 16777216.0);
+}
+
+void rodrigues(double ax, double ay, double az, double ang, double* R) {
+  const double n = std::sqrt(ax * ax + ay * ay + az * az);
+  ax /= n; ay /= n; az /= n;
+  const double c = std::cos(ang), s = std::sin(ang), C = 1 - c;
+  const double M[9] = {c + ax * ax * C, ax * ay * C - az * s, ax * az * C + ay * s, ay * ax * C + az * s, c + ay * ay * C,
+                       ay * az * C - ax * s, az * ax * C - ay * s, az * ay * C + ax * s, c + az * az * C};
+  for (int k = 0; k < 9; k++) R[k] = M[k];
+}
+
+cv::Mat scene_T(int cam, double scale = 1.0) {  // 4x4 [scale*R | scale*t]
+  cv::Mat T(4, 4, CV_32F);
+  for (int r = 0; r < 3; r++) {
+    for (int c = 0; c < 3; c++) T.at<float>(r, c) = (float)(scale * g_scene.R[cam][3 * r + c]);
+    T.at<float>(r, 3) = (float)(scale * g_scene.t[cam][r]);
+  }
+  T.at<float>(3, 3) = 1.f;
+  return T;
+}
+
+void scene_center(int cam, double* O) {  // -R^T t
+  for (int c = 0; c < 3; c++) {
+    O[c] = 0;
+    for (int r = 0; r < 3; r++) O[c] -= g_scene.R[cam][3 * r + c] * g_scene.t[cam][r];
+  }
+}
+
+double scene_depth(int i) {
+  if (g_scene.mode == 0) return 1.0;
+  if (hash01((uint32_t)i, 1) < 0.06) return -(1.0 + 5.0 * hash01((uint32_t)i, 2));  // behind the camera
+  return 1.5 + 10.0 * hash01((uint32_t)i, 3);
+}
+
+// camera-frame point that projects to (u, v) at the depth of point i
+void scene_backproject(float u, float v, int i, double* Xc) {
+  const double z = scene_depth(i);
+  Xc[0] = ((double)u - g_scene.cx) * z / g_scene.fx;
+  Xc[1] = ((double)v - g_scene.cy) * z / g_scene.fy;
+  Xc[2] = z;
+}
+
+void scene_to_world(int cam, const double* Xc, double* Xw) {  // R^T (Xc - t)
+  for (int c = 0; c < 3; c++) {
+    Xw[c] = 0;
+    for (int r = 0; r < 3; r++) Xw[c] += g_scene.R[cam][3 * r + c] * (Xc[r] - g_scene.t[cam][r]);
+  }
+}
+
+cv::Mat scene_point(int cam, float u, float v, int i) {
+  if (g_scene.mode == 0) return vec3(u, v, 1.f);
+  double Xc[3], Xw[3];
+  scene_backproject(u, v, i, Xc);
+  scene_to_world(cam, Xc, Xw);
+  return vec3((float)Xw[0], (float)Xw[1], (float)Xw[2]);
+}
+
+// distance-invariance band of point p seen from camera `cam` such that PredictScale returns `lvl`
+// (MapPoint.cc:421-453: ceil(log(max/dist)/log(1.2)); the middle of the level's bin), or a band the point is outside of
+void scene_band(MapPoint* p, int cam, int lvl, int i) {
+  double O[3];
+  scene_center(cam, O);
+  const double dx = p->mWorldPos.at<float>(0) - O[0], dy = p->mWorldPos.at<float>(1) - O[1], dz = p->mWorldPos.at<float>(2) - O[2];
+  const float dist = (float)std::sqrt(dx * dx + dy * dy + dz * dz);
+  p->mfMaxDistance = dist * std::pow(1.2f, (float)lvl - 0.5f);
+  p->mfMinDistance = 0.f;
+  if (g_scene.mode == 0) return;
+  const double h = hash01((uint32_t)i, 4);
+  if (h < 0.08) p->mfMaxDistance = dist / 1.5f;       // farther than 1.2 * max
+  else if (h < 0.15) p->mfMinDistance = dist * 1.6f;  // nearer than 0.8 * min
+}
+
+// viewing direction of point p from camera `cam`; in scene mode ~15 % are tilted 75 degrees away (cos < 0.5)
+cv::Mat scene_normal(const MapPoint* p, int cam, int i) {
+  double O[3];
+  scene_center(cam, O);
+  double n[3] = {p->mWorldPos.at<float>(0) - O[0], p->mWorldPos.at<float>(1) - O[1], p->mWorldPos.at<float>(2) - O[2]};
+  const double d = std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+  for (double& x : n) x /= d;
+  if (g_scene.mode && hash01((uint32_t)i, 5) < 0.15) {
+    double q[3] = {n[1], -n[0], 0.0};  // perpendicular (n is never along z alone here)
+    double qn = std::sqrt(q[0] * q[0] + q[1] * q[1]);
+    if (qn < 1e-9) { q[0] = 1; q[1] = 0; qn = 1; }
+    const double c = std::cos(75.0 * M_PI / 180.0), s = std::sin(75.0 * M_PI / 180.0);
+    for (int k = 0; k < 3; k++) n[k] = c * n[k] + s * q[k] / qn;
+  }
+  return vec3((float)n[0], (float)n[1], (float)n[2]);
+}
+
 void levels(const float* sf, const float* sigma2, int n_levels, float log_scale, std::vector<float>& vsf,
             std::vector<float>& vs2, std::vector<float>& vis2, int& nl, float& lsf) {
   vsf.assign(sf, sf + n_levels);
@@ -99,8 +208,9 @@ void fill_frame(Frame& F, const float* desc, const ora_kp* kps, int n, const ora
   F.mDescriptors = desc_mat(desc, n);
   F.mvpMapPoints.assign((size_t)n, nullptr);
   F.mvbOutlier.assign((size_t)n, false);
-  F.mTcw = eye4();
-  Frame::fx = Frame::fy = 1.f; Frame::cx = Frame::cy = 0.f;
+  F.mTcw = scene_T(0);
+  Frame::fx = g_scene.fx; Frame::fy = g_scene.fy; Frame::cx = g_scene.cx; Frame::cy = g_scene.cy;
+  Frame::invfx = 1.f / Frame::fx; Frame::invfy = 1.f / Frame::fy;
   if (g) {
     Frame::mnMinX = g->min_x; Frame::mnMaxX = g->max_x; Frame::mnMinY = g->min_y; Frame::mnMaxY = g->max_y;
     Frame::mfGridElementWidthInv = g->inv_w; Frame::mfGridElementHeightInv = g->inv_h;
@@ -108,14 +218,21 @@ void fill_frame(Frame& F, const float* desc, const ora_kp* kps, int n, const ora
   }
 }
 
+void set_keyframe_camera(KeyFrame& K, int cam) {
+  K.Tcw = scene_T(cam);
+  double O[3];
+  scene_center(cam, O);
+  K.Ow = vec3((float)O[0], (float)O[1], (float)O[2]);
+  K.fx = g_scene.fx; K.fy = g_scene.fy; K.cx = g_scene.cx; K.cy = g_scene.cy;
+  K.invfx = 1.f / K.fx; K.invfy = 1.f / K.fy;
+}
+
 void fill_keyframe(KeyFrame& K, const float* desc, const ora_kp* kps, int n, const ora_grid* g) {
   K.N = n;
   K.mvKeys = K.mvKeysUn = keypoints(kps, n);
   K.mDescriptors = desc_mat(desc, n);
   K.mvpMapPoints.assign((size_t)n, nullptr);
-  K.Tcw = eye4();
-  K.Ow = vec3(0, 0, 0);
-  K.fx = K.fy = 1.f; K.cx = K.cy = 0.f; K.invfx = K.invfy = 1.f;
+  set_keyframe_camera(K, 0);
   if (g) {
     K.mnMinX = (int)g->min_x; K.mnMaxX = (int)g->max_x; K.mnMinY = (int)g->min_y; K.mnMaxY = (int)g->max_y;
     K.mfGridElementWidthInv = g->inv_w; K.mfGridElementHeightInv = g->inv_h;
@@ -152,6 +269,20 @@ void attach_valid(Pool& pool, KeyFrame& K, const uint8_t* valid, int n) {
 }  // namespace
 
 extern "C" {
+
+// ------------------------------------------------------------------------------------------- scene
+void ref_set_scene(int mode, unsigned seed) {
+  g_scene = Scene();
+  if (!mode) return;
+  g_scene.mode = 1;
+  g_scene.seed = seed;
+  g_scene.fx = 458.654f; g_scene.fy = 457.296f; g_scene.cx = 367.215f; g_scene.cy = 248.375f;  // EuRoC cam0
+  for (int cam = 0; cam < 2; cam++) {
+    rodrigues(hash01(cam, 10) - 0.5, hash01(cam, 11) - 0.5, hash01(cam, 12) + 0.2, 0.1 + 0.4 * hash01(cam, 13), g_scene.R[cam]);
+    for (int k = 0; k < 3; k++) g_scene.t[cam][k] = 2.0 * hash01(cam, 14 + k) - 1.0;
+  }
+  g_scene.s = 0.9 + 0.4 * hash01(7, 17);
+}
 
 // ------------------------------------------------------------------------------------------- scalar pieces
 float ref_descriptor_distance(const float* a, const float* b) {
@@ -368,7 +499,7 @@ int ref_sbp_frame_frame(const float* desc_t, const ora_kp* kps_t, int n_t, const
       Cur.mvpMapPoints[j]->nObs = 1;
     }
   Last.N = n_q;
-  Last.mTcw = eye4();
+  Last.mTcw = scene_T(1);
   Last.mvKeys.resize((size_t)n_q);
   Last.mvKeysUn.resize((size_t)n_q);
   Last.mvpMapPoints.assign((size_t)n_q, nullptr);
@@ -378,7 +509,7 @@ int ref_sbp_frame_frame(const float* desc_t, const ora_kp* kps_t, int n_t, const
     Last.mvKeys[i].angle = Last.mvKeysUn[i].angle = q[i].angle;
     if (!q[i].valid && !(i & 1)) continue;
     MapPoint* p = pool.make(i);
-    p->mWorldPos = vec3(q[i].u, q[i].v, 1.f);
+    p->mWorldPos = scene_point(0, q[i].u, q[i].v, i);
     p->nObs = q[i].blocks ? 1 : 0;
     p->mDescriptor = desc_row(desc_q + (size_t)i * ORA_DESC_DIM);
     Last.mvpMapPoints[i] = p;
@@ -395,6 +526,31 @@ static void set_distance_for_level(MapPoint* p, float u, float v, int lvl) {
   const float dist = std::sqrt(u * u + v * v + 1.f);
   p->mfMaxDistance = dist * std::pow(1.2f, (float)lvl - 0.5f);
   p->mfMinDistance = 0.f;
+}
+
+// band for a point whose distance to the observing camera is `dist` (scene mode; see scene_band)
+static void band_for_dist(MapPoint* p, float dist, int lvl, int i) {
+  p->mfMaxDistance = dist * std::pow(1.2f, (float)lvl - 0.5f);
+  p->mfMinDistance = 0.f;
+  const double h = hash01((uint32_t)i, 4);
+  if (h < 0.08) p->mfMaxDistance = dist / 1.5f;
+  else if (h < 0.15) p->mfMinDistance = dist * 1.6f;
+}
+
+// world position, distance band and (optionally) normal of candidate point i that should project to (u, v) in camera 0
+static void place_point(MapPoint* p, float u, float v, int lvl, int i, bool with_normal) {
+  if (g_scene.mode == 0) {  // exactly the objects the identity-pose goldens were generated from
+    p->mWorldPos = vec3(u, v, 1.f);
+    set_distance_for_level(p, u, v, lvl);
+    if (with_normal) {
+      const float d = std::sqrt(u * u + v * v + 1.f);
+      p->mNormalVector = vec3(u / d, v / d, 1.f / d);
+    }
+    return;
+  }
+  p->mWorldPos = scene_point(0, u, v, i);
+  scene_band(p, 0, lvl, i);
+  if (with_normal) p->mNormalVector = scene_normal(p, 0, i);
 }
 
 // a6: SearchByProjection(Frame& Cur, KeyFrame*, sAlreadyFound, th, ORBdist)  (ORBmatcher.cc:1455-1582);
@@ -420,8 +576,7 @@ int ref_sbp_frame_keyframe(const float* desc_t, const ora_kp* kps_t, int n_t, co
     K.mvKeysUn[i].angle = q[i].angle;
     if (!q[i].valid && i % 3 == 0) continue;
     MapPoint* p = pool.make(i);
-    p->mWorldPos = vec3(q[i].u, q[i].v, 1.f);
-    set_distance_for_level(p, q[i].u, q[i].v, level[i]);
+    place_point(p, q[i].u, q[i].v, level[i], i, false);
     p->mDescriptor = desc_row(desc_q + (size_t)i * ORA_DESC_DIM);
     K.mvpMapPoints[i] = p;
     if (!q[i].valid) {
@@ -452,16 +607,13 @@ int ref_sbp_keyframe_sim3(const float* desc_t, const ora_kp* kps_t, int n_t, con
   std::vector<MapPoint*> pts((size_t)n_q);
   for (int i = 0; i < n_q; i++) {
     MapPoint* p = pool.make(i);
-    p->mWorldPos = vec3(q[i].u, q[i].v, 1.f);
-    set_distance_for_level(p, q[i].u, q[i].v, level[i]);
-    const float d = std::sqrt(q[i].u * q[i].u + q[i].v * q[i].v + 1.f);
-    p->mNormalVector = vec3(q[i].u / d, q[i].v / d, 1.f / d);
+    place_point(p, q[i].u, q[i].v, level[i], i, true);
     p->mDescriptor = desc_row(desc_q + (size_t)i * ORA_DESC_DIM);
     if (!q[i].valid) p->mbBad = true;
     pts[i] = p;
   }
   ORBmatcher m(nnratio, true);
-  const int nm = m.SearchByProjection(&K, eye4(), pts, matched, th);
+  const int nm = m.SearchByProjection(&K, scene_T(0, g_scene.s), pts, matched, th);
   for (int j = 0; j < n_t; j++) assign[j] = (matched[j] && matched[j]->id >= 0) ? matched[j]->id : -1;
   return nm;
 }
@@ -492,10 +644,7 @@ struct FuseRig {
     for (int i = 0; i < n_q; i++) {
       if (!q[i].valid && (i % 3) == 0) continue;  // null entry (Fuse(KF, vector) tolerates them)
       MapPoint* p = pool.make(i);
-      p->mWorldPos = vec3(q[i].u, q[i].v, 1.f);
-      set_distance_for_level(p, q[i].u, q[i].v, level[i]);
-      const float d = std::sqrt(q[i].u * q[i].u + q[i].v * q[i].v + 1.f);
-      p->mNormalVector = vec3(q[i].u / d, q[i].v / d, 1.f / d);
+      place_point(p, q[i].u, q[i].v, level[i], i, true);
       p->mDescriptor = desc_row(desc_q + (size_t)i * ORA_DESC_DIM);
       p->nObs = mp_obs[i];
       if (!q[i].valid) p->mbBad = true;
@@ -541,7 +690,7 @@ int ref_fuse_sim3(const float* desc_t, const ora_kp* kps_t, int n_t, const ora_g
     }
   std::vector<MapPoint*> repl((size_t)n_q, nullptr);
   ORBmatcher m(0.8f, true);
-  const int nf = m.Fuse(&R.K, eye4(), R.pts, th, repl);
+  const int nf = m.Fuse(&R.K, scene_T(0, g_scene.s), R.pts, th, repl);
   for (int i = 0; i < n_q; i++) {
     replace[i] = repl[i] ? repl[i]->GetIndexInKeyFrame(&R.K) : -1;
     added[i] = R.pts[i]->mObservations.count(&R.K) ? (int)R.pts[i]->mObservations[&R.K] : -1;
@@ -565,12 +714,29 @@ int ref_search_by_sim3(const float* desc1, const ora_kp* kps1, int n1, const flo
          K1.mnScaleLevels, lsf);
   K1.mfLogScaleFactor = lsf;
   K2.mvScaleFactors = K1.mvScaleFactors; K2.mnScaleLevels = n_levels; K2.mfLogScaleFactor = lsf;
+  // relative Sim3 (camera 2 -> camera 1): identity in mode 0; in scene mode a genuine one, KF2 on the second pose
+  double R12d[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, t12d[3] = {0, 0, 0}, s12d = 1.0;
+  if (g_scene.mode) {
+    set_keyframe_camera(K2, 1);
+    rodrigues(0.3, -0.5, 0.8, 0.21, R12d);
+    t12d[0] = 0.3; t12d[1] = -0.2; t12d[2] = 0.12;
+    s12d = 1.1;
+  }
   for (int i = 0; i < n1; i++)
     if (valid1[i] || (i & 1)) {
       MapPoint* p = pool.make(i);
       p->mbBad = !valid1[i];
-      p->mWorldPos = vec3(uv1[2 * i], uv1[2 * i + 1], 1.f);
-      set_distance_for_level(p, uv1[2 * i], uv1[2 * i + 1], level1[i]);
+      if (g_scene.mode == 0) {
+        p->mWorldPos = vec3(uv1[2 * i], uv1[2 * i + 1], 1.f);
+        set_distance_for_level(p, uv1[2 * i], uv1[2 * i + 1], level1[i]);
+      } else {  // seen in camera 2 at uv1: Xc2 -> Xc1 = s12 R12 Xc2 + t12 -> world through camera 1 (pose 0)
+        double X2[3], X1[3], Xw[3];
+        scene_backproject(uv1[2 * i], uv1[2 * i + 1], i, X2);
+        for (int r = 0; r < 3; r++) X1[r] = s12d * (R12d[3 * r] * X2[0] + R12d[3 * r + 1] * X2[1] + R12d[3 * r + 2] * X2[2]) + t12d[r];
+        scene_to_world(0, X1, Xw);
+        p->mWorldPos = vec3((float)Xw[0], (float)Xw[1], (float)Xw[2]);
+        band_for_dist(p, (float)std::sqrt(X2[0] * X2[0] + X2[1] * X2[1] + X2[2] * X2[2]), level1[i], i);
+      }
       p->mDescriptor = desc_row(mpdesc1 + (size_t)i * ORA_DESC_DIM);
       K1.mvpMapPoints[i] = p;
     }
@@ -578,8 +744,18 @@ int ref_search_by_sim3(const float* desc1, const ora_kp* kps1, int n1, const flo
     if (valid2[j] || (j & 1)) {
       MapPoint* p = pool.make(j);
       p->mbBad = !valid2[j];
-      p->mWorldPos = vec3(uv2[2 * j], uv2[2 * j + 1], 1.f);
-      set_distance_for_level(p, uv2[2 * j], uv2[2 * j + 1], level2[j]);
+      if (g_scene.mode == 0) {
+        p->mWorldPos = vec3(uv2[2 * j], uv2[2 * j + 1], 1.f);
+        set_distance_for_level(p, uv2[2 * j], uv2[2 * j + 1], level2[j]);
+      } else {  // seen in camera 1 at uv2: Xc1 -> Xc2 = (1/s12) R12^T (Xc1 - t12) -> world through camera 2 (pose 1)
+        double X1[3], X2[3], Xw[3];
+        scene_backproject(uv2[2 * j], uv2[2 * j + 1], 100000 + j, X1);
+        for (int c = 0; c < 3; c++)
+          X2[c] = (R12d[c] * (X1[0] - t12d[0]) + R12d[3 + c] * (X1[1] - t12d[1]) + R12d[6 + c] * (X1[2] - t12d[2])) / s12d;
+        scene_to_world(1, X2, Xw);
+        p->mWorldPos = vec3((float)Xw[0], (float)Xw[1], (float)Xw[2]);
+        band_for_dist(p, (float)std::sqrt(X1[0] * X1[0] + X1[1] * X1[1] + X1[2] * X1[2]), level2[j], 100000 + j);
+      }
       p->mDescriptor = desc_row(mpdesc2 + (size_t)j * ORA_DESC_DIM);
       p->mObservations[&K2] = (size_t)j;
       K2.mvpMapPoints[j] = p;
@@ -592,10 +768,11 @@ int ref_search_by_sim3(const float* desc1, const ora_kp* kps1, int n1, const flo
       pre.push_back(m12[i]);
     }
   cv::Mat R12(3, 3, CV_32F);
-  for (int i = 0; i < 3; i++) R12.at<float>(i, i) = 1.f;
+  for (int r = 0; r < 3; r++)
+    for (int c = 0; c < 3; c++) R12.at<float>(r, c) = (float)R12d[3 * r + c];
   ORBmatcher m(0.85f, true);
-  const float s12 = 1.f;
-  const int nf = m.SearchBySim3(&K1, &K2, m12, s12, R12, vec3(0, 0, 0), th);
+  const float s12 = (float)s12d;
+  const int nf = m.SearchBySim3(&K1, &K2, m12, s12, R12, vec3((float)t12d[0], (float)t12d[1], (float)t12d[2]), th);
   for (int i = 0; i < n1; i++) match12[i] = m12[i] ? m12[i]->id : -1;
   return nf;
 }

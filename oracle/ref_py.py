@@ -385,3 +385,9 @@ def stereo_row_match(desc_l, kps_l, desc_r, kps_r, scale_factors, n_rows, max_d)
     lib().ref_stereo_row_match(_p(desc_l), _p(kps_l), len(kps_l), _p(desc_r), _p(kps_r), len(kps_r), _p(sf), len(sf),
                                int(n_rows), C.c_float(max_d), _p(best), _p(dist))
     return best, dist
+
+
+def set_scene(mode=0, seed=0):
+    """mode 0: identity poses (the flat goldens); mode 1: real intrinsics, random SE3 / Sim3 poses, points behind the
+    camera, outside the distance band and beyond the viewing gate (oracle/ref_driver.cc `Scene`). Global: reset to 0."""
+    lib().ref_set_scene(int(mode), C.c_uint(int(seed)))

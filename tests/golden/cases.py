@@ -155,6 +155,15 @@ def cases():
     out.append(("c5_full_pair", "bow_kfkf_full", dict(a=c5["kfs"][0], b=c5["kfs"][1], ratio=0.85, ori=1)))
     c4 = S.config4(n=2000, n_pairs=1, seed_extra=51)
     out.append(("c4_full_pair", "tri", dict(c=c4, ori=0)))
+    # The pose-dependent overloads once more with REAL poses (oracle/ref_driver.cc `Scene`, mode 1): EuRoC intrinsics,
+    # random SE3 / Sim3, ~6 % of the points behind the camera, ~15 % outside the distance-invariance band, ~15 % of the
+    # normals beyond the 60 degree gate. These exercise the host-side gates of the adaptor (Rcw*x3Dw+tcw, PredictScale,
+    # decompose_sim3 ...: ORBmatcher.cc:331-368, 852-888, 1459-1510); the flat C ABI and the oracle take windows, not
+    # poses, so only tests/test_adaptor.py runs them (reference build for the golden file, adaptor build on the GPU).
+    base = {n: (k, a) for n, k, a in out}
+    for n in ("proj_f2f", "proj_reloc", "proj_sim3", "fuse", "fuse_sim3", "sim3"):
+        k, a = base[n]
+        out.append((n + "_posed", k, dict(a, scene=7 + len(out))))
     return out
 
 
@@ -186,12 +195,18 @@ def pair_dists(ref, da, db, ia, ib):
     return np.array([ref.descriptor_distance(da[i], db[j]) for i, j in zip(ia, ib)], np.float32)
 
 
-def run_case(ref, name, kind, a):
+def run_case(ref, name, kind, a, sha=None):
     """Runs one case through the flat ref_* harness API (oracle/ref_py.py) -- the reference build for the golden file,
     or the C++ adaptor build under test -- and returns {name/key: array}."""
+    if "scene" in a:  # real poses (see cases()): the harness keeps the scene in a global, reset whatever happens
+        ref.set_scene(1, a["scene"])
+        try:
+            return run_case(ref, name, kind, {k: v for k, v in a.items() if k != "scene"}, sha=digest(a))
+        finally:
+            ref.set_scene(0, 0)
     S = synth()
     out = {}
-    out[name + "/sha"] = np.frombuffer(bytes.fromhex(digest(a)), np.uint8)
+    out[name + "/sha"] = np.frombuffer(bytes.fromhex(sha or digest(a)), np.uint8)
     if kind == "bow":
         c = a["c"]
         nm, m = ref.search_by_bow_kf_f(c["desc_a"], c["kps_a"], c["fv_a"], c["valid_a"], c["desc_b"], c["kps_b"], c["fv_b"], a["ratio"], a["ori"])
