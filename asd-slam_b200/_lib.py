@@ -36,6 +36,11 @@ EXPORTS = [
     "asdm_job_prepare", "asdm_job_run", "asdm_job_fetch", "asdm_job_fetch_async", "asdm_job_settle", "asdm_job_out_stride",
     "asdm_job_device_outputs", "asdm_job_destroy",
     "asdm_shared_alloc", "asdm_shared_open", "asdm_shared_close", "asdm_shared_free", "asdm_job_set_publish",
+    "asdm_group_create", "asdm_group_join", "asdm_group_destroy", "asdm_group_last_error", "asdm_group_world",
+    "asdm_group_local_count", "asdm_group_local_rank", "asdm_group_ctx", "asdm_group_host_alloc", "asdm_group_host_free",
+    "asdm_group_host_barrier", "asdm_group_sets_create", "asdm_group_job_prepare", "asdm_group_job_units",
+    "asdm_group_job_stride", "asdm_group_job_run", "asdm_group_job_wait", "asdm_group_job_counts", "asdm_group_job_fetch",
+    "asdm_group_job_gathered", "asdm_group_job_destroy",
     "asdm_distinctive_descriptors",
     "asdm_vocab_create", "asdm_vocab_release", "asdm_vocab_transform",
     "asdm_bowdb_create", "asdm_bowdb_release", "asdm_bowdb_add", "asdm_bowdb_erase", "asdm_bowdb_clear", "asdm_bowdb_size",
@@ -75,6 +80,14 @@ class JobDesc(C.Structure):
                 ("nnratio", C.c_float), ("check_ori", C.c_int32), ("F12", C.c_void_p), ("epipoles", C.c_void_p),
                 ("scale_factors", C.c_void_p), ("level_sigma2", C.c_void_p), ("n_levels", C.c_int32),
                 ("row_begin", C.c_void_p), ("row_end", C.c_void_p)]
+
+
+class GJobDesc(C.Structure):
+    _fields_ = [("job", JobDesc), ("blocks_per_pair", C.c_int32), ("gather", C.c_int32)]
+
+
+ASDM_GATHER_DEVICE = 1
+ALLGATHER_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t)
 
 
 class VocabDesc(C.Structure):
@@ -143,6 +156,29 @@ def load():
     lib.asdm_shared_free.argtypes = [vp, vp]
     lib.asdm_job_set_publish.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.c_int, C.c_int, C.c_int]
     lib.asdm_job_destroy.argtypes = [vp]
+    lib.asdm_group_create.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_size_t, C.POINTER(vp)]
+    lib.asdm_group_join.argtypes = [vp, C.c_int, C.c_int, C.c_size_t, ALLGATHER_FN, vp, C.POINTER(vp)]
+    lib.asdm_group_destroy.argtypes = [vp]
+    lib.asdm_group_last_error.argtypes = [vp]
+    lib.asdm_group_last_error.restype = C.c_char_p
+    lib.asdm_group_world.argtypes = [vp]
+    lib.asdm_group_local_count.argtypes = [vp]
+    lib.asdm_group_local_rank.argtypes = [vp, C.c_int]
+    lib.asdm_group_ctx.argtypes = [vp, C.c_int]
+    lib.asdm_group_ctx.restype = vp
+    lib.asdm_group_host_alloc.argtypes = [vp, C.c_size_t, C.POINTER(vp)]
+    lib.asdm_group_host_free.argtypes = [vp, vp]
+    lib.asdm_group_host_barrier.argtypes = [vp]
+    lib.asdm_group_sets_create.argtypes = [vp, C.POINTER(SetDesc), C.c_int, C.POINTER(vp)]
+    lib.asdm_group_job_prepare.argtypes = [vp, C.POINTER(GJobDesc), C.POINTER(vp)]
+    lib.asdm_group_job_units.argtypes = [vp]
+    lib.asdm_group_job_stride.argtypes = [vp]
+    lib.asdm_group_job_run.argtypes = [vp, vp, vp, vp]
+    lib.asdm_group_job_wait.argtypes = [vp]
+    lib.asdm_group_job_counts.argtypes = [vp, vp, vp]
+    lib.asdm_group_job_fetch.argtypes = [vp, vp, vp, vp]
+    lib.asdm_group_job_gathered.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
+    lib.asdm_group_job_destroy.argtypes = [vp]
     lib.asdm_distinctive_descriptors.argtypes = [vp, C.POINTER(vp), C.c_int, C.c_int, vp, vp, vp, vp, vp]
     lib.asdm_desc_block_bytes.argtypes = [C.c_int]
     lib.asdm_desc_block_bytes.restype = C.c_size_t

@@ -115,7 +115,22 @@ struct asdm_set {
   uint32_t* node_id = nullptr;    // [n] FeatureVector node of the feature
   int32_t* fv_pos = nullptr;      // [n] CSR position of the feature in the FeatureVector, -1 if absent
   std::vector<uint8_t> tmap_bf;   // CUtensorMap (128 B) over desc_bf, built lazily
+  // Sets replicated over a multi-GPU group (group.cu) are VIEWS into the group's device window: rows, bf16 copy, norms,
+  // keypoints and FeatureVector arrays belong to the slab of their batch (refcounted), only the grid bucket is the
+  // set's own (allocated by the first projection-gated search).
+  struct GroupSlab* slab = nullptr;
+  void* grid_mem = nullptr;
 };
+
+struct asdm_group;
+struct GroupSlab {
+  asdm_group* g = nullptr;
+  int member = 0;            // local member whose window holds this copy
+  size_t off = 0, bytes = 0; // range of the window
+  int ref = 0;               // sets alive (guarded by the context mutex of the member)
+  int32_t* h_flags = nullptr; // page-locked [n_sets]: tensor-core range flags of the batch, copied back after the exchange
+};
+void group_slab_release(GroupSlab* s);  // group.cu
 
 // DBoW2 vocabulary tree resident on the device (kernels_vocab.cuh) plus the host copies of what the BowVector needs
 struct asdm_vocab {
@@ -138,7 +153,11 @@ struct asdm_vocab {
 #define ASDM_MAX_PEERS 16
 struct PublishArgs {
   int n = 0;                        // 0 = the job keeps its results local
-  int row0 = 0;                     // first row of this rank's records (rank * per_rank)
+  int row0 = 0;                     // record slot of local unit k = row0 + k * row_step (counts always; rows unless row_map)
+  int row_step = 1;                 // 1: this rank's units are contiguous (rank-major); world: round-robin deal, unit-major
+  const int32_t* row_map = nullptr; // device array [n_pairs], or null: destination ROW of unit k when units are row blocks
+                                    // of a pair (several units share a row and each publishes only its own columns)
+  int col_range = 0;                // 1: publish columns [rowA0, rowA1) of the unit only (row-block units)
   int stride = 0;                   // entries per row of the gathered arrays
   int multicast = 0;                // destinations are NVLink multicast (NVLS) addresses: one store reaches every rank
   int no_dist = 0;                  // publish index lists + counts only (what the reference calls return); distances stay local

@@ -9,6 +9,7 @@
 
 #include "host_util.cuh"
 #include "kernels_dense.cuh"
+#include "jobs.cuh"
 
 // Smallest keep threshold t such that a candidate farther than t can neither be accepted (d > TH_LOW) nor make
 // the ratio test fail as second best: for every fp32 d > t, fl(nnratio*d) > th_accept >= best1.
@@ -27,38 +28,7 @@ void jobs_init_device() {
 }
 
 // ------------------------------------------------------------------------------- batched keyframe-pair jobs
-struct asdm_job {
-  asdm_ctx* ctx = nullptr;
-  int kind = 0;
-  int n_pairs = 0;
-  int n_stride = 0;    // max nA over pairs (query slots per pair)
-  int m_stride = 0;    // max nB over pairs
-  int out_stride = 0;  // entries per pair in match12 / dist12
-  PublishArgs pub{};   // gathered arrays of every rank the resolve kernel also stores into (asdm_job_set_publish)
-  BowParams P{};
-  std::vector<asdm_set*> sets;  // retained
-  std::vector<PairDesc> h_pairs;
-  DevBuf d_pairs, d_masks, d_cnt, d_cand, d_owner, d_acc, d_flags, d_match, d_dist, d_nm;
-  DevBuf d_work, d_tmaps, d_list, d_seg_count, d_rb, d_cmin, d_setdesc;
-  // d_masks / d_pairs / d_work / d_tmaps / d_setdesc are views into d_in (every input of the job, brought over by ONE
-  // pull); d_flags / d_seg_count / d_cnt are views into d_zero (everything a run has to clear, ONE fill)
-  DevBuf d_in, d_zero;
-  size_t zero_bytes = 0;
-  int cap = 8;
-  int use_tc = 0;
-  int n_work = 0;
-  int list_cap = 0;  // total hit slots; split evenly into n_seg segments of seg_cap
-  int n_seg = 0, seg_cap = 0;
-  float t_keep_tc = 0.f;
-  bool ran = false;
-  void* prefetched[3] = {nullptr, nullptr, nullptr};  // destinations of asdm_job_fetch_async
-  bool prefetch_valid = false;
-  bool tc_pending = false;     // tensor-core route taken before every set's range flag was back (validated in settle)
-  int32_t* h_flags = nullptr;  // pinned, 8 ints: [0] cand overflow, [1] list overflow, [2] list count
-  bool h_flags_owned = false;  // true when the context's slot slab was exhausted and the job allocated its own
-};
-
-static void job_free(asdm_job* j) {
+void job_free(asdm_job* j) {
   if (!j) return;
   asdm_ctx* ctx = j->ctx;
   cudaSetDevice(ctx->device);
@@ -81,7 +51,7 @@ static void job_free(asdm_job* j) {
   delete j;
 }
 
-static int job_alloc_scratch(asdm_job* j) {
+int job_alloc_scratch(asdm_job* j) {
   asdm_ctx* ctx = j->ctx;
   const size_t P = (size_t)j->n_pairs;
   int rc;
@@ -111,7 +81,7 @@ static int job_alloc_scratch(asdm_job* j) {
   return ASDM_OK;
 }
 
-static int job_prepare(asdm_ctx* ctx, const asdm_job_desc* d, int kind_internal, asdm_job** out) {
+int job_prepare(asdm_ctx* ctx, const asdm_job_desc* d, int kind_internal, asdm_job** out) {
   if (!ctx || !d || !out) return ASDM_ERR_INVALID;
   *out = nullptr;
   if (d->n_kf <= 0 || d->n_pairs < 0 || !d->sets || !d->masks || (d->n_pairs > 0 && (!d->ia || !d->ib)))
@@ -333,7 +303,7 @@ static int job_prepare(asdm_ctx* ctx, const asdm_job_desc* d, int kind_internal,
   return ASDM_OK;
 }
 
-static int job_run(asdm_job* j) {
+int job_run(asdm_job* j) {
   asdm_ctx* ctx = j->ctx;
   CK(cudaSetDevice(ctx->device));
   ctx->stat_launches = 0;
@@ -392,7 +362,7 @@ static int job_run(asdm_job* j) {
 
 // Waits for the run; when a candidate pool overflowed, grows it and runs again (results are only ever taken
 // from a run without overflow).
-static int job_settle(asdm_job* j) {
+int job_settle(asdm_job* j) {
   asdm_ctx* ctx = j->ctx;
   if (!j->ran) {
     int rc = job_run(j);

@@ -161,18 +161,22 @@ __device__ __forceinline__ void pub_store1(void* p, int v, bool mc) {
 }
 
 __device__ __forceinline__ void publish_row(const PublishArgs& pub, int pair, const int32_t* __restrict__ matchp,
-                                            const float* __restrict__ distp, int out_n, int nm) {
+                                            const float* __restrict__ distp, int out_n, int nm, int c0 = 0, int c1 = 0) {
   const int t = threadIdx.x, nt = blockDim.x;
-  const size_t row = (size_t)(pub.row0 + pair);
+  const size_t slot = (size_t)pub.row0 + (size_t)pair * pub.row_step;
+  const size_t row = pub.row_map ? (size_t)pub.row_map[pair] : slot;
   const bool mc = pub.multicast != 0;
   const bool wd = pub.no_dist == 0;
-  const bool vec = (pub.stride & 3) == 0 && ((reinterpret_cast<uintptr_t>(matchp) | reinterpret_cast<uintptr_t>(distp)) & 15) == 0;
+  // columns [lo, hi) of the destination row belong to this unit: the whole row (padded to the gathered stride with -1),
+  // or the unit's own query rows when a pair is split into row blocks
+  const int lo = pub.col_range ? c0 : 0, hi = pub.col_range ? c1 : pub.stride;
+  const bool vec = (pub.stride & 3) == 0 && (lo & 3) == 0 &&
+                   ((reinterpret_cast<uintptr_t>(matchp) | reinterpret_cast<uintptr_t>(distp)) & 15) == 0;
   if (vec) {
-    const int n4 = pub.stride >> 2;
-    for (int k = t; k < n4; k += nt) {
+    const int hi4 = hi & ~3;
+    for (int e = lo + 4 * t; e < hi4; e += 4 * nt) {
       int4 m = make_int4(-1, -1, -1, -1);
       float4 d = make_float4(-1.f, -1.f, -1.f, -1.f);
-      const int e = k * 4;
       if (e + 3 < out_n) {
         m = *reinterpret_cast<const int4*>(matchp + e);
         d = *reinterpret_cast<const float4*>(distp + e);
@@ -187,8 +191,16 @@ __device__ __forceinline__ void publish_row(const PublishArgs& pub, int pair, co
         if (wd) pub_store4(pub.dist[p] + row * pub.stride + e, di, mc);
       }
     }
+    for (int k = hi4 + t; k < hi; k += nt) {  // a block that ends off a 16-byte boundary (the last block of a pair)
+      const int m = k < out_n ? matchp[k] : -1;
+      const float d = k < out_n ? distp[k] : -1.f;
+      for (int p = 0; p < pub.n; p++) {
+        pub_store1(pub.match[p] + row * pub.stride + k, m, mc);
+        if (wd) pub_store1(pub.dist[p] + row * pub.stride + k, __float_as_int(d), mc);
+      }
+    }
   } else {
-    for (int k = t; k < pub.stride; k += nt) {
+    for (int k = lo + t; k < hi; k += nt) {
       const int m = k < out_n ? matchp[k] : -1;
       const float d = k < out_n ? distp[k] : -1.f;
       for (int p = 0; p < pub.n; p++) {
@@ -198,8 +210,8 @@ __device__ __forceinline__ void publish_row(const PublishArgs& pub, int pair, co
     }
   }
   if (t == 0)
-    for (int p = 0; p < pub.n; p++) pub_store1(pub.nm[p] + row, nm, mc);
-  __threadfence_system();  // the stores are on their way to the other GPUs before this CTA retires
+    for (int p = 0; p < pub.n; p++) pub_store1(pub.nm[p] + slot, nm, mc);
+  __threadfence_system();  // the stores are on their way to the other GPUs / the host before this CTA retires
 }
 
 __global__ void __launch_bounds__(512) k_resolve_bow(const PairDesc* __restrict__ pairs, BowParams P, int cap,
@@ -429,6 +441,6 @@ __global__ void __launch_bounds__(512) k_resolve_tri(const PairDesc* __restrict_
   }
   if (pub.n) {
     __syncthreads();
-    publish_row(pub, pair, matchp, distp, nA, s_count);
+    publish_row(pub, pair, matchp, distp, nA, s_count, pd.rowA0, pd.rowA1 >= nA ? pub.stride : pd.rowA1);  // the last block pads the row
   }
 }

@@ -15,7 +15,13 @@ void set_free(asdm_set* s) {
   if (!s) return;
   asdm_ctx* ctx = s->ctx;
   cudaSetDevice(ctx->device);
-  dev_free(ctx, s->desc);  // one arena: every other device pointer lives inside it (or in the batch's side block)
+  if (s->slab) {  // a view into a group window: the slab goes back when its last set does
+    if (--s->slab->ref == 0) group_slab_release(s->slab);
+    s->h_flag = nullptr;  // lives in the slab's page-locked block
+  } else {
+    dev_free(ctx, s->desc);  // one arena: every other device pointer lives inside it (or in the batch's side block)
+  }
+  dev_free(ctx, s->grid_mem);
   dev_free(ctx, s->fv_mem);
   if (s->side && --s->side->ref == 0) {
     dev_free(ctx, s->side->p);
@@ -30,6 +36,16 @@ void set_free(asdm_set* s) {
 int ensure_grid(asdm_ctx* ctx, asdm_set* s) {
   if (!s->has_grid || s->grid_built) return ASDM_OK;
   const int nc = s->grid.cols * s->grid.rows;
+  if (!s->cell_start) {  // view sets carry no bucket arrays of their own until a projection-gated search asks
+    const size_t o_ci = align_up((size_t)(nc + 1) * sizeof(int32_t), 256), o_tmp = o_ci + align_up((size_t)s->n_pad * sizeof(int32_t), 256),
+                 o_ckp = o_tmp + align_up((size_t)s->n_pad * sizeof(int32_t), 256), total = o_ckp + (size_t)s->n_pad * sizeof(int4);
+    CK(dev_alloc(ctx, &s->grid_mem, total));
+    char* b = (char*)s->grid_mem;
+    s->cell_start = (int32_t*)b;
+    s->cell_items = (int32_t*)(b + o_ci);
+    s->cell_tmp = (int32_t*)(b + o_tmp);
+    s->cell_kp = (int4*)(b + o_ckp);
+  }
   const size_t smem = (size_t)(nc + 1) * sizeof(int32_t);
   if (smem > 48 * 1024) cudaFuncSetAttribute(k_build_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   k_build_grid<<<1, 1024, smem, ctx->stream>>>(s->kps, s->n, s->grid, s->cell_tmp, s->cell_start, s->cell_items, s->cell_kp);
@@ -50,7 +66,7 @@ int resolve_tc_flags(asdm_ctx* ctx, asdm_set* const* sets, int n) {
     asdm_set* s = sets[k];
     if (s->tc_ok >= 0) continue;
     s->tc_ok = (s->h_flag && *s->h_flag == 0) ? 1 : 0;
-    slot_put(ctx, s->h_flag);
+    if (!s->slab) slot_put(ctx, s->h_flag);  // a view's flag lives in its slab's page-locked block
     s->h_flag = nullptr;
   }
   return ASDM_OK;

@@ -302,6 +302,79 @@ int asdm_shared_free(asdm_ctx* ctx, void* dptr);  /* a pointer from asdm_shared_
 int asdm_job_set_publish(asdm_job* job, int n_ranks, void* const* match, void* const* dist, void* const* nmatches,
                          int row0, int stride, int flags);
 
+/* ------------------------------------------------------------------ multi-GPU groups (north_star (3)) */
+/* The batched keyframe-pair searches over several GPUs from plain C / C++: no libtorch, no NCCL, no Python on the path.
+ * A group is `world` ranks, one GPU each. Two ways to get one:
+ *   asdm_group_create  one process drives every GPU (the SLAM process: LocalMapping::CreateNewMapPoints over
+ *                      LocalMapping.cc:335-370, LoopClosing::ComputeSim3 over LoopClosing.cc:291-318). `devices` may name a
+ *                      GPU more than once (two ranks on one GPU: how the tests run on a single-GPU box).
+ *   asdm_group_join    one process per GPU (the bench contract). The processes of the node exchange the handles of their
+ *                      device windows through `allgather`, a caller-supplied all-gather of small host blobs (MPI, a pipe,
+ *                      torch.distributed ...), called a few times inside asdm_group_join / asdm_group_host_alloc only --
+ *                      never on the search path. All ranks must make the same group calls in the same order.
+ * Every rank owns a WINDOW of device memory that every other rank can store into (peer access inside one process, cudaIpc
+ * mappings between processes). Replicated keyframes and gathered results live at the same offset of every window, so no
+ * handle is exchanged after the group exists. Exchange steps are fused into the producing kernels (peer stores over
+ * NVLink) and ordered by a device-side barrier (one flag store per peer + a bounded spin: asdm_group_* never blocks the
+ * host on another rank except in asdm_group_job_wait / asdm_group_host_barrier). */
+typedef struct asdm_group asdm_group;
+typedef struct asdm_gjob asdm_gjob;
+typedef int (*asdm_allgather_fn)(void* user, const void* send, void* recv, size_t bytes_per_rank); /* 0 = ok; rank order */
+
+int asdm_group_create(const int* devices, int n, size_t window_bytes /* 0 = 2 GiB */, asdm_group** out);
+int asdm_group_join(asdm_ctx* ctx, int rank, int world, size_t window_bytes, asdm_allgather_fn allgather, void* user,
+                    asdm_group** out);
+int asdm_group_destroy(asdm_group* g);
+const char* asdm_group_last_error(const asdm_group* g);
+int asdm_group_world(const asdm_group* g);
+int asdm_group_local_count(const asdm_group* g);       /* ranks hosted by this process */
+int asdm_group_local_rank(const asdm_group* g, int l); /* global rank of local member l */
+asdm_ctx* asdm_group_ctx(asdm_group* g, int l);        /* its context (streams, options, counters) */
+/* Host memory every rank's GPU can store into and every process of the group can read: page-locked; one process: plain
+ * pinned memory; several: one shared mapping (memfd) registered with CUDA in each. Collective. */
+int asdm_group_host_alloc(asdm_group* g, size_t bytes, void** out);
+int asdm_group_host_free(asdm_group* g, void* p);
+int asdm_group_host_barrier(asdm_group* g); /* all processes of the group (no-op with one process) */
+
+/* A batch of keyframes replicated on every GPU of the group: keyframe k crosses PCIe ONCE -- rank k % world
+ * uploads it from descs[k] (only the process hosting that rank reads descs[k].desc / kps / featvec; n, and whether kps /
+ * grid / featvec are given, must agree everywhere) -- and the owner's pack kernel stores the fp32 rows, the bf16 copy, the
+ * norms, the keypoints and the FeatureVector arrays straight into every peer's window. out[k * local_count + l] = the
+ * set of keyframe k on local member l: an ordinary asdm_set (a view; release each with asdm_set_release). Asynchronous:
+ * descs[k].desc must stay valid until the next synchronising call. Searches queued later on the members' streams see
+ * the whole batch (a device-side barrier closes the exchange). */
+int asdm_group_sets_create(asdm_group* g, const asdm_set_desc* descs, int n_sets, asdm_set** out);
+
+/* A batched search dealt over the group: unit u (a pair, or one of `blocks_per_pair` 128-row-aligned query row blocks of a
+ * pair: triangulation without rotation check only, see asdm_job_desc) belongs to rank u % world. job.sets = the array
+ * asdm_group_sets_create returned ([n_kf * local_count]). */
+enum { ASDM_GATHER_DEVICE = 1 }; /* every rank's GPU also receives every unit's records (asdm_group_job_gathered) */
+typedef struct {
+  asdm_job_desc job;
+  int32_t blocks_per_pair; /* >= 1 */
+  int32_t gather;          /* 0 or ASDM_GATHER_DEVICE */
+} asdm_gjob_desc;
+int asdm_group_job_prepare(asdm_group* g, const asdm_gjob_desc* desc, asdm_gjob** out);
+int asdm_group_job_units(const asdm_gjob* j);  /* n_pairs, or more when pairs are split */
+int asdm_group_job_stride(const asdm_gjob* j); /* entries per result row */
+/* Launches the units of every local member; returns without waiting. h_match / h_dist: [n_pairs][stride] in the caller's
+ * pair order, h_unit_nm: [units] -- device-visible host memory (asdm_group_host_alloc / asdm_host_alloc) the kernels
+ * store the finished rows into as each unit retires, every rank over its own PCIe link; any of them may be NULL. */
+int asdm_group_job_run(asdm_gjob* j, int32_t* h_match, float* h_dist, int32_t* h_unit_nm);
+/* Waits for the local units (growing candidate pools and re-running if one overflowed) and for the other processes of the
+ * group: afterwards the host arrays handed to asdm_group_job_run are complete. */
+int asdm_group_job_wait(asdm_gjob* j);
+/* nmatches[p] = sum of the counts of pair p's units */
+int asdm_group_job_counts(const asdm_gjob* j, const int32_t* h_unit_nm, int32_t* nmatches);
+/* run + wait + copy into ordinary (pageable) arrays: the whole batch on every process, as one un-sharded asdm_job
+ * over all pairs would report it. Any pointer may be NULL. */
+int asdm_group_job_fetch(asdm_gjob* j, int32_t* match12, float* dist12, int32_t* nmatches);
+/* ASDM_GATHER_DEVICE: device pointers, on local member l, of the records of ALL units as the last run left them
+ * (match / dist: [units or pairs][stride] as above, unit_nm: [units]); valid after asdm_group_job_wait, or for work
+ * queued on the member's stream behind asdm_group_job_run (the device-side barrier orders it). */
+int asdm_group_job_gathered(asdm_gjob* j, int l, void** match, void** dist, void** unit_nm);
+int asdm_group_job_destroy(asdm_gjob* j);
+
 /* ------------------------------------------------------------------ map-point descriptor maintenance */
 /* MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:271-338) for a batch of map points, e.g. all points matched by
  * a new keyframe (LocalMapping.cc:245, 535, 628). Observations of point p are rows (sets[obs_set[e]], obs_row[e]),
