@@ -96,11 +96,10 @@ class Group:
     def host_barrier(self):
         self.check(self.lib.asdm_group_host_barrier(self.h))
 
-    def sets_create(self, descs, kps=None, grid=None, featvecs=None):
-        """asdm_group_sets_create: keyframe k crosses PCIe once (rank k % world uploads descs[k]) and is replicated by
-        the owner's pack kernel. Returns sets[k][l] = DescriptorSet of keyframe k on local member l. descs[k] must stay
-        alive and unmodified until the next synchronising call."""
-        m, L = len(descs), self.local_count
+    def prepare_sets(self, descs, kps=None, grid=None, featvecs=None):
+        """The argument block of sets_create, converted once (a keyframe batch that is uploaded again and again: the e2e
+        arm of bench.py). Pass the result to sets_create(prepared=...)."""
+        m = len(descs)
         g = None
         if grid is not None:
             g = grid if isinstance(grid, Grid) else Grid(*grid)
@@ -123,6 +122,14 @@ class Group:
                 fv = FeatVec(len(node_ids), ptr(node_ids), ptr(off), ptr(idx))
                 a.featvec = C.pointer(fv)
                 keep.append((node_ids, off, idx, fv))
+        return (arr, m, keep, list(descs))
+
+    def sets_create(self, descs=None, kps=None, grid=None, featvecs=None, prepared=None):
+        """asdm_group_sets_create: keyframe k crosses PCIe once (rank k % world uploads descs[k]) and is replicated by
+        the owner's pack kernel. Returns sets[k][l] = DescriptorSet of keyframe k on local member l. descs[k] must stay
+        alive and unmodified until the next synchronising call."""
+        arr, m, _keep, descs = prepared if prepared is not None else self.prepare_sets(descs, kps, grid, featvecs)
+        L = self.local_count
         hs = (C.c_void_p * (m * L))()
         self.check(self.lib.asdm_group_sets_create(self.h, arr, m, hs))
         out = []
@@ -134,6 +141,12 @@ class Group:
                 row.append(s)
             out.append(row)
         return out
+
+    @staticmethod
+    def release_sets(sets):
+        for row in sets:
+            for s in row:
+                s.release()
 
     def close(self):
         if self.h:

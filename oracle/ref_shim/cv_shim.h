@@ -9,6 +9,7 @@
 #include <cassert>
 #include <cmath>
 #include <limits>
+#include <memory>
 #include <cstring>
 #include <vector>
 
@@ -35,6 +36,113 @@ struct KeyPoint {
   int octave = 0, class_id = -1;
 };
 
+#ifdef ASD_CV_VIEWS
+// ---- header semantics, as cv::Mat has them (OpenCV 3.2 core/mat.hpp): copies, row(), col(), rowRange(), colRange() and
+// reshape() are HEADERS over shared, reference-counted data; only clone(), create() and convertTo() allocate, and
+// convertTo allocates its destination once. oracle/Makefile builds the reference a second time with -DASD_CV_VIEWS
+// (oracle/_ref/libref_orbmatcher_views.so): the goldens must come out bit-identical, and bench.py reports the reference's
+// speed in both modes so the share of this stand-in in the reference's cost is known.
+class Mat {
+ public:
+  int rows = 0, cols = 0;
+  Mat() {}
+  Mat(int r, int c, int type) { create(r, c, type); }
+  void create(int r, int c, int type) {
+    rows = r; cols = c; type_ = type; step_ = c; off_ = 0;
+    buf_ = std::make_shared<Buf>();
+    buf_->f.assign(type == CV_32F ? (size_t)r * c : 0, 0.f);
+    buf_->d.assign(type == CV_64F ? (size_t)r * c : 0, 0.0);
+  }
+  int type() const { return type_; }
+  bool empty() const { return rows == 0 || cols == 0; }
+  void release() { create(0, 0, type_); }
+  static Mat zeros(int r, int c, int type) { return Mat(r, c, type); }
+  Mat clone() const {
+    Mat o(rows, cols, type_);
+    for (int i = 0; i < rows; i++)
+      for (int j = 0; j < cols; j++) o.set(i, j, get(i, j));
+    return o;
+  }
+  template <typename T> T& at(int i, int j) { return data<T>()[(size_t)i * step_ + j]; }
+  template <typename T> const T& at(int i, int j) const { return data<T>()[(size_t)i * step_ + j]; }
+  // single-index access of a vector (n x 1 or 1 x n)
+  template <typename T> T& at(int i) { return cols == 1 ? data<T>()[(size_t)i * step_] : data<T>()[i]; }
+  template <typename T> const T& at(int i) const { return cols == 1 ? data<T>()[(size_t)i * step_] : data<T>()[i]; }
+  template <typename T> T* ptr(int i = 0) { return data<T>() + (size_t)i * step_; }
+  template <typename T> const T* ptr(int i = 0) const { return data<T>() + (size_t)i * step_; }
+
+  Mat rowRange(int a, int b) const { return block(a, b, 0, cols); }
+  Mat colRange(int a, int b) const { return block(0, rows, a, b); }
+  Mat row(int i) const { return block(i, i + 1, 0, cols); }
+  Mat col(int j) const { return block(0, rows, j, j + 1); }
+  Mat t() const {
+    Mat o(cols, rows, type_);
+    for (int i = 0; i < rows; i++)
+      for (int j = 0; j < cols; j++) o.set(j, i, get(i, j));
+    return o;
+  }
+  Mat reshape(int cn, int r) const {  // a header when the data is continuous (all the matcher ever reshapes is a row)
+    assert(cn == 1 && r > 0);
+    (void)cn;
+    if (!(rows == 1 || step_ == cols)) return clone().reshape(cn, r);
+    Mat o = *this;
+    o.rows = r;
+    o.cols = rows * cols / r;
+    o.step_ = o.cols;
+    return o;
+  }
+  void convertTo(Mat& dst, int rtype) const {
+    const Mat src = *this;  // dst may alias this
+    dst.create(src.rows, src.cols, rtype);
+    for (int i = 0; i < src.rows; i++)
+      for (int j = 0; j < src.cols; j++) dst.set(i, j, src.get(i, j));
+  }
+  template <typename T> operator std::vector<T>() const {
+    std::vector<T> v((size_t)rows * cols);
+    for (int i = 0; i < rows; i++)
+      for (int j = 0; j < cols; j++) v[(size_t)i * cols + j] = (T)get(i, j);
+    return v;
+  }
+  double dot(const Mat& o) const {
+    double s = 0;
+    for (int i = 0; i < rows; i++)
+      for (int j = 0; j < cols; j++) s += get(i, j) * o.get(i, j);
+    return s;
+  }
+  double get(int i, int j) const {
+    const size_t at = off_ + (size_t)i * step_ + j;
+    return type_ == CV_32F ? (double)buf_->f[at] : buf_->d[at];
+  }
+  void set(int i, int j, double v) {
+    const size_t at = off_ + (size_t)i * step_ + j;
+    if (type_ == CV_32F) buf_->f[at] = (float)v;
+    else buf_->d[at] = v;
+  }
+
+ private:
+  struct Buf {
+    std::vector<float> f;
+    std::vector<double> d;
+  };
+  template <typename T> T* data();
+  template <typename T> const T* data() const;
+  Mat block(int r0, int r1, int c0, int c1) const {
+    Mat o = *this;
+    o.rows = r1 - r0;
+    o.cols = c1 - c0;
+    o.off_ = off_ + (size_t)r0 * step_ + c0;
+    return o;
+  }
+  int type_ = CV_32F;
+  int step_ = 0;     // elements between consecutive rows
+  size_t off_ = 0;   // first element inside the shared buffer
+  std::shared_ptr<Buf> buf_;
+};
+template <> inline float* Mat::data<float>() { assert(type_ == CV_32F); return buf_->f.data() + off_; }
+template <> inline const float* Mat::data<float>() const { assert(type_ == CV_32F); return buf_->f.data() + off_; }
+template <> inline double* Mat::data<double>() { assert(type_ == CV_64F); return buf_->d.data() + off_; }
+template <> inline const double* Mat::data<double>() const { assert(type_ == CV_64F); return buf_->d.data() + off_; }
+#else
 class Mat {
  public:
   int rows = 0, cols = 0;
@@ -121,6 +229,8 @@ template <> inline float* Mat::data<float>() { assert(type_ == CV_32F); return f
 template <> inline const float* Mat::data<float>() const { assert(type_ == CV_32F); return f_.data(); }
 template <> inline double* Mat::data<double>() { assert(type_ == CV_64F); return d_.data(); }
 template <> inline const double* Mat::data<double>() const { assert(type_ == CV_64F); return d_.data(); }
+
+#endif  // ASD_CV_VIEWS
 
 // element-wise results are rounded to the matrix type once per element, as OpenCV's float kernels do
 inline Mat operator*(const Mat& a, const Mat& b) {

@@ -280,3 +280,29 @@ def test_stereo_row_match_against_the_reference_text(pkg, oracle, ref, n, seed, 
     assert np.array_equal(od.view(np.uint32), rd.view(np.uint32))
     if n >= 300:
         assert (rb >= 0).sum() > n // 4
+
+
+def test_reference_with_header_semantics_mat_reproduces_the_goldens(ref):
+    """oracle/_ref/libref_orbmatcher_views.so = the same unmodified ORBmatcher.cc with the cv::Mat stand-in in header mode
+    (row() / reshape() / copies share data, convertTo allocates once: what OpenCV 3.2 does). It is only there so that
+    bench.py can time the reference without the stand-in's copies; it must compute exactly the same results."""
+    import os
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    sys.path.insert(0, os.path.join(here, "golden"))
+    import cases as C
+    views = os.path.join(os.path.dirname(here), "oracle", "_ref", "libref_orbmatcher_views.so")
+    if not os.path.exists(views):
+        pytest.skip("header-mode reference build missing")
+    gold = np.load(os.path.join(here, "golden", "ref_golden.npz"))
+    ref.use(views)
+    try:
+        for name, kind, a in C.cases():
+            if name in ("c5_full_pair", "c4_full_pair"):
+                continue  # seconds each; the small cases cover every entry point
+            for k, v in C.run_case(ref, name, kind, a).items():
+                want = gold[k]
+                same = np.array_equal(v.view(np.uint32), want.view(np.uint32)) if v.dtype == np.float32 else np.array_equal(v, want)
+                assert same, k
+    finally:
+        ref.use(None)

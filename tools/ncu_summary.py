@@ -1,6 +1,8 @@
 #!/usr/bin/env python
 """Summarise an .ncu-rep (read on the CPU box): key raw metrics + the most-stalled SASS lines.
-usage: tools/ncu_summary.py gpurun_out/prof.ncu-rep [n_top]  > profiles/<name>.txt"""
+usage: tools/ncu_summary.py gpurun_out/prof.ncu-rep [n_top] [kernel source file ...]  > profiles/<name>.txt
+Source files named after n_top are recorded as `source_blob: <path> <git blob hash>` lines: bench.py only takes
+roofline.traffic from a summary whose blob hash equals the kernel source it is running."""
 import csv
 import io
 import subprocess
@@ -8,6 +10,9 @@ import sys
 
 rep = sys.argv[1]
 ntop = int(sys.argv[2]) if len(sys.argv) > 2 else 30
+for path in sys.argv[3:]:
+    blob = subprocess.run(["git", "hash-object", path], capture_output=True, text=True).stdout.strip()
+    print(f"source_blob: {path} {blob}")
 KEYS = ["gpu__time_duration.sum", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
         "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed", "dram__bytes_read.sum ", "dram__bytes_write.sum ",
         "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
