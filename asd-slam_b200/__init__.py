@@ -13,5 +13,5 @@ from ._lib import (ASDM_JOB_BOW_KF_KF, ASDM_JOB_TRIANGULATION, ASDM_PROJ_BEST_ON
                    KP_DTYPE, PROJ_QUERY_DTYPE, AsdmError)
 from .matcher import (ComputeDistinctiveDescriptors, Context, DescriptorSet, KeyFrameDatabase, ORBmatcher, ORBVocabulary,  # noqa: F401
                       PairJob, StreamedPairSweep, save_map_blocks)
-from .group import Group, GroupJob, torch_allgather  # noqa: F401
+from .group import Group, GroupJob, StreamedGroupSweep, torch_allgather  # noqa: F401
 from .shard import GatheredResults, PairShards, ReplicatedDescriptors, ShardedPairJob, all_gather_results  # noqa: F401

@@ -177,11 +177,7 @@ static int bowdb_run(asdm_bowdb* db, const uint32_t* word_id, const double* valu
     while (log2bits < 19 && (1 << log2bits) < ctx->opt_bowdb_filter_bits * n) log2bits++;
     const size_t tab_bytes = ((size_t)8 << log2cap) + ((size_t)1 << (log2bits - 3));
     if (!ctx->opt_bowdb_search && n > 0 && tab_bytes <= (size_t)200 * 1024 && word_id[n - 1] != 0xffffffffu) {
-      static bool attr_set = false;
-      if (!attr_set) {
-        CK(cudaFuncSetAttribute(k_bowdb_query_hash, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set = true;
-      }
+      CK(cudaFuncSetAttribute(k_bowdb_query_hash, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));  // per device
       int per_sm = 1;
       CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bowdb_query_hash, BOWDB_HASH_WARPS * 32, tab_bytes));
       const int grid = std::min((ns + BOWDB_HASH_WARPS - 1) / BOWDB_HASH_WARPS, std::max(per_sm, 1) * ctx->sm_count);

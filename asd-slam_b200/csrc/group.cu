@@ -69,8 +69,13 @@ struct GroupMember {
   char* peer[ASDM_MAX_PEERS] = {};   // every rank's window as this member's device addresses it (peer[rank] == win)
   bool opened[ASDM_MAX_PEERS] = {};  // cudaIpc mappings to close
   WinAlloc alloc;
-  uint32_t epoch = 0;                // barriers queued so far (identical on every rank)
+  // Two barrier channels, each used on ONE stream so that its epochs are announced in order: 0 = the main stream (records
+  // gathered by jobs), 1 = the preparation stream (keyframe batches replicated into the windows)
+  uint32_t epoch[2] = {0, 0};        // barriers queued so far per channel (identical on every rank)
   int32_t* h_err = nullptr;          // page-locked: raised by a barrier that ran out of patience
+  // recorded on the main stream whenever a range of this window is released: what is queued there up to that point may
+  // still read the range, so whoever takes it next orders itself behind this event (and behind nothing queued later)
+  cudaEvent_t rel_evt = nullptr;
 };
 
 struct HostCtl {  // shared by the processes of the group (one page)
@@ -154,24 +159,26 @@ __global__ void k_group_wait(const uint32_t* mine, int n, uint32_t epoch, int32_
 
 // A barrier is queued in two halves so that a process hosting several ranks can queue every member's signal before any
 // member's wait: the host never blocks on a stream whose wait kernel needs a signal it has not launched yet.
-static int group_signal(asdm_group* g, GroupMember& M) {
+enum { CH_MAIN = 0, CH_PREP = 1 };
+static int group_signal(asdm_group* g, GroupMember& M, int ch) {
   asdm_ctx* ctx = M.ctx;
-  ++M.epoch;
+  ++M.epoch[ch];
   if (g->world == 1) return ASDM_OK;
   GCK(cudaSetDevice(ctx->device));
   BarrierPeers P;
   P.n = g->world;
-  for (int r = 0; r < g->world; r++) P.flags[r] = (uint32_t*)M.peer[r];
-  k_group_signal<<<1, 32, 0, ctx->stream>>>(P, M.rank, M.epoch);
+  for (int r = 0; r < g->world; r++) P.flags[r] = (uint32_t*)M.peer[r] + ch * ASDM_MAX_PEERS;
+  k_group_signal<<<1, 32, 0, ch == CH_MAIN ? ctx->stream : ctx->prep_stream>>>(P, M.rank, M.epoch[ch]);
   ctx->stat_total_launches++;
   GCK(cudaGetLastError());
   return ASDM_OK;
 }
-static int group_wait(asdm_group* g, GroupMember& M) {  // for the epoch of the last group_signal
+static int group_wait(asdm_group* g, GroupMember& M, int ch) {  // for the epoch of the channel's last group_signal
   asdm_ctx* ctx = M.ctx;
   if (g->world == 1) return ASDM_OK;
   GCK(cudaSetDevice(ctx->device));
-  k_group_wait<<<1, 32, 0, ctx->stream>>>((const uint32_t*)M.win, g->world, M.epoch, M.h_err, 10ull * 1000000000ull);
+  k_group_wait<<<1, 32, 0, ch == CH_MAIN ? ctx->stream : ctx->prep_stream>>>((const uint32_t*)M.win + ch * ASDM_MAX_PEERS, g->world,
+                                                                           M.epoch[ch], M.h_err, 10ull * 1000000000ull);
   ctx->stat_total_launches++;
   GCK(cudaGetLastError());
   return ASDM_OK;
@@ -251,6 +258,8 @@ static int group_finish_setup(asdm_group* g) {
     GCK(cudaStreamSynchronize(M.ctx->stream));
     GCK(cudaHostAlloc((void**)&M.h_err, 64, cudaHostAllocMapped | cudaHostAllocPortable));
     *M.h_err = 0;
+    GCK(cudaEventCreateWithFlags(&M.rel_evt, cudaEventDisableTiming));
+    GCK(cudaEventRecord(M.rel_evt, M.ctx->stream));
     M.alloc.reset(WIN_HEADER, g->win_bytes);
   }
   return ASDM_OK;
@@ -396,6 +405,7 @@ extern "C" int asdm_group_destroy(asdm_group* g) {
       if (M.opened[r]) cudaIpcCloseMemHandle(M.peer[r]);
     if (M.win) cudaFree(M.win);
     if (M.h_err) cudaFreeHost(M.h_err);
+    if (M.rel_evt) cudaEventDestroy(M.rel_evt);
     if (M.own_ctx) asdm_destroy(M.ctx);
   }
   cudaGetLastError();
@@ -468,10 +478,16 @@ extern "C" int asdm_group_host_barrier(asdm_group* g) {
 }
 
 // ------------------------------------------------------------------------------------------------ replicated sets
+static void window_release(GroupMember& M, size_t off, size_t bytes) {
+  cudaSetDevice(M.ctx->device);
+  if (cudaEventRecord(M.rel_evt, M.ctx->stream) != cudaSuccess) cudaGetLastError();
+  M.alloc.release(off, bytes);
+}
+
 void group_slab_release(GroupSlab* s) {
   asdm_group* g = s->g;
   GroupMember& M = g->m[(size_t)s->member];
-  M.alloc.release(s->off, s->bytes);
+  window_release(M, s->off, s->bytes);
   if (s->h_flags) cudaFreeHost(s->h_flags);
   delete s;
 }
@@ -597,15 +613,16 @@ extern "C" int asdm_group_sets_create(asdm_group* g, const asdm_set_desc* descs,
     GCB(cudaHostAlloc((void**)&slab->h_flags, align_up((size_t)n_sets * 4, 64), cudaHostAllocDefault));
     for (int k = 0; k < n_sets; k++) slab->h_flags[k] = 1;  // "not proven" until the device flags are back
     char* win = M.win + base_off;
-    // my own range is mine to clear now: peers only store into it after the barrier below. The main stream orders this
-    // behind every search that still reads the previous occupant of the range.
-    {
-      int rc = zero_device(ctx, win + o_flags, align_up((size_t)n_sets * 4, 256));
-      if (rc) return bail(rc);
-    }
+    // The range may have had an occupant: whatever this rank still has queued on it was queued on the main stream before
+    // the release (rel_evt). The upload and the preparation streams order themselves behind that -- and behind nothing
+    // queued later, so the searches of earlier waves run while this batch crosses PCIe. My own range is mine to clear:
+    // peers only store into it after the barrier below.
+    GCB(cudaStreamWaitEvent(ctx->upload_stream, M.rel_evt, 0));
+    GCB(cudaStreamWaitEvent(ctx->prep_stream, M.rel_evt, 0));
+    GCB(cudaMemsetAsync(win + o_flags, 0, align_up((size_t)n_sets * 4, 256), ctx->prep_stream));
     // B1: every rank has left behind whatever it had queued on the previous occupant of this range
     {
-      int rc = group_signal(g, M);
+      int rc = group_signal(g, M, CH_PREP);
       if (rc) return bail(rc);
     }
   }
@@ -617,11 +634,9 @@ extern "C" int asdm_group_sets_create(asdm_group* g, const asdm_set_desc* descs,
     const size_t base_off = slabs[(size_t)l]->off;
     char* win = M.win + base_off;
     {
-      int rc = group_wait(g, M);
+      int rc = group_wait(g, M, CH_PREP);
       if (rc) return bail(rc);
     }
-    GCB(cudaEventRecord(ctx->prep_done, ctx->stream));
-    GCB(cudaStreamWaitEvent(ctx->upload_stream, ctx->prep_done, 0));
     // ---- uploads of the keyframes this rank owns (k % W == rank): rows straight from the caller's buffer, the small
     // arrays through the page-locked arena, the push table last
     int n_owned = 0, max_pad = 0;
@@ -681,11 +696,9 @@ extern "C" int asdm_group_sets_create(asdm_group* g, const asdm_set_desc* descs,
       ctx->stat_total_launches++;
       GCB(cudaGetLastError());
     }
-    GCB(cudaEventRecord(ctx->prep_done, ctx->prep_stream));
-    GCB(cudaStreamWaitEvent(ctx->stream, ctx->prep_done, 0));
     // B2: every owner's rows have landed in this window
     {
-      int rc = group_signal(g, M);
+      int rc = group_signal(g, M, CH_PREP);
       if (rc) return bail(rc);
     }
   }
@@ -697,10 +710,12 @@ extern "C" int asdm_group_sets_create(asdm_group* g, const asdm_set_desc* descs,
     GroupSlab* slab = slabs[(size_t)l];
     char* win = M.win + slab->off;
     {
-      int rc = group_wait(g, M);
+      int rc = group_wait(g, M, CH_PREP);
       if (rc) return bail(rc);
     }
-    GCB(cudaMemcpyAsync(slab->h_flags, win + o_flags, (size_t)n_sets * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    GCB(cudaMemcpyAsync(slab->h_flags, win + o_flags, (size_t)n_sets * 4, cudaMemcpyDeviceToHost, ctx->prep_stream));
+    GCB(cudaEventRecord(ctx->prep_done, ctx->prep_stream));
+    GCB(cudaStreamWaitEvent(ctx->stream, ctx->prep_done, 0));  // whatever is queued on the main stream from here on sees the batch
     // ---- the views
     for (int k = 0; k < n_sets; k++) {
       const asdm_set_desc& d = descs[k];
@@ -887,6 +902,20 @@ extern "C" int asdm_group_job_run(asdm_gjob* j, int32_t* h_match, float* h_dist,
   if (host && (!device_visible(h_match) || !device_visible(h_unit_nm) || (h_dist && !device_visible(h_dist))))
     return gfail(g, ASDM_ERR_INVALID, "host result arrays must be page-locked (asdm_group_host_alloc / asdm_host_alloc)");
   j->gen ^= 1;
+  if ((j->gather & ASDM_GATHER_DEVICE) && !j->ran) {
+    // The gathered records live in a range of every window that other jobs may have used before: nobody stores into a
+    // peer's range until that peer has prepared this job too (and so is done with whatever was there).
+    for (int l = 0; l < L; l++) {
+      std::lock_guard<std::recursive_mutex> lkc(g->m[(size_t)l].ctx->mu);
+      const int rc = group_signal(g, g->m[(size_t)l], CH_MAIN);
+      if (rc) return rc;
+    }
+    for (int l = 0; l < L; l++) {
+      std::lock_guard<std::recursive_mutex> lkc(g->m[(size_t)l].ctx->mu);
+      const int rc = group_wait(g, g->m[(size_t)l], CH_MAIN);
+      if (rc) return rc;
+    }
+  }
   for (int l = 0; l < L; l++) {
     GroupMember& M = g->m[(size_t)l];
     asdm_gjob::Local& X = j->loc[(size_t)l];
@@ -923,12 +952,12 @@ extern "C" int asdm_group_job_run(asdm_gjob* j, int32_t* h_match, float* h_dist,
     pub.no_dist = want_dist ? 0 : 1;
     int rc = job_run(job);
     if (rc) return gfail(g, rc, asdm_last_error(M.ctx));
-    if ((j->gather & ASDM_GATHER_DEVICE) && (rc = group_signal(g, M))) return rc;
+    if ((j->gather & ASDM_GATHER_DEVICE) && (rc = group_signal(g, M, CH_MAIN))) return rc;
   }
   if (j->gather & ASDM_GATHER_DEVICE)  // every rank's rows have landed in every window once this has run
     for (int l = 0; l < L; l++) {
       std::lock_guard<std::recursive_mutex> lkc(g->m[(size_t)l].ctx->mu);
-      const int rc = group_wait(g, g->m[(size_t)l]);
+      const int rc = group_wait(g, g->m[(size_t)l], CH_MAIN);
       if (rc) return rc;
     }
   j->ran = true;
@@ -1011,7 +1040,7 @@ extern "C" int asdm_group_job_destroy(asdm_gjob* j) {
     if (X.job) asdm_job_destroy(X.job);
     if (X.has_gather) {
       std::lock_guard<std::recursive_mutex> lkc(M.ctx->mu);
-      M.alloc.release(j->g_off, j->g_bytes);
+      window_release(M, j->g_off, j->g_bytes);
     }
   }
   if (j->st_match) asdm_group_host_free(g, j->st_match);

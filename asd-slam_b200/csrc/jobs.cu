@@ -364,6 +364,7 @@ int job_run(asdm_job* j) {
 // from a run without overflow).
 int job_settle(asdm_job* j) {
   asdm_ctx* ctx = j->ctx;
+  CK(cudaSetDevice(ctx->device));  // a process may drive several GPUs (asdm_group_create): never rely on the current device
   if (!j->ran) {
     int rc = job_run(j);
     if (rc) return rc;

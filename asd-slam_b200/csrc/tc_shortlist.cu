@@ -400,12 +400,13 @@ cudaError_t asdm_tc_row_bounds_launch(asdm_ctx* ctx, const TcSetDesc* d_sets, co
 template <int EPI_WARPS, int A_STAGES, int B_BUFS, bool NO_EPI, bool EARLY>
 static cudaError_t tc_launch(asdm_ctx* ctx, const PairDesc* d_pairs, const void* d_tmaps, const TcWork* d_work, int n_work,
                              float t_half, TcHit* d_list, int seg_cap, int32_t* d_seg_count, int32_t* d_list_total) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  // the attribute belongs to the (function, device) pair: a process may drive several GPUs (asdm_group_create)
+  static unsigned long long attr_set = 0;  // bit d: done on device d
+  if (ctx->device >= 64 || !((attr_set >> ctx->device) & 1ull)) {
     cudaError_t e = cudaFuncSetAttribute(k_tc_shortlist<EPI_WARPS, A_STAGES, B_BUFS, NO_EPI, EARLY>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem(A_STAGES, B_BUFS));
     if (e != cudaSuccess) return e;
-    attr_set = true;
+    if (ctx->device < 64) attr_set |= 1ull << ctx->device;
   }
   const int grid = n_work < ctx->sm_count ? n_work : ctx->sm_count;
   k_tc_shortlist<EPI_WARPS, A_STAGES, B_BUFS, NO_EPI, EARLY><<<grid, 64 + 32 * EPI_WARPS, tc_smem(A_STAGES, B_BUFS), ctx->stream>>>(

@@ -215,3 +215,46 @@ class GroupJob:
         if self.h:
             self.g.lib.asdm_group_job_destroy(self.h)
             self.h = None
+
+
+class StreamedGroupSweep:
+    """A keyframe-pair sweep over keyframes that are NOT yet resident, on a Group: the keyframes are uploaded in index
+    order, in waves (each keyframe once over PCIe by its owner, replicated by the pack kernel), and the pairs are searched
+    in readiness order -- wave w holds the pairs whose later keyframe arrived with wave w and is dealt over the ranks as
+    soon as that wave is queued, so the searches overlap the uploads of the later waves (matcher.StreamedPairSweep is the
+    single-GPU form). Finished rows are stored by the resolve kernels into the caller's host arrays; row r belongs to pair
+    `order[r]`."""
+
+    def __init__(self, group, kind, descs, kps, grid, featvecs, ia, ib, nnratio=0.6, check_ori=True, bounds=None):
+        self.g, self.kind = group, kind
+        self.n_kf = len(descs)
+        self.ia, self.ib = _i32(ia), _i32(ib)
+        self.nnratio, self.check_ori = nnratio, check_ori
+        if bounds is None:
+            bounds = sorted({max(2, int(round(self.n_kf * f))) for f in (0.375, 0.5625, 0.72, 0.845, 0.94, 1.0)})
+        self.bounds = [int(b) for b in bounds]
+        assert self.bounds[-1] == self.n_kf
+        later = np.maximum(self.ia, self.ib)
+        self.order = np.argsort(later, kind="stable").astype(np.int64)
+        cuts = np.searchsorted(later[self.order], self.bounds, side="left")
+        self.slices = [(int(a), int(b)) for a, b in zip(np.concatenate(([0], cuts[:-1])), cuts)]
+        lo = [0] + self.bounds[:-1]
+        # argument blocks converted once: the same keyframes are uploaded step after step (bench.py e2e arm)
+        self.prepared = [group.prepare_sets(descs[a:b], kps[a:b], grid, featvecs[a:b]) for a, b in zip(lo, self.bounds)]
+
+    def run(self, masks, h_match, h_unit_nm):
+        """h_match [n_pairs, stride] / h_unit_nm [n_pairs]: host arrays of Group.host_array. Returns the sets (the caller
+        releases them with Group.release_sets)."""
+        sets, jobs = [], []
+        for (a, b), prep, bound in zip(self.slices, self.prepared, self.bounds):
+            sets.extend(self.g.sets_create(prepared=prep))
+            if b <= a:
+                continue
+            sel = self.order[a:b]
+            jb = GroupJob(self.g, self.kind, sets[:bound], masks[:bound], self.ia[sel], self.ib[sel], self.nnratio, self.check_ori)
+            jb.run(h_match[a:b], None, h_unit_nm[a:b])
+            jobs.append(jb)
+        for jb in jobs:
+            jb.wait()
+            jb.destroy()
+        return sets

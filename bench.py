@@ -434,21 +434,25 @@ def run_ours(args):
         except pkg.AsdmError:  # no shared mapping on this box: every process keeps the rows of its own units
             h_match, h_nm, shared_host = ctx.pinned((n_job_pairs, S), np.int32), ctx.pinned((job.n_units,), np.int32), False
 
+        waves = [int(x) for x in args.waves.split(",")] if args.waves else None
+        gsweep = G.StreamedGroupSweep(grp, pkg.ASDM_JOB_BOW_KF_KF, h_desc, kps_all, c["grid"], fv_all, g_ia, g_ib, c["nnratio"],
+                                      c["check_ori"], bounds=waves)
+
         def e2e_step():
-            ss = grp.sets_create(prepared=prepared)
-            jb = G.GroupJob(grp, pkg.ASDM_JOB_BOW_KF_KF, ss, masks, g_ia, g_ib, c["nnratio"], c["check_ori"])
-            jb.run(h_match, None, h_nm)
-            jb.wait()
-            jb.destroy()
-            G.Group.release_sets(ss)
-        what = ("per step: each keyframe uploaded once (rank k%N, page-locked host memory) and replicated to every GPU by the "
-                "pack kernel (peer stores over NVLink), job dealt round-robin by the library, every rank's resolve kernel stores "
+            G.Group.release_sets(gsweep.run(masks, h_match, h_nm))
+        what = (f"per step, in {len(gsweep.bounds)} readiness waves (keyframe bounds {gsweep.bounds}) whose searches overlap the later "
+                "uploads: each keyframe uploaded once (rank k%N, page-locked host memory) and replicated to every GPU by the "
+                "pack kernel (peer stores over NVLink), pairs dealt round-robin by the library, every rank's resolve kernel stores "
                 "its rows into " + ("one host block shared by the processes (memfd)" if shared_host else "its own page-locked block") +
                 " over its own PCIe link (indices + counts: what SearchByBoW returns), host barrier")
         own_kf = len(range(rank, len(kfs), world))
         own_h2d = own_kf * (n * 512 + n * 24) + sum(len(k["valid"]) for k in kfs) + 8 * (n_job_pairs // world)
         h2d = sum(k["desc"].nbytes for k in kfs) + h2d_side + world * (sum(len(k["valid"]) for k in kfs) + 8 * (n_job_pairs // world))
+        resent = sum(sum(len(k["valid"]) for k in kfs[:bd]) for bd in gsweep.bounds[:-1])  # every wave re-sends the masks it may touch
+        h2d += world * resent
+        own_h2d += resent
         d2h = n_job_pairs * S * 4 + job.n_units * 4
+    e2e_step()
     e2e_step()
     barrier()
     ctx.synchronize()
@@ -459,9 +463,14 @@ def run_ours(args):
     e2e_ms = max_over_ranks(1e3 * (time.perf_counter() - te) / e2e_steps)
     if world == 1:
         e2e_same = bool(np.array_equal(h_match, match[sweep.order]) and np.array_equal(h_nm, nm[sweep.order]))
-    else:  # a shared block holds the whole batch in every process; private blocks the rows of this rank's units
-        mine = np.arange(n_job_pairs) if shared_host else np.arange(rank, n_job_pairs, world)
-        e2e_same = bool(np.array_equal(h_match[mine], match[mine]) and np.array_equal(h_nm[mine], nm[mine]))
+    elif shared_host:  # the shared block holds the whole batch in every process, rows in readiness order
+        e2e_same = bool(np.array_equal(h_match, match[gsweep.order]) and np.array_equal(h_nm, nm[gsweep.order]))
+    else:  # private blocks: the rows of this rank's units (unit u of a wave runs on rank u % world)
+        ok = True
+        for a, b_ in gsweep.slices:
+            rows = np.arange(a + rank, b_, world)
+            ok &= bool(np.array_equal(h_match[rows], match[gsweep.order[rows]]) and np.array_equal(h_nm[rows], nm[gsweep.order[rows]]))
+        e2e_same = ok
     assert e2e_same, "e2e results differ from the resident-input results"
     # PCIe as this box delivers it (page-locked host -> device, 64 MB): the floor of a cold sweep
     # (on torch's own stream: its pinned-memory allocator records an event on every stream a block was used on when the
@@ -620,6 +629,7 @@ def main():
                     help="weak: 512 pairs per GPU (default); strong: the same 512 pairs dealt over the GPUs")
     ap.add_argument("--pairs", type=int, default=N_PAIRS, help="keyframe pairs per step (per GPU under weak scaling)")
     ap.add_argument("--window-mb", type=int, default=3072, help="device window of the multi-GPU group per rank")
+    ap.add_argument("--waves", default="", help="e2e at N>1: keyframe bounds of the readiness waves, e.g. 16,32,48,64 (default: 6 waves)")
     ap.add_argument("--no-ref", action="store_true", help="skip the whole-pair run of the reference's own matcher (about 15 s)")
     ap.add_argument("--tc-variant", type=int, default=0, help="tuning: pipeline shape of the tensor-core kernel")
     ap.add_argument("--epi-warps", type=int, default=0, help="tuning: epilogue warps of the tensor-core kernel (4 or 8)")

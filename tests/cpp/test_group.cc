@@ -19,11 +19,13 @@
 
 #include "asdmatch.h"
 
+static asdm_group* g_group = nullptr;
 #define CHECK(call)                                                                          \
   do {                                                                                       \
     int rc__ = (call);                                                                       \
     if (rc__ != 0) {                                                                         \
-      fprintf(stderr, "%s:%d: %s -> %d\n", __FILE__, __LINE__, #call, rc__);                 \
+      fprintf(stderr, "%s:%d: %s -> %d (%s)\n", __FILE__, __LINE__, #call, rc__,             \
+              g_group ? asdm_group_last_error(g_group) : "");                                \
       exit(2);                                                                               \
     }                                                                                        \
   } while (0)
@@ -177,6 +179,7 @@ int main(int argc, char** argv) {
   // ---- the group
   asdm_group* g = nullptr;
   CHECK(asdm_group_create(devices.data(), W, (size_t)512 << 20, &g));
+  g_group = g;
   int bad = 0;
   for (int round = 0; round < 2; round++) {  // twice: the second batch recycles the window range of the first
     std::vector<asdm_set*> gsets((size_t)n_kf * W);
