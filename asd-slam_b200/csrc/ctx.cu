@@ -294,6 +294,7 @@ extern "C" int asdm_set_option(asdm_ctx* ctx, const char* key, int value) {
   if (!strcmp(key, "force_exact")) ctx->opt_force_exact = value;
   else if (!strcmp(key, "init_serial")) ctx->opt_init_serial = value;
   else if (!strcmp(key, "proj_legacy")) ctx->opt_proj_legacy = value;
+  else if (!strcmp(key, "resolve_level")) ctx->resolve_level_hint = std::min(std::max(value, 0), 2);
   else if (!strcmp(key, "proj_ent_cap")) ctx->proj_ent_cap = std::max(value, 64);
   else if (!strcmp(key, "voc_direct")) ctx->opt_voc_direct = value;
   else if (!strcmp(key, "voc_exact")) ctx->opt_voc_exact = value;

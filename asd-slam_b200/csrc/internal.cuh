@@ -78,6 +78,7 @@ struct asdm_ctx {
   int opt_time_kernels = 0;     // record CUDA events around the distance stage of every job run
   std::vector<cudaEvent_t> ev;  // pairs (begin, end), drained by asdm_get_stat("dist_stage_us")
   int proj_ent_cap = 1 << 16;  // entries of the projection candidate pool (grows on overflow)
+  int resolve_level_hint = 0;  // highest k_resolve_bow budget level a job of this context needed (or option "resolve_level")
   int opt_proj_legacy = 0;     // 1 = the three-kernel projection search (gather / dist / resolve) instead of k_proj_fused
   int32_t stat_proj_ns[6] = {0, 0, 0, 0, 0, 0};  // k_proj_fused of the last call: phase durations (ns) and sweeps
   int32_t stat_proj_host_ns[3] = {0, 0, 0};      // host side of the same call: staging | launch | wait

@@ -25,6 +25,7 @@ float bow_keep_threshold(float nnratio, float th_accept) {
 void jobs_init_device() {
   cudaFuncSetAttribute(k_cand_exact, cudaFuncAttributeMaxDynamicSharedMemorySize,
                        (int)(ASDM_DESC_DIM * (CE_TM + CE_TN) * sizeof(float)));
+  cudaFuncSetAttribute(k_resolve_bow, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
 }
 
 // ------------------------------------------------------------------------------- batched keyframe-pair jobs
@@ -349,12 +350,31 @@ int job_run(asdm_job* j) {
                                                        (const int32_t*)j->d_cnt.p, (const Cand*)j->d_cand.p,
                                                        (int32_t*)j->d_acc.p, (int32_t*)j->d_match.p,
                                                        (float*)j->d_dist.p, (int32_t*)j->d_nm.p, j->pub);
-  else
-    k_resolve_bow<<<j->n_pairs, 512, 0, ctx->stream>>>(pairs, j->P, j->cap, j->n_stride, j->m_stride, j->out_stride,
-                                                       (const int32_t*)j->d_cnt.p, (Cand*)j->d_cand.p,
-                                                       (int32_t*)j->d_owner.p, (int32_t*)j->d_acc.p,
-                                                       (int32_t*)j->d_match.p, (float*)j->d_dist.p,
-                                                       (int32_t*)j->d_nm.p, j->pub);
+  else {
+    // greedy resolve with its working set in shared memory; the record budget escalates when a pair had more queries
+    // with candidates than fit: 100 KB (two CTAs per SM) -> 200 KB -> the global-memory kernel
+    int level = std::max(j->resolve_level, ctx->resolve_level_hint);
+    size_t smem = 0;
+    int max_act = 0;
+    for (; level < 2; level++) {
+      const size_t budget = level == 0 ? 100 * 1024 : 200 * 1024, fixed = (size_t)j->m_stride * 4 + 64;
+      if (fixed + 64 * (sizeof(BowRec) + 8) > budget) continue;
+      max_act = (int)std::min<size_t>((size_t)j->n_stride, (budget - fixed) / (sizeof(BowRec) + 8));
+      smem = rb_smem_bytes(j->m_stride, max_act);
+      break;
+    }
+    j->resolve_level = level;
+    if (level < 2)
+      k_resolve_bow<<<j->n_pairs, 512, smem, ctx->stream>>>(pairs, j->P, j->cap, j->n_stride, j->m_stride, j->out_stride,
+                                                            (const int32_t*)j->d_cnt.p, (Cand*)j->d_cand.p, (int32_t*)j->d_match.p,
+                                                            (float*)j->d_dist.p, (int32_t*)j->d_nm.p, max_act, flags + 3, j->pub);
+    else
+      k_resolve_bow_global<<<j->n_pairs, 512, 0, ctx->stream>>>(pairs, j->P, j->cap, j->n_stride, j->m_stride, j->out_stride,
+                                                                (const int32_t*)j->d_cnt.p, (Cand*)j->d_cand.p,
+                                                                (int32_t*)j->d_owner.p, (int32_t*)j->d_acc.p,
+                                                                (int32_t*)j->d_match.p, (float*)j->d_dist.p,
+                                                                (int32_t*)j->d_nm.p, j->pub);
+  }
   LAUNCHED(ctx);
   CK(cudaGetLastError());
   return ASDM_OK;
@@ -391,10 +411,14 @@ int job_settle(asdm_job* j) {
         continue;
       }
     }
-    const bool cand_over = j->h_flags[0] != 0, list_over = j->h_flags[1] != 0;
+    const bool cand_over = j->h_flags[0] != 0, list_over = j->h_flags[1] != 0, rec_over = j->h_flags[3] != 0;
     ctx->stat_tc_pairs = j->use_tc ? j->h_flags[2] : 0;
-    if (!cand_over && !list_over) return ASDM_OK;
+    if (!cand_over && !list_over && !rec_over) return ASDM_OK;
     ctx->stat_retries++;
+    if (rec_over) {  // more queries with candidates than the resolve kernel's shared-memory records: next budget
+      j->resolve_level = std::min(j->resolve_level + 1, 2);
+      ctx->resolve_level_hint = std::max(ctx->resolve_level_hint, j->resolve_level);
+    }
     if (cand_over) j->cap = std::min(std::max(j->cap * 2, 2), std::max(j->m_stride, 2));
     if (list_over) {
       const long need = std::max<long>(2 * (long)j->h_flags[2] + 4096, (long)j->list_cap * 2);

@@ -21,6 +21,7 @@ struct asdm_job {
   size_t zero_bytes = 0;
   int cap = 8;
   int use_tc = 0;
+  int resolve_level = 0;  // k_resolve_bow record budget: 0 = 100 KB, 1 = 200 KB, 2 = global-memory kernel
   int n_work = 0;
   int list_cap = 0;  // total hit slots; split evenly into n_seg segments of seg_cap
   int n_seg = 0, seg_cap = 0;

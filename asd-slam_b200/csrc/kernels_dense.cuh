@@ -99,29 +99,68 @@ __global__ void __launch_bounds__(256) k_cand_exact(const PairDesc* __restrict__
   }
 }
 
-// Exact rerank of the tensor-core short list: one CTA per list segment, one thread per listed (pair, i, j).
+// Exact rerank of the tensor-core short list: one CTA per list segment, warp-cooperative. A warp takes RR_BATCH hits at
+// a time: lanes 0..7 read the hit records and evaluate the gates, then for every live hit the 32 lanes load its two
+// 512-byte rows with ONE coalesced load each (lane l owns floats 4l..4l+3), square the differences and park them in
+// shared memory; lane c finally adds hit c's 128 terms in index order with one fp32 accumulator -- the reference's
+// summation (ORBmatcher.cc:1637-1644) to the bit, without a warp ever touching 32 different rows in one instruction.
 // flags[1] is raised when a segment overflowed (the host grows the list and reruns the job).
-__global__ void __launch_bounds__(256) k_rerank(const PairDesc* __restrict__ pairs, BowParams P, int cap,
-                                                int n_stride, const TcHit* __restrict__ list,
-                                                const int32_t* __restrict__ seg_count, int seg_cap,
-                                                int32_t* __restrict__ cnt, Cand* __restrict__ cand,
-                                                int32_t* __restrict__ flags) {
+#define RR_WARPS 8
+#define RR_BATCH 8
+#define RR_ROW 132
+__global__ void __launch_bounds__(RR_WARPS * 32) k_rerank(const PairDesc* __restrict__ pairs, BowParams P, int cap,
+                                                          int n_stride, const TcHit* __restrict__ list,
+                                                          const int32_t* __restrict__ seg_count, int seg_cap,
+                                                          int32_t* __restrict__ cnt, Cand* __restrict__ cand,
+                                                          int32_t* __restrict__ flags) {
+  __shared__ __align__(16) float s_sq[RR_WARPS][RR_BATCH * RR_ROW];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   int n = seg_count[blockIdx.x];
   if (n > seg_cap) {
     if (threadIdx.x == 0) flags[1] = 1;
     n = seg_cap;
   }
   const TcHit* __restrict__ seg = list + (size_t)blockIdx.x * seg_cap;
-  for (int e = threadIdx.x; e < n; e += blockDim.x) {
-    const TcHit h = seg[e];
-    const PairDesc& pd = pairs[h.pair];
-    const int i = h.i, j = h.j;
-    if (i >= pd.nA || j >= pd.nB) continue;
-    if (!bow_query_ok(pd, P, i) || !bow_target_ok(pd, P, j)) continue;
-    if (pd.nodeA[i] != pd.nodeB[j]) continue;
-    const float d = asdm_exact_dist(pd.descA + (size_t)i * ASDM_DESC_DIM, pd.descB + (size_t)j * ASDM_DESC_DIM);
-    if (!(d <= P.t_keep)) continue;
-    cand_append(cnt, cand, cap, pair_slot(h.pair, n_stride, i), j, d, flags);
+  float* sq = s_sq[warp];
+  for (int b0 = warp * RR_BATCH; b0 < n; b0 += RR_WARPS * RR_BATCH) {
+    const int nb = min(RR_BATCH, n - b0);
+    // lanes 0..nb-1: one hit each -- record, gates, row pointers
+    int hp = 0, hi = 0, hj = 0;
+    bool live = false;
+    if (lane < nb) {
+      const TcHit h = seg[b0 + lane];
+      hp = h.pair; hi = h.i; hj = h.j;
+      const PairDesc& pd = pairs[hp];
+      live = hi < pd.nA && hj < pd.nB && bow_query_ok(pd, P, hi) && bow_target_ok(pd, P, hj) && pd.nodeA[hi] == pd.nodeB[hj];
+    }
+    const unsigned lives = __ballot_sync(0xffffffffu, live);
+    if (!lives) continue;
+    for (int c = 0; c < nb; c++) {
+      if (!((lives >> c) & 1u)) continue;
+      const int p = __shfl_sync(0xffffffffu, hp, c), i = __shfl_sync(0xffffffffu, hi, c), j = __shfl_sync(0xffffffffu, hj, c);
+      const PairDesc& pd = pairs[p];
+      const float4 a4 = __ldg(reinterpret_cast<const float4*>(pd.descA + (size_t)i * ASDM_DESC_DIM) + lane);
+      const float4 b4 = __ldg(reinterpret_cast<const float4*>(pd.descB + (size_t)j * ASDM_DESC_DIM) + lane);
+      float4 s;
+      float d;
+      d = __fsub_rn(a4.x, b4.x); s.x = __fmul_rn(d, d);
+      d = __fsub_rn(a4.y, b4.y); s.y = __fmul_rn(d, d);
+      d = __fsub_rn(a4.z, b4.z); s.z = __fmul_rn(d, d);
+      d = __fsub_rn(a4.w, b4.w); s.w = __fmul_rn(d, d);
+      *reinterpret_cast<float4*>(sq + c * RR_ROW + 4 * lane) = s;
+    }
+    __syncwarp();
+    if (live) {
+      const float4* row = reinterpret_cast<const float4*>(sq + lane * RR_ROW);
+      float acc = 0.f;
+#pragma unroll 8
+      for (int k = 0; k < ASDM_DESC_DIM / 4; k++) {
+        const float4 x = row[k];
+        acc = __fadd_rn(acc, x.x); acc = __fadd_rn(acc, x.y); acc = __fadd_rn(acc, x.z); acc = __fadd_rn(acc, x.w);
+      }
+      if (acc <= P.t_keep) cand_append(cnt, cand, cap, pair_slot(hp, n_stride, hi), hj, acc, flags);
+    }
+    __syncwarp();
   }
 }
 
@@ -214,7 +253,7 @@ __device__ __forceinline__ void publish_row(const PublishArgs& pub, int pair, co
   __threadfence_system();  // the stores are on their way to the other GPUs / the host before this CTA retires
 }
 
-__global__ void __launch_bounds__(512) k_resolve_bow(const PairDesc* __restrict__ pairs, BowParams P, int cap,
+__global__ void __launch_bounds__(512) k_resolve_bow_global(const PairDesc* __restrict__ pairs, BowParams P, int cap,
                                                      int n_stride, int m_stride, int out_stride,
                                                      const int32_t* __restrict__ cnt, Cand* __restrict__ cand,
                                                      int32_t* __restrict__ owner, int32_t* __restrict__ acc,
@@ -350,16 +389,221 @@ __global__ void __launch_bounds__(512) k_resolve_bow(const PairDesc* __restrict_
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// The same greedy resolve with its working set in shared memory (one CTA per keyframe pair): nine queries in ten have no
+// candidate at all, so the CTA first compacts the queries that do into 48-byte records -- position in the reference's
+// query order, candidate count and the RB_TOPK nearest candidates ranked as the reference's scan ranks them (distance,
+// then FeatureVector position of the target) -- and replays the greedy order over those records only, against owner[]
+// in shared memory. A query needs its best and second-best candidate among those not taken by earlier queries, so the
+// short list decides unless (all but one of) its entries are taken; then the full candidate slots are scanned again.
+// k_resolve_bow_global (above) remains for pairs whose records do not fit (rb_fits()).
+#define RB_TOPK 4
+struct BowRec {
+  int32_t i, pos;   // query feature and its position in the reference's loop (FeatureVector order)
+  int32_t n, pad;   // candidates listed
+  int2 top[RB_TOPK];  // {target, distance bits}, x = -1: none
+};
+__host__ __device__ inline size_t rb_smem_bytes(int n_b, int max_act) {
+  return (size_t)max_act * (sizeof(BowRec) + 8) + (size_t)n_b * 4 + 64;
+}
+
+__global__ void __launch_bounds__(512) k_resolve_bow(const PairDesc* __restrict__ pairs, BowParams P, int cap,
+                                                     int n_stride, int m_stride, int out_stride,
+                                                     const int32_t* __restrict__ cnt, Cand* __restrict__ cand,
+                                                     int32_t* __restrict__ match, float* __restrict__ dist,
+                                                     int32_t* __restrict__ nmatches, int max_act,
+                                                     int32_t* __restrict__ fallback, const PublishArgs pub) {
+  extern __shared__ __align__(16) unsigned char rb_smem[];
+  const int pair = blockIdx.x;
+  const PairDesc& pd = pairs[pair];
+  const int nA = pd.nA, nB = pd.nB;
+  const int32_t* cntp = cnt + (size_t)pair * n_stride;
+  const Cand* candp = cand + (size_t)pair * n_stride * cap;
+  int32_t* matchp = match + (size_t)pair * out_stride;
+  float* distp = dist + (size_t)pair * out_stride;
+  BowRec* rec = reinterpret_cast<BowRec*>(rb_smem);
+  int32_t* accj = reinterpret_cast<int32_t*>(rec + max_act);
+  float* accd = reinterpret_cast<float*>(accj + max_act);
+  int32_t* own = reinterpret_cast<int32_t*>(accd + max_act);  // [nB] smallest query position currently accepting target j
+  __shared__ int s_nact, s_changed, s_count, s_pruned, s_over;
+  __shared__ int s_hist[ASDM_HISTO_LENGTH];
+  __shared__ int s_keep[3];
+  const int t = threadIdx.x, nt = blockDim.x, lane = t & 31;
+  if (t == 0) { s_nact = 0; s_count = 0; s_pruned = 0; s_over = 0; }
+  if (t < ASDM_HISTO_LENGTH) s_hist[t] = 0;
+  const int out_n = (P.kind == KIND_BOW_KF_F) ? nB : nA;
+  for (int k = t; k < out_n; k += nt) {
+    matchp[k] = -1;
+    distp[k] = -1.f;
+  }
+  for (int j = t; j < nB; j += nt) own[j] = INT_MAX;
+  __syncthreads();
+  // ---- queries with candidates -> records
+  for (int i = t; i < nA; i += nt) {
+    const int n = min(cntp[i], cap);
+    if (n == 0) continue;
+    const Cand* L = candp + (size_t)i * cap;
+    int tj[RB_TOPK], tp[RB_TOPK];
+    float td[RB_TOPK];
+#pragma unroll
+    for (int k = 0; k < RB_TOPK; k++) { tj[k] = -1; tp[k] = INT_MAX; td[k] = 0.f; }
+    for (int c = 0; c < n; c++) {
+      const Cand x = L[c];
+      float dd = x.d;
+      int jj = x.j, pp = pd.posB[x.j];
+      bool ins = false;  // strict '<' in the reference: among equal distances the first target in scan order wins
+#pragma unroll
+      for (int k = 0; k < RB_TOPK; k++) {
+        if (ins || tj[k] < 0 || dd < td[k] || (dd == td[k] && pp < tp[k])) {
+          const float xd = td[k];
+          const int xj = tj[k], xp = tp[k];
+          td[k] = dd; tj[k] = jj; tp[k] = pp;
+          dd = xd; jj = xj; pp = xp;
+          ins = true;
+        }
+      }
+    }
+    const int slot = atomicAdd(&s_nact, 1);
+    if (slot < max_act) {
+      BowRec R;
+      R.i = i; R.pos = pd.posA[i]; R.n = n; R.pad = 0;
+#pragma unroll
+      for (int k = 0; k < RB_TOPK; k++) R.top[k] = make_int2(tj[k], __float_as_int(td[k]));
+      rec[slot] = R;
+      accj[slot] = -1;
+    } else {
+      s_over = 1;
+    }
+  }
+  __syncthreads();
+  if (s_over) {  // does not fit: the host sees the flag and resolves this job with k_resolve_bow_global
+    if (t == 0) *fallback = 1;
+    return;
+  }
+  const int n_act = s_nact;
+  for (;;) {
+    if (t == 0) s_changed = 0;
+    __syncthreads();
+    for (int a = t; a < n_act; a += nt) {
+      const BowRec R = rec[a];
+      unsigned avail = 0;
+#pragma unroll
+      for (int k = 0; k < RB_TOPK; k++) {
+        const int j = R.top[k].x;
+        const int o = own[j < 0 ? 0 : j];
+        avail |= (j >= 0 && o >= R.pos) ? (1u << k) : 0u;  // taken by an earlier query (vpMapPointMatches / vbMatched2)
+      }
+      const unsigned rest = avail & (avail - 1u);
+      const int k1 = __ffs(avail) - 1, k2 = __ffs(rest) - 1;
+      int2 E1 = R.top[0], E2 = R.top[0];
+#pragma unroll
+      for (int k = 1; k < RB_TOPK; k++) {
+        E1 = k1 == k ? R.top[k] : E1;
+        E2 = k2 == k ? R.top[k] : E2;
+      }
+      float d1 = ASDM_BEST_INIT_BOW, d2 = ASDM_BEST_INIT_BOW;
+      int j1 = -1;
+      if (k1 >= 0) { j1 = E1.x; d1 = __int_as_float(E1.y); }
+      if (k2 >= 0) d2 = __int_as_float(E2.y);
+      if (k2 < 0 && R.n > RB_TOPK) {
+        // fewer than two of the short list are free: the reference's scan over everything listed (:219-228)
+        d1 = ASDM_BEST_INIT_BOW; d2 = ASDM_BEST_INIT_BOW; j1 = -1;
+        int p1 = INT_MAX, p2 = INT_MAX;
+        const Cand* L = candp + (size_t)R.i * cap;
+        for (int c = 0; c < R.n; c++) {
+          const Cand x = L[c];
+          if (own[x.j] < R.pos) continue;
+          const int px = pd.posB[x.j];
+          if (x.d < d1 || (x.d == d1 && px < p1)) {
+            d2 = d1; p2 = p1;
+            d1 = x.d; p1 = px; j1 = x.j;
+          } else if (x.d < d2 || (x.d == d2 && px < p2)) {
+            d2 = x.d; p2 = px;
+          }
+        }
+      }
+      const bool pass = P.strict ? (d1 < P.th_accept) : (d1 <= P.th_accept);
+      const int dec = (j1 >= 0 && pass && d1 < __fmul_rn(P.nnratio, d2)) ? j1 : -1;
+      if (dec != accj[a]) {
+        accj[a] = dec;
+        s_changed = 1;
+      }
+      accd[a] = d1;
+    }
+    __syncthreads();
+    for (int j = t; j < nB; j += nt) own[j] = INT_MAX;
+    __syncthreads();
+    for (int a = t; a < n_act; a += nt) {
+      const int j = accj[a];
+      if (j >= 0) atomicMin(own + j, rec[a].pos);
+    }
+    __syncthreads();
+    if (!s_changed) break;
+  }
+  // rotation consistency (ORBmatcher.cc:242-253, 274-294 / :616-626, 645-663): one shared-memory add per distinct bin
+  // of a warp (__match_any_sync), counts by shuffle
+  int my_count = 0;
+  for (int a0 = 0; a0 < n_act; a0 += nt) {
+    const int a = a0 + t;
+    int bin = -1;
+    if (a < n_act && accj[a] >= 0) {
+      my_count++;
+      if (P.check_ori) bin = asdm_rot_bin(pd.kpA[rec[a].i].angle, pd.kpB[accj[a]].angle);
+    }
+    if (P.check_ori) {
+      const unsigned peers = __match_any_sync(0xffffffffu, bin);
+      if (bin >= 0 && lane == __ffs(peers) - 1) atomicAdd(&s_hist[bin], __popc(peers));
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) my_count += __shfl_xor_sync(0xffffffffu, my_count, o);
+  if (lane == 0 && my_count) atomicAdd(&s_count, my_count);
+  __syncthreads();
+  if (t == 0) {
+    if (P.check_ori) {
+      asdm_three_maxima(s_hist, ASDM_HISTO_LENGTH, s_keep[0], s_keep[1], s_keep[2]);
+      int pruned = 0;
+      for (int b = 0; b < ASDM_HISTO_LENGTH; b++)
+        if (b != s_keep[0] && b != s_keep[1] && b != s_keep[2]) pruned += s_hist[b];
+      s_pruned = pruned;
+    }
+    nmatches[pair] = s_count - s_pruned;
+  }
+  __syncthreads();
+  for (int a = t; a < n_act; a += nt) {
+    const int j = accj[a];
+    if (j < 0) continue;
+    const int i = rec[a].i;
+    if (P.check_ori) {
+      const int b = asdm_rot_bin(pd.kpA[i].angle, pd.kpB[j].angle);
+      if (b != s_keep[0] && b != s_keep[1] && b != s_keep[2]) continue;
+    }
+    if (P.kind == KIND_BOW_KF_F) {
+      matchp[j] = i;
+      distp[j] = accd[a];
+    } else {
+      matchp[i] = j;
+      distp[i] = accd[a];
+    }
+  }
+  if (pub.n) {
+    __syncthreads();  // the row is complete (block-wide) before it is copied out
+    publish_row(pub, pair, matchp, distp, out_n, s_count - s_pruned);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // SearchForTriangulation selection (ORBmatcher.cc:718-774). No cross-query state (vbMatched2 is never set),
 // so each query is independent: among listed candidates (d <= TH_LOW) that pass the epipole gate (:743-747)
 // and CheckDistEpipolarLine (:136-153), the running "dist > bestDist -> continue" keeps the LAST candidate in
 // scan order among equal minima.
-__device__ __forceinline__ bool tri_geo_ok(const PairDesc& pd, const BowParams& P, int i, int j) {
+// scale_factors / level_sigma2: the level tables of BowParams, staged in shared memory by the caller (indexing a
+// kernel-parameter array with a runtime index compiles to a chain of constant loads per candidate)
+__device__ __forceinline__ bool tri_geo_ok(const PairDesc& pd, const float* scale_factors, const float* level_sigma2, int i, int j) {
   const asdm_kp k2 = pd.kpB[j];
   const float x2 = k2.x, y2 = k2.y;
   const int o2 = k2.octave;
   const float distex = __fsub_rn(pd.ex, x2), distey = __fsub_rn(pd.ey, y2);
-  if (__fadd_rn(__fmul_rn(distex, distex), __fmul_rn(distey, distey)) < __fmul_rn(100.f, P.scale_factors[o2]))
+  if (__fadd_rn(__fmul_rn(distex, distex), __fmul_rn(distey, distey)) < __fmul_rn(100.f, scale_factors[o2]))
     return false;
   const float x1 = pd.kpA[i].x, y1 = pd.kpA[i].y;
   const float* F = pd.F12;
@@ -370,7 +614,7 @@ __device__ __forceinline__ bool tri_geo_ok(const PairDesc& pd, const BowParams& 
   const float den = __fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b));
   if (den == 0.f) return false;
   const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
-  return (double)dsqr < __dmul_rn(3.84, (double)P.level_sigma2[o2]);
+  return (double)dsqr < __dmul_rn(3.84, (double)level_sigma2[o2]);
 }
 
 __global__ void __launch_bounds__(512) k_resolve_tri(const PairDesc* __restrict__ pairs, BowParams P, int cap,
@@ -389,9 +633,20 @@ __global__ void __launch_bounds__(512) k_resolve_tri(const PairDesc* __restrict_
   __shared__ int s_hist[ASDM_HISTO_LENGTH];
   __shared__ int s_keep[3];
   __shared__ int s_count;
+  __shared__ float s_sf[ASDM_MAX_LEVELS], s_ls[ASDM_MAX_LEVELS];
   const int t = threadIdx.x, nt = blockDim.x;
   if (t < ASDM_HISTO_LENGTH) s_hist[t] = 0;
   if (t == 0) s_count = 0;
+  if (t < ASDM_MAX_LEVELS) {
+    float a = 0.f, b = 0.f;
+#pragma unroll
+    for (int l = 0; l < ASDM_MAX_LEVELS; l++) {
+      a = l == t ? P.scale_factors[l] : a;
+      b = l == t ? P.level_sigma2[l] : b;
+    }
+    s_sf[t] = a;
+    s_ls[t] = b;
+  }
   __syncthreads();
   for (int i = t; i < nA; i += nt) {
     const int n = min(cntp[i], cap);
@@ -405,7 +660,7 @@ __global__ void __launch_bounds__(512) k_resolve_tri(const PairDesc* __restrict_
       // running "<=" minimum in scan order == smallest d, largest scan position among equals
       const bool better = (bj < 0) ? (x.d <= best) : (x.d < best || (x.d == best && px > bpos));
       if (!better) continue;
-      if (!tri_geo_ok(pd, P, i, x.j)) continue;
+      if (!tri_geo_ok(pd, s_sf, s_ls, i, x.j)) continue;
       best = x.d; bj = x.j; bpos = px;
     }
     accp[i] = bj;

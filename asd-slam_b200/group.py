@@ -242,19 +242,34 @@ class StreamedGroupSweep:
         # argument blocks converted once: the same keyframes are uploaded step after step (bench.py e2e arm)
         self.prepared = [group.prepare_sets(descs[a:b], kps[a:b], grid, featvecs[a:b]) for a, b in zip(lo, self.bounds)]
 
-    def run(self, masks, h_match, h_unit_nm):
+    def run(self, masks, h_match, h_unit_nm, timers=None):
         """h_match [n_pairs, stride] / h_unit_nm [n_pairs]: host arrays of Group.host_array. Returns the sets (the caller
-        releases them with Group.release_sets)."""
+        releases them with Group.release_sets). timers: dict that receives the host seconds spent per phase."""
+        import time
         sets, jobs = [], []
+        tick = time.perf_counter
+        t = tick()
+
+        def lap(key):
+            nonlocal t
+            if timers is not None:
+                now = tick()
+                timers[key] = timers.get(key, 0.0) + now - t
+                t = now
         for (a, b), prep, bound in zip(self.slices, self.prepared, self.bounds):
             sets.extend(self.g.sets_create(prepared=prep))
+            lap("sets_create")
             if b <= a:
                 continue
             sel = self.order[a:b]
             jb = GroupJob(self.g, self.kind, sets[:bound], masks[:bound], self.ia[sel], self.ib[sel], self.nnratio, self.check_ori)
+            lap("job_prepare")
             jb.run(h_match[a:b], None, h_unit_nm[a:b])
+            lap("job_run")
             jobs.append(jb)
         for jb in jobs:
             jb.wait()
+            lap("job_wait")
             jb.destroy()
+            lap("job_destroy")
         return sets

@@ -438,8 +438,13 @@ def run_ours(args):
         gsweep = G.StreamedGroupSweep(grp, pkg.ASDM_JOB_BOW_KF_KF, h_desc, kps_all, c["grid"], fv_all, g_ia, g_ib, c["nnratio"],
                                       c["check_ori"], bounds=waves)
 
+        e2e_timers = {}
+
         def e2e_step():
-            G.Group.release_sets(gsweep.run(masks, h_match, h_nm))
+            ss = gsweep.run(masks, h_match, h_nm, e2e_timers)
+            tr = time.perf_counter()
+            G.Group.release_sets(ss)
+            e2e_timers["release_sets"] = e2e_timers.get("release_sets", 0.0) + time.perf_counter() - tr
         what = (f"per step, in {len(gsweep.bounds)} readiness waves (keyframe bounds {gsweep.bounds}) whose searches overlap the later "
                 "uploads: each keyframe uploaded once (rank k%N, page-locked host memory) and replicated to every GPU by the "
                 "pack kernel (peer stores over NVLink), pairs dealt round-robin by the library, every rank's resolve kernel stores "
@@ -454,6 +459,8 @@ def run_ours(args):
         d2h = n_job_pairs * S * 4 + job.n_units * 4
     e2e_step()
     e2e_step()
+    if world > 1:
+        e2e_timers.clear()
     barrier()
     ctx.synchronize()
     te = time.perf_counter()
@@ -598,6 +605,7 @@ def run_ours(args):
                "keyframe_pairs_per_sec": n_job_pairs * args.steps / (ms * 1e-3),
                "e2e": {"value": total_units / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                        "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms, "floor_ms": e2e_floor_ms, "pcie_h2d_gbs": pcie_gbs,
+                       "host_ms_per_step_by_phase": ({k: 1e3 * v / e2e_steps for k, v in e2e_timers.items()} if world > 1 else None),
                        "floor_what": "the busiest rank's keyframe upload (bytes / measured page-locked H2D bandwidth); the searches and "
                                      "the read-back of the results can hide behind it, nothing else can shrink it",
                        "what": what},
