@@ -247,6 +247,8 @@ extern "C" int asdm_destroy(asdm_ctx* ctx) {
   if (ctx->stage) cudaFreeHost(ctx->stage);
   if (ctx->slot_slab) cudaFreeHost(ctx->slot_slab);
   if (ctx->proj_ctl) cudaFree(ctx->proj_ctl);
+  for (cudaEvent_t e : ctx->stage_ev)
+    if (e) cudaEventDestroy(e);
   if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
   if (ctx->upload_stream) cudaStreamDestroy(ctx->upload_stream);
   if (ctx->upload_done) cudaEventDestroy(ctx->upload_done);
@@ -321,6 +323,16 @@ extern "C" int asdm_get_stat(asdm_ctx* ctx, const char* key, int64_t* value) {
   else if (!strcmp(key, "tc_used")) *value = ctx->stat_tc_used;
   else if (!strcmp(key, "tc_pairs")) *value = ctx->stat_tc_pairs;
   else if (!strcmp(key, "sm_count")) *value = ctx->sm_count;
+  else if (!strncmp(key, "job_us_", 7)) {  // stage durations of the last job run (time_kernels == 2), after a synchronisation
+    static const char* names[4] = {"zero", "distance", "rerank", "resolve"};
+    *value = -1;
+    for (int k = 0; k < 4; k++)
+      if (!strcmp(key + 7, names[k]) && ctx->stage_ev[k] && ctx->stage_ev[k + 1]) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, ctx->stage_ev[k], ctx->stage_ev[k + 1]) == cudaSuccess) *value = (int64_t)(ms * 1000.0f + 0.5f);
+        else cudaGetLastError();
+      }
+  }
   else if (!strncmp(key, "proj_host_ns_", 13) && key[13] >= '0' && key[13] <= '2' && !key[14]) *value = ctx->stat_proj_host_ns[key[13] - '0'];
   else if (!strncmp(key, "proj_ns_", 8) && key[8] >= '0' && key[8] <= '5' && !key[9]) *value = ctx->stat_proj_ns[key[8] - '0'];
   else if (!strcmp(key, "dist_stage_us") || !strcmp(key, "dist_stage_runs")) {

@@ -77,6 +77,7 @@ struct asdm_ctx {
   DevBuf scratch[12];
   int opt_time_kernels = 0;     // record CUDA events around the distance stage of every job run
   std::vector<cudaEvent_t> ev;  // pairs (begin, end), drained by asdm_get_stat("dist_stage_us")
+  cudaEvent_t stage_ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // time_kernels == 2: begin | zero | distance | rerank | resolve of the last run
   int proj_ent_cap = 1 << 16;  // entries of the projection candidate pool (grows on overflow)
   int resolve_level_hint = 0;  // highest k_resolve_bow budget level a job of this context needed (or option "resolve_level")
   int opt_proj_legacy = 0;     // 1 = the three-kernel projection search (gather / dist / resolve) instead of k_proj_fused
@@ -210,9 +211,11 @@ struct BowParams {
 #define KIND_TRIANGULATION 2
 #define KIND_BOW_KF_F 3
 
-struct Cand {
+struct Cand {  // 16 B: one LDG.128 brings everything the resolve kernels rank a candidate by
   int32_t j;
   float d;
+  int32_t pos;  // posB[j]: the target's place in the reference's scan (tie order among equal distances)
+  int32_t pad;  // posA[i] << 5 | rotation bin of the pair (cand_meta)
 };
 
 struct TcHit {  // one (pair, query, target) short-listed by the tensor-core kernel

@@ -95,6 +95,7 @@ int job_prepare(asdm_ctx* ctx, const asdm_job_desc* d, int kind_internal, asdm_j
   for (int k = 0; k < d->n_kf; k++) {
     const asdm_set* s = d->sets[k];
     if (!s || s->ctx != ctx || !d->masks[k]) return fail(ctx, ASDM_ERR_INVALID, "bad keyframe set / mask");
+    if (s->n >= (1 << 24)) return fail(ctx, ASDM_ERR_INVALID, "keyframe set too large for a batched search (2^24 features)");
     if (!s->has_fv) return fail(ctx, ASDM_ERR_INVALID, "keyframe set has no FeatureVector (asdm_set_featvec)");
     if (!s->has_kps) return fail(ctx, ASDM_ERR_INVALID, "keyframe set has no keypoints");
   }
@@ -314,9 +315,21 @@ int job_run(asdm_job* j) {
   if (j->n_pairs == 0) return ASDM_OK;
   const PairDesc* pairs = (const PairDesc*)j->d_pairs.p;
   int32_t* flags = (int32_t*)j->d_flags.p;
+  if (ctx->opt_time_kernels == 2) {
+    if (!ctx->stage_ev[0]) CK(cudaEventCreate(&ctx->stage_ev[0]));
+    CK(cudaEventRecord(ctx->stage_ev[0], ctx->stream));
+  }
   {
     const int rc = zero_device(ctx, j->d_zero.p, j->zero_bytes);  // flags | hit-list segment counts | candidate counts
     if (rc) return rc;
+  }
+  // time_kernels == 2: one event behind every stage of this run (zero | distance | rerank | resolve), read back through
+  // asdm_get_stat("job_us_<stage>") after a synchronisation -- the in-step duration of each kernel, warm caches, no profiler
+  const bool stages = ctx->opt_time_kernels == 2;
+  if (stages) {
+    for (int k = 0; k < 5; k++)
+      if (!ctx->stage_ev[k]) CK(cudaEventCreate(&ctx->stage_ev[k]));
+    CK(cudaEventRecord(ctx->stage_ev[1], ctx->stream));  // [0] sits in front of the fill above
   }
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   if (ctx->opt_time_kernels) {
@@ -329,9 +342,11 @@ int job_run(asdm_job* j) {
                                 (TcHit*)j->d_list.p, j->seg_cap, (int32_t*)j->d_seg_count.p, flags + 2));
     LAUNCHED(ctx);
     if (ev1) CK(cudaEventRecord(ev1, ctx->stream));
-    k_rerank<<<j->n_seg, 256, 0, ctx->stream>>>(pairs, j->P, j->cap, j->n_stride, (const TcHit*)j->d_list.p,
-                                                (const int32_t*)j->d_seg_count.p, j->seg_cap, (int32_t*)j->d_cnt.p,
-                                                (Cand*)j->d_cand.p, flags);
+    if (stages) CK(cudaEventRecord(ctx->stage_ev[2], ctx->stream));
+    if (j->n_seg > RR_MAX_SEG) return fail(ctx, ASDM_ERR_INTERNAL, "more hit-list segments than k_rerank can scan");
+    k_rerank<<<ctx->sm_count * 5, RR_WARPS * 32, 0, ctx->stream>>>(pairs, j->P, j->cap, j->n_stride, (const TcHit*)j->d_list.p,
+                                                                   (const int32_t*)j->d_seg_count.p, j->n_seg, j->seg_cap,
+                                                                   (int32_t*)j->d_cnt.p, (Cand*)j->d_cand.p, flags);
     LAUNCHED(ctx);
   } else {
     dim3 grid((j->n_stride + CE_TM - 1) / CE_TM, (j->m_stride + CE_TN - 1) / CE_TN, j->n_pairs);
@@ -345,6 +360,7 @@ int job_run(asdm_job* j) {
     ctx->ev.push_back(ev0);
     ctx->ev.push_back(ev1);
   }
+  if (stages) CK(cudaEventRecord(ctx->stage_ev[3], ctx->stream));
   if (j->kind == KIND_TRIANGULATION)
     k_resolve_tri<<<j->n_pairs, 512, 0, ctx->stream>>>(pairs, j->P, j->cap, j->n_stride, j->out_stride,
                                                        (const int32_t*)j->d_cnt.p, (const Cand*)j->d_cand.p,
@@ -376,6 +392,7 @@ int job_run(asdm_job* j) {
                                                                 (int32_t*)j->d_nm.p, j->pub);
   }
   LAUNCHED(ctx);
+  if (stages) CK(cudaEventRecord(ctx->stage_ev[4], ctx->stream));
   CK(cudaGetLastError());
   return ASDM_OK;
 }

@@ -18,11 +18,18 @@ __device__ __forceinline__ bool bow_target_ok(const PairDesc& pd, const BowParam
 
 __device__ __forceinline__ int pair_slot(int pair, int n_stride, int i) { return pair * n_stride + i; }
 
-__device__ __forceinline__ void cand_append(int32_t* cnt, Cand* cand, int cap, int qslot, int j, float d,
+// What the resolve kernels need of a listed pair besides (j, d): the target's scan position, the query's position in the
+// reference's loop and the rotation bin of the pair -- gathered here, by the thread that already holds i and j, so that
+// the resolve kernel never chases posA / posB / keypoint angles through global memory.
+__device__ __forceinline__ int cand_meta(const PairDesc& pd, const BowParams& P, int i, int j) {
+  const int bin = P.check_ori ? asdm_rot_bin(pd.kpA[i].angle, pd.kpB[j].angle) : 0;  // e.g. ORBmatcher.cc:245-250
+  return (pd.posA[i] << 5) | bin;
+}
+__device__ __forceinline__ void cand_append(int32_t* cnt, Cand* cand, int cap, int qslot, int j, float d, int pos, int meta,
                                             int32_t* overflow) {
   const int s = atomicAdd(cnt + qslot, 1);
   if (s < cap) {
-    cand[(size_t)qslot * cap + s] = Cand{j, d};
+    *reinterpret_cast<int4*>(cand + (size_t)qslot * cap + s) = make_int4(j, __float_as_int(d), pos, meta);
   } else {
     *overflow = 1;
   }
@@ -94,7 +101,7 @@ __global__ void __launch_bounds__(256) k_cand_exact(const PairDesc* __restrict__
       if (!(acc[r][c] <= P.t_keep)) continue;
       if (!bow_query_ok(pd, P, i) || !bow_target_ok(pd, P, j)) continue;
       if (pd.nodeA[i] != pd.nodeB[j]) continue;
-      cand_append(cnt, cand, cap, pair_slot(pair, n_stride, i), j, acc[r][c], overflow);
+      cand_append(cnt, cand, cap, pair_slot(pair, n_stride, i), j, acc[r][c], pd.posB[j], cand_meta(pd, P, i, j), overflow);
     }
   }
 }
@@ -108,30 +115,73 @@ __global__ void __launch_bounds__(256) k_cand_exact(const PairDesc* __restrict__
 #define RR_WARPS 8
 #define RR_BATCH 8
 #define RR_ROW 132
+#define RR_MAX_SEG 2048
+// Persistent and balanced: the hit list is segmented by (CTA, epilogue warp) of the shortlist kernel and the segments are
+// far from equal, so every CTA first turns the segment counts into a prefix sum (shared memory) and the warps of the whole
+// grid then take batches of RR_BATCH consecutive hits of the FLATTENED list, round-robin; a hit's segment is found by
+// binary search in the prefix.
 __global__ void __launch_bounds__(RR_WARPS * 32) k_rerank(const PairDesc* __restrict__ pairs, BowParams P, int cap,
                                                           int n_stride, const TcHit* __restrict__ list,
-                                                          const int32_t* __restrict__ seg_count, int seg_cap,
+                                                          const int32_t* __restrict__ seg_count, int n_seg, int seg_cap,
                                                           int32_t* __restrict__ cnt, Cand* __restrict__ cand,
                                                           int32_t* __restrict__ flags) {
   __shared__ __align__(16) float s_sq[RR_WARPS][RR_BATCH * RR_ROW];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  int n = seg_count[blockIdx.x];
-  if (n > seg_cap) {
-    if (threadIdx.x == 0) flags[1] = 1;
-    n = seg_cap;
+  __shared__ int s_prefix[RR_MAX_SEG + 1];
+  __shared__ int s_warp_tot[RR_WARPS];
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  // inclusive scan of the (clamped) segment counts, RR_WARPS * 32 at a time
+  int carry = 0;
+  for (int base = 0; base < n_seg; base += RR_WARPS * 32) {
+    const int s = base + t;
+    int v = 0;
+    if (s < n_seg) {
+      v = seg_count[s];
+      if (v > seg_cap) {
+        flags[1] = 1;
+        v = seg_cap;
+      }
+    }
+    int x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) s_warp_tot[warp] = x;
+    __syncthreads();
+    int woff = 0;
+    for (int w = 0; w < warp; w++) woff += s_warp_tot[w];
+    int tot = 0;
+    for (int w = 0; w < RR_WARPS; w++) tot += s_warp_tot[w];
+    if (s < n_seg) s_prefix[s + 1] = carry + woff + x;
+    carry += tot;
+    __syncthreads();
   }
-  const TcHit* __restrict__ seg = list + (size_t)blockIdx.x * seg_cap;
+  if (t == 0) s_prefix[0] = 0;
+  __syncthreads();
+  const int total = s_prefix[n_seg];
   float* sq = s_sq[warp];
-  for (int b0 = warp * RR_BATCH; b0 < n; b0 += RR_WARPS * RR_BATCH) {
-    const int nb = min(RR_BATCH, n - b0);
-    // lanes 0..nb-1: one hit each -- record, gates, row pointers
-    int hp = 0, hi = 0, hj = 0;
+  const int n_batches = (total + RR_BATCH - 1) / RR_BATCH;
+  for (int b = blockIdx.x * RR_WARPS + warp; b < n_batches; b += gridDim.x * RR_WARPS) {
+    const int f0 = b * RR_BATCH, nb = min(RR_BATCH, total - f0);
+    // lanes 0..nb-1: one hit each -- where it lives, its record, the gates
+    int hp = 0, hi = 0, hj = 0, hpos = 0;
     bool live = false;
     if (lane < nb) {
-      const TcHit h = seg[b0 + lane];
+      const int f = f0 + lane;
+      int lo = 0, hi_s = n_seg;  // largest s with prefix[s] <= f
+      while (hi_s - lo > 1) {
+        const int mid = (lo + hi_s) >> 1;
+        if (s_prefix[mid] <= f) lo = mid;
+        else hi_s = mid;
+      }
+      const TcHit h = list[(size_t)lo * seg_cap + (f - s_prefix[lo])];
       hp = h.pair; hi = h.i; hj = h.j;
       const PairDesc& pd = pairs[hp];
-      live = hi < pd.nA && hj < pd.nB && bow_query_ok(pd, P, hi) && bow_target_ok(pd, P, hj) && pd.nodeA[hi] == pd.nodeB[hj];
+      if (hi < pd.nA && hj < pd.nB && bow_query_ok(pd, P, hi) && pd.maskB[hj] == P.mask_sense) {
+        hpos = pd.posB[hj];
+        live = hpos >= 0 && pd.nodeA[hi] == pd.nodeB[hj];
+      }
     }
     const unsigned lives = __ballot_sync(0xffffffffu, live);
     if (!lives) continue;
@@ -158,7 +208,7 @@ __global__ void __launch_bounds__(RR_WARPS * 32) k_rerank(const PairDesc* __rest
         const float4 x = row[k];
         acc = __fadd_rn(acc, x.x); acc = __fadd_rn(acc, x.y); acc = __fadd_rn(acc, x.z); acc = __fadd_rn(acc, x.w);
       }
-      if (acc <= P.t_keep) cand_append(cnt, cand, cap, pair_slot(hp, n_stride, hi), hj, acc, flags);
+      if (acc <= P.t_keep) cand_append(cnt, cand, cap, pair_slot(hp, n_stride, hi), hj, acc, hpos, cand_meta(pairs[hp], P, hi, hj), flags);
     }
     __syncwarp();
   }
@@ -400,7 +450,7 @@ __global__ void __launch_bounds__(512) k_resolve_bow_global(const PairDesc* __re
 struct BowRec {
   int32_t i, pos;   // query feature and its position in the reference's loop (FeatureVector order)
   int32_t n, pad;   // candidates listed
-  int2 top[RB_TOPK];  // {target, distance bits}, x = -1: none
+  int2 top[RB_TOPK];  // {target | rotation bin << 24, distance bits}, x = -1: none
 };
 __host__ __device__ inline size_t rb_smem_bytes(int n_b, int max_act) {
   return (size_t)max_act * (sizeof(BowRec) + 8) + (size_t)n_b * 4 + 64;
@@ -437,43 +487,75 @@ __global__ void __launch_bounds__(512) k_resolve_bow(const PairDesc* __restrict_
   }
   for (int j = t; j < nB; j += nt) own[j] = INT_MAX;
   __syncthreads();
-  // ---- queries with candidates -> records
-  for (int i = t; i < nA; i += nt) {
-    const int n = min(cntp[i], cap);
-    if (n == 0) continue;
-    const Cand* L = candp + (size_t)i * cap;
-    int tj[RB_TOPK], tp[RB_TOPK];
-    float td[RB_TOPK];
+  // ---- queries with candidates -> records. Pass 1 compacts the queries that have any (one coalesced read of the counts,
+  // positions handed out by a ballot per warp); pass 2 spreads those over all threads, each candidate one 16-byte load.
+  int32_t* act_i = accj;  // [max_act] scratch: the active query of every slot (accj is initialised afterwards)
+  for (int i0 = 0; i0 < nA; i0 += 8 * nt) {
+    int c8[8];
 #pragma unroll
-    for (int k = 0; k < RB_TOPK; k++) { tj[k] = -1; tp[k] = INT_MAX; td[k] = 0.f; }
-    for (int c = 0; c < n; c++) {
-      const Cand x = L[c];
-      float dd = x.d;
-      int jj = x.j, pp = pd.posB[x.j];
-      bool ins = false;  // strict '<' in the reference: among equal distances the first target in scan order wins
+    for (int u = 0; u < 8; u++) {  // eight independent loads in flight per thread
+      const int i = i0 + u * nt + t;
+      c8[u] = i < nA ? cntp[i] : 0;
+    }
 #pragma unroll
-      for (int k = 0; k < RB_TOPK; k++) {
-        if (ins || tj[k] < 0 || dd < td[k] || (dd == td[k] && pp < tp[k])) {
-          const float xd = td[k];
-          const int xj = tj[k], xp = tp[k];
-          td[k] = dd; tj[k] = jj; tp[k] = pp;
-          dd = xd; jj = xj; pp = xp;
-          ins = true;
-        }
+    for (int u = 0; u < 8; u++) {
+      const int i = i0 + u * nt + t;
+      const bool has = c8[u] > 0;
+      const unsigned m = __ballot_sync(0xffffffffu, has);
+      int base = 0;
+      if (lane == 0 && m) base = atomicAdd(&s_nact, __popc(m));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (has) {
+        const int slot = base + __popc(m & ((1u << lane) - 1u));
+        if (slot < max_act) act_i[slot] = i;
+        else s_over = 1;
       }
     }
-    const int slot = atomicAdd(&s_nact, 1);
-    if (slot < max_act) {
+  }
+  __syncthreads();
+  if (!s_over) {
+    const int n_all = s_nact;
+    for (int a = t; a < n_all; a += nt) {
+      const int i = act_i[a], n = min(cntp[i], cap);
+      const int4* L = reinterpret_cast<const int4*>(candp + (size_t)i * cap);
+      int tj[RB_TOPK], tp[RB_TOPK];
+      float td[RB_TOPK];
+#pragma unroll
+      for (int k = 0; k < RB_TOPK; k++) { tj[k] = -1; tp[k] = INT_MAX; td[k] = 0.f; }
+      int pos_i = 0;
+      for (int c0 = 0; c0 < n; c0 += 4) {
+        int4 x[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) x[u] = c0 + u < n ? __ldg(L + c0 + u) : make_int4(-1, 0, 0, 0);
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          if (x[u].x < 0) continue;
+          pos_i = x[u].w >> 5;
+          float dd = __int_as_float(x[u].y);
+          int jj = x[u].x | ((x[u].w & 31) << 24), pp = x[u].z;
+          bool ins = false;  // strict '<' in the reference: among equal distances the first target in scan order wins
+#pragma unroll
+          for (int k = 0; k < RB_TOPK; k++) {
+            if (ins || tj[k] < 0 || dd < td[k] || (dd == td[k] && pp < tp[k])) {
+              const float xd = td[k];
+              const int xj = tj[k], xp = tp[k];
+              td[k] = dd; tj[k] = jj; tp[k] = pp;
+              dd = xd; jj = xj; pp = xp;
+              ins = true;
+            }
+          }
+        }
+      }
       BowRec R;
-      R.i = i; R.pos = pd.posA[i]; R.n = n; R.pad = 0;
+      R.i = i; R.pos = pos_i; R.n = n; R.pad = 0;
 #pragma unroll
       for (int k = 0; k < RB_TOPK; k++) R.top[k] = make_int2(tj[k], __float_as_int(td[k]));
-      rec[slot] = R;
-      accj[slot] = -1;
-    } else {
-      s_over = 1;
+      rec[a] = R;
     }
   }
+  __syncthreads();
+  if (!s_over)
+    for (int a = t; a < s_nact; a += nt) accj[a] = -1;
   __syncthreads();
   if (s_over) {  // does not fit: the host sees the flag and resolves this job with k_resolve_bow_global
     if (t == 0) *fallback = 1;
@@ -489,7 +571,7 @@ __global__ void __launch_bounds__(512) k_resolve_bow(const PairDesc* __restrict_
 #pragma unroll
       for (int k = 0; k < RB_TOPK; k++) {
         const int j = R.top[k].x;
-        const int o = own[j < 0 ? 0 : j];
+        const int o = own[j < 0 ? 0 : (j & 0xffffff)];
         avail |= (j >= 0 && o >= R.pos) ? (1u << k) : 0u;  // taken by an earlier query (vpMapPointMatches / vbMatched2)
       }
       const unsigned rest = avail & (avail - 1u);
@@ -501,7 +583,7 @@ __global__ void __launch_bounds__(512) k_resolve_bow(const PairDesc* __restrict_
         E2 = k2 == k ? R.top[k] : E2;
       }
       float d1 = ASDM_BEST_INIT_BOW, d2 = ASDM_BEST_INIT_BOW;
-      int j1 = -1;
+      int j1 = -1;  // target | rotation bin << 24
       if (k1 >= 0) { j1 = E1.x; d1 = __int_as_float(E1.y); }
       if (k2 >= 0) d2 = __int_as_float(E2.y);
       if (k2 < 0 && R.n > RB_TOPK) {
@@ -512,10 +594,10 @@ __global__ void __launch_bounds__(512) k_resolve_bow(const PairDesc* __restrict_
         for (int c = 0; c < R.n; c++) {
           const Cand x = L[c];
           if (own[x.j] < R.pos) continue;
-          const int px = pd.posB[x.j];
+          const int px = x.pos;
           if (x.d < d1 || (x.d == d1 && px < p1)) {
             d2 = d1; p2 = p1;
-            d1 = x.d; p1 = px; j1 = x.j;
+            d1 = x.d; p1 = px; j1 = x.j | ((x.pad & 31) << 24);
           } else if (x.d < d2 || (x.d == d2 && px < p2)) {
             d2 = x.d; p2 = px;
           }
@@ -534,10 +616,12 @@ __global__ void __launch_bounds__(512) k_resolve_bow(const PairDesc* __restrict_
     __syncthreads();
     for (int a = t; a < n_act; a += nt) {
       const int j = accj[a];
-      if (j >= 0) atomicMin(own + j, rec[a].pos);
+      if (j >= 0) atomicMin(own + (j & 0xffffff), rec[a].pos);
     }
     __syncthreads();
-    if (!s_changed) break;
+    const int changed = s_changed;
+    __syncthreads();  // everybody has read the flag before thread 0 clears it for the next sweep
+    if (!changed) break;
   }
   // rotation consistency (ORBmatcher.cc:242-253, 274-294 / :616-626, 645-663): one shared-memory add per distinct bin
   // of a warp (__match_any_sync), counts by shuffle
@@ -547,7 +631,7 @@ __global__ void __launch_bounds__(512) k_resolve_bow(const PairDesc* __restrict_
     int bin = -1;
     if (a < n_act && accj[a] >= 0) {
       my_count++;
-      if (P.check_ori) bin = asdm_rot_bin(pd.kpA[rec[a].i].angle, pd.kpB[accj[a]].angle);
+      if (P.check_ori) bin = accj[a] >> 24;
     }
     if (P.check_ori) {
       const unsigned peers = __match_any_sync(0xffffffffu, bin);
@@ -570,11 +654,10 @@ __global__ void __launch_bounds__(512) k_resolve_bow(const PairDesc* __restrict_
   }
   __syncthreads();
   for (int a = t; a < n_act; a += nt) {
-    const int j = accj[a];
-    if (j < 0) continue;
-    const int i = rec[a].i;
+    if (accj[a] < 0) continue;
+    const int j = accj[a] & 0xffffff, i = rec[a].i;
     if (P.check_ori) {
-      const int b = asdm_rot_bin(pd.kpA[i].angle, pd.kpB[j].angle);
+      const int b = accj[a] >> 24;
       if (b != s_keep[0] && b != s_keep[1] && b != s_keep[2]) continue;
     }
     if (P.kind == KIND_BOW_KF_F) {

@@ -356,7 +356,9 @@ __global__ void __launch_bounds__(PF_WARPS * 32) k_proj_fused(const ProjFusedArg
         if (j >= 0 && (rec[a].cnt_blocks >> 31)) atomicMin(own + j, rec[a].qid);
       }
       __syncthreads();
-      if (!s_changed) break;
+      const int changed = s_changed;
+      __syncthreads();  // everybody has read the flag before thread 0 clears it for the next sweep
+      if (!changed) break;
     }
     const unsigned long long ts4 = pf_now();
     // F.mvpMapPoints[bestIdx] = pMP: the last accepting query owns the keypoint

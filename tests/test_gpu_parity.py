@@ -185,6 +185,55 @@ def test_c5_loop_sweep_job(pkg, ctx, oracle, force_exact):
         s.release()
 
 
+@pytest.mark.parametrize("level", [0, 1, 2])
+def test_resolve_kernel_levels_agree_with_oracle(pkg, ctx, oracle, level):
+    """k_resolve_bow keeps its records in shared memory under two budgets (levels 0, 1) and falls back to the global-memory
+    kernel (level 2); many pairs in one launch so that CTAs of different speeds overlap (a race in the sweep flag once
+    slipped through the small cases). All three must equal the oracle."""
+    c = pkg.synth.config5(n=1500, n_pairs=96, n_kf=12, n_nodes=3)
+    kfs = c["kfs"]
+    ctx.set_option("resolve_level", level)
+    try:
+        sets = [pkg.DescriptorSet(ctx, k["desc"], k["kps"], c["grid"], k["fv"]) for k in kfs]
+        job = pkg.PairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, sets, [k["valid"] for k in kfs], c["ia"], c["ib"], c["nnratio"], c["check_ori"])
+        for rep in range(3):
+            job.run()
+            nm, match, dist = job.fetch()
+            if rep == 0:
+                onm, omatch, odist = oracle.batch_bow_kf_kf(kfs, c["ia"], c["ib"], c["nnratio"], c["check_ori"], threads=oracle.max_threads())
+            _eq(nm, onm, "nmatches")
+            _eq(match[:, :1500], omatch, "match12")
+            _eq_dist(dist[:, :1500], odist, "dist12")
+        job.destroy()
+        for s in sets:
+            s.release()
+    finally:
+        ctx.set_option("resolve_level", 0)
+
+
+def test_resolve_record_budget_escalates(pkg, ctx, oracle):
+    """More queries with candidates than the 100 KB record budget holds (4000-feature keyframes, most features matched):
+    the job must notice, rerun with the larger budget and still equal the oracle."""
+    c = pkg.synth.config5(n=4000, n_pairs=3, n_kf=3, n_nodes=1)
+    kfs = c["kfs"]
+    ones = [np.ones(4000, np.uint8) for _ in kfs]
+    for k, v in zip(kfs, ones):
+        k["valid"] = v
+    ctx.set_option("resolve_level", 0)
+    sets = [pkg.DescriptorSet(ctx, k["desc"], k["kps"], c["grid"], k["fv"]) for k in kfs]
+    job = pkg.PairJob(ctx, pkg.ASDM_JOB_BOW_KF_KF, sets, ones, c["ia"], c["ib"], 0.95, True)
+    job.run()
+    nm, match, dist = job.fetch()
+    onm, omatch, odist = oracle.batch_bow_kf_kf(kfs, c["ia"], c["ib"], 0.95, 1, threads=oracle.max_threads())
+    _eq(nm, onm, "nmatches")
+    _eq(match[:, :4000], omatch, "match12")
+    _eq_dist(dist[:, :4000], odist, "dist12")
+    job.destroy()
+    for s in sets:
+        s.release()
+    ctx.set_option("resolve_level", 0)
+
+
 def test_small_cand_cap_retries(pkg, ctx, oracle):
     """Candidate pools start tiny and must grow transparently (no silent truncation)."""
     c = pkg.synth.config1(500, 500)
