@@ -40,7 +40,7 @@ EXPORTS = [
     "asdm_group_local_count", "asdm_group_local_rank", "asdm_group_ctx", "asdm_group_host_alloc", "asdm_group_host_free",
     "asdm_group_host_barrier", "asdm_group_sets_create", "asdm_group_job_prepare", "asdm_group_job_units",
     "asdm_group_job_stride", "asdm_group_job_run", "asdm_group_job_wait", "asdm_group_job_counts", "asdm_group_job_fetch",
-    "asdm_group_job_gathered", "asdm_group_job_destroy",
+    "asdm_group_job_gathered", "asdm_group_job_flush", "asdm_group_job_destroy",
     "asdm_distinctive_descriptors",
     "asdm_vocab_create", "asdm_vocab_release", "asdm_vocab_transform",
     "asdm_bowdb_create", "asdm_bowdb_release", "asdm_bowdb_add", "asdm_bowdb_erase", "asdm_bowdb_clear", "asdm_bowdb_size",
@@ -87,6 +87,7 @@ class GJobDesc(C.Structure):
 
 
 ASDM_GATHER_DEVICE = 1
+ASDM_GATHER_NO_DIST = 2
 ALLGATHER_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t)
 
 
@@ -178,6 +179,7 @@ def load():
     lib.asdm_group_job_counts.argtypes = [vp, vp, vp]
     lib.asdm_group_job_fetch.argtypes = [vp, vp, vp, vp]
     lib.asdm_group_job_gathered.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
+    lib.asdm_group_job_flush.argtypes = [vp]
     lib.asdm_group_job_destroy.argtypes = [vp]
     lib.asdm_distinctive_descriptors.argtypes = [vp, C.POINTER(vp), C.c_int, C.c_int, vp, vp, vp, vp, vp]
     lib.asdm_desc_block_bytes.argtypes = [C.c_int]

@@ -76,6 +76,10 @@ struct GroupMember {
   // recorded on the main stream whenever a range of this window is released: what is queued there up to that point may
   // still read the range, so whoever takes it next orders itself behind this event (and behind nothing queued later)
   cudaEvent_t rel_evt = nullptr;
+  // The barriers that close the exchange of a job's records run on a stream of their own, behind the job's kernels, so
+  // that the NEXT job's distance kernel already runs while the last rows of this one are still crossing NVLink
+  cudaStream_t bar_stream = nullptr;
+  cudaEvent_t ev_main = nullptr, ev_sync = nullptr;
 };
 
 struct HostCtl {  // shared by the processes of the group (one page)
@@ -168,7 +172,7 @@ static int group_signal(asdm_group* g, GroupMember& M, int ch) {
   BarrierPeers P;
   P.n = g->world;
   for (int r = 0; r < g->world; r++) P.flags[r] = (uint32_t*)M.peer[r] + ch * ASDM_MAX_PEERS;
-  k_group_signal<<<1, 32, 0, ch == CH_MAIN ? ctx->stream : ctx->prep_stream>>>(P, M.rank, M.epoch[ch]);
+  k_group_signal<<<1, 32, 0, ch == CH_MAIN ? M.bar_stream : ctx->prep_stream>>>(P, M.rank, M.epoch[ch]);
   ctx->stat_total_launches++;
   GCK(cudaGetLastError());
   return ASDM_OK;
@@ -177,7 +181,7 @@ static int group_wait(asdm_group* g, GroupMember& M, int ch) {  // for the epoch
   asdm_ctx* ctx = M.ctx;
   if (g->world == 1) return ASDM_OK;
   GCK(cudaSetDevice(ctx->device));
-  k_group_wait<<<1, 32, 0, ch == CH_MAIN ? ctx->stream : ctx->prep_stream>>>((const uint32_t*)M.win + ch * ASDM_MAX_PEERS, g->world,
+  k_group_wait<<<1, 32, 0, ch == CH_MAIN ? M.bar_stream : ctx->prep_stream>>>((const uint32_t*)M.win + ch * ASDM_MAX_PEERS, g->world,
                                                                            M.epoch[ch], M.h_err, 10ull * 1000000000ull);
   ctx->stat_total_launches++;
   GCK(cudaGetLastError());
@@ -260,6 +264,9 @@ static int group_finish_setup(asdm_group* g) {
     *M.h_err = 0;
     GCK(cudaEventCreateWithFlags(&M.rel_evt, cudaEventDisableTiming));
     GCK(cudaEventRecord(M.rel_evt, M.ctx->stream));
+    GCK(cudaStreamCreateWithFlags(&M.bar_stream, cudaStreamNonBlocking));
+    GCK(cudaEventCreateWithFlags(&M.ev_main, cudaEventDisableTiming));
+    GCK(cudaEventCreateWithFlags(&M.ev_sync, cudaEventDisableTiming));
     M.alloc.reset(WIN_HEADER, g->win_bytes);
   }
   return ASDM_OK;
@@ -406,6 +413,12 @@ extern "C" int asdm_group_destroy(asdm_group* g) {
     if (M.win) cudaFree(M.win);
     if (M.h_err) cudaFreeHost(M.h_err);
     if (M.rel_evt) cudaEventDestroy(M.rel_evt);
+    if (M.bar_stream) {
+      cudaStreamSynchronize(M.bar_stream);
+      cudaStreamDestroy(M.bar_stream);
+    }
+    if (M.ev_main) cudaEventDestroy(M.ev_main);
+    if (M.ev_sync) cudaEventDestroy(M.ev_sync);
     if (M.own_ctx) asdm_destroy(M.ctx);
   }
   cudaGetLastError();
@@ -763,6 +776,8 @@ struct asdm_gjob {
     int n_local = 0;
     DevBuf row_map;
     bool has_gather = false;
+    cudaEvent_t ev_bar[2] = {nullptr, nullptr};  // barrier behind the run that filled generation g has completed
+    bool bar_valid[2] = {false, false};
   };
   std::vector<Local> loc;
   // ASDM_GATHER_DEVICE: two generations of [rows][stride] match | dist and [units] counts at the same offset of every window
@@ -902,18 +917,26 @@ extern "C" int asdm_group_job_run(asdm_gjob* j, int32_t* h_match, float* h_dist,
   if (host && (!device_visible(h_match) || !device_visible(h_unit_nm) || (h_dist && !device_visible(h_dist))))
     return gfail(g, ASDM_ERR_INVALID, "host result arrays must be page-locked (asdm_group_host_alloc / asdm_host_alloc)");
   j->gen ^= 1;
-  if ((j->gather & ASDM_GATHER_DEVICE) && !j->ran) {
+  const bool gather = (j->gather & ASDM_GATHER_DEVICE) != 0;
+  if (gather && !j->ran) {
     // The gathered records live in a range of every window that other jobs may have used before: nobody stores into a
     // peer's range until that peer has prepared this job too (and so is done with whatever was there).
     for (int l = 0; l < L; l++) {
-      std::lock_guard<std::recursive_mutex> lkc(g->m[(size_t)l].ctx->mu);
-      const int rc = group_signal(g, g->m[(size_t)l], CH_MAIN);
+      GroupMember& M = g->m[(size_t)l];
+      std::lock_guard<std::recursive_mutex> lkc(M.ctx->mu);
+      GCK(cudaSetDevice(M.ctx->device));
+      GCK(cudaEventRecord(M.ev_main, M.ctx->stream));
+      GCK(cudaStreamWaitEvent(M.bar_stream, M.ev_main, 0));
+      const int rc = group_signal(g, M, CH_MAIN);
       if (rc) return rc;
     }
     for (int l = 0; l < L; l++) {
-      std::lock_guard<std::recursive_mutex> lkc(g->m[(size_t)l].ctx->mu);
-      const int rc = group_wait(g, g->m[(size_t)l], CH_MAIN);
+      GroupMember& M = g->m[(size_t)l];
+      std::lock_guard<std::recursive_mutex> lkc(M.ctx->mu);
+      const int rc = group_wait(g, M, CH_MAIN);
       if (rc) return rc;
+      GCK(cudaEventRecord(M.ev_sync, M.bar_stream));
+      GCK(cudaStreamWaitEvent(M.ctx->stream, M.ev_sync, 0));
     }
   }
   for (int l = 0; l < L; l++) {
@@ -929,10 +952,9 @@ extern "C" int asdm_group_job_run(asdm_gjob* j, int32_t* h_match, float* h_dist,
     pub.col_range = j->split ? 1 : 0;
     pub.stride = j->stride;
     int n = 0;
-    // every destination takes the same records: distances travel unless the host side has no room for them
-    bool want_dist = true;
+    unsigned dist_mask = 0;  // which destinations take the distance rows
     if (host) {
-      if (!h_dist) want_dist = false;
+      if (h_dist) dist_mask |= 1u << n;
       pub.match[n] = h_match;
       pub.dist[n] = h_dist ? h_dist : (float*)h_match;
       pub.nm[n] = h_unit_nm;
@@ -941,6 +963,9 @@ extern "C" int asdm_group_job_run(asdm_gjob* j, int32_t* h_match, float* h_dist,
     if (j->gather & ASDM_GATHER_DEVICE) {
       for (int r = 0; r < W; r++) {
         char* b = M.peer[r] + j->g_off + (size_t)j->gen * j->gen_bytes;
+        // ASDM_GATHER_NO_DIST: peers receive what the reference's calls return (index lists + counts); the distances of
+        // a unit stay with the rank that computed it (its own window still gets them)
+        if (!(j->gather & ASDM_GATHER_NO_DIST) || r == M.rank) dist_mask |= 1u << n;
         pub.match[n] = (int32_t*)b;
         pub.dist[n] = (float*)(b + j->o_dist);
         pub.nm[n] = (int32_t*)(b + j->o_nm);
@@ -949,18 +974,51 @@ extern "C" int asdm_group_job_run(asdm_gjob* j, int32_t* h_match, float* h_dist,
     }
     if (n > ASDM_MAX_PEERS) return gfail(g, ASDM_ERR_INVALID, "too many publish destinations (world + host > 16)");
     pub.n = n;
-    pub.no_dist = want_dist ? 0 : 1;
+    pub.dist_mask = dist_mask;
+    pub.no_dist = dist_mask ? 0 : 1;
+    // This run fills generation `gen`, which the run before the previous one filled too: a peer may still be reading
+    // those rows until it has started the previous run -- i.e. until the barrier behind the previous run has completed.
+    if (gather && X.bar_valid[j->gen ^ 1]) {
+      GCK(cudaSetDevice(M.ctx->device));
+      GCK(cudaStreamWaitEvent(M.ctx->stream, X.ev_bar[j->gen ^ 1], 0));
+    }
     int rc = job_run(job);
     if (rc) return gfail(g, rc, asdm_last_error(M.ctx));
-    if ((j->gather & ASDM_GATHER_DEVICE) && (rc = group_signal(g, M, CH_MAIN))) return rc;
+    if (gather) {  // the barrier follows the kernels on its own stream: the next run does not queue behind it
+      GCK(cudaEventRecord(M.ev_main, M.ctx->stream));
+      GCK(cudaStreamWaitEvent(M.bar_stream, M.ev_main, 0));
+      if ((rc = group_signal(g, M, CH_MAIN))) return rc;
+    }
   }
-  if (j->gather & ASDM_GATHER_DEVICE)  // every rank's rows have landed in every window once this has run
+  if (gather)  // every rank's rows have landed in every window once this has run
     for (int l = 0; l < L; l++) {
-      std::lock_guard<std::recursive_mutex> lkc(g->m[(size_t)l].ctx->mu);
-      const int rc = group_wait(g, g->m[(size_t)l], CH_MAIN);
+      GroupMember& M = g->m[(size_t)l];
+      asdm_gjob::Local& X = j->loc[(size_t)l];
+      std::lock_guard<std::recursive_mutex> lkc(M.ctx->mu);
+      const int rc = group_wait(g, M, CH_MAIN);
       if (rc) return rc;
+      if (!X.ev_bar[j->gen]) GCK(cudaEventCreateWithFlags(&X.ev_bar[j->gen], cudaEventDisableTiming));
+      GCK(cudaEventRecord(X.ev_bar[j->gen], M.bar_stream));
+      X.bar_valid[j->gen] = true;
     }
   j->ran = true;
+  return ASDM_OK;
+}
+
+// Orders whatever is queued next on the members' streams behind the exchange of the last run (stream-side, no host wait):
+// device code that reads asdm_group_job_gathered() goes behind this.
+extern "C" int asdm_group_job_flush(asdm_gjob* j) {
+  if (!j) return ASDM_ERR_INVALID;
+  asdm_group* g = j->g;
+  std::lock_guard<std::recursive_mutex> lk(g->mu);
+  for (size_t l = 0; l < g->m.size(); l++) {
+    GroupMember& M = g->m[l];
+    asdm_gjob::Local& X = j->loc[l];
+    if (!(j->gather & ASDM_GATHER_DEVICE) || !X.bar_valid[j->gen]) continue;
+    std::lock_guard<std::recursive_mutex> lkc(M.ctx->mu);
+    GCK(cudaSetDevice(M.ctx->device));
+    GCK(cudaStreamWaitEvent(M.ctx->stream, X.ev_bar[j->gen], 0));
+  }
   return ASDM_OK;
 }
 
@@ -974,10 +1032,9 @@ extern "C" int asdm_group_job_wait(asdm_gjob* j) {
     std::lock_guard<std::recursive_mutex> lkc(M.ctx->mu);
     int rc = job_settle(j->loc[l].job);
     if (rc) return gfail(g, rc, asdm_last_error(M.ctx));
-    if (j->loc[l].n_local == 0) {  // nothing ran on this member, but its barrier kernels may still be in flight
-      GCK(cudaSetDevice(M.ctx->device));
-      GCK(cudaStreamSynchronize(M.ctx->stream));
-    }
+    GCK(cudaSetDevice(M.ctx->device));
+    if (j->loc[l].n_local == 0) GCK(cudaStreamSynchronize(M.ctx->stream));  // nothing ran here, but set-up work may be queued
+    if (j->gather & ASDM_GATHER_DEVICE) GCK(cudaStreamSynchronize(M.bar_stream));  // the exchange of the last run
     if (*M.h_err) {
       *M.h_err = 0;
       return gfail(g, ASDM_ERR_INTERNAL, "device barrier timed out: a rank of the group never arrived");
@@ -1038,6 +1095,13 @@ extern "C" int asdm_group_job_destroy(asdm_gjob* j) {
       release(M.ctx, X.row_map);
     }
     if (X.job) asdm_job_destroy(X.job);
+    for (cudaEvent_t& e : X.ev_bar)
+      if (e) {
+        cudaSetDevice(M.ctx->device);
+        cudaStreamSynchronize(M.bar_stream);
+        cudaEventDestroy(e);
+        e = nullptr;
+      }
     if (X.has_gather) {
       std::lock_guard<std::recursive_mutex> lkc(M.ctx->mu);
       window_release(M, j->g_off, j->g_bytes);

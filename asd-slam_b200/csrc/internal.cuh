@@ -163,6 +163,7 @@ struct PublishArgs {
   int stride = 0;                   // entries per row of the gathered arrays
   int multicast = 0;                // destinations are NVLink multicast (NVLS) addresses: one store reaches every rank
   int no_dist = 0;                  // publish index lists + counts only (what the reference calls return); distances stay local
+  unsigned dist_mask = 0xffffffffu; // bit p: destination p takes the distance rows too (when no_dist == 0)
   int32_t* match[ASDM_MAX_PEERS];   // [world * per_rank][stride]
   float* dist[ASDM_MAX_PEERS];
   int32_t* nm[ASDM_MAX_PEERS];      // [world * per_rank]

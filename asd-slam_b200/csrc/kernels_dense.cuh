@@ -277,7 +277,7 @@ __device__ __forceinline__ void publish_row(const PublishArgs& pub, int pair, co
       const int4 di = make_int4(__float_as_int(d.x), __float_as_int(d.y), __float_as_int(d.z), __float_as_int(d.w));
       for (int p = 0; p < pub.n; p++) {
         pub_store4(pub.match[p] + row * pub.stride + e, m, mc);
-        if (wd) pub_store4(pub.dist[p] + row * pub.stride + e, di, mc);
+        if (wd && ((pub.dist_mask >> p) & 1u)) pub_store4(pub.dist[p] + row * pub.stride + e, di, mc);
       }
     }
     for (int k = hi4 + t; k < hi; k += nt) {  // a block that ends off a 16-byte boundary (the last block of a pair)
@@ -285,7 +285,7 @@ __device__ __forceinline__ void publish_row(const PublishArgs& pub, int pair, co
       const float d = k < out_n ? distp[k] : -1.f;
       for (int p = 0; p < pub.n; p++) {
         pub_store1(pub.match[p] + row * pub.stride + k, m, mc);
-        if (wd) pub_store1(pub.dist[p] + row * pub.stride + k, __float_as_int(d), mc);
+        if (wd && ((pub.dist_mask >> p) & 1u)) pub_store1(pub.dist[p] + row * pub.stride + k, __float_as_int(d), mc);
       }
     }
   } else {
@@ -294,7 +294,7 @@ __device__ __forceinline__ void publish_row(const PublishArgs& pub, int pair, co
       const float d = k < out_n ? distp[k] : -1.f;
       for (int p = 0; p < pub.n; p++) {
         pub_store1(pub.match[p] + row * pub.stride + k, m, mc);
-        if (wd) pub_store1(pub.dist[p] + row * pub.stride + k, __float_as_int(d), mc);
+        if (wd && ((pub.dist_mask >> p) & 1u)) pub_store1(pub.dist[p] + row * pub.stride + k, __float_as_int(d), mc);
       }
     }
   }

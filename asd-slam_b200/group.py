@@ -15,7 +15,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._lib import ASDM_GATHER_DEVICE, ASDM_JOB_TRIANGULATION, KP_DTYPE, AsdmError, FeatVec, GJobDesc, Grid, SetDesc, ptr
+from ._lib import ASDM_GATHER_DEVICE, ASDM_GATHER_NO_DIST, ASDM_JOB_TRIANGULATION, KP_DTYPE, AsdmError, FeatVec, GJobDesc, Grid, SetDesc, ptr
 from .matcher import Context, DescriptorSet, _f32, _i32, _u8
 
 
@@ -159,7 +159,7 @@ class GroupJob:
     `blocks_per_pair` row blocks of a pair -- runs on rank u % world."""
 
     def __init__(self, group, kind, sets, masks, ia, ib, nnratio=0.6, check_ori=True, F12=None, epipoles=None, scale_factors=None,
-                 level_sigma2=None, blocks_per_pair=1, gather_device=False):
+                 level_sigma2=None, blocks_per_pair=1, gather_device=False, gather_dist=True):
         self.g = group
         L, n_kf = group.local_count, len(sets)
         self.n_pairs = len(ia)
@@ -177,7 +177,7 @@ class GroupJob:
             j.F12, j.epipoles, j.scale_factors, j.level_sigma2 = ptr(k["F12"]), ptr(k["ep"]), ptr(k["sf"]), ptr(k["ls"])
             j.n_levels = len(k["sf"])
         d.blocks_per_pair = int(blocks_per_pair)
-        d.gather = ASDM_GATHER_DEVICE if gather_device else 0
+        d.gather = (ASDM_GATHER_DEVICE | (0 if gather_dist else ASDM_GATHER_NO_DIST)) if gather_device else 0
         h = C.c_void_p()
         group.check(group.lib.asdm_group_job_prepare(group.h, C.byref(d), C.byref(h)))
         self.h = h
@@ -191,6 +191,10 @@ class GroupJob:
 
     def wait(self):
         self.g.check(self.g.lib.asdm_group_job_wait(self.h))
+
+    def flush(self):
+        """Orders what is queued next on the members' streams behind the exchange of the last run (no host wait)."""
+        self.g.check(self.g.lib.asdm_group_job_flush(self.h))
 
     def counts(self, h_unit_nm):
         nm = np.empty(self.n_pairs, np.int32)

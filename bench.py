@@ -297,7 +297,7 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    def time_steps(step, steps, warm):
+    def time_steps(step, steps, warm, flush=None):
         """ms per step of `step()` (queues work on the context stream), device-timed, max over ranks."""
         for _ in range(warm):
             step()
@@ -307,6 +307,8 @@ def run_ours(args):
         e0.record(stream)
         for _ in range(steps):
             step()
+        if flush is not None:
+            flush()  # the exchange of the last step closes inside the timed region
         e1.record(stream)
         ctx.synchronize()
         return max_over_ranks(e0.elapsed_time(e1)) / steps
@@ -327,7 +329,8 @@ def run_ours(args):
     # ---- resident arm: the keyframes are uploaded (once over PCIe, replicated over NVLink by the pack kernel) before
     # the timed region, as the SLAM system does at keyframe creation; a step = the sweep + the exchange of the results
     sets = grp.sets_create(prepared=prepared)
-    job = G.GroupJob(grp, pkg.ASDM_JOB_BOW_KF_KF, sets, masks, g_ia, g_ib, c["nnratio"], c["check_ori"], gather_device=world > 1)
+    job = G.GroupJob(grp, pkg.ASDM_JOB_BOW_KF_KF, sets, masks, g_ia, g_ib, c["nnratio"], c["check_ori"], gather_device=world > 1,
+                     gather_dist=args.gather_dist)
     S = job.stride
     for _ in range(max(args.warmup, 3)):
         job.run()
@@ -344,6 +347,7 @@ def run_ours(args):
     e0.record(stream)
     for _ in range(args.steps):
         job.run()
+    job.flush()  # the exchange of the last step closes inside the timed region
     e1.record(stream)
     ctx.synchronize()
     barrier()
@@ -365,9 +369,10 @@ def run_ours(args):
     if not strong:
         k_steps = max(10, args.steps)
         if world > 1:
-            job_s = G.GroupJob(grp, pkg.ASDM_JOB_BOW_KF_KF, sets, masks, ia1, ib1, c["nnratio"], c["check_ori"], gather_device=True)
+            job_s = G.GroupJob(grp, pkg.ASDM_JOB_BOW_KF_KF, sets, masks, ia1, ib1, c["nnratio"], c["check_ori"], gather_device=True,
+                               gather_dist=args.gather_dist)
             job_s.run(); job_s.wait()
-            ms_n = time_steps(job_s.run, k_steps, 3)
+            ms_n = time_steps(job_s.run, k_steps, 3, job_s.flush)
             job_s.wait()
             nm_s, match_s, _ = job_s.fetch()
             job_s.destroy()
@@ -506,7 +511,7 @@ def run_ours(args):
     blocks = 1 if world == 1 else 2
     j1 = G.GroupJob(grp, pkg.ASDM_JOB_TRIANGULATION, sets4, m4, c4["ia"], c4["ib"], blocks_per_pair=blocks, gather_device=world > 1, **tri)
     j1.run(); j1.wait()
-    ms_c4_one = time_steps(j1.run, 100, 5)
+    ms_c4_one = time_steps(j1.run, 100, 5, j1.flush)
     j1.wait()
     nm4, match4, dist4 = j1.fetch()
     j1.destroy()
@@ -515,7 +520,7 @@ def run_ours(args):
     jB = G.GroupJob(grp, pkg.ASDM_JOB_TRIANGULATION, sets4, m4, np.tile(c4["ia"], reps), np.tile(c4["ib"], reps), blocks_per_pair=1,
                     gather_device=world > 1, **triB)
     jB.run(); jB.wait()
-    ms_c4_batch = time_steps(jB.run, 20, 3)
+    ms_c4_batch = time_steps(jB.run, 20, 3, jB.flush)
     jB.wait()
     jB.destroy()
     G.Group.release_sets(sets4)
@@ -600,8 +605,9 @@ def run_ours(args):
                           "l2": "inputs larger than L2 (197 MB of descriptors + candidate pools vs 126 MB); no flush",
                           "timed_region_ms": ms, "tensor_core_shortlist": bool(tc_used), "shortlist_hits_per_step": int(shortlist_hits),
                           "sharding": ("asdm_group_* (csrc/group.cu): units dealt round-robin; every rank's resolve kernel stores its finished "
-                                       "match / distance / count records into every GPU's window (peer stores over NVLink), device-side "
-                                       "flag barrier -- no NCCL on the data path") if world > 1 else "single GPU"},
+                                       + ("match / distance / count" if args.gather_dist else "match / count (what SearchByBoW returns; distances stay "
+                                          "with the rank that computed them)") + " records into every GPU's window (peer stores over NVLink), "
+                                       "device-side flag barrier on its own stream -- no NCCL on the data path") if world > 1 else "single GPU"},
                "keyframe_pairs_per_sec": n_job_pairs * args.steps / (ms * 1e-3),
                "e2e": {"value": total_units / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                        "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms, "floor_ms": e2e_floor_ms, "pcie_h2d_gbs": pcie_gbs,
@@ -638,6 +644,7 @@ def main():
     ap.add_argument("--pairs", type=int, default=N_PAIRS, help="keyframe pairs per step (per GPU under weak scaling)")
     ap.add_argument("--window-mb", type=int, default=3072, help="device window of the multi-GPU group per rank")
     ap.add_argument("--waves", default="", help="e2e at N>1: keyframe bounds of the readiness waves, e.g. 16,32,48,64 (default: 6 waves)")
+    ap.add_argument("--gather-dist", action="store_true", help="N>1: the distance rows cross NVLink too (default: index lists + counts)")
     ap.add_argument("--no-ref", action="store_true", help="skip the whole-pair run of the reference's own matcher (about 15 s)")
     ap.add_argument("--tc-variant", type=int, default=0, help="tuning: pipeline shape of the tensor-core kernel")
     ap.add_argument("--epi-warps", type=int, default=0, help="tuning: epilogue warps of the tensor-core kernel (4 or 8)")

@@ -348,11 +348,15 @@ int asdm_group_sets_create(asdm_group* g, const asdm_set_desc* descs, int n_sets
 /* A batched search dealt over the group: unit u (a pair, or one of `blocks_per_pair` 128-row-aligned query row blocks of a
  * pair: triangulation without rotation check only, see asdm_job_desc) belongs to rank u % world. job.sets = the array
  * asdm_group_sets_create returned ([n_kf * local_count]). */
-enum { ASDM_GATHER_DEVICE = 1 }; /* every rank's GPU also receives every unit's records (asdm_group_job_gathered) */
+enum {
+  ASDM_GATHER_DEVICE = 1, /* every rank's GPU also receives every unit's records (asdm_group_job_gathered) */
+  ASDM_GATHER_NO_DIST = 2 /* ... index lists + counts only, what the reference's calls return (vpMatches12, vMatchedPairs): the
+                           * distance rows of a unit stay on the rank that computed it (half the NVLink traffic) */
+};
 typedef struct {
   asdm_job_desc job;
   int32_t blocks_per_pair; /* >= 1 */
-  int32_t gather;          /* 0 or ASDM_GATHER_DEVICE */
+  int32_t gather;          /* 0, ASDM_GATHER_DEVICE, or ASDM_GATHER_DEVICE | ASDM_GATHER_NO_DIST */
 } asdm_gjob_desc;
 int asdm_group_job_prepare(asdm_group* g, const asdm_gjob_desc* desc, asdm_gjob** out);
 int asdm_group_job_units(const asdm_gjob* j);  /* n_pairs, or more when pairs are split */
@@ -370,9 +374,12 @@ int asdm_group_job_counts(const asdm_gjob* j, const int32_t* h_unit_nm, int32_t*
  * over all pairs would report it. Any pointer may be NULL. */
 int asdm_group_job_fetch(asdm_gjob* j, int32_t* match12, float* dist12, int32_t* nmatches);
 /* ASDM_GATHER_DEVICE: device pointers, on local member l, of the records of ALL units as the last run left them
- * (match / dist: [units or pairs][stride] as above, unit_nm: [units]); valid after asdm_group_job_wait, or for work
- * queued on the member's stream behind asdm_group_job_run (the device-side barrier orders it). */
+ * (match / dist: [units or pairs][stride] as above, unit_nm: [units]); complete after asdm_group_job_wait, or -- without
+ * a host wait -- for work queued on the member's stream behind asdm_group_job_flush. The barrier that closes the exchange
+ * of a run is queued on a stream of its own: the next run's kernels do not wait for the last rows of this one to cross
+ * NVLink (two generations of arrays alternate). */
 int asdm_group_job_gathered(asdm_gjob* j, int l, void** match, void** dist, void** unit_nm);
+int asdm_group_job_flush(asdm_gjob* j);
 int asdm_group_job_destroy(asdm_gjob* j);
 
 /* ------------------------------------------------------------------ map-point descriptor maintenance */

@@ -64,7 +64,8 @@ def test_group_in_one_process_matches_oracle(pkg, ctx, oracle, kind, n, blocks, 
         descs = [np.ascontiguousarray(k["desc"], np.float32) for k in c["kfs"]]
         for step in range(2):  # the second batch recycles the window range of the first
             sets = g.sets_create(descs, [k["kps"] for k in c["kfs"]], c["grid"], [k["fv"] for k in c["kfs"]])
-            job = G.GroupJob(g, job_kind, sets, masks, c["ia"], c["ib"], blocks_per_pair=blocks, gather_device=(step == 1), **kw)
+            job = G.GroupJob(g, job_kind, sets, masks, c["ia"], c["ib"], blocks_per_pair=blocks, gather_device=(step == 1),
+                             gather_dist=(world == 2), **kw)
             nm, match, dist = job.fetch()
             assert np.array_equal(nm, ref[0]) and ref[0].sum() > 0
             assert np.array_equal(match[:, :n], ref[1])
