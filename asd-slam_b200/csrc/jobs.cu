@@ -344,7 +344,12 @@ int job_run(asdm_job* j) {
     if (ev1) CK(cudaEventRecord(ev1, ctx->stream));
     if (stages) CK(cudaEventRecord(ctx->stage_ev[2], ctx->stream));
     if (j->n_seg > RR_MAX_SEG) return fail(ctx, ASDM_ERR_INTERNAL, "more hit-list segments than k_rerank can scan");
-    k_rerank<<<ctx->sm_count * 5, RR_WARPS * 32, 0, ctx->stream>>>(pairs, j->P, j->cap, j->n_stride, (const TcHit*)j->d_list.p,
+    int rr_per_sm = 4;  // persistent: exactly the CTAs that are resident (the batches are dealt round-robin over the grid)
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&rr_per_sm, k_rerank, RR_WARPS * 32, 0) != cudaSuccess || rr_per_sm < 1) {
+      cudaGetLastError();
+      rr_per_sm = 1;
+    }
+    k_rerank<<<ctx->sm_count * rr_per_sm, RR_WARPS * 32, 0, ctx->stream>>>(pairs, j->P, j->cap, j->n_stride, (const TcHit*)j->d_list.p,
                                                                    (const int32_t*)j->d_seg_count.p, j->n_seg, j->seg_cap,
                                                                    (int32_t*)j->d_cnt.p, (Cand*)j->d_cand.p, flags);
     LAUNCHED(ctx);

@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(256) k_cand_exact(const PairDesc* __restrict__
 // far from equal, so every CTA first turns the segment counts into a prefix sum (shared memory) and the warps of the whole
 // grid then take batches of RR_BATCH consecutive hits of the FLATTENED list, round-robin; a hit's segment is found by
 // binary search in the prefix.
-__global__ void __launch_bounds__(RR_WARPS * 32) k_rerank(const PairDesc* __restrict__ pairs, BowParams P, int cap,
+__global__ void __launch_bounds__(RR_WARPS * 32, 4) k_rerank(const PairDesc* __restrict__ pairs, BowParams P, int cap,
                                                           int n_stride, const TcHit* __restrict__ list,
                                                           const int32_t* __restrict__ seg_count, int n_seg, int seg_cap,
                                                           int32_t* __restrict__ cnt, Cand* __restrict__ cand,
@@ -164,8 +164,9 @@ __global__ void __launch_bounds__(RR_WARPS * 32) k_rerank(const PairDesc* __rest
   const int n_batches = (total + RR_BATCH - 1) / RR_BATCH;
   for (int b = blockIdx.x * RR_WARPS + warp; b < n_batches; b += gridDim.x * RR_WARPS) {
     const int f0 = b * RR_BATCH, nb = min(RR_BATCH, total - f0);
-    // lanes 0..nb-1: one hit each -- where it lives, its record, the gates
+    // lanes 0..nb-1: one hit each -- where it lives, its record, the gates, the addresses of its two rows
     int hp = 0, hi = 0, hj = 0, hpos = 0;
+    unsigned long long pa = 0, pb = 0;
     bool live = false;
     if (lane < nb) {
       const int f = f0 + lane;
@@ -182,22 +183,37 @@ __global__ void __launch_bounds__(RR_WARPS * 32) k_rerank(const PairDesc* __rest
         hpos = pd.posB[hj];
         live = hpos >= 0 && pd.nodeA[hi] == pd.nodeB[hj];
       }
+      pa = reinterpret_cast<unsigned long long>(pd.descA + (size_t)hi * ASDM_DESC_DIM);
+      pb = reinterpret_cast<unsigned long long>(pd.descB + (size_t)hj * ASDM_DESC_DIM);
     }
     const unsigned lives = __ballot_sync(0xffffffffu, live);
     if (!lives) continue;
-    for (int c = 0; c < nb; c++) {
-      if (!((lives >> c) & 1u)) continue;
-      const int p = __shfl_sync(0xffffffffu, hp, c), i = __shfl_sync(0xffffffffu, hi, c), j = __shfl_sync(0xffffffffu, hj, c);
-      const PairDesc& pd = pairs[p];
-      const float4 a4 = __ldg(reinterpret_cast<const float4*>(pd.descA + (size_t)i * ASDM_DESC_DIM) + lane);
-      const float4 b4 = __ldg(reinterpret_cast<const float4*>(pd.descB + (size_t)j * ASDM_DESC_DIM) + lane);
-      float4 s;
-      float d;
-      d = __fsub_rn(a4.x, b4.x); s.x = __fmul_rn(d, d);
-      d = __fsub_rn(a4.y, b4.y); s.y = __fmul_rn(d, d);
-      d = __fsub_rn(a4.z, b4.z); s.z = __fmul_rn(d, d);
-      d = __fsub_rn(a4.w, b4.w); s.w = __fmul_rn(d, d);
-      *reinterpret_cast<float4*>(sq + c * RR_ROW + 4 * lane) = s;
+    // the row loads go out four hits at a time before the first one is used: 8 x 512 B in flight per warp (all 16 at once
+    // costs 96 registers and two resident CTAs less per SM -- measured slower)
+#pragma unroll
+    for (int h0 = 0; h0 < RR_BATCH; h0 += 4) {
+      float4 a4[4], b4[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int c = h0 + u;
+        const unsigned long long qa = __shfl_sync(0xffffffffu, pa, c), qb = __shfl_sync(0xffffffffu, pb, c);
+        if ((lives >> c) & 1u) {
+          a4[u] = __ldg(reinterpret_cast<const float4*>(qa) + lane);
+          b4[u] = __ldg(reinterpret_cast<const float4*>(qb) + lane);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int c = h0 + u;
+        if (!((lives >> c) & 1u)) continue;
+        float4 s;
+        float d;
+        d = __fsub_rn(a4[u].x, b4[u].x); s.x = __fmul_rn(d, d);
+        d = __fsub_rn(a4[u].y, b4[u].y); s.y = __fmul_rn(d, d);
+        d = __fsub_rn(a4[u].z, b4[u].z); s.z = __fmul_rn(d, d);
+        d = __fsub_rn(a4[u].w, b4[u].w); s.w = __fmul_rn(d, d);
+        *reinterpret_cast<float4*>(sq + c * RR_ROW + 4 * lane) = s;
+      }
     }
     __syncwarp();
     if (live) {

@@ -74,8 +74,12 @@ def ncu_traffic():
         if blob not in text.split("== kernel", 1)[0]:
             continue
         tot = 0.0
-        for m in re.finditer(r"dram__bytes_(read|write)\.sum\s+([0-9.]+)\s+(\w+)", text):
-            tot += float(m.group(2)) * mult.get(m.group(3), 1.0)
+        for section in text.split("== kernel")[1:]:  # a summary may hold several kernels: only k_tc_shortlist's counters
+            if "k_tc_shortlist" not in section.split("\n", 1)[0]:
+                continue
+            for m in re.finditer(r"dram__bytes_(read|write)\.sum\s+([0-9.]+)\s+(\w+)", section):
+                tot += float(m.group(2)) * mult.get(m.group(3), 1.0)
+            break
         return (tot or None), os.path.relpath(path, ROOT)
     return None, f"no ncu summary under profiles/ for tc_shortlist.cu blob {blob[:12]}"
 
