@@ -27,7 +27,7 @@ HISTO_LENGTH = 30
 
 # every symbol include/asdmatch.h declares (tests/test_abi.py checks the .so exports exactly these)
 EXPORTS = [
-    "asdm_create", "asdm_destroy", "asdm_last_error", "asdm_stream", "asdm_synchronize", "asdm_set_stream",
+    "asdm_create", "asdm_fork", "asdm_destroy", "asdm_last_error", "asdm_stream", "asdm_synchronize", "asdm_set_stream",
     "asdm_host_alloc", "asdm_host_free", "asdm_set_option", "asdm_get_stat",
     "asdm_set_create", "asdm_set_create_async", "asdm_set_create_batch", "asdm_set_retain", "asdm_set_release", "asdm_set_size", "asdm_set_featvec",
     "asdm_set_read_desc", "asdm_desc_block_bytes", "asdm_set_save_blocks", "asdm_set_load_block",
@@ -115,6 +115,7 @@ def load():
     lib = C.CDLL(LIB_PATH)
     vp, i32, f32 = C.c_void_p, C.c_int32, C.c_float
     lib.asdm_create.argtypes = [C.c_int, C.POINTER(vp)]
+    lib.asdm_fork.argtypes = [vp, C.POINTER(vp)]
     lib.asdm_destroy.argtypes = [vp]
     lib.asdm_last_error.argtypes = [vp]
     lib.asdm_last_error.restype = C.c_char_p

@@ -167,6 +167,7 @@ int stage_upload(asdm_ctx* ctx, void* dst, const void* src, size_t bytes, cudaSt
 
 enum { SLOT_BYTES = 64, SLOT_COUNT = 4096 };
 int32_t* slot_get(asdm_ctx* ctx) {
+  std::lock_guard<std::mutex> lk(ctx->slot_mu);
   if (!ctx->slot_slab) {
     if (cudaHostAlloc((void**)&ctx->slot_slab, (size_t)SLOT_BYTES * SLOT_COUNT, cudaHostAllocMapped) != cudaSuccess) {
       cudaGetLastError();
@@ -184,6 +185,7 @@ int32_t* slot_get(asdm_ctx* ctx) {
   return p;
 }
 void slot_put(asdm_ctx* ctx, int32_t* p) {
+  std::lock_guard<std::mutex> lk(ctx->slot_mu);
   if (p) ctx->slot_free.push_back((int)(((char*)p - ctx->slot_slab) / SLOT_BYTES));
 }
 
@@ -200,6 +202,7 @@ extern "C" int asdm_create(int device, asdm_ctx** out) {
   asdm_ctx* ctx = new (std::nothrow) asdm_ctx();
   if (!ctx) return ASDM_ERR_OOM;
   ctx->device = device;
+  ctx->family = ctx;
   if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaStreamCreateWithFlags(&ctx->upload_stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaStreamCreateWithFlags(&ctx->prep_stream, cudaStreamNonBlocking) != cudaSuccess ||
@@ -234,6 +237,19 @@ extern "C" int asdm_create(int device, asdm_ctx** out) {
     }
   }
   *out = ctx;
+  return ASDM_OK;
+}
+
+// One context per thread of the SLAM system (upstream ORB-SLAM2 runs tracking, local mapping and loop closing
+// concurrently): a forked context has its own streams, staging arena, scratch and lock, so a thread never waits for
+// another thread's search -- and it may search the sets the other contexts of the family created (Frame / KeyFrame
+// descriptors are uploaded once, by whoever builds the object).
+extern "C" int asdm_fork(asdm_ctx* parent, asdm_ctx** out) {
+  if (!parent || !out) return ASDM_ERR_INVALID;
+  const int rc = asdm_create(parent->device, out);
+  if (rc) return rc;
+  (*out)->family = parent->family;
+  (*out)->opt_force_exact = parent->opt_force_exact;
   return ASDM_OK;
 }
 

@@ -15,6 +15,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <deque>
 #include <map>
 #include <new>
 
@@ -25,11 +26,13 @@
 // symmetric object sits at the same offset of every window without any handle exchange.
 struct WinAlloc {
   std::map<size_t, size_t> free_;  // offset -> length
+  std::mutex mu;                   // sets (and with them their slab's range) are released from any thread
   void reset(size_t lo, size_t hi) {
     free_.clear();
     free_[lo] = hi - lo;
   }
   bool alloc(size_t bytes, size_t* off) {
+    std::lock_guard<std::mutex> lk(mu);
     bytes = align_up(std::max(bytes, (size_t)1), 4096);
     for (auto it = free_.begin(); it != free_.end(); ++it)
       if (it->second >= bytes) {
@@ -42,6 +45,7 @@ struct WinAlloc {
     return false;
   }
   void release(size_t off, size_t bytes) {
+    std::lock_guard<std::mutex> lk(mu);
     bytes = align_up(std::max(bytes, (size_t)1), 4096);
     auto it = free_.emplace(off, bytes).first;
     auto nx = std::next(it);
@@ -97,7 +101,7 @@ struct HostBlock {
 struct asdm_group {
   int world = 1;
   int n_proc = 1;
-  std::vector<GroupMember> m;
+  std::deque<GroupMember> m;  // (a member holds a mutex: never moved)
   asdm_allgather_fn xchg = nullptr;
   void* user = nullptr;
   size_t win_bytes = 0;
@@ -759,6 +763,7 @@ extern "C" int asdm_group_sets_create(asdm_group* g, const asdm_set_desc* descs,
         s->fv_pos = (int32_t*)(win + y.o_fv + (size_t)y.n_pad * 4);
         s->has_fv = true;
       }
+      if (set_mark_ready(ctx, s, ctx->prep_stream)) return bail(gfail(g, ASDM_ERR_CUDA, "cudaEventRecord(set ready)"));
     }
   }
 #undef GCB
@@ -846,7 +851,8 @@ extern "C" int asdm_group_job_prepare(asdm_group* g, const asdm_gjob_desc* gd, a
     std::vector<asdm_set*> sets((size_t)d.n_kf);
     for (int k = 0; k < d.n_kf; k++) {
       sets[(size_t)k] = d.sets[(size_t)k * L + l];
-      if (sets[(size_t)k]->ctx != ctx) return bail(gfail(g, ASDM_ERR_INVALID, "job.sets[k * local_count + l] must live on local member l"));
+      if (sets[(size_t)k]->ctx->device != ctx->device || sets[(size_t)k]->ctx->family != ctx->family)
+        return bail(gfail(g, ASDM_ERR_INVALID, "job.sets[k * local_count + l] must live on the GPU of local member l"));
     }
     std::vector<int32_t> ia, ib, rb, re, rmap;
     std::vector<float> F12, ep;

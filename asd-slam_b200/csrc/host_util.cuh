@@ -40,6 +40,10 @@ void slot_put(asdm_ctx* ctx, int32_t* p);
 
 // ---- sets.cu
 void set_free(asdm_set* s);
+// records s->ready on `stream` (creating the event on first use): call behind everything that writes the set's arrays
+int set_mark_ready(asdm_ctx* ctx, asdm_set* s, cudaStream_t stream);
+// a search of `ctx` is about to read `s`: same family required; a foreign context's stream is ordered behind s->ready
+int use_set(asdm_ctx* ctx, asdm_set* s);
 int ensure_grid(asdm_ctx* ctx, asdm_set* s);
 int resolve_tc_flags(asdm_ctx* ctx, asdm_set* const* sets, int n);
 int set_create_impl(asdm_ctx* ctx, const float* desc, int n, int row_stride_bytes, const asdm_kp* kps,

@@ -46,6 +46,10 @@ struct asdm_ctx {
   size_t block_cache_bytes = 0;
   std::recursive_mutex mu;
   std::string err;
+  // Contexts forked from one another (asdm_fork: one per thread of the SLAM system, each with its own streams, staging
+  // arena and scratch) form a family on one GPU and may search each other's sets; `family` names the root.
+  asdm_ctx* family = nullptr;
+  std::mutex slot_mu;  // the pinned slot slab is handed out / taken back from any thread that releases a set
   int opt_force_exact = 0;
   int opt_cand_cap = 8;
   int opt_list_cap_per_query = 4;  // tensor-core short list slots per query row (grows on overflow)
@@ -90,7 +94,7 @@ struct asdm_ctx {
 // one copy (asdm_set_create_batch); the sets of the batch share it
 struct SideBlock {
   void* p = nullptr;
-  int ref = 0;  // guarded by the context mutex
+  std::atomic<int> ref{0};  // sets may be released from any thread of the family
 };
 
 struct asdm_set {
@@ -122,6 +126,13 @@ struct asdm_set {
   // set's own (allocated by the first projection-gated search).
   struct GroupSlab* slab = nullptr;
   void* grid_mem = nullptr;
+  // Shared use across the contexts of a family: `ready` is recorded behind whatever last wrote the set's arrays (pack
+  // kernel, FeatureVector upload, vocabulary transform); a context other than the owner orders its stream behind it
+  // (use_set). The lazily built parts (grid bucket, tensor map, range flag) are guarded by `mu`.
+  std::mutex mu;
+  cudaEvent_t ready = nullptr;
+  cudaEvent_t grid_ev = nullptr;   // behind k_build_grid, recorded on the stream of the context that built it
+  asdm_ctx* grid_builder = nullptr;
 };
 
 struct asdm_group;
@@ -129,7 +140,7 @@ struct GroupSlab {
   asdm_group* g = nullptr;
   int member = 0;            // local member whose window holds this copy
   size_t off = 0, bytes = 0; // range of the window
-  int ref = 0;               // sets alive (guarded by the context mutex of the member)
+  std::atomic<int> ref{0};   // sets alive (released from any thread)
   int32_t* h_flags = nullptr; // page-locked [n_sets]: tensor-core range flags of the batch, copied back after the exchange
 };
 void group_slab_release(GroupSlab* s);  // group.cu

@@ -94,7 +94,8 @@ int job_prepare(asdm_ctx* ctx, const asdm_job_desc* d, int kind_internal, asdm_j
     return fail(ctx, ASDM_ERR_INVALID, "row ranges need both arrays and a triangulation job without rotation check");
   for (int k = 0; k < d->n_kf; k++) {
     const asdm_set* s = d->sets[k];
-    if (!s || s->ctx != ctx || !d->masks[k]) return fail(ctx, ASDM_ERR_INVALID, "bad keyframe set / mask");
+    if (!s || !d->masks[k]) return fail(ctx, ASDM_ERR_INVALID, "bad keyframe set / mask");
+    if (s->ctx->family != ctx->family) return fail(ctx, ASDM_ERR_INVALID, "keyframe set belongs to a context of another family (asdm_fork)");
     if (s->n >= (1 << 24)) return fail(ctx, ASDM_ERR_INVALID, "keyframe set too large for a batched search (2^24 features)");
     if (!s->has_fv) return fail(ctx, ASDM_ERR_INVALID, "keyframe set has no FeatureVector (asdm_set_featvec)");
     if (!s->has_kps) return fail(ctx, ASDM_ERR_INVALID, "keyframe set has no keypoints");
@@ -113,6 +114,8 @@ int job_prepare(asdm_ctx* ctx, const asdm_job_desc* d, int kind_internal, asdm_j
   for (int k = 0; k < d->n_kf; k++) {
     asdm_set_retain(d->sets[k]);
     j->sets.push_back(d->sets[k]);
+    const int ru = use_set(ctx, d->sets[k]);  // sets created on another context of the family: order behind their writes
+    if (ru) return bail(ru);
   }
   // masks of all keyframes, packed
   std::vector<size_t> mask_off(d->n_kf);

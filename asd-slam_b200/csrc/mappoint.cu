@@ -22,6 +22,11 @@ extern "C" int asdm_distinctive_descriptors(asdm_ctx* ctx, asdm_set* const* sets
   const int n_obs = obs_off[n_points];
   if (obs_off[0] != 0 || n_obs < 0 || (n_obs > 0 && (!obs_set || !obs_row)))
     return fail(ctx, ASDM_ERR_INVALID, "bad observation offsets");
+  for (int k = 0; k < n_sets; k++)
+    if (sets[k]) {
+      const int ru = use_set(ctx, sets[k]);
+      if (ru) return ru;
+    }
   std::vector<int32_t> small, large;
   std::vector<int64_t> d_off;
   int64_t scratch_floats = 0;
@@ -29,7 +34,7 @@ extern "C" int asdm_distinctive_descriptors(asdm_ctx* ctx, asdm_set* const* sets
     const int N = obs_off[p + 1] - obs_off[p];
     if (N < 0) return fail(ctx, ASDM_ERR_INVALID, "observation offsets not ascending");
     for (int e = obs_off[p]; e < obs_off[p + 1]; e++) {
-      if (obs_set[e] < 0 || obs_set[e] >= n_sets || !sets[obs_set[e]] || sets[obs_set[e]]->ctx != ctx)
+      if (obs_set[e] < 0 || obs_set[e] >= n_sets || !sets[obs_set[e]] || sets[obs_set[e]]->ctx->family != ctx->family)
         return fail(ctx, ASDM_ERR_INVALID, "observation names an unknown keyframe set");
       if (obs_row[e] < 0 || obs_row[e] >= sets[obs_set[e]]->n) return fail(ctx, ASDM_ERR_INVALID, "observation row out of range");
     }

@@ -110,6 +110,7 @@ static int search_by_projection_legacy(asdm_ctx* ctx, asdm_set* target, const as
   ctx->stat_retries = 0;
   const int n_t = target->n;
   int rc;
+  if ((rc = use_set(ctx, target)) || (q_set && (rc = use_set(ctx, q_set)))) return rc;
   if ((rc = ensure(ctx, ctx->scratch[SC_QUERY], (size_t)std::max(nq, 1) * sizeof(asdm_proj_query)))) return rc;
   // queries, masks and row maps are caller memory (pageable): staged through the pinned arena so nothing blocks
   if (nq > 0 && (rc = stage_upload(ctx, ctx->scratch[SC_QUERY].p, q, (size_t)nq * sizeof(asdm_proj_query)))) return rc;
@@ -136,7 +137,7 @@ static int search_by_projection_legacy(asdm_ctx* ctx, asdm_set* target, const as
     d_rows = (const int32_t*)ctx->scratch[SC_QDESC].p;
     d_desc_q = (const float*)((const char*)ctx->scratch[SC_QDESC].p + map_bytes);
   } else {
-    if (q_set->ctx != ctx) return fail(ctx, ASDM_ERR_INVALID, "query set belongs to another context");
+    if (q_set->ctx->family != ctx->family) return fail(ctx, ASDM_ERR_INVALID, "query set belongs to a context of another family");
     d_desc_q = q_set->desc;
     if (q_rows) {
       for (int i = 0; i < nq; i++)
@@ -250,6 +251,7 @@ static int search_by_projection_impl(asdm_ctx* ctx, asdm_set* target, const asdm
   ctx->stat_retries = 0;
   const int n_t = target->n;
   int rc;
+  if ((rc = use_set(ctx, target)) || (q_set && (rc = use_set(ctx, q_set)))) return rc;
   ProjFusedArgs A;
   memset(&A, 0, sizeof A);
   if (p->chi2_max > 0.0) {
@@ -259,7 +261,7 @@ static int search_by_projection_impl(asdm_ctx* ctx, asdm_set* target, const asdm
     memcpy(A.G.inv_level_sigma2, p->inv_level_sigma2, (size_t)p->n_levels * sizeof(float));
   }
   if (q_set && !desc_q) {
-    if (q_set->ctx != ctx) return fail(ctx, ASDM_ERR_INVALID, "query set belongs to another context");
+    if (q_set->ctx->family != ctx->family) return fail(ctx, ASDM_ERR_INVALID, "query set belongs to a context of another family");
     if (!q_rows && nq > q_set->n) return fail(ctx, ASDM_ERR_INVALID, "more queries than rows in the query set");
   }
   int nv = 0;
@@ -413,6 +415,7 @@ extern "C" int asdm_search_for_initialization(asdm_ctx* ctx, asdm_set* f1, asdm_
   ctx->stat_retries = 0;
   const int n1 = f1->n, n2 = f2->n;
   int rc;
+  if ((rc = use_set(ctx, f1)) || (rc = use_set(ctx, f2))) return rc;
   if ((rc = ensure(ctx, ctx->scratch[SC_QUERY], (size_t)std::max(n1, 1) * sizeof(asdm_proj_query)))) return rc;
   // state: prev[2*n1] matched_dist[n2] matches21[n2] matches12[n1] dist12[n1] pushed[n1] nm
   const size_t N1 = (size_t)std::max(n1, 1), N2 = (size_t)std::max(n2, 1);
@@ -508,6 +511,7 @@ extern "C" int asdm_stereo_row_match(asdm_ctx* ctx, asdm_set* left, asdm_set* ri
   const int n_l = left->n;
   if (n_l == 0) return ASDM_OK;
   int rc;
+  if ((rc = use_set(ctx, left)) || (rc = use_set(ctx, right))) return rc;
   // one launch and one wait: the level table rides in the kernel parameters, the results are stored by the kernel into
   // the page-locked arena (zero-copy) and handed to the caller's arrays after the wait
   const size_t NL = ((size_t)n_l + 3) & ~(size_t)3;  // best_r | best_dist, each padded to 16 bytes

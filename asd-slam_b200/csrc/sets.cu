@@ -11,10 +11,26 @@
 #include "kernels_set.cuh"
 
 // --------------------------------------------------------------------------------------- descriptor sets
+int set_mark_ready(asdm_ctx* ctx, asdm_set* s, cudaStream_t stream) {
+  if (!s->ready) CK(cudaEventCreateWithFlags(&s->ready, cudaEventDisableTiming));
+  CK(cudaEventRecord(s->ready, stream));
+  return ASDM_OK;
+}
+
+int use_set(asdm_ctx* ctx, asdm_set* s) {
+  if (!s) return fail(ctx, ASDM_ERR_INVALID, "null set");
+  if (s->ctx == ctx) return ASDM_OK;  // the owner's main stream already waits for every write at the time it is queued
+  if (s->ctx->family != ctx->family) return fail(ctx, ASDM_ERR_INVALID, "set belongs to a context of another family (asdm_fork)");
+  if (s->ready) CK(cudaStreamWaitEvent(ctx->stream, s->ready, 0));
+  return ASDM_OK;
+}
+
 void set_free(asdm_set* s) {
   if (!s) return;
   asdm_ctx* ctx = s->ctx;
   cudaSetDevice(ctx->device);
+  if (s->ready) cudaEventDestroy(s->ready);
+  if (s->grid_ev) cudaEventDestroy(s->grid_ev);
   if (s->slab) {  // a view into a group window: the slab goes back when its last set does
     if (--s->slab->ref == 0) group_slab_release(s->slab);
     s->h_flag = nullptr;  // lives in the slab's page-locked block
@@ -34,7 +50,12 @@ void set_free(asdm_set* s) {
 // Frame::AssignFeaturesToGrid (Frame.cc:123-138) on the device, on first use: only the projection-gated searches read
 // the bucket, so keyframes that only ever meet BoW-gated searches (loop-closure sweeps) never pay for it.
 int ensure_grid(asdm_ctx* ctx, asdm_set* s) {
-  if (!s->has_grid || s->grid_built) return ASDM_OK;
+  if (!s->has_grid) return ASDM_OK;
+  std::lock_guard<std::mutex> lks(s->mu);
+  if (s->grid_built) {  // built on another context's stream: order behind it
+    if (s->grid_builder != ctx && s->grid_ev) CK(cudaStreamWaitEvent(ctx->stream, s->grid_ev, 0));
+    return ASDM_OK;
+  }
   const int nc = s->grid.cols * s->grid.rows;
   if (!s->cell_start) {  // view sets carry no bucket arrays of their own until a projection-gated search asks
     const size_t o_ci = align_up((size_t)(nc + 1) * sizeof(int32_t), 256), o_tmp = o_ci + align_up((size_t)s->n_pad * sizeof(int32_t), 256),
@@ -51,6 +72,9 @@ int ensure_grid(asdm_ctx* ctx, asdm_set* s) {
   k_build_grid<<<1, 1024, smem, ctx->stream>>>(s->kps, s->n, s->grid, s->cell_tmp, s->cell_start, s->cell_items, s->cell_kp);
   LAUNCHED(ctx);
   CK(cudaGetLastError());
+  if (!s->grid_ev) CK(cudaEventCreateWithFlags(&s->grid_ev, cudaEventDisableTiming));
+  CK(cudaEventRecord(s->grid_ev, ctx->stream));
+  s->grid_builder = ctx;
   s->grid_built = true;
   return ASDM_OK;
 }
@@ -64,9 +88,10 @@ int resolve_tc_flags(asdm_ctx* ctx, asdm_set* const* sets, int n) {
   synced(ctx);
   for (int k = 0; k < n; k++) {
     asdm_set* s = sets[k];
+    std::lock_guard<std::mutex> lks(s->mu);
     if (s->tc_ok >= 0) continue;
     s->tc_ok = (s->h_flag && *s->h_flag == 0) ? 1 : 0;
-    if (!s->slab) slot_put(ctx, s->h_flag);  // a view's flag lives in its slab's page-locked block
+    if (!s->slab) slot_put(s->ctx, s->h_flag);  // the owner's slab; a view's flag lives in its slab's page-locked block
     s->h_flag = nullptr;
   }
   return ASDM_OK;
@@ -168,6 +193,7 @@ int set_create_impl(asdm_ctx* ctx, const float* desc, int n, int row_stride_byte
   if (s->h_flag) CKS(cudaMemcpyAsync(s->h_flag, s->d_flags, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->prep_stream));
   CKS(cudaEventRecord(ctx->prep_done, ctx->prep_stream));
   CKS(cudaStreamWaitEvent(ctx->stream, ctx->prep_done, 0));  // whatever is queued on the main stream from here on sees the set
+  if (set_mark_ready(ctx, s, ctx->prep_stream)) return bail(ASDM_ERR_CUDA);  // ... and so does any other context of the family
   if (grid) {  // the grid bucket itself is built by the first projection-gated search (ensure_grid)
     s->grid = *grid;
     s->has_grid = true;
@@ -343,6 +369,8 @@ extern "C" int asdm_set_create_batch(asdm_ctx* ctx, const asdm_set_desc* descs, 
   LAUNCHED(ctx);
   CKB(cudaEventRecord(ctx->prep_done, ctx->prep_stream));
   CKB(cudaStreamWaitEvent(ctx->stream, ctx->prep_done, 0));
+  for (int k = 0; k < n_sets; k++)
+    if (set_mark_ready(ctx, out[k], ctx->prep_stream)) return bail(ASDM_ERR_CUDA);
   CKB(cudaGetLastError());
   bool need_sync = false;
   for (int k = 0; k < n_sets; k++) need_sync |= !out[k]->h_flag;
@@ -368,11 +396,9 @@ extern "C" int asdm_set_retain(asdm_set* s) {
 
 extern "C" int asdm_set_release(asdm_set* s) {
   if (!s) return ASDM_ERR_INVALID;
-  if (s->ref.fetch_sub(1) == 1) {
-    asdm_ctx* ctx = s->ctx;
-    std::lock_guard<std::recursive_mutex> lk(ctx->mu);
-    set_free(s);  // stream-ordered free: searches already queued on this set finish first
-  }
+  if (s->ref.fetch_sub(1) == 1)
+    set_free(s);  // stream-ordered free on the owner's stream (searches it queued on the set finish first); takes no context
+                  // lock: a thread of the family may drop the last reference while the owner waits inside a search
   return ASDM_OK;
 }
 
@@ -418,6 +444,11 @@ extern "C" int asdm_set_featvec(asdm_set* s, const asdm_featvec* fv) {
   CK(cudaMemcpyAsync(s->node_id, h, (size_t)s->n_pad * 8, cudaMemcpyHostToDevice, ctx->upload_stream));
   CK(cudaEventRecord(ctx->upload_done, ctx->upload_stream));
   CK(cudaStreamWaitEvent(ctx->stream, ctx->upload_done, 0));
+  {  // the other contexts of the family wait for the pack (already behind `ready`) AND this upload
+    if (s->ready) CK(cudaStreamWaitEvent(ctx->upload_stream, s->ready, 0));
+    const int rr = set_mark_ready(ctx, s, ctx->upload_stream);
+    if (rr) return rr;
+  }
   s->has_fv = true;
   return ASDM_OK;
 }
@@ -446,7 +477,7 @@ extern "C" int asdm_set_save_blocks(asdm_ctx* ctx, asdm_set* const* sets, int n_
   CK(cudaSetDevice(ctx->device));
   size_t off = 0;
   for (int k = 0; k < n_sets; k++) {
-    if (!sets[k] || sets[k]->ctx != ctx) return fail(ctx, ASDM_ERR_INVALID, "set of another context");
+    if (!sets[k] || use_set(ctx, sets[k])) return fail(ctx, ASDM_ERR_INVALID, "set of another context family");
     off += asdm_desc_block_bytes(sets[k]->n);
   }
   if (off > cap) return fail(ctx, ASDM_ERR_INVALID, "output buffer too small for the descriptor blocks");

@@ -366,6 +366,7 @@ typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_
                                     CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
 int asdm_tc_build_tmap(asdm_ctx* ctx, asdm_set* set) {
+  std::lock_guard<std::mutex> lks(set->mu);  // a set may be prepared for jobs of several contexts at once
   if (!set->tmap_bf.empty()) return ASDM_OK;
   if (!ctx->tmap_encode) {
     void* fn = nullptr;

@@ -138,6 +138,10 @@ extern "C" int asdm_vocab_transform(asdm_ctx* ctx, asdm_vocab* voc, asdm_set* s,
   k_fv_rank<<<dim3((n + 127) / 128, (n + FV_JT - 1) / FV_JT), 128, 0, ctx->stream>>>(d_key, n, s->fv_pos);
   LAUNCHED(ctx);
   CK(cudaGetLastError());
+  {  // the FeatureVector arrays were rewritten on this stream: what the other contexts of the family wait for
+    const int rr = set_mark_ready(ctx, s, ctx->stream);
+    if (rr) return rr;
+  }
   const bool want_host = word_id || node_id || in_fv || bow_n || bow_id || bow_val;
   if (!want_host) return ASDM_OK;  // stays asynchronous: the searches that follow are ordered on the same stream
   void* h = nullptr;

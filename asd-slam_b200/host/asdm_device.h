@@ -21,6 +21,7 @@ namespace asdm {
 struct DeviceSet {
   asdm_set* set = nullptr;
   bool has_fv = false;
+  uint64_t fv_sig = 0;  // signature of the FeatureVector that is attached on the device (AttachFeatureVector)
   ~DeviceSet() {
     if (set) asdm_set_release(set);
   }
@@ -33,14 +34,25 @@ struct DeviceSet {
   std::abort();
 }
 
-// One context per process (the fork runs tracking, mapping and loop closing on one thread; the library serialises
-// calls on a context anyway).  ASDM_DEVICE selects the GPU.
-inline asdm_ctx* Context() {
-  static asdm_ctx* ctx = [] {
+// One root context per process and one forked context per THREAD that calls the matcher (asdm_fork): upstream ORB-SLAM2
+// runs tracking, local mapping and loop closing concurrently, and a context serialises its calls -- blocking waits
+// included -- on its own lock. Forked contexts share the descriptor sets, so a Frame uploaded by the tracking thread is
+// searched by the mapping thread without another upload. ASDM_DEVICE selects the GPU.
+inline asdm_ctx* RootContext() {
+  static asdm_ctx* root = [] {
     const char* e = std::getenv("ASDM_DEVICE");
     asdm_ctx* c = nullptr;
     const int rc = asdm_create(e ? std::atoi(e) : 0, &c);
     if (rc != ASDM_OK) Die("asdm_create (a B200 is required; there is no CPU fallback)", rc, nullptr);
+    return c;
+  }();
+  return root;
+}
+inline asdm_ctx* Context() {
+  thread_local asdm_ctx* ctx = [] {
+    asdm_ctx* c = nullptr;
+    const int rc = asdm_fork(RootContext(), &c);
+    if (rc != ASDM_OK) Die("asdm_fork", rc, RootContext());
     return c;
   }();
   return ctx;
@@ -75,17 +87,28 @@ inline std::shared_ptr<DeviceSet> Upload(const MAT& desc, const std::vector<KP>&
   return d;
 }
 
-// DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned>>) -> CSR, attached once per set
+// DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned>>) -> CSR, attached to the set on the device. The copy is
+// keyed on a signature of the vector's content: mFeatVec may still be empty at the first search and is recomputed by
+// ComputeBoW later (Frame.cc:289-296, KeyFrame.cc:203-219) -- a device copy that is attached "once" would go stale
+// silently. Flattening costs one pass over the features (microseconds); the upload only happens when the content changed.
+// Invariant for the integration: whoever REPLACES mDescriptors or mvKeysUn resets mDev.
 template <class FV>
 inline void AttachFeatureVector(DeviceSet& d, const FV& fv) {
-  if (d.has_fv) return;
   std::vector<uint32_t> ids;
   std::vector<int32_t> off(1, 0), idx;
+  uint64_t sig = 1469598103934665603ull;  // FNV-1a over (node, indices...)
+  auto mix = [&sig](uint64_t v) { sig = (sig ^ v) * 1099511628211ull; };
   for (typename FV::const_iterator it = fv.begin(); it != fv.end(); ++it) {
     ids.push_back((uint32_t)it->first);
-    for (size_t k = 0; k < it->second.size(); k++) idx.push_back((int32_t)it->second[k]);
+    mix(0x9e3779b97f4a7c15ull + (uint64_t)it->first);
+    for (size_t k = 0; k < it->second.size(); k++) {
+      idx.push_back((int32_t)it->second[k]);
+      mix((uint64_t)it->second[k]);
+    }
     off.push_back((int32_t)idx.size());
   }
+  if (d.has_fv && d.fv_sig == sig) return;
+  d.fv_sig = sig;
   asdm_featvec c;
   c.n_nodes = (int32_t)ids.size();
   c.node_ids = ids.data();

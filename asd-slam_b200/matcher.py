@@ -43,6 +43,15 @@ class Context:
         self.h = h
         self.device = int(device)
 
+    def fork(self):
+        """asdm_fork: a context for another thread on the same GPU that may search this context's sets."""
+        c = Context.__new__(Context)
+        c.lib, c.device = self.lib, self.device
+        h = C.c_void_p()
+        self.check(self.lib.asdm_fork(self.h, C.byref(h)))
+        c.h = h
+        return c
+
     def check(self, rc):
         if rc != 0:
             raise AsdmError(f"libasdmatch_cuda error {rc}: {self.lib.asdm_last_error(self.h).decode()}")

@@ -15,8 +15,8 @@
  *    asdm_last_error() gives the message of the last failure on that context;
  *  - host buffers are caller-owned; device buffers are library-owned (asdm_set, asdm_job) and come from the
  *    device's stream-ordered memory pool, so creating / releasing sets and jobs never synchronises the device;
- *  - a context owns one CUDA stream; calls on one context are serialised by an internal mutex, so
- *    the three ORB-SLAM2 threads may share it; use one context per GPU;
+ *  - a context owns its CUDA streams; calls on one context are serialised by an internal mutex. Threads that must not
+ *    wait for each other take a context each (asdm_fork) and share the descriptor sets;
  *  - there is NO CPU fallback: without a CUDA device asdm_create fails with ASDM_ERR_CUDA.
  *
  * Result contract: index lists are bit-identical to the reference's CPU matcher on the same inputs;
@@ -76,6 +76,13 @@ typedef struct {
 
 /* ---------------------------------------------------------------------------------------- context */
 int asdm_create(int device, asdm_ctx** out);
+/* A second context on the same GPU for another thread of the SLAM system (upstream ORB-SLAM2 runs tracking, local mapping
+ * and loop closing concurrently): its own streams, staging arena, scratch and lock -- a thread never waits for another
+ * thread's search -- and the right to search the sets the other contexts of the family created (a Frame's descriptors are
+ * uploaded once, by the thread that builds it). The library orders the streams (an event per set behind whatever last
+ * wrote it); the caller keeps a set alive while a call on it is in progress, as with any shared object, and destroys the
+ * forked contexts before the parent. */
+int asdm_fork(asdm_ctx* parent, asdm_ctx** out);
 int asdm_destroy(asdm_ctx* ctx);
 const char* asdm_last_error(const asdm_ctx* ctx);
 void* asdm_stream(asdm_ctx* ctx); /* the context's cudaStream_t, for event timing by the caller */
