@@ -262,6 +262,7 @@ extern "C" int asdm_destroy(asdm_ctx* ctx) {
   for (cudaEvent_t e : ctx->ev) cudaEventDestroy(e);
   if (ctx->stage) cudaFreeHost(ctx->stage);
   if (ctx->slot_slab) cudaFreeHost(ctx->slot_slab);
+  if (ctx->res_host) cudaFreeHost(ctx->res_host);
   if (ctx->proj_ctl) cudaFree(ctx->proj_ctl);
   for (cudaEvent_t e : ctx->stage_ev)
     if (e) cudaEventDestroy(e);

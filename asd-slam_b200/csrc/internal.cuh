@@ -75,6 +75,8 @@ struct asdm_ctx {
   // consumed in stream order; the arena rewinds whenever the library synchronises the stream.
   char* stage = nullptr;
   size_t stage_cap = 0, stage_off = 0;
+  char* res_host = nullptr;  // page-locked result block of the single-pair searches (their kernels store the rows here)
+  size_t res_cap = 0;
   // Pinned 64-byte slots with object lifetime (per-job overflow flags, per-set tensor-core range flag)
   char* slot_slab = nullptr;
   std::vector<int> slot_free;

@@ -654,19 +654,44 @@ static int single_pair(asdm_ctx* ctx, int kind, asdm_set* a, const uint8_t* mask
   asdm_job* j = nullptr;
   int rc = job_prepare(ctx, &d, kind, &j);
   if (rc) return rc;
-  rc = job_run(j);
+  // The resolve kernel stores the finished row straight into the page-locked arena (its publish epilogue, one
+  // destination): no copy nodes behind the kernels, one wait per call.
+  const size_t n = (size_t)j->out_stride, row_bytes = align_up(n * 4, 64);
+  void* hres = nullptr;
+  if (!rc && 2 * row_bytes + 64 > ctx->res_cap) {  // (not the staging arena: a rerun inside job_settle may stage again)
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->res_host) cudaFreeHost(ctx->res_host);
+    ctx->res_host = nullptr;
+    ctx->res_cap = 0;
+    const size_t want = std::max(2 * (2 * row_bytes + 64), (size_t)256 << 10);
+    if (cudaHostAlloc((void**)&ctx->res_host, want, cudaHostAllocMapped) != cudaSuccess) {
+      cudaGetLastError();
+      rc = fail(ctx, ASDM_ERR_OOM, "page-locked result block");
+    } else {
+      ctx->res_cap = want;
+    }
+  }
+  hres = ctx->res_host;
+  if (!rc) {
+    char* hb = (char*)hres;
+    j->pub = PublishArgs();
+    j->pub.n = 1;
+    j->pub.stride = (int)n;
+    j->pub.match[0] = (int32_t*)hb;
+    j->pub.dist[0] = (float*)(hb + row_bytes);
+    j->pub.nm[0] = (int32_t*)(hb + 2 * row_bytes);
+    j->pub.no_dist = dist ? 0 : 1;
+    memset(hb, 0xff, row_bytes);  // an empty search launches nothing: -1 rows, zero matches
+    memset(hb + row_bytes, 0, row_bytes + 64);
+    rc = job_run(j);
+  }
   if (!rc) rc = job_settle(j);
   const int64_t launches = ctx->stat_launches;
   if (!rc) {
-    int32_t nm = 0;
-    const size_t n = (size_t)j->out_stride;
-    cudaError_t e = cudaMemcpyAsync(match, j->d_match.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream);
-    if (e == cudaSuccess && dist)
-      e = cudaMemcpyAsync(dist, j->d_dist.p, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(&nm, j->d_nm.p, sizeof nm, cudaMemcpyDeviceToHost, ctx->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    if (e != cudaSuccess) rc = fail(ctx, ASDM_ERR_CUDA, "result download", e);
-    if (nmatches) *nmatches = nm;
+    const char* hb = (const char*)hres;
+    memcpy(match, hb, n * sizeof(int32_t));
+    if (dist) memcpy(dist, hb + row_bytes, n * sizeof(float));
+    if (nmatches) *nmatches = *(const int32_t*)(hb + 2 * row_bytes);
   }
   job_free(j);
   ctx->stat_launches = launches;

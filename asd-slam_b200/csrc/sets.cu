@@ -85,7 +85,7 @@ int resolve_tc_flags(asdm_ctx* ctx, asdm_set* const* sets, int n) {
   for (int k = 0; k < n; k++) pending |= sets[k]->tc_ok < 0;
   if (!pending) return ASDM_OK;
   CK(cudaStreamSynchronize(ctx->stream));
-  synced(ctx);
+  // (no synced(ctx): job_prepare calls this with its input block staged and not pulled yet -- the arena must not rewind)
   for (int k = 0; k < n; k++) {
     asdm_set* s = sets[k];
     std::lock_guard<std::mutex> lks(s->mu);

@@ -550,3 +550,25 @@ def test_batch_created_sets_in_projection_search(pkg, ctx, oracle):
             assert nm == onm
     for F in sets:
         F.release()
+
+
+def test_single_pair_inputs_survive_flag_resolution(pkg, ctx, oracle):
+    """A single-pair search whose sets still have their range flags in flight resolves them INSIDE job_prepare, with
+    the job's input block already staged in the page-locked arena at offset 0 (the previous call rewound it). Nothing
+    staged or written by the host afterwards may land on that block before the device has pulled it (seen once: the
+    result block of the call overlapped the masks and the tensor maps)."""
+    c = pkg.synth.config1(4000, 4000, n_nodes=6)
+    valid = np.ones(4000, np.uint8)
+    mt = pkg.ORBmatcher(ctx, 0.8, True)
+    onm, omatch, odist = oracle.search_by_bow_kf_f(c["desc_a"], c["kps_a"], c["fv_a"], valid, c["desc_b"], c["kps_b"],
+                                                   c["fv_b"], 0.8, 1)
+    old = pkg.DescriptorSet(ctx, c["desc_a"][:64])
+    for _ in range(6):
+        A, B = _sets_pair(pkg, ctx, c)           # flags in flight
+        old.read_desc(0, 8)                      # waits for the stream and rewinds the arena
+        nm, match, dist = mt.SearchByBoW_KF_F(A, valid, B)
+        _eq(match, omatch, "match after flag resolution")
+        _eq_dist(dist, odist, "dist after flag resolution")
+        assert nm == onm
+        A.release(); B.release()
+    old.release()
