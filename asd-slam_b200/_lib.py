@@ -38,7 +38,7 @@ EXPORTS = [
     "asdm_shared_alloc", "asdm_shared_open", "asdm_shared_close", "asdm_shared_free", "asdm_job_set_publish",
     "asdm_group_create", "asdm_group_join", "asdm_group_destroy", "asdm_group_last_error", "asdm_group_world",
     "asdm_group_local_count", "asdm_group_local_rank", "asdm_group_ctx", "asdm_group_host_alloc", "asdm_group_host_free",
-    "asdm_group_host_barrier", "asdm_group_sets_create", "asdm_group_job_prepare", "asdm_group_job_units",
+    "asdm_group_host_barrier", "asdm_group_sets_create", "asdm_group_job_prepare", "asdm_group_plan_units", "asdm_group_job_units",
     "asdm_group_job_stride", "asdm_group_job_run", "asdm_group_job_wait", "asdm_group_job_counts", "asdm_group_job_fetch",
     "asdm_group_job_gathered", "asdm_group_job_flush", "asdm_group_job_destroy",
     "asdm_distinctive_descriptors",
@@ -173,6 +173,7 @@ def load():
     lib.asdm_group_host_barrier.argtypes = [vp]
     lib.asdm_group_sets_create.argtypes = [vp, C.POINTER(SetDesc), C.c_int, C.POINTER(vp)]
     lib.asdm_group_job_prepare.argtypes = [vp, C.POINTER(GJobDesc), C.POINTER(vp)]
+    lib.asdm_group_plan_units.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, C.c_int, C.POINTER(C.c_int)]
     lib.asdm_group_job_units.argtypes = [vp]
     lib.asdm_group_job_stride.argtypes = [vp]
     lib.asdm_group_job_run.argtypes = [vp, vp, vp, vp]

@@ -795,6 +795,28 @@ struct asdm_gjob {
   bool ran = false;
 };
 
+// The unit plan of a group job: pure host arithmetic, the same on every rank (no device, no communication).
+extern "C" int asdm_group_plan_units(const int32_t* query_rows, int n_pairs, int blocks_per_pair, int world, int32_t* unit_pair,
+                                     int32_t* unit_row0, int32_t* unit_row1, int32_t* unit_rank, int cap, int* n_units) {
+  if (n_pairs < 0 || (n_pairs > 0 && !query_rows) || blocks_per_pair < 1 || world < 1 || !n_units) return ASDM_ERR_INVALID;
+  int nu = 0;
+  for (int p = 0; p < n_pairs; p++) {
+    const int n = query_rows[p];
+    if (n < 0) return ASDM_ERR_INVALID;
+    // <= blocks_per_pair blocks on 128-row boundaries: no tile of the tensor-core kernel is computed twice
+    const int tiles = (n + 127) / 128, nb = std::max(1, std::min(blocks_per_pair, tiles));
+    for (int b = 0; b < nb; b++, nu++) {
+      if (nu >= cap) return ASDM_ERR_INVALID;
+      if (unit_pair) unit_pair[nu] = p;
+      if (unit_row0) unit_row0[nu] = std::min(n, (int)((long)tiles * b / nb) * 128);
+      if (unit_row1) unit_row1[nu] = b + 1 == nb ? n : std::min(n, (int)((long)tiles * (b + 1) / nb) * 128);
+      if (unit_rank) unit_rank[nu] = nu % world;  // round-robin deal: unit u runs on rank u % world
+    }
+  }
+  *n_units = nu;
+  return ASDM_OK;
+}
+
 extern "C" int asdm_group_job_prepare(asdm_group* g, const asdm_gjob_desc* gd, asdm_gjob** out) {
   if (!g || !gd || !out) return ASDM_ERR_INVALID;
   *out = nullptr;
@@ -822,21 +844,26 @@ extern "C" int asdm_group_job_prepare(asdm_group* g, const asdm_gjob_desc* gd, a
     asdm_group_job_destroy(j);
     return code;
   };
-  // units: pair p as a whole, or its query rows cut into <= bpp blocks on 128-row boundaries (no tensor-core tile twice)
-  std::vector<int32_t> u_r0, u_r1;
+  // units: pair p as a whole, or its query rows cut into <= bpp blocks on 128-row boundaries (asdm_group_plan_units)
+  std::vector<int32_t> u_r0, u_r1, rows_of((size_t)std::max(d.n_pairs, 1));
   int stride = 1;
   for (int p = 0; p < d.n_pairs; p++) {
     if (d.ia[p] < 0 || d.ia[p] >= d.n_kf || d.ib[p] < 0 || d.ib[p] >= d.n_kf) return bail(gfail(g, ASDM_ERR_INVALID, "pair index out of range"));
-    const int n = d.sets[(size_t)d.ia[p] * L]->n;
-    stride = std::max(stride, n);
-    const int tiles = (n + 127) / 128, nb = std::max(1, std::min(bpp, tiles));
-    for (int b = 0; b < nb; b++) {
-      j->unit_pair.push_back(p);
-      u_r0.push_back(std::min(n, (int)((long)tiles * b / nb) * 128));
-      u_r1.push_back(b + 1 == nb ? n : std::min(n, (int)((long)tiles * (b + 1) / nb) * 128));
-    }
+    rows_of[(size_t)p] = d.sets[(size_t)d.ia[p] * L]->n;
+    stride = std::max(stride, rows_of[(size_t)p]);
   }
-  j->n_units = (int)j->unit_pair.size();
+  {
+    const size_t cap = (size_t)std::max(d.n_pairs, 1) * bpp;
+    j->unit_pair.resize(cap);
+    u_r0.resize(cap);
+    u_r1.resize(cap);
+    int nu = 0;
+    const int rc = asdm_group_plan_units(rows_of.data(), d.n_pairs, bpp, W, j->unit_pair.data(), u_r0.data(), u_r1.data(), nullptr,
+                                         (int)cap, &nu);
+    if (rc) return bail(gfail(g, rc, "unit plan"));
+    j->unit_pair.resize((size_t)nu);
+    j->n_units = nu;
+  }
   j->stride = stride;
   if (j->gather & ASDM_GATHER_DEVICE) {
     const size_t rows = (size_t)std::max(d.n_pairs, 1);

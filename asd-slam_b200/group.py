@@ -37,6 +37,21 @@ def torch_allgather(group=None):
     return fn
 
 
+def plan_units(query_rows, blocks_per_pair, world):
+    """asdm_group_plan_units: the unit table of a group job -- (unit_pair, row0, row1, rank) arrays, host arithmetic only
+    (works without a GPU; every rank computes the same table)."""
+    lib = _lib.load()
+    rows = np.ascontiguousarray(query_rows, np.int32)
+    cap = max(1, len(rows)) * max(1, int(blocks_per_pair))
+    up, r0, r1, rk = (np.empty(cap, np.int32) for _ in range(4))
+    n = C.c_int(0)
+    rc = lib.asdm_group_plan_units(_lib.ptr(rows), len(rows), int(blocks_per_pair), int(world), _lib.ptr(up), _lib.ptr(r0),
+                                   _lib.ptr(r1), _lib.ptr(rk), cap, C.byref(n))
+    if rc:
+        raise _lib.AsdmError(f"asdm_group_plan_units: error {rc}")
+    return up[:n.value].copy(), r0[:n.value].copy(), r1[:n.value].copy(), rk[:n.value].copy()
+
+
 class Group:
     def __init__(self, lib, h, cb=None):
         self.lib, self.h, self._cb = lib, h, cb

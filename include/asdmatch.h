@@ -366,6 +366,13 @@ typedef struct {
   int32_t gather;          /* 0, ASDM_GATHER_DEVICE, or ASDM_GATHER_DEVICE | ASDM_GATHER_NO_DIST */
 } asdm_gjob_desc;
 int asdm_group_job_prepare(asdm_group* g, const asdm_gjob_desc* desc, asdm_gjob** out);
+/* The unit plan asdm_group_job_prepare derives, as plain host arithmetic (no device, no communication; every rank computes
+ * the same table): pair p with query_rows[p] rows becomes min(blocks_per_pair, ceil(rows / 128)) units whose row ranges
+ * [unit_row0, unit_row1) start on 128-row boundaries and tile [0, rows); unit u is searched by rank u % world. Output
+ * arrays of `cap` entries (each may be NULL); *n_units = units planned. Replaces the per-pair loop bodies the reference
+ * runs serially (LocalMapping.cc:335-370, LoopClosing.cc:291-318) as the scheduling step of the sharded form. */
+int asdm_group_plan_units(const int32_t* query_rows, int n_pairs, int blocks_per_pair, int world, int32_t* unit_pair,
+                          int32_t* unit_row0, int32_t* unit_row1, int32_t* unit_rank, int cap, int* n_units);
 int asdm_group_job_units(const asdm_gjob* j);  /* n_pairs, or more when pairs are split */
 int asdm_group_job_stride(const asdm_gjob* j); /* entries per result row */
 /* Launches the units of every local member; returns without waiting. h_match / h_dist: [n_pairs][stride] in the caller's
