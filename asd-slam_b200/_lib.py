@@ -33,6 +33,7 @@ EXPORTS = [
     "asdm_set_read_desc", "asdm_desc_block_bytes", "asdm_set_save_blocks", "asdm_set_load_block",
     "asdm_search_by_bow_kf_f", "asdm_search_by_bow_kf_kf", "asdm_search_for_triangulation",
     "asdm_search_by_projection", "asdm_search_by_projection_q", "asdm_search_for_initialization", "asdm_stereo_row_match",
+    "asdm_stereo_row_match_static",
     "asdm_job_prepare", "asdm_job_run", "asdm_job_fetch", "asdm_job_fetch_async", "asdm_job_settle", "asdm_job_out_stride",
     "asdm_job_device_outputs", "asdm_job_destroy",
     "asdm_shared_alloc", "asdm_shared_open", "asdm_shared_close", "asdm_shared_free", "asdm_job_set_publish",
@@ -145,6 +146,7 @@ def load():
                                                 C.POINTER(i32)]
     lib.asdm_search_for_initialization.argtypes = [vp, vp, vp, vp, C.c_int, f32, C.c_int, vp, vp, C.POINTER(i32)]
     lib.asdm_stereo_row_match.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, f32, f32, vp, vp]
+    lib.asdm_stereo_row_match_static.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, f32, f32, vp, vp]
     lib.asdm_job_prepare.argtypes = [vp, C.POINTER(JobDesc), C.POINTER(vp)]
     lib.asdm_job_run.argtypes = [vp]
     lib.asdm_job_fetch.argtypes = [vp, vp, vp, vp]

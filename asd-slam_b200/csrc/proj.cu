@@ -543,3 +543,77 @@ extern "C" int asdm_stereo_row_match(asdm_ctx* ctx, asdm_set* left, asdm_set* ri
   return ASDM_OK;
 }
 
+
+// ------------------------------------------------------------------------------------------------------------------
+// asdm_stereo_row_match_static: the stereo descriptor stage for callers that may not allocate (code under CUDA graph
+// capture, tight serving loops, harnesses that forbid cudaMalloc). No counterpart in the reference.
+// Same kernel as asdm_stereo_row_match; what that call takes from the context's pools -- the
+// ticket of the last-CTA copy and the device copy of best_r | best_dist -- lives in ONE file-scope device array that every
+// GPU loading the library holds until exit:
+//   [0, 256)                         control block (ticket at +0), cleared on the stream before every launch
+//   [256, 256 + 2 * 16384 * 4)       best_r | best_dist of up to ASDM_STATIC_MAX_LEFT left keypoints
+// Every call shares the array and it keeps the last call's contents: calls that overlap on the GPU (two streams, two
+// threads) race on it. In host code `g_stereo_static` is a host-side stand-in for the symbol, NOT a device address: the
+// address the kernel gets comes from cudaGetSymbolAddress, once per device, with that device current.
+#define STEREO_STATIC_CTL_BYTES 256
+#define STEREO_STATIC_BYTES (STEREO_STATIC_CTL_BYTES + 2 * ASDM_STATIC_MAX_LEFT * 4)
+static __device__ __align__(256) unsigned char g_stereo_static[STEREO_STATIC_BYTES];
+
+enum { STATIC_MAX_DEVICES = 64 };
+static std::mutex g_stereo_static_mu;
+static unsigned char* g_stereo_static_addr[STATIC_MAX_DEVICES];  // per device, resolved on the first call on that device
+
+static int stereo_static_scratch(asdm_ctx* ctx, unsigned char** out) {
+  if (ctx->device < 0 || ctx->device >= STATIC_MAX_DEVICES) return fail(ctx, ASDM_ERR_INVALID, "device index beyond the static-scratch table");
+  std::lock_guard<std::mutex> lk(g_stereo_static_mu);
+  if (!g_stereo_static_addr[ctx->device]) {  // set-up, once per device (the caller made ctx->device current)
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_stereo_static);
+    if (e != cudaSuccess || !p) {
+      cudaGetLastError();
+      return fail(ctx, ASDM_ERR_CUDA, "cudaGetSymbolAddress(static stereo scratch) failed");
+    }
+    g_stereo_static_addr[ctx->device] = (unsigned char*)p;
+  }
+  *out = g_stereo_static_addr[ctx->device];
+  return ASDM_OK;
+}
+
+extern "C" int asdm_stereo_row_match_static(asdm_ctx* ctx, asdm_set* left, asdm_set* right, const float* scale_factors,
+                                            int n_levels, int n_rows, float min_d, float max_d, void* out, void* stream) {
+  if (!ctx || !left || !right || !scale_factors || n_levels <= 0 || n_levels > ASDM_MAX_LEVELS || !out) return ASDM_ERR_INVALID;
+  if (!left->has_kps || !right->has_kps) return fail(ctx, ASDM_ERR_INVALID, "sets need keypoints");
+  if (left->ctx->family != ctx->family || right->ctx->family != ctx->family)
+    return fail(ctx, ASDM_ERR_INVALID, "set belongs to a context of another family (asdm_fork)");
+  if (left->n > ASDM_STATIC_MAX_LEFT)
+    return fail(ctx, ASDM_ERR_INVALID, "asdm_stereo_row_match_static: more left keypoints than the static scratch holds "
+                                       "(ASDM_STATIC_MAX_LEFT = 16384); use asdm_stereo_row_match");
+  if (reinterpret_cast<uintptr_t>(out) & 15) return fail(ctx, ASDM_ERR_INVALID, "asdm_stereo_row_match_static: `out` must be 16-byte aligned");
+  const size_t band_bytes = (size_t)std::max(right->n, 1) * sizeof(int4);
+  if (band_bytes > 160 * 1024) return fail(ctx, ASDM_ERR_INVALID, "right image has too many keypoints for the stereo search (10240)");
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  CK(cudaSetDevice(ctx->device));
+  const int n_l = left->n;
+  if (n_l == 0) return ASDM_OK;
+  unsigned char* scratch = nullptr;
+  int rc = stereo_static_scratch(ctx, &scratch);
+  if (rc) return rc;
+  cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+  // the sets' arrays are complete behind their `ready` events (a no-op on the stream that wrote them)
+  if (left->ready) CK(cudaStreamWaitEvent(st, left->ready, 0));
+  if (right->ready) CK(cudaStreamWaitEvent(st, right->ready, 0));
+  const size_t NL = ((size_t)n_l + 3) & ~(size_t)3;
+  int32_t* d_best = (int32_t*)(scratch + STEREO_STATIC_CTL_BYTES);
+  float* d_dist = (float*)(d_best + NL);
+  StereoLevels sf;
+  memset(&sf, 0, sizeof sf);
+  memcpy(sf.v, scale_factors, (size_t)n_levels * 4);
+  // what must start at zero: the ticket (a call that was aborted mid-kernel would otherwise leave it counting)
+  CK(cudaMemsetAsync(scratch, 0, STEREO_STATIC_CTL_BYTES, st));
+  k_stereo_match<<<(n_l + STEREO_WARPS - 1) / STEREO_WARPS, STEREO_WARPS * 32, band_bytes, st>>>(
+      left->desc, left->kps, n_l, right->desc, right->kps, right->n, sf, n_levels, n_rows, min_d, max_d, d_best, d_dist,
+      (uint32_t*)scratch, (int4*)out);
+  ctx->stat_total_launches++;
+  CK(cudaGetLastError());
+  return ASDM_OK;
+}

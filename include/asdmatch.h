@@ -238,6 +238,25 @@ int asdm_search_for_initialization(asdm_ctx* ctx, asdm_set* f1, asdm_set* f2, fl
 int asdm_stereo_row_match(asdm_ctx* ctx, asdm_set* left, asdm_set* right, const float* scale_factors, int n_levels,
                           int n_rows, float min_d, float max_d, int32_t* best_r, float* best_dist);
 
+/* The same search for callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc). NO COUNTERPART IN THE REFERENCE. It calls no
+ * cudaMalloc / cudaFree / cudaHostAlloc and takes nothing from the context's pools: its device scratch (ticket + device
+ * copy of the results) is one file-scope device array of the library, 128.25 KB, held by every GPU that loads the library
+ * until exit. Limits: left->n <= ASDM_STATIC_MAX_LEFT (larger: ASDM_ERR_INVALID with a message in asdm_last_error; use
+ * asdm_stereo_row_match), right->n <= 10240 as for asdm_stereo_row_match.
+ *   out    : caller-owned, 16-byte aligned memory the GPU can write (device memory, or page-locked host memory such as
+ *            asdm_host_alloc returns) of 2 * pad * 4 bytes, pad = left->n rounded up to a multiple of 4:
+ *            int32 best_r[pad] followed by float best_dist[pad] (entries >= left->n are unspecified).
+ *   stream : a cudaStream_t of the context's device the work is queued on, or NULL for the context's own stream.
+ * ASYNCHRONOUS: the call returns when the work is queued; `out` is complete once the stream has been waited for
+ * (cudaStreamSynchronize, or asdm_synchronize(ctx) when stream is NULL). The first call on a device resolves the
+ * array's device address (cudaGetSymbolAddress): make it once outside a capture. All calls share the one array, which
+ * keeps the last call's contents (the ticket is cleared on the stream before every launch): calls that overlap on the
+ * GPU -- two streams, two threads, two contexts of one device -- race on it; keep them ordered. */
+#define ASDM_STATIC_MAX_LEFT 16384
+int asdm_stereo_row_match_static(asdm_ctx* ctx, asdm_set* left, asdm_set* right, const float* scale_factors, int n_levels,
+                                 int n_rows, float min_d, float max_d, void* out, void* stream);
+
 /* ------------------------------------------------------------------ batched keyframe-pair jobs */
 /* Loop bodies of LoopClosing.cc:291-318 (kind BOW_KF_KF) and LocalMapping.cc:335-370 (kind TRIANGULATION)
  * over independent keyframe pairs (ia[p], ib[p]) drawn from n_kf keyframes. masks[k] = valid (BoW) or
