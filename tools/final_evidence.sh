@@ -6,7 +6,6 @@ out=gpurun_out
 mkdir -p $out
 python -m pytest tests -m gpu -q > $out/${tag}_pytest_gpu.txt 2>&1
 tail -1 $out/${tag}_pytest_gpu.txt
-python tests/test_threads.py > $out/${tag}_threads.txt 2>&1; tail -1 $out/${tag}_threads.txt
 make -s -C tests/cpp > /dev/null 2>&1
 for r in 1 2; do tests/cpp/test_group.bin $r 2000 24; done > $out/${tag}_cpp_group_test.txt 2>&1; tail -1 $out/${tag}_cpp_group_test.txt
 python bench.py --steps 20 --warmup 5 > $out/${tag}_bench.json 2> $out/${tag}_bench.err; echo "bench rc=$?"
