@@ -474,6 +474,9 @@ def run_ours(args):
             h_match, h_nm, shared_host = ctx.pinned((n_job_pairs, S), np.int32), ctx.pinned((job.n_units,), np.int32), False
 
         waves = [int(x) for x in args.waves.split(",")] if args.waves else None
+        if waves is None and world >= 4:  # a rank's upload share is short next to its searches: three waves measured best at 8
+            nk = len(kfs)
+            waves = sorted({max(2, int(round(nk * f))) for f in (0.375, 0.69, 1.0)})
         gsweep = G.StreamedGroupSweep(grp, pkg.ASDM_JOB_BOW_KF_KF, h_desc, kps_all, c["grid"], fv_all, g_ia, g_ib, c["nnratio"],
                                       c["check_ori"], bounds=waves)
 
@@ -686,7 +689,7 @@ def main():
                     help="weak: 512 pairs per GPU (default); strong: the same 512 pairs dealt over the GPUs")
     ap.add_argument("--pairs", type=int, default=N_PAIRS, help="keyframe pairs per step (per GPU under weak scaling)")
     ap.add_argument("--window-mb", type=int, default=3072, help="device window of the multi-GPU group per rank")
-    ap.add_argument("--waves", default="", help="e2e at N>1: keyframe bounds of the readiness waves, e.g. 16,32,48,64 (default: 6 waves)")
+    ap.add_argument("--waves", default="", help="e2e at N>1: keyframe bounds of the readiness waves, e.g. 16,32,48,64 (default: 6 waves at N=2, 3 at N>=4)")
     ap.add_argument("--gather-dist", action="store_true", help="N>1: the distance rows cross NVLink too (default: index lists + counts)")
     ap.add_argument("--no-ref", action="store_true", help="skip the whole-pair run of the reference's own matcher (about 15 s)")
     ap.add_argument("--tc-variant", type=int, default=0, help="tuning: pipeline shape of the tensor-core kernel")
