@@ -771,6 +771,7 @@ extern "C" int asdm_group_sets_create(asdm_group* g, const asdm_set_desc* descs,
 }
 
 // ------------------------------------------------------------------------------------------------ sharded jobs
+enum { GJOB_GENS = 3 };  // generations of the gathered records (see asdm_group_job_run)
 struct asdm_gjob {
   asdm_group* g = nullptr;
   int kind = 0, n_pairs = 0, n_units = 0, stride = 1, gather = 0;
@@ -781,13 +782,13 @@ struct asdm_gjob {
     int n_local = 0;
     DevBuf row_map;
     bool has_gather = false;
-    cudaEvent_t ev_bar[2] = {nullptr, nullptr};  // barrier behind the run that filled generation g has completed
-    bool bar_valid[2] = {false, false};
+    cudaEvent_t ev_bar[GJOB_GENS] = {nullptr, nullptr, nullptr};  // barrier behind the run that filled generation g has completed
+    bool bar_valid[GJOB_GENS] = {false, false, false};
   };
   std::vector<Local> loc;
-  // ASDM_GATHER_DEVICE: two generations of [rows][stride] match | dist and [units] counts at the same offset of every window
+  // ASDM_GATHER_DEVICE: GJOB_GENS generations of [rows][stride] match | dist and [units] counts at the same offset of every window
   size_t g_off = 0, g_bytes = 0, o_dist = 0, o_nm = 0, gen_bytes = 0;
-  int gen = 1;
+  int gen = GJOB_GENS - 1;
   // staging of asdm_group_job_fetch
   int32_t* st_match = nullptr;
   float* st_dist = nullptr;
@@ -870,7 +871,7 @@ extern "C" int asdm_group_job_prepare(asdm_group* g, const asdm_gjob_desc* gd, a
     j->o_dist = align_up(rows * stride * 4, 256);
     j->o_nm = j->o_dist + align_up(rows * stride * 4, 256);
     j->gen_bytes = j->o_nm + align_up((size_t)std::max(j->n_units, 1) * 4, 256);
-    j->g_bytes = 2 * j->gen_bytes;
+    j->g_bytes = GJOB_GENS * j->gen_bytes;
   }
   for (int l = 0; l < L; l++) {
     GroupMember& M = g->m[(size_t)l];
@@ -949,7 +950,7 @@ extern "C" int asdm_group_job_run(asdm_gjob* j, int32_t* h_match, float* h_dist,
   if (host && (!h_match || !h_unit_nm)) return gfail(g, ASDM_ERR_INVALID, "host results need at least the match rows and the unit counts");
   if (host && (!device_visible(h_match) || !device_visible(h_unit_nm) || (h_dist && !device_visible(h_dist))))
     return gfail(g, ASDM_ERR_INVALID, "host result arrays must be page-locked (asdm_group_host_alloc / asdm_host_alloc)");
-  j->gen ^= 1;
+  j->gen = (j->gen + 1) % GJOB_GENS;
   const bool gather = (j->gather & ASDM_GATHER_DEVICE) != 0;
   if (gather && !j->ran) {
     // The gathered records live in a range of every window that other jobs may have used before: nobody stores into a
@@ -1009,11 +1010,15 @@ extern "C" int asdm_group_job_run(asdm_gjob* j, int32_t* h_match, float* h_dist,
     pub.n = n;
     pub.dist_mask = dist_mask;
     pub.no_dist = dist_mask ? 0 : 1;
-    // This run fills generation `gen`, which the run before the previous one filled too: a peer may still be reading
-    // those rows until it has started the previous run -- i.e. until the barrier behind the previous run has completed.
-    if (gather && X.bar_valid[j->gen ^ 1]) {
+    // This run (s) fills generation `gen`, which run s-3 filled too: a peer may still be reading those rows (device code it
+    // queued behind asdm_group_job_flush) until it has started ITS run s-2 -- which it has once the barrier behind run s-2
+    // has completed here. With three generations a run therefore waits for the barrier of the run BEFORE the previous
+    // one: the exchange of run s-1 (signal, peers' arrival, wait: ~12 us of dependent launches plus the ranks' skew) is
+    // still in flight while run s computes, instead of sitting between every two runs.
+    const int g_need = (j->gen + 1) % GJOB_GENS;  // generation of run s-2
+    if (gather && X.bar_valid[g_need]) {
       GCK(cudaSetDevice(M.ctx->device));
-      GCK(cudaStreamWaitEvent(M.ctx->stream, X.ev_bar[j->gen ^ 1], 0));
+      GCK(cudaStreamWaitEvent(M.ctx->stream, X.ev_bar[g_need], 0));
     }
     int rc = job_run(job);
     if (rc) return gfail(g, rc, asdm_last_error(M.ctx));

@@ -410,7 +410,7 @@ int asdm_group_job_fetch(asdm_gjob* j, int32_t* match12, float* dist12, int32_t*
  * (match / dist: [units or pairs][stride] as above, unit_nm: [units]); complete after asdm_group_job_wait, or -- without
  * a host wait -- for work queued on the member's stream behind asdm_group_job_flush. The barrier that closes the exchange
  * of a run is queued on a stream of its own: the next run's kernels do not wait for the last rows of this one to cross
- * NVLink (two generations of arrays alternate). */
+ * NVLink (three generations of arrays alternate, so the exchange of a run overlaps the next run). */
 int asdm_group_job_gathered(asdm_gjob* j, int l, void** match, void** dist, void** unit_nm);
 int asdm_group_job_flush(asdm_gjob* j);
 int asdm_group_job_destroy(asdm_gjob* j);

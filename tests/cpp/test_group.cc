@@ -227,6 +227,53 @@ int main(int argc, char** argv) {
             snprintf(what, sizeof what, "round %d %s, records gathered on the GPU of rank %d", round, t ? "triangulation" : "loop sweep", l);
             bad += compare(what, m, ref_m[t], dd, ref_d[t], nm, ref_n[t]);
           }
+          // Pipelined runs: the gathered records rotate through three generations so that the exchange of a run overlaps
+          // the next run. Learn the three generations (one run each), poison them on every rank, queue four runs back to
+          // back without a host wait in between, then every generation on every rank must hold the reference again.
+          std::vector<std::vector<void*>> gen_m(3), gen_d(3), gen_n(3);
+          for (int k = 0; k < 3; k++) {
+            CHECK(asdm_group_job_run(job, nullptr, nullptr, nullptr));
+            CHECK(asdm_group_job_wait(job));
+            for (int l = 0; l < W; l++) {
+              void *gm = nullptr, *gdist = nullptr, *gn = nullptr;
+              CHECK(asdm_group_job_gathered(job, l, &gm, &gdist, &gn));
+              gen_m[(size_t)k].push_back(gm);
+              gen_d[(size_t)k].push_back(gdist);
+              gen_n[(size_t)k].push_back(gn);
+            }
+          }
+          if (gen_m[0][0] == gen_m[1][0] || gen_m[1][0] == gen_m[2][0] || gen_m[0][0] == gen_m[2][0]) {
+            printf("%s: the gathered records do not rotate through three generations  DIFFERENT\n", what);
+            bad++;
+          }
+          for (int k = 0; k < 3; k++)
+            for (int l = 0; l < W; l++) {
+              cudaSetDevice(devices[(size_t)l]);
+              cudaMemset(gen_m[(size_t)k][(size_t)l], 0x5a, m.size() * 4);
+              cudaMemset(gen_d[(size_t)k][(size_t)l], 0x5a, dd.size() * 4);
+              cudaMemset(gen_n[(size_t)k][(size_t)l], 0x5a, (size_t)U * 4);
+            }
+          for (int l = 0; l < W; l++) {
+            cudaSetDevice(devices[(size_t)l]);
+            cudaDeviceSynchronize();
+          }
+          for (int k = 0; k < 4; k++) CHECK(asdm_group_job_run(job, nullptr, nullptr, nullptr));
+          CHECK(asdm_group_job_wait(job));
+          for (int k = 0; k < 3; k++)
+            for (int l = 0; l < W; l++) {
+              std::vector<int32_t> un((size_t)U);
+              cudaSetDevice(devices[(size_t)l]);
+              if (cudaMemcpy(m.data(), gen_m[(size_t)k][(size_t)l], m.size() * 4, cudaMemcpyDeviceToHost) != cudaSuccess ||
+                  cudaMemcpy(dd.data(), gen_d[(size_t)k][(size_t)l], dd.size() * 4, cudaMemcpyDeviceToHost) != cudaSuccess ||
+                  cudaMemcpy(un.data(), gen_n[(size_t)k][(size_t)l], un.size() * 4, cudaMemcpyDeviceToHost) != cudaSuccess) {
+                fprintf(stderr, "cudaMemcpy of the gathered records failed\n");
+                return 2;
+              }
+              CHECK(asdm_group_job_counts(job, un.data(), nm.data()));
+              snprintf(what, sizeof what, "round %d %s, pipelined runs, generation %d on the GPU of rank %d", round,
+                       t ? "triangulation" : "loop sweep", k, l);
+              bad += compare(what, m, ref_m[t], dd, ref_d[t], nm, ref_n[t]);
+            }
           CHECK(asdm_group_host_free(g, hm));
           CHECK(asdm_group_host_free(g, hd));
           CHECK(asdm_group_host_free(g, hn));
