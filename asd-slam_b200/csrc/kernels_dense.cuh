@@ -316,7 +316,9 @@ __device__ __forceinline__ void publish_row(const PublishArgs& pub, int pair, co
   }
   if (t == 0)
     for (int p = 0; p < pub.n; p++) pub_store1(pub.nm[p] + slot, nm, mc);
-  __threadfence_system();  // the stores are on their way to the other GPUs / the host before this CTA retires
+  // No system fence here (there was one: 512 MEMBAR.SYS + ERRBAR per CTA, 8 us of a 30 us kernel). Nobody reads these rows
+  // before this KERNEL has completed: the host after a stream synchronisation, the peers behind the group barrier, whose
+  // signal is a later kernel of this stream that fences (k_group_signal) and stores with release.sys semantics.
 }
 
 __global__ void __launch_bounds__(512) k_resolve_bow_global(const PairDesc* __restrict__ pairs, BowParams P, int cap,
