@@ -129,19 +129,29 @@ __global__ void __launch_bounds__(RR_WARPS * 32, 4) k_rerank(const PairDesc* __r
   __shared__ int s_prefix[RR_MAX_SEG + 1];
   __shared__ int s_warp_tot[RR_WARPS];
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  // inclusive scan of the (clamped) segment counts, RR_WARPS * 32 at a time
-  int carry = 0;
-  for (int base = 0; base < n_seg; base += RR_WARPS * 32) {
-    const int s = base + t;
-    int v = 0;
-    if (s < n_seg) {
-      v = seg_count[s];
-      if (v > seg_cap) {
-        flags[1] = 1;
-        v = seg_cap;
+  // inclusive scan of the (clamped) segment counts in ONE pass: thread t owns `per` consecutive segments (<= 8), adds them
+  // up, the block scans the 256 partial sums (shuffles + one hop through shared memory) and the thread writes its
+  // segments' prefixes. (Round by round, 256 segments at a time, this prologue was half of the kernel's instructions on a
+  // short list -- every one of the 592 CTAs runs it.)
+  {
+    const int per = (n_seg + RR_WARPS * 32 - 1) / (RR_WARPS * 32);
+    const int s0 = t * per;
+    int v[RR_MAX_SEG / (RR_WARPS * 32)];
+    int sum = 0;
+#pragma unroll
+    for (int k = 0; k < RR_MAX_SEG / (RR_WARPS * 32); k++) {
+      v[k] = 0;
+      if (k < per && s0 + k < n_seg) {
+        int c = seg_count[s0 + k];
+        if (c > seg_cap) {
+          flags[1] = 1;
+          c = seg_cap;
+        }
+        v[k] = c;
       }
+      sum += v[k];
     }
-    int x = v;
+    int x = sum;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       const int y = __shfl_up_sync(0xffffffffu, x, o);
@@ -149,13 +159,15 @@ __global__ void __launch_bounds__(RR_WARPS * 32, 4) k_rerank(const PairDesc* __r
     }
     if (lane == 31) s_warp_tot[warp] = x;
     __syncthreads();
-    int woff = 0;
-    for (int w = 0; w < warp; w++) woff += s_warp_tot[w];
-    int tot = 0;
-    for (int w = 0; w < RR_WARPS; w++) tot += s_warp_tot[w];
-    if (s < n_seg) s_prefix[s + 1] = carry + woff + x;
-    carry += tot;
-    __syncthreads();
+    int run = x - sum;  // exclusive prefix of this thread within the block
+#pragma unroll
+    for (int w = 0; w < RR_WARPS; w++) run += w < warp ? s_warp_tot[w] : 0;
+#pragma unroll
+    for (int k = 0; k < RR_MAX_SEG / (RR_WARPS * 32); k++)
+      if (k < per && s0 + k < n_seg) {
+        run += v[k];
+        s_prefix[s0 + k + 1] = run;
+      }
   }
   if (t == 0) s_prefix[0] = 0;
   __syncthreads();

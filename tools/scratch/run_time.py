@@ -1,4 +1,4 @@
-"""ms per job run (back to back, no events between the kernels) for a sweep of P pairs, options toggled: pdl 0 / 1."""
+"""ms per job run (back to back, no events between the kernels) for a sweep of P pairs on one GPU, no exchange."""
 import importlib, sys, os, time, numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
@@ -16,8 +16,7 @@ for P in [int(x) for x in (sys.argv[1] if len(sys.argv) > 1 else "512,64").split
     job.settle()
     ref = None
     for rep in range(2):
-        for pdl in (0, 1):
-            ctx.set_option("pdl", pdl)
+        for pdl in (0,):
             for _ in range(5):
                 job.run()
             ctx.synchronize()
@@ -31,7 +30,7 @@ for P in [int(x) for x in (sys.argv[1] if len(sys.argv) > 1 else "512,64").split
             if ref is None:
                 ref = (nm.copy(), match.copy(), dist.copy())
             same = np.array_equal(nm, ref[0]) and np.array_equal(match, ref[1]) and np.array_equal(dist.view(np.uint32), ref[2].view(np.uint32))
-            print(f"pairs {P} pdl {pdl}: {ms:.4f} ms per run, same results {same}")
+            print(f"pairs {P}: {ms:.4f} ms per run, same results {same}")
     job.destroy()
     for s in sets:
         s.release()
