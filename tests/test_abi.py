@@ -52,3 +52,31 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cc", ".cpp")) or f == "Makefile":
                 txt = open(os.path.join(base, f), errors="ignore").read()
                 assert "oracle_py" not in txt and "liboracle" not in txt and "asd_oracle" not in txt, os.path.join(base, f)
+
+
+def header_prototypes():
+    """{name: number of parameters} of every function prototype in include/asdmatch.h."""
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    src = re.sub(r"typedef[^;]*\(\s*\*[^;]*;", "", src)  # function-pointer typedefs are not prototypes
+    out = {}
+    for name, args in re.findall(r"\b(asdm_[a-z0-9_]+)\s*\(([^()]*)\)\s*;", src, flags=re.S):
+        args = args.strip()
+        out[name] = 0 if args in ("", "void") else len(args.split(","))
+    return out
+
+
+def test_ctypes_argument_counts_match_the_header(pkg):
+    """A ctypes binding with one argument too few or too many corrupts the call silently: every function whose argtypes
+    the mirror sets must take as many parameters as its prototype declares."""
+    lib = pkg._lib.load()
+    protos = header_prototypes()
+    assert set(protos) == set(declared_functions())
+    checked = 0
+    for name, n in protos.items():
+        at = getattr(lib, name).argtypes
+        if at is None:
+            continue
+        assert len(at) == n, f"{name}: the header declares {n} parameters, the ctypes mirror passes {len(at)}"
+        checked += 1
+    assert checked >= 40
